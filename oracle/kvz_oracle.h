@@ -1,0 +1,153 @@
+/*
+ * oracle/kvz_oracle.h -- TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement of the Kvazaar inner-encode-loop arithmetic (SURVEY.md 8a
+ * rows A1-A17), written from the algorithm description and checked against
+ * (a) the reference's own known-answer tests (tests/sad_tests.c,
+ * tests/satd_tests.c, tests/dct_tests.c, tests/coeff_sum_tests.c) and
+ * (b) the unmodified reference compiled into oracle/_ref/libkvazaar_ref.so.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may
+ * load this library.  The product (libkvz_cuda.so) never links or calls it.
+ *
+ * Pixel-typed functions exist twice: suffix _8 (uint8_t pixels, 8-bit build
+ * of the reference) and _10 (uint16_t pixels, KVZ_BIT_DEPTH=10 build).
+ */
+#ifndef KVZ_ORACLE_H_
+#define KVZ_ORACLE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- motion-search side structures (bit-depth independent) ---- */
+
+typedef struct {
+  uint8_t dir;        /* 1 = L0, 2 = L1, 3 = bi (inter.h:36-41) */
+  uint8_t ref[2];
+  int16_t mv[2][2];   /* quarter-pel */
+} kvzo_merge_cand;
+
+typedef struct {
+  /* frame geometry */
+  int32_t width, height;          /* luma plane, stride == width */
+  /* PU */
+  int32_t origin_x, origin_y, pu_w, pu_h;
+  int32_t tile_off_x, tile_off_y;
+  /* candidates */
+  int16_t mv_cand[2][2];
+  int32_t num_merge_cand;
+  kvzo_merge_cand merge_cand[5];
+  uint8_t ref_LX[2][16];
+  int32_t ref_idx;
+  int32_t extra_mv[2];            /* quarter-pel */
+  /* config */
+  int32_t lambda_sqrt_i;          /* (int32_t)(lambda_sqrt + 0.5), search_inter.c:411 */
+  int32_t owf, wpp, sao_type, deblock_enable, mv_constraint;
+  int32_t max_ref_lcu_right, max_ref_lcu_down;
+  int32_t fme_level, me_early_termination, me_max_steps;
+  int32_t ime_algorithm;          /* enum kvz_ime_algorithm (kvazaar.h) */
+  /* in/out */
+  int32_t best_mv[2];             /* quarter-pel */
+  uint32_t best_cost, best_bitcost;
+} kvzo_me_job;
+
+enum { KVZO_IME_HEXBS = 0, KVZO_IME_TZ = 1, KVZO_IME_FULL = 2, KVZO_IME_FULL8 = 3,
+       KVZO_IME_FULL16 = 4, KVZO_IME_FULL32 = 5, KVZO_IME_FULL64 = 6, KVZO_IME_DIA = 7 };
+
+/* search_inter.c:373-412 */
+uint32_t kvzo_mvd_cost(const kvzo_me_job *j, int x, int y, int mv_shift, uint32_t *bitcost);
+/* search_inter.c:87-172 (x,y quarter-pel) */
+int kvzo_fracmv_within_tile(const kvzo_me_job *j, int x, int y);
+/* search_inter.c:326-370 with cost_out == NULL */
+int kvzo_select_mv_cand(const int16_t mv_cand[2][2], int mv_x, int mv_y);
+
+/* ---- transforms / quant (bit depth is a run-time argument) ---- */
+
+/* strategies/generic/dct-generic.c:206-617; n in {4,8,16,32}; dst4 != 0
+ * selects the 4x4 DST (strategies-dct.c:59-113) */
+void kvzo_fwd_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
+void kvzo_inv_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
+
+typedef struct {
+  int32_t qp;             /* state->qp (luma QP of the CTU) */
+  int32_t bitdepth;
+  int32_t slice_is_intra; /* frame->slicetype == KVZ_SLICE_I */
+  int32_t signhide;       /* cfg.signhide_enable */
+  int32_t cu_is_intra;    /* block_type == CU_INTRA (scaling-list class; flat lists ignore it) */
+} kvzo_q_cfg;
+
+int32_t kvzo_scaled_qp(int type, int qp, int qp_offset);     /* transform.c:129-143 */
+/* quant-generic.c:37-163, flat scaling list; type 0 luma / 2 chroma; scan_idx 0 diag 1 hor 2 ver */
+void kvzo_quant(const kvzo_q_cfg *c, const int16_t *coef, int16_t *q_coef, int width, int type, int scan_idx);
+/* quant-generic.c:279-321, flat scaling list */
+void kvzo_dequant(const kvzo_q_cfg *c, const int16_t *q_coef, int16_t *coef, int width, int type);
+uint32_t kvzo_coeff_abs_sum(const int16_t *c, uint32_t n);    /* quant-generic.c:323-330 */
+/* kvz_g_sig_last_scan[scan_idx][log2_size-1] (tables.c): position list in coding order */
+void kvzo_scan_order(int scan_idx, int log2_size, uint32_t *out);
+void kvzo_transformskip(int bitdepth, const int16_t *block, int16_t *coeff, int n);   /* transform.c:151-161 */
+void kvzo_itransformskip(int bitdepth, int16_t *block, const int16_t *coeff, int n);  /* transform.c:169-181 */
+
+/* ---- pixel-typed API, generated for SFX in {8, 10} ---- */
+#define KVZO_DECLARE(PIX, SFX) \
+  /* A1 picture-generic.c:86-99 */ \
+  unsigned kvzo_reg_sad_##SFX(const PIX *a, const PIX *b, int w, int h, unsigned sa, unsigned sb); \
+  /* A2 image.c:320-479: SAD with per-pixel coordinate clamp of the reference block */ \
+  unsigned kvzo_image_sad_##SFX(const PIX *pic, const PIX *ref, int W, int H, \
+                                int pic_x, int pic_y, int ref_x, int ref_y, int bw, int bh); \
+  /* A6 picture-generic.c:189-196,343-346,460-486 (contiguous NxN) */ \
+  unsigned kvzo_sad_nxn_##SFX(int n, const PIX *a, const PIX *b); \
+  unsigned kvzo_satd_nxn_##SFX(int n, const PIX *a, const PIX *b); \
+  /* A7 strategies-picture.h:62-100 */ \
+  unsigned kvzo_satd_any_size_##SFX(int w, int h, const PIX *a, int sa, const PIX *b, int sb); \
+  /* A7 picture-generic.c:392-456 incl. the dropped 4-wide strips */ \
+  void kvzo_satd_any_size_quad_##SFX(int w, int h, const PIX *const preds[4], int stride, \
+                                     const PIX *orig, int orig_stride, unsigned costs[4]); \
+  /* A8 image.c:488-545 */ \
+  unsigned kvzo_image_satd_##SFX(const PIX *pic, const PIX *ref, int W, int H, \
+                                 int pic_x, int pic_y, int ref_x, int ref_y, int bw, int bh); \
+  /* A16 picture-generic.c:521-536 */ \
+  unsigned kvzo_ssd_##SFX(const PIX *a, const PIX *b, int sa, int sb, int width); \
+  /* A10/A11: HEVC separable interpolation of a w x h block whose top-left integer \
+   * sample is (x0,y0) in the (clamped) reference plane, displaced by the \
+   * quarter-pel offset (qx,qy) (any integer; >>2 = whole samples). \
+   * Follows ipol-generic.c:122-157 (two passes, int16 intermediates). */ \
+  void kvzo_interp_luma_##SFX(const PIX *ref, int W, int H, int x0, int y0, int qx, int qy, \
+                              int w, int h, PIX *dst, int dst_stride); \
+  void kvzo_interp_luma14_##SFX(const PIX *ref, int W, int H, int x0, int y0, int qx, int qy, \
+                                int w, int h, int16_t *dst, int dst_stride); \
+  /* chroma: eighth-pel offset, ipol-generic.c:660-728 */ \
+  void kvzo_interp_chroma_##SFX(const PIX *ref, int W, int H, int x0, int y0, int ox, int oy, \
+                                int w, int h, PIX *dst, int dst_stride); \
+  void kvzo_interp_chroma14_##SFX(const PIX *ref, int W, int H, int x0, int y0, int ox, int oy, \
+                                  int w, int h, int16_t *dst, int dst_stride); \
+  /* the four candidate blocks one FME step emits (ipol-generic.c:192-658): \
+   * step 0 hpel hor/ver, 1 hpel diag, 2 qpel hor/ver, 3 qpel diag around the \
+   * half-pel offset (hx,hy) in {-1,0,1}; out[4][64*64], stride 64 */ \
+  void kvzo_fme_blocks_##SFX(const PIX *ref, int W, int H, int x0, int y0, int w, int h, \
+                             int step, int hx, int hy, PIX *out); \
+  /* A12 picture-generic.c:538-588 on flat arrays */ \
+  void kvzo_bipred_blend_##SFX(const int16_t *s0, const int16_t *s1, int n, PIX *dst); \
+  /* A3 integer search (search_inter.c:282-956) and search_frac (:965-1128) */ \
+  void kvzo_ime_##SFX(kvzo_me_job *j, const PIX *pic, const PIX *ref); \
+  void kvzo_fme_##SFX(kvzo_me_job *j, const PIX *pic, const PIX *ref); \
+  void kvzo_int_satd_##SFX(kvzo_me_job *j, const PIX *pic, const PIX *ref); \
+  /* A14 quant-generic.c:180-273 without RDOQ, flat lists; returns has_coeffs */ \
+  int kvzo_quantize_residual_##SFX(const kvzo_q_cfg *c, int width, int color, int scan_idx, \
+                                   int use_trskip, int in_stride, int out_stride, \
+                                   const PIX *ref_in, const PIX *pred_in, PIX *rec_out, \
+                                   int16_t *coeff_out); \
+  /* A17 intra.c:281-332 + intra-generic.c:37-189 + intra.c:195-279. \
+   * ref_top/ref_left: 2*w+1 samples, [0] = top-left corner */ \
+  void kvzo_intra_predict_##SFX(const PIX *ref_top, const PIX *ref_left, int log2_width, \
+                                int mode, int is_chroma, int filter_boundary, PIX *dst);
+
+KVZO_DECLARE(uint8_t, 8)
+KVZO_DECLARE(uint16_t, 10)
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,415 @@
+/*
+ * oracle/ref_shim.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * Compiled INTO oracle/_ref/libkvazaar_ref.so in place of the reference's
+ * src/search_inter.c: it #includes that file from where it lies under
+ * /root/reference (nothing is copied) so that the file-static search
+ * functions (check_mv_cost, search_mv_full, hexagon_search, search_frac,
+ * calc_mvd_cost ... search_inter.c:195-1128) become callable from the parity
+ * tests through plain-C wrappers.  The wrappers only build the minimal
+ * encoder_state_t / encoder_control_t the reference functions read and then
+ * call the UNMODIFIED reference code.
+ *
+ * Also wraps the strategies whose signatures take encoder_state_t*
+ * (quant / dequant / quantize_residual, strategies-quant.h:36-48) and the
+ * ipol functions (strategies-ipol.h:36-48) behind plain-pointer signatures.
+ */
+#include "search_inter.c"   /* resolved through -I$(REF)/src */
+
+#include <string.h>
+#include "strategyselector.h"
+#include "scalinglist.h"
+#include "context.h"
+#include "transform.h"
+#include "intra.h"
+#include "strategies/strategies-quant.h"
+#include "strategies/strategies-dct.h"
+#include "strategies/strategies-intra.h"
+
+/* ---- plain-C job description shared with tests (mirrored in python) ---- */
+typedef struct {
+  /* frame */
+  int32_t width, height;
+  const kvz_pixel *pic_y;     /* source luma, stride == width */
+  const kvz_pixel *ref_y;     /* reference luma, stride == width */
+  /* PU */
+  int32_t origin_x, origin_y, pu_w, pu_h;
+  int32_t tile_off_x, tile_off_y;
+  /* candidates */
+  int16_t mv_cand[2][2];
+  int32_t num_merge_cand;
+  uint8_t merge_dir[5];
+  uint8_t merge_ref[5][2];
+  int16_t merge_mv[5][2][2];
+  uint8_t ref_LX[2][16];
+  int32_t ref_idx;
+  int32_t extra_mv[2];        /* quarter-pel, as search_pu_inter_ref:1188 */
+  /* config */
+  double  lambda_sqrt;
+  int32_t owf, wpp, sao_type, deblock_enable, mv_constraint;
+  int32_t max_ref_lcu_right, max_ref_lcu_down;
+  int32_t fme_level, me_early_termination, me_max_steps;
+  int32_t ime_algorithm;      /* enum kvz_ime_algorithm */
+  /* in/out */
+  int32_t best_mv[2];         /* quarter-pel */
+  uint32_t best_cost, best_bitcost;
+} ref_me_job;
+
+typedef struct {
+  encoder_state_t state;
+  encoder_control_t ctrl;
+  encoder_state_config_frame_t frame;
+  encoder_state_config_tile_t tile;
+  videoframe_t vframe;
+  kvz_picture pic, ref;
+} fake_env;
+
+static int g_shim_init_done = 0;
+
+int ref_shim_init(int cpuid)
+{
+  /* kvazaar.c:81 -- fills the global strategy pointers */
+  int ok = kvz_strategyselector_init(cpuid, KVZ_BIT_DEPTH);
+  g_shim_init_done = ok;
+  return ok;
+}
+
+int ref_shim_bitdepth(void) { return KVZ_BIT_DEPTH; }
+
+static void env_from_job(fake_env *e, const ref_me_job *j, inter_search_info_t *info_out)
+{
+  memset(e, 0, sizeof(*e));
+  e->state.encoder_control = &e->ctrl;
+  e->state.frame = &e->frame;
+  e->state.tile = &e->tile;
+  e->state.lambda_sqrt = j->lambda_sqrt;
+  e->tile.frame = &e->vframe;
+  e->tile.offset_x = j->tile_off_x;
+  e->tile.offset_y = j->tile_off_y;
+  e->vframe.width = j->width;
+  e->vframe.height = j->height;
+  e->vframe.source = &e->pic;
+  e->pic.y = (kvz_pixel *)j->pic_y; e->pic.width = j->width; e->pic.height = j->height; e->pic.stride = j->width;
+  e->ref.y = (kvz_pixel *)j->ref_y; e->ref.width = j->width; e->ref.height = j->height; e->ref.stride = j->width;
+  memcpy(e->frame.ref_LX, j->ref_LX, sizeof(e->frame.ref_LX));
+  e->ctrl.cfg.owf = j->owf;
+  e->ctrl.cfg.wpp = j->wpp;
+  e->ctrl.cfg.sao_type = j->sao_type;
+  e->ctrl.cfg.deblock_enable = j->deblock_enable;
+  e->ctrl.cfg.mv_constraint = j->mv_constraint;
+  e->ctrl.cfg.fme_level = j->fme_level;
+  e->ctrl.cfg.me_early_termination = j->me_early_termination;
+  e->ctrl.cfg.me_max_steps = j->me_max_steps;
+  e->ctrl.cfg.ime_algorithm = j->ime_algorithm;
+  e->ctrl.cfg.mv_rdo = 0;
+  e->ctrl.max_inter_ref_lcu.right = j->max_ref_lcu_right;
+  e->ctrl.max_inter_ref_lcu.down = j->max_ref_lcu_down;
+  e->ctrl.bitdepth = KVZ_BIT_DEPTH;
+
+  inter_search_info_t info = {
+    .state = &e->state,
+    .pic = &e->pic,
+    .ref = &e->ref,
+    .ref_idx = j->ref_idx,
+    .origin = { j->origin_x, j->origin_y },
+    .width = j->pu_w,
+    .height = j->pu_h,
+    .mvd_cost_func = calc_mvd_cost,
+  };
+  memcpy(info.mv_cand, j->mv_cand, sizeof(info.mv_cand));
+  info.num_merge_cand = j->num_merge_cand;
+  for (int i = 0; i < 5; i++) {
+    info.merge_cand[i].dir = j->merge_dir[i];
+    info.merge_cand[i].ref[0] = j->merge_ref[i][0];
+    info.merge_cand[i].ref[1] = j->merge_ref[i][1];
+    memcpy(info.merge_cand[i].mv, j->merge_mv[i], sizeof(info.merge_cand[i].mv));
+  }
+  memcpy(info_out, &info, sizeof(info));
+}
+
+/* Integer motion estimation exactly as search_pu_inter_ref:1208-1239. */
+int ref_shim_ime(ref_me_job *j)
+{
+  fake_env *e = malloc(sizeof(fake_env));
+  inter_search_info_t info;
+  env_from_job(e, j, &info);
+  vector2d_t mv = { j->extra_mv[0], j->extra_mv[1] };
+  int search_range = 32;
+  switch (j->ime_algorithm) {
+    case KVZ_IME_FULL64: search_range = 64; break;
+    case KVZ_IME_FULL32: search_range = 32; break;
+    case KVZ_IME_FULL16: search_range = 16; break;
+    case KVZ_IME_FULL8:  search_range = 8;  break;
+    default: break;
+  }
+  info.best_cost = UINT32_MAX;
+  switch (j->ime_algorithm) {
+    case KVZ_IME_TZ: tz_search(&info, mv); break;
+    case KVZ_IME_FULL64: case KVZ_IME_FULL32: case KVZ_IME_FULL16:
+    case KVZ_IME_FULL8: case KVZ_IME_FULL:
+      search_mv_full(&info, search_range, mv); break;
+    case KVZ_IME_DIA: diamond_search(&info, mv, j->me_max_steps); break;
+    default: hexagon_search(&info, mv, j->me_max_steps); break;
+  }
+  j->best_mv[0] = info.best_mv.x; j->best_mv[1] = info.best_mv.y;
+  j->best_cost = info.best_cost; j->best_bitcost = info.best_bitcost;
+  free(e);
+  return 1;
+}
+
+/* Fractional refinement: search_frac (search_inter.c:965) from best_mv. */
+int ref_shim_fme(ref_me_job *j)
+{
+  fake_env *e = malloc(sizeof(fake_env));
+  inter_search_info_t info;
+  env_from_job(e, j, &info);
+  info.best_mv.x = j->best_mv[0]; info.best_mv.y = j->best_mv[1];
+  info.best_cost = j->best_cost; info.best_bitcost = j->best_bitcost;
+  search_frac(&info);
+  j->best_mv[0] = info.best_mv.x; j->best_mv[1] = info.best_mv.y;
+  j->best_cost = info.best_cost; j->best_bitcost = info.best_bitcost;
+  free(e);
+  return 1;
+}
+
+/* SATD at the integer MV: the else-branch of search_pu_inter_ref:1244-1256 */
+int ref_shim_int_satd(ref_me_job *j)
+{
+  fake_env *e = malloc(sizeof(fake_env));
+  inter_search_info_t info;
+  env_from_job(e, j, &info);
+  uint32_t c = kvz_image_calc_satd(&e->pic, &e->ref, j->origin_x, j->origin_y,
+      j->tile_off_x + j->origin_x + (j->best_mv[0] >> 2),
+      j->tile_off_y + j->origin_y + (j->best_mv[1] >> 2), j->pu_w, j->pu_h);
+  c += j->best_bitcost * (int)(j->lambda_sqrt + 0.5);
+  j->best_cost = c;
+  free(e);
+  return 1;
+}
+
+/* calc_mvd_cost (search_inter.c:373) for one mv. */
+uint32_t ref_shim_mvd_cost(ref_me_job *j, int x, int y, int mv_shift, uint32_t *bitcost)
+{
+  fake_env *e = malloc(sizeof(fake_env));
+  inter_search_info_t info;
+  env_from_job(e, j, &info);
+  uint32_t c = calc_mvd_cost(&e->state, x, y, mv_shift, info.mv_cand, info.merge_cand,
+                             info.num_merge_cand, info.ref_idx, bitcost);
+  free(e);
+  return c;
+}
+
+int ref_shim_fracmv_within_tile(ref_me_job *j, int x, int y)
+{
+  fake_env *e = malloc(sizeof(fake_env));
+  inter_search_info_t info;
+  env_from_job(e, j, &info);
+  int r = fracmv_within_tile(&info, x, y);
+  free(e);
+  return r;
+}
+
+unsigned ref_shim_image_calc_sad(const kvz_pixel *pic, const kvz_pixel *ref, int w, int h,
+                                 int pic_x, int pic_y, int ref_x, int ref_y, int bw, int bh)
+{
+  kvz_picture p = {0}, r = {0};
+  p.y = (kvz_pixel *)pic; p.width = w; p.height = h; p.stride = w;
+  r.y = (kvz_pixel *)ref; r.width = w; r.height = h; r.stride = w;
+  return kvz_image_calc_sad(&p, &r, pic_x, pic_y, ref_x, ref_y, bw, bh);
+}
+
+unsigned ref_shim_image_calc_satd(const kvz_pixel *pic, const kvz_pixel *ref, int w, int h,
+                                  int pic_x, int pic_y, int ref_x, int ref_y, int bw, int bh)
+{
+  kvz_picture p = {0}, r = {0};
+  p.y = (kvz_pixel *)pic; p.width = w; p.height = h; p.stride = w;
+  r.y = (kvz_pixel *)ref; r.width = w; r.height = h; r.stride = w;
+  return kvz_image_calc_satd(&p, &r, pic_x, pic_y, ref_x, ref_y, bw, bh);
+}
+
+/* ---- ipol wrappers (encoder argument is unused by the strategies) ---- */
+/* Runs the FME filter ladder of search_frac:1046-1060 up to and including
+ * `step`, with the given half-pel offsets for the qpel steps, on an extended
+ * block fetched like search_frac:1008.  Writes filtered[4][64*64]. */
+int ref_shim_fme_filter(const kvz_pixel *ref_y, int ref_w, int ref_h,
+                        int x, int y, int mvx, int mvy, int w, int h,
+                        int step, int fme_level, int hpel_off_x, int hpel_off_y,
+                        kvz_pixel *filtered_out /* [4][64*64] */)
+{
+  encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+  kvz_extended_block src = { 0, 0, 0, 0 };
+  kvz_pixel (*filtered)[LCU_WIDTH * LCU_WIDTH] = (void *)filtered_out;
+  int16_t (*intermediate)[(KVZ_EXT_BLOCK_W_LUMA + 1) * LCU_WIDTH] =
+      malloc(sizeof(int16_t) * 5 * (KVZ_EXT_BLOCK_W_LUMA + 1) * LCU_WIDTH);
+  int16_t hor_first_cols[5][KVZ_EXT_BLOCK_W_LUMA + 1];
+  const int iw = ((w + 7) >> 3) << 3, ih = ((h + 7) >> 3) << 3;
+  kvz_get_extended_block(x, y, mvx - 1, mvy - 1, 0, 0, (kvz_pixel *)ref_y, ref_w, ref_h,
+                         KVZ_LUMA_FILTER_TAPS, iw + 1, ih + 1, &src);
+  ipol_blocks_func *steps[4] = {
+    kvz_filter_hpel_blocks_hor_ver_luma, kvz_filter_hpel_blocks_diag_luma,
+    kvz_filter_qpel_blocks_hor_ver_luma, kvz_filter_qpel_blocks_diag_luma,
+  };
+  for (int s = 0; s <= step; s++) {
+    int ox = s >= 2 ? hpel_off_x : 0, oy = s >= 2 ? hpel_off_y : 0;
+    steps[s](ctrl, src.orig_topleft, src.stride, iw, ih, filtered, intermediate,
+             fme_level, hor_first_cols, ox, oy);
+  }
+  if (src.malloc_used) free(src.buffer);
+  free(intermediate);
+  free(ctrl);
+  return 1;
+}
+
+/* Final MC sample functions, called like inter.c:43-140 (luma) with an
+ * extended block so that edge clamping matches the encoder's use. */
+int ref_shim_mc_luma(const kvz_pixel *ref_y, int ref_w, int ref_h, int x, int y,
+                     int mvx_q, int mvy_q, int w, int h, kvz_pixel *dst, int dst_stride,
+                     int16_t *dst14 /* may be NULL */)
+{
+  encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+  kvz_extended_block src = { 0, 0, 0, 0 };
+  int16_t mv[2] = { (int16_t)mvx_q, (int16_t)mvy_q };
+  kvz_get_extended_block(x, y, mvx_q >> 2, mvy_q >> 2, 0, 0, (kvz_pixel *)ref_y, ref_w, ref_h,
+                         KVZ_LUMA_FILTER_TAPS, w, h, &src);
+  if (dst14)
+    kvz_sample_14bit_quarterpel_luma(ctrl, src.orig_topleft, src.stride, w, h, dst14, dst_stride,
+                                     mv[0] & 3, mv[1] & 3, mv);
+  else
+    kvz_sample_quarterpel_luma(ctrl, src.orig_topleft, src.stride, w, h, dst, dst_stride,
+                               mv[0] & 3, mv[1] & 3, mv);
+  if (src.malloc_used) free(src.buffer);
+  free(ctrl);
+  return 1;
+}
+
+/* chroma: x,y,w,h in chroma samples, mv in luma quarter-pel (= chroma 1/8) */
+int ref_shim_mc_chroma(const kvz_pixel *ref_c, int ref_w, int ref_h, int x, int y,
+                       int mvx_q, int mvy_q, int w, int h, kvz_pixel *dst, int dst_stride,
+                       int16_t *dst14)
+{
+  encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+  kvz_extended_block src = { 0, 0, 0, 0 };
+  int16_t mv[2] = { (int16_t)mvx_q, (int16_t)mvy_q };
+  kvz_get_extended_block(x, y, mvx_q >> 3, mvy_q >> 3, 0, 0, (kvz_pixel *)ref_c, ref_w, ref_h,
+                         KVZ_CHROMA_FILTER_TAPS, w, h, &src);
+  if (dst14)
+    kvz_sample_14bit_octpel_chroma(ctrl, src.orig_topleft, src.stride, w, h, dst14, dst_stride,
+                                   mv[0] & 7, mv[1] & 7, mv);
+  else
+    kvz_sample_octpel_chroma(ctrl, src.orig_topleft, src.stride, w, h, dst, dst_stride,
+                             mv[0] & 7, mv[1] & 7, mv);
+  if (src.malloc_used) free(src.buffer);
+  free(ctrl);
+  return 1;
+}
+
+/* ---- quant family ---- */
+typedef struct {
+  int32_t qp;            /* state->qp */
+  int32_t slice_is_intra;/* frame->slicetype == KVZ_SLICE_I */
+  int32_t signhide;      /* cfg.signhide_enable */
+  int32_t rdoq;          /* cfg.rdoq_enable */
+  int32_t rdoq_skip;
+  int32_t cu_is_intra;   /* block_type == CU_INTRA */
+  double  lambda;
+} ref_q_cfg;
+
+typedef struct {
+  encoder_state_t state;
+  encoder_control_t ctrl;
+  encoder_state_config_frame_t frame;
+} fake_qenv;
+
+static fake_qenv *qenv_make(const ref_q_cfg *c)
+{
+  fake_qenv *e = calloc(1, sizeof(*e));
+  e->state.encoder_control = &e->ctrl;
+  e->state.frame = &e->frame;
+  e->state.qp = (int8_t)c->qp;
+  e->state.lambda = c->lambda;
+  e->frame.slicetype = c->slice_is_intra ? KVZ_SLICE_I : KVZ_SLICE_P;
+  e->ctrl.bitdepth = KVZ_BIT_DEPTH;
+  e->ctrl.cfg.signhide_enable = c->signhide;
+  e->ctrl.cfg.rdoq_enable = c->rdoq;
+  e->ctrl.cfg.rdoq_skip = c->rdoq_skip;
+  kvz_scalinglist_init(&e->ctrl.scaling_list);
+  kvz_scalinglist_process(&e->ctrl.scaling_list, KVZ_BIT_DEPTH);
+  if (c->rdoq) {
+    kvz_init_contexts(&e->state, c->qp, e->frame.slicetype);
+  }
+  return e;
+}
+
+static void qenv_free(fake_qenv *e)
+{
+  kvz_scalinglist_destroy(&e->ctrl.scaling_list);
+  free(e);
+}
+
+int ref_shim_quant(const ref_q_cfg *c, coeff_t *coef, coeff_t *q_coef, int width, int type, int scan_idx)
+{
+  fake_qenv *e = qenv_make(c);
+  kvz_quant(&e->state, coef, q_coef, width, width, (int8_t)type, (int8_t)scan_idx,
+            c->cu_is_intra ? CU_INTRA : CU_INTER);
+  qenv_free(e);
+  return 1;
+}
+
+int ref_shim_dequant(const ref_q_cfg *c, coeff_t *q_coef, coeff_t *coef, int width, int type)
+{
+  fake_qenv *e = qenv_make(c);
+  kvz_dequant(&e->state, q_coef, coef, width, width, (int8_t)type,
+              c->cu_is_intra ? CU_INTRA : CU_INTER);
+  qenv_free(e);
+  return 1;
+}
+
+int ref_shim_rdoq(const ref_q_cfg *c, coeff_t *coef, coeff_t *q_coef, int width, int type,
+                  int scan_idx, int tr_depth)
+{
+  fake_qenv *e = qenv_make(c);
+  kvz_rdoq(&e->state, coef, q_coef, width, width, (int8_t)type, (int8_t)scan_idx,
+           c->cu_is_intra ? CU_INTRA : CU_INTER, (int8_t)tr_depth);
+  qenv_free(e);
+  return 1;
+}
+
+int ref_shim_quantize_residual(const ref_q_cfg *c, int width, int color, int scan_idx, int use_trskip,
+                               int in_stride, int out_stride, const kvz_pixel *ref_in,
+                               const kvz_pixel *pred_in, kvz_pixel *rec_out, coeff_t *coeff_out)
+{
+  fake_qenv *e = qenv_make(c);
+  cu_info_t cu; memset(&cu, 0, sizeof(cu));
+  cu.type = c->cu_is_intra ? CU_INTRA : CU_INTER;
+  cu.part_size = SIZE_2Nx2N;
+  int r = kvz_quantize_residual(&e->state, &cu, width, (color_t)color,
+                                (coeff_scan_order_t)scan_idx, use_trskip, in_stride, out_stride,
+                                ref_in, pred_in, rec_out, coeff_out);
+  qenv_free(e);
+  return r;
+}
+
+/* dct selector exactly as transform.c:189-215 */
+int ref_shim_transform2d(int16_t *block, int16_t *coeff, int size, int color, int cu_is_intra, int inverse)
+{
+  encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+  ctrl->bitdepth = KVZ_BIT_DEPTH;
+  if (inverse) kvz_itransform2d(ctrl, block, coeff, size, (color_t)color, cu_is_intra ? CU_INTRA : CU_INTER);
+  else         kvz_transform2d(ctrl, block, coeff, size, (color_t)color, cu_is_intra ? CU_INTRA : CU_INTER);
+  free(ctrl);
+  return 1;
+}
+
+/* ---- intra prediction: kvz_intra_predict (intra.c:281) on caller refs ---- */
+int ref_shim_intra_predict(const kvz_pixel *ref_top, const kvz_pixel *ref_left, /* 2*w+1 each, [0]=corner */
+                           int log2_width, int mode, int color, int filter_boundary, kvz_pixel *dst)
+{
+  kvz_intra_references refs;
+  memset(&refs, 0, sizeof(refs));
+  int n = 2 * (1 << log2_width) + 1;
+  memcpy(refs.ref.top, ref_top, n * sizeof(kvz_pixel));
+  memcpy(refs.ref.left, ref_left, n * sizeof(kvz_pixel));
+  refs.filtered_initialized = false;
+  kvz_intra_predict(&refs, log2_width, mode, (color_t)color, dst, filter_boundary);
+  return 1;
+}
