@@ -1,0 +1,110 @@
+/*
+ * include/kvz_cuda.h -- C ABI of libkvz_cuda.so, the B200 (sm_100a) implementation
+ * of Kvazaar's inner encode loop.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, and returns
+ * 1 on success / 0 on failure exactly like the reference's strategy registration
+ * (src/strategyselector.c:216-256); kvz_cuda_last_error() then says why.  There
+ * is NO CPU fallback: without a usable CUDA device every compute call fails.
+ *
+ * Two faces:
+ *   (1) the PER-CALL face mirrors the reference's strategy typedefs byte for byte
+ *       (host pointers in, host pointers out) so the functions can be registered
+ *       with kvz_strategyselector_register() under strategy name "cuda"
+ *       (priority 50) -- see INTEGRATION.md.  It exists for parity and for the
+ *       kernel sweep; a launch per 8x8 block is not how throughput is obtained.
+ *   (2) the BATCH face works on device-resident planes and arrays of jobs and is
+ *       what a frame-level host loop calls (suggested names of SURVEY.md 8b).
+ *
+ * kvz_pixel is uint8_t (KVZ_BIT_DEPTH 8, src/kvazaar.h:72-77); entry points that
+ * also exist for the 10-bit build carry a `bitdepth` argument and then take
+ * uint16_t samples through `const void *`.
+ */
+#ifndef KVZ_CUDA_H_
+#define KVZ_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define KVZ_CUDA_API __attribute__((visibility("default")))
+#else
+#define KVZ_CUDA_API
+#endif
+
+typedef uint8_t kvz_cuda_pixel;   /* kvz_pixel of the 8-bit build */
+
+/* ------------------------------------------------------------------ */
+/* lifecycle / plumbing                                                  */
+/* ------------------------------------------------------------------ */
+
+/* Select the device and create the library's streams and scratch buffers.
+ * Replaces nothing in the reference; called from the glue's
+ * kvz_strategy_register_*_cuda() (src/strategies/strategies-picture.c:66-88). */
+KVZ_CUDA_API int kvz_cuda_init(int device);
+KVZ_CUDA_API void kvz_cuda_shutdown(void);
+KVZ_CUDA_API const char *kvz_cuda_last_error(void);
+KVZ_CUDA_API int kvz_cuda_device_count(void);
+/* number of kernels this library has launched since init (bench.py: gpu_launches) */
+KVZ_CUDA_API unsigned long long kvz_cuda_launch_count(void);
+
+/* device memory for host languages that have no CUDA binding of their own */
+KVZ_CUDA_API void *kvz_cuda_malloc(size_t bytes);
+KVZ_CUDA_API void kvz_cuda_free(void *dptr);
+KVZ_CUDA_API void *kvz_cuda_malloc_host(size_t bytes);      /* pinned */
+KVZ_CUDA_API void kvz_cuda_free_host(void *hptr);
+KVZ_CUDA_API int kvz_cuda_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream);
+KVZ_CUDA_API int kvz_cuda_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream);
+KVZ_CUDA_API int kvz_cuda_memset(void *dst, int value, size_t bytes, void *stream);
+KVZ_CUDA_API int kvz_cuda_stream_sync(void *stream);
+
+/* ------------------------------------------------------------------ */
+/* BATCH face: reference-picture preparation                             */
+/* ------------------------------------------------------------------ */
+
+/* Border a plane with `pad` replicated samples per side: reading the border is
+ * the per-pixel coordinate clamp of image.c:320-452 / ipol-generic.c:761-781.
+ * dst holds (w+2*pad) x (h+2*pad) samples, rows dst_pitch SAMPLES apart. */
+KVZ_CUDA_API int kvz_cuda_pad_plane(const void *d_src, int w, int h, int src_pitch,
+                                    void *d_dst, int pad, int dst_pitch, int bitdepth, void *stream);
+/* border needed by kvz_cuda_ime_sad_maps() for a given search range */
+KVZ_CUDA_API int kvz_cuda_ime_required_pad(int range);
+
+/* ------------------------------------------------------------------ */
+/* BATCH face: dense integer motion estimation  (rows A1-A3)             */
+/* ------------------------------------------------------------------ */
+
+typedef struct kvz_cuda_ime_desc {
+  int32_t width, height;        /* luma size of the pictures */
+  int32_t bitdepth;             /* 8 (10: see DESIGN.md) */
+  int32_t range;                /* 8, 16, 32, 64 = --me full8..full64 (search_inter.c:1208-1215) */
+  int32_t tile_x, tile_y, tile_w, tile_h;   /* tile searched; whole frame = 0,0,width,height */
+  int32_t cur_pitch;            /* bytes per row of the current plane */
+  int32_t ref_pitch;            /* bytes per row of the padded reference plane */
+  int32_t ref_pad;              /* its border, >= kvz_cuda_ime_required_pad(range) */
+} kvz_cuda_ime_desc;
+
+/* entries per (PU, dy) row of the maps: roundup(2*range+1, 16) */
+KVZ_CUDA_API int kvz_cuda_ime_map_pitch(int range);
+/* bytes of the map of PU size 8<<level (level 0..3) for this descriptor */
+KVZ_CUDA_API size_t kvz_cuda_ime_map_bytes(const kvz_cuda_ime_desc *d, int level);
+
+/* For one (current, reference) pair: SAD of every 8x8/16x16/32x32/64x64 PU of every
+ * CTU against the edge-clamped reference at every (dx,dy) in [-range,range]^2.
+ *   map[level][ctu * n*n + py*n + px][dy+range][dx+range],  n = 8 >> level,
+ * rows map_pitch entries apart; uint16 for levels 0,1 and uint32 for 2,3.
+ * Replaces the zero-window loop of search_mv_full (search_inter.c:891-895) over
+ * check_mv_cost -> kvz_image_calc_sad -> kvz_reg_sad for ALL PUs of the frame. */
+KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,
+                                       const void *d_cur, const void *d_ref_padded,
+                                       uint16_t *d_sad8, uint16_t *d_sad16,
+                                       uint32_t *d_sad32, uint32_t *d_sad64, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KVZ_CUDA_H_ */

@@ -1,0 +1,94 @@
+"""ctypes bindings of include/kvz_cuda.h (one Python function per C entry point)."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class KvzCudaError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "libkvz_cuda.so")
+
+
+class ImeDesc(C.Structure):
+    """kvz_cuda_ime_desc"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bitdepth", C.c_int32),
+                ("range", C.c_int32),
+                ("tile_x", C.c_int32), ("tile_y", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
+                ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32)]
+
+
+# name -> (restype, argtypes); every symbol include/kvz_cuda.h declares
+_VP = C.c_void_p
+SIGNATURES = {
+    "kvz_cuda_init": (C.c_int, [C.c_int]),
+    "kvz_cuda_shutdown": (None, []),
+    "kvz_cuda_last_error": (C.c_char_p, []),
+    "kvz_cuda_device_count": (C.c_int, []),
+    "kvz_cuda_launch_count": (C.c_ulonglong, []),
+    "kvz_cuda_malloc": (_VP, [C.c_size_t]),
+    "kvz_cuda_free": (None, [_VP]),
+    "kvz_cuda_malloc_host": (_VP, [C.c_size_t]),
+    "kvz_cuda_free_host": (None, [_VP]),
+    "kvz_cuda_memcpy_h2d": (C.c_int, [_VP, _VP, C.c_size_t, _VP]),
+    "kvz_cuda_memcpy_d2h": (C.c_int, [_VP, _VP, C.c_size_t, _VP]),
+    "kvz_cuda_memset": (C.c_int, [_VP, C.c_int, C.c_size_t, _VP]),
+    "kvz_cuda_stream_sync": (C.c_int, [_VP]),
+    "kvz_cuda_pad_plane": (C.c_int, [_VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP]),
+    "kvz_cuda_ime_required_pad": (C.c_int, [C.c_int]),
+    "kvz_cuda_ime_map_pitch": (C.c_int, [C.c_int]),
+    "kvz_cuda_ime_map_bytes": (C.c_size_t, [C.POINTER(ImeDesc), C.c_int]),
+    "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+}
+
+
+def lib():
+    """Load libkvz_cuda.so (built in-tree by __graft_entry__.build())."""
+    global _LIB
+    if _LIB is None:
+        path = lib_path()
+        if not os.path.exists(path):
+            raise KvzCudaError(
+                f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)")
+        L = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def check(ok, what):
+    if not ok:
+        msg = lib().kvz_cuda_last_error()
+        raise KvzCudaError(f"{what} failed: {msg.decode() if msg else 'unknown error'}")
+
+
+_inited = None
+
+
+def init(device=0):
+    """kvz_cuda_init(); raises if no B200 is present."""
+    global _inited
+    if _inited != device:
+        check(lib().kvz_cuda_init(device), "kvz_cuda_init")
+        _inited = device
+    return device
+
+
+def launch_count():
+    return int(lib().kvz_cuda_launch_count())
+
+
+def ime_required_pad(rng):
+    return int(lib().kvz_cuda_ime_required_pad(rng))
+
+
+def ime_map_pitch(rng):
+    return int(lib().kvz_cuda_ime_map_pitch(rng))

@@ -1,0 +1,137 @@
+// kvazaar_b200/csrc/capi.cu -- extern "C" entry points of libkvz_cuda.so
+// (declared in include/kvz_cuda.h; plumbing + the batch integer-ME face).
+#include "../../include/kvz_cuda.h"
+#include "common.cuh"
+#include "ime_sad.cuh"
+
+namespace kvz {
+thread_local char g_last_error[512] = "";
+unsigned long long g_launch_count = 0;
+static int g_device = -1;
+}  // namespace kvz
+
+using namespace kvz;
+
+extern "C" {
+
+int kvz_cuda_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int kvz_cuda_init(int device)
+{
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail_msg("kvz_cuda_init: no CUDA device (this library has no CPU fallback)");
+  }
+  if (device < 0 || device >= n) return fail_msg("kvz_cuda_init: bad device index");
+  KVZ_CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  KVZ_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    snprintf(g_last_error, sizeof(g_last_error),
+             "kvz_cuda_init: device is sm_%d%d, library is built for sm_100a only", prop.major, prop.minor);
+    return 0;
+  }
+  KVZ_CUDA_TRY(cudaFree(0));
+  g_device = device;
+  return 1;
+}
+
+void kvz_cuda_shutdown(void) { g_device = -1; }
+
+const char *kvz_cuda_last_error(void) { return g_last_error; }
+
+unsigned long long kvz_cuda_launch_count(void) { return g_launch_count; }
+
+void *kvz_cuda_malloc(size_t bytes)
+{
+  void *p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) { fail("cudaMalloc", cudaGetLastError(), __FILE__, __LINE__); return nullptr; }
+  return p;
+}
+
+void kvz_cuda_free(void *dptr) { if (dptr) cudaFree(dptr); }
+
+void *kvz_cuda_malloc_host(size_t bytes)
+{
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) { fail("cudaMallocHost", cudaGetLastError(), __FILE__, __LINE__); return nullptr; }
+  return p;
+}
+
+void kvz_cuda_free_host(void *hptr) { if (hptr) cudaFreeHost(hptr); }
+
+int kvz_cuda_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream)
+{
+  KVZ_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return 1;
+}
+
+int kvz_cuda_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream)
+{
+  KVZ_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return 1;
+}
+
+int kvz_cuda_memset(void *dst, int value, size_t bytes, void *stream)
+{
+  KVZ_CUDA_TRY(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream));
+  return 1;
+}
+
+int kvz_cuda_stream_sync(void *stream)
+{
+  KVZ_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  return 1;
+}
+
+int kvz_cuda_pad_plane(const void *d_src, int w, int h, int src_pitch, void *d_dst, int pad,
+                       int dst_pitch, int bitdepth, void *stream)
+{
+  if (!d_src || !d_dst || w <= 0 || h <= 0 || pad < 0) return fail_msg("kvz_cuda_pad_plane: bad argument");
+  return launch_pad_plane(d_src, w, h, src_pitch, d_dst, pad, dst_pitch, bitdepth, (cudaStream_t)stream);
+}
+
+int kvz_cuda_ime_required_pad(int range) { return (range + 96 + 31) & ~31; }
+
+int kvz_cuda_ime_map_pitch(int range) { return ime_map_pitch(range); }
+
+size_t kvz_cuda_ime_map_bytes(const kvz_cuda_ime_desc *d, int level)
+{
+  if (!d || level < 0 || level > 3) return 0;
+  const size_t ctus = (size_t)((d->tile_w + 63) / 64) * ((d->tile_h + 63) / 64);
+  const size_t n = 8 >> level;
+  const size_t k = 2 * d->range + 1;
+  return ctus * n * n * k * ime_map_pitch(d->range) * (level < 2 ? 2 : 4);
+}
+
+int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const void *d_ref_padded,
+                          uint16_t *d_sad8, uint16_t *d_sad16, uint32_t *d_sad32, uint32_t *d_sad64,
+                          void *stream)
+{
+  if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
+    return fail_msg("kvz_cuda_ime_sad_maps: null argument");
+  if (d->bitdepth != 8) return fail_msg("kvz_cuda_ime_sad_maps: only bitdepth 8 is implemented");
+  if (d->ref_pad < kvz_cuda_ime_required_pad(d->range)) return fail_msg("kvz_cuda_ime_sad_maps: ref_pad too small");
+  if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 7) || (d->ref_pad & 7) ||
+      (d->tile_x & 63) || (d->tile_y & 63) || (d->tile_w & 7) || (d->tile_h & 7))
+    return fail_msg("kvz_cuda_ime_sad_maps: width/pitches/pad must be multiples of 8, tile origin of 64");
+  ImeSadParams p;
+  p.cur = (const uint8_t *)d_cur;
+  p.ref = (const uint8_t *)d_ref_padded;
+  p.width = d->width; p.height = d->height;
+  p.cur_pitch = d->cur_pitch; p.ref_pitch = d->ref_pitch; p.pad = d->ref_pad;
+  p.tile_x = d->tile_x; p.tile_y = d->tile_y; p.tile_w = d->tile_w; p.tile_h = d->tile_h;
+  p.ctus_x = (d->tile_w + 63) / 64; p.ctus_y = (d->tile_h + 63) / 64;
+  p.map_pitch = ime_map_pitch(d->range);
+  p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
+  return launch_ime_sad_dense(p, d->range, (cudaStream_t)stream);
+}
+
+}  // extern "C"

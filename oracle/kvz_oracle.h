@@ -139,6 +139,9 @@ void kvzo_itransformskip(int bitdepth, int16_t *block, const int16_t *coeff, int
                                    int use_trskip, int in_stride, int out_stride, \
                                    const PIX *ref_in, const PIX *pred_in, PIX *rec_out, \
                                    int16_t *coeff_out); \
+  /* test helper: SAD of one PU over the whole zero-centred window */ \
+  void kvzo_dense_sad_map_##SFX(const PIX *pic, const PIX *ref, int W, int H, int x, int y, \
+                                int bw, int bh, int r, uint32_t *out); \
   /* A17 intra.c:281-332 + intra-generic.c:37-189 + intra.c:195-279. \
    * ref_top/ref_left: 2*w+1 samples, [0] = top-left corner */ \
   void kvzo_intra_predict_##SFX(const PIX *ref_top, const PIX *ref_left, int log2_width, \

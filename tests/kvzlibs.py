@@ -200,3 +200,19 @@ def synth_luma(seed, w, h, frames, bitdepth=8, motion=(5, 3)):
         win = tex[oy:oy + h, ox:ox + w] + rng.integers(-4, 5, size=(h, w))
         out.append(np.clip(win, 0, (1 << bitdepth) - 1).astype(dt))
     return out
+
+
+def aligned(shape, dtype, align=64):
+    """numpy array whose data pointer is `align`-byte aligned (the reference's
+    AVX2 strategies use aligned loads on coefficient buffers)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    raw = np.zeros(n * dtype.itemsize + align, dtype=np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n * dtype.itemsize].view(dtype).reshape(shape)
+
+
+def aligned_copy(a, align=64):
+    out = aligned(a.shape, a.dtype, align)
+    out[...] = a
+    return out

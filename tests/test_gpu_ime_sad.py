@@ -1,0 +1,98 @@
+"""GPU parity: dense full-search SAD maps (kvz_cuda_ime_sad_maps) vs the oracle's
+kvz_image_calc_sad restatement, through the C ABI.  Bit-exact (integer work)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import kvzlibs
+from kvzlibs import ptr
+
+pytestmark = pytest.mark.gpu
+
+
+def _maps_vs_oracle(width, height, rng_, pic, ref, sample_pus=None, seed=0):
+    import torch
+    import kvazaar_b200 as kb
+    O = kvzlibs.oracle()
+    srch = kb.ImeSearch(width, height, rng_)
+    cur_d = torch.from_numpy(pic).cuda()
+    ref_d = torch.from_numpy(ref).cuda()
+    padded = kb.PaddedPlane(width, height, srch.pad).fill_from(ref_d)
+    maps = [m.cpu().numpy() for m in srch.run(cur_d, padded)]
+    torch.cuda.synchronize()
+    k = 2 * rng_ + 1
+    rs = np.random.default_rng(seed)
+    checked = 0
+    for level in range(4):
+        size = 8 << level
+        pus = [(x, y) for y in range(0, height - size + 1, size) for x in range(0, width - size + 1, size)]
+        if sample_pus is not None and len(pus) > sample_pus:
+            idx = rs.choice(len(pus), sample_pus, replace=False)
+            # always keep the corners: they exercise the edge clamp on both axes
+            pus = [pus[0], pus[-1]] + [pus[i] for i in idx]
+        for (x, y) in pus:
+            want = np.zeros(k * k, dtype=np.uint32)
+            O.kvzo_dense_sad_map_8(ptr(pic), ptr(ref), width, height, x, y, size, size, rng_, ptr(want))
+            row = srch.pu_index(level, x, y)
+            got = maps[level][row][:, :k].astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
+            assert np.array_equal(got, want.reshape(k, k)), (level, x, y)
+            checked += 1
+    return checked
+
+
+@pytest.mark.parametrize("rng_", [8, 16, 32])
+def test_small_frame_all_pus(rng_):
+    # 200x136: partial CTUs on both axes (200 = 3*64+8, 136 = 2*64+8)
+    w, h = 200, 136
+    f = kvzlibs.synth_luma(7, w, h, 2)
+    n = _maps_vs_oracle(w, h, rng_, f[1], f[0])
+    assert n > 400
+
+
+def test_white_noise_full64():
+    w, h = 128, 64
+    rs = np.random.default_rng(99)
+    pic = rs.integers(0, 256, (h, w), dtype=np.uint8)
+    ref = rs.integers(0, 256, (h, w), dtype=np.uint8)
+    _maps_vs_oracle(w, h, 64, pic, ref)
+
+
+def test_extremes_no_overflow():
+    # 0 vs 255 everywhere: SAD8 = 16320, SAD16 = 65280 (uint16 ceiling), SAD64 = 1044480
+    w, h = 64, 64
+    pic = np.zeros((h, w), dtype=np.uint8)
+    ref = np.full((h, w), 255, dtype=np.uint8)
+    _maps_vs_oracle(w, h, 8, pic, ref)
+
+
+def test_1080p_sampled_pus():
+    # BASELINE config 2 geometry; oracle on a sample of PUs (incl. the last, 56-row CTU row)
+    w, h = 1920, 1080
+    f = kvzlibs.synth_luma(2, w, h, 2)
+    _maps_vs_oracle(w, h, 32, f[1], f[0], sample_pus=24, seed=5)
+
+
+def test_hierarchy_property_1080p():
+    """Size-independent property at full size: every 16/32/64 cost is the exact sum
+    of its four children at the same displacement."""
+    import torch
+    import kvazaar_b200 as kb
+    w, h, r = 1920, 1080, 32
+    f = kvzlibs.synth_luma(3, w, h, 2)
+    srch = kb.ImeSearch(w, h, r)
+    padded = kb.PaddedPlane(w, h, srch.pad).fill_from(torch.from_numpy(f[0]).cuda())
+    maps = srch.run(torch.from_numpy(f[1]).cuda(), padded)
+    k = 2 * r + 1
+    n_ctu = srch.ctus_x * srch.ctus_y
+    # only CTUs fully inside the picture carry all four levels
+    full = [cy * srch.ctus_x + cx for cy in range(h // 64) for cx in range(w // 64)]
+    full_t = torch.tensor(full, device="cuda")
+    prev = (maps[0].view(n_ctu, 8, 8, k, -1)[full_t][..., :k].to(torch.int64) & 0xFFFF)
+    for level in range(1, 4):
+        n = 8 >> level
+        cur = maps[level].view(n_ctu, n, n, k, -1)[full_t][..., :k].to(torch.int64)
+        cur = cur & (0xFFFF if level < 2 else 0xFFFFFFFF)
+        s = prev.view(len(full), n, 2, n, 2, k, k).sum(dim=(2, 4))
+        assert torch.equal(s, cur), level
+        prev = cur
