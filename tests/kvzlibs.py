@@ -89,6 +89,7 @@ def ptr(a):
 
 _oracle = None
 _ref = None
+_ref_cpuid = None
 
 
 def build_oracle():
@@ -117,9 +118,9 @@ def have_ref():
 
 def ref(cpuid=1):
     """Load the compiled reference; cpuid=1 selects AVX2 strategies, 0 generic."""
-    global _ref
-    if _ref is None:
-        L = C.CDLL(REF_SO)
+    global _ref, _ref_cpuid
+    if _ref is None or _ref_cpuid != cpuid:
+        L = _ref if _ref is not None else C.CDLL(REF_SO)
         # strategyselector prints its report to stderr; silence it
         devnull = os.open(os.devnull, os.O_WRONLY)
         saved = os.dup(2)
@@ -135,13 +136,14 @@ def ref(cpuid=1):
             getattr(L, n).restype = C.c_uint
         L.ref_shim_mvd_cost.restype = C.c_uint32
         _ref = L
+        _ref_cpuid = cpuid
     return _ref
 
 
-def ref_strategy(name, restype, argtypes):
+def ref_strategy(name, restype, argtypes, cpuid=1):
     """Fetch one of the reference's global strategy function pointers
     (e.g. 'kvz_reg_sad', strategies-picture.c:32-63) as a callable."""
-    L = ref()
+    L = ref(cpuid)
     addr = C.c_void_p.in_dll(L, name).value
     return C.CFUNCTYPE(restype, *argtypes)(addr)
 
