@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of BASELINE.json config 2 on B200: full-search motion estimation
+of 1920x1080 8-bit frames (--me full32, -r 4: every 8x8/16x16/32x32/64x64 PU of the frame
+against 4 reference pictures, 65x65 integer candidates each).
+
+One "step" = one frame: for each of the 4 references pad the reference plane, produce the
+dense SAD maps (kvz_cuda_ime_sad_maps) and run the per-PU motion decision
+(kvz_cuda_me_search: exact search_mv_full + search_frac semantics, search_inter.c:886-1128).
+
+  value : ME Gcand/s with the planes already resident in HBM
+  e2e   : the same through the C ABI from HOST buffers (H2D of the current + reference luma
+          planes and D2H of the per-PU results inside the timed region)
+  --impl reference : the reference's own CPU code (oracle/_ref, search_mv_full +
+          search_frac through ref_shim) on all host threads, on a bounded sample of PUs.
+
+Prints ONE JSON line (contract in the task statement / DESIGN.md section Measurement).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+W, H, RANGE, NREFS = 1920, 1080, 32, 4
+PU_COUNTS = {8: 32400, 16: 8040, 32: 1980, 64: 480}       # 42900 PUs
+METRIC = "ME Gcand/s (1080p --me full32 -r 4: integer + fractional motion search, all 2Nx2N PUs 8..64)"
+UNIT = "Gcand/s"
+
+
+def cands_per_frame():
+    k = 2 * RANGE + 1
+    return sum(PU_COUNTS.values()) * k * k * NREFS
+
+
+def synth_frames(n, seed=2):
+    import kvzlibs
+    return kvzlibs.synth_luma(seed, W, H, n)
+
+
+# ----------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ----------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.samples, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        hi = sorted(sm)[len(sm) // 2:]           # upper half = samples under load
+        return {"sm_mhz": float(np.median(hi)), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+# reference arm: the reference's own CPU code on host threads
+# ----------------------------------------------------------------------------------------
+def reference_step_fn(frames, pus_per_level, threads, fme_level=4):
+    """Returns (fn, cands_per_call): fn() runs search_mv_full + search_frac of the compiled
+    reference (oracle/_ref via ref_shim, search_inter.c:886-1128) for a sample of PUs of the
+    1080p frame against NREFS references on `threads` host threads."""
+    import kvzlibs
+    from concurrent.futures import ThreadPoolExecutor
+    L = kvzlibs.ref(1)
+    cur, refs = frames[NREFS], [frames[NREFS - 1 - i] for i in range(NREFS)]
+    rs = np.random.default_rng(7)
+    jobs = []
+    for size, n in pus_per_level.items():
+        nx, ny = W // size, H // size
+        for i in rs.choice(nx * ny, n, replace=False):
+            for r in range(NREFS):
+                _, rj = kvzlibs.job_pair(
+                    width=W, height=H, origin_x=int(i % nx) * size, origin_y=int(i // nx) * size,
+                    pu_w=size, pu_h=size, tile_off_x=0, tile_off_y=0, ref_idx=r, lambda_sqrt=LAMBDA_SQRT,
+                    owf=0, wpp=0, sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu_right=1,
+                    max_ref_lcu_down=1, fme_level=fme_level, me_early_termination=0, me_max_steps=-1,
+                    ime_algorithm=5)
+                rj.pic_y, rj.ref_y = cur.ctypes.data, refs[r].ctypes.data
+                jobs.append(rj)
+    k = 2 * RANGE + 1
+
+    def one(j):
+        L.ref_shim_ime(C.byref(j))
+        if fme_level > 0:
+            L.ref_shim_fme(C.byref(j))
+
+    pool = ThreadPoolExecutor(threads)
+
+    def fn():
+        list(pool.map(one, jobs, chunksize=max(1, len(jobs) // (threads * 8))))
+    return fn, len(jobs) * k * k, f"{sum(pus_per_level.values())} PUs ({pus_per_level}) x {NREFS} refs of one 1080p frame"
+
+
+# bounded CPU sample: 1/6 of the frame's PUs at every size (same mix as the full frame)
+REF_SAMPLE = {8: 5400, 16: 1340, 32: 330, 64: 80}
+LAMBDA_SQRT = 27.0     # sqrt(lambda) of a QP-32-class frame; cost = bits * (int)(lambda_sqrt + .5)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    frames = synth_frames(NREFS + 1)
+    pus = REF_SAMPLE
+    fn, cands, sample = reference_step_fn(frames, pus, threads)
+    for _ in range(max(1, min(args.warmup, 1))):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn()
+    dt = (time.perf_counter() - t0) / args.steps
+    v = cands / dt / 1e9
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage",
+                   "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ----------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import kvazaar_b200 as kb
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback on the hot path)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    kb.init(local)
+
+    # every rank searches its own frames (same-temporal-layer frames of the GOP-8 pyramid are
+    # independent): weak scaling, no data-path collective inside the ME stage
+    frames = synth_frames(NREFS + 1, seed=2 + rank)
+    pipe = kb.MePipeline(W, H, RANGE, NREFS, lambda_sqrt=LAMBDA_SQRT, fme_level=4)
+    host_cur = torch.from_numpy(frames[NREFS]).pin_memory()
+    host_refs = [torch.from_numpy(frames[NREFS - 1 - i]).pin_memory() for i in range(NREFS)]
+    pipe.upload(host_cur, host_refs)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        pipe.step_resident()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    l0 = kb.launch_count()
+    kt0 = pipe.kernel_time_ms("sad")
+    ms = timed(pipe.step_resident, args.steps)
+    launches = kb.launch_count() - l0
+    sad_ms = (pipe.kernel_time_ms("sad") - kt0) if False else None
+    # dominant kernel timed alone with events on its own stream
+    sad_ms = pipe.time_sad_kernel(iters=max(5, args.steps))
+    clk = clocks.stop() if rank == 0 else None
+
+    # e2e through the C ABI from host buffers
+    for _ in range(2):
+        pipe.step_from_host(host_cur, host_refs)
+    ms_e2e = timed(lambda: pipe.step_from_host(host_cur, host_refs), args.steps)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    cands = cands_per_frame() * world
+    value = cands / (ms / args.steps * 1e-3) / 1e9
+    e2e = cands / (ms_e2e / args.steps * 1e-3) / 1e9
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    int_peak = kb.measure_int_pipe_peak()
+    abs_diffs = pipe.ime.algorithmic_abs_diffs()
+    map_bytes = pipe.ime.algorithmic_bytes()
+    achieved_ops = abs_diffs / (sad_ms * 1e-3)
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage: "
+                               "pad + dense SAD maps + per-PU decision + fractional refinement, "
+                               "42900 PUs x 4225 candidates x 4 refs per step",
+                   "frames_per_s": 1e3 / (ms / args.steps) * world,
+                   "l2": "inputs+outputs per step (%.0f MB of SAD maps) exceed the 126 MB L2" % (map_bytes * NREFS / 1e6),
+                   "stages": pipe.stages},
+        "clocks": clk,
+        "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "ime_sad_dense_kernel<32>", "bound": "hbm",
+                     "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                     "traffic": pipe.NCU_TRAFFIC_BYTES, "ms_per_launch": sad_ms,
+                     "algorithmic_bytes": map_bytes},
+        "roofline_int_pipe": {"kernel": "ime_sad_dense_kernel<32>", "bound": "int_pipe",
+                              "achieved": achieved_ops / 1e12, "peak": int_peak / 1e12, "unit": "Tabsdiff/s",
+                              "frac": achieved_ops / int_peak,
+                              "peak_source": "kvz_cuda_measure_int_pipe_peak (VABSDIFF4.U8.ACC register loop, measured in this run)",
+                              "algorithmic_abs_diffs": abs_diffs},
+    }
+    # bounded CPU baseline on the same host, rank 0, N=1 only
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        fn, c, sample = reference_step_fn(frames, REF_SAMPLE, threads)
+        t0 = time.perf_counter()
+        fn()
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": c / dt / 1e9, "unit": UNIT, "cores": threads, "kind": "reference",
+                               "sample": sample + f", {dt:.1f} s"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -52,6 +52,11 @@ KVZ_CUDA_API int kvz_cuda_device_count(void);
 /* number of kernels this library has launched since init (bench.py: gpu_launches) */
 KVZ_CUDA_API unsigned long long kvz_cuda_launch_count(void);
 
+/* Measured integer-pipe denominator for the SAD kernels' roofline: pixel
+ * absolute differences per second a register-only VABSDIFF4.U8.ACC loop reaches on this
+ * device.  Replaces nothing in the reference. */
+KVZ_CUDA_API int kvz_cuda_measure_int_pipe_peak(double *abs_diffs_per_s);
+
 /* device memory for host languages that have no CUDA binding of their own */
 KVZ_CUDA_API void *kvz_cuda_malloc(size_t bytes);
 KVZ_CUDA_API void kvz_cuda_free(void *dptr);

@@ -30,6 +30,7 @@ SIGNATURES = {
     "kvz_cuda_last_error": (C.c_char_p, []),
     "kvz_cuda_device_count": (C.c_int, []),
     "kvz_cuda_launch_count": (C.c_ulonglong, []),
+    "kvz_cuda_measure_int_pipe_peak": (C.c_int, [C.POINTER(C.c_double)]),
     "kvz_cuda_malloc": (_VP, [C.c_size_t]),
     "kvz_cuda_free": (None, [_VP]),
     "kvz_cuda_malloc_host": (_VP, [C.c_size_t]),
@@ -84,6 +85,13 @@ def init(device=0):
 
 def launch_count():
     return int(lib().kvz_cuda_launch_count())
+
+
+def measure_int_pipe_peak():
+    """pixel absolute differences / s of a register-only VABSDIFF4 loop on this device"""
+    v = C.c_double(0.0)
+    check(lib().kvz_cuda_measure_int_pipe_peak(C.byref(v)), "kvz_cuda_measure_int_pipe_peak")
+    return v.value
 
 
 def ime_required_pad(rng):

@@ -10,6 +10,8 @@ unsigned long long g_launch_count = 0;
 static int g_device = -1;
 }  // namespace kvz
 
+namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
+
 using namespace kvz;
 
 extern "C" {
@@ -48,6 +50,12 @@ void kvz_cuda_shutdown(void) { g_device = -1; }
 const char *kvz_cuda_last_error(void) { return g_last_error; }
 
 unsigned long long kvz_cuda_launch_count(void) { return g_launch_count; }
+
+int kvz_cuda_measure_int_pipe_peak(double *abs_diffs_per_s)
+{
+  if (!abs_diffs_per_s) return fail_msg("kvz_cuda_measure_int_pipe_peak: null argument");
+  return measure_vabsdiff4_peak(abs_diffs_per_s, 0);
+}
 
 void *kvz_cuda_malloc(size_t bytes)
 {

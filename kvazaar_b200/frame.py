@@ -88,6 +88,14 @@ class ImeSearch:
         ctu = (y // 64) * self.ctus_x + (x // 64)
         return ctu * n * n + ((y % 64) // size) * n + (x % 64) // size
 
+    def algorithmic_bytes(self):
+        """Bytes one launch must move: the four SAD maps written once (the entries that
+        exist, K x K per PU) plus the two luma planes read once."""
+        tw, th = self.tile[2], self.tile[3]
+        kk = self.k * self.k
+        pus = [(tw // (8 << l)) * (th // (8 << l)) for l in range(4)]
+        return kk * (2 * pus[0] + 2 * pus[1] + 4 * pus[2] + 4 * pus[3]) + 2 * tw * th
+
     def algorithmic_abs_diffs(self):
         """N8 * 64 * (2R+1)^2 pixel differences per launch."""
         tw, th = self.tile[2], self.tile[3]
