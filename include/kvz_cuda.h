@@ -109,6 +109,77 @@ KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,
                                        uint16_t *d_sad8, uint16_t *d_sad16,
                                        uint32_t *d_sad32, uint32_t *d_sad64, void *stream);
 
+/* ------------------------------------------------------------------ */
+/* BATCH face: per-PU motion decision  (rows A3, A4, A5, A7-A10)         */
+/* ------------------------------------------------------------------ */
+
+#define KVZ_CUDA_MAX_REFS 16      /* MAX_REF_PIC_COUNT (global.h) */
+
+/* inter_merge_cand_t (inter.h:36-41) */
+typedef struct kvz_cuda_merge_cand {
+  uint8_t dir;                  /* 1 = L0, 2 = L1, 3 = bi */
+  uint8_t ref[2];
+  uint8_t reserved;
+  int16_t mv[2][2];             /* quarter-pel */
+} kvz_cuda_merge_cand;
+
+/* one search_pu_inter() call (search_inter.c:1451-1524): a PU and its merge candidates */
+typedef struct kvz_cuda_me_pu {
+  int16_t x, y;                 /* luma origin, tile-relative (info->origin) */
+  uint8_t w, h;                 /* multiples of 8, <= 64 */
+  uint8_t num_merge_cand;
+  uint8_t num_jobs;             /* references searched: jobs[first_job .. first_job+num_jobs) in ref_idx order */
+  uint32_t first_job;
+  kvz_cuda_merge_cand merge_cand[5];
+} kvz_cuda_me_pu;
+
+/* one search_pu_inter_ref() call (search_inter.c:1134-1297) */
+typedef struct kvz_cuda_me_job {
+  int16_t mv_cand[2][2];        /* AMVP candidates for this reference (inter.c:1209) */
+  int16_t extra_mv[2];          /* colocated CU's vector in the reference (search_inter.c:1188-1206) */
+  uint8_t ref_idx;
+  uint8_t reserved[3];
+} kvz_cuda_me_job;
+
+typedef struct kvz_cuda_me_result {
+  int16_t mv[2];                /* info->best_mv, quarter-pel */
+  uint32_t cost;                /* info->best_cost */
+  uint32_t bitcost;             /* info->best_bitcost */
+  uint8_t merged, merge_idx;    /* search_inter.c:1260-1273 */
+  uint8_t mv_cand_idx;          /* select_mv_cand (search_inter.c:1277-1279) */
+  uint8_t took;                 /* 1 if this reference lowered *inter_cost (search_inter.c:1281) */
+} kvz_cuda_me_result;
+
+typedef struct kvz_cuda_me_ref {
+  const void *d_ref_padded;     /* border-replicated luma of the reference picture */
+  int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 64 (and >= kvz_cuda_ime_required_pad for the maps) */
+  const uint16_t *d_sad8, *d_sad16;   /* maps of kvz_cuda_ime_sad_maps() for (current, this reference); */
+  const uint32_t *d_sad32, *d_sad64;  /* NULL = evaluate the zero window on demand as well */
+} kvz_cuda_me_ref;
+
+typedef struct kvz_cuda_me_frame {
+  int32_t width, height, bitdepth;
+  int32_t range;                /* search_range of search_mv_full */
+  int32_t tile_x, tile_y, tile_w, tile_h;
+  const void *d_cur;            /* source luma */
+  int32_t cur_pitch;
+  int32_t lambda_sqrt_i;        /* (int32_t)(state->lambda_sqrt + 0.5), search_inter.c:411 */
+  int32_t fme_level;            /* cfg.fme_level 0..4 */
+  int32_t owf, wpp, sao_type, deblock_enable, mv_constraint;   /* inputs of fracmv_within_tile */
+  int32_t max_ref_lcu_right, max_ref_lcu_down;                 /* ctrl->max_inter_ref_lcu (encoder.c:240-241) */
+  uint8_t ref_LX[2][16];        /* state->frame->ref_LX */
+  int32_t n_refs;
+  kvz_cuda_me_ref refs[KVZ_CUDA_MAX_REFS];   /* indexed by ref_idx */
+} kvz_cuda_me_frame;
+
+/* For each PU and each of its jobs: integer full search (search_mv_full), then fractional
+ * refinement (search_frac) or SATD at the integer vector, the merge-index match and the AMVP
+ * candidate choice, with *inter_cost carried over the PU's reference loop -- the body of
+ * search_pu_inter_ref (search_inter.c:1134-1297) for all PUs of a batch at once.
+ * d_pus, d_jobs, d_results are device arrays; results[i] belongs to jobs[i]. */
+KVZ_CUDA_API int kvz_cuda_me_search(const kvz_cuda_me_frame *frame, const kvz_cuda_me_pu *d_pus, int n_pus,
+                                    const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,6 +22,27 @@ class ImeDesc(C.Structure):
                 ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32)]
 
 
+MAX_REFS = 16
+
+
+class MeRef(C.Structure):
+    """kvz_cuda_me_ref"""
+    _fields_ = [("d_ref_padded", C.c_void_p), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32),
+                ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p), ("d_sad32", C.c_void_p), ("d_sad64", C.c_void_p)]
+
+
+class MeFrame(C.Structure):
+    """kvz_cuda_me_frame"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bitdepth", C.c_int32), ("range", C.c_int32),
+                ("tile_x", C.c_int32), ("tile_y", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
+                ("d_cur", C.c_void_p), ("cur_pitch", C.c_int32), ("lambda_sqrt_i", C.c_int32),
+                ("fme_level", C.c_int32), ("owf", C.c_int32), ("wpp", C.c_int32), ("sao_type", C.c_int32),
+                ("deblock_enable", C.c_int32), ("mv_constraint", C.c_int32),
+                ("max_ref_lcu_right", C.c_int32), ("max_ref_lcu_down", C.c_int32),
+                ("ref_LX", (C.c_uint8 * 16) * 2), ("n_refs", C.c_int32),
+                ("refs", MeRef * MAX_REFS)]
+
+
 # name -> (restype, argtypes); every symbol include/kvz_cuda.h declares
 _VP = C.c_void_p
 SIGNATURES = {
@@ -44,6 +65,7 @@ SIGNATURES = {
     "kvz_cuda_ime_map_pitch": (C.c_int, [C.c_int]),
     "kvz_cuda_ime_map_bytes": (C.c_size_t, [C.POINTER(ImeDesc), C.c_int]),
     "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "kvz_cuda_me_search": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
 }
 
 

@@ -3,6 +3,7 @@
 #include "../../include/kvz_cuda.h"
 #include "common.cuh"
 #include "ime_sad.cuh"
+#include "me_search.cuh"
 
 namespace kvz {
 thread_local char g_last_error[512] = "";
@@ -140,6 +141,37 @@ int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const v
   p.map_pitch = ime_map_pitch(d->range);
   p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
   return launch_ime_sad_dense(p, d->range, (cudaStream_t)stream);
+}
+
+int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
+                       const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream)
+{
+  if (!fr || !d_pus || !d_jobs || !d_results || !fr->d_cur) return fail_msg("kvz_cuda_me_search: null argument");
+  if (fr->bitdepth != 8) return fail_msg("kvz_cuda_me_search: only bitdepth 8 is implemented");
+  if (fr->range != 8 && fr->range != 16 && fr->range != 32 && fr->range != 64)
+    return fail_msg("kvz_cuda_me_search: range must be 8, 16, 32 or 64");
+  if (fr->n_refs < 1 || fr->n_refs > KVZ_CUDA_MAX_REFS) return fail_msg("kvz_cuda_me_search: bad n_refs");
+  if (fr->fme_level < 0 || fr->fme_level > 4) return fail_msg("kvz_cuda_me_search: fme_level must be 0..4");
+  MeFrame f;
+  memset(&f, 0, sizeof(f));
+  f.cur = (const uint8_t *)fr->d_cur; f.cur_pitch = fr->cur_pitch;
+  f.width = fr->width; f.height = fr->height;
+  f.tile_x = fr->tile_x; f.tile_y = fr->tile_y; f.tile_w = fr->tile_w; f.tile_h = fr->tile_h;
+  f.ctus_x = (fr->tile_w + 63) / 64;
+  f.range = fr->range; f.map_pitch = ime_map_pitch(fr->range);
+  f.lambda_sqrt_i = fr->lambda_sqrt_i;
+  f.fme_level = fr->fme_level; f.owf = fr->owf; f.wpp = fr->wpp; f.sao_type = fr->sao_type;
+  f.deblock_enable = fr->deblock_enable; f.mv_constraint = fr->mv_constraint;
+  f.max_ref_lcu_right = fr->max_ref_lcu_right; f.max_ref_lcu_down = fr->max_ref_lcu_down;
+  f.n_refs = fr->n_refs;
+  memcpy(f.ref_LX, fr->ref_LX, sizeof(f.ref_LX));
+  for (int i = 0; i < fr->n_refs; i++) {
+    const kvz_cuda_me_ref &r = fr->refs[i];
+    if (!r.d_ref_padded || r.ref_pad < 64 || (r.ref_pitch & 3)) return fail_msg("kvz_cuda_me_search: bad reference plane");
+    f.refs[i].plane = (const uint8_t *)r.d_ref_padded; f.refs[i].pitch = r.ref_pitch; f.refs[i].pad = r.ref_pad;
+    f.refs[i].sad8 = r.d_sad8; f.refs[i].sad16 = r.d_sad16; f.refs[i].sad32 = r.d_sad32; f.refs[i].sad64 = r.d_sad64;
+  }
+  return launch_me_search(f, d_pus, d_jobs, d_results, n_pus, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,33 @@
+// kvazaar_b200/csrc/me_search.cuh -- launch interface of the per-PU motion decision kernel
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/kvz_cuda.h"
+
+namespace kvz {
+
+struct MeRef {
+  const uint8_t *plane;      // border-replicated reference luma
+  int pitch, pad;            // bytes per row, border width
+  const uint16_t *sad8, *sad16;   // dense maps of this (current, reference) pair; may be null
+  const uint32_t *sad32, *sad64;
+};
+
+struct MeFrame {
+  const uint8_t *cur;
+  int cur_pitch;
+  int width, height;
+  int tile_x, tile_y, tile_w, tile_h;
+  int ctus_x;
+  int range, map_pitch;
+  int lambda_sqrt_i;
+  int fme_level, owf, wpp, sao_type, deblock_enable, mv_constraint, max_ref_lcu_right, max_ref_lcu_down;
+  int n_refs;
+  uint8_t ref_LX[2][16];
+  MeRef refs[KVZ_CUDA_MAX_REFS];
+};
+
+int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
+                     kvz_cuda_me_result *results, int n_pus, cudaStream_t stream);
+
+}  // namespace kvz

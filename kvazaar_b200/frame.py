@@ -100,3 +100,60 @@ class ImeSearch:
         """N8 * 64 * (2R+1)^2 pixel differences per launch."""
         tw, th = self.tile[2], self.tile[3]
         return (tw // 8) * (th // 8) * 64 * self.k * self.k
+
+
+# numpy mirrors of the job structures of include/kvz_cuda.h
+import numpy as np  # noqa: E402
+
+MERGE_CAND_DT = np.dtype([("dir", "u1"), ("ref", "u1", (2,)), ("reserved", "u1"), ("mv", "<i2", (2, 2))])
+ME_PU_DT = np.dtype([("x", "<i2"), ("y", "<i2"), ("w", "u1"), ("h", "u1"), ("num_merge_cand", "u1"),
+                     ("num_jobs", "u1"), ("first_job", "<u4"), ("merge_cand", MERGE_CAND_DT, (5,))])
+ME_JOB_DT = np.dtype([("mv_cand", "<i2", (2, 2)), ("extra_mv", "<i2", (2,)), ("ref_idx", "u1"),
+                      ("reserved", "u1", (3,))])
+ME_RESULT_DT = np.dtype([("mv", "<i2", (2,)), ("cost", "<u4"), ("bitcost", "<u4"), ("merged", "u1"),
+                         ("merge_idx", "u1"), ("mv_cand_idx", "u1"), ("took", "u1")])
+assert MERGE_CAND_DT.itemsize == 12 and ME_PU_DT.itemsize == 72
+assert ME_JOB_DT.itemsize == 16 and ME_RESULT_DT.itemsize == 16
+
+
+class MeSearch:
+    """Per-PU motion decision (kvz_cuda_me_search) for one current picture against up to 16
+    references; mirrors the reference loop of search_pu_inter (search_inter.c:1451-1524)."""
+
+    def __init__(self, width, height, rng=32, fme_level=4, lambda_sqrt=27.0, tile=None, owf=0, wpp=0,
+                 sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu=(1, 1), ref_LX=None):
+        capi.init(torch.cuda.current_device())
+        fr = capi.MeFrame()
+        fr.width, fr.height, fr.bitdepth, fr.range = width, height, 8, rng
+        fr.tile_x, fr.tile_y, fr.tile_w, fr.tile_h = tile or (0, 0, width, height)
+        fr.lambda_sqrt_i = int(lambda_sqrt + 0.5)
+        fr.fme_level, fr.owf, fr.wpp, fr.sao_type = fme_level, owf, wpp, sao_type
+        fr.deblock_enable, fr.mv_constraint = deblock_enable, mv_constraint
+        fr.max_ref_lcu_right, fr.max_ref_lcu_down = max_ref_lcu
+        for l in range(2):
+            for i in range(16):
+                fr.ref_LX[l][i] = ref_LX[l][i] if ref_LX is not None else i
+        self.frame = fr
+        self._keep = []
+
+    def set_current(self, cur):
+        self.frame.d_cur = cur.data_ptr()
+        self.frame.cur_pitch = cur.stride(0) * cur.element_size()
+        self._keep.append(cur)
+
+    def set_refs(self, padded_planes, maps=None):
+        """padded_planes: list of PaddedPlane; maps: list (per ref) of the 4 map tensors or None."""
+        self.frame.n_refs = len(padded_planes)
+        for i, pp in enumerate(padded_planes):
+            r = self.frame.refs[i]
+            r.d_ref_padded, r.ref_pitch, r.ref_pad = pp.data.data_ptr(), pp.pitch_bytes, pp.pad
+            m = maps[i] if maps is not None else None
+            r.d_sad8, r.d_sad16, r.d_sad32, r.d_sad64 = [t.data_ptr() for t in m] if m is not None else [None] * 4
+        self._keep.append((padded_planes, maps))
+
+    def run(self, d_pus, n_pus, d_jobs, d_results):
+        """device tensors (uint8 views of the ME_*_DT arrays)"""
+        capi.check(capi.lib().kvz_cuda_me_search(
+            C.byref(self.frame), C.c_void_p(d_pus.data_ptr()), n_pus, C.c_void_p(d_jobs.data_ptr()),
+            C.c_void_p(d_results.data_ptr()), _stream_ptr()), "kvz_cuda_me_search")
+        return d_results

@@ -1,0 +1,62 @@
+"""GPU parity: kvz_cuda_me_search (integer full search + fractional refinement + merge/AMVP
+bookkeeping, search_inter.c:886-1297) against the oracle, through the C ABI.  Bit-exact."""
+import numpy as np
+import pytest
+
+import kvzlibs
+import me_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 16, 32, 64), **cfg):
+    rs = np.random.default_rng(seed)
+    f = kvzlibs.synth_luma(seed, width, height, n_refs + 1)
+    cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
+    pus, jobs = me_oracle.random_pus(rs, width, height, n_refs, count, sizes=sizes, mv_span=rng)
+    lam = int(rs.integers(3, 45))
+    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps, **cfg)
+    want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, fme, lam, **cfg)
+    me_oracle.assert_results_equal(got, want, pus)
+    return got
+
+
+@pytest.mark.parametrize("fme", [0, 1, 2, 3, 4])
+def test_small_frame_range8(fme):
+    _run(200, 136, 8, fme, 2, 60, 100 + fme)
+
+
+def test_range16_three_refs():
+    got = _run(256, 192, 16, 4, 3, 48, 7)
+    assert got["took"].reshape(-1, 3)[:, 0].all()        # the first reference always lowers MAX_INT
+
+
+def test_owf_wpp_restriction():
+    _run(256, 192, 16, 4, 2, 48, 8, owf=1, wpp=1)
+    _run(256, 192, 8, 2, 2, 32, 9, owf=1, wpp=1, sao_type=0)
+
+
+def test_mv_constraint_frame_and_tile_margin():
+    _run(200, 136, 8, 4, 2, 40, 10, mv_constraint=4)
+    _run(200, 136, 8, 4, 1, 24, 11, mv_constraint=1)
+
+
+def test_without_dense_maps():
+    # zero window evaluated on demand as well (what non-2Nx2N PUs use)
+    _run(200, 136, 8, 4, 2, 24, 12, use_maps=False)
+
+
+def test_white_noise():
+    rs = np.random.default_rng(99)
+    w, h, n_refs, rng = 192, 128, 2, 16
+    cur = rs.integers(0, 256, (h, w), dtype=np.uint8)
+    refs = [rs.integers(0, 256, (h, w), dtype=np.uint8) for _ in range(n_refs)]
+    pus, jobs = me_oracle.random_pus(rs, w, h, n_refs, 40, mv_span=rng)
+    got = me_oracle.gpu_search(pus, jobs, cur, refs, w, h, rng, 4, 20)
+    want = me_oracle.oracle_search(pus, jobs, cur, refs, w, h, rng, 4, 20)
+    me_oracle.assert_results_equal(got, want, pus)
+
+
+def test_1080p_full32_sampled():
+    # BASELINE config 2 geometry; oracle on a sample of PUs
+    _run(1920, 1080, 32, 4, 2, 24, 13)
