@@ -103,39 +103,59 @@ class Clocks:
 # reference arm: the reference's own CPU code on host threads
 # ----------------------------------------------------------------------------------------
 def reference_step_fn(frames, pus_per_level, threads, fme_level=4):
-    """Returns (fn, cands_per_call): fn() runs search_mv_full + search_frac of the compiled
-    reference (oracle/_ref via ref_shim, search_inter.c:886-1128) for a sample of PUs of the
-    1080p frame against NREFS references on `threads` host threads."""
+    """Returns (fn, cands_per_call, description): fn() runs search_mv_full + search_frac of the
+    compiled reference (oracle/_ref via ref_shim, search_inter.c:886-1128) for a sample of the
+    frame's PUs -- same candidates as the GPU arm (kvazaar_b200.pipeline.frame_pus) -- against
+    NREFS references on `threads` host threads, carrying *inter_cost over each PU's reference
+    loop like search_pu_inter (search_inter.c:1505-1511)."""
     import kvzlibs
     from concurrent.futures import ThreadPoolExecutor
+    from kvazaar_b200.pipeline import frame_pus
     L = kvzlibs.ref(1)
     cur, refs = frames[NREFS], [frames[NREFS - 1 - i] for i in range(NREFS)]
+    pus, jobs = frame_pus(W, H, NREFS)
     rs = np.random.default_rng(7)
-    jobs = []
+    chosen = []
     for size, n in pus_per_level.items():
-        nx, ny = W // size, H // size
-        for i in rs.choice(nx * ny, n, replace=False):
-            for r in range(NREFS):
-                _, rj = kvzlibs.job_pair(
-                    width=W, height=H, origin_x=int(i % nx) * size, origin_y=int(i // nx) * size,
-                    pu_w=size, pu_h=size, tile_off_x=0, tile_off_y=0, ref_idx=r, lambda_sqrt=LAMBDA_SQRT,
-                    owf=0, wpp=0, sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu_right=1,
-                    max_ref_lcu_down=1, fme_level=fme_level, me_early_termination=0, me_max_steps=-1,
-                    ime_algorithm=5)
-                rj.pic_y, rj.ref_y = cur.ctypes.data, refs[r].ctypes.data
-                jobs.append(rj)
+        idx = np.nonzero(pus["w"] == size)[0]
+        chosen.extend(rs.choice(idx, n, replace=False).tolist())
+    work = []
+    for pi in chosen:
+        pu = pus[pi]
+        per_ref = []
+        for q in range(NREFS):
+            jb = jobs[int(pu["first_job"]) + q]
+            merge = [(int(m["dir"]), int(m["ref"][0]), int(m["ref"][1]), int(m["mv"][0][0]), int(m["mv"][0][1]),
+                      int(m["mv"][1][0]), int(m["mv"][1][1])) for m in pu["merge_cand"][:int(pu["num_merge_cand"])]]
+            _, rj = kvzlibs.job_pair(
+                width=W, height=H, origin_x=int(pu["x"]), origin_y=int(pu["y"]), pu_w=int(pu["w"]), pu_h=int(pu["h"]),
+                tile_off_x=0, tile_off_y=0, ref_idx=int(jb["ref_idx"]), lambda_sqrt=LAMBDA_SQRT,
+                mv_cand=jb["mv_cand"].tolist(), merge=merge, extra_mv=tuple(int(v) for v in jb["extra_mv"]),
+                owf=0, wpp=0, sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu_right=1,
+                max_ref_lcu_down=1, fme_level=fme_level, me_early_termination=0, me_max_steps=-1,
+                ime_algorithm=5)
+            rj.pic_y, rj.ref_y = cur.ctypes.data, refs[q].ctypes.data
+            per_ref.append(rj)
+        work.append(per_ref)
     k = 2 * RANGE + 1
 
-    def one(j):
-        L.ref_shim_ime(C.byref(j))
-        if fme_level > 0:
-            L.ref_shim_fme(C.byref(j))
+    def one(per_ref):
+        inter_cost = 0x7FFFFFFF
+        for j in per_ref:
+            L.ref_shim_ime(C.byref(j))
+            if fme_level > 0 and j.best_cost < inter_cost:
+                L.ref_shim_fme(C.byref(j))
+            elif j.best_cost < 0xFFFFFFFF:
+                L.ref_shim_int_satd(C.byref(j))
+            if j.best_cost < inter_cost:
+                inter_cost = j.best_cost
 
     pool = ThreadPoolExecutor(threads)
 
     def fn():
-        list(pool.map(one, jobs, chunksize=max(1, len(jobs) // (threads * 8))))
-    return fn, len(jobs) * k * k, f"{sum(pus_per_level.values())} PUs ({pus_per_level}) x {NREFS} refs of one 1080p frame"
+        list(pool.map(one, work))
+    desc = f"{sum(pus_per_level.values())} PUs ({pus_per_level}) x {NREFS} refs of one 1080p frame"
+    return fn, len(work) * NREFS * k * k, desc
 
 
 # bounded CPU sample: 1/6 of the frame's PUs at every size (same mix as the full frame)
@@ -213,24 +233,31 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    for _ in range(max(args.warmup, 3)):
-        pipe.step_resident()
     clocks = Clocks(local)
     if rank == 0:
         clocks.start()
+    for _ in range(max(args.warmup, 3)):
+        pipe.step_resident()
     l0 = kb.launch_count()
-    kt0 = pipe.kernel_time_ms("sad")
     ms = timed(pipe.step_resident, args.steps)
     launches = kb.launch_count() - l0
-    sad_ms = (pipe.kernel_time_ms("sad") - kt0) if False else None
-    # dominant kernel timed alone with events on its own stream
-    sad_ms = pipe.time_sad_kernel(iters=max(5, args.steps))
-    clk = clocks.stop() if rank == 0 else None
 
     # e2e through the C ABI from host buffers
     for _ in range(2):
         pipe.step_from_host(host_cur, host_refs)
     ms_e2e = timed(lambda: pipe.step_from_host(host_cur, host_refs), args.steps)
+
+    # per-kernel times, each kernel alone with events on the launching stream
+    sad_ms = pipe.time_sad_kernel(iters=max(5, args.steps))
+    search_ms = pipe.time_me_search(iters=max(3, args.steps // 2))
+    # keep the same load up for >= 1.5 s so that nvidia-smi (100 ms period) sees it
+    t_end = time.perf_counter() + 1.5
+    while time.perf_counter() < t_end:
+        pipe.step_resident()
+        torch.cuda.synchronize()
+    clk = clocks.stop() if rank == 0 else None
+    if clk is not None:
+        clk["note"] = "sampled every 100 ms from warm-up to the end of 1.5 s of identical untimed steps"
 
     if rank != 0:
         if world > 1:
@@ -249,31 +276,37 @@ def run_ours(args):
     abs_diffs = pipe.ime.algorithmic_abs_diffs()
     map_bytes = pipe.ime.algorithmic_bytes()
     achieved_ops = abs_diffs / (sad_ms * 1e-3)
+    step_ms = ms / args.steps
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage: "
-                               "pad + dense SAD maps + per-PU decision + fractional refinement, "
-                               "42900 PUs x 4225 candidates x 4 refs per step",
-                   "frames_per_s": 1e3 / (ms / args.steps) * world,
-                   "l2": "inputs+outputs per step (%.0f MB of SAD maps) exceed the 126 MB L2" % (map_bytes * NREFS / 1e6),
-                   "stages": pipe.stages},
+                               "pad + dense SAD maps + per-PU decision (search_mv_full) + fractional "
+                               "refinement (search_frac), 42900 PUs x 4225 candidates x 4 refs per step",
+                   "frames_per_s": 1e3 / step_ms * world,
+                   "l2": "per step %.0f MB of SAD maps are written and read back: larger than the 126 MB L2, "
+                         "no flush needed" % (map_bytes * NREFS / 1e6),
+                   "stages": pipe.stages,
+                   "kernel_ms": {"ime_sad_dense x1": sad_ms, "me_search x1": search_ms,
+                                 "share_sad": NREFS * sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
         "clocks": clk,
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes},
         "gpu_launches": int(launches),
-        "roofline": {"kernel": "ime_sad_dense_kernel<32>", "bound": "hbm",
-                     "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                     "traffic": pipe.NCU_TRAFFIC_BYTES, "ms_per_launch": sad_ms,
-                     "algorithmic_bytes": map_bytes},
-        "roofline_int_pipe": {"kernel": "ime_sad_dense_kernel<32>", "bound": "int_pipe",
-                              "achieved": achieved_ops / 1e12, "peak": int_peak / 1e12, "unit": "Tabsdiff/s",
-                              "frac": achieved_ops / int_peak,
-                              "peak_source": "kvz_cuda_measure_int_pipe_peak (VABSDIFF4.U8.ACC register loop, measured in this run)",
-                              "algorithmic_abs_diffs": abs_diffs},
+        # the dense SAD kernel is bound by the integer (ALU) pipe; the denominator is
+        # measured in this run by a register-only VABSDIFF4 loop (MEASURED_PEAKS.json has no integer figure)
+        "roofline": {"kernel": "ime_sad_dense_kernel<32>", "bound": "int_pipe",
+                     "achieved": achieved_ops / 1e12, "peak": int_peak / 1e12, "unit": "Tabsdiff/s",
+                     "frac": achieved_ops / int_peak,
+                     "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",
+                     "algorithmic_abs_diffs": abs_diffs, "ms_per_launch": sad_ms,
+                     "traffic": pipe.NCU_TRAFFIC_BYTES},
+        "roofline_hbm": {"kernel": "ime_sad_dense_kernel<32>", "bound": "hbm",
+                         "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "traffic": pipe.NCU_TRAFFIC_BYTES, "algorithmic_bytes": map_bytes},
     }
     # bounded CPU baseline on the same host, rank 0, N=1 only
     if world == 1 and not args.no_cpu_baseline:

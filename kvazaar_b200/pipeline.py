@@ -7,16 +7,50 @@ torch supplies device memory, pinned host buffers, streams and events only.
 """
 import ctypes as C
 
+import numpy as np
 import torch
 
 from . import capi
-from .frame import ImeSearch, PaddedPlane
+from .frame import ME_JOB_DT, ME_PU_DT, ME_RESULT_DT, ImeSearch, MeSearch, PaddedPlane
+
+
+def frame_pus(width, height, n_refs, true_mv_px=(5, 3), sizes=(64, 32, 16, 8)):
+    """Every 2Nx2N PU (64..8) fully inside the picture, largest first, with the candidates a
+    steady-state encode of a globally translating clip produces: merge candidate 0 and AMVP
+    candidate 0 are the neighbours' vector (the true motion towards that reference), merge
+    candidate 1 / AMVP candidate 1 the zero vector, and extra_mv the colocated CU's vector
+    (search_inter.c:1188-1206).  true_mv_px is the motion per frame of temporal distance."""
+    n = sum((width // s) * (height // s) for s in sizes)
+    pus = np.zeros(n, ME_PU_DT)
+    jobs = np.zeros(n * n_refs, ME_JOB_DT)
+    i = 0
+    for s in sizes:
+        ys, xs = np.meshgrid(np.arange(height // s) * s, np.arange(width // s) * s, indexing="ij")
+        m = xs.size
+        pus["x"][i:i + m], pus["y"][i:i + m] = xs.ravel(), ys.ravel()
+        pus["w"][i:i + m] = pus["h"][i:i + m] = s
+        i += m
+    pus["num_merge_cand"] = 2
+    pus["num_jobs"] = n_refs
+    pus["first_job"] = np.arange(n, dtype=np.uint32) * n_refs
+    pus["merge_cand"]["dir"][:, 0] = 1
+    pus["merge_cand"]["mv"][:, 0, 0, 0] = true_mv_px[0] * 4
+    pus["merge_cand"]["mv"][:, 0, 0, 1] = true_mv_px[1] * 4
+    pus["merge_cand"]["dir"][:, 1] = 1
+    j = jobs.reshape(n, n_refs)
+    for r in range(n_refs):
+        j["ref_idx"][:, r] = r
+        j["mv_cand"][:, r, 0, 0] = true_mv_px[0] * 4 * (r + 1)
+        j["mv_cand"][:, r, 0, 1] = true_mv_px[1] * 4 * (r + 1)
+        j["extra_mv"][:, r, 0] = true_mv_px[0] * 4 * (r + 1)
+        j["extra_mv"][:, r, 1] = true_mv_px[1] * 4 * (r + 1)
+    return pus, jobs
 
 
 class MePipeline:
     # dram__bytes_read.sum + dram__bytes_write.sum of one ime_sad_dense_kernel<32> launch at
     # 1080p from profiles/ (ncu --set full); None until a capture has been taken
-    NCU_TRAFFIC_BYTES = None
+    NCU_TRAFFIC_BYTES = 484260096   # r01a capture: 67.98 MB read + 416.28 MB written
 
     def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda"):
         capi.init(torch.cuda.current_device())
@@ -26,10 +60,22 @@ class MePipeline:
         self.cur = torch.empty((height, width), dtype=torch.uint8, device=device)
         self.refs = [torch.empty((height, width), dtype=torch.uint8, device=device) for _ in range(n_refs)]
         self.padded = [PaddedPlane(width, height, self.ime.pad, device=device) for _ in range(n_refs)]
-        self.stages = ["pad_plane", "ime_sad_maps"]
-        self.h2d_bytes = (1 + n_refs) * width * height
-        self.d2h_bytes = 0
-        self._result_host = None
+        self.maps = [[torch.empty_like(m) for m in self.ime.maps] for _ in range(n_refs)]
+        self.search = MeSearch(width, height, rng, fme_level=fme_level, lambda_sqrt=lambda_sqrt)
+        self.search.set_current(self.cur)
+        self.search.set_refs(self.padded, self.maps)
+        self.stages = ["pad_plane x%d" % n_refs, "ime_sad_maps x%d" % n_refs, "me_search (IME decision + FME) x1"]
+        # PUs / jobs of the frame (host, pinned) and their device copies
+        pus, jobs = frame_pus(width, height, n_refs)
+        self.n_pus, self.n_jobs = len(pus), len(jobs)
+        self.host_pus = torch.from_numpy(pus.view(np.uint8).reshape(-1)).pin_memory()
+        self.host_jobs = torch.from_numpy(jobs.view(np.uint8).reshape(-1)).pin_memory()
+        self.d_pus = self.host_pus.to(device)
+        self.d_jobs = self.host_jobs.to(device)
+        self.d_results = torch.zeros(self.n_jobs * ME_RESULT_DT.itemsize, dtype=torch.uint8, device=device)
+        self.host_results = torch.zeros(self.n_jobs * ME_RESULT_DT.itemsize, dtype=torch.uint8).pin_memory()
+        self.h2d_bytes = (1 + n_refs) * width * height + self.host_pus.numel() + self.host_jobs.numel()
+        self.d2h_bytes = self.host_results.numel()
 
     # ---- data movement ----
     def upload(self, host_cur, host_refs):
@@ -41,19 +87,35 @@ class MePipeline:
     def step_resident(self):
         for r in range(self.n_refs):
             self.padded[r].fill_from(self.refs[r])
+            self.ime.maps = self.maps[r]
             self.ime.run(self.cur, self.padded[r])
-            self._decide(r)
+        self.search.run(self.d_pus, self.n_pus, self.d_jobs, self.d_results)
 
     def step_from_host(self, host_cur, host_refs):
         self.upload(host_cur, host_refs)
+        self.d_pus.copy_(self.host_pus, non_blocking=True)
+        self.d_jobs.copy_(self.host_jobs, non_blocking=True)
         self.step_resident()
-        self._download()
-
-    def _decide(self, r):
-        pass
-
-    def _download(self):
+        self.host_results.copy_(self.d_results, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+
+    def results(self):
+        """kvz_cuda_me_result per job, as a numpy structured array (after step_from_host)"""
+        return self.host_results.numpy().view(ME_RESULT_DT)
+
+    def time_stage(self, fn, iters=5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    def time_me_search(self, iters=5):
+        return self.time_stage(lambda: self.search.run(self.d_pus, self.n_pus, self.d_jobs, self.d_results), iters)
 
     # ---- dominant kernel alone ----
     def time_sad_kernel(self, iters=10):
