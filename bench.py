@@ -289,7 +289,7 @@ def run_ours(args):
                          "no flush needed" % (map_bytes * NREFS / 1e6),
                    "stages": pipe.stages,
                    "kernel_ms": {"ime_sad_dense x1": sad_ms, "me_search x1": search_ms,
-                                 "share_sad": NREFS * sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
+                                 "sad_launches_per_step": pipe.n_sad_launches, "share_sad": pipe.n_sad_launches * sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
         "clocks": clk,
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes},

@@ -90,7 +90,10 @@ typedef struct kvz_cuda_ime_desc {
   int32_t tile_x, tile_y, tile_w, tile_h;   /* tile searched; whole frame = 0,0,width,height */
   int32_t cur_pitch;            /* bytes per row of the current plane */
   int32_t ref_pitch;            /* bytes per row of the padded reference plane */
-  int32_t ref_pad;              /* its border, >= kvz_cuda_ime_required_pad(range) */
+  int32_t ref_pad;              /* its border, >= kvz_cuda_ime_required_pad(range) + max(|center_x|, |center_y|) */
+  int32_t center_x, center_y;   /* window centre in whole samples (any integers):
+                                   0,0 = the zero window of search_mv_full (search_inter.c:891-895); another
+                                   centre = the window round extra_mv / a merge candidate (search_inter.c:898-955) */
 } kvz_cuda_ime_desc;
 
 /* entries per (PU, dy) row of the maps: roundup(2*range+1, 16) */
@@ -150,11 +153,21 @@ typedef struct kvz_cuda_me_result {
   uint8_t took;                 /* 1 if this reference lowered *inter_cost (search_inter.c:1281) */
 } kvz_cuda_me_result;
 
+#define KVZ_CUDA_MAX_MAPSETS 4
+
+/* one result of kvz_cuda_ime_sad_maps() for (current, this reference) and the window centre it was made for */
+typedef struct kvz_cuda_me_mapset {
+  int32_t center_x, center_y;
+  const uint16_t *d_sad8, *d_sad16;
+  const uint32_t *d_sad32, *d_sad64;
+} kvz_cuda_me_mapset;
+
 typedef struct kvz_cuda_me_ref {
   const void *d_ref_padded;     /* border-replicated luma of the reference picture */
-  int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 64 (and >= kvz_cuda_ime_required_pad for the maps) */
-  const uint16_t *d_sad8, *d_sad16;   /* maps of kvz_cuda_ime_sad_maps() for (current, this reference); */
-  const uint32_t *d_sad32, *d_sad64;  /* NULL = evaluate the zero window on demand as well */
+  int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 64 (and what the maps needed) */
+  int32_t n_mapsets;            /* windows of search_mv_full whose centre matches a map set are read from it, */
+  int32_t reserved;             /* every other window is evaluated on demand (0 sets = everything on demand) */
+  kvz_cuda_me_mapset mapsets[KVZ_CUDA_MAX_MAPSETS];
 } kvz_cuda_me_ref;
 
 typedef struct kvz_cuda_me_frame {

@@ -19,16 +19,26 @@ class ImeDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bitdepth", C.c_int32),
                 ("range", C.c_int32),
                 ("tile_x", C.c_int32), ("tile_y", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
-                ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32)]
+                ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32),
+                ("center_x", C.c_int32), ("center_y", C.c_int32)]
 
 
 MAX_REFS = 16
 
 
+MAX_MAPSETS = 4
+
+
+class MeMapSet(C.Structure):
+    """kvz_cuda_me_mapset"""
+    _fields_ = [("center_x", C.c_int32), ("center_y", C.c_int32),
+                ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p), ("d_sad32", C.c_void_p), ("d_sad64", C.c_void_p)]
+
+
 class MeRef(C.Structure):
     """kvz_cuda_me_ref"""
     _fields_ = [("d_ref_padded", C.c_void_p), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32),
-                ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p), ("d_sad32", C.c_void_p), ("d_sad64", C.c_void_p)]
+                ("n_mapsets", C.c_int32), ("reserved", C.c_int32), ("mapsets", MeMapSet * MAX_MAPSETS)]
 
 
 class MeFrame(C.Structure):

@@ -127,8 +127,11 @@ int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const v
   if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
     return fail_msg("kvz_cuda_ime_sad_maps: null argument");
   if (d->bitdepth != 8) return fail_msg("kvz_cuda_ime_sad_maps: only bitdepth 8 is implemented");
-  if (d->ref_pad < kvz_cuda_ime_required_pad(d->range)) return fail_msg("kvz_cuda_ime_sad_maps: ref_pad too small");
-  if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 7) || (d->ref_pad & 7) ||
+  {
+    const int ac = abs(d->center_x) > abs(d->center_y) ? abs(d->center_x) : abs(d->center_y);
+    if (d->ref_pad < kvz_cuda_ime_required_pad(d->range) + ac) return fail_msg("kvz_cuda_ime_sad_maps: ref_pad too small for this range and centre");
+  }
+  if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 3) || (d->ref_pad & 3) ||
       (d->tile_x & 63) || (d->tile_y & 63) || (d->tile_w & 7) || (d->tile_h & 7))
     return fail_msg("kvz_cuda_ime_sad_maps: width/pitches/pad must be multiples of 8, tile origin of 64");
   ImeSadParams p;
@@ -138,6 +141,7 @@ int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const v
   p.cur_pitch = d->cur_pitch; p.ref_pitch = d->ref_pitch; p.pad = d->ref_pad;
   p.tile_x = d->tile_x; p.tile_y = d->tile_y; p.tile_w = d->tile_w; p.tile_h = d->tile_h;
   p.ctus_x = (d->tile_w + 63) / 64; p.ctus_y = (d->tile_h + 63) / 64;
+  p.center_x = d->center_x; p.center_y = d->center_y;
   p.map_pitch = ime_map_pitch(d->range);
   p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
   return launch_ime_sad_dense(p, d->range, (cudaStream_t)stream);
@@ -169,7 +173,13 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
     const kvz_cuda_me_ref &r = fr->refs[i];
     if (!r.d_ref_padded || r.ref_pad < 64 || (r.ref_pitch & 3)) return fail_msg("kvz_cuda_me_search: bad reference plane");
     f.refs[i].plane = (const uint8_t *)r.d_ref_padded; f.refs[i].pitch = r.ref_pitch; f.refs[i].pad = r.ref_pad;
-    f.refs[i].sad8 = r.d_sad8; f.refs[i].sad16 = r.d_sad16; f.refs[i].sad32 = r.d_sad32; f.refs[i].sad64 = r.d_sad64;
+    if (r.n_mapsets < 0 || r.n_mapsets > KVZ_CUDA_MAX_MAPSETS) return fail_msg("kvz_cuda_me_search: bad n_mapsets");
+    f.refs[i].n_sets = r.n_mapsets;
+    for (int m = 0; m < r.n_mapsets; m++) {
+      f.refs[i].sets[m].cx = r.mapsets[m].center_x; f.refs[i].sets[m].cy = r.mapsets[m].center_y;
+      f.refs[i].sets[m].sad8 = r.mapsets[m].d_sad8; f.refs[i].sets[m].sad16 = r.mapsets[m].d_sad16;
+      f.refs[i].sets[m].sad32 = r.mapsets[m].d_sad32; f.refs[i].sets[m].sad64 = r.mapsets[m].d_sad64;
+    }
   }
   return launch_me_search(f, d_pus, d_jobs, d_results, n_pus, (cudaStream_t)stream);
 }

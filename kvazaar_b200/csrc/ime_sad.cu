@@ -74,12 +74,18 @@ ime_sad_dense_kernel(ImeSadParams p)
   // ---- stage the reference tile: rows ctu_y-R .. ctu_y+R+63, 80 bytes from
   //      column ctu_x - R + 16*chunk of the border-replicated plane ----
   {
-    const uint8_t *src = p.ref + (size_t)(ctu_y - R + p.pad) * p.ref_pitch + (ctu_x - R + kChunkDx * chunk + p.pad);
+    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x - R + kChunkDx * chunk + p.pad);
     constexpr int kVecPerRow = kTilePitch / 8;
+    // the window centre makes the source address arbitrary: fetch aligned words and realign
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
+    const int sh = (int)(a0 & 3) * 8;
+    const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
     for (int i = tid; i < Smem<R>::kRows * kVecPerRow; i += kThreads) {
       const int r = i / kVecPerRow, v = i % kVecPerRow;
-      const uint2 val = *reinterpret_cast<const uint2 *>(src + (size_t)r * p.ref_pitch + v * 8);
-      *reinterpret_cast<uint2 *>(&sm.tile[r * kTilePitch + v * 8]) = val;
+      const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch + v * 8);
+      const uint32_t w0 = w[0], w1 = w[1], w2 = sh ? w[2] : 0u;
+      *reinterpret_cast<uint2 *>(&sm.tile[r * kTilePitch + v * 8]) =
+          make_uint2(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh));
     }
     // current CTU, coordinates clamped into the picture for partial CTUs
     for (int i = tid; i < 64 * 8; i += kThreads) {

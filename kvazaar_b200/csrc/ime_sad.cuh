@@ -13,6 +13,7 @@ struct ImeSadParams {
   int pad;                 // border of the padded reference plane
   int tile_x, tile_y, tile_w, tile_h;   // tile rectangle searched (whole frame: 0,0,width,height)
   int ctus_x, ctus_y;      // CTUs in the tile
+  int center_x, center_y;  // window centre: map[dy+R][dx+R] is the SAD at displacement (center_x+dx, center_y+dy)
   int map_pitch;           // entries per (pu, dy) row of every map: roundup(2R+1, 16)
   uint16_t *sad8;          // [ctu*64 + by*8+bx][2R+1][map_pitch]
   uint16_t *sad16;         // [ctu*16 + py*4+px][2R+1][map_pitch]

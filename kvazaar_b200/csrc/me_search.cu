@@ -270,11 +270,8 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
 
   // level of the dense maps that holds this PU, if any
   int level = -1;
-  if (j.w == j.h && (j.w == 8 || j.w == 16 || j.w == 32 || j.w == 64) && (j.x % j.w) == 0 && (j.y % j.h) == 0) {
+  if (j.w == j.h && (j.w == 8 || j.w == 16 || j.w == 32 || j.w == 64) && (j.x % j.w) == 0 && (j.y % j.h) == 0)
     level = j.w == 8 ? 0 : j.w == 16 ? 1 : j.w == 32 ? 2 : 3;
-    if ((level == 0 && !ref.sad8) || (level == 1 && !ref.sad16) || (level == 2 && !ref.sad32) || (level == 3 && !ref.sad64))
-      level = -1;
-  }
 
   unsigned long long best = ~0ull;
 
@@ -321,14 +318,26 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       best = key < best ? key : best;
     };
 
-    if (wi == 0 && level >= 0) {
-      // zero window straight from the dense maps (8 entries per load)
+    // a map set made for this window centre?  (duplicates of earlier windows need no skipping:
+    // with equal cost the earlier window's key is smaller)
+    int si = -1;
+    if (level >= 0) {
+      for (int m = 0; m < ref.n_sets; m++) {
+        const MeMapSet &ms = ref.sets[m];
+        const void *mp = level == 0 ? (const void *)ms.sad8 : level == 1 ? (const void *)ms.sad16
+                       : level == 2 ? (const void *)ms.sad32 : (const void *)ms.sad64;
+        if (ms.cx == cx && ms.cy == cy && mp != nullptr) { si = m; break; }
+      }
+    }
+    if (si >= 0) {
+      const MeMapSet &ms = ref.sets[si];
+      // window straight from the dense maps (8 entries per load)
       const int n = 8 >> level;
       const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
       const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
       const int vec_per_row = (K + 7) >> 3;
       if (level < 2) {
-        const uint16_t *map = (level == 0 ? ref.sad8 : ref.sad16) + prow * K * f.map_pitch;
+        const uint16_t *map = (level == 0 ? ms.sad8 : ms.sad16) + prow * K * f.map_pitch;
         for (int i = g.tid; i < K * vec_per_row; i += G) {
           const int row = i / vec_per_row, c0 = (i % vec_per_row) * 8;
           const uint4 v = __ldg(reinterpret_cast<const uint4 *>(map + (size_t)row * f.map_pitch + c0));
@@ -338,7 +347,7 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
             if (c0 + e < K) consider(row, c0 + e, (wv[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu);
         }
       } else {
-        const uint32_t *map = (level == 2 ? ref.sad32 : ref.sad64) + prow * K * f.map_pitch;
+        const uint32_t *map = (level == 2 ? ms.sad32 : ms.sad64) + prow * K * f.map_pitch;
         for (int i = g.tid; i < K * vec_per_row; i += G) {
           const int row = i / vec_per_row, c0 = (i % vec_per_row) * 8;
           const uint4 v0 = __ldg(reinterpret_cast<const uint4 *>(map + (size_t)row * f.map_pitch + c0));

@@ -6,11 +6,17 @@
 
 namespace kvz {
 
+struct MeMapSet {
+  int cx, cy;                // window centre the maps were made for
+  const uint16_t *sad8, *sad16;
+  const uint32_t *sad32, *sad64;
+};
+
 struct MeRef {
   const uint8_t *plane;      // border-replicated reference luma
   int pitch, pad;            // bytes per row, border width
-  const uint16_t *sad8, *sad16;   // dense maps of this (current, reference) pair; may be null
-  const uint32_t *sad32, *sad64;
+  int n_sets;
+  MeMapSet sets[KVZ_CUDA_MAX_MAPSETS];   // dense maps of this (current, reference) pair
 };
 
 struct MeFrame {

@@ -48,11 +48,12 @@ class ImeSearch:
     search range; `run` fills them with one kernel launch.
     """
 
-    def __init__(self, width, height, rng=32, bitdepth=8, tile=None, device="cuda"):
+    def __init__(self, width, height, rng=32, bitdepth=8, tile=None, device="cuda", max_center=0):
         capi.init(torch.cuda.current_device())
         self.width, self.height, self.range, self.bitdepth = width, height, rng, bitdepth
         self.tile = tile or (0, 0, width, height)
-        self.pad = capi.ime_required_pad(rng)
+        # border the reference planes need: the search range plus the farthest window centre
+        self.pad = capi.ime_required_pad(rng) + ((max_center + 31) & ~31)
         self.map_pitch = capi.ime_map_pitch(rng)
         self.k = 2 * rng + 1
         tw, th = self.tile[2], self.tile[3]
@@ -65,9 +66,13 @@ class ImeSearch:
             self.maps.append(torch.empty((n_ctu * n * n, self.k, self.map_pitch), dtype=dt, device=device))
         self.desc = capi.ImeDesc()
 
-    def run(self, cur, ref_padded):
-        """cur: (H, W) uint8 device tensor; ref_padded: PaddedPlane with pad >= self.pad."""
+    def run(self, cur, ref_padded, center=(0, 0), maps=None):
+        """cur: (H, W) uint8 device tensor; ref_padded: PaddedPlane with pad >= self.pad;
+        center: window centre (whole samples); maps: the four tensors to fill (default self.maps)."""
+        if maps is not None:
+            self.maps = maps
         d = self.desc
+        d.center_x, d.center_y = center
         d.width, d.height, d.bitdepth, d.range = self.width, self.height, self.bitdepth, self.range
         d.tile_x, d.tile_y, d.tile_w, d.tile_h = self.tile
         d.cur_pitch = cur.stride(0) * cur.element_size()
@@ -142,13 +147,24 @@ class MeSearch:
         self._keep.append(cur)
 
     def set_refs(self, padded_planes, maps=None):
-        """padded_planes: list of PaddedPlane; maps: list (per ref) of the 4 map tensors or None."""
+        """padded_planes: list of PaddedPlane; maps: per reference either the 4 zero-window map
+        tensors, or a list of ((center_x, center_y), [4 tensors]) map sets, or None."""
         self.frame.n_refs = len(padded_planes)
         for i, pp in enumerate(padded_planes):
             r = self.frame.refs[i]
             r.d_ref_padded, r.ref_pitch, r.ref_pad = pp.data.data_ptr(), pp.pitch_bytes, pp.pad
             m = maps[i] if maps is not None else None
-            r.d_sad8, r.d_sad16, r.d_sad32, r.d_sad64 = [t.data_ptr() for t in m] if m is not None else [None] * 4
+            if m is None:
+                sets = []
+            elif isinstance(m[0], tuple):
+                sets = m
+            else:
+                sets = [((0, 0), m)]
+            r.n_mapsets = len(sets)
+            for k, (c, t) in enumerate(sets):
+                ms = r.mapsets[k]
+                ms.center_x, ms.center_y = c
+                ms.d_sad8, ms.d_sad16, ms.d_sad32, ms.d_sad64 = [x.data_ptr() for x in t]
         self._keep.append((padded_planes, maps))
 
     def run(self, d_pus, n_pus, d_jobs, d_results):

@@ -47,6 +47,30 @@ def frame_pus(width, height, n_refs, true_mv_px=(5, 3), sizes=(64, 32, 16, 8)):
     return pus, jobs
 
 
+def window_centres(pus, jobs, n_refs, max_sets=3):
+    """The most frequent non-zero window centres search_mv_full will visit per reference
+    (search_inter.c:898-955): extra_mv >> 2 and the uni-directional merge candidates >> 2.
+    Dense maps are made for these; any other window is evaluated on demand by me_search."""
+    out = []
+    jj = jobs.reshape(len(pus), -1)
+    for r in range(n_refs):
+        cnt = {}
+        ex = jj["extra_mv"][:, r].astype(np.int64) >> 2
+        for c, n in zip(*np.unique(ex, axis=0, return_counts=True)):
+            cnt[tuple(int(v) for v in c)] = cnt.get(tuple(int(v) for v in c), 0) + int(n)
+        for m in range(5):
+            sel = (pus["num_merge_cand"] > m) & (pus["merge_cand"]["dir"][:, m] != 3)
+            if not sel.any():
+                continue
+            d = pus["merge_cand"]["dir"][sel, m].astype(np.int64) - 1
+            mv = pus["merge_cand"]["mv"][sel, m][np.arange(int(sel.sum())), d].astype(np.int64) >> 2
+            for c, n in zip(*np.unique(mv, axis=0, return_counts=True)):
+                cnt[tuple(int(v) for v in c)] = cnt.get(tuple(int(v) for v in c), 0) + int(n)
+        cnt.pop((0, 0), None)
+        out.append([c for c, _ in sorted(cnt.items(), key=lambda kv: -kv[1])[:max_sets]])
+    return out
+
+
 class MePipeline:
     # dram__bytes_read.sum + dram__bytes_write.sum of one ime_sad_dense_kernel<32> launch at
     # 1080p from profiles/ (ncu --set full); None until a capture has been taken
@@ -56,17 +80,23 @@ class MePipeline:
         capi.init(torch.cuda.current_device())
         self.width, self.height, self.range, self.n_refs = width, height, rng, n_refs
         self.lambda_sqrt, self.fme_level = lambda_sqrt, fme_level
-        self.ime = ImeSearch(width, height, rng, device=device)
+        pus, jobs = frame_pus(width, height, n_refs)
+        self.centres = [[(0, 0)] + c for c in window_centres(pus, jobs, n_refs)]
+        max_c = max(max(abs(c[0]), abs(c[1])) for cs in self.centres for c in cs)
+        self.ime = ImeSearch(width, height, rng, device=device, max_center=max_c)
         self.cur = torch.empty((height, width), dtype=torch.uint8, device=device)
         self.refs = [torch.empty((height, width), dtype=torch.uint8, device=device) for _ in range(n_refs)]
         self.padded = [PaddedPlane(width, height, self.ime.pad, device=device) for _ in range(n_refs)]
-        self.maps = [[torch.empty_like(m) for m in self.ime.maps] for _ in range(n_refs)]
+        self.maps = [[(c, [torch.empty_like(m) for m in self.ime.maps]) for c in self.centres[r]]
+                     for r in range(n_refs)]
+        self.n_sad_launches = sum(len(c) for c in self.centres)
         self.search = MeSearch(width, height, rng, fme_level=fme_level, lambda_sqrt=lambda_sqrt)
         self.search.set_current(self.cur)
         self.search.set_refs(self.padded, self.maps)
-        self.stages = ["pad_plane x%d" % n_refs, "ime_sad_maps x%d" % n_refs, "me_search (IME decision + FME) x1"]
+        self.stages = ["pad_plane x%d" % n_refs,
+                       "ime_sad_maps x%d (zero window + the frequent extra_mv / merge windows per reference)" % self.n_sad_launches,
+                       "me_search (IME decision + FME) x1"]
         # PUs / jobs of the frame (host, pinned) and their device copies
-        pus, jobs = frame_pus(width, height, n_refs)
         self.n_pus, self.n_jobs = len(pus), len(jobs)
         self.host_pus = torch.from_numpy(pus.view(np.uint8).reshape(-1)).pin_memory()
         self.host_jobs = torch.from_numpy(jobs.view(np.uint8).reshape(-1)).pin_memory()
@@ -87,8 +117,8 @@ class MePipeline:
     def step_resident(self):
         for r in range(self.n_refs):
             self.padded[r].fill_from(self.refs[r])
-            self.ime.maps = self.maps[r]
-            self.ime.run(self.cur, self.padded[r])
+            for c, m in self.maps[r]:
+                self.ime.run(self.cur, self.padded[r], center=c, maps=m)
         self.search.run(self.d_pus, self.n_pus, self.d_jobs, self.d_results)
 
     def step_from_host(self, host_cur, host_refs):
@@ -120,6 +150,7 @@ class MePipeline:
     # ---- dominant kernel alone ----
     def time_sad_kernel(self, iters=10):
         self.padded[0].fill_from(self.refs[0])
+        self.ime.maps = self.maps[0][0][1]
         for _ in range(2):
             self.ime.run(self.cur, self.padded[0])
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

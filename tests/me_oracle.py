@@ -108,19 +108,23 @@ def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sq
     return res
 
 
-def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, **cfg):
+def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), **cfg):
     """The CUDA path through the C ABI for the same inputs (numpy in, numpy out)."""
     import torch
     import kvazaar_b200 as kb
     from kvazaar_b200.frame import ME_RESULT_DT, MeSearch
     cur_d = torch.from_numpy(cur).cuda()
-    ime = kb.ImeSearch(width, height, rng)
+    max_c = max([0] + [max(abs(c[0]), abs(c[1])) for c in centres])
+    ime = kb.ImeSearch(width, height, rng, max_center=max_c)
     planes, maps = [], []
     for r in refs:
         pp = kb.PaddedPlane(width, height, ime.pad).fill_from(torch.from_numpy(r).cuda())
         planes.append(pp)
         if use_maps:
-            maps.append([m.clone() for m in ime.run(cur_d, pp)])
+            sets = [((0, 0), [m.clone() for m in ime.run(cur_d, pp)])]
+            for c in centres:
+                sets.append((tuple(c), [m.clone() for m in ime.run(cur_d, pp, center=tuple(c))]))
+            maps.append(sets)
     ms = MeSearch(width, height, rng, fme_level=fme_level, lambda_sqrt=float(lambda_sqrt_i), **cfg)
     ms.set_current(cur_d)
     ms.set_refs(planes, maps if use_maps else None)

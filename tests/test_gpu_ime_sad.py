@@ -11,15 +11,15 @@ from kvzlibs import ptr
 pytestmark = pytest.mark.gpu
 
 
-def _maps_vs_oracle(width, height, rng_, pic, ref, sample_pus=None, seed=0):
+def _maps_vs_oracle(width, height, rng_, pic, ref, sample_pus=None, seed=0, center=(0, 0)):
     import torch
     import kvazaar_b200 as kb
     O = kvzlibs.oracle()
-    srch = kb.ImeSearch(width, height, rng_)
+    srch = kb.ImeSearch(width, height, rng_, max_center=max(abs(center[0]), abs(center[1])))
     cur_d = torch.from_numpy(pic).cuda()
     ref_d = torch.from_numpy(ref).cuda()
     padded = kb.PaddedPlane(width, height, srch.pad).fill_from(ref_d)
-    maps = [m.cpu().numpy() for m in srch.run(cur_d, padded)]
+    maps = [m.cpu().numpy() for m in srch.run(cur_d, padded, center=center)]
     torch.cuda.synchronize()
     k = 2 * rng_ + 1
     rs = np.random.default_rng(seed)
@@ -33,7 +33,13 @@ def _maps_vs_oracle(width, height, rng_, pic, ref, sample_pus=None, seed=0):
             pus = [pus[0], pus[-1]] + [pus[i] for i in idx]
         for (x, y) in pus:
             want = np.zeros(k * k, dtype=np.uint32)
-            O.kvzo_dense_sad_map_8(ptr(pic), ptr(ref), width, height, x, y, size, size, rng_, ptr(want))
+            if center == (0, 0):
+                O.kvzo_dense_sad_map_8(ptr(pic), ptr(ref), width, height, x, y, size, size, rng_, ptr(want))
+            else:
+                for dy in range(-rng_, rng_ + 1):
+                    for dx in range(-rng_, rng_ + 1):
+                        want[(dy + rng_) * k + dx + rng_] = O.kvzo_image_sad_8(
+                            ptr(pic), ptr(ref), width, height, x, y, x + center[0] + dx, y + center[1] + dy, size, size)
             row = srch.pu_index(level, x, y)
             got = maps[level][row][:, :k].astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
             assert np.array_equal(got, want.reshape(k, k)), (level, x, y)
@@ -48,6 +54,14 @@ def test_small_frame_all_pus(rng_):
     f = kvzlibs.synth_luma(7, w, h, 2)
     n = _maps_vs_oracle(w, h, rng_, f[1], f[0])
     assert n > 400
+
+
+@pytest.mark.parametrize("center", [(5, 3), (-10, 7), (20, -12), (-1, -30)])
+def test_centred_window(center):
+    # the windows search_mv_full opens round extra_mv / merge candidates (search_inter.c:898-955)
+    w, h = 136, 72
+    f = kvzlibs.synth_luma(17, w, h, 2)
+    _maps_vs_oracle(w, h, 8, f[1], f[0], sample_pus=10, seed=3, center=center)
 
 
 def test_white_noise_full64():

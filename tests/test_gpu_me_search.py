@@ -9,13 +9,22 @@ import me_oracle
 pytestmark = pytest.mark.gpu
 
 
-def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 16, 32, 64), **cfg):
+def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 16, 32, 64), centres=(), **cfg):
     rs = np.random.default_rng(seed)
     f = kvzlibs.synth_luma(seed, width, height, n_refs + 1)
     cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
     pus, jobs = me_oracle.random_pus(rs, width, height, n_refs, count, sizes=sizes, mv_span=rng)
+    if centres:
+        # make the extra_mv / first merge candidate of most PUs land on the cached window centres
+        for i in range(count):
+            c = centres[i % len(centres)]
+            if i % 4 != 3:
+                jobs["extra_mv"][i * n_refs:(i + 1) * n_refs] = (c[0] * 4 + 1, c[1] * 4 + 2)
+            if pus[i]["num_merge_cand"] > 0 and pus[i]["merge_cand"][0]["dir"] != 3:
+                pus[i]["merge_cand"][0]["mv"][:] = (c[0] * 4, c[1] * 4)
     lam = int(rs.integers(3, 45))
-    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps, **cfg)
+    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps,
+                               centres=centres, **cfg)
     want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, fme, lam, **cfg)
     me_oracle.assert_results_equal(got, want, pus)
     return got
@@ -44,6 +53,12 @@ def test_mv_constraint_frame_and_tile_margin():
 def test_without_dense_maps():
     # zero window evaluated on demand as well (what non-2Nx2N PUs use)
     _run(200, 136, 8, 4, 2, 24, 12, use_maps=False)
+
+
+def test_cached_window_centres():
+    # windows round extra_mv / merge candidates served from centred dense maps, the rest on demand
+    _run(256, 192, 16, 4, 2, 48, 14, centres=[(5, 3), (-7, 10)])
+    _run(200, 136, 8, 2, 2, 40, 15, centres=[(-13, -6)])
 
 
 def test_white_noise():
