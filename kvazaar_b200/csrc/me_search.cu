@@ -172,8 +172,8 @@ __device__ __forceinline__ unsigned long long group_min(const Group<G> &g, unsig
 
 // per-window separable tables of the AMVP bit cost: bits = min_c(gx[c][col] + gy[c][row])
 struct BitTables {
-  uint8_t gx[2][132];
-  uint8_t gy[2][132];
+  alignas(16) uint2 gx[132];     // lambda * bits of column i for AMVP candidate 0 (.x) and 1 (.y)
+  uint2 gy[132];                 // same for row i
 };
 
 template <int G, int S>
@@ -281,11 +281,9 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
     g.sync();
     for (int i = g.tid; i < K; i += G) {
       const int qx = (cx - R + i) * 4, qy = (cy - R + i) * 4;
-#pragma unroll
-      for (int c = 0; c < 2; c++) {
-        sm.bt.gx[c][i] = (uint8_t)golomb_bits(abs(qx - j.mv_cand[c][0]));
-        sm.bt.gy[c][i] = (uint8_t)golomb_bits(abs(qy - j.mv_cand[c][1]));
-      }
+      const uint32_t lam = (uint32_t)j.lambda;
+      sm.bt.gx[i] = make_uint2(lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
+      sm.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
     }
     if (g.tid == 0) {
       int n = 0;
@@ -306,14 +304,16 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
     g.sync();
     const int n_hit = sm.n_hit;
 
+    // exact per-candidate path: tile restriction and merge override included
     auto consider = [&](int row, int col, uint32_t sad) {
       const int mx = cx - R + col, my = cy - R + row;
       if (!free_mv && !within_tile(f, j, mx * 4, my * 4)) return;
-      uint32_t bits = min((uint32_t)sm.bt.gx[0][col] + sm.bt.gy[0][row], (uint32_t)sm.bt.gx[1][col] + sm.bt.gy[1][row]);
+      const uint2 bx = sm.bt.gx[col], by = sm.bt.gy[row];
+      uint32_t mvd = min(bx.x + by.x, bx.y + by.y);
       const int pos = row * K + col;
       for (int q = 0; q < n_hit; q++)
-        if (sm.hit_pos[q] == pos) bits = (uint32_t)sm.hit_bits[q];
-      const uint32_t cost = sad + bits * (uint32_t)j.lambda;
+        if (sm.hit_pos[q] == pos) mvd = (uint32_t)sm.hit_bits[q] * (uint32_t)j.lambda;
+      const uint32_t cost = sad + mvd;
       const unsigned long long key = ((unsigned long long)cost << 32) | (unsigned)((wi << 16) | pos);
       best = key < best ? key : best;
     };
@@ -331,32 +331,62 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
     }
     if (si >= 0) {
       const MeMapSet &ms = ref.sets[si];
-      // window straight from the dense maps (8 entries per load)
+      // Window straight from the dense maps.  K = 8m + 1: m full vectors of 8 entries per row,
+      // then the last column.  A thread meets its candidates in visiting order, so within the
+      // window a strict '<' keeps the first of equal costs.
       const int n = 8 >> level;
       const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
       const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
-      const int vec_per_row = (K + 7) >> 3;
-      if (level < 2) {
-        const uint16_t *map = (level == 0 ? ms.sad8 : ms.sad16) + prow * K * f.map_pitch;
-        for (int i = g.tid; i < K * vec_per_row; i += G) {
-          const int row = i / vec_per_row, c0 = (i % vec_per_row) * 8;
-          const uint4 v = __ldg(reinterpret_cast<const uint4 *>(map + (size_t)row * f.map_pitch + c0));
-          const uint32_t wv[4] = { v.x, v.y, v.z, v.w };
+      const int vpr = K >> 3;
+      uint32_t wbest = 0xFFFFFFFFu;
+      int wpos = 0;
+      // vectors holding a merge-override position take the exact path
+      int hv[5];
 #pragma unroll
-          for (int e = 0; e < 8; e++)
-            if (c0 + e < K) consider(row, c0 + e, (wv[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu);
+      for (int q = 0; q < 5; q++)
+        hv[q] = (q < n_hit && (sm.hit_pos[q] % K) < K - 1) ? (sm.hit_pos[q] / K) * vpr + ((sm.hit_pos[q] % K) >> 3) : -1;
+      const bool fast = free_mv;
+      const uint16_t *map16 = (level == 0 ? ms.sad8 : ms.sad16) + prow * K * f.map_pitch;
+      const uint32_t *map32 = (level == 2 ? ms.sad32 : ms.sad64) + prow * K * f.map_pitch;
+      for (int i = g.tid; i < K * vpr; i += G) {
+        const int row = i / vpr, c0 = (i - row * vpr) * 8;
+        uint32_t sad[8];
+        if (level < 2) {
+          const uint4 v = __ldg(reinterpret_cast<const uint4 *>(map16 + (size_t)row * f.map_pitch + c0));
+          sad[0] = v.x & 0xFFFFu; sad[1] = v.x >> 16; sad[2] = v.y & 0xFFFFu; sad[3] = v.y >> 16;
+          sad[4] = v.z & 0xFFFFu; sad[5] = v.z >> 16; sad[6] = v.w & 0xFFFFu; sad[7] = v.w >> 16;
+        } else {
+          const uint4 v0 = __ldg(reinterpret_cast<const uint4 *>(map32 + (size_t)row * f.map_pitch + c0));
+          const uint4 v1 = __ldg(reinterpret_cast<const uint4 *>(map32 + (size_t)row * f.map_pitch + c0 + 4));
+          sad[0] = v0.x; sad[1] = v0.y; sad[2] = v0.z; sad[3] = v0.w;
+          sad[4] = v1.x; sad[5] = v1.y; sad[6] = v1.z; sad[7] = v1.w;
         }
-      } else {
-        const uint32_t *map = (level == 2 ? ms.sad32 : ms.sad64) + prow * K * f.map_pitch;
-        for (int i = g.tid; i < K * vec_per_row; i += G) {
-          const int row = i / vec_per_row, c0 = (i % vec_per_row) * 8;
-          const uint4 v0 = __ldg(reinterpret_cast<const uint4 *>(map + (size_t)row * f.map_pitch + c0));
-          const uint4 v1 = __ldg(reinterpret_cast<const uint4 *>(map + (size_t)row * f.map_pitch + c0 + 4));
-          const uint32_t wv[8] = { v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w };
+        const bool special = !fast || i == hv[0] || i == hv[1] || i == hv[2] || i == hv[3] || i == hv[4];
+        if (special) {
 #pragma unroll
-          for (int e = 0; e < 8; e++)
-            if (c0 + e < K) consider(row, c0 + e, wv[e]);
+          for (int e = 0; e < 8; e++) consider(row, c0 + e, sad[e]);
+        } else {
+          const uint2 by = sm.bt.gy[row];
+          const uint4 *bxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
+#pragma unroll
+          for (int e2 = 0; e2 < 4; e2++) {
+            const uint4 bx = bxp[e2];                 // columns c0+2*e2 and c0+2*e2+1
+            const uint32_t ca = sad[2 * e2] + min(bx.x + by.x, bx.y + by.y);
+            const uint32_t cb = sad[2 * e2 + 1] + min(bx.z + by.x, bx.w + by.y);
+            if (ca < wbest) { wbest = ca; wpos = row * K + c0 + 2 * e2; }
+            if (cb < wbest) { wbest = cb; wpos = row * K + c0 + 2 * e2 + 1; }
+          }
         }
+      }
+      // last column
+      for (int row = g.tid; row < K; row += G) {
+        const uint32_t sad = level < 2 ? (uint32_t)__ldg(map16 + (size_t)row * f.map_pitch + K - 1)
+                                       : __ldg(map32 + (size_t)row * f.map_pitch + K - 1);
+        consider(row, K - 1, sad);
+      }
+      if (wbest != 0xFFFFFFFFu) {
+        const unsigned long long key = ((unsigned long long)wbest << 32) | (unsigned)((wi << 16) | wpos);
+        best = key < best ? key : best;
       }
     } else {
       // on demand, skipping what an earlier window of this list already covered
