@@ -193,6 +193,46 @@ typedef struct kvz_cuda_me_frame {
 KVZ_CUDA_API int kvz_cuda_me_search(const kvz_cuda_me_frame *frame, const kvz_cuda_me_pu *d_pus, int n_pus,
                                     const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream);
 
+/* ------------------------------------------------------------------ */
+/* BATCH face: block costs  (rows A1, A2, A6, A7, A8, A16)               */
+/* ------------------------------------------------------------------ */
+
+enum kvz_cuda_cost_kind {
+  KVZ_CUDA_COST_REG_SAD = 0,    /* reg_sad_func (strategies-picture.h:102): any w x h, no bit-depth shift */
+  KVZ_CUDA_COST_SAD_NXN = 1,    /* cost_pixel_nxn_func sad_NxN: w = h = strides = N */
+  KVZ_CUDA_COST_SATD_NXN = 2,   /* cost_pixel_nxn_func satd_NxN, N = 4..64 */
+  KVZ_CUDA_COST_SATD_ANY = 3,   /* cost_pixel_any_size_func kvz_satd_any_size: w, h multiples of 4 */
+  KVZ_CUDA_COST_SATD_QUAD = 4,  /* one prediction of kvz_satd_any_size_quad (its 4-wide strips are dropped) */
+  KVZ_CUDA_COST_SSD = 5         /* pixels_calc_ssd_func: w x w */
+};
+
+typedef struct kvz_cuda_block_job {
+  uint32_t a_offset, b_offset;  /* byte offsets of the two blocks in the buffers d_a, d_b */
+  int32_t a_stride, b_stride;   /* samples per row */
+  int16_t w, h;
+  int32_t kind;                 /* enum kvz_cuda_cost_kind */
+} kvz_cuda_block_job;
+
+/* out[i] = cost of jobs[i]; dual / quad variants are 2 / 4 jobs sharing one original block. */
+KVZ_CUDA_API int kvz_cuda_block_costs(const void *d_a, const void *d_b, const kvz_cuda_block_job *d_jobs,
+                                      int n_jobs, int bitdepth, uint32_t *d_out, void *stream);
+
+enum kvz_cuda_image_cost_kind { KVZ_CUDA_IMAGE_SAD = 0, KVZ_CUDA_IMAGE_SATD = 1 };
+
+typedef struct kvz_cuda_image_cost_job {
+  int32_t pic_x, pic_y;         /* block in the source picture */
+  int32_t ref_x, ref_y;         /* block in the reference, may lie partly or wholly outside */
+  int16_t w, h;
+  int32_t kind;                 /* enum kvz_cuda_image_cost_kind */
+} kvz_cuda_image_cost_job;
+
+/* kvz_image_calc_sad (image.c:455-479) / kvz_image_calc_satd (image.c:488-545) for a batch of
+ * block pairs on two UNPADDED planes of width x height: the reference coordinates are clamped
+ * per sample exactly like image.c:320-452. */
+KVZ_CUDA_API int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const void *d_ref, int ref_pitch,
+                                      int width, int height, const kvz_cuda_image_cost_job *d_jobs,
+                                      int n_jobs, int bitdepth, uint32_t *d_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -75,6 +75,8 @@ SIGNATURES = {
     "kvz_cuda_ime_map_pitch": (C.c_int, [C.c_int]),
     "kvz_cuda_ime_map_bytes": (C.c_size_t, [C.POINTER(ImeDesc), C.c_int]),
     "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_me_search": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
 }
 

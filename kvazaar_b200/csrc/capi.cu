@@ -11,6 +11,12 @@ unsigned long long g_launch_count = 0;
 static int g_device = -1;
 }  // namespace kvz
 
+namespace kvz {
+int launch_block_cost(const void *base_a, const void *base_b, const kvz_cuda_block_job *jobs, int n_jobs,
+                      int bitdepth, uint32_t *out, cudaStream_t stream);
+int launch_image_cost(const void *pic, int pic_pitch, const void *ref, int ref_pitch, int width, int height,
+                      const kvz_cuda_image_cost_job *jobs, int n_jobs, int bitdepth, uint32_t *out, cudaStream_t stream);
+}
 namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
 
 using namespace kvz;
@@ -182,6 +188,24 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
     }
   }
   return launch_me_search(f, d_pus, d_jobs, d_results, n_pus, (cudaStream_t)stream);
+}
+
+int kvz_cuda_block_costs(const void *d_a, const void *d_b, const kvz_cuda_block_job *d_jobs, int n_jobs,
+                         int bitdepth, uint32_t *d_out, void *stream)
+{
+  if (!d_a || !d_b || !d_jobs || !d_out || n_jobs < 0) return fail_msg("kvz_cuda_block_costs: bad argument");
+  if (bitdepth != 8) return fail_msg("kvz_cuda_block_costs: only bitdepth 8 is implemented");
+  return launch_block_cost(d_a, d_b, d_jobs, n_jobs, bitdepth, d_out, (cudaStream_t)stream);
+}
+
+int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const void *d_ref, int ref_pitch, int width, int height,
+                         const kvz_cuda_image_cost_job *d_jobs, int n_jobs, int bitdepth, uint32_t *d_out, void *stream)
+{
+  if (!d_pic || !d_ref || !d_jobs || !d_out || n_jobs < 0 || width <= 0 || height <= 0)
+    return fail_msg("kvz_cuda_image_costs: bad argument");
+  if (bitdepth != 8) return fail_msg("kvz_cuda_image_costs: only bitdepth 8 is implemented");
+  return launch_image_cost(d_pic, pic_pitch, d_ref, ref_pitch, width, height, d_jobs, n_jobs, bitdepth, d_out,
+                           (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -25,6 +25,7 @@
 // CTA), the whole 128-thread CTA for larger ones.
 #include "common.cuh"
 #include "me_search.cuh"
+#include "satd.cuh"
 
 namespace kvz {
 namespace {
@@ -189,46 +190,6 @@ struct GroupSmem {
   int hit_bits[5];
   int n_hit;
 };
-
-// ---- 8-point Hadamard of one row in registers ----
-__device__ __forceinline__ void hadamard8(int (&d)[8])
-{
-#pragma unroll
-  for (int len = 1; len < 8; len <<= 1) {
-#pragma unroll
-    for (int i = 0; i < 8; i += 2 * len) {
-#pragma unroll
-      for (int k = i; k < i + len; k++) {
-        const int p = d[k], q = d[k + len];
-        d[k] = p + q;
-        d[k + len] = p - q;
-      }
-    }
-  }
-}
-
-// sum |H D H^T| of an 8x8 difference block held one row per lane by 8 consecutive lanes;
-// every lane returns the block's SATD ((sum + 2) >> 2, picture-generic.c:321-327)
-__device__ __forceinline__ uint32_t satd8_rows(int (&d)[8], int lane8)
-{
-  hadamard8(d);
-#pragma unroll
-  for (int o = 1; o < 8; o <<= 1) {
-    const bool upper = (lane8 & o) != 0;
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-      const int other = __shfl_xor_sync(0xffffffffu, d[i], o);
-      d[i] = upper ? other - d[i] : d[i] + other;
-    }
-  }
-  uint32_t s = 0;
-#pragma unroll
-  for (int i = 0; i < 8; i++) s += (uint32_t)abs(d[i]);
-  s += __shfl_xor_sync(0xffffffffu, s, 1);
-  s += __shfl_xor_sync(0xffffffffu, s, 2);
-  s += __shfl_xor_sync(0xffffffffu, s, 4);
-  return (s + 2) >> 2;
-}
 
 template <int G, int S>
 __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu,
