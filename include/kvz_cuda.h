@@ -233,6 +233,59 @@ KVZ_CUDA_API int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const vo
                                       int width, int height, const kvz_cuda_image_cost_job *d_jobs,
                                       int n_jobs, int bitdepth, uint32_t *d_out, void *stream);
 
+/* ------------------------------------------------------------------ */
+/* BATCH face: transforms and quantisation  (rows A13, A14)              */
+/* ------------------------------------------------------------------ */
+
+/* `count` contiguous n x n int16 blocks (n = 4, 8, 16, 32).  dst4 != 0 selects the 4x4 DST that
+ * kvz_get_dct_func / kvz_get_idct_func (strategies-dct.c:59-113) pick for intra luma 4x4.
+ * Replaces dct_func kvz_dct_NxN / kvz_idct_NxN / kvz_fast_{forward,inverse}_dst_4x4
+ * (strategies-dct.h:32-52; generic: dct-generic.c:206-617). */
+KVZ_CUDA_API int kvz_cuda_transform_blocks(int n, int dst4, int inverse, int bitdepth, const int16_t *d_in,
+                                           int16_t *d_out, int count, void *stream);
+
+/* the fields of encoder_state_t / encoder_control_t that kvz_quant and kvz_dequant read */
+typedef struct kvz_cuda_quant_cfg {
+  int32_t qp;               /* state->qp */
+  int32_t bitdepth;         /* encoder->bitdepth */
+  int32_t slice_is_intra;   /* state->frame->slicetype == KVZ_SLICE_I (rounding offset 171 vs 85) */
+  int32_t signhide;         /* cfg.signhide_enable */
+  int32_t cu_is_intra;      /* block_type == CU_INTRA: scaling-list class; unused by the flat list */
+} kvz_cuda_quant_cfg;
+
+/* quant_func kvz_quant (strategies-quant.h:36; quant-generic.c:37-163) for `count` n x n blocks;
+ * type 0 luma / 2 chroma, scan_idx 0 diagonal / 1 horizontal / 2 vertical.  Flat scaling list only. */
+KVZ_CUDA_API int kvz_cuda_quant_blocks(const kvz_cuda_quant_cfg *cfg, int n, int type, int scan_idx,
+                                       const int16_t *d_coef, int16_t *d_q_coef, int count, void *stream);
+/* dequant_func kvz_dequant (quant-generic.c:279-321) */
+KVZ_CUDA_API int kvz_cuda_dequant_blocks(const kvz_cuda_quant_cfg *cfg, int n, int type,
+                                         const int16_t *d_q_coef, int16_t *d_coef, int count, void *stream);
+/* coeff_abs_sum_func (quant-generic.c:323-330): out[i] = sum |coeffs[i * per_block ..]| */
+KVZ_CUDA_API int kvz_cuda_coeff_abs_sums(const int16_t *d_coeffs, int per_block, int count, uint32_t *d_out,
+                                         void *stream);
+
+/* one kvz_quantize_residual() call (strategies-quant.h:38-42; quant-generic.c:180-273) */
+typedef struct kvz_cuda_residual_job {
+  uint32_t ref_offset, pred_offset;   /* byte offsets of ref_in / pred_in in d_ref / d_pred (stride in_stride) */
+  uint32_t rec_offset;                /* byte offset of rec_out in d_rec (stride out_stride) */
+  uint32_t coeff_offset;              /* element offset of coeff_out in d_coeff (width*width contiguous) */
+  int32_t in_stride, out_stride;
+  uint8_t width;                      /* 4, 8, 16, 32 */
+  uint8_t color;                      /* color_t: 0 Y, 1 U, 2 V */
+  uint8_t scan_idx;                   /* coeff_scan_order_t */
+  uint8_t use_trskip;
+  int8_t qp;                          /* state->qp of the CTU */
+  uint8_t cu_is_intra;                /* cur_cu->type == CU_INTRA (selects the 4x4 DST) */
+  uint8_t reserved[2];
+} kvz_cuda_residual_job;
+
+/* Fused residual -> transform -> quant -> dequant -> inverse transform -> reconstruction for a batch
+ * of transform blocks; cfg->qp and cfg->cu_is_intra are taken from each job.  d_has_coeffs[i] is the
+ * function's return value.  RDOQ (rdo.c:548-885) is not applied: this is the cfg.rdoq_enable == 0 path. */
+KVZ_CUDA_API int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred,
+                                             void *d_rec, int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs,
+                                             int n_jobs, uint8_t *d_has_coeffs, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

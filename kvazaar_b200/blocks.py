@@ -52,3 +52,67 @@ def image_costs(d_pic, d_ref, jobs, bitdepth=8):
                                                _p(d_jobs), len(jobs), bitdepth, _p(out), _stream()),
                "kvz_cuda_image_costs")
     return out
+
+
+RESIDUAL_JOB_DT = np.dtype([("ref_offset", "<u4"), ("pred_offset", "<u4"), ("rec_offset", "<u4"),
+                            ("coeff_offset", "<u4"), ("in_stride", "<i4"), ("out_stride", "<i4"),
+                            ("width", "u1"), ("color", "u1"), ("scan_idx", "u1"), ("use_trskip", "u1"),
+                            ("qp", "i1"), ("cu_is_intra", "u1"), ("reserved", "u1", (2,))])
+assert RESIDUAL_JOB_DT.itemsize == 32
+
+
+def transform_blocks(d_in, n, inverse=False, dst4=False, bitdepth=8):
+    """d_in: device int16 tensor of `count` contiguous n x n blocks -> same-shaped output
+    (kvz_dct_NxN / kvz_idct_NxN / the 4x4 DST, dct-generic.c:206-617)."""
+    capi.init(torch.cuda.current_device())
+    out = torch.empty_like(d_in)
+    count = d_in.numel() // (n * n)
+    capi.check(capi.lib().kvz_cuda_transform_blocks(n, int(dst4), int(inverse), bitdepth, _p(d_in), _p(out), count,
+                                                    _stream()), "kvz_cuda_transform_blocks")
+    return out
+
+
+def _qcfg(qp, bitdepth, slice_is_intra, signhide, cu_is_intra):
+    return capi.QuantCfg(qp, bitdepth, int(slice_is_intra), int(signhide), int(cu_is_intra))
+
+
+def quant_blocks(d_coef, n, qp, type_=0, scan_idx=0, slice_is_intra=False, signhide=False, bitdepth=8):
+    """kvz_quant (quant-generic.c:37-163) for contiguous n x n int16 blocks."""
+    capi.init(torch.cuda.current_device())
+    out = torch.empty_like(d_coef)
+    cfg = _qcfg(qp, bitdepth, slice_is_intra, signhide, slice_is_intra)
+    capi.check(capi.lib().kvz_cuda_quant_blocks(C.byref(cfg), n, type_, scan_idx, _p(d_coef), _p(out),
+                                                d_coef.numel() // (n * n), _stream()), "kvz_cuda_quant_blocks")
+    return out
+
+
+def dequant_blocks(d_q, n, qp, type_=0, bitdepth=8):
+    """kvz_dequant (quant-generic.c:279-321)."""
+    capi.init(torch.cuda.current_device())
+    out = torch.empty_like(d_q)
+    cfg = _qcfg(qp, bitdepth, False, False, False)
+    capi.check(capi.lib().kvz_cuda_dequant_blocks(C.byref(cfg), n, type_, _p(d_q), _p(out), d_q.numel() // (n * n),
+                                                  _stream()), "kvz_cuda_dequant_blocks")
+    return out
+
+
+def coeff_abs_sums(d_coeffs, per_block):
+    capi.init(torch.cuda.current_device())
+    count = d_coeffs.numel() // per_block
+    out = torch.zeros(count, dtype=torch.int32, device="cuda")
+    capi.check(capi.lib().kvz_cuda_coeff_abs_sums(_p(d_coeffs), per_block, count, _p(out), _stream()),
+               "kvz_cuda_coeff_abs_sums")
+    return out
+
+
+def quantize_residuals(d_ref, d_pred, d_rec, d_coeff, jobs, slice_is_intra=False, signhide=False, bitdepth=8):
+    """Fused kvz_quantize_residual (quant-generic.c:180-273) for a batch of transform blocks;
+    jobs: numpy RESIDUAL_JOB_DT array.  Returns the has_coeffs flags (device uint8)."""
+    capi.init(torch.cuda.current_device())
+    d_jobs = _dev(jobs)
+    has = torch.zeros(len(jobs), dtype=torch.uint8, device="cuda")
+    cfg = _qcfg(0, bitdepth, slice_is_intra, signhide, False)
+    capi.check(capi.lib().kvz_cuda_quantize_residuals(C.byref(cfg), _p(d_ref), _p(d_pred), _p(d_rec), _p(d_coeff),
+                                                      _p(d_jobs), len(jobs), _p(has), _stream()),
+               "kvz_cuda_quantize_residuals")
+    return has

@@ -53,6 +53,12 @@ class MeFrame(C.Structure):
                 ("refs", MeRef * MAX_REFS)]
 
 
+class QuantCfg(C.Structure):
+    """kvz_cuda_quant_cfg"""
+    _fields_ = [("qp", C.c_int32), ("bitdepth", C.c_int32), ("slice_is_intra", C.c_int32),
+                ("signhide", C.c_int32), ("cu_is_intra", C.c_int32)]
+
+
 # name -> (restype, argtypes); every symbol include/kvz_cuda.h declares
 _VP = C.c_void_p
 SIGNATURES = {
@@ -77,6 +83,11 @@ SIGNATURES = {
     "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
+    "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
+    "kvz_cuda_dequant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
+    "kvz_cuda_coeff_abs_sums": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_quantize_residuals": (C.c_int, [C.POINTER(QuantCfg), _VP, _VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
     "kvz_cuda_me_search": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
 }
 

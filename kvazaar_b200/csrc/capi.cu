@@ -17,6 +17,15 @@ int launch_block_cost(const void *base_a, const void *base_b, const kvz_cuda_blo
 int launch_image_cost(const void *pic, int pic_pitch, const void *ref, int ref_pitch, int width, int height,
                       const kvz_cuda_image_cost_job *jobs, int n_jobs, int bitdepth, uint32_t *out, cudaStream_t stream);
 }
+namespace kvz {
+int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
+                           cudaStream_t stream);
+int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
+                       int16_t *out, int count, cudaStream_t stream);
+int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32_t *out, cudaStream_t stream);
+int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
+                             const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream);
+}
 namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
 
 using namespace kvz;
@@ -206,6 +215,54 @@ int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const void *d_ref, in
   if (bitdepth != 8) return fail_msg("kvz_cuda_image_costs: only bitdepth 8 is implemented");
   return launch_image_cost(d_pic, pic_pitch, d_ref, ref_pitch, width, height, d_jobs, n_jobs, bitdepth, d_out,
                            (cudaStream_t)stream);
+}
+
+int kvz_cuda_transform_blocks(int n, int dst4, int inverse, int bitdepth, const int16_t *d_in, int16_t *d_out,
+                              int count, void *stream)
+{
+  if (!d_in || !d_out || count < 0) return fail_msg("kvz_cuda_transform_blocks: bad argument");
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_transform_blocks: bitdepth must be 8 or 10");
+  return launch_transform_batch(n, dst4, inverse, bitdepth, d_in, d_out, count, (cudaStream_t)stream);
+}
+
+static int check_qcfg(const kvz_cuda_quant_cfg *c, const char *who)
+{
+  if (!c) return fail_msg(who);
+  if ((c->bitdepth != 8 && c->bitdepth != 10) || c->qp < -12 || c->qp > 51) return fail_msg(who);
+  return 1;
+}
+
+int kvz_cuda_quant_blocks(const kvz_cuda_quant_cfg *cfg, int n, int type, int scan_idx, const int16_t *d_coef,
+                          int16_t *d_q_coef, int count, void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_quant_blocks: bad cfg") ) return 0;
+  if (!d_coef || !d_q_coef || count < 0 || scan_idx < 0 || scan_idx > 2) return fail_msg("kvz_cuda_quant_blocks: bad argument");
+  return launch_quant_batch(*cfg, n, type, scan_idx, 0, d_coef, d_q_coef, count, (cudaStream_t)stream);
+}
+
+int kvz_cuda_dequant_blocks(const kvz_cuda_quant_cfg *cfg, int n, int type, const int16_t *d_q_coef, int16_t *d_coef,
+                            int count, void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_dequant_blocks: bad cfg")) return 0;
+  if (!d_coef || !d_q_coef || count < 0) return fail_msg("kvz_cuda_dequant_blocks: bad argument");
+  return launch_quant_batch(*cfg, n, type, 0, 1, d_q_coef, d_coef, count, (cudaStream_t)stream);
+}
+
+int kvz_cuda_coeff_abs_sums(const int16_t *d_coeffs, int per_block, int count, uint32_t *d_out, void *stream)
+{
+  if (!d_coeffs || !d_out || per_block <= 0 || count < 0) return fail_msg("kvz_cuda_coeff_abs_sums: bad argument");
+  return launch_coeff_abs_sum(d_coeffs, per_block, count, d_out, (cudaStream_t)stream);
+}
+
+int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred, void *d_rec,
+                                int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs, int n_jobs,
+                                uint8_t *d_has_coeffs, void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_quantize_residuals: bad cfg")) return 0;
+  if (cfg->bitdepth != 8) return fail_msg("kvz_cuda_quantize_residuals: only bitdepth 8 is implemented");
+  if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || n_jobs < 0)
+    return fail_msg("kvz_cuda_quantize_residuals: bad argument");
+  return launch_quantize_residual(*cfg, d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has_coeffs, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -87,3 +87,32 @@ def test_scaled_qp(oracle_lib):
     assert oracle_lib.kvzo_scaled_qp(2, 30, 0) == 29
     assert oracle_lib.kvzo_scaled_qp(2, 43, 0) == 37
     assert oracle_lib.kvzo_scaled_qp(2, 51, 0) == 45
+
+
+@pytest.mark.parametrize("cpuid", [0, 1], ids=["generic", "avx2"])
+def test_quantize_residual_vs_reference(oracle_lib, ref_lib, cpuid):
+    # the fused residual -> T -> Q -> Q^-1 -> T^-1 -> recon path (quant-generic.c:180-273), rdoq off
+    L = kvzlibs.ref(cpuid)
+    rs = np.random.default_rng(77)
+    for n in (4, 8, 16, 32):
+        for it in range(24):
+            qp = int(rs.integers(10, 46))
+            color = int(rs.integers(0, 3)) if n < 32 else 0
+            intra = int(rs.integers(0, 2))
+            trskip = int(n == 4 and rs.random() < 0.3)
+            signhide = int(rs.integers(0, 2))
+            scan = int(rs.integers(0, 3)) if n <= 8 else 0
+            stride = n + 8 * int(rs.integers(0, 3))
+            ref_in = kvzlibs.aligned_copy(rs.integers(0, 256, (n, stride), dtype=np.uint8))
+            noise = rs.integers(-int(rs.integers(1, 40)), 40, (n, stride))
+            pred = kvzlibs.aligned_copy(np.clip(ref_in.astype(np.int64) + noise, 0, 255).astype(np.uint8))
+            rc = kvzlibs.RefQCfg(qp, intra, signhide, 0, 0, intra, 0.0)
+            oc = kvzlibs.OracleQCfg(qp, 8, intra, signhide, intra)
+            rec_w = kvzlibs.aligned((n, stride), np.uint8); rec_g = kvzlibs.aligned((n, stride), np.uint8)
+            co_w = kvzlibs.aligned((n * n,), np.int16); co_g = kvzlibs.aligned((n * n,), np.int16)
+            hw = L.ref_shim_quantize_residual(C.byref(rc), n, color, scan, trskip, stride, stride,
+                                              ptr(ref_in), ptr(pred), ptr(rec_w), ptr(co_w))
+            hg = oracle_lib.kvzo_quantize_residual_8(C.byref(oc), n, color, scan, trskip, stride, stride,
+                                                     ptr(ref_in), ptr(pred), ptr(rec_g), ptr(co_g))
+            assert hg == hw and np.array_equal(co_g, co_w), ("coeff", n, it, qp, color, intra, trskip)
+            assert np.array_equal(rec_g[:, :n], rec_w[:, :n]), ("rec", n, it)
