@@ -286,6 +286,40 @@ KVZ_CUDA_API int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, cons
                                              void *d_rec, int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs,
                                              int n_jobs, uint8_t *d_has_coeffs, void *stream);
 
+/* ------------------------------------------------------------------ */
+/* BATCH face: fractional-sample interpolation  (rows A9, A10, A11, A12) */
+/* ------------------------------------------------------------------ */
+
+enum kvz_cuda_interp_mode {
+  KVZ_CUDA_INTERP_PIXEL = 0,    /* kvz_sample_quarterpel_luma / kvz_sample_octpel_chroma: clipped pixels */
+  KVZ_CUDA_INTERP_14BIT = 1,    /* kvz_sample_14bit_*: int16 intermediate precision for bi-prediction */
+  KVZ_CUDA_INTERP_FME = 2       /* one candidate block of kvz_filter_{hpel,qpel}_blocks_*_luma (int16 wrap kept) */
+};
+
+typedef struct kvz_cuda_interp_job {
+  int32_t x, y;                 /* top-left whole sample of the block in the plane (xpos + tile offset) */
+  int32_t mv_x, mv_y;           /* displacement: quarter-pel (luma) or eighth-pel (chroma), any integer */
+  int16_t w, h;                 /* <= 64 (luma), <= 32 (chroma) */
+  uint8_t chroma;               /* 0: 8-tap luma filter, 1: 4-tap chroma filter */
+  uint8_t mode;                 /* enum kvz_cuda_interp_mode */
+  uint8_t reserved[2];
+  uint32_t dst_offset;          /* element offset in d_dst8 (modes 0, 2) or d_dst16 (mode 1) */
+  int32_t dst_stride;
+} kvz_cuda_interp_job;
+
+/* Interpolates a batch of blocks of one UNPADDED plane (width x height, pitch bytes per row); samples outside
+ * the plane are the clamped ones kvz_get_extended_block (ipol-generic.c:731-784) would have copied.
+ * Replaces kvz_sample_quarterpel_luma, kvz_sample_octpel_chroma and their 14-bit variants
+ * (strategies-ipol.h:44-48), and, four jobs per call, the ipol_blocks_func filters (strategies-ipol.h:36-38). */
+KVZ_CUDA_API int kvz_cuda_interp_blocks(const void *d_plane, int pitch, int width, int height, int bitdepth,
+                                        const kvz_cuda_interp_job *d_jobs, int n_jobs,
+                                        void *d_dst8, int16_t *d_dst16, void *stream);
+
+/* inter_recon_bipred_func on flat arrays of 14-bit samples: dst = clip((s0 + s1 + offset) >> (15 - bitdepth))
+ * (picture-generic.c:553-570) */
+KVZ_CUDA_API int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1, size_t n, int bitdepth,
+                                       void *d_dst, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -116,3 +116,30 @@ def quantize_residuals(d_ref, d_pred, d_rec, d_coeff, jobs, slice_is_intra=False
                                                       _p(d_jobs), len(jobs), _p(has), _stream()),
                "kvz_cuda_quantize_residuals")
     return has
+
+
+INTERP_PIXEL, INTERP_14BIT, INTERP_FME = 0, 1, 2
+INTERP_JOB_DT = np.dtype([("x", "<i4"), ("y", "<i4"), ("mv_x", "<i4"), ("mv_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
+                          ("chroma", "u1"), ("mode", "u1"), ("reserved", "u1", (2,)), ("dst_offset", "<u4"),
+                          ("dst_stride", "<i4")])
+assert INTERP_JOB_DT.itemsize == 32
+
+
+def interp_blocks(d_plane, jobs, d_dst8=None, d_dst16=None, bitdepth=8):
+    """Luma (8-tap, 1/4-pel) / chroma (4-tap, 1/8-pel) interpolation of a batch of blocks of one
+    unpadded device plane; jobs: numpy INTERP_JOB_DT array."""
+    capi.init(torch.cuda.current_device())
+    h, w = d_plane.shape
+    d_jobs = _dev(jobs)
+    capi.check(capi.lib().kvz_cuda_interp_blocks(
+        _p(d_plane), d_plane.stride(0), w, h, bitdepth, _p(d_jobs), len(jobs),
+        _p(d_dst8) if d_dst8 is not None else None, _p(d_dst16) if d_dst16 is not None else None, _stream()),
+        "kvz_cuda_interp_blocks")
+
+
+def bipred_blend(d_s0, d_s1, bitdepth=8):
+    capi.init(torch.cuda.current_device())
+    out = torch.empty(d_s0.shape, dtype=torch.uint8, device="cuda")
+    capi.check(capi.lib().kvz_cuda_bipred_blend(_p(d_s0), _p(d_s1), d_s0.numel(), bitdepth, _p(out), _stream()),
+               "kvz_cuda_bipred_blend")
+    return out

@@ -88,6 +88,8 @@ SIGNATURES = {
     "kvz_cuda_dequant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_coeff_abs_sums": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_quantize_residuals": (C.c_int, [C.POINTER(QuantCfg), _VP, _VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
+    "kvz_cuda_interp_blocks": (C.c_int, [_VP, C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.c_int, _VP, _VP, _VP]),
+    "kvz_cuda_bipred_blend": (C.c_int, [_VP, _VP, C.c_size_t, C.c_int, _VP, _VP]),
     "kvz_cuda_me_search": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
 }
 

@@ -26,6 +26,11 @@ int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32
 int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
                              const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream);
 }
+namespace kvz {
+int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
+                  void *dst8, int16_t *dst16, cudaStream_t stream);
+int launch_bipred_blend(const int16_t *s0, const int16_t *s1, size_t n, int bitdepth, void *dst, cudaStream_t stream);
+}
 namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
 
 using namespace kvz;
@@ -263,6 +268,22 @@ int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, const void *d_ref
   if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || n_jobs < 0)
     return fail_msg("kvz_cuda_quantize_residuals: bad argument");
   return launch_quantize_residual(*cfg, d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has_coeffs, (cudaStream_t)stream);
+}
+
+int kvz_cuda_interp_blocks(const void *d_plane, int pitch, int width, int height, int bitdepth,
+                           const kvz_cuda_interp_job *d_jobs, int n_jobs, void *d_dst8, int16_t *d_dst16, void *stream)
+{
+  if (!d_plane || !d_jobs || n_jobs < 0 || width <= 0 || height <= 0 || (!d_dst8 && !d_dst16))
+    return fail_msg("kvz_cuda_interp_blocks: bad argument");
+  if (bitdepth != 8) return fail_msg("kvz_cuda_interp_blocks: only bitdepth 8 is implemented");
+  return launch_interp(d_plane, pitch, width, height, bitdepth, d_jobs, n_jobs, d_dst8, d_dst16, (cudaStream_t)stream);
+}
+
+int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1, size_t n, int bitdepth, void *d_dst, void *stream)
+{
+  if (!d_s0 || !d_s1 || !d_dst) return fail_msg("kvz_cuda_bipred_blend: null argument");
+  if (bitdepth != 8) return fail_msg("kvz_cuda_bipred_blend: only bitdepth 8 is implemented");
+  return launch_bipred_blend(d_s0, d_s1, n, bitdepth, d_dst, (cudaStream_t)stream);
 }
 
 }  // extern "C"
