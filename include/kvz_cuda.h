@@ -320,6 +320,29 @@ KVZ_CUDA_API int kvz_cuda_interp_blocks(const void *d_plane, int pitch, int widt
 KVZ_CUDA_API int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1, size_t n, int bitdepth,
                                        void *d_dst, void *stream);
 
+/* ------------------------------------------------------------------ */
+/* BATCH face: intra prediction and rough mode costs  (row A17)          */
+/* ------------------------------------------------------------------ */
+
+typedef struct kvz_cuda_intra_job {
+  uint32_t ref_offset;          /* byte offset in d_refs of this PU's reference samples: top[2w+1] then left[2w+1],
+                                   [0] = the top-left corner (kvz_intra_references.ref, intra.h) */
+  uint32_t orig_offset;         /* byte offset of the source block in d_orig */
+  int32_t orig_stride;
+  uint32_t pred_offset;         /* byte offset in d_preds of this PU's 35 predictions (35 * w * w samples) */
+  uint8_t log2_width;           /* 2..5 */
+  uint8_t is_chroma;            /* color != COLOR_Y */
+  uint8_t filter_boundary;      /* !(cfg->lossless && cfg->implicit_rdpcm), search_intra.c:420 */
+  uint8_t has_orig;             /* 0: predictions only */
+} kvz_cuda_intra_job;
+
+/* For each PU: kvz_intra_predict (intra.c:281-332; angular_pred_func / intra_pred_planar_func of
+ * strategies-intra.h:32-43 inside) for all 35 modes, and d_costs[(pu * 35 + mode) * 2 + {0, 1}] =
+ * {satd_NxN, sad_NxN}(prediction, source) -- every cost search_intra_rough (search_intra.c:404-545) can ask for.
+ * d_preds may be NULL; d_costs / d_orig may be NULL when no job has has_orig. */
+KVZ_CUDA_API int kvz_cuda_intra_mode_costs(const void *d_refs, const void *d_orig, const kvz_cuda_intra_job *d_jobs,
+                                           int n_jobs, int bitdepth, uint32_t *d_costs, void *d_preds, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

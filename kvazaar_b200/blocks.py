@@ -143,3 +143,24 @@ def bipred_blend(d_s0, d_s1, bitdepth=8):
     capi.check(capi.lib().kvz_cuda_bipred_blend(_p(d_s0), _p(d_s1), d_s0.numel(), bitdepth, _p(out), _stream()),
                "kvz_cuda_bipred_blend")
     return out
+
+
+INTRA_JOB_DT = np.dtype([("ref_offset", "<u4"), ("orig_offset", "<u4"), ("orig_stride", "<i4"), ("pred_offset", "<u4"),
+                         ("log2_width", "u1"), ("is_chroma", "u1"), ("filter_boundary", "u1"), ("has_orig", "u1")])
+assert INTRA_JOB_DT.itemsize == 20
+
+
+def intra_mode_costs(d_refs, d_orig, jobs, want_preds=False, bitdepth=8):
+    """All 35 intra predictions of each PU and their {SATD, SAD} against the source block.
+    Returns (costs int32 [n, 35, 2] device tensor, preds uint8 device tensor or None)."""
+    capi.init(torch.cuda.current_device())
+    d_jobs = _dev(jobs)
+    costs = torch.zeros((len(jobs), 35, 2), dtype=torch.int32, device="cuda")
+    preds = None
+    if want_preds:
+        total = int(jobs["pred_offset"].max()) + 35 * (1 << (2 * int(jobs["log2_width"][np.argmax(jobs["pred_offset"])])))
+        preds = torch.zeros(total, dtype=torch.uint8, device="cuda")
+    capi.check(capi.lib().kvz_cuda_intra_mode_costs(
+        _p(d_refs), _p(d_orig) if d_orig is not None else None, _p(d_jobs), len(jobs), bitdepth, _p(costs),
+        _p(preds) if preds is not None else None, _stream()), "kvz_cuda_intra_mode_costs")
+    return costs, preds

@@ -31,6 +31,10 @@ int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, cons
                   void *dst8, int16_t *dst16, cudaStream_t stream);
 int launch_bipred_blend(const int16_t *s0, const int16_t *s1, size_t n, int bitdepth, void *dst, cudaStream_t stream);
 }
+namespace kvz {
+int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
+                       uint32_t *costs, void *preds, cudaStream_t stream);
+}
 namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
 
 using namespace kvz;
@@ -284,6 +288,14 @@ int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1, size_t n, in
   if (!d_s0 || !d_s1 || !d_dst) return fail_msg("kvz_cuda_bipred_blend: null argument");
   if (bitdepth != 8) return fail_msg("kvz_cuda_bipred_blend: only bitdepth 8 is implemented");
   return launch_bipred_blend(d_s0, d_s1, n, bitdepth, d_dst, (cudaStream_t)stream);
+}
+
+int kvz_cuda_intra_mode_costs(const void *d_refs, const void *d_orig, const kvz_cuda_intra_job *d_jobs, int n_jobs,
+                              int bitdepth, uint32_t *d_costs, void *d_preds, void *stream)
+{
+  if (!d_refs || !d_jobs || n_jobs < 0 || (!d_costs && !d_preds)) return fail_msg("kvz_cuda_intra_mode_costs: bad argument");
+  if (bitdepth != 8) return fail_msg("kvz_cuda_intra_mode_costs: only bitdepth 8 is implemented");
+  return launch_intra_costs(d_refs, d_orig, d_jobs, n_jobs, d_costs, d_preds, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -2,6 +2,7 @@
 // (picture-generic.c:148-183 satd_4x4, :201-327 satd_8x8 sub-block)
 #pragma once
 #include <stdint.h>
+#include "common.cuh"
 
 namespace kvz {
 
@@ -70,6 +71,92 @@ __device__ __forceinline__ uint32_t satd4_thread(int (&d)[16])
     s += (uint32_t)(abs(a + g) + abs(b + e) + abs(a - g) + abs(b - e));
   }
   return (s + 1) >> 1;
+}
+
+// ---- warp-level costs over pixel fetchers ----
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// pixel fetchers: plain strided block, or plane with the coordinate clamped into it
+struct StridedBlock {
+  const uint8_t *p;
+  int stride;
+  __device__ __forceinline__ int operator()(int x, int y) const { return p[(size_t)y * stride + x]; }
+};
+
+struct ClampedPlane {
+  const uint8_t *p;
+  int pitch, w, h, x0, y0;
+  __device__ __forceinline__ int operator()(int x, int y) const
+  {
+    return p[(size_t)clampi(y0 + y, 0, h - 1) * pitch + clampi(x0 + x, 0, w - 1)];
+  }
+};
+
+template <typename FA, typename FB>
+__device__ inline uint32_t warp_sad(const FA &a, const FB &b, int w, int h, int lane)
+{
+  uint32_t s = 0;
+  for (int i = lane; i < w * h; i += 32) {
+    const int y = i / w, x = i - y * w;
+    s += (uint32_t)abs(a(x, y) - b(x, y));
+  }
+  return warp_sum(s);
+}
+
+template <typename FA, typename FB>
+__device__ inline uint32_t warp_ssd(const FA &a, const FB &b, int w, int h, int lane)
+{
+  uint32_t s = 0;
+  for (int i = lane; i < w * h; i += 32) {
+    const int y = i / w, x = i - y * w;
+    const int d = a(x, y) - b(x, y);
+    s += (uint32_t)(d * d);
+  }
+  return warp_sum(s);
+}
+
+// sum of 8x8 SATDs over the tiles of the area [x0, x0+w) x [y0, y0+h) (w, h multiples of 8)
+template <typename FA, typename FB>
+__device__ inline uint32_t warp_satd8_area(const FA &a, const FB &b, int x0, int y0, int w, int h, int lane)
+{
+  const int tx_n = w >> 3, tiles = tx_n * (h >> 3);
+  const int lane8 = lane & 7, sub = lane >> 3;
+  uint32_t total = 0;
+  for (int t0 = 0; t0 < tiles; t0 += 4) {
+    const int t = t0 + sub;
+    const bool on = t < tiles;
+    const int ty = on ? t / tx_n : 0, tx = on ? t - ty * tx_n : 0;
+    int d[8];
+#pragma unroll
+    for (int x = 0; x < 8; x++)
+      d[x] = a(x0 + tx * 8 + x, y0 + ty * 8 + lane8) - b(x0 + tx * 8 + x, y0 + ty * 8 + lane8);
+    const uint32_t s = satd8_rows(d, lane8);
+    if (on && lane8 == 0) total += s;
+  }
+  return warp_sum(total);
+}
+
+// sum of 4x4 SATDs over `count` blocks starting at (x0, y0) and stepping by (sx, sy)
+template <typename FA, typename FB>
+__device__ inline uint32_t warp_satd4_strip(const FA &a, const FB &b, int x0, int y0, int sx, int sy, int count, int lane)
+{
+  uint32_t total = 0;
+  for (int i = lane; i < count; i += 32) {
+    int d[16];
+#pragma unroll
+    for (int y = 0; y < 4; y++)
+#pragma unroll
+      for (int x = 0; x < 4; x++)
+        d[4 * y + x] = a(x0 + i * sx + x, y0 + i * sy + y) - b(x0 + i * sx + x, y0 + i * sy + y);
+    total += satd4_thread(d);
+  }
+  return warp_sum(total);
 }
 
 }  // namespace kvz
