@@ -1,0 +1,527 @@
+// kvazaar_b200/csrc/percall.cu
+//
+// PER-CALL face: functions with exactly the strategy typedefs of the reference
+// (strategies-picture.h:102-136, strategies-dct.h:32, strategies-quant.h:48,
+// strategies-intra.h:32-43, strategies-ipol.h:36-48) so that they can be handed to
+// kvz_strategyselector_register() under strategy name "cuda".  Each call stages its host
+// buffers through pinned memory, launches the same kernels the batch face uses on a
+// batch of one, and waits.  This face exists for parity tests and the kernel sweep
+// (BASELINE config 5); a launch per 8x8 block is not how throughput is obtained.
+// Thread-safe through one lock (strategies are called from every threadqueue worker).
+#include <mutex>
+
+#include "common.cuh"
+#include "../../include/kvz_cuda.h"
+#include "../../include/kvz_cuda_strategies.h"
+
+namespace kvz {
+int launch_block_cost(const void *base_a, const void *base_b, const kvz_cuda_block_job *jobs, int n_jobs,
+                      int bitdepth, uint32_t *out, cudaStream_t stream);
+int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
+                           cudaStream_t stream);
+int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32_t *out, cudaStream_t stream);
+int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
+                       uint32_t *costs, void *preds, cudaStream_t stream);
+int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
+                  void *dst8, int16_t *dst16, cudaStream_t stream);
+
+namespace {
+
+constexpr size_t kStage = 1 << 20;      // bytes of each staging buffer
+
+struct PerCall {
+  std::mutex lock;
+  cudaStream_t stream = nullptr;
+  uint8_t *h = nullptr, *d = nullptr;   // pinned host / device staging, kStage bytes each
+  bool ready = false;
+  bool init()
+  {
+    if (ready) return true;
+    if (cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) != cudaSuccess) return false;
+    if (cudaMallocHost(&h, kStage) != cudaSuccess) return false;
+    if (cudaMalloc(&d, kStage) != cudaSuccess) return false;
+    ready = true;
+    return true;
+  }
+};
+
+PerCall g_pc;
+
+[[noreturn]] void die(const char *what)
+{
+  // a cost function cannot report failure (SURVEY.md 8b "Errors"): fail loudly, never fall back
+  fprintf(stderr, "libkvz_cuda: %s failed: %s\n", what, g_last_error);
+  abort();
+}
+
+// layout of the staging buffers for one call: [0, in_bytes) inputs, then outputs
+struct Stage {
+  std::unique_lock<std::mutex> guard;
+  size_t in_bytes = 0, out_bytes = 0;
+  explicit Stage(const char *who) : guard(g_pc.lock)
+  {
+    if (!g_pc.init()) { fail_msg("per-call staging buffers"); die(who); }
+  }
+  template <typename T> T *in(size_t count)      // reserve input space, 16-byte aligned
+  {
+    in_bytes = (in_bytes + 15) & ~(size_t)15;
+    T *p = reinterpret_cast<T *>(g_pc.h + in_bytes);
+    in_bytes += count * sizeof(T);
+    return p;
+  }
+  template <typename T> const T *dev(const T *host_ptr) const
+  {
+    return reinterpret_cast<const T *>(g_pc.d + (reinterpret_cast<const uint8_t *>(host_ptr) - g_pc.h));
+  }
+  template <typename T> T *dev(T *host_ptr) const
+  {
+    return reinterpret_cast<T *>(g_pc.d + (reinterpret_cast<uint8_t *>(host_ptr) - g_pc.h));
+  }
+  // outputs live after the inputs; call after all in<>() reservations
+  template <typename T> T *out(size_t count)
+  {
+    size_t off = (in_bytes + out_bytes + 15) & ~(size_t)15;
+    out_bytes = off - in_bytes + count * sizeof(T);
+    return reinterpret_cast<T *>(g_pc.h + off);
+  }
+  void upload(const char *who)
+  {
+    if (cudaMemcpyAsync(g_pc.d, g_pc.h, in_bytes, cudaMemcpyHostToDevice, g_pc.stream) != cudaSuccess) die(who);
+  }
+  void download(const char *who)
+  {
+    if (cudaMemcpyAsync(g_pc.h + in_bytes, g_pc.d + in_bytes, out_bytes, cudaMemcpyDeviceToHost, g_pc.stream) != cudaSuccess) die(who);
+    if (cudaStreamSynchronize(g_pc.stream) != cudaSuccess) { fail("stream sync", cudaGetLastError(), __FILE__, __LINE__); die(who); }
+  }
+};
+
+void pack_rows(uint8_t *dst, const uint8_t *src, int w, int h, size_t stride)
+{
+  for (int y = 0; y < h; y++) memcpy(dst + (size_t)y * w, src + (size_t)y * stride, (size_t)w);
+}
+
+// one or more predictions against one original block
+void cost_call(const char *who, int kind, int w, int h, const uint8_t *const *preds, size_t pred_stride, int n_preds,
+               const uint8_t *orig, size_t orig_stride, unsigned *costs_out)
+{
+  Stage st(who);
+  uint8_t *o = st.in<uint8_t>((size_t)w * h);
+  pack_rows(o, orig, w, h, orig_stride);
+  uint8_t *p = st.in<uint8_t>((size_t)w * h * n_preds);
+  for (int k = 0; k < n_preds; k++) pack_rows(p + (size_t)k * w * h, preds[k], w, h, pred_stride);
+  kvz_cuda_block_job *jobs = st.in<kvz_cuda_block_job>(n_preds);
+  for (int k = 0; k < n_preds; k++) {
+    jobs[k].a_offset = (uint32_t)(k * w * h); jobs[k].b_offset = 0;
+    jobs[k].a_stride = w; jobs[k].b_stride = w;
+    jobs[k].w = (int16_t)w; jobs[k].h = (int16_t)h; jobs[k].kind = kind;
+  }
+  uint32_t *out = st.out<uint32_t>(n_preds);
+  st.upload(who);
+  if (!launch_block_cost(st.dev(p), st.dev(o), st.dev(jobs), n_preds, 8, st.dev(out), g_pc.stream)) die(who);
+  st.download(who);
+  for (int k = 0; k < n_preds; k++) costs_out[k] = out[k];
+}
+
+unsigned cost_pair(const char *who, int kind, int w, int h, const uint8_t *a, size_t sa, const uint8_t *b, size_t sb)
+{
+  unsigned c = 0;
+  cost_call(who, kind, w, h, &a, sa, 1, b, sb, &c);
+  return c;
+}
+
+}  // namespace
+}  // namespace kvz
+
+using namespace kvz;
+
+namespace kvz {
+int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
+                       int16_t *out, int count, cudaStream_t stream);
+int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
+                             const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream);
+}
+
+extern "C" {
+
+// ---------------- picture ----------------
+unsigned kvz_cuda_reg_sad(const kvz_cuda_px *data1, const kvz_cuda_px *data2, int width, int height,
+                          unsigned stride1, unsigned stride2)
+{
+  return cost_pair("kvz_cuda_reg_sad", KVZ_CUDA_COST_REG_SAD, width, height, data1, stride1, data2, stride2);
+}
+
+#define KVZ_NXN(N)                                                                                         \
+  unsigned kvz_cuda_sad_##N##x##N(const kvz_cuda_px *b1, const kvz_cuda_px *b2)                            \
+  { return cost_pair("kvz_cuda_sad_" #N "x" #N, KVZ_CUDA_COST_SAD_NXN, N, N, b1, N, b2, N); }              \
+  unsigned kvz_cuda_satd_##N##x##N(const kvz_cuda_px *b1, const kvz_cuda_px *b2)                           \
+  { return cost_pair("kvz_cuda_satd_" #N "x" #N, KVZ_CUDA_COST_SATD_NXN, N, N, b1, N, b2, N); }            \
+  void kvz_cuda_sad_##N##x##N##_dual(const kvz_cuda_pred_buffer preds, const kvz_cuda_px *orig,            \
+                                     unsigned num_modes, unsigned *costs_out)                              \
+  {                                                                                                        \
+    const uint8_t *p[8];                                                                                   \
+    for (unsigned i = 0; i < num_modes && i < 8; i++) p[i] = preds[i];                                     \
+    cost_call("kvz_cuda_sad_" #N "x" #N "_dual", KVZ_CUDA_COST_SAD_NXN, N, N, p, N, (int)num_modes, orig, N, costs_out);   \
+  }                                                                                                        \
+  void kvz_cuda_satd_##N##x##N##_dual(const kvz_cuda_pred_buffer preds, const kvz_cuda_px *orig,           \
+                                      unsigned num_modes, unsigned *costs_out)                             \
+  {                                                                                                        \
+    const uint8_t *p[8];                                                                                   \
+    for (unsigned i = 0; i < num_modes && i < 8; i++) p[i] = preds[i];                                     \
+    cost_call("kvz_cuda_satd_" #N "x" #N "_dual", KVZ_CUDA_COST_SATD_NXN, N, N, p, N, (int)num_modes, orig, N, costs_out);  \
+  }
+KVZ_NXN(4)
+KVZ_NXN(8)
+KVZ_NXN(16)
+KVZ_NXN(32)
+KVZ_NXN(64)
+#undef KVZ_NXN
+
+unsigned kvz_cuda_satd_any_size(int width, int height, const kvz_cuda_px *block1, int stride1,
+                                const kvz_cuda_px *block2, int stride2)
+{
+  return cost_pair("kvz_cuda_satd_any_size", KVZ_CUDA_COST_SATD_ANY, width, height, block1, (size_t)stride1, block2, (size_t)stride2);
+}
+
+void kvz_cuda_satd_any_size_quad(int width, int height, const kvz_cuda_px **preds, const int stride,
+                                 const kvz_cuda_px *orig, const int orig_stride, unsigned num_modes,
+                                 unsigned *costs_out, int8_t *valid)
+{
+  (void)valid;    // the generic strategy evaluates all predictions too (picture-generic.c:392-456)
+  cost_call("kvz_cuda_satd_any_size_quad", KVZ_CUDA_COST_SATD_QUAD, width, height, preds, (size_t)stride, (int)num_modes,
+            orig, (size_t)orig_stride, costs_out);
+}
+
+unsigned kvz_cuda_pixels_calc_ssd(const kvz_cuda_px *ref, const kvz_cuda_px *rec, const int ref_stride,
+                                  const int rec_stride, const int width)
+{
+  return cost_pair("kvz_cuda_pixels_calc_ssd", KVZ_CUDA_COST_SSD, width, width, ref, (size_t)ref_stride, rec, (size_t)rec_stride);
+}
+
+// ---------------- dct ----------------
+static unsigned transform_call(const char *who, int n, int dst4, int inverse, int8_t bitdepth, const int16_t *input,
+                               int16_t *output)
+{
+  Stage st(who);
+  int16_t *in = st.in<int16_t>((size_t)n * n);
+  memcpy(in, input, sizeof(int16_t) * n * n);
+  int16_t *out = st.out<int16_t>((size_t)n * n);
+  st.upload(who);
+  if (!launch_transform_batch(n, dst4, inverse, bitdepth, st.dev(in), st.dev(out), 1, g_pc.stream)) die(who);
+  st.download(who);
+  memcpy(output, out, sizeof(int16_t) * n * n);
+  return 0;
+}
+
+#define KVZ_TR(name, n, dst4, inv) \
+  unsigned name(int8_t bitdepth, const int16_t *input, int16_t *output) { return transform_call(#name, n, dst4, inv, bitdepth, input, output); }
+KVZ_TR(kvz_cuda_fast_forward_dst_4x4, 4, 1, 0)
+KVZ_TR(kvz_cuda_dct_4x4, 4, 0, 0)
+KVZ_TR(kvz_cuda_dct_8x8, 8, 0, 0)
+KVZ_TR(kvz_cuda_dct_16x16, 16, 0, 0)
+KVZ_TR(kvz_cuda_dct_32x32, 32, 0, 0)
+KVZ_TR(kvz_cuda_fast_inverse_dst_4x4, 4, 1, 1)
+KVZ_TR(kvz_cuda_idct_4x4, 4, 0, 1)
+KVZ_TR(kvz_cuda_idct_8x8, 8, 0, 1)
+KVZ_TR(kvz_cuda_idct_16x16, 16, 0, 1)
+KVZ_TR(kvz_cuda_idct_32x32, 32, 0, 1)
+#undef KVZ_TR
+
+// ---------------- quant ----------------
+uint32_t kvz_cuda_coeff_abs_sum(const kvz_cuda_coeff *coeffs, size_t length)
+{
+  const char *who = "kvz_cuda_coeff_abs_sum";
+  Stage st(who);
+  int16_t *in = st.in<int16_t>(length);
+  memcpy(in, coeffs, sizeof(int16_t) * length);
+  uint32_t *out = st.out<uint32_t>(1);
+  st.upload(who);
+  if (!launch_coeff_abs_sum(st.dev(in), (int)length, 1, st.dev(out), g_pc.stream)) die(who);
+  st.download(who);
+  return out[0];
+}
+
+int kvz_cuda_quant_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_coeff *coef, kvz_cuda_coeff *q_coef,
+                        int32_t width, int32_t height, int8_t type, int8_t scan_idx)
+{
+  const char *who = "kvz_cuda_quant_host";
+  if (!cfg || width != height) return fail_msg("kvz_cuda_quant_host: bad argument");
+  Stage st(who);
+  int16_t *in = st.in<int16_t>((size_t)width * width);
+  memcpy(in, coef, sizeof(int16_t) * width * width);
+  int16_t *out = st.out<int16_t>((size_t)width * width);
+  st.upload(who);
+  if (!launch_quant_batch(*cfg, width, type, scan_idx, 0, st.dev(in), st.dev(out), 1, g_pc.stream)) return 0;
+  st.download(who);
+  memcpy(q_coef, out, sizeof(int16_t) * width * width);
+  return 1;
+}
+
+int kvz_cuda_dequant_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_coeff *q_coef, kvz_cuda_coeff *coef,
+                          int32_t width, int32_t height, int8_t type)
+{
+  const char *who = "kvz_cuda_dequant_host";
+  if (!cfg || width != height) return fail_msg("kvz_cuda_dequant_host: bad argument");
+  Stage st(who);
+  int16_t *in = st.in<int16_t>((size_t)width * width);
+  memcpy(in, q_coef, sizeof(int16_t) * width * width);
+  int16_t *out = st.out<int16_t>((size_t)width * width);
+  st.upload(who);
+  if (!launch_quant_batch(*cfg, width, type, 0, 1, st.dev(in), st.dev(out), 1, g_pc.stream)) return 0;
+  st.download(who);
+  memcpy(coef, out, sizeof(int16_t) * width * width);
+  return 1;
+}
+
+int kvz_cuda_quantize_residual_host(const kvz_cuda_quant_cfg *cfg, int width, int color, int scan_order, int use_trskip,
+                                    int in_stride, int out_stride, const kvz_cuda_px *ref_in, const kvz_cuda_px *pred_in,
+                                    kvz_cuda_px *rec_out, kvz_cuda_coeff *coeff_out)
+{
+  const char *who = "kvz_cuda_quantize_residual_host";
+  if (!cfg) return fail_msg("kvz_cuda_quantize_residual_host: bad argument");
+  Stage st(who);
+  const size_t nn = (size_t)width * width;
+  uint8_t *r = st.in<uint8_t>(nn), *p = st.in<uint8_t>(nn);
+  pack_rows(r, ref_in, width, width, (size_t)in_stride);
+  pack_rows(p, pred_in, width, width, (size_t)in_stride);
+  kvz_cuda_residual_job *jb = st.in<kvz_cuda_residual_job>(1);
+  memset(jb, 0, sizeof(*jb));
+  jb->in_stride = width; jb->out_stride = width;
+  jb->width = (uint8_t)width; jb->color = (uint8_t)color; jb->scan_idx = (uint8_t)scan_order;
+  jb->use_trskip = (uint8_t)use_trskip; jb->qp = (int8_t)cfg->qp; jb->cu_is_intra = (uint8_t)cfg->cu_is_intra;
+  uint8_t *rec = st.out<uint8_t>(nn);
+  int16_t *co = st.out<int16_t>(nn);
+  uint8_t *has = st.out<uint8_t>(1);
+  st.upload(who);
+  if (!launch_quantize_residual(*cfg, st.dev(r), st.dev(p), st.dev(rec), st.dev(co), st.dev(jb), 1, st.dev(has), g_pc.stream))
+    die(who);
+  st.download(who);
+  memcpy(coeff_out, co, sizeof(int16_t) * nn);
+  for (int y = 0; y < width; y++) memcpy(rec_out + (size_t)y * out_stride, rec + (size_t)y * width, (size_t)width);
+  return has[0];
+}
+
+// ---------------- intra ----------------
+// angular_pred_func / intra_pred_planar_func receive the references kvz_intra_predict has already
+// chosen (filtered or not), so the job runs as chroma (no smoothing, no boundary filters) and
+// the wanted mode is picked from the 35 predictions.
+static void intra_call(const char *who, int lg, int mode, const kvz_cuda_px *top, const kvz_cuda_px *left, kvz_cuda_px *dst)
+{
+  const int w = 1 << lg, n = 2 * w + 1;
+  Stage st(who);
+  uint8_t *refs = st.in<uint8_t>((size_t)2 * n);
+  memcpy(refs, top, (size_t)n);
+  memcpy(refs + n, left, (size_t)n);
+  kvz_cuda_intra_job *jb = st.in<kvz_cuda_intra_job>(1);
+  memset(jb, 0, sizeof(*jb));
+  jb->log2_width = (uint8_t)lg; jb->is_chroma = 1;
+  uint8_t *preds = st.out<uint8_t>((size_t)35 * w * w);
+  st.upload(who);
+  if (!launch_intra_costs(st.dev(refs), nullptr, st.dev(jb), 1, nullptr, st.dev(preds), g_pc.stream)) die(who);
+  st.download(who);
+  memcpy(dst, preds + (size_t)mode * w * w, (size_t)w * w);
+}
+
+void kvz_cuda_angular_pred(const int_fast8_t log2_width, const int_fast8_t intra_mode, const kvz_cuda_px *const in_ref_above,
+                           const kvz_cuda_px *const in_ref_left, kvz_cuda_px *const dst)
+{
+  intra_call("kvz_cuda_angular_pred", log2_width, intra_mode, in_ref_above, in_ref_left, dst);
+}
+
+void kvz_cuda_intra_pred_planar(const int_fast8_t log2_width, const kvz_cuda_px *const ref_top,
+                                const kvz_cuda_px *const ref_left, kvz_cuda_px *const dst)
+{
+  intra_call("kvz_cuda_intra_pred_planar", log2_width, 0, ref_top, ref_left, dst);
+}
+
+// ---------------- ipol ----------------
+static void sample_call(const char *who, bool chroma, bool hi, const kvz_cuda_px *src, int src_stride, int w, int h,
+                        void *dst, int dst_stride, const int16_t mv[2])
+{
+  const int taps = chroma ? 4 : 8, before = taps / 2 - 1, mask = chroma ? 7 : 3;
+  const int ww = w + taps - 1, wh = h + taps - 1;
+  Stage st(who);
+  uint8_t *win = st.in<uint8_t>((size_t)ww * wh);
+  pack_rows(win, src - (ptrdiff_t)before * src_stride - before, ww, wh, (size_t)src_stride);
+  kvz_cuda_interp_job *jb = st.in<kvz_cuda_interp_job>(1);
+  memset(jb, 0, sizeof(*jb));
+  jb->x = before; jb->y = before; jb->mv_x = mv[0] & mask; jb->mv_y = mv[1] & mask;
+  jb->w = (int16_t)w; jb->h = (int16_t)h; jb->chroma = chroma; jb->mode = hi ? KVZ_CUDA_INTERP_14BIT : KVZ_CUDA_INTERP_PIXEL;
+  jb->dst_offset = 0; jb->dst_stride = w;
+  uint8_t *o8 = hi ? nullptr : st.out<uint8_t>((size_t)w * h);
+  int16_t *o16 = hi ? st.out<int16_t>((size_t)w * h) : nullptr;
+  st.upload(who);
+  if (!launch_interp(st.dev(win), ww, ww, wh, 8, st.dev(jb), 1, hi ? nullptr : (void *)st.dev(o8), hi ? st.dev(o16) : nullptr,
+                     g_pc.stream)) die(who);
+  st.download(who);
+  for (int y = 0; y < h; y++) {
+    if (hi) memcpy((int16_t *)dst + (size_t)y * dst_stride, o16 + (size_t)y * w, sizeof(int16_t) * w);
+    else memcpy((uint8_t *)dst + (size_t)y * dst_stride, o8 + (size_t)y * w, (size_t)w);
+  }
+}
+
+void kvz_cuda_sample_quarterpel_luma(const void *, kvz_cuda_px *src, int16_t src_stride, int width, int height,
+                                     kvz_cuda_px *dst, int16_t dst_stride, int8_t, int8_t, const int16_t mv[2])
+{ sample_call("kvz_cuda_sample_quarterpel_luma", false, false, src, src_stride, width, height, dst, dst_stride, mv); }
+
+void kvz_cuda_sample_octpel_chroma(const void *, kvz_cuda_px *src, int16_t src_stride, int width, int height,
+                                   kvz_cuda_px *dst, int16_t dst_stride, int8_t, int8_t, const int16_t mv[2])
+{ sample_call("kvz_cuda_sample_octpel_chroma", true, false, src, src_stride, width, height, dst, dst_stride, mv); }
+
+void kvz_cuda_sample_14bit_quarterpel_luma(const void *, kvz_cuda_px *src, int16_t src_stride, int width, int height,
+                                           int16_t *dst, int16_t dst_stride, int8_t, int8_t, const int16_t mv[2])
+{ sample_call("kvz_cuda_sample_14bit_quarterpel_luma", false, true, src, src_stride, width, height, dst, dst_stride, mv); }
+
+void kvz_cuda_sample_14bit_octpel_chroma(const void *, kvz_cuda_px *src, int16_t src_stride, int width, int height,
+                                         int16_t *dst, int16_t dst_stride, int8_t, int8_t, const int16_t mv[2])
+{ sample_call("kvz_cuda_sample_14bit_octpel_chroma", true, true, src, src_stride, width, height, dst, dst_stride, mv); }
+
+// The FME block filters: src is orig_topleft of an extended block fetched one sample up-left of the
+// integer vector with (width + 1) x (height + 1) samples and 4 samples of margin (search_inter.c:1008-1013),
+// so the block at the integer vector starts at src + (1, 1).
+static void fme_blocks_call(const char *who, const kvz_cuda_px *src, int src_stride, int w, int h,
+                            kvz_cuda_px filtered[4][64 * 64], const int q[4][2])
+{
+  const int ww = w + 9, wh = h + 9;
+  Stage st(who);
+  uint8_t *win = st.in<uint8_t>((size_t)ww * wh);
+  pack_rows(win, src - (ptrdiff_t)4 * src_stride - 4, ww, wh, (size_t)src_stride);
+  kvz_cuda_interp_job *jb = st.in<kvz_cuda_interp_job>(4);
+  memset(jb, 0, sizeof(*jb) * 4);
+  for (int k = 0; k < 4; k++) {
+    jb[k].x = 5; jb[k].y = 5; jb[k].mv_x = q[k][0]; jb[k].mv_y = q[k][1];
+    jb[k].w = (int16_t)w; jb[k].h = (int16_t)h; jb[k].mode = KVZ_CUDA_INTERP_FME;
+    jb[k].dst_offset = (uint32_t)(k * w * h); jb[k].dst_stride = w;
+  }
+  uint8_t *o = st.out<uint8_t>((size_t)4 * w * h);
+  st.upload(who);
+  if (!launch_interp(st.dev(win), ww, ww, wh, 8, st.dev(jb), 4, st.dev(o), nullptr, g_pc.stream)) die(who);
+  st.download(who);
+  for (int k = 0; k < 4; k++)
+    for (int y = 0; y < h; y++) memcpy(&filtered[k][y * 64], o + ((size_t)k * h + y) * w, (size_t)w);
+}
+
+void kvz_cuda_filter_hpel_blocks_hor_ver_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS)
+{
+  (void)encoder; (void)hor_intermediate; (void)fme_level; (void)hor_first_cols; (void)sample_off_x; (void)sample_off_y;
+  const int q[4][2] = { { -2, 0 }, { 2, 0 }, { 0, -2 }, { 0, 2 } };
+  fme_blocks_call("kvz_cuda_filter_hpel_blocks_hor_ver_luma", src, src_stride, width, height, filtered, q);
+}
+
+void kvz_cuda_filter_hpel_blocks_diag_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS)
+{
+  (void)encoder; (void)hor_intermediate; (void)fme_level; (void)hor_first_cols; (void)sample_off_x; (void)sample_off_y;
+  const int q[4][2] = { { -2, -2 }, { 2, -2 }, { -2, 2 }, { 2, 2 } };
+  fme_blocks_call("kvz_cuda_filter_hpel_blocks_diag_luma", src, src_stride, width, height, filtered, q);
+}
+
+void kvz_cuda_filter_qpel_blocks_hor_ver_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS)
+{
+  (void)encoder; (void)hor_intermediate; (void)fme_level; (void)hor_first_cols;
+  const int ox = 2 * sample_off_x, oy = 2 * sample_off_y;
+  const int q[4][2] = { { ox - 1, oy }, { ox + 1, oy }, { ox, oy - 1 }, { ox, oy + 1 } };
+  fme_blocks_call("kvz_cuda_filter_qpel_blocks_hor_ver_luma", src, src_stride, width, height, filtered, q);
+}
+
+void kvz_cuda_filter_qpel_blocks_diag_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS)
+{
+  (void)encoder; (void)hor_intermediate; (void)fme_level; (void)hor_first_cols;
+  const int ox = 2 * sample_off_x, oy = 2 * sample_off_y;
+  const int q[4][2] = { { ox - 1, oy - 1 }, { ox + 1, oy - 1 }, { ox - 1, oy + 1 }, { ox + 1, oy + 1 } };
+  fme_blocks_call("kvz_cuda_filter_qpel_blocks_diag_luma", src, src_stride, width, height, filtered, q);
+}
+
+// ---------------- registration ----------------
+// Same type strings as STRATEGIES_*_EXPORTS (strategies-picture.h:173-198, -dct.h:54-68,
+// -quant.h:58-62, -intra.h:54-56, -ipol.h:64-73).
+#define KVZ_REG(type, fn) ok &= register_fn(opaque, type, "cuda", 50, (void *)&fn)
+
+static int cuda_usable()
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail_msg("kvz_strategy_register_*_cuda: no CUDA device (there is no CPU fallback)");
+  }
+  return 1;
+}
+
+int kvz_strategy_register_picture_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  KVZ_REG("reg_sad", kvz_cuda_reg_sad);
+  KVZ_REG("sad_4x4", kvz_cuda_sad_4x4); KVZ_REG("sad_8x8", kvz_cuda_sad_8x8); KVZ_REG("sad_16x16", kvz_cuda_sad_16x16);
+  KVZ_REG("sad_32x32", kvz_cuda_sad_32x32); KVZ_REG("sad_64x64", kvz_cuda_sad_64x64);
+  KVZ_REG("satd_4x4", kvz_cuda_satd_4x4); KVZ_REG("satd_8x8", kvz_cuda_satd_8x8); KVZ_REG("satd_16x16", kvz_cuda_satd_16x16);
+  KVZ_REG("satd_32x32", kvz_cuda_satd_32x32); KVZ_REG("satd_64x64", kvz_cuda_satd_64x64);
+  KVZ_REG("satd_any_size", kvz_cuda_satd_any_size);
+  KVZ_REG("sad_4x4_dual", kvz_cuda_sad_4x4_dual); KVZ_REG("sad_8x8_dual", kvz_cuda_sad_8x8_dual);
+  KVZ_REG("sad_16x16_dual", kvz_cuda_sad_16x16_dual); KVZ_REG("sad_32x32_dual", kvz_cuda_sad_32x32_dual);
+  KVZ_REG("sad_64x64_dual", kvz_cuda_sad_64x64_dual);
+  KVZ_REG("satd_4x4_dual", kvz_cuda_satd_4x4_dual); KVZ_REG("satd_8x8_dual", kvz_cuda_satd_8x8_dual);
+  KVZ_REG("satd_16x16_dual", kvz_cuda_satd_16x16_dual); KVZ_REG("satd_32x32_dual", kvz_cuda_satd_32x32_dual);
+  KVZ_REG("satd_64x64_dual", kvz_cuda_satd_64x64_dual);
+  KVZ_REG("satd_any_size_quad", kvz_cuda_satd_any_size_quad);
+  KVZ_REG("pixels_calc_ssd", kvz_cuda_pixels_calc_ssd);
+  return ok;
+}
+
+int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  KVZ_REG("fast_forward_dst_4x4", kvz_cuda_fast_forward_dst_4x4);
+  KVZ_REG("dct_4x4", kvz_cuda_dct_4x4); KVZ_REG("dct_8x8", kvz_cuda_dct_8x8);
+  KVZ_REG("dct_16x16", kvz_cuda_dct_16x16); KVZ_REG("dct_32x32", kvz_cuda_dct_32x32);
+  KVZ_REG("fast_inverse_dst_4x4", kvz_cuda_fast_inverse_dst_4x4);
+  KVZ_REG("idct_4x4", kvz_cuda_idct_4x4); KVZ_REG("idct_8x8", kvz_cuda_idct_8x8);
+  KVZ_REG("idct_16x16", kvz_cuda_idct_16x16); KVZ_REG("idct_32x32", kvz_cuda_idct_32x32);
+  return ok;
+}
+
+int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  // quant / quantize_residual / dequant read encoder_state_t: their one-line wrappers live in the
+  // glue and call kvz_cuda_{quant,quantize_residual,dequant}_host
+  KVZ_REG("coeff_abs_sum", kvz_cuda_coeff_abs_sum);
+  return ok;
+}
+
+int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  KVZ_REG("angular_pred", kvz_cuda_angular_pred);
+  KVZ_REG("intra_pred_planar", kvz_cuda_intra_pred_planar);
+  return ok;
+}
+
+int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  KVZ_REG("filter_hpel_blocks_hor_ver_luma", kvz_cuda_filter_hpel_blocks_hor_ver_luma);
+  KVZ_REG("filter_hpel_blocks_diag_luma", kvz_cuda_filter_hpel_blocks_diag_luma);
+  KVZ_REG("filter_qpel_blocks_hor_ver_luma", kvz_cuda_filter_qpel_blocks_hor_ver_luma);
+  KVZ_REG("filter_qpel_blocks_diag_luma", kvz_cuda_filter_qpel_blocks_diag_luma);
+  KVZ_REG("sample_quarterpel_luma", kvz_cuda_sample_quarterpel_luma);
+  KVZ_REG("sample_octpel_chroma", kvz_cuda_sample_octpel_chroma);
+  KVZ_REG("sample_14bit_quarterpel_luma", kvz_cuda_sample_14bit_quarterpel_luma);
+  KVZ_REG("sample_14bit_octpel_chroma", kvz_cuda_sample_14bit_octpel_chroma);
+  // get_extended_block stays with the host's generic strategy: it only copies memory
+  return ok;
+}
+
+}  // extern "C"

@@ -45,3 +45,44 @@ def test_map_geometry_helpers():
     import ctypes as C
     assert kb.lib().kvz_cuda_ime_map_bytes(C.byref(d), 0) == 510 * 64 * 65 * 80 * 2
     assert kb.lib().kvz_cuda_ime_map_bytes(C.byref(d), 3) == 510 * 65 * 80 * 4
+
+
+def _declared_strategy_symbols():
+    text = open(os.path.join(ROOT, "include", "kvz_cuda_strategies.h")).read()
+    return sorted(set(re.findall(r"KVZ_CUDA_API[^;(]*?\b(kvz_(?:cuda|strategy_register)_\w+)\s*\(", text)))
+
+
+def test_per_call_face_exports_every_strategy_symbol():
+    L = kb.lib()
+    names = _declared_strategy_symbols()
+    assert len(names) >= 50
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/kvz_cuda_strategies.h but not exported"
+    # every strategy type of the hot path has a per-call function (STRATEGIES_*_EXPORTS of the reference)
+    for t in ["reg_sad", "satd_any_size", "satd_any_size_quad", "pixels_calc_ssd", "coeff_abs_sum", "angular_pred",
+              "intra_pred_planar", "sample_quarterpel_luma", "sample_octpel_chroma", "filter_hpel_blocks_hor_ver_luma",
+              "filter_qpel_blocks_diag_luma", "dct_32x32", "idct_4x4", "fast_forward_dst_4x4"] + \
+             [f"{k}_{n}x{n}{d}" for k in ("sad", "satd") for n in (4, 8, 16, 32, 64) for d in ("", "_dual")]:
+        assert hasattr(L, "kvz_cuda_" + t), t
+
+
+def test_registration_contract_without_device(ref_lib):
+    """kvz_strategy_register_*_cuda(opaque, bitdepth, kvz_strategyselector_register): at another bit depth
+    nothing is registered and 1 is returned (like avx2/picture-avx2.c:1230); without a device 0 is
+    returned so that kvz_strategyselector_init fails encoder_open (strategyselector.c:54-95)."""
+    import ctypes as C
+    import torch
+    L = kb.lib()
+
+    class StrategyList(C.Structure):      # strategy_list_t (strategyselector.h:47-53)
+        _fields_ = [("count", C.c_uint), ("allocated", C.c_uint), ("strategies", C.c_void_p)]
+
+    reg = C.cast(ref_lib.kvz_strategyselector_register, C.c_void_p)
+    for fam in ("picture", "dct", "quant", "intra", "ipol"):
+        fn = getattr(L, f"kvz_strategy_register_{fam}_cuda")
+        fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_uint8, C.c_void_p]
+        lst = StrategyList()
+        assert fn(C.byref(lst), 10, reg) == 1 and lst.count == 0
+        if not torch.cuda.is_available():
+            assert fn(C.byref(lst), 8, reg) == 0 and lst.count == 0
+            assert b"no CUDA device" in L.kvz_cuda_last_error()
