@@ -233,19 +233,39 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    from kvazaar_b200 import shard
+    counter = [0]
+
+    def exchange():
+        # the one exchange step of the sharded pipeline: the rank that reconstructed the
+        # newest reference publishes its luma plane to all ranks over NCCL/NVLink
+        if world > 1:
+            shard.publish_reference(pipe.refs[0], src=counter[0] % world)
+            counter[0] += 1
+
+    def step_resident():
+        exchange()
+        pipe.step_resident()
+
+    def step_e2e():
+        exchange()
+        pipe.step_from_host(host_cur, host_refs)
+
     clocks = Clocks(local)
     if rank == 0:
         clocks.start()
     for _ in range(max(args.warmup, 3)):
-        pipe.step_resident()
+        step_resident()
     l0 = kb.launch_count()
-    ms = timed(pipe.step_resident, args.steps)
+    ms = timed(step_resident, args.steps)
     launches = kb.launch_count() - l0
 
     # e2e through the C ABI from host buffers
     for _ in range(2):
-        pipe.step_from_host(host_cur, host_refs)
-    ms_e2e = timed(lambda: pipe.step_from_host(host_cur, host_refs), args.steps)
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    if world > 1:
+        pipe.upload(host_cur, host_refs)      # restore this rank's own reference 0 for the kernel timings
 
     # per-kernel times, each kernel alone with events on the launching stream
     sad_ms = pipe.time_sad_kernel(iters=max(5, args.steps))
@@ -287,7 +307,8 @@ def run_ours(args):
                    "frames_per_s": 1e3 / step_ms * world,
                    "l2": "per step %.0f MB of SAD maps are written and read back: larger than the 126 MB L2, "
                          "no flush needed" % (map_bytes * NREFS / 1e6),
-                   "stages": pipe.stages,
+                   "stages": pipe.stages + (["publish_reference (NCCL broadcast of one luma plane) x1"] if world > 1 else []),
+                   "parallelism": "frames of one temporal layer per GPU (weak scaling), no data-path collective in ME",
                    "kernel_ms": {"ime_sad_dense x1": sad_ms, "me_search x1": search_ms,
                                  "sad_launches_per_step": pipe.n_sad_launches, "share_sad": pipe.n_sad_launches * sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
         "clocks": clk,
