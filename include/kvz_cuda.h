@@ -96,15 +96,19 @@ typedef struct kvz_cuda_ime_desc {
                                    centre = the window round extra_mv / a merge candidate (search_inter.c:898-955) */
 } kvz_cuda_ime_desc;
 
-/* entries per (PU, dy) row of the maps: roundup(2*range+1, 16) */
+/* entries per row of the maps: roundup(2*range+1, 16) */
 KVZ_CUDA_API int kvz_cuda_ime_map_pitch(int range);
 /* bytes of the map of PU size 8<<level (level 0..3) for this descriptor */
 KVZ_CUDA_API size_t kvz_cuda_ime_map_bytes(const kvz_cuda_ime_desc *d, int level);
 
 /* For one (current, reference) pair: SAD of every 8x8/16x16/32x32/64x64 PU of every
  * CTU against the edge-clamped reference at every (dx,dy) in [-range,range]^2.
- *   map[level][ctu * n*n + py*n + px][dy+range][dx+range],  n = 8 >> level,
- * rows map_pitch entries apart; uint16 for levels 0,1 and uint32 for 2,3.
+ * With K = 2*range+1 and n = 8 >> level, PU p = ctu * n*n + py*n + px owns K+1 rows of
+ * map_pitch entries (uint16 for levels 0,1 and uint32 for 2,3):
+ *   map[level][p][dy+range][dx+range]   for dx in [-range, range)   (rows 0..K-1)
+ *   map[level][p][K][dy+range]          for dx = +range             (row K)
+ * -- the last column is stored as a row so that every store of the kernels covers whole
+ * 32-byte sectors; the remaining entries of a row (up to map_pitch) are unspecified.
  * Replaces the zero-window loop of search_mv_full (search_inter.c:891-895) over
  * check_mv_cost -> kvz_image_calc_sad -> kvz_reg_sad for ALL PUs of the frame. */
 KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,

@@ -141,7 +141,7 @@ size_t kvz_cuda_ime_map_bytes(const kvz_cuda_ime_desc *d, int level)
   const size_t ctus = (size_t)((d->tile_w + 63) / 64) * ((d->tile_h + 63) / 64);
   const size_t n = 8 >> level;
   const size_t k = 2 * d->range + 1;
-  return ctus * n * n * k * ime_map_pitch(d->range) * (level < 2 ? 2 : 4);
+  return ctus * n * n * (k + 1) * ime_map_pitch(d->range) * (level < 2 ? 2 : 4);   // row K = the column dx = +R
 }
 
 int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const void *d_ref_padded,

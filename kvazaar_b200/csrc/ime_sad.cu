@@ -12,22 +12,23 @@
 //       -> kvz_reg_sad (strategies/generic/picture-generic.c:86-99)
 // for the zero-centred window of search_mv_full (search_inter.c:891-895).
 //
-// Design (sm_100a):
-//  * the reference plane lives in HBM with replicated borders (pad_plane
-//    kernel) so a tile fetch never needs per-pixel clamping: clamping the
-//    coordinate == reading the replicated border;
-//  * one CTA = one CTU x one chunk of 16 horizontal displacements.  The
-//    (2R+64) x 80-byte reference tile and the 64x64 current CTU are staged in
-//    shared memory once and reused for all 2R+1 vertical displacements;
-//  * one thread = one 8x8 block x 4 consecutive dx.  It slides down the
-//    reference rows; each row is loaded once (3 LDS), realigned to the 4 byte
-//    shifts (6 SHF) and consumed by 8 current rows x 4 shifts x 2 words
-//    = 64 VABSDIFF4.U8.ACC, i.e. 256 pixel differences per 9 non-SAD
-//    instructions.  Eight (dy) x four (dx) accumulators rotate through a
-//    statically indexed register window (loop unrolled by 8);
-//  * every completed dy row is written as full 32-byte sectors (4 lanes x 8 B)
-//    and staged in shared memory, where 4 warps (alternating by parity so the
-//    load is even) form the 16/32/64 sums with packed adds and shuffles.
+// Design (sm_100a), v2:
+//  * the reference plane lives in HBM with replicated borders (pad_plane kernel) so a
+//    tile fetch never needs per-pixel clamping;
+//  * one CTA = one CTU x one chunk of 16 horizontal displacements (plus one light CTA per
+//    CTU for the 65th column).  The (2R+64)-row reference tile is staged in shared memory
+//    FOUR times, pre-shifted by 0..3 bytes, so that every operand of the inner loop is an
+//    aligned word: no funnel shifts compete with the SAD instructions for the ALU pipe;
+//  * one thread = one 8x8 block x 4 displacements dx = g + 4j of byte-shift g.  It slides
+//    down the tile rows: 3 LDS (5 words) feed 64 VABSDIFF4.U8.ACC per row.  Eight (dy)
+//    x four (dx) accumulators rotate through a statically indexed register window; a new
+//    accumulator starts from the zero register instead of being cleared; the first and
+//    the last 8-row iterations are specialised so that no product outside the window is
+//    ever issued;
+//  * finished rows go to a shared-memory ring (4 STS.U16, no packing, no global address
+//    arithmetic in the compute loop).  Every 8 rows all threads turn writer: 16-byte
+//    vectors of the 8x8 map, and the 16/32/64 sums formed with packed u16 adds and
+//    shuffles, each map written exactly once in full 32-byte sectors.
 #include "common.cuh"
 #include "ime_sad.cuh"
 
@@ -36,7 +37,7 @@ namespace kvz {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kTilePitch = 80;        // bytes per staged reference row (20 words)
+constexpr int kRowWords = 20;         // staged words per tile row and copy (80 bytes)
 constexpr int kChunkDx = 16;          // horizontal displacements per CTA
 
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c)
@@ -46,162 +47,311 @@ __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c)
   return d;
 }
 
+constexpr int kRawWords = 22;           // aligned source words per tile row (84 bytes + up to 3 of misalignment)
+
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src)
+{
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// ring-slot position of an 8x8 block: the low two bits are swizzled with the 32x32 PU index so that
+// the four PUs read by one warp of the writer fall into different banks
+__device__ __forceinline__ int stage_slot(int blk) { return blk ^ (((blk >> 2) & 1) | ((blk >> 4) & 2)); }
+
 template <int R>
-struct Smem {
+struct Geo {
+  static constexpr int K = 2 * R + 1;
   static constexpr int kRows = 2 * R + 64;
-  static constexpr int kK = 2 * R + 1;
-  alignas(16) uint8_t tile[kRows * kTilePitch];
-  alignas(16) uint8_t cur[64 * 64];
-  alignas(16) uint16_t stage[2][64][kChunkDx];   // [parity][block][dx in chunk]
-  uint32_t sad64[kK][kChunkDx];
+  static constexpr int kCopyWords = kRows * kRowWords + 8;     // == 8 (mod 32): the 4 copies hit disjoint banks
+  static constexpr int kChunks = R / 8;                         // chunks of 16 dx: [-R, R); dx = +R is the last column
+  static constexpr int kIters = R / 4 + 1;                     // 8 tile rows each
+  static constexpr size_t kStageBytes = 8 * 64 * kChunkDx * 2;
+  static constexpr size_t kRawBytes = (size_t)kRows * kRawWords * 4;     // overlays the stage ring before the first iteration
+  static constexpr size_t kSmemBytes = (size_t)4 * kCopyWords * 4 + 64 * 64 + (kRawBytes > kStageBytes ? kRawBytes : kStageBytes);
+};
+
+struct SmemView {
+  uint32_t *tile;       // [4][kCopyWords]
+  uint8_t *cur;         // [64][64]
+  uint16_t *stage;      // [8][64][16]
+};
+
+// ---- compute: 8 tile rows of a normal chunk ----
+// PH 0: first iteration (rows 0..7: only products with u >= y exist, only dy 0 completes),
+// PH 1: middle, PH 2: last iteration (rows 2R..2R+7: only products with u <= y exist).
+template <int PH>
+__device__ __forceinline__ void rows8(const uint32_t *trow, const uint32_t (&cur)[8][2], uint32_t (&acc)[8][4],
+                                      uint16_t *stg /* &stage[0][blk][g] */)
+{
+#pragma unroll
+  for (int u = 0; u < 8; u++) {
+    const uint32_t *rp = trow + u * kRowWords;
+    const uint2 a = *reinterpret_cast<const uint2 *>(rp);
+    const uint2 b = *reinterpret_cast<const uint2 *>(rp + 2);
+    const uint32_t w[5] = { a.x, a.y, b.x, b.y, rp[4] };
+#pragma unroll
+    for (int y = 0; y < 8; y++) {
+      if (PH == 0 && u < y) continue;
+      if (PH == 2 && u > y) continue;
+      const int slot = (u - y) & 7;                 // accumulator of dy = 8m + u - y
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const uint32_t c0 = (y == 0) ? 0u : acc[slot][j];      // a new dy starts from the zero register
+        acc[slot][j] = sad4(cur[y][1], w[j + 1], sad4(cur[y][0], w[j], c0));
+      }
+    }
+    // dy = 8m + u - 7 is complete (always in PH 1/2; in PH 0 only for u == 7)
+    if (PH != 0 || u == 7) {
+      const int slot = (u + 1) & 7;
+      uint16_t *o = stg + u * (64 * kChunkDx);
+#pragma unroll
+      for (int j = 0; j < 4; j++) o[4 * j] = (uint16_t)acc[slot][j];
+    }
+  }
+}
+
+// ---- writer: the 8 dy rows finished by one iteration of a normal chunk ----
+// Per-thread output positions (element offsets; every map of a launch has < 2^31 entries).
+struct WriterPos {
+  uint32_t o8;        // sad8 entry of (blk, dy 0, first dx of this thread's half)
+  uint32_t o16, o32, o64;
+  uint32_t src8;      // u16 index of the thread's 8 dx inside a ring slot
+  uint32_t src16;     // u32 index of (first block of the 32x32 PU, dx pair) inside a ring slot
 };
 
 template <int R>
-__global__ void __launch_bounds__(kThreads, 3)
+__device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, int chunk, int tid)
+{
+  constexpr uint32_t K = Geo<R>::K;
+  const uint32_t rs = (uint32_t)p.map_pitch;
+  WriterPos w;
+  const int blk = (tid >> 1) & 63, half = tid & 1;
+  w.o8 = ((uint32_t)ctu * 64 + blk) * (K + 1) * rs + chunk * kChunkDx + half * 8;
+  w.src8 = stage_slot(blk) * kChunkDx + half * 8;
+  const int lane = tid & 31, p32 = lane >> 3, dxp = lane & 7;
+  const uint32_t col = chunk * kChunkDx + 2 * dxp;
+  w.o16 = ((uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2) * (K + 1) * rs + col;
+  w.o32 = ((uint32_t)ctu * 4 + p32) * (K + 1) * rs + col;
+  w.o64 = (uint32_t)ctu * (K + 1) * rs + col;
+  w.src16 = ((p32 >> 1) * 32 + (p32 & 1) * 4) * (kChunkDx / 2) + dxp;
+  return w;
+}
+
+template <int R>
+__device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPos &wp, const uint16_t *stage, int m, int tid)
+{
+  constexpr uint32_t K = Geo<R>::K;
+  const uint32_t rs = (uint32_t)p.map_pitch;
+  const int k0 = 8 * m - 7;                       // dy of ring slot 0
+  // (a) 8x8 map: thread = (block, half of the 16 dx), ring slots u0, u0+2, u0+4, u0+6
+  {
+    const int u0 = tid >> 7;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int u = u0 + 2 * i, k = k0 + u;
+      if (k >= 0)
+        *reinterpret_cast<uint4 *>(p.sad8 + wp.o8 + (uint32_t)k * rs) =
+            *reinterpret_cast<const uint4 *>(stage + u * (64 * kChunkDx) + wp.src8);
+    }
+  }
+  // (b) 16x16 / 32x32 / 64x64: thread = (ring slot, 32x32 PU, pair of dx)
+  {
+    const int u = tid >> 5, p32 = (tid >> 3) & 3;
+    const int k = k0 + u;
+    if (k >= 0) {                                   // uniform per warp
+      const uint32_t *st = reinterpret_cast<const uint32_t *>(stage) + u * (64 * kChunkDx / 2) + wp.src16;
+      const int sw = p32;                           // stage_slot() of the PU's blocks: low two bits ^ p32
+      uint32_t lo = 0, hi = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        // 16x16 PU q of the 32x32 PU: blocks (2(q>>1), 2(q&1)) + {0,1}x{0,1}
+        const int b = (q >> 1) * 16 + (q & 1) * 2;
+        // packed u16 pairs: 4 x 16320 < 65536, no carry between the halves
+        const uint32_t s16 = st[((b) ^ sw) * 8] + st[((b + 1) ^ sw) * 8] + st[((b + 8) ^ sw) * 8] + st[((b + 9) ^ sw) * 8];
+        *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * (K + 1) + (uint32_t)k) * rs) = s16;
+        lo += s16 & 0xFFFFu;
+        hi += s16 >> 16;
+      }
+      *reinterpret_cast<uint2 *>(p.sad32 + wp.o32 + (uint32_t)k * rs) = make_uint2(lo, hi);
+      lo += __shfl_xor_sync(0xffffffffu, lo, 8);  hi += __shfl_xor_sync(0xffffffffu, hi, 8);
+      lo += __shfl_xor_sync(0xffffffffu, lo, 16); hi += __shfl_xor_sync(0xffffffffu, hi, 16);
+      if (p32 == 0) *reinterpret_cast<uint2 *>(p.sad64 + wp.o64 + (uint32_t)k * rs) = make_uint2(lo, hi);
+    }
+  }
+}
+
+template <int R>
+__device__ __forceinline__ void stage_cur(const ImeSadParams &p, uint8_t *cur, int ctu_x, int ctu_y, int tid, int nthreads)
+{
+  // current CTU, coordinates clamped into the picture for partial CTUs
+  for (int i = tid; i < 64 * 8; i += nthreads) {
+    const int r = i >> 3, v = i & 7;
+    const int y = min(ctu_y + r, p.height - 1);
+    const int x = min(ctu_x + v * 8, p.width - 8);
+    *reinterpret_cast<uint2 *>(&cur[r * 64 + v * 8]) = *reinterpret_cast<const uint2 *>(p.cur + (size_t)y * p.cur_pitch + x);
+  }
+}
+
+#ifndef KVZ_SAD_MINB
+#define KVZ_SAD_MINB 2
+#endif
+// one CTA = 16 dx (one chunk) x all dy of one CTU
+template <int R>
+__global__ void __launch_bounds__(kThreads, KVZ_SAD_MINB)
 ime_sad_dense_kernel(ImeSadParams p)
 {
-  constexpr int K = 2 * R + 1;
-  constexpr int kGroupsValid = R / 2 + 1;            // groups of 4 dx; last holds dx == +R only
-  __shared__ Smem<R> sm;
-
-  const int chunk = blockIdx.x;
-  const int ctu = blockIdx.y;
-  const int ctu_cx = ctu % p.ctus_x, ctu_cy = ctu / p.ctus_x;
-  const int ctu_x = p.tile_x + ctu_cx * 64;          // frame-absolute luma position
-  const int ctu_y = p.tile_y + ctu_cy * 64;
+  constexpr int CW = Geo<R>::kCopyWords;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x;
-
-  // ---- stage the reference tile: rows ctu_y-R .. ctu_y+R+63, 80 bytes from
-  //      column ctu_x - R + 16*chunk of the border-replicated plane ----
+  constexpr int kChunks = Geo<R>::kChunks;
   {
-    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x - R + kChunkDx * chunk + p.pad);
-    constexpr int kVecPerRow = kTilePitch / 8;
-    // the window centre makes the source address arbitrary: fetch aligned words and realign
+    const int bid = blockIdx.x;
+    uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
+    uint8_t *cur_s = smem_raw + (size_t)4 * CW * 4;
+    uint16_t *stage = reinterpret_cast<uint16_t *>(cur_s + 64 * 64);
+    const int chunk = bid % kChunks, ctu = bid / kChunks;
+    const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
+    {
+      // tile rows ctu_y+cy-R .., 84 bytes from column ctu_x+cx-R+16*chunk, as 4 byte-shifted copies
+      const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch +
+                           (ctu_x + p.center_x - R + kChunkDx * chunk + p.pad);
+      const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
+      const int sh = (int)(a0 & 3) * 8;
+      const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
+      // (1) raw rows (22 aligned words each) straight into shared memory, all copies in flight at once
+      uint32_t *raw = reinterpret_cast<uint32_t *>(stage);
+      for (int i = tid; i < Geo<R>::kRows * kRawWords; i += kThreads) {
+        const int r = i / kRawWords, mw = i - r * kRawWords;
+        cp_async4(raw + i, src_al + (size_t)r * p.ref_pitch + 4 * mw);
+      }
+      stage_cur<R>(p, cur_s, ctu_x, ctu_y, tid, kThreads);
+      cp_async_wait_all();
+      __syncthreads();
+      // (2) the four byte-shifted copies
+      for (int i = tid; i < Geo<R>::kRows * kRowWords; i += kThreads) {
+        const int r = i / kRowWords, mw = i - r * kRowWords;
+        const uint32_t *w = raw + r * kRawWords + mw;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+        const uint32_t t0 = __funnelshift_r(w0, w1, sh), t1 = __funnelshift_r(w1, w2, sh);
+        tile[0 * CW + i] = t0;
+        tile[1 * CW + i] = __funnelshift_r(t0, t1, 8);
+        tile[2 * CW + i] = __funnelshift_r(t0, t1, 16);
+        tile[3 * CW + i] = __funnelshift_r(t0, t1, 24);
+      }
+    }
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31;
+    const int by = warp, bx = lane >> 2, g = lane & 3, blk = by * 8 + bx;
+    uint32_t cur[8][2];
+#pragma unroll
+    for (int y = 0; y < 8; y++) {
+      const uint2 v = *reinterpret_cast<const uint2 *>(&cur_s[(by * 8 + y) * 64 + bx * 8]);
+      cur[y][0] = v.x; cur[y][1] = v.y;
+    }
+    uint32_t acc[8][4];
+    const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
+    uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
+    const WriterPos wp = writer_pos<R>(p, ctu, chunk, tid);
+    rows8<0>(trow, cur, acc, stg);
+    __syncthreads();
+    write_rows<R>(p, wp, stage, 0, tid);
+    __syncthreads();
+    for (int m = 1; m < Geo<R>::kIters - 1; m++) {
+      rows8<1>(trow + m * 8 * kRowWords, cur, acc, stg);
+      __syncthreads();
+      write_rows<R>(p, wp, stage, m, tid);
+      __syncthreads();
+    }
+    rows8<2>(trow + (Geo<R>::kIters - 1) * 8 * kRowWords, cur, acc, stg);
+    __syncthreads();
+    write_rows<R>(p, wp, stage, Geo<R>::kIters - 1, tid);
+  }
+}
+
+// ---- the last column (dx = +R) of every map, stored as row K of each PU's map (entry dy + R) ----
+// One CTA per CTU; thread = (row of 8x8 blocks, dy) with dy along the lanes, so that the K entries of a
+// PU are written as one contiguous, fully covered row (a column of 2-byte entries at the row pitch
+// would cost a DRAM read-modify-write per entry).
+constexpr int kLcWords = 17;            // tile row pitch in words: odd, lanes (= rows) fall into distinct banks
+
+template <int R>
+struct LcSmem {
+  uint32_t tile[Geo<R>::kRows * kLcWords];
+  alignas(16) uint8_t cur[64 * 64];
+  uint4 part16[8][((2 * R + 1) + 15) & ~15];     // per block row: sums of horizontally adjacent 8x8 pairs
+  uint2 part32[4][((2 * R + 1) + 15) & ~15];     // per 16x16 row: sums of horizontally adjacent 16x16 pairs
+  uint32_t part64[2][((2 * R + 1) + 15) & ~15];
+};
+
+template <int R>
+__global__ void __launch_bounds__(kThreads)
+ime_sad_lastcol_kernel(ImeSadParams p)
+{
+  constexpr int K = Geo<R>::K;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  LcSmem<R> &sm = *reinterpret_cast<LcSmem<R> *>(smem_raw);
+  const int tid = threadIdx.x, ctu = blockIdx.x;
+  const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
+  const int rs = p.map_pitch;
+  {
+    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x + R + p.pad);
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
     const int sh = (int)(a0 & 3) * 8;
     const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
-    for (int i = tid; i < Smem<R>::kRows * kVecPerRow; i += kThreads) {
-      const int r = i / kVecPerRow, v = i % kVecPerRow;
-      const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch + v * 8);
-      const uint32_t w0 = w[0], w1 = w[1], w2 = sh ? w[2] : 0u;
-      *reinterpret_cast<uint2 *>(&sm.tile[r * kTilePitch + v * 8]) =
-          make_uint2(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh));
+#pragma unroll 4
+    for (int i = tid; i < Geo<R>::kRows * 16; i += kThreads) {
+      const int r = i >> 4, mw = i & 15;
+      const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch) + mw;
+      sm.tile[r * kLcWords + mw] = __funnelshift_r(w[0], w[1], sh);
     }
-    // current CTU, coordinates clamped into the picture for partial CTUs
-    for (int i = tid; i < 64 * 8; i += kThreads) {
-      const int r = i >> 3, v = i & 7;
-      const int y = min(ctu_y + r, p.height - 1);
-      const int x = min(ctu_x + v * 8, p.width - 8);
-      const uint2 val = *reinterpret_cast<const uint2 *>(p.cur + (size_t)y * p.cur_pitch + x);
-      *reinterpret_cast<uint2 *>(&sm.cur[r * 64 + v * 8]) = val;
-    }
-    for (int i = tid; i < K * kChunkDx; i += kThreads) (&sm.sad64[0][0])[i] = 0;
-    for (int i = tid; i < 2 * 64 * kChunkDx / 2; i += kThreads) reinterpret_cast<uint32_t *>(&sm.stage[0][0][0])[i] = 0;
+    stage_cur<R>(p, sm.cur, ctu_x, ctu_y, tid, kThreads);
   }
   __syncthreads();
-
-  // ---- thread role in the compute phase ----
-  const int warp = tid >> 5, lane = tid & 31;
-  const int by = warp;                 // 8 warps <-> 8 block rows of the CTU
-  const int bx = lane >> 2;            // 8 blocks per row
-  const int gl = lane & 3;             // dx group inside the chunk
-  const int g = chunk * 4 + gl;
-  const int blk = by * 8 + bx;
-  const bool blk_valid = (ctu_x + bx * 8 + 8 <= p.tile_x + p.tile_w) && (ctu_y + by * 8 + 8 <= p.tile_y + p.tile_h);
-  const bool active = blk_valid && g < kGroupsValid;
-
-  uint32_t cur[8][2];
+  // 8x8: item = (block row by, entry k); entries K .. pitch-1 of the row are written as zero
+  for (int item = tid; item < 8 * rs; item += kThreads) {
+    const int by = item / rs, k = item - by * rs;
+    uint32_t s8[8];
 #pragma unroll
-  for (int y = 0; y < 8; y++) {
-    const uint2 v = *reinterpret_cast<const uint2 *>(&sm.cur[(by * 8 + y) * 64 + bx * 8]);
-    cur[y][0] = v.x; cur[y][1] = v.y;
-  }
-  uint32_t acc[8][4];
-#pragma unroll
-  for (int s = 0; s < 8; s++)
-#pragma unroll
-    for (int f = 0; f < 4; f++) acc[s][f] = 0;
-
-  const uint8_t *rowp = &sm.tile[(by * 8) * kTilePitch + bx * 8 + gl * 4];
-  // global destinations
-  const size_t pu8 = (size_t)ctu * 64 + blk;
-  uint16_t *out8 = p.sad8 + pu8 * K * p.map_pitch + g * 4;
-
-  // reduction role (threads of 4 warps; which 4 alternates with k parity)
-  const int rwarp = warp & 3;          // p32 index: (p32x, p32y)
-  const int qx = lane >> 4, dxl = lane & 15;
-  const int p16x = 2 * (rwarp & 1) + qx;
-  const int p16y0 = 2 * (rwarp >> 1);
-  uint16_t *out16a = p.sad16 + ((size_t)ctu * 16 + (p16y0 + 0) * 4 + p16x) * K * p.map_pitch + chunk * kChunkDx + dxl;
-  uint16_t *out16b = p.sad16 + ((size_t)ctu * 16 + (p16y0 + 1) * 4 + p16x) * K * p.map_pitch + chunk * kChunkDx + dxl;
-  uint32_t *out32 = p.sad32 + ((size_t)ctu * 4 + rwarp) * K * p.map_pitch + chunk * kChunkDx + dxl;
-
-  constexpr int kIters = (2 * R + 8) / 8;
-  for (int m = 0; m < kIters; m++) {
-#pragma unroll
-    for (int u = 0; u < 8; u++) {
-      const int s = m * 8 + u;
-      if (active) {
-        const uint8_t *rp = rowp + s * kTilePitch;
-        const uint32_t w0 = *reinterpret_cast<const uint32_t *>(rp);
-        const uint32_t w1 = *reinterpret_cast<const uint32_t *>(rp + 4);
-        const uint32_t w2 = *reinterpret_cast<const uint32_t *>(rp + 8);
-        uint32_t lo[4], hi[4];
-        lo[0] = w0; hi[0] = w1;
-#pragma unroll
-        for (int f = 1; f < 4; f++) {
-          lo[f] = __funnelshift_r(w0, w1, 8 * f);
-          hi[f] = __funnelshift_r(w1, w2, 8 * f);
-        }
+    for (int bx = 0; bx < 8; bx++) {
+      uint32_t acc = 0;
+      if (k < K) {
 #pragma unroll
         for (int y = 0; y < 8; y++) {
-          const int slot = (u - y) & 7;          // accumulator of k = s - y
-#pragma unroll
-          for (int f = 0; f < 4; f++) {
-            acc[slot][f] = sad4(cur[y][0], lo[f], acc[slot][f]);
-            acc[slot][f] = sad4(cur[y][1], hi[f], acc[slot][f]);
-          }
+          const uint2 c = *reinterpret_cast<const uint2 *>(&sm.cur[(by * 8 + y) * 64 + bx * 8]);
+          const uint32_t *t = &sm.tile[(by * 8 + y + k) * kLcWords + 2 * bx];
+          acc = sad4(c.y, t[1], sad4(c.x, t[0], acc));
         }
       }
-      // row k = s - 7 is complete
-      const int k = s - 7;
-      const int slot = (u + 1) & 7;
-      if (k >= 0 && k < K) {               // uniform across the CTA
-        const uint32_t v0 = acc[slot][0] | (acc[slot][1] << 16);
-        const uint32_t v1 = acc[slot][2] | (acc[slot][3] << 16);
-        const int par = k & 1;
-        if (active) {
-          *reinterpret_cast<uint2 *>(out8 + (size_t)k * p.map_pitch) = make_uint2(v0, v1);
-          *reinterpret_cast<uint2 *>(&sm.stage[par][blk][gl * 4]) = make_uint2(v0, v1);
-        }
-        __syncthreads();
-        if ((warp >> 2) == par) {
-          // SAD16 of two vertically adjacent 16x16 PUs, then 32x32, then 64x64
-          const uint16_t (*st)[kChunkDx] = sm.stage[par];
-          const int b0 = (2 * p16y0) * 8 + 2 * p16x;
-          const uint32_t a = (uint32_t)st[b0][dxl] + st[b0 + 1][dxl] + st[b0 + 8][dxl] + st[b0 + 9][dxl];
-          const uint32_t b = (uint32_t)st[b0 + 16][dxl] + st[b0 + 17][dxl] + st[b0 + 24][dxl] + st[b0 + 25][dxl];
-          out16a[(size_t)k * p.map_pitch] = (uint16_t)a;
-          out16b[(size_t)k * p.map_pitch] = (uint16_t)b;
-          uint32_t s32 = a + b;
-          s32 += __shfl_xor_sync(0xffffffffu, s32, 16);
-          if (lane < 16) {
-            out32[(size_t)k * p.map_pitch] = s32;
-            atomicAdd(&sm.sad64[k][dxl], s32);
-          }
-        }
-      }
-#pragma unroll
-      for (int f = 0; f < 4; f++) acc[slot][f] = 0;
+      s8[bx] = acc;
+      p.sad8[(((size_t)ctu * 64 + by * 8 + bx) * (K + 1) + K) * rs + k] = (uint16_t)acc;
     }
+    sm.part16[by][k] = make_uint4(s8[0] + s8[1], s8[2] + s8[3], s8[4] + s8[5], s8[6] + s8[7]);
   }
   __syncthreads();
-  // flush the 64x64 sums
-  uint32_t *out64 = p.sad64 + (size_t)ctu * K * p.map_pitch + chunk * kChunkDx;
-  for (int i = tid; i < K * kChunkDx; i += kThreads) {
-    const int k = i / kChunkDx, d = i % kChunkDx;
-    out64[(size_t)k * p.map_pitch + d] = sm.sad64[k][d];
+  for (int item = tid; item < 4 * rs; item += kThreads) {
+    const int r16 = item / rs, k = item - r16 * rs;
+    const uint4 a = sm.part16[2 * r16][k], b = sm.part16[2 * r16 + 1][k];
+    const uint32_t s16[4] = { a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w };
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+      p.sad16[(((size_t)ctu * 16 + r16 * 4 + q) * (K + 1) + K) * rs + k] = (uint16_t)s16[q];
+    sm.part32[r16][k] = make_uint2(s16[0] + s16[1], s16[2] + s16[3]);
   }
+  __syncthreads();
+  for (int item = tid; item < 2 * rs; item += kThreads) {
+    const int r32 = item / rs, k = item - r32 * rs;
+    const uint2 a = sm.part32[2 * r32][k], b = sm.part32[2 * r32 + 1][k];
+    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 0) * (K + 1) + K) * rs + k] = a.x + b.x;
+    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 1) * (K + 1) + K) * rs + k] = a.y + b.y;
+    sm.part64[r32][k] = a.x + b.x + a.y + b.y;
+  }
+  __syncthreads();
+  for (int k = tid; k < rs; k += kThreads)
+    p.sad64[((size_t)ctu * (K + 1) + K) * rs + k] = sm.part64[0][k] + sm.part64[1][k];
 }
 
 // ---- replicate-pad a plane (image.c:320-452 == clamp-to-edge) ----
@@ -234,19 +384,32 @@ int launch_pad_plane(const void *src, int w, int h, int src_pitch, void *dst, in
   return 1;
 }
 
+template <int R>
+static int launch_r(const ImeSadParams &p, cudaStream_t stream)
+{
+  auto kern = ime_sad_dense_kernel<R>;
+  KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Geo<R>::kSmemBytes));
+  const int n_ctu = p.ctus_x * p.ctus_y;
+  kern<<<Geo<R>::kChunks * n_ctu, kThreads, Geo<R>::kSmemBytes, stream>>>(p);       // R/8 chunks of 16 dx per CTU
+  count_launch();
+  auto kern_lc = ime_sad_lastcol_kernel<R>;
+  KVZ_CUDA_TRY(cudaFuncSetAttribute(kern_lc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcSmem<R>)));
+  kern_lc<<<n_ctu, kThreads, sizeof(LcSmem<R>), stream>>>(p);                         // dx = +R
+  count_launch();
+  return 1;
+}
+
 int launch_ime_sad_dense(const ImeSadParams &p, int range, cudaStream_t stream)
 {
-  const int groups = range / 2 + 1;
-  const int chunks = (groups + 3) / 4;
-  dim3 grid(chunks, p.ctus_x * p.ctus_y);
+  int ok;
   switch (range) {
-    case 8:  ime_sad_dense_kernel<8><<<grid, kThreads, 0, stream>>>(p); break;
-    case 16: ime_sad_dense_kernel<16><<<grid, kThreads, 0, stream>>>(p); break;
-    case 32: ime_sad_dense_kernel<32><<<grid, kThreads, 0, stream>>>(p); break;
-    case 64: ime_sad_dense_kernel<64><<<grid, kThreads, 0, stream>>>(p); break;
+    case 8:  ok = launch_r<8>(p, stream); break;
+    case 16: ok = launch_r<16>(p, stream); break;
+    case 32: ok = launch_r<32>(p, stream); break;
+    case 64: ok = launch_r<64>(p, stream); break;
     default: return fail_msg("ime_sad_dense: range must be 8, 16, 32 or 64");
   }
-  count_launch();
+  if (!ok) return 0;
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
 }

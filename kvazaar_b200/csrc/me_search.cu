@@ -307,8 +307,8 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       for (int q = 0; q < 5; q++)
         hv[q] = (q < n_hit && (sm.hit_pos[q] % K) < K - 1) ? (sm.hit_pos[q] / K) * vpr + ((sm.hit_pos[q] % K) >> 3) : -1;
       const bool fast = free_mv;
-      const uint16_t *map16 = (level == 0 ? ms.sad8 : ms.sad16) + prow * K * f.map_pitch;
-      const uint32_t *map32 = (level == 2 ? ms.sad32 : ms.sad64) + prow * K * f.map_pitch;
+      const uint16_t *map16 = (level == 0 ? ms.sad8 : ms.sad16) + prow * (K + 1) * f.map_pitch;
+      const uint32_t *map32 = (level == 2 ? ms.sad32 : ms.sad64) + prow * (K + 1) * f.map_pitch;
       for (int i = g.tid; i < K * vpr; i += G) {
         const int row = i / vpr, c0 = (i - row * vpr) * 8;
         uint32_t sad[8];
@@ -341,8 +341,8 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       }
       // last column
       for (int row = g.tid; row < K; row += G) {
-        const uint32_t sad = level < 2 ? (uint32_t)__ldg(map16 + (size_t)row * f.map_pitch + K - 1)
-                                       : __ldg(map32 + (size_t)row * f.map_pitch + K - 1);
+        const uint32_t sad = level < 2 ? (uint32_t)__ldg(map16 + (size_t)K * f.map_pitch + row)   // row K = column dx = +R
+                                       : __ldg(map32 + (size_t)K * f.map_pitch + row);
         consider(row, K - 1, sad);
       }
       if (wbest != 0xFFFFFFFFu) {

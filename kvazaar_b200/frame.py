@@ -45,7 +45,9 @@ class ImeSearch:
     """Dense integer motion estimation of one picture against one reference.
 
     Owns the four SAD maps (8x8, 16x16, 32x32, 64x64 PUs) for a picture size and
-    search range; `run` fills them with one kernel launch.
+    search range; `run` fills them (kvz_cuda_ime_sad_maps).  A PU's map is K + 1 rows of
+    `map_pitch` entries: rows 0..K-1 hold dx = -R..R-1 of each dy, row K holds the column
+    dx = +R (entry dy + R) -- see include/kvz_cuda.h; `window()` undoes that.
     """
 
     def __init__(self, width, height, rng=32, bitdepth=8, tile=None, device="cuda", max_center=0):
@@ -63,7 +65,7 @@ class ImeSearch:
         for level in range(4):
             n = 8 >> level
             dt = torch.int16 if level < 2 else torch.int32
-            self.maps.append(torch.empty((n_ctu * n * n, self.k, self.map_pitch), dtype=dt, device=device))
+            self.maps.append(torch.empty((n_ctu * n * n, self.k + 1, self.map_pitch), dtype=dt, device=device))
         self.desc = capi.ImeDesc()
 
     def run(self, cur, ref_padded, center=(0, 0), maps=None):
@@ -84,6 +86,14 @@ class ImeSearch:
             C.c_void_p(self.maps[2].data_ptr()), C.c_void_p(self.maps[3].data_ptr()), _stream_ptr()),
             "kvz_cuda_ime_sad_maps")
         return self.maps
+
+    @staticmethod
+    def window(m):
+        """(..., K + 1, pitch) map storage (torch or numpy) -> (..., K, K) window, [dy + R, dx + R]."""
+        k = m.shape[-2] - 1
+        out = m[..., :k, :k].clone() if isinstance(m, torch.Tensor) else m[..., :k, :k].copy()
+        out[..., :, k - 1] = m[..., k, :k]
+        return out
 
     def pu_index(self, level, x, y):
         """Map row of the PU of size 8<<level whose top-left luma sample is (x, y)

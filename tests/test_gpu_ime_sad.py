@@ -41,7 +41,7 @@ def _maps_vs_oracle(width, height, rng_, pic, ref, sample_pus=None, seed=0, cent
                         want[(dy + rng_) * k + dx + rng_] = O.kvzo_image_sad_8(
                             ptr(pic), ptr(ref), width, height, x, y, x + center[0] + dx, y + center[1] + dy, size, size)
             row = srch.pu_index(level, x, y)
-            got = maps[level][row][:, :k].astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
+            got = kb.ImeSearch.window(maps[level][row]).astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
             assert np.array_equal(got, want.reshape(k, k)), (level, x, y)
             checked += 1
     return checked
@@ -102,10 +102,10 @@ def test_hierarchy_property_1080p():
     # only CTUs fully inside the picture carry all four levels
     full = [cy * srch.ctus_x + cx for cy in range(h // 64) for cx in range(w // 64)]
     full_t = torch.tensor(full, device="cuda")
-    prev = (maps[0].view(n_ctu, 8, 8, k, -1)[full_t][..., :k].to(torch.int64) & 0xFFFF)
+    prev = (kb.ImeSearch.window(maps[0].view(n_ctu, 8, 8, k + 1, -1)[full_t]).to(torch.int64) & 0xFFFF)
     for level in range(1, 4):
         n = 8 >> level
-        cur = maps[level].view(n_ctu, n, n, k, -1)[full_t][..., :k].to(torch.int64)
+        cur = kb.ImeSearch.window(maps[level].view(n_ctu, n, n, k + 1, -1)[full_t]).to(torch.int64)
         cur = cur & (0xFFFF if level < 2 else 0xFFFFFFFF)
         s = prev.view(len(full), n, 2, n, 2, k, k).sum(dim=(2, 4))
         assert torch.equal(s, cur), level
