@@ -44,7 +44,7 @@ def test_map_geometry_helpers():
                      tile_w=1920, tile_h=1080)
     import ctypes as C
     assert kb.lib().kvz_cuda_ime_map_bytes(C.byref(d), 0) == 510 * 64 * 66 * 80 * 2   # K + 1 rows per PU: row K is the column dx = +R
-    assert kb.lib().kvz_cuda_ime_map_bytes(C.byref(d), 3) == 510 * 65 * 80 * 4
+    assert kb.lib().kvz_cuda_ime_map_bytes(C.byref(d), 3) == 510 * 66 * 80 * 4
 
 
 def _declared_strategy_symbols():
