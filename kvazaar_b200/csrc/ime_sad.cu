@@ -196,10 +196,91 @@ __device__ __forceinline__ void stage_cur(const ImeSadParams &p, uint8_t *cur, i
   }
 }
 
+// ---- the last column (dx = +R) of every map, stored as row K of each PU's map (entry dy + R) ----
+// One CTA per CTU; thread = (row of 8x8 blocks, dy) with dy along the lanes, so that the K entries of a
+// PU are written as one contiguous, fully covered row (a column of 2-byte entries at the row pitch
+// would cost a DRAM read-modify-write per entry).
+constexpr int kLcWords = 17;            // tile row pitch in words: odd, lanes (= rows) fall into distinct banks
+
+template <int R>
+struct LcSmem {
+  uint32_t tile[Geo<R>::kRows * kLcWords];
+  alignas(16) uint8_t cur[64 * 64];
+  uint4 part16[8][((2 * R + 1) + 15) & ~15];     // per block row: sums of horizontally adjacent 8x8 pairs
+  uint2 part32[4][((2 * R + 1) + 15) & ~15];     // per 16x16 row: sums of horizontally adjacent 16x16 pairs
+  uint32_t part64[2][((2 * R + 1) + 15) & ~15];
+};
+
+template <int R>
+__device__ __forceinline__ void last_column(const ImeSadParams &p, unsigned char *smem_raw, int ctu)
+{
+  constexpr int K = Geo<R>::K;
+  LcSmem<R> &sm = *reinterpret_cast<LcSmem<R> *>(smem_raw);
+  const int tid = threadIdx.x;
+  const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
+  const int rs = p.map_pitch;
+  {
+    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x + R + p.pad);
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
+    const int sh = (int)(a0 & 3) * 8;
+    const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
+#pragma unroll 4
+    for (int i = tid; i < Geo<R>::kRows * 16; i += kThreads) {
+      const int r = i >> 4, mw = i & 15;
+      const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch) + mw;
+      sm.tile[r * kLcWords + mw] = __funnelshift_r(w[0], w[1], sh);
+    }
+    stage_cur<R>(p, sm.cur, ctu_x, ctu_y, tid, kThreads);
+  }
+  __syncthreads();
+  // 8x8: item = (block row by, entry k); entries K .. pitch-1 of the row are written as zero
+  for (int item = tid; item < 8 * rs; item += kThreads) {
+    const int by = item / rs, k = item - by * rs;
+    uint32_t s8[8];
+#pragma unroll
+    for (int bx = 0; bx < 8; bx++) {
+      uint32_t acc = 0;
+      if (k < K) {
+#pragma unroll
+        for (int y = 0; y < 8; y++) {
+          const uint2 c = *reinterpret_cast<const uint2 *>(&sm.cur[(by * 8 + y) * 64 + bx * 8]);
+          const uint32_t *t = &sm.tile[(by * 8 + y + k) * kLcWords + 2 * bx];
+          acc = sad4(c.y, t[1], sad4(c.x, t[0], acc));
+        }
+      }
+      s8[bx] = acc;
+      p.sad8[(((size_t)ctu * 64 + by * 8 + bx) * (K + 1) + K) * rs + k] = (uint16_t)acc;
+    }
+    sm.part16[by][k] = make_uint4(s8[0] + s8[1], s8[2] + s8[3], s8[4] + s8[5], s8[6] + s8[7]);
+  }
+  __syncthreads();
+  for (int item = tid; item < 4 * rs; item += kThreads) {
+    const int r16 = item / rs, k = item - r16 * rs;
+    const uint4 a = sm.part16[2 * r16][k], b = sm.part16[2 * r16 + 1][k];
+    const uint32_t s16[4] = { a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w };
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+      p.sad16[(((size_t)ctu * 16 + r16 * 4 + q) * (K + 1) + K) * rs + k] = (uint16_t)s16[q];
+    sm.part32[r16][k] = make_uint2(s16[0] + s16[1], s16[2] + s16[3]);
+  }
+  __syncthreads();
+  for (int item = tid; item < 2 * rs; item += kThreads) {
+    const int r32 = item / rs, k = item - r32 * rs;
+    const uint2 a = sm.part32[2 * r32][k], b = sm.part32[2 * r32 + 1][k];
+    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 0) * (K + 1) + K) * rs + k] = a.x + b.x;
+    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 1) * (K + 1) + K) * rs + k] = a.y + b.y;
+    sm.part64[r32][k] = a.x + b.x + a.y + b.y;
+  }
+  __syncthreads();
+  for (int k = tid; k < rs; k += kThreads)
+    p.sad64[((size_t)ctu * (K + 1) + K) * rs + k] = sm.part64[0][k] + sm.part64[1][k];
+}
+
 #ifndef KVZ_SAD_MINB
 #define KVZ_SAD_MINB 2
 #endif
-// one CTA = 16 dx (one chunk) x all dy of one CTU
+// one CTA = 16 dx (one chunk) x all dy of one CTU; the first n_ctu CTAs do the last column instead
+// (they are short and latency bound: started first, they overlap the rest)
 template <int R>
 __global__ void __launch_bounds__(kThreads, KVZ_SAD_MINB)
 ime_sad_dense_kernel(ImeSadParams p)
@@ -208,8 +289,11 @@ ime_sad_dense_kernel(ImeSadParams p)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x;
   constexpr int kChunks = Geo<R>::kChunks;
-  {
-    const int bid = blockIdx.x;
+  const int n_ctu = p.ctus_x * p.ctus_y;
+  if ((int)blockIdx.x < n_ctu) {
+    last_column<R>(p, smem_raw, blockIdx.x);
+  } else {
+    const int bid = blockIdx.x - n_ctu;
     uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
     uint8_t *cur_s = smem_raw + (size_t)4 * CW * 4;
     uint16_t *stage = reinterpret_cast<uint16_t *>(cur_s + 64 * 64);
@@ -272,88 +356,6 @@ ime_sad_dense_kernel(ImeSadParams p)
   }
 }
 
-// ---- the last column (dx = +R) of every map, stored as row K of each PU's map (entry dy + R) ----
-// One CTA per CTU; thread = (row of 8x8 blocks, dy) with dy along the lanes, so that the K entries of a
-// PU are written as one contiguous, fully covered row (a column of 2-byte entries at the row pitch
-// would cost a DRAM read-modify-write per entry).
-constexpr int kLcWords = 17;            // tile row pitch in words: odd, lanes (= rows) fall into distinct banks
-
-template <int R>
-struct LcSmem {
-  uint32_t tile[Geo<R>::kRows * kLcWords];
-  alignas(16) uint8_t cur[64 * 64];
-  uint4 part16[8][((2 * R + 1) + 15) & ~15];     // per block row: sums of horizontally adjacent 8x8 pairs
-  uint2 part32[4][((2 * R + 1) + 15) & ~15];     // per 16x16 row: sums of horizontally adjacent 16x16 pairs
-  uint32_t part64[2][((2 * R + 1) + 15) & ~15];
-};
-
-template <int R>
-__global__ void __launch_bounds__(kThreads)
-ime_sad_lastcol_kernel(ImeSadParams p)
-{
-  constexpr int K = Geo<R>::K;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  LcSmem<R> &sm = *reinterpret_cast<LcSmem<R> *>(smem_raw);
-  const int tid = threadIdx.x, ctu = blockIdx.x;
-  const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
-  const int rs = p.map_pitch;
-  {
-    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x + R + p.pad);
-    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
-    const int sh = (int)(a0 & 3) * 8;
-    const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
-#pragma unroll 4
-    for (int i = tid; i < Geo<R>::kRows * 16; i += kThreads) {
-      const int r = i >> 4, mw = i & 15;
-      const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch) + mw;
-      sm.tile[r * kLcWords + mw] = __funnelshift_r(w[0], w[1], sh);
-    }
-    stage_cur<R>(p, sm.cur, ctu_x, ctu_y, tid, kThreads);
-  }
-  __syncthreads();
-  // 8x8: item = (block row by, entry k); entries K .. pitch-1 of the row are written as zero
-  for (int item = tid; item < 8 * rs; item += kThreads) {
-    const int by = item / rs, k = item - by * rs;
-    uint32_t s8[8];
-#pragma unroll
-    for (int bx = 0; bx < 8; bx++) {
-      uint32_t acc = 0;
-      if (k < K) {
-#pragma unroll
-        for (int y = 0; y < 8; y++) {
-          const uint2 c = *reinterpret_cast<const uint2 *>(&sm.cur[(by * 8 + y) * 64 + bx * 8]);
-          const uint32_t *t = &sm.tile[(by * 8 + y + k) * kLcWords + 2 * bx];
-          acc = sad4(c.y, t[1], sad4(c.x, t[0], acc));
-        }
-      }
-      s8[bx] = acc;
-      p.sad8[(((size_t)ctu * 64 + by * 8 + bx) * (K + 1) + K) * rs + k] = (uint16_t)acc;
-    }
-    sm.part16[by][k] = make_uint4(s8[0] + s8[1], s8[2] + s8[3], s8[4] + s8[5], s8[6] + s8[7]);
-  }
-  __syncthreads();
-  for (int item = tid; item < 4 * rs; item += kThreads) {
-    const int r16 = item / rs, k = item - r16 * rs;
-    const uint4 a = sm.part16[2 * r16][k], b = sm.part16[2 * r16 + 1][k];
-    const uint32_t s16[4] = { a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w };
-#pragma unroll
-    for (int q = 0; q < 4; q++)
-      p.sad16[(((size_t)ctu * 16 + r16 * 4 + q) * (K + 1) + K) * rs + k] = (uint16_t)s16[q];
-    sm.part32[r16][k] = make_uint2(s16[0] + s16[1], s16[2] + s16[3]);
-  }
-  __syncthreads();
-  for (int item = tid; item < 2 * rs; item += kThreads) {
-    const int r32 = item / rs, k = item - r32 * rs;
-    const uint2 a = sm.part32[2 * r32][k], b = sm.part32[2 * r32 + 1][k];
-    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 0) * (K + 1) + K) * rs + k] = a.x + b.x;
-    p.sad32[(((size_t)ctu * 4 + r32 * 2 + 1) * (K + 1) + K) * rs + k] = a.y + b.y;
-    sm.part64[r32][k] = a.x + b.x + a.y + b.y;
-  }
-  __syncthreads();
-  for (int k = tid; k < rs; k += kThreads)
-    p.sad64[((size_t)ctu * (K + 1) + K) * rs + k] = sm.part64[0][k] + sm.part64[1][k];
-}
-
 // ---- replicate-pad a plane (image.c:320-452 == clamp-to-edge) ----
 template <typename PIX>
 __global__ void pad_plane_kernel(const PIX *src, int w, int h, int src_pitch, PIX *dst, int pad, int dst_pitch)
@@ -390,11 +392,8 @@ static int launch_r(const ImeSadParams &p, cudaStream_t stream)
   auto kern = ime_sad_dense_kernel<R>;
   KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Geo<R>::kSmemBytes));
   const int n_ctu = p.ctus_x * p.ctus_y;
-  kern<<<Geo<R>::kChunks * n_ctu, kThreads, Geo<R>::kSmemBytes, stream>>>(p);       // R/8 chunks of 16 dx per CTU
-  count_launch();
-  auto kern_lc = ime_sad_lastcol_kernel<R>;
-  KVZ_CUDA_TRY(cudaFuncSetAttribute(kern_lc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcSmem<R>)));
-  kern_lc<<<n_ctu, kThreads, sizeof(LcSmem<R>), stream>>>(p);                         // dx = +R
+  static_assert(sizeof(LcSmem<R>) <= Geo<R>::kSmemBytes, "last-column CTAs share the launch's shared memory size");
+  kern<<<(Geo<R>::kChunks + 1) * n_ctu, kThreads, Geo<R>::kSmemBytes, stream>>>(p);   // per CTU: dx = +R, then R/8 chunks of 16 dx
   count_launch();
   return 1;
 }
