@@ -3,26 +3,25 @@
 // Per-PU motion decision on device: for every PU of a batch and every reference
 // picture it is searched against, reproduce search_pu_inter_ref()
 // (search_inter.c:1134-1297) minus the candidate derivation (the AMVP / merge
-// candidates are inputs):
+// candidates are inputs).  Two kernels:
 //
-//   1. integer search = search_mv_full (search_inter.c:886-956): the zero
-//      window is read from the dense SAD maps of ime_sad.cu; the windows round
-//      the previous-frame vector and the merge candidates are evaluated on
-//      demand from the border-replicated reference plane.  Every candidate costs
-//      SAD + calc_mvd_cost (search_inter.c:373-412) and the winner is the FIRST
-//      candidate in the reference's visiting order with the smallest cost
-//      (check_mv_cost accepts on strict '<', search_inter.c:195-232), which is a
-//      lexicographic arg-min over (cost, window, row, column);
-//   2. fractional refinement = search_frac (search_inter.c:965-1128): the 8-tap
-//      filters of kvz_filter_{hpel,qpel}_blocks_*_luma (ipol-generic.c:192-658,
-//      int16 intermediates included) and kvz_satd_any_size_quad, four candidates
-//      per step, gated by `best_cost < *inter_cost` carried across the reference
-//      loop of search_pu_inter (search_inter.c:1505-1511); otherwise SATD at the
-//      integer vector (search_inter.c:1244-1256);
-//   3. merge-index match and select_mv_cand (search_inter.c:1258-1297).
-//
-// One thread GROUP works on one PU: a warp for PUs up to 16x16 (four PUs per
-// CTA), the whole 128-thread CTA for larger ones.
+//   me_scan_kernel   integer search = search_mv_full (search_inter.c:886-956), one warp per
+//      (PU, reference) job -- the jobs of a PU do not depend on each other here.  Windows
+//      whose centre has a dense SAD map set (ime_sad.cu) are read from it, the others are
+//      evaluated on demand from the border-replicated reference plane.  Every candidate
+//      costs SAD + calc_mvd_cost (search_inter.c:373-412) and the winner is the FIRST
+//      candidate in the reference's visiting order with the smallest cost (check_mv_cost
+//      accepts on strict '<', search_inter.c:195-232): a lexicographic arg-min over
+//      (cost, window, row, column).  The winner is parked in the job's result record.
+//   me_refine_kernel  per PU, references in order (the `*inter_cost` carry of
+//      search_pu_inter, search_inter.c:1505-1511, makes this part sequential):
+//      fractional refinement = search_frac (search_inter.c:965-1128) with the 8-tap
+//      filters of kvz_filter_{hpel,qpel}_blocks_*_luma (ipol-generic.c:192-658, int16
+//      intermediates included) and kvz_satd_any_size_quad, four candidates per step,
+//      gated by `best_cost < *inter_cost`; otherwise SATD at the integer vector
+//      (search_inter.c:1244-1256); then the merge-index match and select_mv_cand
+//      (search_inter.c:1258-1297).  A warp works on a PU up to 16x16 (four PUs per
+//      CTA), the whole 128-thread CTA on a larger one.
 #include "common.cuh"
 #include "me_search.cuh"
 #include "satd.cuh"
@@ -39,9 +38,34 @@ __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c)
   return d;
 }
 
-__device__ __constant__ int8_t c_luma_fir[4][8] = {       // HEVC luma DCT-IF (filter.c:54-60)
-  { 0, 0, 0, 64, 0, 0, 0, 0 }, { -1, 4, -10, 58, 17, -5, 1, 0 },
-  { -1, 4, -11, 40, 40, -11, 4, -1 }, { 0, 1, -5, 17, 58, -10, 4, -1 } };
+// HEVC luma DCT-IF (filter.c:54-60): { 0, 0, 0, 64, 0, 0, 0, 0 }, { -1, 4, -10, 58, 17, -5, 1, 0 },
+// { -1, 4, -11, 40, 40, -11, 4, -1 }, { 0, 1, -5, 17, 58, -10, 4, -1 }, packed as signed bytes
+// (t0..t3) and (t4..t7) for dp4a / dp2a
+#define KVZ_PACK4(a, b, c, d) ((uint32_t)((a) & 0xFF) | ((uint32_t)((b) & 0xFF) << 8) | ((uint32_t)((c) & 0xFF) << 16) | ((uint32_t)((d) & 0xFF) << 24))
+__device__ __constant__ uint32_t c_fir4[4][2] = {
+  { KVZ_PACK4(0, 0, 0, 64), KVZ_PACK4(0, 0, 0, 0) }, { KVZ_PACK4(-1, 4, -10, 58), KVZ_PACK4(17, -5, 1, 0) },
+  { KVZ_PACK4(-1, 4, -11, 40), KVZ_PACK4(40, -11, 4, -1) }, { KVZ_PACK4(0, 1, -5, 17), KVZ_PACK4(58, -10, 4, -1) } };
+
+// c + sum of 4 (unsigned byte of a) x (signed byte of b)
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c)
+{
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+// c + a.lo16 * b.byte0 + a.hi16 * b.byte1   (signed), and the same with bytes 2, 3
+__device__ __forceinline__ int dp2a_lo_ss(uint32_t a, uint32_t b, int c)
+{
+  int d;
+  asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_ss(uint32_t a, uint32_t b, int c)
+{
+  int d;
+  asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
 
 // 2*floor(log2(v+2)): get_ep_ex_golomb_bitcost (search_inter.c:235-253)
 __device__ __forceinline__ uint32_t golomb_bits(uint32_t v) { return 2u * (31u - __clz(v + 2u)); }
@@ -60,18 +84,43 @@ struct Group {
   }
 };
 
+__device__ __forceinline__ uint32_t pack_mv(int x, int y) { return ((uint32_t)x << 16) | ((uint32_t)y & 0xFFFFu); }
+
 struct JobCtx {
-  // PU
-  int x, y, w, h;            // tile-relative origin, size
+  int x, y, w, h;            // PU: tile-relative origin, size
   int ref_idx;
   int16_t mv_cand[2][2];
-  int n_merge;
-  const kvz_cuda_merge_cand *merge;
   int lambda;
+  // merge candidates that point into this reference with one vector (inter_merge_cand_t, dir != 3):
+  // packed quarter-pel vector of candidate i, valid if bit i of mvalid
+  uint32_t mkey[5];
+  uint32_t mvalid;
 };
 
+__device__ __forceinline__ void make_ctx(JobCtx &j, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                                         const kvz_cuda_me_job &job)
+{
+  j.x = pu.x; j.y = pu.y; j.w = pu.w; j.h = pu.h;
+  j.ref_idx = job.ref_idx;
+  j.mv_cand[0][0] = job.mv_cand[0][0]; j.mv_cand[0][1] = job.mv_cand[0][1];
+  j.mv_cand[1][0] = job.mv_cand[1][0]; j.mv_cand[1][1] = job.mv_cand[1][1];
+  j.lambda = f.lambda_sqrt_i;
+  j.mvalid = 0;
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    j.mkey[i] = 0;
+    if (i < pu.num_merge_cand) {
+      const kvz_cuda_merge_cand m = merge[i];
+      if (m.dir != 3 && f.ref_LX[m.dir - 1][m.ref[m.dir - 1]] == job.ref_idx) {
+        j.mkey[i] = pack_mv(m.mv[m.dir - 1][0], m.mv[m.dir - 1][1]);
+        j.mvalid |= 1u << i;
+      }
+    }
+  }
+}
+
 // fracmv_within_tile (search_inter.c:87-172); x,y quarter-pel
-__device__ bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
+__device__ __noinline__ bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
 {
   const bool frac_luma = (x % 4 != 0) || (y % 4 != 0);
   const bool frac_chroma = (x % 8 != 0) || (y % 8 != 0);
@@ -95,26 +144,28 @@ __device__ bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
 }
 
 // calc_mvd_cost (search_inter.c:373-412): bits for vector (x,y) << mv_shift
-__device__ uint32_t mvd_cost_bits(const MeFrame &f, const JobCtx &j, int x, int y, int mv_shift)
+__device__ __forceinline__ uint32_t mvd_cost_bits(const JobCtx &j, int x, int y, int mv_shift)
 {
   x *= 1 << mv_shift;
   y *= 1 << mv_shift;
-  for (int i = 0; i < j.n_merge; i++) {
-    const kvz_cuda_merge_cand &m = j.merge[i];
-    if (m.dir == 3) continue;
-    const int l = m.dir - 1;
-    if (m.mv[l][0] == x && m.mv[l][1] == y && f.ref_LX[l][m.ref[l]] == j.ref_idx) return (uint32_t)i;
-  }
+  const uint32_t q = pack_mv(x, y);
+  // the first merge candidate with this vector wins: its index is the bit count
+  uint32_t hit = 0;
+#pragma unroll
+  for (int i = 4; i >= 0; i--)
+    if (((j.mvalid >> i) & 1u) && j.mkey[i] == q) hit = (uint32_t)i | 0x100u;
+  if (hit) return hit & 0xFFu;
   const uint32_t c0 = mvd_bits(x - j.mv_cand[0][0], y - j.mv_cand[0][1]);
   const uint32_t c1 = mvd_bits(x - j.mv_cand[1][0], y - j.mv_cand[1][1]);
   return min(c0, c1);
 }
 
-// SAD of the PU (staged in smem, pitch 64) against the reference block whose top-left
-// sample is (rx, ry) in frame coordinates: kvz_image_calc_sad (image.c:455-479).  The
-// block origin is clamped into the replicated border, which reads the same samples as
-// the per-pixel coordinate clamp as long as pad >= PU size.
-__device__ uint32_t sad_on_demand(const MeFrame &f, const MeRef &r, const uint8_t *cur, int w, int h, int rx, int ry)
+// SAD of the PU (rows `cur_pitch` apart) against the reference block whose top-left sample is
+// (rx, ry) in frame coordinates: kvz_image_calc_sad (image.c:455-479).  The block origin is
+// clamped into the replicated border, which reads the same samples as the per-pixel
+// coordinate clamp as long as pad >= PU size.
+__device__ __noinline__ uint32_t sad_on_demand(const MeFrame &f, const MeRef &r, const uint8_t *cur, int cur_pitch, int w, int h,
+                                               int rx, int ry)
 {
   rx = clampi(rx, -r.pad, f.width + r.pad - w);
   ry = clampi(ry, -r.pad, f.height + r.pad - h);
@@ -125,7 +176,7 @@ __device__ uint32_t sad_on_demand(const MeFrame &f, const MeRef &r, const uint8_
   const int wpitch = r.pitch >> 2;
   uint32_t acc = 0;
   for (int yy = 0; yy < h; yy++) {
-    const uint32_t *cw = reinterpret_cast<const uint32_t *>(cur + yy * 64);
+    const uint32_t *cw = reinterpret_cast<const uint32_t *>(cur + (size_t)yy * cur_pitch);
     uint32_t prev = __ldg(rw);
     for (int c = 0; c < (w >> 2); c++) {
       uint32_t v = prev;
@@ -136,39 +187,21 @@ __device__ uint32_t sad_on_demand(const MeFrame &f, const MeRef &r, const uint8_
       } else if (c + 1 < (w >> 2)) {
         prev = __ldg(rw + c + 1);
       }
-      acc = sad4(cw[c], v, acc);
+      acc = sad4(__ldg(cw + c), v, acc);
     }
     rw += wpitch;
   }
   return acc;
 }
 
-// sample of the replicated plane with the coordinate clamped into it (== the per-pixel
-// clamp of kvz_get_extended_block, ipol-generic.c:761-781)
-__device__ __forceinline__ int ref_px(const MeFrame &f, const MeRef &r, int x, int y)
-{
-  x = clampi(x, -r.pad, f.width + r.pad - 1);
-  y = clampi(y, -r.pad, f.height + r.pad - 1);
-  return r.plane[(size_t)(y + r.pad) * r.pitch + (x + r.pad)];
-}
-
-template <int G>
-__device__ __forceinline__ unsigned long long group_min(const Group<G> &g, unsigned long long v, unsigned long long *scratch)
+__device__ __forceinline__ unsigned long long warp_min(unsigned long long v)
 {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const unsigned long long t = __shfl_xor_sync(0xffffffffu, v, o);
     v = t < v ? t : v;
   }
-  if (G == 32) return v;
-  const int warp = g.tid >> 5;
-  g.sync();
-  if ((g.tid & 31) == 0) scratch[warp] = v;
-  g.sync();
-  unsigned long long m = scratch[0];
-#pragma unroll
-  for (int i = 1; i < G / 32; i++) m = scratch[i] < m ? scratch[i] : m;
-  return m;
+  return v;
 }
 
 // per-window separable tables of the AMVP bit cost: bits = min_c(gx[c][col] + gy[c][row])
@@ -177,36 +210,51 @@ struct BitTables {
   uint2 gy[132];                 // same for row i
 };
 
-template <int G, int S>
-struct GroupSmem {
-  static constexpr int kWinPitch = S + 16;
-  alignas(16) uint8_t cur[S * 64 > 0 ? S * 64 : 1];            // PU rows, pitch 64
-  alignas(16) uint8_t win[(S + 9) * kWinPitch];                // FME source window
-  alignas(16) int16_t hor[4][(S + 7) * S];                     // horizontally filtered candidates
+// ======================================================================================
+// integer search: one warp per (PU, reference) job
+// ======================================================================================
+struct ScanSmem {
   BitTables bt;
-  unsigned long long red[4];
-  uint32_t cost4[4];
   int hit_pos[5];
   int hit_bits[5];
   int n_hit;
 };
 
-template <int G, int S>
-__device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu,
-                               const kvz_cuda_me_job &job, uint32_t &inter_cost, kvz_cuda_me_result *out)
+// one search window of search_mv_full
+struct WinCtx {
+  const MeFrame *f;
+  const JobCtx *j;
+  const ScanSmem *sm;
+  int cx, cy;               // centre (whole samples)
+  int R, K;
+  int n_hit;
+  bool free_mv;             // no tile / WPP restriction applies
+};
+
+// exact cost of one candidate: tile restriction and merge override included; ~0u if excluded
+__device__ __noinline__ uint32_t exact_cost(const WinCtx &w, int row, int col, uint32_t sad)
 {
+  const int mx = w.cx - w.R + col, my = w.cy - w.R + row;
+  if (!w.free_mv && !within_tile(*w.f, *w.j, mx * 4, my * 4)) return 0xFFFFFFFFu;
+  const uint2 bx = w.sm->bt.gx[col], by = w.sm->bt.gy[row];
+  uint32_t mvd = min(bx.x + by.x, bx.y + by.y);
+  const int pos = row * w.K + col;
+  for (int q = 0; q < w.n_hit; q++)
+    if (w.sm->hit_pos[q] == pos) mvd = (uint32_t)w.sm->hit_bits[q] * (uint32_t)w.j->lambda;
+  return sad + mvd;
+}
+
+__device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                         const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
+{
+  constexpr int G = 32;
   JobCtx j;
-  j.x = pu.x; j.y = pu.y; j.w = pu.w; j.h = pu.h;
-  j.ref_idx = job.ref_idx;
-  j.mv_cand[0][0] = job.mv_cand[0][0]; j.mv_cand[0][1] = job.mv_cand[0][1];
-  j.mv_cand[1][0] = job.mv_cand[1][0]; j.mv_cand[1][1] = job.mv_cand[1][1];
-  j.n_merge = pu.num_merge_cand;
-  j.merge = pu.merge_cand;
-  j.lambda = f.lambda_sqrt_i;
+  make_ctx(j, f, pu, merge, job);
   const MeRef &ref = f.refs[job.ref_idx];
   const int R = f.range, K = 2 * R + 1;
   const bool free_mv = !(f.owf && f.wpp) && f.mv_constraint == 0;
   const int fx0 = f.tile_x + j.x, fy0 = f.tile_y + j.y;       // frame-absolute PU origin
+  const uint8_t *cur = f.cur + (size_t)fy0 * f.cur_pitch + fx0;
 
   // ---- window list of search_mv_full ----
   int wcx[7], wcy[7], nwin = 1;
@@ -214,14 +262,14 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
   {
     const int ex = job.extra_mv[0] >> 2, ey = job.extra_mv[1] >> 2;
     bool in_merge = false;                       // mv_in_merge (search_inter.c:260-273)
-    for (int i = 0; i < j.n_merge; i++) {
-      const kvz_cuda_merge_cand &m = j.merge[i];
+    for (int i = 0; i < pu.num_merge_cand; i++) {
+      const kvz_cuda_merge_cand &m = merge[i];
       if (m.dir == 3) continue;
       if (((m.mv[m.dir - 1][0] + 2) >> 2) == ex && ((m.mv[m.dir - 1][1] + 2) >> 2) == ey) in_merge = true;
     }
     if (!in_merge) { wcx[nwin] = ex; wcy[nwin] = ey; nwin++; }
-    for (int i = 0; i < j.n_merge; i++) {
-      const kvz_cuda_merge_cand &m = j.merge[i];
+    for (int i = 0; i < pu.num_merge_cand; i++) {
+      const kvz_cuda_merge_cand &m = merge[i];
       if (m.dir == 3) continue;
       const int mx = m.mv[m.dir - 1][0] >> 2, my = m.mv[m.dir - 1][1] >> 2;
       if (mx == 0 && my == 0) continue;
@@ -239,21 +287,21 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
   for (int wi = 0; wi < nwin; wi++) {
     const int cx = wcx[wi], cy = wcy[wi];
     // separable AMVP bit tables and the merge overrides of this window
-    g.sync();
-    for (int i = g.tid; i < K; i += G) {
+    __syncwarp();
+    for (int i = lane; i < K; i += G) {
       const int qx = (cx - R + i) * 4, qy = (cy - R + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
       sm.bt.gx[i] = make_uint2(lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
       sm.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
     }
-    if (g.tid == 0) {
+    if (lane == 0) {
       int n = 0;
-      for (int i = 0; i < j.n_merge; i++) {
-        const kvz_cuda_merge_cand &m = j.merge[i];
-        if (m.dir == 3) continue;
-        const int l = m.dir - 1;
-        if ((m.mv[l][0] & 3) || (m.mv[l][1] & 3) || f.ref_LX[l][m.ref[l]] != j.ref_idx) continue;
-        const int col = (m.mv[l][0] >> 2) - (cx - R), row = (m.mv[l][1] >> 2) - (cy - R);
+#pragma unroll
+      for (int i = 0; i < 5; i++) {
+        if (!((j.mvalid >> i) & 1u)) continue;
+        const int mvx = (int16_t)(j.mkey[i] >> 16), mvy = (int16_t)(j.mkey[i] & 0xFFFFu);
+        if ((mvx & 3) || (mvy & 3)) continue;
+        const int col = (mvx >> 2) - (cx - R), row = (mvy >> 2) - (cy - R);
         if (col < 0 || col >= K || row < 0 || row >= K) continue;
         const int pos = row * K + col;
         bool dup = false;
@@ -262,22 +310,12 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       }
       sm.n_hit = n;
     }
-    g.sync();
-    const int n_hit = sm.n_hit;
-
-    // exact per-candidate path: tile restriction and merge override included
-    auto consider = [&](int row, int col, uint32_t sad) {
-      const int mx = cx - R + col, my = cy - R + row;
-      if (!free_mv && !within_tile(f, j, mx * 4, my * 4)) return;
-      const uint2 bx = sm.bt.gx[col], by = sm.bt.gy[row];
-      uint32_t mvd = min(bx.x + by.x, bx.y + by.y);
-      const int pos = row * K + col;
-      for (int q = 0; q < n_hit; q++)
-        if (sm.hit_pos[q] == pos) mvd = (uint32_t)sm.hit_bits[q] * (uint32_t)j.lambda;
-      const uint32_t cost = sad + mvd;
-      const unsigned long long key = ((unsigned long long)cost << 32) | (unsigned)((wi << 16) | pos);
-      best = key < best ? key : best;
-    };
+    __syncwarp();
+    WinCtx wc;
+    wc.f = &f; wc.j = &j; wc.sm = &sm; wc.cx = cx; wc.cy = cy; wc.R = R; wc.K = K; wc.n_hit = sm.n_hit; wc.free_mv = free_mv;
+    const int n_hit = wc.n_hit;
+    uint32_t wbest = 0xFFFFFFFFu;
+    int wpos = 0;
 
     // a map set made for this window centre?  (duplicates of earlier windows need no skipping:
     // with equal cost the earlier window's key is smaller)
@@ -292,66 +330,123 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
     }
     if (si >= 0) {
       const MeMapSet &ms = ref.sets[si];
-      // Window straight from the dense maps.  K = 8m + 1: m full vectors of 8 entries per row,
-      // then the last column.  A thread meets its candidates in visiting order, so within the
-      // window a strict '<' keeps the first of equal costs.
+      // Window straight from the dense maps: rows 0..K-1 hold K-1 = 8*vpr columns as vectors of 8
+      // entries, row K holds the last column.  A lane owns one vector column (8 window columns) and
+      // walks down the rows, so it meets its candidates in visiting order and a strict '<' keeps the
+      // first of equal costs.
       const int n = 8 >> level;
       const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
       const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
-      const int vpr = K >> 3;
-      uint32_t wbest = 0xFFFFFFFFu;
-      int wpos = 0;
-      // vectors holding a merge-override position take the exact path
-      int hv[5];
+      const int vpr = K >> 3;                              // 2, 4, 8 or 16
+      const int lv = 31 - __clz(vpr);
+      const int vec = lane & (vpr - 1), c0 = vec * 8;
+      const int rstep = G >> lv;
+      // rows of this lane's vector column that hold a merge-override position
+      int hrow[5];
 #pragma unroll
-      for (int q = 0; q < 5; q++)
-        hv[q] = (q < n_hit && (sm.hit_pos[q] % K) < K - 1) ? (sm.hit_pos[q] / K) * vpr + ((sm.hit_pos[q] % K) >> 3) : -1;
-      const bool fast = free_mv;
-      const uint16_t *map16 = (level == 0 ? ms.sad8 : ms.sad16) + prow * (K + 1) * f.map_pitch;
-      const uint32_t *map32 = (level == 2 ? ms.sad32 : ms.sad64) + prow * (K + 1) * f.map_pitch;
-      for (int i = g.tid; i < K * vpr; i += G) {
-        const int row = i / vpr, c0 = (i - row * vpr) * 8;
-        uint32_t sad[8];
-        if (level < 2) {
-          const uint4 v = __ldg(reinterpret_cast<const uint4 *>(map16 + (size_t)row * f.map_pitch + c0));
-          sad[0] = v.x & 0xFFFFu; sad[1] = v.x >> 16; sad[2] = v.y & 0xFFFFu; sad[3] = v.y >> 16;
-          sad[4] = v.z & 0xFFFFu; sad[5] = v.z >> 16; sad[6] = v.w & 0xFFFFu; sad[7] = v.w >> 16;
-        } else {
-          const uint4 v0 = __ldg(reinterpret_cast<const uint4 *>(map32 + (size_t)row * f.map_pitch + c0));
-          const uint4 v1 = __ldg(reinterpret_cast<const uint4 *>(map32 + (size_t)row * f.map_pitch + c0 + 4));
-          sad[0] = v0.x; sad[1] = v0.y; sad[2] = v0.z; sad[3] = v0.w;
-          sad[4] = v1.x; sad[5] = v1.y; sad[6] = v1.z; sad[7] = v1.w;
+      for (int q = 0; q < 5; q++) {
+        const int hp = q < n_hit ? sm.hit_pos[q] : -1;
+        const int hr = hp / K, hc = hp - hr * K;
+        hrow[q] = (hp >= 0 && hc < K - 1 && (hc >> 3) == vec) ? hr : -1;
+      }
+      // column terms of this lane's 8 columns, index in the vector folded into the low 3 bits:
+      // cost << 3 | e  =  (sad << 3) + min(a0, a1 + d) + (b0 << 3),  d = (b1 - b0) << 3
+      int a0[8], a1[8];
+#pragma unroll
+      for (int e = 0; e < 8; e++) {
+        const uint2 bx = sm.bt.gx[c0 + e];
+        a0[e] = (int)(bx.x << 3) | e;
+        a1[e] = (int)(bx.y << 3) | e;
+      }
+      auto fast8 = [&](int row, const int (&s8)[8]) {       // s8 = sad << 3
+        const uint2 by = sm.bt.gy[row];
+        const int d = ((int)by.y - (int)by.x) * 8;
+        int k[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) k[e] = s8[e] + min(a0[e], a1[e] + d);
+        const int m = min(min(min(k[0], k[1]), min(k[2], k[3])), min(min(k[4], k[5]), min(k[6], k[7])));
+        const uint32_t cost = (uint32_t)((m >> 3) + (int)by.x);
+        if (cost < wbest) { wbest = cost; wpos = row * K + c0 + (m & 7); }
+      };
+      auto exact8 = [&](int row, const uint32_t (&sad)[8]) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+          const uint32_t cost = exact_cost(wc, row, c0 + e, sad[e]);
+          if (cost < wbest) { wbest = cost; wpos = row * K + c0 + e; }
         }
-        const bool special = !fast || i == hv[0] || i == hv[1] || i == hv[2] || i == hv[3] || i == hv[4];
-        if (special) {
+      };
+      auto is_special = [&](int row) {
+        return !free_mv || row == hrow[0] || row == hrow[1] || row == hrow[2] || row == hrow[3] || row == hrow[4];
+      };
+      if (level < 2) {
+        // 8x8 / 16x16 PUs: uint16 maps, four rows in flight per lane
+        const uint16_t *mp = (level == 0 ? ms.sad8 : ms.sad16) + prow * (K + 1) * f.map_pitch + c0;
+        for (int r0 = lane >> lv; r0 < K; r0 += 4 * rstep) {
+          uint4 v[4];
 #pragma unroll
-          for (int e = 0; e < 8; e++) consider(row, c0 + e, sad[e]);
-        } else {
-          const uint2 by = sm.bt.gy[row];
-          const uint4 *bxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
+          for (int u = 0; u < 4; u++) {
+            const int row = r0 + u * rstep;
+            v[u] = row < K ? __ldg(reinterpret_cast<const uint4 *>(mp + (size_t)row * f.map_pitch)) : make_uint4(0, 0, 0, 0);
+          }
 #pragma unroll
-          for (int e2 = 0; e2 < 4; e2++) {
-            const uint4 bx = bxp[e2];                 // columns c0+2*e2 and c0+2*e2+1
-            const uint32_t ca = sad[2 * e2] + min(bx.x + by.x, bx.y + by.y);
-            const uint32_t cb = sad[2 * e2 + 1] + min(bx.z + by.x, bx.w + by.y);
-            if (ca < wbest) { wbest = ca; wpos = row * K + c0 + 2 * e2; }
-            if (cb < wbest) { wbest = cb; wpos = row * K + c0 + 2 * e2 + 1; }
+          for (int u = 0; u < 4; u++) {
+            const int row = r0 + u * rstep;
+            if (row >= K) break;
+            const uint32_t w4[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
+            if (is_special(row)) {
+              uint32_t sad[8];
+#pragma unroll
+              for (int e = 0; e < 8; e++) sad[e] = (e & 1) ? w4[e >> 1] >> 16 : w4[e >> 1] & 0xFFFFu;
+              exact8(row, sad);
+            } else {
+              int s8[8];
+#pragma unroll
+              for (int e = 0; e < 8; e++) s8[e] = (int)((e & 1) ? (w4[e >> 1] >> 13) & 0x7FFF8u : (w4[e >> 1] << 3) & 0x7FFF8u);
+              fast8(row, s8);
+            }
+          }
+        }
+      } else {
+        // 32x32 / 64x64 PUs: uint32 maps, two rows in flight per lane
+        const uint32_t *mp = (level == 2 ? ms.sad32 : ms.sad64) + prow * (K + 1) * f.map_pitch + c0;
+        for (int r0 = lane >> lv; r0 < K; r0 += 2 * rstep) {
+          uint4 v[2][2];
+#pragma unroll
+          for (int u = 0; u < 2; u++) {
+            const int row = r0 + u * rstep;
+            const uint4 *q = reinterpret_cast<const uint4 *>(mp + (size_t)row * f.map_pitch);
+            v[u][0] = row < K ? __ldg(q) : make_uint4(0, 0, 0, 0);
+            v[u][1] = row < K ? __ldg(q + 1) : make_uint4(0, 0, 0, 0);
+          }
+#pragma unroll
+          for (int u = 0; u < 2; u++) {
+            const int row = r0 + u * rstep;
+            if (row >= K) break;
+            const uint32_t sad[8] = { v[u][0].x, v[u][0].y, v[u][0].z, v[u][0].w, v[u][1].x, v[u][1].y, v[u][1].z, v[u][1].w };
+            if (is_special(row)) {
+              exact8(row, sad);
+            } else {
+              int s8[8];
+#pragma unroll
+              for (int e = 0; e < 8; e++) s8[e] = (int)(sad[e] << 3);
+              fast8(row, s8);
+            }
           }
         }
       }
-      // last column
-      for (int row = g.tid; row < K; row += G) {
-        const uint32_t sad = level < 2 ? (uint32_t)__ldg(map16 + (size_t)K * f.map_pitch + row)   // row K = column dx = +R
-                                       : __ldg(map32 + (size_t)K * f.map_pitch + row);
-        consider(row, K - 1, sad);
-      }
-      if (wbest != 0xFFFFFFFFu) {
-        const unsigned long long key = ((unsigned long long)wbest << 32) | (unsigned)((wi << 16) | wpos);
-        best = key < best ? key : best;
+      // last column: row K of the map, entry = window row.  Within a lane the positions of the last
+      // column are not all later than those of the vector column, so both the cost and the
+      // position decide.
+      for (int row = lane; row < K; row += G) {
+        const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + (prow * (K + 1) + K) * f.map_pitch + row)
+                                       : __ldg((level == 2 ? ms.sad32 : ms.sad64) + (prow * (K + 1) + K) * f.map_pitch + row);
+        const uint32_t cost = exact_cost(wc, row, K - 1, sad);
+        const int pos = row * K + K - 1;
+        if (cost < wbest || (cost == wbest && cost != 0xFFFFFFFFu && pos < wpos)) { wbest = cost; wpos = pos; }
       }
     } else {
       // on demand, skipping what an earlier window of this list already covered
-      for (int p = g.tid; p < K * K; p += G) {
+      for (int p = lane; p < K * K; p += G) {
         const int row = p / K, col = p % K;
         const int mx = cx - R + col, my = cy - R + row;
         bool covered = false;
@@ -359,36 +454,107 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
           covered |= (mx >= wcx[q] - R && mx <= wcx[q] + R && my >= wcy[q] - R && my <= wcy[q] + R);
         if (covered) continue;
         if (!free_mv && !within_tile(f, j, mx * 4, my * 4)) continue;
-        consider(row, col, sad_on_demand(f, ref, sm.cur, j.w, j.h, fx0 + mx, fy0 + my));
+        const uint32_t cost = exact_cost(wc, row, col, sad_on_demand(f, ref, cur, f.cur_pitch, j.w, j.h, fx0 + mx, fy0 + my));
+        if (cost < wbest) { wbest = cost; wpos = p; }
       }
     }
+    if (wbest != 0xFFFFFFFFu) {
+      const unsigned long long key = ((unsigned long long)wbest << 32) | (unsigned)((wi << 16) | wpos);
+      best = key < best ? key : best;
+    }
   }
-  best = group_min<G>(g, best, sm.red);
+  best = warp_min(best);
 
-  // ---- winner of the integer search ----
-  int best_mvx = 0, best_mvy = 0;            // quarter-pel (info->best_mv starts at 0,0)
-  uint32_t best_cost = 0xFFFFFFFFu, best_bits = 0;
-  if (best != ~0ull) {
-    const int wi = (int)((best >> 16) & 0xFFFF), pos = (int)(best & 0xFFFF);
-    best_mvx = (wcx[wi] - R + pos % K) * 4;
-    best_mvy = (wcy[wi] - R + pos / K) * 4;
-    best_cost = (uint32_t)(best >> 32);
-    best_bits = mvd_cost_bits(f, j, best_mvx >> 2, best_mvy >> 2, 2);
+  // ---- winner of the integer search, parked in the job's result record ----
+  if (lane == 0) {
+    int best_mvx = 0, best_mvy = 0;            // quarter-pel (info->best_mv starts at 0,0)
+    uint32_t best_cost = 0xFFFFFFFFu, best_bits = 0;
+    if (best != ~0ull) {
+      const int wi = (int)((best >> 16) & 0xFFFF), pos = (int)(best & 0xFFFF);
+      best_mvx = (wcx[wi] - R + pos % K) * 4;
+      best_mvy = (wcy[wi] - R + pos / K) * 4;
+      best_cost = (uint32_t)(best >> 32);
+      best_bits = mvd_cost_bits(j, best_mvx >> 2, best_mvy >> 2, 2);
+    }
+    kvz_cuda_me_result r;
+    r.mv[0] = (int16_t)best_mvx; r.mv[1] = (int16_t)best_mvy;
+    r.cost = best_cost; r.bitcost = best_bits;
+    r.merged = 0; r.merge_idx = 0; r.mv_cand_idx = 0; r.took = 0;
+    *out = r;
   }
+}
+
+constexpr int kScanWarps = 4;
+#ifndef KVZ_SCAN_MINB
+#define KVZ_SCAN_MINB 6
+#endif
+
+__global__ void __launch_bounds__(kScanWarps * 32, KVZ_SCAN_MINB)
+me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
+               const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *__restrict__ results, int n_pus)
+{
+  __shared__ ScanSmem sm[kScanWarps];
+  __shared__ kvz_cuda_merge_cand merge[5];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const kvz_cuda_me_pu &pu = pus[blockIdx.x];
+  if (threadIdx.x < 5) merge[threadIdx.x] = pu.merge_cand[threadIdx.x];
+  __syncthreads();
+  for (int q = warp; q < pu.num_jobs; q += kScanWarps)
+    scan_job(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q);
+}
+
+// ======================================================================================
+// refinement: fractional search / integer SATD, merge match, candidate choice, carry
+// ======================================================================================
+template <int G, int S>
+struct RefineSmem {
+  static constexpr int kWinPitch = S + 16;
+  alignas(16) uint8_t cur[S * 64];                             // PU rows, pitch 64
+  alignas(16) uint8_t win[(S + 9) * kWinPitch + 16];           // source window round the integer vector
+  alignas(16) uint32_t pp[3][(S + 7) * S];                     // horizontally filtered planes, vertical int16 pairs
+  kvz_cuda_merge_cand merge[5];
+  uint32_t cost4[4];
+};
+
+template <int G, int S>
+__device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu,
+                           const kvz_cuda_me_job &job, uint32_t &inter_cost, kvz_cuda_me_result *out)
+{
+  JobCtx j;
+  make_ctx(j, f, pu, sm.merge, job);
+  const MeRef &ref = f.refs[job.ref_idx];
+  const bool free_mv = !(f.owf && f.wpp) && f.mv_constraint == 0;
+  const int fx0 = f.tile_x + j.x, fy0 = f.tile_y + j.y;       // frame-absolute PU origin
+
+  // winner of the integer search (me_scan_kernel)
+  int best_mvx = out->mv[0], best_mvy = out->mv[1];
+  uint32_t best_cost = out->cost, best_bits = out->bitcost;
 
   const bool do_fme = f.fme_level > 0 && best_cost < inter_cost;
   const bool do_satd = !do_fme && best_cost < 0xFFFFFFFFu;
   if (do_fme || do_satd) {
-    // ---- source window round the integer vector: columns -4..w+3, rows -4..h+4 ----
+    // ---- source window round the integer vector: columns -4..w+3(+pad), rows -4..h+4 ----
+    // The window origin is clamped into the replicated border: with pad >= w + 20 this reads the same
+    // samples as the per-pixel clamp of kvz_get_extended_block (ipol-generic.c:761-781).
     const int imx = best_mvx >> 2, imy = best_mvy >> 2;
-    const int bx = fx0 + imx, by = fy0 + imy;
-    constexpr int WP = GroupSmem<G, S>::kWinPitch;
-    g.sync();
-    for (int i = g.tid; i < (j.h + 9) * (j.w + 8); i += G) {
-      const int r = i / (j.w + 8), c = i % (j.w + 8);
-      sm.win[r * WP + c] = (uint8_t)ref_px(f, ref, bx - 4 + c, by - 4 + r);
+    constexpr int WP = RefineSmem<G, S>::kWinPitch;
+    {
+      const int ox = clampi(fx0 + imx - 4, -ref.pad, f.width + ref.pad - (j.w + 20));
+      const int oy = clampi(fy0 + imy - 4, -ref.pad, f.height + ref.pad - (j.h + 9));
+      const uint8_t *p0 = ref.plane + (size_t)(oy + ref.pad) * ref.pitch + (ox + ref.pad);
+      const uintptr_t a0 = reinterpret_cast<uintptr_t>(p0);
+      const int sh = (int)(a0 & 3) * 8;
+      const uint32_t *rw = reinterpret_cast<const uint32_t *>(a0 & ~(uintptr_t)3);
+      const int wpr = (j.w + 12) >> 2, wpitch = ref.pitch >> 2;      // words per window row (w + 8 used, 4 spare)
+      g.sync();
+      for (int i = g.tid; i < (j.h + 9) * wpr; i += G) {
+        const int r = i / wpr, c = i - r * wpr;
+        const uint32_t *q = rw + (size_t)r * wpitch + c;
+        const uint32_t lo = __ldg(q), hi = __ldg(q + 1);
+        *reinterpret_cast<uint32_t *>(&sm.win[r * WP + c * 4]) = __funnelshift_r(lo, hi, sh);
+      }
+      g.sync();
     }
-    g.sync();
 
     const int tiles_x = j.w >> 3, tiles = tiles_x * (j.h >> 3);
     const int lane8 = g.tid & 7;
@@ -402,10 +568,14 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       const int t = on ? (u >> 3) : 0;
       const int ty = t / tiles_x, tx = t % tiles_x;
       int d[8];
-      const uint8_t *c = sm.cur + (ty * 8 + lane8) * 64 + tx * 8;
-      const uint8_t *p = sm.win + (ty * 8 + lane8 + 4) * WP + tx * 8 + 4;
+      const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * 64 + tx * 8);
+      const uint8_t *pr = sm.win + (ty * 8 + lane8 + 4) * WP + tx * 8 + 4;
+      const uint32_t p0 = *reinterpret_cast<const uint32_t *>(pr), p1 = *reinterpret_cast<const uint32_t *>(pr + 4);
 #pragma unroll
-      for (int x = 0; x < 8; x++) d[x] = (int)c[x] - (int)p[x];
+      for (int x = 0; x < 4; x++) {
+        d[x] = (int)((cw.x >> (8 * x)) & 0xFF) - (int)((p0 >> (8 * x)) & 0xFF);
+        d[x + 4] = (int)((cw.y >> (8 * x)) & 0xFF) - (int)((p1 >> (8 * x)) & 0xFF);
+      }
       const uint32_t s = satd8_rows(d, lane8);
       if (on && lane8 == 0) atomicAdd(&sm.cost4[0], s);
     }
@@ -417,16 +587,63 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
       best_cost = satd_int + best_bits * (uint32_t)j.lambda;
     } else {
       // ---- search_frac ----
+      // Horizontally filtered planes are shared between the candidates that use them
+      // (kvz_filter_hpel/qpel_blocks_*_luma, ipol-generic.c:192-658, do the same): plane (fx, sx)
+      // holds H[r][x] = sum_t fir[fx][t] * win[r][x + sx + 1 + t] for rows r = 0..h+7 (source rows
+      // -4..h+3) as int16, stored as vertical pairs PP[r][x] = (H[r][x], H[r+1][x]) so that the
+      // vertical 8-tap filter is four 2-way dot products.  Three planes are alive at a time.
+      const int PW = j.w;                                   // words per plane row
+      auto make_plane = [&](int slot, int fx, int sx) {
+        const uint32_t t_lo = c_fir4[fx][0], t_hi = c_fir4[fx][1];
+        const int o = sx + 1;                                // byte offset inside the aligned 12-byte run
+        const int strips = j.w >> 2;
+        uint32_t *dst = sm.pp[slot];
+        for (int it = g.tid; it < (j.h + 7) * strips; it += G) {
+          const int r = it / strips, x = (it - r * strips) * 4;
+          int hv[2][4];
+#pragma unroll
+          for (int rr = 0; rr < 2; rr++) {
+            const uint32_t *wr = reinterpret_cast<const uint32_t *>(&sm.win[(r + rr) * WP + x]);
+            const uint32_t w0 = wr[0], w1 = wr[1], w2 = wr[2];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              const uint32_t lo = __funnelshift_rc(w0, w1, 8 * (o + q)), hi = __funnelshift_rc(w1, w2, 8 * (o + q));
+              hv[rr][q] = dp4a_us(hi, t_hi, dp4a_us(lo, t_lo, 0));
+            }
+          }
+          uint4 o4;
+          o4.x = __byte_perm((uint32_t)hv[0][0], (uint32_t)hv[1][0], 0x5410);
+          o4.y = __byte_perm((uint32_t)hv[0][1], (uint32_t)hv[1][1], 0x5410);
+          o4.z = __byte_perm((uint32_t)hv[0][2], (uint32_t)hv[1][2], 0x5410);
+          o4.w = __byte_perm((uint32_t)hv[0][3], (uint32_t)hv[1][3], 0x5410);
+          *reinterpret_cast<uint4 *>(&dst[r * PW + x]) = o4;
+        }
+      };
+      int slot_l = 0, slot_r = 1, slot_0 = 2, slot_a = -1, slot_b = -1;   // planes (2,-1), (2,0), (0,0), px=-1, px=+1
+      make_plane(slot_l, 2, -1);
+      make_plane(slot_r, 2, 0);
+      make_plane(slot_0, 0, 0);
+
       const int sqx[9] = { 0, -1, 1, 0, 0, -1, 1, -1, 1 };
       const int sqy[9] = { 0, 0, 0, -1, 1, -1, -1, 1, 1 };
       int mvx = imx, mvy = imy;
-      uint32_t bits0 = mvd_cost_bits(f, j, mvx, mvy, 2);
+      uint32_t bits0 = mvd_cost_bits(j, mvx, mvy, 2);
       uint32_t fbest_cost = satd_int + bits0 * (uint32_t)j.lambda;
       uint32_t fbest_bits = bits0;
       int best_index = 0, hx = 0, hy = 0, i = 1;
       mvx *= 2; mvy *= 2;
       for (int step = 0; step < f.fme_level; step++) {
         const int mv_shift = step < 2 ? 1 : 0;
+        if (step == 2) {
+          // quarter-pel planes round the best half-pel position; they take the slots of the half-pel
+          // planes that the remaining candidates do not read
+          g.sync();
+          if (hx < 0) { slot_a = slot_r; slot_b = slot_0; }
+          else if (hx > 0) { slot_a = slot_l; slot_b = slot_0; }
+          else { slot_a = slot_l; slot_b = slot_r; }
+          make_plane(slot_a, (2 * hx - 1) & 3, (2 * hx - 1) >> 2);
+          make_plane(slot_b, (2 * hx + 1) & 3, (2 * hx + 1) >> 2);
+        }
         // quarter-pel displacement of the 4 candidates relative to the integer vector
         int qx[4], qy[4];
 #pragma unroll
@@ -437,26 +654,6 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
         }
         g.sync();
         if (g.tid < 4) sm.cost4[g.tid] = 0;
-        // horizontal pass: hor[k][r][x], r = 0..h+6 (ipol-generic.c:233-262 et al.)
-        const int hw = j.w >> 2;                              // 4 outputs per item
-        const int items = 4 * (j.h + 7) * hw;
-        for (int it = g.tid; it < items; it += G) {
-          const int k = it / ((j.h + 7) * hw);
-          const int rem = it % ((j.h + 7) * hw);
-          const int r = rem / hw, x = (rem % hw) * 4;
-          const int sx = qx[k] >> 2, fx = qx[k] & 3, sy = qy[k] >> 2;
-          const uint8_t *src = sm.win + (r + sy + 1) * WP + (x + sx + 1);
-          int px[11];
-#pragma unroll
-          for (int q = 0; q < 11; q++) px[q] = src[q];
-#pragma unroll
-          for (int o = 0; o < 4; o++) {
-            int s = 0;
-#pragma unroll
-            for (int t = 0; t < 8; t++) s += c_luma_fir[fx][t] * px[o + t];
-            sm.hor[k][r * j.w + x + o] = (int16_t)s;          // >> (BD-8) == >> 0
-          }
-        }
         g.sync();
         // vertical pass + SATD: one 8x8 tile row per lane, 8 lanes per tile
         const int units = 4 * tiles * 8;
@@ -466,26 +663,31 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
           const int k = on ? u / (tiles * 8) : 0;
           const int t = on ? (u % (tiles * 8)) >> 3 : 0;
           const int ty = t / tiles_x, tx = t % tiles_x;
-          const int fy = qy[k] & 3;
+          const int cqx = qx[k], cqy = qy[k];
+          const int slot = (cqx & 1) ? (cqx == 2 * hx - 1 ? slot_a : slot_b) : (cqx < 0 ? slot_l : cqx == 0 ? slot_0 : slot_r);
+          const int fy = cqy & 3, sy = cqy >> 2;
+          const uint32_t t_lo = c_fir4[fy][0], t_hi = c_fir4[fy][1];
+          const uint32_t *pp = sm.pp[slot] + (ty * 8 + lane8 + sy + 1) * PW + tx * 8;
           int acc[8];
 #pragma unroll
           for (int x = 0; x < 8; x++) acc[x] = 0;
-          const int16_t *hp = sm.hor[k] + (ty * 8 + lane8) * j.w + tx * 8;
 #pragma unroll
-          for (int t8 = 0; t8 < 8; t8++) {
-            const int cf = c_luma_fir[fy][t8];
-            const uint4 v = *reinterpret_cast<const uint4 *>(hp + t8 * j.w);
-            const uint32_t wv[4] = { v.x, v.y, v.z, v.w };
+          for (int i2 = 0; i2 < 4; i2++) {
+            const uint4 va = *reinterpret_cast<const uint4 *>(pp + 2 * i2 * PW);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(pp + 2 * i2 * PW + 4);
+            const uint32_t wv[8] = { va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w };
+            const uint32_t tp = i2 < 2 ? t_lo : t_hi;
 #pragma unroll
-            for (int x = 0; x < 8; x++) acc[x] += cf * (int)(int16_t)((wv[x >> 1] >> ((x & 1) * 16)) & 0xFFFF);
+            for (int x = 0; x < 8; x++)
+              acc[x] = (i2 & 1) ? dp2a_hi_ss(wv[x], tp, acc[x]) : dp2a_lo_ss(wv[x], tp, acc[x]);
           }
           int d[8];
-          const uint8_t *c = sm.cur + (ty * 8 + lane8) * 64 + tx * 8;
+          const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * 64 + tx * 8);
 #pragma unroll
           for (int x = 0; x < 8; x++) {
             const int v16 = (int)(int16_t)(acc[x] >> 6);       // int16 store of ipol-generic.c:285 et al.
             const int pix = clampi((v16 + 32) >> 6, 0, 255);
-            d[x] = (int)c[x] - pix;
+            d[x] = (int)(((x < 4 ? cw.x : cw.y) >> (8 * (x & 3))) & 0xFF) - pix;
           }
           const uint32_t s = satd8_rows(d, lane8);
           if (on && lane8 == 0) atomicAdd(&sm.cost4[k], s);
@@ -500,7 +702,7 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
           costs[k] = sm.cost4[k];
           bits[k] = 0;
           if (ok[k]) {
-            bits[k] = mvd_cost_bits(f, j, cxk, cyk, mv_shift);
+            bits[k] = mvd_cost_bits(j, cxk, cyk, mv_shift);
             costs[k] += bits[k] * (uint32_t)j.lambda;
           }
         }
@@ -525,10 +727,10 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
 
   // ---- merge match, AMVP candidate choice, carry of *inter_cost (search_inter.c:1258-1297) ----
   int merged = 0, merge_idx = 0;
-  for (merge_idx = 0; merge_idx < j.n_merge; merge_idx++) {
-    const kvz_cuda_merge_cand &m = j.merge[merge_idx];
-    if (m.dir != 3 && m.mv[m.dir - 1][0] == best_mvx && m.mv[m.dir - 1][1] == best_mvy &&
-        f.ref_LX[m.dir - 1][m.ref[m.dir - 1]] == j.ref_idx) { merged = 1; break; }
+  {
+    const uint32_t q = pack_mv(best_mvx, best_mvy);
+    for (merge_idx = 0; merge_idx < pu.num_merge_cand; merge_idx++)
+      if (((j.mvalid >> merge_idx) & 1u) && j.mkey[merge_idx] == q) { merged = 1; break; }
   }
   int cu_mv_cand = 0;
   if (!merged) {
@@ -541,6 +743,7 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
   }
   const bool took = best_cost < inter_cost;
   if (took) inter_cost = best_cost;
+  g.sync();                                   // everyone has read the parked winner
   if (g.tid == 0) {
     kvz_cuda_me_result r;
     r.mv[0] = (int16_t)best_mvx; r.mv[1] = (int16_t)best_mvy;
@@ -553,32 +756,33 @@ __device__ void search_one_ref(const Group<G> &g, GroupSmem<G, S> &sm, const MeF
 
 template <int G, int S>
 __global__ void __launch_bounds__(kCtaThreads)
-me_search_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
-                 const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *__restrict__ results, int n_pus)
+me_refine_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
+                 const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *results, int n_pus)
 {
   constexpr int kGroups = kCtaThreads / G;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  GroupSmem<G, S> *all = reinterpret_cast<GroupSmem<G, S> *>(smem_raw);
+  RefineSmem<G, S> *all = reinterpret_cast<RefineSmem<G, S> *>(smem_raw);
   Group<G> g;
   g.tid = threadIdx.x % G;
   g.id = threadIdx.x / G;
-  GroupSmem<G, S> &sm = all[g.id];
+  RefineSmem<G, S> &sm = all[g.id];
   const int pi = blockIdx.x * kGroups + g.id;
   if (pi >= n_pus) return;
   const kvz_cuda_me_pu &pu = pus[pi];
   const bool small = pu.w <= 16 && pu.h <= 16;
   if (small != (S == 16)) return;            // the other instantiation owns this PU
 
-  // stage the PU's source block (pitch 64)
+  // stage the PU's source block (pitch 64) and its merge candidates
   for (int i = g.tid; i < pu.h * (pu.w >> 2); i += G) {
     const int r = i / (pu.w >> 2), c = i % (pu.w >> 2);
     const uint8_t *src = f.cur + (size_t)(f.tile_y + pu.y + r) * f.cur_pitch + f.tile_x + pu.x + c * 4;
     *reinterpret_cast<uint32_t *>(&sm.cur[r * 64 + c * 4]) = *reinterpret_cast<const uint32_t *>(src);
   }
+  if (g.tid < 5) sm.merge[g.tid] = pu.merge_cand[g.tid];
   g.sync();
   uint32_t inter_cost = 0x7FFFFFFFu;         // *inter_cost = MAX_INT (search_inter.c:1460)
   for (int q = 0; q < pu.num_jobs; q++)
-    search_one_ref<G, S>(g, sm, f, pu, jobs[pu.first_job + q], inter_cost, results + pu.first_job + q);
+    refine_job<G, S>(g, sm, f, pu, jobs[pu.first_job + q], inter_cost, results + pu.first_job + q);
 }
 
 }  // namespace
@@ -587,19 +791,22 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
                      kvz_cuda_me_result *results, int n_pus, cudaStream_t stream)
 {
   if (n_pus <= 0) return 1;
+  me_scan_kernel<<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
   {
-    using K = GroupSmem<32, 16>;
-    const size_t smem = sizeof(K) * 4;
-    auto kern = me_search_kernel<32, 16>;
+    using SM = RefineSmem<32, 16>;
+    const size_t smem = sizeof(SM) * 4;
+    auto kern = me_refine_kernel<32, 16>;
     KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(n_pus + 3) / 4, kCtaThreads, smem, stream>>>(f, pus, jobs, results, n_pus);
     count_launch();
     KVZ_CUDA_LAUNCH_CHECK();
   }
   {
-    using K = GroupSmem<128, 64>;
-    const size_t smem = sizeof(K);
-    auto kern = me_search_kernel<128, 64>;
+    using SM = RefineSmem<128, 64>;
+    const size_t smem = sizeof(SM);
+    auto kern = me_refine_kernel<128, 64>;
     KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<n_pus, kCtaThreads, smem, stream>>>(f, pus, jobs, results, n_pus);
     count_launch();
