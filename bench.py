@@ -306,7 +306,7 @@ def run_ours(args):
                                "refinement (search_frac), 42900 PUs x 4225 candidates x 4 refs per step",
                    "frames_per_s": 1e3 / step_ms * world,
                    "l2": "per step %.0f MB of SAD maps are written and read back: larger than the 126 MB L2, "
-                         "no flush needed" % (map_bytes * NREFS / 1e6),
+                         "no flush needed" % (map_bytes * pipe.n_sad_launches / 1e6),
                    "stages": pipe.stages + (["publish_reference (NCCL broadcast of one luma plane) x1"] if world > 1 else []),
                    "parallelism": "frames of one temporal layer per GPU (weak scaling), no data-path collective in ME",
                    "kernel_ms": {"ime_sad_dense x1": sad_ms, "me_search x1": search_ms,

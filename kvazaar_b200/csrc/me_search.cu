@@ -21,7 +21,7 @@
 //      gated by `best_cost < *inter_cost`; otherwise SATD at the integer vector
 //      (search_inter.c:1244-1256); then the merge-index match and select_mv_cand
 //      (search_inter.c:1258-1297).  A warp works on a PU up to 16x16 (four PUs per
-//      CTA), the whole 128-thread CTA on a larger one.
+//      CTA), the whole 256-thread CTA on a larger one.
 #include "common.cuh"
 #include "me_search.cuh"
 #include "satd.cuh"
@@ -30,6 +30,10 @@ namespace kvz {
 namespace {
 
 constexpr int kCtaThreads = 128;
+#ifndef KVZ_BIG_GROUP
+#define KVZ_BIG_GROUP 256
+#endif
+constexpr int kBigGroup = KVZ_BIG_GROUP;    // threads working on one PU larger than 16x16
 
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c)
 {
@@ -213,6 +217,14 @@ struct BitTables {
 // ======================================================================================
 // integer search: one warp per (PU, reference) job
 // ======================================================================================
+constexpr int kScanWarps = 4;
+#ifndef KVZ_SCAN_DEPTH
+#define KVZ_SCAN_DEPTH 2      // map rows in flight per lane (uint16 maps)
+#endif
+#ifndef KVZ_SCAN_MINB
+#define KVZ_SCAN_MINB 6
+#endif
+
 struct ScanSmem {
   BitTables bt;
   int hit_pos[5];
@@ -381,15 +393,15 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
       if (level < 2) {
         // 8x8 / 16x16 PUs: uint16 maps, four rows in flight per lane
         const uint16_t *mp = (level == 0 ? ms.sad8 : ms.sad16) + prow * (K + 1) * f.map_pitch + c0;
-        for (int r0 = lane >> lv; r0 < K; r0 += 4 * rstep) {
-          uint4 v[4];
+        for (int r0 = lane >> lv; r0 < K; r0 += KVZ_SCAN_DEPTH * rstep) {
+          uint4 v[KVZ_SCAN_DEPTH];
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
+          for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
             const int row = r0 + u * rstep;
             v[u] = row < K ? __ldg(reinterpret_cast<const uint4 *>(mp + (size_t)row * f.map_pitch)) : make_uint4(0, 0, 0, 0);
           }
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
+          for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
             const int row = r0 + u * rstep;
             if (row >= K) break;
             const uint32_t w4[4] = { v[u].x, v[u].y, v[u].z, v[u].w };
@@ -437,12 +449,24 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
       // last column: row K of the map, entry = window row.  Within a lane the positions of the last
       // column are not all later than those of the vector column, so both the cost and the
       // position decide.
-      for (int row = lane; row < K; row += G) {
-        const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + (prow * (K + 1) + K) * f.map_pitch + row)
-                                       : __ldg((level == 2 ? ms.sad32 : ms.sad64) + (prow * (K + 1) + K) * f.map_pitch + row);
-        const uint32_t cost = exact_cost(wc, row, K - 1, sad);
-        const int pos = row * K + K - 1;
-        if (cost < wbest || (cost == wbest && cost != 0xFFFFFFFFu && pos < wpos)) { wbest = cost; wpos = pos; }
+      {
+        const uint2 bxl = sm.bt.gx[K - 1];
+        bool hit_last = false;                      // a merge override inside the last column?
+        for (int q = 0; q < n_hit; q++) hit_last |= (sm.hit_pos[q] % K) == K - 1;
+        const size_t lrow = (prow * (K + 1) + K) * f.map_pitch;
+        for (int row = lane; row < K; row += G) {
+          const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + lrow + row)
+                                         : __ldg((level == 2 ? ms.sad32 : ms.sad64) + lrow + row);
+          uint32_t cost;
+          if (free_mv && !hit_last) {
+            const uint2 by = sm.bt.gy[row];
+            cost = sad + min(bxl.x + by.x, bxl.y + by.y);
+          } else {
+            cost = exact_cost(wc, row, K - 1, sad);
+          }
+          const int pos = row * K + K - 1;
+          if (cost < wbest || (cost == wbest && cost != 0xFFFFFFFFu && pos < wpos)) { wbest = cost; wpos = pos; }
+        }
       }
     } else {
       // on demand, skipping what an earlier window of this list already covered
@@ -484,10 +508,6 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
   }
 }
 
-constexpr int kScanWarps = 4;
-#ifndef KVZ_SCAN_MINB
-#define KVZ_SCAN_MINB 6
-#endif
 
 __global__ void __launch_bounds__(kScanWarps * 32, KVZ_SCAN_MINB)
 me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
@@ -693,17 +713,23 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
           if (on && lane8 == 0) atomicAdd(&sm.cost4[k], s);
         }
         g.sync();
+        // lane k of every warp prices candidate k, then the four lanes are read by all
         uint32_t costs[4], bits[4];
         bool ok[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
+        {
+          const int k = g.tid & 3;
           const int cxk = mvx + sqx[i + k], cyk = mvy + sqy[i + k];
-          ok[k] = free_mv || within_tile(f, j, cxk * (1 << mv_shift), cyk * (1 << mv_shift));
-          costs[k] = sm.cost4[k];
-          bits[k] = 0;
-          if (ok[k]) {
-            bits[k] = mvd_cost_bits(j, cxk, cyk, mv_shift);
-            costs[k] += bits[k] * (uint32_t)j.lambda;
+          const bool okk = free_mv || within_tile(f, j, cxk * (1 << mv_shift), cyk * (1 << mv_shift));
+          uint32_t ck = sm.cost4[k], bk = 0;
+          if (okk) {
+            bk = mvd_cost_bits(j, cxk, cyk, mv_shift);
+            ck += bk * (uint32_t)j.lambda;
+          }
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            costs[q] = __shfl_sync(0xffffffffu, ck, q);
+            bits[q] = __shfl_sync(0xffffffffu, bk, q);
+            ok[q] = __shfl_sync(0xffffffffu, (int)okk, q) != 0;
           }
         }
 #pragma unroll
@@ -754,12 +780,12 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
   }
 }
 
-template <int G, int S>
-__global__ void __launch_bounds__(kCtaThreads)
+template <int G, int S, int T>
+__global__ void __launch_bounds__(T)
 me_refine_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
                  const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *results, int n_pus)
 {
-  constexpr int kGroups = kCtaThreads / G;
+  constexpr int kGroups = T / G;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RefineSmem<G, S> *all = reinterpret_cast<RefineSmem<G, S> *>(smem_raw);
   Group<G> g;
@@ -797,18 +823,18 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
   {
     using SM = RefineSmem<32, 16>;
     const size_t smem = sizeof(SM) * 4;
-    auto kern = me_refine_kernel<32, 16>;
+    auto kern = me_refine_kernel<32, 16, kCtaThreads>;
     KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(n_pus + 3) / 4, kCtaThreads, smem, stream>>>(f, pus, jobs, results, n_pus);
     count_launch();
     KVZ_CUDA_LAUNCH_CHECK();
   }
   {
-    using SM = RefineSmem<128, 64>;
+    using SM = RefineSmem<kBigGroup, 64>;
     const size_t smem = sizeof(SM);
-    auto kern = me_refine_kernel<128, 64>;
+    auto kern = me_refine_kernel<kBigGroup, 64, kBigGroup>;
     KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<n_pus, kCtaThreads, smem, stream>>>(f, pus, jobs, results, n_pus);
+    kern<<<n_pus, kBigGroup, smem, stream>>>(f, pus, jobs, results, n_pus);
     count_launch();
     KVZ_CUDA_LAUNCH_CHECK();
   }

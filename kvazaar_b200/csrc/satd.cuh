@@ -37,11 +37,11 @@ __device__ __forceinline__ uint32_t satd8_rows(int (&d)[8], int lane8)
   hadamard8(d);
 #pragma unroll
   for (int o = 1; o < 8; o <<= 1) {
-    const bool upper = (lane8 & o) != 0;
+    const int sgn = (lane8 & o) ? -1 : 1;            // upper lane of the pair: other - d, lower: other + d
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       const int other = __shfl_xor_sync(0xffffffffu, d[i], o);
-      d[i] = upper ? other - d[i] : d[i] + other;
+      d[i] = other + sgn * d[i];
     }
   }
   uint32_t s = 0;
