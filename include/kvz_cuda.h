@@ -116,6 +116,24 @@ KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,
                                        uint16_t *d_sad8, uint16_t *d_sad16,
                                        uint32_t *d_sad32, uint32_t *d_sad64, void *stream);
 
+/* The same for a rectangular box of displacements, dx in [x0, x0+n_dx), dy in [y0, y0+n_dy): one box that
+ * covers all the windows search_mv_full visits for a reference (zero window, extra_mv window, merge-candidate
+ * windows; search_inter.c:891-955) computes every displacement once, where separate windows overlap.
+ *   map[level][p][dy - y0][dx - x0],  rows n_dx entries apart (plain row-major, no extra row).
+ * n_dx must be a multiple of 16 and n_dy == 1 (mod 8): round the box up, surplus entries are ignored
+ * by kvz_cuda_me_search.  ref_pad must be >= 96 + max(|x0|, |x0+n_dx|, |y0|, |y0+n_dy|). */
+typedef struct kvz_cuda_ime_box_desc {
+  int32_t width, height, bitdepth;
+  int32_t tile_x, tile_y, tile_w, tile_h;
+  int32_t cur_pitch, ref_pitch, ref_pad;
+  int32_t x0, y0, n_dx, n_dy;
+} kvz_cuda_ime_box_desc;
+KVZ_CUDA_API size_t kvz_cuda_ime_box_map_bytes(const kvz_cuda_ime_box_desc *d, int level);
+KVZ_CUDA_API int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d,
+                                           const void *d_cur, const void *d_ref_padded,
+                                           uint16_t *d_sad8, uint16_t *d_sad16,
+                                           uint32_t *d_sad32, uint32_t *d_sad64, void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: per-PU motion decision  (rows A3, A4, A5, A7-A10)         */
 /* ------------------------------------------------------------------ */
@@ -159,9 +177,11 @@ typedef struct kvz_cuda_me_result {
 
 #define KVZ_CUDA_MAX_MAPSETS 4
 
-/* one result of kvz_cuda_ime_sad_maps() for (current, this reference) and the window centre it was made for */
+/* one result of kvz_cuda_ime_sad_maps() for (current, this reference) and the window centre it was made
+ * for (n_dx == 0), or of kvz_cuda_ime_sad_box_maps() (n_dx, n_dy > 0; center_x, center_y = x0, y0 of the box) */
 typedef struct kvz_cuda_me_mapset {
   int32_t center_x, center_y;
+  int32_t n_dx, n_dy;
   const uint16_t *d_sad8, *d_sad16;
   const uint32_t *d_sad32, *d_sad64;
 } kvz_cuda_me_mapset;
@@ -169,8 +189,9 @@ typedef struct kvz_cuda_me_mapset {
 typedef struct kvz_cuda_me_ref {
   const void *d_ref_padded;     /* border-replicated luma of the reference picture */
   int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 64 (and what the maps needed) */
-  int32_t n_mapsets;            /* windows of search_mv_full whose centre matches a map set are read from it, */
-  int32_t reserved;             /* every other window is evaluated on demand (0 sets = everything on demand) */
+  int32_t n_mapsets;            /* a job whose windows all lie inside a box set is searched from that box; else each */
+  int32_t reserved;             /* window whose centre matches a window set is read from it and every other window
+                                   is evaluated on demand (0 sets = everything on demand) */
   kvz_cuda_me_mapset mapsets[KVZ_CUDA_MAX_MAPSETS];
 } kvz_cuda_me_ref;
 

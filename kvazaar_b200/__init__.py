@@ -9,8 +9,8 @@ but every compute call raises :class:`KvzCudaError` without a B200.
 from .capi import (KvzCudaError, lib, lib_path, init, launch_count, ImeDesc,  # noqa: F401
                    ime_required_pad, ime_map_pitch)
 from .capi import measure_int_pipe_peak  # noqa: F401
-from .frame import PaddedPlane, ImeSearch  # noqa: F401
+from .frame import PaddedPlane, ImeSearch, ImeBoxSearch  # noqa: F401
 from .pipeline import MePipeline  # noqa: F401
 
 __all__ = ["KvzCudaError", "lib", "lib_path", "init", "launch_count", "ImeDesc",
-           "ime_required_pad", "ime_map_pitch", "PaddedPlane", "ImeSearch", "MePipeline", "measure_int_pipe_peak"]
+           "ime_required_pad", "ime_map_pitch", "PaddedPlane", "ImeSearch", "ImeBoxSearch", "MePipeline", "measure_int_pipe_peak"]

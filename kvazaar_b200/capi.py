@@ -29,9 +29,17 @@ MAX_REFS = 16
 MAX_MAPSETS = 4
 
 
+class ImeBoxDesc(C.Structure):
+    """kvz_cuda_ime_box_desc"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("bitdepth", C.c_int32),
+                ("tile_x", C.c_int32), ("tile_y", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
+                ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32),
+                ("x0", C.c_int32), ("y0", C.c_int32), ("n_dx", C.c_int32), ("n_dy", C.c_int32)]
+
+
 class MeMapSet(C.Structure):
     """kvz_cuda_me_mapset"""
-    _fields_ = [("center_x", C.c_int32), ("center_y", C.c_int32),
+    _fields_ = [("center_x", C.c_int32), ("center_y", C.c_int32), ("n_dx", C.c_int32), ("n_dy", C.c_int32),
                 ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p), ("d_sad32", C.c_void_p), ("d_sad64", C.c_void_p)]
 
 
@@ -81,6 +89,8 @@ SIGNATURES = {
     "kvz_cuda_ime_map_pitch": (C.c_int, [C.c_int]),
     "kvz_cuda_ime_map_bytes": (C.c_size_t, [C.POINTER(ImeDesc), C.c_int]),
     "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "kvz_cuda_ime_box_map_bytes": (C.c_size_t, [C.POINTER(ImeBoxDesc), C.c_int]),
+    "kvz_cuda_ime_sad_box_maps": (C.c_int, [C.POINTER(ImeBoxDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

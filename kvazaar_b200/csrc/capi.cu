@@ -165,10 +165,48 @@ int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d, const void *d_cur, const v
   p.cur_pitch = d->cur_pitch; p.ref_pitch = d->ref_pitch; p.pad = d->ref_pad;
   p.tile_x = d->tile_x; p.tile_y = d->tile_y; p.tile_w = d->tile_w; p.tile_h = d->tile_h;
   p.ctus_x = (d->tile_w + 63) / 64; p.ctus_y = (d->tile_h + 63) / 64;
-  p.center_x = d->center_x; p.center_y = d->center_y;
   p.map_pitch = ime_map_pitch(d->range);
   p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
-  return launch_ime_sad_dense(p, d->range, (cudaStream_t)stream);
+  return launch_ime_sad_dense(p, d->range, d->center_x, d->center_y, (cudaStream_t)stream);
+}
+
+size_t kvz_cuda_ime_box_map_bytes(const kvz_cuda_ime_box_desc *d, int level)
+{
+  if (!d || level < 0 || level > 3) return 0;
+  const size_t ctus = (size_t)((d->tile_w + 63) / 64) * ((d->tile_h + 63) / 64);
+  const size_t n = 8 >> level;
+  return ctus * n * n * (size_t)d->n_dy * (size_t)d->n_dx * (level < 2 ? 2 : 4);
+}
+
+int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur, const void *d_ref_padded,
+                              uint16_t *d_sad8, uint16_t *d_sad16, uint32_t *d_sad32, uint32_t *d_sad64,
+                              void *stream)
+{
+  if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
+    return fail_msg("kvz_cuda_ime_sad_box_maps: null argument");
+  if (d->bitdepth != 8) return fail_msg("kvz_cuda_ime_sad_box_maps: only bitdepth 8 is implemented");
+  if (d->n_dx <= 0 || (d->n_dx & 15) || d->n_dy <= 0 || (d->n_dy & 7) != 1)
+    return fail_msg("kvz_cuda_ime_sad_box_maps: n_dx must be a multiple of 16 and n_dy == 1 (mod 8)");
+  {
+    int far = abs(d->x0);
+    if (abs(d->x0 + d->n_dx) > far) far = abs(d->x0 + d->n_dx);
+    if (abs(d->y0) > far) far = abs(d->y0);
+    if (abs(d->y0 + d->n_dy) > far) far = abs(d->y0 + d->n_dy);
+    if (d->ref_pad < 96 + far) return fail_msg("kvz_cuda_ime_sad_box_maps: ref_pad too small for this box");
+  }
+  if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 3) || (d->ref_pad & 3) ||
+      (d->tile_x & 63) || (d->tile_y & 63) || (d->tile_w & 7) || (d->tile_h & 7))
+    return fail_msg("kvz_cuda_ime_sad_box_maps: width/pitches/pad must be multiples of 8, tile origin of 64");
+  ImeSadParams p;
+  p.cur = (const uint8_t *)d_cur;
+  p.ref = (const uint8_t *)d_ref_padded;
+  p.width = d->width; p.height = d->height;
+  p.cur_pitch = d->cur_pitch; p.ref_pitch = d->ref_pitch; p.pad = d->ref_pad;
+  p.tile_x = d->tile_x; p.tile_y = d->tile_y; p.tile_w = d->tile_w; p.tile_h = d->tile_h;
+  p.ctus_x = (d->tile_w + 63) / 64; p.ctus_y = (d->tile_h + 63) / 64;
+  p.map_pitch = d->n_dx;
+  p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
+  return launch_ime_sad_box(p, d->x0, d->y0, d->n_dx, d->n_dy, (cudaStream_t)stream);
 }
 
 int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
@@ -201,6 +239,10 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
     f.refs[i].n_sets = r.n_mapsets;
     for (int m = 0; m < r.n_mapsets; m++) {
       f.refs[i].sets[m].cx = r.mapsets[m].center_x; f.refs[i].sets[m].cy = r.mapsets[m].center_y;
+      f.refs[i].sets[m].n_dx = r.mapsets[m].n_dx; f.refs[i].sets[m].n_dy = r.mapsets[m].n_dy;
+      if (r.mapsets[m].n_dx < 0 || (r.mapsets[m].n_dx & 15) || r.mapsets[m].n_dx > kMeMaxBox || r.mapsets[m].n_dy < 0 ||
+          r.mapsets[m].n_dy > kMeMaxBox || (r.mapsets[m].n_dx > 0) != (r.mapsets[m].n_dy > 0))
+        return fail_msg("kvz_cuda_me_search: bad box map set");
       f.refs[i].sets[m].sad8 = r.mapsets[m].d_sad8; f.refs[i].sets[m].sad16 = r.mapsets[m].d_sad16;
       f.refs[i].sets[m].sad32 = r.mapsets[m].d_sad32; f.refs[i].sets[m].sad64 = r.mapsets[m].d_sad64;
     }

@@ -62,16 +62,20 @@ __device__ __forceinline__ void cp_async_wait_all()
 // the four PUs read by one warp of the writer fall into different banks
 __device__ __forceinline__ int stage_slot(int blk) { return blk ^ (((blk >> 2) & 1) | ((blk >> 4) & 2)); }
 
-template <int R>
+// geometry of one launch (runtime): n_dy displacement rows need n_dy + 63 tile rows
 struct Geo {
-  static constexpr int K = 2 * R + 1;
-  static constexpr int kRows = 2 * R + 64;
-  static constexpr int kCopyWords = kRows * kRowWords + 8;     // == 8 (mod 32): the 4 copies hit disjoint banks
-  static constexpr int kChunks = R / 8;                         // chunks of 16 dx: [-R, R); dx = +R is the last column
-  static constexpr int kIters = R / 4 + 1;                     // 8 tile rows each
-  static constexpr size_t kStageBytes = 8 * 64 * kChunkDx * 2;
-  static constexpr size_t kRawBytes = (size_t)kRows * kRawWords * 4;     // overlays the stage ring before the first iteration
-  static constexpr size_t kSmemBytes = (size_t)4 * kCopyWords * 4 + 64 * 64 + (kRawBytes > kStageBytes ? kRawBytes : kStageBytes);
+  int n_dy, rows, copy_words, iters;
+  __host__ __device__ explicit Geo(int n_dy_) : n_dy(n_dy_)
+  {
+    rows = n_dy + 63;
+    copy_words = ((rows * kRowWords + 31) & ~31) + 8;          // == 8 (mod 32): the 4 copies hit disjoint banks
+    iters = (n_dy + 7) >> 3;                                    // 8 tile rows each; the last one is partial
+  }
+  __host__ __device__ size_t smem_bytes() const
+  {
+    const size_t stage = 8 * 64 * kChunkDx * 2, raw = (size_t)rows * kRawWords * 4;   // raw overlays the ring before the first iteration
+    return (size_t)4 * copy_words * 4 + 64 * 64 + (raw > stage ? raw : stage);
+  }
 };
 
 struct SmemView {
@@ -123,28 +127,26 @@ struct WriterPos {
   uint32_t src16;     // u32 index of (first block of the 32x32 PU, dx pair) inside a ring slot
 };
 
-template <int R>
 __device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, int chunk, int tid)
 {
-  constexpr uint32_t K = Geo<R>::K;
+  const uint32_t PR = (uint32_t)p.pu_rows;
   const uint32_t rs = (uint32_t)p.map_pitch;
   WriterPos w;
   const int blk = (tid >> 1) & 63, half = tid & 1;
-  w.o8 = ((uint32_t)ctu * 64 + blk) * (K + 1) * rs + chunk * kChunkDx + half * 8;
+  w.o8 = ((uint32_t)ctu * 64 + blk) * PR * rs + chunk * kChunkDx + half * 8;
   w.src8 = stage_slot(blk) * kChunkDx + half * 8;
   const int lane = tid & 31, p32 = lane >> 3, dxp = lane & 7;
   const uint32_t col = chunk * kChunkDx + 2 * dxp;
-  w.o16 = ((uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2) * (K + 1) * rs + col;
-  w.o32 = ((uint32_t)ctu * 4 + p32) * (K + 1) * rs + col;
-  w.o64 = (uint32_t)ctu * (K + 1) * rs + col;
+  w.o16 = ((uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2) * PR * rs + col;
+  w.o32 = ((uint32_t)ctu * 4 + p32) * PR * rs + col;
+  w.o64 = (uint32_t)ctu * PR * rs + col;
   w.src16 = ((p32 >> 1) * 32 + (p32 & 1) * 4) * (kChunkDx / 2) + dxp;
   return w;
 }
 
-template <int R>
 __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPos &wp, const uint16_t *stage, int m, int tid)
 {
-  constexpr uint32_t K = Geo<R>::K;
+  const uint32_t PR = (uint32_t)p.pu_rows;
   const uint32_t rs = (uint32_t)p.map_pitch;
   const int k0 = 8 * m - 7;                       // dy of ring slot 0
   // (a) 8x8 map: thread = (block, half of the 16 dx), ring slots u0, u0+2, u0+4, u0+6
@@ -172,7 +174,7 @@ __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPo
         const int b = (q >> 1) * 16 + (q & 1) * 2;
         // packed u16 pairs: 4 x 16320 < 65536, no carry between the halves
         const uint32_t s16 = st[((b) ^ sw) * 8] + st[((b + 1) ^ sw) * 8] + st[((b + 8) ^ sw) * 8] + st[((b + 9) ^ sw) * 8];
-        *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * (K + 1) + (uint32_t)k) * rs) = s16;
+        *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * PR + (uint32_t)k) * rs) = s16;
         lo += s16 & 0xFFFFu;
         hi += s16 >> 16;
       }
@@ -184,7 +186,6 @@ __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPo
   }
 }
 
-template <int R>
 __device__ __forceinline__ void stage_cur(const ImeSadParams &p, uint8_t *cur, int ctu_x, int ctu_y, int tid, int nthreads)
 {
   // current CTU, coordinates clamped into the picture for partial CTUs
@@ -204,7 +205,7 @@ constexpr int kLcWords = 17;            // tile row pitch in words: odd, lanes (
 
 template <int R>
 struct LcSmem {
-  uint32_t tile[Geo<R>::kRows * kLcWords];
+  uint32_t tile[(2 * R + 64) * kLcWords];
   alignas(16) uint8_t cur[64 * 64];
   uint4 part16[8][((2 * R + 1) + 15) & ~15];     // per block row: sums of horizontally adjacent 8x8 pairs
   uint2 part32[4][((2 * R + 1) + 15) & ~15];     // per 16x16 row: sums of horizontally adjacent 16x16 pairs
@@ -214,23 +215,23 @@ struct LcSmem {
 template <int R>
 __device__ __forceinline__ void last_column(const ImeSadParams &p, unsigned char *smem_raw, int ctu)
 {
-  constexpr int K = Geo<R>::K;
+  constexpr int K = 2 * R + 1;
   LcSmem<R> &sm = *reinterpret_cast<LcSmem<R> *>(smem_raw);
   const int tid = threadIdx.x;
   const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
   const int rs = p.map_pitch;
   {
-    const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch + (ctu_x + p.center_x + R + p.pad);
+    const uint8_t *src = p.ref + (size_t)(ctu_y + p.y0 + p.pad) * p.ref_pitch + (ctu_x + p.x0 + 2 * R + p.pad);
     const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
     const int sh = (int)(a0 & 3) * 8;
     const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
 #pragma unroll 4
-    for (int i = tid; i < Geo<R>::kRows * 16; i += kThreads) {
+    for (int i = tid; i < (2 * R + 64) * 16; i += kThreads) {
       const int r = i >> 4, mw = i & 15;
       const uint32_t *w = reinterpret_cast<const uint32_t *>(src_al + (size_t)r * p.ref_pitch) + mw;
       sm.tile[r * kLcWords + mw] = __funnelshift_r(w[0], w[1], sh);
     }
-    stage_cur<R>(p, sm.cur, ctu_x, ctu_y, tid, kThreads);
+    stage_cur(p, sm.cur, ctu_x, ctu_y, tid, kThreads);
   }
   __syncthreads();
   // 8x8: item = (block row by, entry k); entries K .. pitch-1 of the row are written as zero
@@ -279,19 +280,20 @@ __device__ __forceinline__ void last_column(const ImeSadParams &p, unsigned char
 #ifndef KVZ_SAD_MINB
 #define KVZ_SAD_MINB 2
 #endif
-// one CTA = 16 dx (one chunk) x all dy of one CTU; the first n_ctu CTAs do the last column instead
-// (they are short and latency bound: started first, they overlap the rest)
+// one CTA = 16 dx (one chunk) x all dy of one CTU.  R > 0: square window, the first n_ctu CTAs do the last
+// column instead (they are short and latency bound: started first, they overlap the rest); R == 0: box
 template <int R>
 __global__ void __launch_bounds__(kThreads, KVZ_SAD_MINB)
 ime_sad_dense_kernel(ImeSadParams p)
 {
-  constexpr int CW = Geo<R>::kCopyWords;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x;
-  constexpr int kChunks = Geo<R>::kChunks;
-  const int n_ctu = p.ctus_x * p.ctus_y;
-  if ((int)blockIdx.x < n_ctu) {
-    last_column<R>(p, smem_raw, blockIdx.x);
+  const Geo geo(p.n_dy);
+  const int CW = geo.copy_words;
+  const int kChunks = p.n_chunks;
+  const int n_ctu = R > 0 ? p.ctus_x * p.ctus_y : 0;
+  if (R > 0 && (int)blockIdx.x < n_ctu) {
+    if constexpr (R > 0) last_column<R>(p, smem_raw, blockIdx.x);
   } else {
     const int bid = blockIdx.x - n_ctu;
     uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
@@ -300,23 +302,22 @@ ime_sad_dense_kernel(ImeSadParams p)
     const int chunk = bid % kChunks, ctu = bid / kChunks;
     const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
     {
-      // tile rows ctu_y+cy-R .., 84 bytes from column ctu_x+cx-R+16*chunk, as 4 byte-shifted copies
-      const uint8_t *src = p.ref + (size_t)(ctu_y + p.center_y - R + p.pad) * p.ref_pitch +
-                           (ctu_x + p.center_x - R + kChunkDx * chunk + p.pad);
+      // tile rows ctu_y+y0 .., 84 bytes from column ctu_x+x0+16*chunk, as 4 byte-shifted copies
+      const uint8_t *src = p.ref + (size_t)(ctu_y + p.y0 + p.pad) * p.ref_pitch + (ctu_x + p.x0 + kChunkDx * chunk + p.pad);
       const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
       const int sh = (int)(a0 & 3) * 8;
       const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
       // (1) raw rows (22 aligned words each) straight into shared memory, all copies in flight at once
       uint32_t *raw = reinterpret_cast<uint32_t *>(stage);
-      for (int i = tid; i < Geo<R>::kRows * kRawWords; i += kThreads) {
+      for (int i = tid; i < geo.rows * kRawWords; i += kThreads) {
         const int r = i / kRawWords, mw = i - r * kRawWords;
         cp_async4(raw + i, src_al + (size_t)r * p.ref_pitch + 4 * mw);
       }
-      stage_cur<R>(p, cur_s, ctu_x, ctu_y, tid, kThreads);
+      stage_cur(p, cur_s, ctu_x, ctu_y, tid, kThreads);
       cp_async_wait_all();
       __syncthreads();
       // (2) the four byte-shifted copies
-      for (int i = tid; i < Geo<R>::kRows * kRowWords; i += kThreads) {
+      for (int i = tid; i < geo.rows * kRowWords; i += kThreads) {
         const int r = i / kRowWords, mw = i - r * kRowWords;
         const uint32_t *w = raw + r * kRawWords + mw;
         const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
@@ -339,20 +340,20 @@ ime_sad_dense_kernel(ImeSadParams p)
     uint32_t acc[8][4];
     const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
     uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
-    const WriterPos wp = writer_pos<R>(p, ctu, chunk, tid);
+    const WriterPos wp = writer_pos(p, ctu, chunk, tid);
     rows8<0>(trow, cur, acc, stg);
     __syncthreads();
-    write_rows<R>(p, wp, stage, 0, tid);
+    write_rows(p, wp, stage, 0, tid);
     __syncthreads();
-    for (int m = 1; m < Geo<R>::kIters - 1; m++) {
+    for (int m = 1; m < geo.iters - 1; m++) {
       rows8<1>(trow + m * 8 * kRowWords, cur, acc, stg);
       __syncthreads();
-      write_rows<R>(p, wp, stage, m, tid);
+      write_rows(p, wp, stage, m, tid);
       __syncthreads();
     }
-    rows8<2>(trow + (Geo<R>::kIters - 1) * 8 * kRowWords, cur, acc, stg);
+    rows8<2>(trow + (geo.iters - 1) * 8 * kRowWords, cur, acc, stg);
     __syncthreads();
-    write_rows<R>(p, wp, stage, Geo<R>::kIters - 1, tid);
+    write_rows(p, wp, stage, geo.iters - 1, tid);
   }
 }
 
@@ -390,27 +391,36 @@ template <int R>
 static int launch_r(const ImeSadParams &p, cudaStream_t stream)
 {
   auto kern = ime_sad_dense_kernel<R>;
-  KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Geo<R>::kSmemBytes));
+  const Geo geo(p.n_dy);
+  size_t smem = geo.smem_bytes();
+  if (R > 0 && sizeof(LcSmem<(R > 0 ? R : 8)>) > smem) smem = sizeof(LcSmem<(R > 0 ? R : 8)>);   // last-column CTAs share the launch
+  if (smem > 113 * 1024) return fail_msg("ime_sad: too many displacement rows for the shared-memory tile");
+  KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int n_ctu = p.ctus_x * p.ctus_y;
-  static_assert(sizeof(LcSmem<R>) <= Geo<R>::kSmemBytes, "last-column CTAs share the launch's shared memory size");
-  kern<<<(Geo<R>::kChunks + 1) * n_ctu, kThreads, Geo<R>::kSmemBytes, stream>>>(p);   // per CTU: dx = +R, then R/8 chunks of 16 dx
+  kern<<<(p.n_chunks + (R > 0 ? 1 : 0)) * n_ctu, kThreads, smem, stream>>>(p);   // per CTU: [dx = +R,] then chunks of 16 dx
   count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
   return 1;
 }
 
-int launch_ime_sad_dense(const ImeSadParams &p, int range, cudaStream_t stream)
+int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, cudaStream_t stream)
 {
-  int ok;
+  p.x0 = center_x - range; p.y0 = center_y - range;
+  p.n_dy = 2 * range + 1; p.n_chunks = range / 8; p.pu_rows = p.n_dy + 1;
   switch (range) {
-    case 8:  ok = launch_r<8>(p, stream); break;
-    case 16: ok = launch_r<16>(p, stream); break;
-    case 32: ok = launch_r<32>(p, stream); break;
-    case 64: ok = launch_r<64>(p, stream); break;
+    case 8:  return launch_r<8>(p, stream);
+    case 16: return launch_r<16>(p, stream);
+    case 32: return launch_r<32>(p, stream);
+    case 64: return launch_r<64>(p, stream);
     default: return fail_msg("ime_sad_dense: range must be 8, 16, 32 or 64");
   }
-  if (!ok) return 0;
-  KVZ_CUDA_LAUNCH_CHECK();
-  return 1;
+}
+
+int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream)
+{
+  if (n_dx <= 0 || (n_dx & 15) || n_dy <= 0 || (n_dy & 7) != 1) return fail_msg("ime_sad_box: n_dx must be a multiple of 16, n_dy == 1 (mod 8)");
+  p.x0 = x0; p.y0 = y0; p.n_dy = n_dy; p.n_chunks = n_dx / 16; p.pu_rows = n_dy;
+  return launch_r<0>(p, stream);
 }
 
 }  // namespace kvz

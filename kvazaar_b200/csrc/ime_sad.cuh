@@ -13,17 +13,24 @@ struct ImeSadParams {
   int pad;                 // border of the padded reference plane
   int tile_x, tile_y, tile_w, tile_h;   // tile rectangle searched (whole frame: 0,0,width,height)
   int ctus_x, ctus_y;      // CTUs in the tile
-  int center_x, center_y;  // window centre: map[dy+R][dx+R] is the SAD at displacement (center_x+dx, center_y+dy)
-  int map_pitch;           // entries per (pu, dy) row of every map: roundup(2R+1, 16)
-  uint16_t *sad8;          // [ctu*64 + by*8+bx][2R+1][map_pitch]
-  uint16_t *sad16;         // [ctu*16 + py*4+px][2R+1][map_pitch]
-  uint32_t *sad32;         // [ctu*4  + py*2+px][2R+1][map_pitch]
-  uint32_t *sad64;         // [ctu][2R+1][map_pitch]
+  int x0, y0;              // first displacement: map[i][j] is the SAD at displacement (x0 + j, y0 + i)
+  int n_dy;                // displacement rows computed, == 1 (mod 8)
+  int n_chunks;            // chunks of 16 displacement columns computed by the chunk CTAs
+  int pu_rows;             // map rows per PU: n_dy, or n_dy + 1 when row n_dy holds the column dx = x0 + 16*n_chunks
+  int map_pitch;           // entries per map row
+  uint16_t *sad8;          // [ctu*64 + by*8+bx][pu_rows][map_pitch]
+  uint16_t *sad16;         // [ctu*16 + py*4+px][pu_rows][map_pitch]
+  uint32_t *sad32;         // [ctu*4  + py*2+px][pu_rows][map_pitch]
+  uint32_t *sad64;         // [ctu][pu_rows][map_pitch]
 };
 
 int ime_map_pitch(int range);
 int launch_pad_plane(const void *src, int w, int h, int src_pitch, void *dst, int pad, int dst_pitch,
                      int bitdepth, cudaStream_t stream);
-int launch_ime_sad_dense(const ImeSadParams &p, int range, cudaStream_t stream);
+// square window [-range, range]^2 round (center_x, center_y): K = 2*range+1 rows of K-1 columns, the last
+// column as row K; fills x0, y0, n_dy, n_chunks, pu_rows of `p`
+int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, cudaStream_t stream);
+// rectangular box: n_dx (multiple of 16) x n_dy (== 1 mod 8) displacements from (x0, y0), plain row-major maps
+int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream);
 
 }  // namespace kvz

@@ -210,8 +210,8 @@ __device__ __forceinline__ unsigned long long warp_min(unsigned long long v)
 
 // per-window separable tables of the AMVP bit cost: bits = min_c(gx[c][col] + gy[c][row])
 struct BitTables {
-  alignas(16) uint2 gx[132];     // lambda * bits of column i for AMVP candidate 0 (.x) and 1 (.y)
-  uint2 gy[132];                 // same for row i
+  alignas(16) uint2 gx[kMeMaxBox];    // lambda * bits of column i for AMVP candidate 0 (.x) and 1 (.y)
+  alignas(16) uint2 gy[kMeMaxBox];    // same for row i
 };
 
 // ======================================================================================
@@ -227,9 +227,10 @@ constexpr int kScanWarps = 4;
 
 struct ScanSmem {
   BitTables bt;
-  int hit_pos[5];
+  int hit_pos[5];             // window position (row * K + col); box scan: row << 16 | col of the box
   int hit_bits[5];
   int n_hit;
+  uint8_t rowwin[kMeMaxBox];  // box scan: windows (bit w) that cover box row i
 };
 
 // one search window of search_mv_full
@@ -295,6 +296,164 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     level = j.w == 8 ? 0 : j.w == 16 ? 1 : j.w == 32 ? 2 : 3;
 
   unsigned long long best = ~0ull;
+
+  // ---- a box map set that covers every window of this job: one pass over the union ----
+  int bi = -1;
+  if (level >= 0) {
+    int lox = wcx[0], hix = wcx[0], loy = wcy[0], hiy = wcy[0];
+    for (int w = 1; w < nwin; w++) {
+      lox = min(lox, wcx[w]); hix = max(hix, wcx[w]);
+      loy = min(loy, wcy[w]); hiy = max(hiy, wcy[w]);
+    }
+    for (int m = 0; m < ref.n_sets; m++) {
+      const MeMapSet &ms = ref.sets[m];
+      const void *mp = level == 0 ? (const void *)ms.sad8 : level == 1 ? (const void *)ms.sad16
+                     : level == 2 ? (const void *)ms.sad32 : (const void *)ms.sad64;
+      if (ms.n_dx > 0 && mp != nullptr && lox - R >= ms.cx && hix + R < ms.cx + ms.n_dx && loy - R >= ms.cy &&
+          hiy + R < ms.cy + ms.n_dy) { bi = m; break; }
+    }
+  }
+  if (bi >= 0) {
+    // Every displacement of the union of the windows is priced once.  A displacement belongs to the
+    // FIRST window of the list that covers it (a later window meets it again with the same cost and
+    // loses the tie), so the key of a candidate is (cost, that window, its position in that window).
+    const MeMapSet &ms = ref.sets[bi];
+    const int bx0 = ms.cx, by0 = ms.cy, n_dx = ms.n_dx, n_dy = ms.n_dy;
+    __syncwarp();
+    for (int i = lane; i < n_dx; i += G) {
+      const int qx = (bx0 + i) * 4;
+      const uint32_t lam = (uint32_t)j.lambda;
+      sm.bt.gx[i] = make_uint2(lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
+    }
+    for (int i = lane; i < n_dy; i += G) {
+      const int qy = (by0 + i) * 4;
+      const uint32_t lam = (uint32_t)j.lambda;
+      sm.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
+      uint32_t wm = 0;
+      for (int w = 0; w < nwin; w++) wm |= (uint32_t)(abs(by0 + i - wcy[w]) <= R) << w;
+      sm.rowwin[i] = (uint8_t)wm;
+    }
+    if (lane == 0) {
+      int n = 0;
+#pragma unroll
+      for (int i = 0; i < 5; i++) {
+        if (!((j.mvalid >> i) & 1u)) continue;
+        const int mvx = (int16_t)(j.mkey[i] >> 16), mvy = (int16_t)(j.mkey[i] & 0xFFFFu);
+        if ((mvx & 3) || (mvy & 3)) continue;
+        const int col = (mvx >> 2) - bx0, row = (mvy >> 2) - by0;
+        if (col < 0 || col >= n_dx || row < 0 || row >= n_dy) continue;
+        const int pos = (row << 16) | col;
+        bool dup = false;
+        for (int q = 0; q < n; q++) dup |= sm.hit_pos[q] == pos;     // first matching candidate wins
+        if (!dup) { sm.hit_pos[n] = pos; sm.hit_bits[n] = i; n++; }
+      }
+      sm.n_hit = n;
+    }
+    __syncwarp();
+    const int n_hit = sm.n_hit;
+    const int n = 8 >> level;
+    const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
+    const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
+    const int vpr = n_dx >> 3;
+    uint32_t wbest = 0xFFFFFFFFu, wkey = 0xFFFFFFFFu;
+
+    // exact pricing of the candidates of one vector that can still win
+    auto exact8 = [&](int row, int c0, const uint32_t (&sad)[8], uint32_t mask) {
+#pragma unroll 1
+      for (int e = 0; e < 8; e++) {
+        if (!((mask >> e) & 1u)) continue;
+        const int col = c0 + e, dx = bx0 + col, dy = by0 + row;
+        if (!free_mv && !within_tile(f, j, dx * 4, dy * 4)) continue;
+        const uint2 gx = sm.bt.gx[col], gy = sm.bt.gy[row];
+        uint32_t mvd = min(gx.x + gy.x, gx.y + gy.y);
+        for (int q = 0; q < n_hit; q++)
+          if (sm.hit_pos[q] == ((row << 16) | col)) mvd = (uint32_t)sm.hit_bits[q] * (uint32_t)j.lambda;
+        const uint32_t cost = sad[e] + mvd;
+        if (cost > wbest) continue;
+        uint32_t key = 0xFFFFFFFFu;
+        for (int w = 0; w < nwin; w++)
+          if (abs(dx - wcx[w]) <= R && abs(dy - wcy[w]) <= R) {
+            key = ((uint32_t)w << 16) | (uint32_t)((dy - wcy[w] + R) * K + dx - wcx[w] + R);
+            break;
+          }
+        if (cost < wbest || key < wkey) { wbest = cost; wkey = key; }
+      }
+    };
+    // columns of the vector at c0 that some window of mask `rw` covers
+    auto cover_mask = [&](int c0, uint32_t rw) {
+      uint32_t mask = 0;
+      for (int w = 0; w < nwin; w++) {
+        if (!((rw >> w) & 1u)) continue;
+        const int lo = wcx[w] - R - bx0 - c0, hi = lo + 2 * R;         // covered columns relative to c0
+        if (hi < 0 || lo > 7) continue;
+        mask |= (0xFFu << max(lo, 0)) & (0xFFu >> (7 - min(hi, 7)));
+      }
+      return mask & 0xFFu;
+    };
+    // window 0 (the zero window) covers most of the box: inside it nothing else needs looking at
+    const int z_r0 = -R - by0, z_c0 = -R - bx0;
+
+    auto price = [&](int row, int vec, const uint32_t (&sad)[8]) {
+      const int c0 = vec * 8;
+      uint32_t mask = 0xFFu;
+      if (!((unsigned)(row - z_r0) <= (unsigned)(2 * R) && c0 >= z_c0 && c0 + 7 <= z_c0 + 2 * R))
+        mask = cover_mask(c0, sm.rowwin[row]);
+      if (mask == 0) return;
+      bool special = !free_mv;
+      for (int q = 0; q < n_hit; q++) special |= (sm.hit_pos[q] >> 3) == ((row << 13) | vec);
+      if (!special) {
+        const uint2 gy = sm.bt.gy[row];
+        const int d = (int)gy.y - (int)gy.x;
+        const uint4 *gxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
+        int m = 0x7FFFFFFF;
+#pragma unroll
+        for (int e2 = 0; e2 < 4; e2++) {
+          const uint4 g4 = gxp[e2];                                       // columns c0+2*e2, c0+2*e2+1
+          // min(a0 + b0, a1 + b1) - b0 = min(a0, a1 + d): signed, b0 is added back below
+          const int ka = (int)sad[2 * e2] + min((int)g4.x, (int)g4.y + d);
+          const int kb = (int)sad[2 * e2 + 1] + min((int)g4.z, (int)g4.w + d);
+          m = min(m, ((mask >> (2 * e2)) & 1u) ? ka : 0x7FFFFFFF);
+          m = min(m, ((mask >> (2 * e2 + 1)) & 1u) ? kb : 0x7FFFFFFF);
+        }
+        if ((uint32_t)(m + (int)gy.x) > wbest) return;
+      }
+      exact8(row, c0, sad, mask);
+    };
+
+    if (level < 2) {
+      const uint16_t *mp = (level == 0 ? ms.sad8 : ms.sad16) + prow * (size_t)n_dy * n_dx;
+      const int total = n_dy * vpr;
+      for (int i0 = lane; i0 < total; i0 += KVZ_SCAN_DEPTH * G) {
+        uint4 v[KVZ_SCAN_DEPTH];
+#pragma unroll
+        for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
+          const int i = i0 + u * G;
+          v[u] = i < total ? __ldg(reinterpret_cast<const uint4 *>(mp) + i) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
+          const int i = i0 + u * G;
+          if (i >= total) break;
+          const int row = i / vpr, vec = i - row * vpr;
+          const uint32_t sad[8] = { v[u].x & 0xFFFFu, v[u].x >> 16, v[u].y & 0xFFFFu, v[u].y >> 16,
+                                    v[u].z & 0xFFFFu, v[u].z >> 16, v[u].w & 0xFFFFu, v[u].w >> 16 };
+          price(row, vec, sad);
+        }
+      }
+    } else {
+      const uint32_t *mp = (level == 2 ? ms.sad32 : ms.sad64) + prow * (size_t)n_dy * n_dx;
+      const int total = n_dy * vpr;
+      for (int i = lane; i < total; i += G) {
+        const uint4 va = __ldg(reinterpret_cast<const uint4 *>(mp) + 2 * i);
+        const uint4 vb = __ldg(reinterpret_cast<const uint4 *>(mp) + 2 * i + 1);
+        const int row = i / vpr, vec = i - row * vpr;
+        const uint32_t sad[8] = { va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w };
+        price(row, vec, sad);
+      }
+    }
+    if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | wkey;
+    nwin = 0;                                     // nothing left for the per-window path
+  }
 
   for (int wi = 0; wi < nwin; wi++) {
     const int cx = wcx[wi], cy = wcy[wi];

@@ -6,8 +6,11 @@
 
 namespace kvz {
 
+constexpr int kMeMaxBox = 272;     // largest box side (displacements) kvz_cuda_me_search reads
+
 struct MeMapSet {
-  int cx, cy;                // window centre the maps were made for
+  int cx, cy;                // window centre the maps were made for; first displacement (x0, y0) of a box
+  int n_dx, n_dy;            // box size, 0 = square window of the frame's range
   const uint16_t *sad8, *sad16;
   const uint32_t *sad32, *sad64;
 };

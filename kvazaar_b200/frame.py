@@ -117,6 +117,52 @@ class ImeSearch:
         return (tw // 8) * (th // 8) * 64 * self.k * self.k
 
 
+class ImeBoxSearch:
+    """Dense SAD maps over a rectangular box of displacements (kvz_cuda_ime_sad_box_maps):
+    map[level][pu][dy - y0][dx - x0], n_dx a multiple of 16, n_dy == 1 (mod 8)."""
+
+    def __init__(self, width, height, box, tile=None, device="cuda"):
+        capi.init(torch.cuda.current_device())
+        self.width, self.height = width, height
+        self.tile = tile or (0, 0, width, height)
+        x0, y0, n_dx, n_dy = box
+        n_dx = (n_dx + 15) & ~15
+        n_dy = ((n_dy - 1 + 7) & ~7) + 1
+        self.box = (x0, y0, n_dx, n_dy)
+        far = max(abs(x0), abs(x0 + n_dx), abs(y0), abs(y0 + n_dy))
+        self.pad = (96 + far + 31) & ~31
+        tw, th = self.tile[2], self.tile[3]
+        self.ctus_x, self.ctus_y = (tw + 63) // 64, (th + 63) // 64
+        n_ctu = self.ctus_x * self.ctus_y
+        self.maps = []
+        for level in range(4):
+            n = 8 >> level
+            dt = torch.int16 if level < 2 else torch.int32
+            self.maps.append(torch.empty((n_ctu * n * n, n_dy, n_dx), dtype=dt, device=device))
+        self.desc = capi.ImeBoxDesc()
+
+    pu_index = ImeSearch.pu_index
+
+    def run(self, cur, ref_padded, maps=None):
+        if maps is not None:
+            self.maps = maps
+        d = self.desc
+        d.width, d.height, d.bitdepth = self.width, self.height, 8
+        d.tile_x, d.tile_y, d.tile_w, d.tile_h = self.tile
+        d.cur_pitch = cur.stride(0) * cur.element_size()
+        d.ref_pitch, d.ref_pad = ref_padded.pitch_bytes, ref_padded.pad
+        d.x0, d.y0, d.n_dx, d.n_dy = self.box
+        capi.check(capi.lib().kvz_cuda_ime_sad_box_maps(
+            C.byref(d), C.c_void_p(cur.data_ptr()), C.c_void_p(ref_padded.data.data_ptr()),
+            C.c_void_p(self.maps[0].data_ptr()), C.c_void_p(self.maps[1].data_ptr()),
+            C.c_void_p(self.maps[2].data_ptr()), C.c_void_p(self.maps[3].data_ptr()), _stream_ptr()),
+            "kvz_cuda_ime_sad_box_maps")
+        return self.maps
+
+    def map_bytes(self):
+        return sum(m.numel() * m.element_size() for m in self.maps)
+
+
 # numpy mirrors of the job structures of include/kvz_cuda.h
 import numpy as np  # noqa: E402
 
@@ -158,7 +204,8 @@ class MeSearch:
 
     def set_refs(self, padded_planes, maps=None):
         """padded_planes: list of PaddedPlane; maps: per reference either the 4 zero-window map
-        tensors, or a list of ((center_x, center_y), [4 tensors]) map sets, or None."""
+        tensors, or a list of map sets -- ((center_x, center_y), [4 tensors]) for a square window,
+        ((x0, y0, n_dx, n_dy), [4 tensors]) for a box -- or None."""
         self.frame.n_refs = len(padded_planes)
         for i, pp in enumerate(padded_planes):
             r = self.frame.refs[i]
@@ -173,7 +220,8 @@ class MeSearch:
             r.n_mapsets = len(sets)
             for k, (c, t) in enumerate(sets):
                 ms = r.mapsets[k]
-                ms.center_x, ms.center_y = c
+                ms.center_x, ms.center_y = c[0], c[1]
+                ms.n_dx, ms.n_dy = (c[2], c[3]) if len(c) == 4 else (0, 0)
                 ms.d_sad8, ms.d_sad16, ms.d_sad32, ms.d_sad64 = [x.data_ptr() for x in t]
         self._keep.append((padded_planes, maps))
 

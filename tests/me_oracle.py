@@ -108,20 +108,26 @@ def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sq
     return res
 
 
-def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), **cfg):
-    """The CUDA path through the C ABI for the same inputs (numpy in, numpy out)."""
+def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), box=None, **cfg):
+    """The CUDA path through the C ABI for the same inputs (numpy in, numpy out).
+    centres: extra square-window map sets; box: (x0, y0, n_dx, n_dy) of one box map set per reference
+    (jobs whose windows all lie inside it are searched from the box)."""
     import torch
     import kvazaar_b200 as kb
     from kvazaar_b200.frame import ME_RESULT_DT, MeSearch
     cur_d = torch.from_numpy(cur).cuda()
     max_c = max([0] + [max(abs(c[0]), abs(c[1])) for c in centres])
     ime = kb.ImeSearch(width, height, rng, max_center=max_c)
+    bx = kb.ImeBoxSearch(width, height, box) if box is not None else None
+    pad = max(ime.pad, bx.pad if bx else 0)
     planes, maps = [], []
     for r in refs:
-        pp = kb.PaddedPlane(width, height, ime.pad).fill_from(torch.from_numpy(r).cuda())
+        pp = kb.PaddedPlane(width, height, pad).fill_from(torch.from_numpy(r).cuda())
         planes.append(pp)
         if use_maps:
             sets = [((0, 0), [m.clone() for m in ime.run(cur_d, pp)])]
+            if bx is not None:
+                sets.insert(0, (bx.box, [m.clone() for m in bx.run(cur_d, pp)]))
             for c in centres:
                 sets.append((tuple(c), [m.clone() for m in ime.run(cur_d, pp, center=tuple(c))]))
             maps.append(sets)

@@ -110,3 +110,31 @@ def test_hierarchy_property_1080p():
         s = prev.view(len(full), n, 2, n, 2, k, k).sum(dim=(2, 4))
         assert torch.equal(s, cur), level
         prev = cur
+
+
+@pytest.mark.parametrize("box", [(-8, -8, 32, 17), (-20, 3, 48, 25), (5, -30, 16, 41)])
+def test_box_maps_small_frame(box):
+    """kvz_cuda_ime_sad_box_maps: every entry of a rectangular displacement box vs the oracle's clamped SAD."""
+    import torch
+    import kvazaar_b200 as kb
+    w, h = 200, 136
+    f = kvzlibs.synth_luma(17, w, h, 2)
+    O = kvzlibs.oracle()
+    srch = kb.ImeBoxSearch(w, h, box)
+    x0, y0, n_dx, n_dy = srch.box
+    padded = kb.PaddedPlane(w, h, srch.pad).fill_from(torch.from_numpy(f[0]).cuda())
+    maps = [m.cpu().numpy() for m in srch.run(torch.from_numpy(f[1]).cuda(), padded)]
+    torch.cuda.synchronize()
+    rs = np.random.default_rng(3)
+    for level in range(4):
+        size = 8 << level
+        pus = [(x, y) for y in range(0, h - size + 1, size) for x in range(0, w - size + 1, size)]
+        if len(pus) > 24:
+            pus = [pus[0], pus[-1]] + [pus[i] for i in rs.choice(len(pus), 22, replace=False)]
+        for (x, y) in pus:
+            got = maps[level][srch.pu_index(level, x, y)].astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
+            want = np.zeros((n_dy, n_dx), np.uint32)
+            for i in range(n_dy):
+                for j in range(n_dx):
+                    want[i, j] = O.kvzo_image_sad_8(ptr(f[1]), ptr(f[0]), w, h, x, y, x + x0 + j, y + y0 + i, size, size)
+            assert np.array_equal(got, want), (level, x, y)

@@ -9,7 +9,7 @@ import me_oracle
 pytestmark = pytest.mark.gpu
 
 
-def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 16, 32, 64), centres=(), **cfg):
+def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 16, 32, 64), centres=(), box=None, **cfg):
     rs = np.random.default_rng(seed)
     f = kvzlibs.synth_luma(seed, width, height, n_refs + 1)
     cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
@@ -24,7 +24,7 @@ def _run(width, height, rng, fme, n_refs, count, seed, use_maps=True, sizes=(8, 
                 pus[i]["merge_cand"][0]["mv"][:] = (c[0] * 4, c[1] * 4)
     lam = int(rs.integers(3, 45))
     got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps,
-                               centres=centres, **cfg)
+                               centres=centres, box=box, **cfg)
     want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, fme, lam, **cfg)
     me_oracle.assert_results_equal(got, want, pus)
     return got
@@ -75,3 +75,26 @@ def test_white_noise():
 def test_1080p_full32_sampled():
     # BASELINE config 2 geometry; oracle on a sample of PUs
     _run(1920, 1080, 32, 4, 2, 24, 13)
+
+
+def test_box_map_sets_union_of_windows():
+    # one box per reference that covers the zero window and the windows round the cached centres: jobs
+    # whose windows all lie inside it take the single-pass union scan (first covering window owns a
+    # displacement), the others the per-window path
+    _run(256, 192, 16, 4, 2, 64, 21, centres=[(5, 3), (-7, 10)], box=(-16 - 7, -16, 16 + 5 + 16 + 7 + 1, 16 + 10 + 16 + 1))
+    _run(256, 192, 8, 4, 3, 64, 22, centres=[(3, -2)], box=(-8, -10, 8 + 3 + 8 + 1, 8 + 10 + 1))
+
+
+def test_box_map_sets_with_restrictions_and_ties():
+    # flat content makes equal costs frequent: the (cost, window, position) order has to hold in the union scan
+    import kvzlibs as kl
+    width, height, rng, n_refs = 200, 136, 8, 2
+    rs = np.random.default_rng(5)
+    f = kl.synth_luma(23, width, height, n_refs + 1)
+    f = [(x // 64) * 64 for x in f]                       # 4 grey levels: many ties
+    cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
+    pus, jobs = me_oracle.random_pus(rs, width, height, n_refs, 48, mv_span=rng)
+    for kw in ({}, {"owf": 1, "wpp": 1}, {"mv_constraint": 4}):
+        got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, 4, 20, box=(-16, -16, 48, 33), **kw)
+        want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, 4, 20, **kw)
+        me_oracle.assert_results_equal(got, want, pus)
