@@ -210,7 +210,7 @@ def run_ours(args):
     # every rank searches its own frames (same-temporal-layer frames of the GOP-8 pyramid are
     # independent): weak scaling, no data-path collective inside the ME stage
     frames = synth_frames(NREFS + 1, seed=2 + rank)
-    pipe = kb.MePipeline(W, H, RANGE, NREFS, lambda_sqrt=LAMBDA_SQRT, fme_level=4)
+    pipe = kb.MePipeline(W, H, RANGE, NREFS, lambda_sqrt=LAMBDA_SQRT, fme_level=4, use_boxes=not args.separate_windows)
     host_cur = torch.from_numpy(frames[NREFS]).pin_memory()
     host_refs = [torch.from_numpy(frames[NREFS - 1 - i]).pin_memory() for i in range(NREFS)]
     pipe.upload(host_cur, host_refs)
@@ -293,41 +293,52 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     int_peak = kb.measure_int_pipe_peak()
-    abs_diffs = pipe.ime.algorithmic_abs_diffs()
-    map_bytes = pipe.ime.algorithmic_bytes()
+    abs_diffs = pipe.algorithmic_abs_diffs            # of all SAD launches of one step
+    map_bytes = pipe.algorithmic_map_bytes + NREFS * 2 * W * H
+    n_sad = pipe.n_sad_launches
     achieved_ops = abs_diffs / (sad_ms * 1e-3)
     step_ms = ms / args.steps
+    kernel = "ime_sad_dense_kernel<0> (box)" if pipe.use_boxes else "ime_sad_dense_kernel<32>"
+    traffic = pipe.NCU_TRAFFIC_BYTES
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage: "
                                "pad + dense SAD maps + per-PU decision (search_mv_full) + fractional "
-                               "refinement (search_frac), 42900 PUs x 4225 candidates x 4 refs per step",
+                               "refinement (search_frac), 42900 PUs x 4 refs per step",
+                   "candidates": "value counts the nominal window only, %d = PUs x 4225 x refs per step, for both arms; "
+                                 "search_mv_full also visits the extra_mv / merge-candidate windows (%d windows of 4225 "
+                                 "per PU here), which the reference arm re-evaluates where they overlap while the device "
+                                 "evaluates each distinct displacement of a PU once (%d SADs per step), with "
+                                 "bit-identical decisions"
+                                 % (cands_per_frame(), sum(len(c) for c in pipe.centres),
+                                    sum(pipe.union_area) * (32400 + 8040 + 1980 + 480)),
                    "frames_per_s": 1e3 / step_ms * world,
                    "l2": "per step %.0f MB of SAD maps are written and read back: larger than the 126 MB L2, "
-                         "no flush needed" % (map_bytes * pipe.n_sad_launches / 1e6),
+                         "no flush needed" % (pipe.map_bytes / 1e6),
                    "stages": pipe.stages + (["publish_reference (NCCL broadcast of one luma plane) x1"] if world > 1 else []),
                    "parallelism": "frames of one temporal layer per GPU (weak scaling), no data-path collective in ME",
-                   "kernel_ms": {"ime_sad_dense x1": sad_ms, "me_search x1": search_ms,
-                                 "sad_launches_per_step": pipe.n_sad_launches, "share_sad": pipe.n_sad_launches * sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
+                   "kernel_ms": {"ime_sad x%d" % n_sad: sad_ms, "me_search (scan + refine x2)": search_ms,
+                                 "share_sad": sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
         "clocks": clk,
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes},
         "gpu_launches": int(launches),
         # the dense SAD kernel is bound by the integer (ALU) pipe; the denominator is
-        # measured in this run by a register-only VABSDIFF4 loop (MEASURED_PEAKS.json has no integer figure)
-        "roofline": {"kernel": "ime_sad_dense_kernel<32>", "bound": "int_pipe",
+        # measured in this run by a register-only VABSDIFF4 loop (MEASURED_PEAKS.json has no integer figure).
+        # achieved = the absolute differences the step's %d launches must evaluate / their summed duration.
+        "roofline": {"kernel": kernel, "bound": "int_pipe",
                      "achieved": achieved_ops / 1e12, "peak": int_peak / 1e12, "unit": "Tabsdiff/s",
                      "frac": achieved_ops / int_peak,
                      "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",
-                     "algorithmic_abs_diffs": abs_diffs, "ms_per_launch": sad_ms,
-                     "traffic": pipe.NCU_TRAFFIC_BYTES},
-        "roofline_hbm": {"kernel": "ime_sad_dense_kernel<32>", "bound": "hbm",
+                     "algorithmic_abs_diffs": abs_diffs, "launches": n_sad, "ms_per_launch": sad_ms / n_sad,
+                     "traffic": traffic},
+        "roofline_hbm": {"kernel": kernel, "bound": "hbm",
                          "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "traffic": pipe.NCU_TRAFFIC_BYTES, "algorithmic_bytes": map_bytes},
+                         "traffic": traffic, "algorithmic_bytes": map_bytes},
     }
     # bounded CPU baseline on the same host, rank 0, N=1 only
     if world == 1 and not args.no_cpu_baseline:
@@ -350,6 +361,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--separate-windows", action="store_true",
+                    help="one square-window SAD map set per window centre instead of one box per reference")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

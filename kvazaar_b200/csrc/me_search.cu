@@ -225,12 +225,20 @@ constexpr int kScanWarps = 4;
 #define KVZ_SCAN_MINB 6
 #endif
 
+constexpr int kScanRing = 8;             // 16-byte pieces in flight per lane of the box scan
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
+{
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+
 struct ScanSmem {
   BitTables bt;
   int hit_pos[5];             // window position (row * K + col); box scan: row << 16 | col of the box
   int hit_bits[5];
   int n_hit;
-  uint8_t rowwin[kMeMaxBox];  // box scan: windows (bit w) that cover box row i
+  alignas(16) uint4 ring[kScanRing][32];   // box scan: per-lane stream of map vectors (cp.async)
+  uint32_t rowinfo[kMeMaxBox];   // box scan, per box row: covered column run lo | hi << 9, bit 18 = several runs, bits 19.. = windows
 };
 
 // one search window of search_mv_full
@@ -257,6 +265,46 @@ __device__ __noinline__ uint32_t exact_cost(const WinCtx &w, int row, int col, u
   return sad + mvd;
 }
 
+// union scan of a box: what the rare paths need
+struct BoxCtx {
+  const MeFrame *f;
+  const JobCtx *j;
+  const ScanSmem *sm;
+  const int *wcx, *wcy;
+  int nwin, n_hit;
+  int bx0, by0, R, K;
+  bool free_mv;
+};
+
+// exact cost of the box entry (row, col): tile restriction and merge override included; ~0u if excluded
+__device__ __noinline__ uint32_t box_price(const BoxCtx &b, int row, int col, uint32_t sad)
+{
+  const int dx = b.bx0 + col, dy = b.by0 + row;
+  if (!b.free_mv && !within_tile(*b.f, *b.j, dx * 4, dy * 4)) return 0xFFFFFFFFu;
+  const uint2 gx = b.sm->bt.gx[col], gy = b.sm->bt.gy[row];
+  uint32_t mvd = min(gx.x + gy.x, gx.y + gy.y);
+  for (int q = 0; q < b.n_hit; q++)
+    if (b.sm->hit_pos[q] == ((row << 16) | col)) mvd = (uint32_t)b.sm->hit_bits[q] * (uint32_t)b.j->lambda;
+  return sad + mvd;
+}
+
+// (first covering window << 16) | position inside that window, of the box entry pos = row << 16 | col
+__device__ __noinline__ uint32_t box_key(const BoxCtx &b, uint32_t pos)
+{
+  const int dx = b.bx0 + (int)(pos & 0xFFFFu), dy = b.by0 + (int)(pos >> 16);
+  for (int w = 0; w < b.nwin; w++)
+    if (abs(dx - b.wcx[w]) <= b.R && abs(dy - b.wcy[w]) <= b.R)
+      return ((uint32_t)w << 16) | (uint32_t)((dy - b.wcy[w] + b.R) * b.K + dx - b.wcx[w] + b.R);
+  return 0xFFFFFFFFu;
+}
+
+// two box entries of equal cost: the one search_mv_full meets first
+__device__ __noinline__ uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint32_t pos_b)
+{
+  return box_key(b, pos_b) < box_key(b, pos_a) ? pos_b : pos_a;
+}
+
+template <bool BOX>
 __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
                          const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
 {
@@ -313,12 +361,23 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
           hiy + R < ms.cy + ms.n_dy) { bi = m; break; }
     }
   }
-  if (bi >= 0) {
+  if ((bi >= 0) != BOX) return;                 // the other instantiation of the kernel owns this job
+  if constexpr (BOX) {
     // Every displacement of the union of the windows is priced once.  A displacement belongs to the
     // FIRST window of the list that covers it (a later window meets it again with the same cost and
     // loses the tie), so the key of a candidate is (cost, that window, its position in that window).
     const MeMapSet &ms = ref.sets[bi];
+    BoxCtx bc;
+    bc.f = &f; bc.j = &j; bc.sm = &sm; bc.wcx = wcx; bc.wcy = wcy; bc.nwin = nwin;
+    bc.bx0 = ms.cx; bc.by0 = ms.cy; bc.R = R; bc.K = K; bc.free_mv = free_mv;
+    uint32_t wbest = 0xFFFFFFFFu, wpos = 0;          // best cost so far and its box entry (row << 16 | col)
     const int bx0 = ms.cx, by0 = ms.cy, n_dx = ms.n_dx, n_dy = ms.n_dy;
+    bool close_x;
+    {
+      int lox = wcx[0], hix = wcx[0];
+      for (int w = 1; w < nwin; w++) { lox = min(lox, wcx[w]); hix = max(hix, wcx[w]); }
+      close_x = hix - lox <= K;
+    }
     __syncwarp();
     for (int i = lane; i < n_dx; i += G) {
       const int qx = (bx0 + i) * 4;
@@ -329,9 +388,26 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
       const int qy = (by0 + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
       sm.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
+      // columns of this row that some window covers: [lo, hi] when they form one run (the usual case:
+      // window centres less than a window apart), else the per-window masks are used
+      int lo = 0x1FF, hi = -1;
       uint32_t wm = 0;
-      for (int w = 0; w < nwin; w++) wm |= (uint32_t)(abs(by0 + i - wcy[w]) <= R) << w;
-      sm.rowwin[i] = (uint8_t)wm;
+      bool one_run = true;
+      for (int w = 0; w < nwin; w++) {
+        if (abs(by0 + i - wcy[w]) > R) continue;
+        wm |= 1u << w;
+        lo = min(lo, wcx[w] - R - bx0); hi = max(hi, wcx[w] + R - bx0);
+        if (close_x) continue;                     // centres within one window width: any subset forms one run
+        // otherwise a window that is not the rightmost one needs a neighbour starting inside or right after it
+        bool rightmost = true, linked = false;
+        for (int v = 0; v < nwin; v++) {
+          if (abs(by0 + i - wcy[v]) > R || wcx[v] <= wcx[w]) continue;
+          rightmost = false;
+          linked |= wcx[v] - wcx[w] <= K;
+        }
+        one_run &= rightmost || linked;
+      }
+      sm.rowinfo[i] = hi < 0 ? 0xFFFFFFFFu : ((uint32_t)lo | ((uint32_t)hi << 9) | (one_run ? 0u : 1u << 18) | (wm << 19));
     }
     if (lane == 0) {
       int n = 0;
@@ -351,110 +427,123 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     }
     __syncwarp();
     const int n_hit = sm.n_hit;
+    bc.n_hit = n_hit;
     const int n = 8 >> level;
     const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
     const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
     const int vpr = n_dx >> 3;
-    uint32_t wbest = 0xFFFFFFFFu, wkey = 0xFFFFFFFFu;
 
-    // exact pricing of the candidates of one vector that can still win
-    auto exact8 = [&](int row, int c0, const uint32_t (&sad)[8], uint32_t mask) {
-#pragma unroll 1
-      for (int e = 0; e < 8; e++) {
-        if (!((mask >> e) & 1u)) continue;
-        const int col = c0 + e, dx = bx0 + col, dy = by0 + row;
-        if (!free_mv && !within_tile(f, j, dx * 4, dy * 4)) continue;
-        const uint2 gx = sm.bt.gx[col], gy = sm.bt.gy[row];
-        uint32_t mvd = min(gx.x + gy.x, gx.y + gy.y);
-        for (int q = 0; q < n_hit; q++)
-          if (sm.hit_pos[q] == ((row << 16) | col)) mvd = (uint32_t)sm.hit_bits[q] * (uint32_t)j.lambda;
-        const uint32_t cost = sad[e] + mvd;
-        if (cost > wbest) continue;
-        uint32_t key = 0xFFFFFFFFu;
-        for (int w = 0; w < nwin; w++)
-          if (abs(dx - wcx[w]) <= R && abs(dy - wcy[w]) <= R) {
-            key = ((uint32_t)w << 16) | (uint32_t)((dy - wcy[w] + R) * K + dx - wcx[w] + R);
-            break;
-          }
-        if (cost < wbest || key < wkey) { wbest = cost; wkey = key; }
-      }
-    };
-    // columns of the vector at c0 that some window of mask `rw` covers
-    auto cover_mask = [&](int c0, uint32_t rw) {
-      uint32_t mask = 0;
-      for (int w = 0; w < nwin; w++) {
-        if (!((rw >> w) & 1u)) continue;
-        const int lo = wcx[w] - R - bx0 - c0, hi = lo + 2 * R;         // covered columns relative to c0
-        if (hi < 0 || lo > 7) continue;
-        mask |= (0xFFu << max(lo, 0)) & (0xFFu >> (7 - min(hi, 7)));
-      }
-      return mask & 0xFFu;
-    };
-    // window 0 (the zero window) covers most of the box: inside it nothing else needs looking at
-    const int z_r0 = -R - by0, z_c0 = -R - bx0;
-
+    const int z_r0 = -R - by0, z_c0 = -R - bx0;     // the zero window (window 0) inside the box
+    int hitv[5];                                    // vectors that hold a merge-override entry: row << 13 | vector
+#pragma unroll
+    for (int q = 0; q < 5; q++) hitv[q] = q < n_hit ? sm.hit_pos[q] >> 3 : -1;
     auto price = [&](int row, int vec, const uint32_t (&sad)[8]) {
       const int c0 = vec * 8;
-      uint32_t mask = 0xFFu;
-      if (!((unsigned)(row - z_r0) <= (unsigned)(2 * R) && c0 >= z_c0 && c0 + 7 <= z_c0 + 2 * R))
-        mask = cover_mask(c0, sm.rowwin[row]);
-      if (mask == 0) return;
-      bool special = !free_mv;
-      for (int q = 0; q < n_hit; q++) special |= (sm.hit_pos[q] >> 3) == ((row << 13) | vec);
-      if (!special) {
-        const uint2 gy = sm.bt.gy[row];
-        const int d = (int)gy.y - (int)gy.x;
-        const uint4 *gxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
-        int m = 0x7FFFFFFF;
-#pragma unroll
-        for (int e2 = 0; e2 < 4; e2++) {
-          const uint4 g4 = gxp[e2];                                       // columns c0+2*e2, c0+2*e2+1
-          // min(a0 + b0, a1 + b1) - b0 = min(a0, a1 + d): signed, b0 is added back below
-          const int ka = (int)sad[2 * e2] + min((int)g4.x, (int)g4.y + d);
-          const int kb = (int)sad[2 * e2 + 1] + min((int)g4.z, (int)g4.w + d);
-          m = min(m, ((mask >> (2 * e2)) & 1u) ? ka : 0x7FFFFFFF);
-          m = min(m, ((mask >> (2 * e2 + 1)) & 1u) ? kb : 0x7FFFFFFF);
+      const uint32_t ri = sm.rowinfo[row];
+      if (ri == 0xFFFFFFFFu) return;
+      uint32_t mask;
+      if (ri & (1u << 18)) {
+        mask = 0;
+        for (int w = 0; w < nwin; w++) {
+          if (!((ri >> (19 + w)) & 1u)) continue;
+          const int lo = wcx[w] - R - bx0 - c0, hi = lo + 2 * R;
+          if (hi < 0 || lo > 7) continue;
+          mask |= (0xFFu << max(lo, 0)) & (0xFFu >> (7 - min(hi, 7)));
         }
-        if ((uint32_t)(m + (int)gy.x) > wbest) return;
+        mask &= 0xFFu;
+      } else {
+        const int lo = (int)(ri & 0x1FFu) - c0, hi = (int)((ri >> 9) & 0x1FFu) - c0;
+        mask = (hi < 0 || lo > 7) ? 0u : (0xFFu << max(lo, 0)) & (0xFFu >> (7 - min(hi, 7))) & 0xFFu;
       }
-      exact8(row, c0, sad, mask);
+      if (mask == 0) return;
+      const int rv = (row << 13) | vec;
+      const bool special = !free_mv || rv == hitv[0] || rv == hitv[1] || rv == hitv[2] || rv == hitv[3] || rv == hitv[4];
+      // candidate (cost, entry): strict improvement is cheap, an equal cost is settled by the visiting order
+      auto claim = [&](uint32_t cost, uint32_t pos) {
+        if (cost < wbest) { wbest = cost; wpos = pos; }
+        else if (cost == wbest && cost != 0xFFFFFFFFu) wpos = box_tie(bc, wpos, pos);
+      };
+      if (special) {
+#pragma unroll
+        for (int e = 0; e < 8; e++)
+          if ((mask >> e) & 1u) claim(box_price(bc, row, c0 + e, sad[e]), ((uint32_t)row << 16) | (uint32_t)(c0 + e));
+        return;
+      }
+      const uint2 gy = sm.bt.gy[row];
+      const int d = (int)gy.y - (int)gy.x;
+      const uint4 *gxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
+      int k[8];
+#pragma unroll
+      for (int e2 = 0; e2 < 4; e2++) {
+        const uint4 g4 = gxp[e2];                                       // columns c0+2*e2, c0+2*e2+1
+        // min(a0 + b0, a1 + b1) - b0 = min(a0, a1 + d): signed, b0 is added back below
+        k[2 * e2] = (int)sad[2 * e2] + min((int)g4.x, (int)g4.y + d);
+        k[2 * e2 + 1] = (int)sad[2 * e2 + 1] + min((int)g4.z, (int)g4.w + d);
+      }
+      if (mask != 0xFFu) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) k[e] = ((mask >> e) & 1u) ? k[e] : 0x0FFFFFFF;
+      }
+      const int m = min(min(min(k[0], k[1]), min(k[2], k[3])), min(min(k[4], k[5]), min(k[6], k[7])));
+      const uint32_t cost = (uint32_t)(m + (int)gy.x);
+      if (cost > wbest) return;
+      uint32_t eq = 0;                                // entries of the vector that reach the minimum
+#pragma unroll
+      for (int e = 0; e < 8; e++) eq |= (uint32_t)(k[e] == m) << e;
+      eq &= mask;
+      // inside the zero window (or with a single window) the row-major order of the box is the visiting order
+      const bool plain = nwin == 1 || ((unsigned)(row - z_r0) <= (unsigned)(2 * R) && c0 >= z_c0 && c0 + 7 <= z_c0 + 2 * R);
+      if (cost < wbest && (plain || (eq & (eq - 1)) == 0)) {
+        wbest = cost; wpos = ((uint32_t)row << 16) | (uint32_t)(c0 + __ffs((int)eq) - 1);
+        return;
+      }
+      for (; eq; eq &= eq - 1) claim(cost, ((uint32_t)row << 16) | (uint32_t)(c0 + __ffs((int)eq) - 1));
     };
 
-    if (level < 2) {
-      const uint16_t *mp = (level == 0 ? ms.sad8 : ms.sad16) + prow * (size_t)n_dy * n_dx;
-      const int total = n_dy * vpr;
-      for (int i0 = lane; i0 < total; i0 += KVZ_SCAN_DEPTH * G) {
-        uint4 v[KVZ_SCAN_DEPTH];
-#pragma unroll
-        for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
-          const int i = i0 + u * G;
-          v[u] = i < total ? __ldg(reinterpret_cast<const uint4 *>(mp) + i) : make_uint4(0, 0, 0, 0);
-        }
-#pragma unroll
-        for (int u = 0; u < KVZ_SCAN_DEPTH; u++) {
-          const int i = i0 + u * G;
-          if (i >= total) break;
-          const int row = i / vpr, vec = i - row * vpr;
-          const uint32_t sad[8] = { v[u].x & 0xFFFFu, v[u].x >> 16, v[u].y & 0xFFFFu, v[u].y >> 16,
-                                    v[u].z & 0xFFFFu, v[u].z >> 16, v[u].w & 0xFFFFu, v[u].w >> 16 };
-          price(row, vec, sad);
+    // Vectors of 8 entries in row-major order, 32 per step.  A lane streams its vectors through a ring in
+    // shared memory with cp.async: kScanRing 16-byte pieces (8 vectors of uint16 entries, 4 of uint32) are
+    // in flight per lane while one is priced -- the scan is bound by HBM latency, not by registers.
+    const int total = n_dy * vpr;
+    const int srow = G / vpr, svec = G - srow * vpr;                // one step of 32 vectors in (row, vec)
+    int row = lane / vpr, vec = lane - row * vpr;
+    const bool wide = level >= 2;                                   // uint32 entries: two pieces per vector
+    const uint4 *mp = wide ? reinterpret_cast<const uint4 *>((level == 2 ? ms.sad32 : ms.sad64) + prow * (size_t)n_dy * n_dx)
+                           : reinterpret_cast<const uint4 *>((level == 0 ? ms.sad8 : ms.sad16) + prow * (size_t)n_dy * n_dx);
+    const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
+    auto issue = [&](int i, int slot) {
+      if (i < total) {
+        if (wide) {
+          cp_async16(&sm.ring[2 * slot][lane], mp + 2 * i);
+          cp_async16(&sm.ring[2 * slot + 1][lane], mp + 2 * i + 1);
+        } else {
+          cp_async16(&sm.ring[slot][lane], mp + i);
         }
       }
-    } else {
-      const uint32_t *mp = (level == 2 ? ms.sad32 : ms.sad64) + prow * (size_t)n_dy * n_dx;
-      const int total = n_dy * vpr;
-      for (int i = lane; i < total; i += G) {
-        const uint4 va = __ldg(reinterpret_cast<const uint4 *>(mp) + 2 * i);
-        const uint4 vb = __ldg(reinterpret_cast<const uint4 *>(mp) + 2 * i + 1);
-        const int row = i / vpr, vec = i - row * vpr;
-        const uint32_t sad[8] = { va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w };
-        price(row, vec, sad);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int t = 0; t < depth; t++) issue(lane + t * G, t);
+    int slot = 0;
+    for (int i = lane; i < total; i += G) {
+      if (wide) asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing / 2 - 1) : "memory");
+      else asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing - 1) : "memory");
+      uint32_t sad[8];
+      if (wide) {
+        const uint4 a = sm.ring[2 * slot][lane], b = sm.ring[2 * slot + 1][lane];
+        sad[0] = a.x; sad[1] = a.y; sad[2] = a.z; sad[3] = a.w; sad[4] = b.x; sad[5] = b.y; sad[6] = b.z; sad[7] = b.w;
+      } else {
+        const uint4 a = sm.ring[slot][lane];
+        sad[0] = a.x & 0xFFFFu; sad[1] = a.x >> 16; sad[2] = a.y & 0xFFFFu; sad[3] = a.y >> 16;
+        sad[4] = a.z & 0xFFFFu; sad[5] = a.z >> 16; sad[6] = a.w & 0xFFFFu; sad[7] = a.w >> 16;
       }
+      issue(i + depth * G, slot);                                   // the slot just read is free again
+      slot = slot + 1 == depth ? 0 : slot + 1;
+      price(row, vec, sad);
+      row += srow; vec += svec;
+      if (vec >= vpr) { vec -= vpr; row++; }
     }
-    if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | wkey;
-    nwin = 0;                                     // nothing left for the per-window path
-  }
-
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | box_key(bc, wpos);
+  } else {
   for (int wi = 0; wi < nwin; wi++) {
     const int cx = wcx[wi], cy = wcy[wi];
     // separable AMVP bit tables and the merge overrides of this window
@@ -646,6 +735,7 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
       best = key < best ? key : best;
     }
   }
+  }
   best = warp_min(best);
 
   // ---- winner of the integer search, parked in the job's result record ----
@@ -668,6 +758,8 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
 }
 
 
+// BOX: the jobs whose windows all lie inside a box map set (single pass over the union); !BOX: the others
+template <bool BOX>
 __global__ void __launch_bounds__(kScanWarps * 32, KVZ_SCAN_MINB)
 me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
                const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *__restrict__ results, int n_pus)
@@ -679,7 +771,7 @@ me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restri
   if (threadIdx.x < 5) merge[threadIdx.x] = pu.merge_cand[threadIdx.x];
   __syncthreads();
   for (int q = warp; q < pu.num_jobs; q += kScanWarps)
-    scan_job(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q);
+    scan_job<BOX>(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q);
 }
 
 // ======================================================================================
@@ -976,7 +1068,15 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
                      kvz_cuda_me_result *results, int n_pus, cudaStream_t stream)
 {
   if (n_pus <= 0) return 1;
-  me_scan_kernel<<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
+  bool any_box = false;
+  for (int r = 0; r < f.n_refs; r++)
+    for (int m = 0; m < f.refs[r].n_sets; m++) any_box |= f.refs[r].sets[m].n_dx > 0;
+  if (any_box) {
+    me_scan_kernel<true><<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+  }
+  me_scan_kernel<false><<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   {

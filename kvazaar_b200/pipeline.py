@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import capi
-from .frame import ME_JOB_DT, ME_PU_DT, ME_RESULT_DT, ImeSearch, MeSearch, PaddedPlane
+from .frame import ME_JOB_DT, ME_PU_DT, ME_RESULT_DT, ImeBoxSearch, ImeSearch, MeSearch, PaddedPlane
 
 
 def frame_pus(width, height, n_refs, true_mv_px=(5, 3), sizes=(64, 32, 16, 8)):
@@ -76,7 +76,10 @@ class MePipeline:
     # 1080p from profiles/ (ncu --set full); None until a capture has been taken
     NCU_TRAFFIC_BYTES = 484260096   # r01a capture: 67.98 MB read + 416.28 MB written
 
-    def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda"):
+    def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda", use_boxes=True):
+        """use_boxes: one box of displacements per reference that covers the zero window and the frequent
+        extra_mv / merge windows (each displacement computed and priced once); False: one square-window
+        map set per window centre, as the reference visits them."""
         capi.init(torch.cuda.current_device())
         self.width, self.height, self.range, self.n_refs = width, height, rng, n_refs
         self.lambda_sqrt, self.fme_level = lambda_sqrt, fme_level
@@ -86,16 +89,43 @@ class MePipeline:
         self.ime = ImeSearch(width, height, rng, device=device, max_center=max_c)
         self.cur = torch.empty((height, width), dtype=torch.uint8, device=device)
         self.refs = [torch.empty((height, width), dtype=torch.uint8, device=device) for _ in range(n_refs)]
-        self.padded = [PaddedPlane(width, height, self.ime.pad, device=device) for _ in range(n_refs)]
-        self.maps = [[(c, [torch.empty_like(m) for m in self.ime.maps]) for c in self.centres[r]]
-                     for r in range(n_refs)]
-        self.n_sad_launches = sum(len(c) for c in self.centres)
+        self.use_boxes = use_boxes
+        k = 2 * rng + 1
+        n_pu = [(width // (8 << l)) * (height // (8 << l)) for l in range(4)]
+        self.union_area = []
+        if use_boxes:
+            self.boxes = []
+            for cs in self.centres:
+                x0, x1 = min(c[0] for c in cs) - rng, max(c[0] for c in cs) + rng
+                y0, y1 = min(c[1] for c in cs) - rng, max(c[1] for c in cs) + rng
+                self.boxes.append(ImeBoxSearch(width, height, (x0, y0, x1 - x0 + 1, y1 - y0 + 1), device=device))
+                cover = np.zeros((y1 - y0 + 1, x1 - x0 + 1), bool)
+                for c in cs:
+                    cover[c[1] - rng - y0:c[1] + rng + 1 - y0, c[0] - rng - x0:c[0] + rng + 1 - x0] = True
+                self.union_area.append(int(cover.sum()))
+            pad = max(self.ime.pad, max(b.pad for b in self.boxes))
+            self.padded = [PaddedPlane(width, height, pad, device=device) for _ in range(n_refs)]
+            self.maps = [[(b.box, b.maps)] for b in self.boxes]
+            self.n_sad_launches = n_refs
+            sad_stage = ("ime_sad_box_maps x%d (one box per reference over the zero window and the frequent extra_mv / "
+                         "merge windows: %s displacements)" % (n_refs, "+".join("%dx%d" % (b.box[2], b.box[3]) for b in self.boxes)))
+        else:
+            self.padded = [PaddedPlane(width, height, self.ime.pad, device=device) for _ in range(n_refs)]
+            self.maps = [[(c, [torch.empty_like(m) for m in self.ime.maps]) for c in self.centres[r]]
+                         for r in range(n_refs)]
+            self.union_area = [k * k * len(cs) for cs in self.centres]
+            self.n_sad_launches = sum(len(c) for c in self.centres)
+            sad_stage = "ime_sad_maps x%d (zero window + the frequent extra_mv / merge windows per reference)" % self.n_sad_launches
+        # 64 absolute differences per 8x8 block and displacement that has to be evaluated
+        self.algorithmic_abs_diffs = sum(n_pu[0] * 64 * a for a in self.union_area)
+        # the maps of those displacements written once (read back once by me_search) + the planes read once
+        self.algorithmic_map_bytes = sum(a * (2 * n_pu[0] + 2 * n_pu[1] + 4 * n_pu[2] + 4 * n_pu[3]) for a in self.union_area)
+        self.map_bytes = sum(m.numel() * m.element_size() for sets in self.maps for _, ms in sets for m in ms)
         self.search = MeSearch(width, height, rng, fme_level=fme_level, lambda_sqrt=lambda_sqrt)
         self.search.set_current(self.cur)
         self.search.set_refs(self.padded, self.maps)
-        self.stages = ["pad_plane x%d" % n_refs,
-                       "ime_sad_maps x%d (zero window + the frequent extra_mv / merge windows per reference)" % self.n_sad_launches,
-                       "me_search (IME decision + FME) x1"]
+        self.stages = ["pad_plane x%d" % n_refs, sad_stage,
+                       "me_search x1 = me_scan (integer decision) + me_refine x2 (fractional search, PUs <= 16 and > 16)"]
         # PUs / jobs of the frame (host, pinned) and their device copies
         self.n_pus, self.n_jobs = len(pus), len(jobs)
         self.host_pus = torch.from_numpy(pus.view(np.uint8).reshape(-1)).pin_memory()
@@ -117,9 +147,17 @@ class MePipeline:
     def step_resident(self):
         for r in range(self.n_refs):
             self.padded[r].fill_from(self.refs[r])
-            for c, m in self.maps[r]:
-                self.ime.run(self.cur, self.padded[r], center=c, maps=m)
+        self.sad_maps()
         self.search.run(self.d_pus, self.n_pus, self.d_jobs, self.d_results)
+
+    def sad_maps(self):
+        """every dense SAD launch of one frame (planes already padded)"""
+        for r in range(self.n_refs):
+            if self.use_boxes:
+                self.boxes[r].run(self.cur, self.padded[r])
+            else:
+                for c, m in self.maps[r]:
+                    self.ime.run(self.cur, self.padded[r], center=c, maps=m)
 
     def step_from_host(self, host_cur, host_refs):
         self.upload(host_cur, host_refs)
@@ -147,20 +185,12 @@ class MePipeline:
     def time_me_search(self, iters=5):
         return self.time_stage(lambda: self.search.run(self.d_pus, self.n_pus, self.d_jobs, self.d_results), iters)
 
-    # ---- dominant kernel alone ----
+    # ---- the dense SAD launches of one frame alone ----
     def time_sad_kernel(self, iters=10):
-        self.padded[0].fill_from(self.refs[0])
-        self.ime.maps = self.maps[0][0][1]
-        for _ in range(2):
-            self.ime.run(self.cur, self.padded[0])
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        e0.record()
-        for _ in range(iters):
-            self.ime.run(self.cur, self.padded[0])
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / iters
+        """ms for all SAD launches of one frame (n_sad_launches of them), planes resident and padded"""
+        for r in range(self.n_refs):
+            self.padded[r].fill_from(self.refs[r])
+        return self.time_stage(self.sad_maps, iters)
 
     def kernel_time_ms(self, name):
         return 0.0
