@@ -779,10 +779,12 @@ me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restri
 // ======================================================================================
 template <int G, int S>
 struct RefineSmem {
-  static constexpr int kWinPitch = S + 16;
-  alignas(16) uint8_t cur[S * 64];                             // PU rows, pitch 64
+  // pitches chosen so that the 8 lanes of a tile (8 consecutive rows) hit distinct banks
+  static constexpr int kWinPitch = S + 20;                     // bytes
+  static constexpr int kCurPitch = 72;                         // bytes
+  alignas(16) uint8_t cur[S * kCurPitch];                      // PU rows
   alignas(16) uint8_t win[(S + 9) * kWinPitch + 16];           // source window round the integer vector
-  alignas(16) uint32_t pp[3][(S + 7) * S];                     // horizontally filtered planes, vertical int16 pairs
+  alignas(16) uint32_t pp[3][(S + 7) * (S + 4)];               // horizontally filtered planes, vertical int16 pairs, pitch w + 4
   kvz_cuda_merge_cand merge[5];
   uint32_t cost4[4];
 };
@@ -808,7 +810,7 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
     // The window origin is clamped into the replicated border: with pad >= w + 20 this reads the same
     // samples as the per-pixel clamp of kvz_get_extended_block (ipol-generic.c:761-781).
     const int imx = best_mvx >> 2, imy = best_mvy >> 2;
-    constexpr int WP = RefineSmem<G, S>::kWinPitch;
+    constexpr int WP = RefineSmem<G, S>::kWinPitch, CP = RefineSmem<G, S>::kCurPitch;
     {
       const int ox = clampi(fx0 + imx - 4, -ref.pad, f.width + ref.pad - (j.w + 20));
       const int oy = clampi(fy0 + imy - 4, -ref.pad, f.height + ref.pad - (j.h + 9));
@@ -829,6 +831,13 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
 
     const int tiles_x = j.w >> 3, tiles = tiles_x * (j.h >> 3);
     const int lane8 = g.tid & 7;
+    // tile index -> (candidate, tile row, tile column); shifts when the PU is a power of two on both axes
+    const bool pow2 = (tiles_x & (tiles_x - 1)) == 0 && (tiles & (tiles - 1)) == 0;
+    const int lg_tx = 31 - __clz(tiles_x), lg_t = 31 - __clz(tiles);
+    auto split = [&](int v, int &k, int &ty, int &tx) {      // v = k * tiles + ty * tiles_x + tx
+      if (pow2) { k = v >> lg_t; const int t = v & (tiles - 1); ty = t >> lg_tx; tx = t & (tiles_x - 1); }
+      else { k = v / tiles; const int t = v - k * tiles; ty = t / tiles_x; tx = t - ty * tiles_x; }
+    };
 
     // SATD at the integer position: kvz_satd_any_size (strategies-picture.h:62-100), 8x8 tiles
     if (g.tid < 4) sm.cost4[g.tid] = 0;
@@ -836,10 +845,10 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
     for (int u0 = 0; u0 < tiles * 8; u0 += G) {
       const int u = u0 + g.tid;
       const bool on = u < tiles * 8;
-      const int t = on ? (u >> 3) : 0;
-      const int ty = t / tiles_x, tx = t % tiles_x;
+      int k0, ty, tx;
+      split(on ? (u >> 3) : 0, k0, ty, tx);
       int d[8];
-      const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * 64 + tx * 8);
+      const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * CP + tx * 8);
       const uint8_t *pr = sm.win + (ty * 8 + lane8 + 4) * WP + tx * 8 + 4;
       const uint32_t p0 = *reinterpret_cast<const uint32_t *>(pr), p1 = *reinterpret_cast<const uint32_t *>(pr + 4);
 #pragma unroll
@@ -863,7 +872,7 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
       // holds H[r][x] = sum_t fir[fx][t] * win[r][x + sx + 1 + t] for rows r = 0..h+7 (source rows
       // -4..h+3) as int16, stored as vertical pairs PP[r][x] = (H[r][x], H[r+1][x]) so that the
       // vertical 8-tap filter is four 2-way dot products.  Three planes are alive at a time.
-      const int PW = j.w;                                   // words per plane row
+      const int PW = j.w + 4;                               // words per plane row (w + 4: conflict-free 16-byte rows)
       auto make_plane = [&](int slot, int fx, int sx) {
         const uint32_t t_lo = c_fir4[fx][0], t_hi = c_fir4[fx][1];
         const int o = sx + 1;                                // byte offset inside the aligned 12-byte run
@@ -931,9 +940,8 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
         for (int u0 = 0; u0 < units; u0 += G) {
           const int u = u0 + g.tid;
           const bool on = u < units;
-          const int k = on ? u / (tiles * 8) : 0;
-          const int t = on ? (u % (tiles * 8)) >> 3 : 0;
-          const int ty = t / tiles_x, tx = t % tiles_x;
+          int k, ty, tx;
+          split(on ? (u >> 3) : 0, k, ty, tx);
           const int cqx = qx[k], cqy = qy[k];
           const int slot = (cqx & 1) ? (cqx == 2 * hx - 1 ? slot_a : slot_b) : (cqx < 0 ? slot_l : cqx == 0 ? slot_0 : slot_r);
           const int fy = cqy & 3, sy = cqy >> 2;
@@ -953,7 +961,7 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
               acc[x] = (i2 & 1) ? dp2a_hi_ss(wv[x], tp, acc[x]) : dp2a_lo_ss(wv[x], tp, acc[x]);
           }
           int d[8];
-          const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * 64 + tx * 8);
+          const uint2 cw = *reinterpret_cast<const uint2 *>(sm.cur + (ty * 8 + lane8) * CP + tx * 8);
 #pragma unroll
           for (int x = 0; x < 8; x++) {
             const int v16 = (int)(int16_t)(acc[x] >> 6);       // int16 store of ipol-generic.c:285 et al.
@@ -1053,7 +1061,7 @@ me_refine_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__rest
   for (int i = g.tid; i < pu.h * (pu.w >> 2); i += G) {
     const int r = i / (pu.w >> 2), c = i % (pu.w >> 2);
     const uint8_t *src = f.cur + (size_t)(f.tile_y + pu.y + r) * f.cur_pitch + f.tile_x + pu.x + c * 4;
-    *reinterpret_cast<uint32_t *>(&sm.cur[r * 64 + c * 4]) = *reinterpret_cast<const uint32_t *>(src);
+    *reinterpret_cast<uint32_t *>(&sm.cur[r * RefineSmem<G, S>::kCurPitch + c * 4]) = *reinterpret_cast<const uint32_t *>(src);
   }
   if (g.tid < 5) sm.merge[g.tid] = pu.merge_cand[g.tid];
   g.sync();
