@@ -120,8 +120,9 @@ KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,
  * covers all the windows search_mv_full visits for a reference (zero window, extra_mv window, merge-candidate
  * windows; search_inter.c:891-955) computes every displacement once, where separate windows overlap.
  *   map[level][p][dy - y0][dx - x0],  rows n_dx entries apart (plain row-major, no extra row).
- * n_dx must be a multiple of 16 and n_dy == 1 (mod 8): round the box up, surplus entries are ignored
- * by kvz_cuda_me_search.  ref_pad must be >= 96 + max(|x0|, |x0+n_dx|, |y0|, |y0+n_dy|). */
+ * n_dx must be a multiple of 8 (round the box up: entries no window covers are ignored by
+ * kvz_cuda_me_search), n_dy is free; both at most 272.
+ * ref_pad must be >= 104 + max(|x0|, |x0+n_dx|, |y0|, |y0+n_dy|). */
 typedef struct kvz_cuda_ime_box_desc {
   int32_t width, height, bitdepth;
   int32_t tile_x, tile_y, tile_w, tile_h;

@@ -185,14 +185,14 @@ int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur,
   if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
     return fail_msg("kvz_cuda_ime_sad_box_maps: null argument");
   if (d->bitdepth != 8) return fail_msg("kvz_cuda_ime_sad_box_maps: only bitdepth 8 is implemented");
-  if (d->n_dx <= 0 || (d->n_dx & 15) || d->n_dy <= 0 || (d->n_dy & 7) != 1)
-    return fail_msg("kvz_cuda_ime_sad_box_maps: n_dx must be a multiple of 16 and n_dy == 1 (mod 8)");
+  if (d->n_dx <= 0 || (d->n_dx & 7) || d->n_dy <= 0 || d->n_dx > kMeMaxBox || d->n_dy > kMeMaxBox)
+    return fail_msg("kvz_cuda_ime_sad_box_maps: n_dx must be a multiple of 8; both sides 1..272");
   {
     int far = abs(d->x0);
     if (abs(d->x0 + d->n_dx) > far) far = abs(d->x0 + d->n_dx);
     if (abs(d->y0) > far) far = abs(d->y0);
     if (abs(d->y0 + d->n_dy) > far) far = abs(d->y0 + d->n_dy);
-    if (d->ref_pad < 96 + far) return fail_msg("kvz_cuda_ime_sad_box_maps: ref_pad too small for this box");
+    if (d->ref_pad < 104 + far) return fail_msg("kvz_cuda_ime_sad_box_maps: ref_pad too small for this box");
   }
   if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 3) || (d->ref_pad & 3) ||
       (d->tile_x & 63) || (d->tile_y & 63) || (d->tile_w & 7) || (d->tile_h & 7))
@@ -240,7 +240,7 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
     for (int m = 0; m < r.n_mapsets; m++) {
       f.refs[i].sets[m].cx = r.mapsets[m].center_x; f.refs[i].sets[m].cy = r.mapsets[m].center_y;
       f.refs[i].sets[m].n_dx = r.mapsets[m].n_dx; f.refs[i].sets[m].n_dy = r.mapsets[m].n_dy;
-      if (r.mapsets[m].n_dx < 0 || (r.mapsets[m].n_dx & 15) || r.mapsets[m].n_dx > kMeMaxBox || r.mapsets[m].n_dy < 0 ||
+      if (r.mapsets[m].n_dx < 0 || (r.mapsets[m].n_dx & 7) || r.mapsets[m].n_dx > kMeMaxBox || r.mapsets[m].n_dy < 0 ||
           r.mapsets[m].n_dy > kMeMaxBox || (r.mapsets[m].n_dx > 0) != (r.mapsets[m].n_dy > 0))
         return fail_msg("kvz_cuda_me_search: bad box map set");
       f.refs[i].sets[m].sad8 = r.mapsets[m].d_sad8; f.refs[i].sets[m].sad16 = r.mapsets[m].d_sad16;

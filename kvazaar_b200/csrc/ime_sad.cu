@@ -29,6 +29,7 @@
 //    arithmetic in the compute loop).  Every 8 rows all threads turn writer: 16-byte
 //    vectors of the 8x8 map, and the 16/32/64 sums formed with packed u16 adds and
 //    shuffles, each map written exactly once in full 32-byte sectors.
+#include <type_traits>
 #include "common.cuh"
 #include "ime_sad.cuh"
 
@@ -85,35 +86,37 @@ struct SmemView {
 };
 
 // ---- compute: 8 tile rows of a normal chunk ----
-// PH 0: first iteration (rows 0..7: only products with u >= y exist, only dy 0 completes),
-// PH 1: middle, PH 2: last iteration (rows 2R..2R+7: only products with u <= y exist).
-template <int PH>
+// PH 0: first iteration (rows 0..7: only products with u - y >= S exist -- S leading rows of the computed
+// range are alignment only -- and only dy 0 completes, if S == 0), PH 1: middle, PH 2: last iteration
+// (only products with u <= y exist).  NJ: displacement columns per thread (4, or 2 in a half chunk).
+template <int PH, int S, int NJ>
 __device__ __forceinline__ void rows8(const uint32_t *trow, const uint32_t (&cur)[8][2], uint32_t (&acc)[8][4],
                                       uint16_t *stg /* &stage[0][blk][g] */)
 {
 #pragma unroll
   for (int u = 0; u < 8; u++) {
+    if (PH == 0 && u < S) continue;
     const uint32_t *rp = trow + u * kRowWords;
     const uint2 a = *reinterpret_cast<const uint2 *>(rp);
-    const uint2 b = *reinterpret_cast<const uint2 *>(rp + 2);
-    const uint32_t w[5] = { a.x, a.y, b.x, b.y, rp[4] };
+    const uint2 b = NJ > 2 ? *reinterpret_cast<const uint2 *>(rp + 2) : make_uint2(rp[2], 0u);
+    const uint32_t w[5] = { a.x, a.y, b.x, b.y, NJ > 2 ? rp[4] : 0u };
 #pragma unroll
     for (int y = 0; y < 8; y++) {
-      if (PH == 0 && u < y) continue;
+      if (PH == 0 && u - y < S) continue;
       if (PH == 2 && u > y) continue;
       const int slot = (u - y) & 7;                 // accumulator of dy = 8m + u - y
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
+      for (int j = 0; j < NJ; j++) {
         const uint32_t c0 = (y == 0) ? 0u : acc[slot][j];      // a new dy starts from the zero register
         acc[slot][j] = sad4(cur[y][1], w[j + 1], sad4(cur[y][0], w[j], c0));
       }
     }
-    // dy = 8m + u - 7 is complete (always in PH 1/2; in PH 0 only for u == 7)
-    if (PH != 0 || u == 7) {
+    // dy = 8m + u - 7 is complete (always in PH 1/2; in PH 0 only for u == 7 and S == 0)
+    if (PH != 0 || (u == 7 && S == 0)) {
       const int slot = (u + 1) & 7;
       uint16_t *o = stg + u * (64 * kChunkDx);
 #pragma unroll
-      for (int j = 0; j < 4; j++) o[4 * j] = (uint16_t)acc[slot][j];
+      for (int j = 0; j < NJ; j++) o[4 * j] = (uint16_t)acc[slot][j];
     }
   }
 }
@@ -144,18 +147,19 @@ __device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, 
   return w;
 }
 
-__device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPos &wp, const uint16_t *stage, int m, int tid)
+// nd: displacement columns of this chunk (16 or 8)
+__device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPos &wp, const uint16_t *stage, int m, int tid, int nd)
 {
   const uint32_t PR = (uint32_t)p.pu_rows;
   const uint32_t rs = (uint32_t)p.map_pitch;
-  const int k0 = 8 * m - 7;                       // dy of ring slot 0
+  const int k0 = 8 * m - 7 - p.skip;              // map row of ring slot 0
   // (a) 8x8 map: thread = (block, half of the 16 dx), ring slots u0, u0+2, u0+4, u0+6
   {
     const int u0 = tid >> 7;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
       const int u = u0 + 2 * i, k = k0 + u;
-      if (k >= 0)
+      if (k >= 0 && (tid & 1) * 8 < nd)
         *reinterpret_cast<uint4 *>(p.sad8 + wp.o8 + (uint32_t)k * rs) =
             *reinterpret_cast<const uint4 *>(stage + u * (64 * kChunkDx) + wp.src8);
     }
@@ -167,6 +171,7 @@ __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPo
     if (k >= 0) {                                   // uniform per warp
       const uint32_t *st = reinterpret_cast<const uint32_t *>(stage) + u * (64 * kChunkDx / 2) + wp.src16;
       const int sw = p32;                           // stage_slot() of the PU's blocks: low two bits ^ p32
+      const bool wr = 2 * (tid & 7) < nd;           // this pair of displacement columns exists
       uint32_t lo = 0, hi = 0;
 #pragma unroll
       for (int q = 0; q < 4; q++) {
@@ -174,14 +179,14 @@ __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPo
         const int b = (q >> 1) * 16 + (q & 1) * 2;
         // packed u16 pairs: 4 x 16320 < 65536, no carry between the halves
         const uint32_t s16 = st[((b) ^ sw) * 8] + st[((b + 1) ^ sw) * 8] + st[((b + 8) ^ sw) * 8] + st[((b + 9) ^ sw) * 8];
-        *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * PR + (uint32_t)k) * rs) = s16;
+        if (wr) *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * PR + (uint32_t)k) * rs) = s16;
         lo += s16 & 0xFFFFu;
         hi += s16 >> 16;
       }
-      *reinterpret_cast<uint2 *>(p.sad32 + wp.o32 + (uint32_t)k * rs) = make_uint2(lo, hi);
+      if (wr) *reinterpret_cast<uint2 *>(p.sad32 + wp.o32 + (uint32_t)k * rs) = make_uint2(lo, hi);
       lo += __shfl_xor_sync(0xffffffffu, lo, 8);  hi += __shfl_xor_sync(0xffffffffu, hi, 8);
       lo += __shfl_xor_sync(0xffffffffu, lo, 16); hi += __shfl_xor_sync(0xffffffffu, hi, 16);
-      if (p32 == 0) *reinterpret_cast<uint2 *>(p.sad64 + wp.o64 + (uint32_t)k * rs) = make_uint2(lo, hi);
+      if (p32 == 0 && wr) *reinterpret_cast<uint2 *>(p.sad64 + wp.o64 + (uint32_t)k * rs) = make_uint2(lo, hi);
     }
   }
 }
@@ -341,19 +346,34 @@ ime_sad_dense_kernel(ImeSadParams p)
     const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
     uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
     const WriterPos wp = writer_pos(p, ctu, chunk, tid);
-    rows8<0>(trow, cur, acc, stg);
-    __syncthreads();
-    write_rows(p, wp, stage, 0, tid);
-    __syncthreads();
-    for (int m = 1; m < geo.iters - 1; m++) {
-      rows8<1>(trow + m * 8 * kRowWords, cur, acc, stg);
+    const int nd = chunk == kChunks - 1 ? p.n_dx_last : kChunkDx;
+    auto run = [&](auto nj_tag) {
+      constexpr int NJ = decltype(nj_tag)::value;
+      switch (p.skip) {
+        case 0: rows8<0, 0, NJ>(trow, cur, acc, stg); break;
+        case 1: rows8<0, 1, NJ>(trow, cur, acc, stg); break;
+        case 2: rows8<0, 2, NJ>(trow, cur, acc, stg); break;
+        case 3: rows8<0, 3, NJ>(trow, cur, acc, stg); break;
+        case 4: rows8<0, 4, NJ>(trow, cur, acc, stg); break;
+        case 5: rows8<0, 5, NJ>(trow, cur, acc, stg); break;
+        case 6: rows8<0, 6, NJ>(trow, cur, acc, stg); break;
+        default: rows8<0, 7, NJ>(trow, cur, acc, stg); break;
+      }
       __syncthreads();
-      write_rows(p, wp, stage, m, tid);
+      if (p.skip == 0) write_rows(p, wp, stage, 0, tid, nd);
       __syncthreads();
-    }
-    rows8<2>(trow + (geo.iters - 1) * 8 * kRowWords, cur, acc, stg);
-    __syncthreads();
-    write_rows(p, wp, stage, geo.iters - 1, tid);
+      for (int m = 1; m < geo.iters - 1; m++) {
+        rows8<1, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg);
+        __syncthreads();
+        write_rows(p, wp, stage, m, tid, nd);
+        __syncthreads();
+      }
+      rows8<2, 0, NJ>(trow + (geo.iters - 1) * 8 * kRowWords, cur, acc, stg);
+      __syncthreads();
+      write_rows(p, wp, stage, geo.iters - 1, tid, nd);
+    };
+    if (nd == kChunkDx) run(std::integral_constant<int, 4>());
+    else run(std::integral_constant<int, 2>());
   }
 }
 
@@ -407,6 +427,7 @@ int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, 
 {
   p.x0 = center_x - range; p.y0 = center_y - range;
   p.n_dy = 2 * range + 1; p.n_chunks = range / 8; p.pu_rows = p.n_dy + 1;
+  p.skip = 0; p.n_dx_last = kChunkDx;
   switch (range) {
     case 8:  return launch_r<8>(p, stream);
     case 16: return launch_r<16>(p, stream);
@@ -418,8 +439,11 @@ int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, 
 
 int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream)
 {
-  if (n_dx <= 0 || (n_dx & 15) || n_dy <= 0 || (n_dy & 7) != 1) return fail_msg("ime_sad_box: n_dx must be a multiple of 16, n_dy == 1 (mod 8)");
-  p.x0 = x0; p.y0 = y0; p.n_dy = n_dy; p.n_chunks = n_dx / 16; p.pu_rows = n_dy;
+  if (n_dx <= 0 || (n_dx & 7) || n_dy <= 0) return fail_msg("ime_sad_box: n_dx must be a positive multiple of 8, n_dy positive");
+  // the kernel computes 8k + 1 rows; the surplus goes in front (alignment rows that are never written)
+  p.skip = (8 - ((n_dy - 1) & 7)) & 7;
+  p.x0 = x0; p.y0 = y0 - p.skip; p.n_dy = n_dy + p.skip; p.pu_rows = n_dy;
+  p.n_chunks = (n_dx + 15) / 16; p.n_dx_last = n_dx - 16 * (p.n_chunks - 1);
   return launch_r<0>(p, stream);
 }
 

@@ -15,7 +15,9 @@ struct ImeSadParams {
   int ctus_x, ctus_y;      // CTUs in the tile
   int x0, y0;              // first displacement: map[i][j] is the SAD at displacement (x0 + j, y0 + i)
   int n_dy;                // displacement rows computed, == 1 (mod 8)
+  int skip;                // the first `skip` (0..7) computed rows are alignment only: map row i = computed row i + skip
   int n_chunks;            // chunks of 16 displacement columns computed by the chunk CTAs
+  int n_dx_last;           // columns of the last chunk: 16 or 8
   int pu_rows;             // map rows per PU: n_dy, or n_dy + 1 when row n_dy holds the column dx = x0 + 16*n_chunks
   int map_pitch;           // entries per map row
   uint16_t *sad8;          // [ctu*64 + by*8+bx][pu_rows][map_pitch]
@@ -30,7 +32,7 @@ int launch_pad_plane(const void *src, int w, int h, int src_pitch, void *dst, in
 // square window [-range, range]^2 round (center_x, center_y): K = 2*range+1 rows of K-1 columns, the last
 // column as row K; fills x0, y0, n_dy, n_chunks, pu_rows of `p`
 int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, cudaStream_t stream);
-// rectangular box: n_dx (multiple of 16) x n_dy (== 1 mod 8) displacements from (x0, y0), plain row-major maps
+// rectangular box: n_dx (multiple of 8) x n_dy displacements from (x0, y0), plain row-major maps
 int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream);
 
 }  // namespace kvz

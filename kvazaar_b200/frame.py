@@ -119,18 +119,17 @@ class ImeSearch:
 
 class ImeBoxSearch:
     """Dense SAD maps over a rectangular box of displacements (kvz_cuda_ime_sad_box_maps):
-    map[level][pu][dy - y0][dx - x0], n_dx a multiple of 16, n_dy == 1 (mod 8)."""
+    map[level][pu][dy - y0][dx - x0], n_dx rounded up to a multiple of 8."""
 
     def __init__(self, width, height, box, tile=None, device="cuda"):
         capi.init(torch.cuda.current_device())
         self.width, self.height = width, height
         self.tile = tile or (0, 0, width, height)
         x0, y0, n_dx, n_dy = box
-        n_dx = (n_dx + 15) & ~15
-        n_dy = ((n_dy - 1 + 7) & ~7) + 1
+        n_dx = (n_dx + 7) & ~7
         self.box = (x0, y0, n_dx, n_dy)
         far = max(abs(x0), abs(x0 + n_dx), abs(y0), abs(y0 + n_dy))
-        self.pad = (96 + far + 31) & ~31
+        self.pad = (104 + far + 31) & ~31
         tw, th = self.tile[2], self.tile[3]
         self.ctus_x, self.ctus_y = (tw + 63) // 64, (th + 63) // 64
         n_ctu = self.ctus_x * self.ctus_y

@@ -112,7 +112,8 @@ def test_hierarchy_property_1080p():
         prev = cur
 
 
-@pytest.mark.parametrize("box", [(-8, -8, 32, 17), (-20, 3, 48, 25), (5, -30, 16, 41)])
+@pytest.mark.parametrize("box", [(-8, -8, 32, 17), (-20, 3, 48, 25), (5, -30, 16, 41), (-9, -7, 24, 12), (-3, -3, 8, 7),
+                                 (-12, -10, 40, 30), (0, 0, 56, 1), (-16, -5, 72, 19)])
 def test_box_maps_small_frame(box):
     """kvz_cuda_ime_sad_box_maps: every entry of a rectangular displacement box vs the oracle's clamped SAD."""
     import torch
