@@ -210,8 +210,8 @@ __device__ __forceinline__ unsigned long long warp_min(unsigned long long v)
 
 // per-window separable tables of the AMVP bit cost: bits = min_c(gx[c][col] + gy[c][row])
 struct BitTables {
-  alignas(16) uint2 gx[kMeMaxBox];    // lambda * bits of column i for AMVP candidate 0 (.x) and 1 (.y)
-  alignas(16) uint2 gy[kMeMaxBox];    // same for row i
+  alignas(16) uint2 gx[132];     // lambda * bits of column i for AMVP candidate 0 (.x) and 1 (.y)
+  alignas(16) uint2 gy[132];     // same for row i
 };
 
 // ======================================================================================
@@ -232,20 +232,42 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
 }
 
-struct ScanSmem {
+// per-warp scratch of the integer search
+template <bool BOX> struct ScanSmemT;
+template <> struct ScanSmemT<false> {         // per-window scan: static
   BitTables bt;
-  int hit_pos[5];             // window position (row * K + col); box scan: row << 16 | col of the box
+  int hit_pos[5];             // window position (row * K + col) of a merge-override entry
   int hit_bits[5];
   int n_hit;
-  alignas(16) uint4 ring[kScanRing][32];   // box scan: per-lane stream of map vectors (cp.async)
-  uint32_t rowinfo[kMeMaxBox];   // box scan, per box row: covered column run lo | hi << 9, bit 18 = several runs, bits 19.. = windows
+};
+template <> struct ScanSmemT<true> {          // box scan: carved out of dynamic shared memory, sized by the largest box
+  uint4 *ring;                // [kScanRing][32] per-lane stream of map vectors (cp.async)
+  // column table, piece-major: pieces 0,1 = candidate-0 bits of entries 0..3 / 4..7 of a vector, 2,3 = candidate 1,
+  // so that lanes on consecutive vectors read consecutive 16-byte pieces (no bank conflicts)
+  uint4 *gxv;                 // [4][nv]
+  int nv;
+  uint2 *gy;                  // lambda * bits of box row i for AMVP candidate 0 (.x) and 1 (.y)
+  uint32_t *rowinfo;          // per box row: covered column run lo | hi << 9, bit 18 = several runs, bits 19.. = windows
+  int *hit_pos;               // row << 16 | col of the box
+  int *hit_bits;
+  int &n_hit;
+  __device__ __forceinline__ uint2 gx(int col) const
+  {
+    const uint32_t *pv = reinterpret_cast<const uint32_t *>(&gxv[((col >> 2) & 1) * nv + (col >> 3)]) + (col & 3);
+    return make_uint2(pv[0], pv[2 * nv * 4]);
+  }
+  __device__ __forceinline__ void set_gx(int col, uint32_t a0, uint32_t a1) const
+  {
+    uint32_t *pv = reinterpret_cast<uint32_t *>(&gxv[((col >> 2) & 1) * nv + (col >> 3)]) + (col & 3);
+    pv[0] = a0; pv[2 * nv * 4] = a1;
+  }
 };
 
 // one search window of search_mv_full
 struct WinCtx {
   const MeFrame *f;
   const JobCtx *j;
-  const ScanSmem *sm;
+  const ScanSmemT<false> *sm;
   int cx, cy;               // centre (whole samples)
   int R, K;
   int n_hit;
@@ -269,7 +291,7 @@ __device__ __noinline__ uint32_t exact_cost(const WinCtx &w, int row, int col, u
 struct BoxCtx {
   const MeFrame *f;
   const JobCtx *j;
-  const ScanSmem *sm;
+  const ScanSmemT<true> *sm;
   const int *wcx, *wcy;
   int nwin, n_hit;
   int bx0, by0, R, K;
@@ -281,7 +303,7 @@ __device__ __noinline__ uint32_t box_price(const BoxCtx &b, int row, int col, ui
 {
   const int dx = b.bx0 + col, dy = b.by0 + row;
   if (!b.free_mv && !within_tile(*b.f, *b.j, dx * 4, dy * 4)) return 0xFFFFFFFFu;
-  const uint2 gx = b.sm->bt.gx[col], gy = b.sm->bt.gy[row];
+  const uint2 gx = b.sm->gx(col), gy = b.sm->gy[row];
   uint32_t mvd = min(gx.x + gy.x, gx.y + gy.y);
   for (int q = 0; q < b.n_hit; q++)
     if (b.sm->hit_pos[q] == ((row << 16) | col)) mvd = (uint32_t)b.sm->hit_bits[q] * (uint32_t)b.j->lambda;
@@ -305,10 +327,12 @@ __device__ __noinline__ uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint32
 }
 
 template <bool BOX>
-__device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
-                         const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
+__device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                         const kvz_cuda_me_job &job, kvz_cuda_me_result *out, bool after_box)
 {
   constexpr int G = 32;
+  // the box instantiation ran first and marked the jobs it left for this one (took = 0xFF)
+  if (!BOX && after_box && __shfl_sync(0xffffffffu, lane == 0 ? (int)out->took : 0, 0) != 0xFF) return;
   JobCtx j;
   make_ctx(j, f, pu, merge, job);
   const MeRef &ref = f.refs[job.ref_idx];
@@ -361,7 +385,10 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
           hiy + R < ms.cy + ms.n_dy) { bi = m; break; }
     }
   }
-  if ((bi >= 0) != BOX) return;                 // the other instantiation of the kernel owns this job
+  if ((bi >= 0) != BOX) {                       // the other instantiation of the kernel owns this job
+    if (BOX && lane == 0) out->took = 0xFF;
+    return;
+  }
   if constexpr (BOX) {
     // Every displacement of the union of the windows is priced once.  A displacement belongs to the
     // FIRST window of the list that covers it (a later window meets it again with the same cost and
@@ -382,12 +409,12 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     for (int i = lane; i < n_dx; i += G) {
       const int qx = (bx0 + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
-      sm.bt.gx[i] = make_uint2(lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
+      sm.set_gx(i, lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
     }
     for (int i = lane; i < n_dy; i += G) {
       const int qy = (by0 + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
-      sm.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
+      sm.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
       // columns of this row that some window covers: [lo, hi] when they form one run (the usual case:
       // window centres less than a window apart), else the per-window masks are used
       int lo = 0x1FF, hi = -1;
@@ -469,17 +496,15 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
           if ((mask >> e) & 1u) claim(box_price(bc, row, c0 + e, sad[e]), ((uint32_t)row << 16) | (uint32_t)(c0 + e));
         return;
       }
-      const uint2 gy = sm.bt.gy[row];
+      const uint2 gy = sm.gy[row];
       const int d = (int)gy.y - (int)gy.x;
-      const uint4 *gxp = reinterpret_cast<const uint4 *>(&sm.bt.gx[c0]);
+      const uint4 a0l = sm.gxv[vec], a0h = sm.gxv[sm.nv + vec], a1l = sm.gxv[2 * sm.nv + vec], a1h = sm.gxv[3 * sm.nv + vec];
+      const int a0[8] = { (int)a0l.x, (int)a0l.y, (int)a0l.z, (int)a0l.w, (int)a0h.x, (int)a0h.y, (int)a0h.z, (int)a0h.w };
+      const int a1[8] = { (int)a1l.x, (int)a1l.y, (int)a1l.z, (int)a1l.w, (int)a1h.x, (int)a1h.y, (int)a1h.z, (int)a1h.w };
       int k[8];
+      // min(a0 + b0, a1 + b1) - b0 = min(a0, a1 + d): signed, b0 is added back below
 #pragma unroll
-      for (int e2 = 0; e2 < 4; e2++) {
-        const uint4 g4 = gxp[e2];                                       // columns c0+2*e2, c0+2*e2+1
-        // min(a0 + b0, a1 + b1) - b0 = min(a0, a1 + d): signed, b0 is added back below
-        k[2 * e2] = (int)sad[2 * e2] + min((int)g4.x, (int)g4.y + d);
-        k[2 * e2 + 1] = (int)sad[2 * e2 + 1] + min((int)g4.z, (int)g4.w + d);
-      }
+      for (int e = 0; e < 8; e++) k[e] = (int)sad[e] + min(a0[e], a1[e] + d);
       if (mask != 0xFFu) {
 #pragma unroll
         for (int e = 0; e < 8; e++) k[e] = ((mask >> e) & 1u) ? k[e] : 0x0FFFFFFF;
@@ -513,10 +538,10 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     auto issue = [&](int i, int slot) {
       if (i < total) {
         if (wide) {
-          cp_async16(&sm.ring[2 * slot][lane], mp + 2 * i);
-          cp_async16(&sm.ring[2 * slot + 1][lane], mp + 2 * i + 1);
+          cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * i);
+          cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * i + 1);
         } else {
-          cp_async16(&sm.ring[slot][lane], mp + i);
+          cp_async16(&sm.ring[slot * 32 + lane], mp + i);
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -528,10 +553,10 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
       else asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing - 1) : "memory");
       uint32_t sad[8];
       if (wide) {
-        const uint4 a = sm.ring[2 * slot][lane], b = sm.ring[2 * slot + 1][lane];
+        const uint4 a = sm.ring[(2 * slot) * 32 + lane], b = sm.ring[(2 * slot + 1) * 32 + lane];
         sad[0] = a.x; sad[1] = a.y; sad[2] = a.z; sad[3] = a.w; sad[4] = b.x; sad[5] = b.y; sad[6] = b.z; sad[7] = b.w;
       } else {
-        const uint4 a = sm.ring[slot][lane];
+        const uint4 a = sm.ring[slot * 32 + lane];
         sad[0] = a.x & 0xFFFFu; sad[1] = a.x >> 16; sad[2] = a.y & 0xFFFFu; sad[3] = a.y >> 16;
         sad[4] = a.z & 0xFFFFu; sad[5] = a.z >> 16; sad[6] = a.w & 0xFFFFu; sad[7] = a.w >> 16;
       }
@@ -544,6 +569,7 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | box_key(bc, wpos);
   } else {
+  if constexpr (!BOX) {
   for (int wi = 0; wi < nwin; wi++) {
     const int cx = wcx[wi], cy = wcy[wi];
     // separable AMVP bit tables and the merge overrides of this window
@@ -736,6 +762,7 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
     }
   }
   }
+  }
   best = warp_min(best);
 
   // ---- winner of the integer search, parked in the job's result record ----
@@ -758,20 +785,43 @@ __device__ void scan_job(int lane, ScanSmem &sm, const MeFrame &f, const kvz_cud
 }
 
 
-// BOX: the jobs whose windows all lie inside a box map set (single pass over the union); !BOX: the others
+// bytes of dynamic shared memory one warp of the box scan needs for boxes up to n_dx x n_dy
+__host__ __device__ inline size_t box_scan_warp_bytes(int n_dx, int n_dy)
+{
+  const size_t b = (size_t)kScanRing * 32 * 16 + (size_t)4 * (n_dx / 8) * 16 + (size_t)n_dy * 8 + (((size_t)n_dy * 4 + 15) & ~(size_t)15) + 48;
+  return (b + 15) & ~(size_t)15;
+}
+
+// BOX: the jobs whose windows all lie inside a box map set (single pass over the union); !BOX: the others.
+// box_dx, box_dy: the largest box sides among the frame's map sets (BOX only)
 template <bool BOX>
 __global__ void __launch_bounds__(kScanWarps * 32, KVZ_SCAN_MINB)
 me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restrict__ pus,
-               const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *__restrict__ results, int n_pus)
+               const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *__restrict__ results, int n_pus,
+               int box_dx, int box_dy)
 {
-  __shared__ ScanSmem sm[kScanWarps];
+  extern __shared__ __align__(16) unsigned char scan_dyn[];
   __shared__ kvz_cuda_merge_cand merge[5];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const kvz_cuda_me_pu &pu = pus[blockIdx.x];
   if (threadIdx.x < 5) merge[threadIdx.x] = pu.merge_cand[threadIdx.x];
   __syncthreads();
-  for (int q = warp; q < pu.num_jobs; q += kScanWarps)
-    scan_job<BOX>(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q);
+  if constexpr (BOX) {
+    unsigned char *base = scan_dyn + warp * box_scan_warp_bytes(box_dx, box_dy);
+    uint4 *ring = reinterpret_cast<uint4 *>(base);
+    uint4 *gxv = ring + kScanRing * 32;
+    const int nv = box_dx / 8;
+    uint2 *gy = reinterpret_cast<uint2 *>(gxv + 4 * nv);
+    uint32_t *rowinfo = reinterpret_cast<uint32_t *>(gy + box_dy);
+    int *hits = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(rowinfo) + (((size_t)box_dy * 4 + 15) & ~(size_t)15));
+    ScanSmemT<true> sm = { ring, gxv, nv, gy, rowinfo, hits, hits + 5, hits[10] };
+    for (int q = warp; q < pu.num_jobs; q += kScanWarps)
+      scan_job<true>(lane, sm, f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q, false);
+  } else {
+    __shared__ ScanSmemT<false> sm[kScanWarps];
+    for (int q = warp; q < pu.num_jobs; q += kScanWarps)
+      scan_job<false>(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q, box_dx > 0);
+  }
 }
 
 // ======================================================================================
@@ -1076,15 +1126,21 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
                      kvz_cuda_me_result *results, int n_pus, cudaStream_t stream)
 {
   if (n_pus <= 0) return 1;
-  bool any_box = false;
+  int box_dx = 0, box_dy = 0;                   // the largest box sides among the map sets
   for (int r = 0; r < f.n_refs; r++)
-    for (int m = 0; m < f.refs[r].n_sets; m++) any_box |= f.refs[r].sets[m].n_dx > 0;
-  if (any_box) {
-    me_scan_kernel<true><<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
+    for (int m = 0; m < f.refs[r].n_sets; m++) {
+      if (f.refs[r].sets[m].n_dx > box_dx) box_dx = f.refs[r].sets[m].n_dx;
+      if (f.refs[r].sets[m].n_dy > box_dy) box_dy = f.refs[r].sets[m].n_dy;
+    }
+  if (box_dx > 0) {
+    const size_t smem = kScanWarps * box_scan_warp_bytes(box_dx, box_dy);
+    auto kern = me_scan_kernel<true>;
+    KVZ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<n_pus, kScanWarps * 32, smem, stream>>>(f, pus, jobs, results, n_pus, box_dx, box_dy);
     count_launch();
     KVZ_CUDA_LAUNCH_CHECK();
   }
-  me_scan_kernel<false><<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus);
+  me_scan_kernel<false><<<n_pus, kScanWarps * 32, 0, stream>>>(f, pus, jobs, results, n_pus, box_dx, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   {
