@@ -547,6 +547,29 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int t = 0; t < depth; t++) issue(lane + t * G, t);
+    // Early rejection: the exact cost of a few likely candidates (the window centres and the two AMVP
+    // predictors, where they are searched) bounds the minimum from above; a vector whose smallest SAD
+    // already exceeds that bound (bit costs are >= 0) can hold neither the winner nor a tie with it.
+    uint32_t seed = 0xFFFFFFFFu;
+    {
+      int sx = 0, sy = 0;
+      bool have = false;
+      if (lane < nwin) { sx = wcx[lane]; sy = wcy[lane]; have = true; }
+      else if (lane == 8 || lane == 9) { sx = (j.mv_cand[lane - 8][0] + 2) >> 2; sy = (j.mv_cand[lane - 8][1] + 2) >> 2; have = true; }
+      if (have) {
+        const int col = sx - bx0, row = sy - by0;
+        const uint32_t pos = ((uint32_t)row << 16) | (uint32_t)col;
+        if (col >= 0 && col < n_dx && row >= 0 && row < n_dy && box_key(bc, pos) != 0xFFFFFFFFu) {
+          const size_t at = (prow * (size_t)n_dy + row) * n_dx + col;
+          const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + at) & 0xFFFFu
+                                         : __ldg((level == 2 ? ms.sad32 : ms.sad64) + at);
+          seed = box_price(bc, row, col, sad);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) seed = min(seed, __shfl_xor_sync(0xffffffffu, seed, o));
+    }
+    uint32_t bound = seed;                          // min(seed, wbest)
     int slot = 0;
     for (int i = lane; i < total; i += G) {
       if (wide) asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing / 2 - 1) : "memory");
@@ -562,7 +585,11 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
       }
       issue(i + depth * G, slot);                                   // the slot just read is free again
       slot = slot + 1 == depth ? 0 : slot + 1;
-      price(row, vec, sad);
+      const uint32_t smin = min(min(min(sad[0], sad[1]), min(sad[2], sad[3])), min(min(sad[4], sad[5]), min(sad[6], sad[7])));
+      if (smin <= bound) {
+        price(row, vec, sad);
+        bound = min(bound, wbest);
+      }
       row += srow; vec += svec;
       if (vec >= vpr) { vec -= vpr; row++; }
     }
