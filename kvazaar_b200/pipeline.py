@@ -73,9 +73,9 @@ def window_centres(pus, jobs, n_refs, max_sets=3):
 
 class MePipeline:
     # dram__bytes_read.sum + dram__bytes_write.sum of the dense SAD launches of one step (the four box launches
-    # of the default 1080p / full32 / 4-reference workload), from profiles/r01b_prof_sad_summary.txt
-    # (ncu --set full): 486.8 + 486.6 + 546.3 + 665.2 MB
-    NCU_TRAFFIC_BYTES = 2184962000
+    # of the default 1080p / full32 / 4-reference workload), from profiles/r01d_prof_sad_summary.txt
+    # (ncu --set full): 431.5 + 472.8 + 494.3 + 626.1 MB
+    NCU_TRAFFIC_BYTES = 2024653000
 
     def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda", use_boxes=True):
         """use_boxes: one box of displacements per reference that covers the zero window and the frequent
