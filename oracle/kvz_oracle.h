@@ -90,6 +90,28 @@ void kvzo_scan_order(int scan_idx, int log2_size, uint32_t *out);
 void kvzo_transformskip(int bitdepth, const int16_t *block, int16_t *coeff, int n);   /* transform.c:151-161 */
 void kvzo_itransformskip(int bitdepth, int16_t *block, const int16_t *coeff, int n);  /* transform.c:169-181 */
 
+/* ---- A15: rate-distortion optimised quantisation (rdo.c:548-885) ---- */
+
+/* the CABAC context states (cabac_ctx_t.uc_state, cabac.h:36-39) that kvz_rdoq reads from
+ * state->cabac.ctx (cabac.h:53-90), in the order of that struct */
+typedef struct {
+  uint8_t cbf_luma[4], cbf_chroma[4];            /* qt_cbf_model_luma / _chroma */
+  uint8_t sig_group[4];                          /* cu_sig_coeff_group_model */
+  uint8_t sig_luma[27], sig_chroma[15];          /* cu_sig_model_* */
+  uint8_t last_y_luma[15], last_y_chroma[15];    /* cu_ctx_last_y_* */
+  uint8_t last_x_luma[15], last_x_chroma[15];    /* cu_ctx_last_x_* */
+  uint8_t one_luma[16], one_chroma[8];           /* cu_one_model_* */
+  uint8_t abs_luma[4], abs_chroma[2];            /* cu_abs_model_* */
+  uint8_t root_cbf;                              /* cu_qt_root_cbf_model */
+  uint8_t reserved[3];
+} kvzo_rdoq_ctx;                                 /* 148 bytes */
+
+/* kvz_rdoq (rdo.c:548-885) + kvz_rdoq_sign_hiding (rdo.c:405-540), flat scaling list.
+ * type 0 luma / 2 chroma, scan_idx 0 diag / 1 hor / 2 ver (hor/ver only for width <= 8).
+ * Every entry of dest is written. */
+void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, const int16_t *coef,
+               int16_t *dest, int width, int type, int scan_idx, int tr_depth);
+
 /* ---- pixel-typed API, generated for SFX in {8, 10} ---- */
 #define KVZO_DECLARE(PIX, SFX) \
   /* A1 picture-generic.c:86-99 */ \

@@ -374,6 +374,67 @@ int ref_shim_rdoq(const ref_q_cfg *c, coeff_t *coef, coeff_t *q_coef, int width,
   return 1;
 }
 
+/* the context states kvz_rdoq reads, in the layout of kvzo_rdoq_ctx / kvz_cuda_rdoq_ctx (148 bytes) */
+typedef struct {
+  uint8_t cbf_luma[4], cbf_chroma[4];
+  uint8_t sig_group[4];
+  uint8_t sig_luma[27], sig_chroma[15];
+  uint8_t last_y_luma[15], last_y_chroma[15];
+  uint8_t last_x_luma[15], last_x_chroma[15];
+  uint8_t one_luma[16], one_chroma[8];
+  uint8_t abs_luma[4], abs_chroma[2];
+  uint8_t root_cbf;
+  uint8_t reserved[3];
+} ref_rdoq_ctx;
+
+#define CTX_COPY(dir, field, member, n) \
+  for (int i_ = 0; i_ < (n); i_++) { \
+    if (dir) cab->ctx.member[i_].uc_state = s->field[i_]; else s->field[i_] = cab->ctx.member[i_].uc_state; }
+
+static void ctx_transfer(int to_cabac, cabac_data_t *cab, ref_rdoq_ctx *s)
+{
+  CTX_COPY(to_cabac, cbf_luma, qt_cbf_model_luma, 4)
+  CTX_COPY(to_cabac, cbf_chroma, qt_cbf_model_chroma, 4)
+  CTX_COPY(to_cabac, sig_group, cu_sig_coeff_group_model, 4)
+  CTX_COPY(to_cabac, sig_luma, cu_sig_model_luma, 27)
+  CTX_COPY(to_cabac, sig_chroma, cu_sig_model_chroma, 15)
+  CTX_COPY(to_cabac, last_y_luma, cu_ctx_last_y_luma, 15)
+  CTX_COPY(to_cabac, last_y_chroma, cu_ctx_last_y_chroma, 15)
+  CTX_COPY(to_cabac, last_x_luma, cu_ctx_last_x_luma, 15)
+  CTX_COPY(to_cabac, last_x_chroma, cu_ctx_last_x_chroma, 15)
+  CTX_COPY(to_cabac, one_luma, cu_one_model_luma, 16)
+  CTX_COPY(to_cabac, one_chroma, cu_one_model_chroma, 8)
+  CTX_COPY(to_cabac, abs_luma, cu_abs_model_luma, 4)
+  CTX_COPY(to_cabac, abs_chroma, cu_abs_model_chroma, 2)
+  if (to_cabac) cab->ctx.cu_qt_root_cbf_model.uc_state = s->root_cbf;
+  else s->root_cbf = cab->ctx.cu_qt_root_cbf_model.uc_state;
+}
+
+/* the states kvz_init_contexts (context.c:209-300) gives a slice of this QP and type */
+int ref_shim_init_rdoq_ctx(int qp, int slice_is_intra, ref_rdoq_ctx *out)
+{
+  ref_q_cfg c; memset(&c, 0, sizeof(c));
+  c.qp = qp; c.slice_is_intra = slice_is_intra; c.rdoq = 1;
+  fake_qenv *e = qenv_make(&c);
+  memset(out, 0, sizeof(*out));
+  ctx_transfer(0, &e->state.cabac, out);
+  qenv_free(e);
+  return 1;
+}
+
+/* kvz_rdoq with caller-chosen context states */
+int ref_shim_rdoq_ctx(const ref_q_cfg *c, const ref_rdoq_ctx *ctx, coeff_t *coef, coeff_t *q_coef, int width,
+                      int type, int scan_idx, int tr_depth)
+{
+  fake_qenv *e = qenv_make(c);
+  ref_rdoq_ctx tmp = *ctx;
+  ctx_transfer(1, &e->state.cabac, &tmp);
+  kvz_rdoq(&e->state, coef, q_coef, width, width, (int8_t)type, (int8_t)scan_idx,
+           c->cu_is_intra ? CU_INTRA : CU_INTER, (int8_t)tr_depth);
+  qenv_free(e);
+  return 1;
+}
+
 int ref_shim_quantize_residual(const ref_q_cfg *c, int width, int color, int scan_idx, int use_trskip,
                                int in_stride, int out_stride, const kvz_pixel *ref_in,
                                const kvz_pixel *pred_in, kvz_pixel *rec_out, coeff_t *coeff_out)

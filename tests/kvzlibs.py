@@ -83,6 +83,27 @@ class RefQCfg(C.Structure):
                 ("lambda_", C.c_double)]
 
 
+class RdoqCtx(C.Structure):
+    """kvzo_rdoq_ctx == ref_rdoq_ctx == kvz_cuda_rdoq_ctx: the CABAC context states kvz_rdoq reads"""
+    _fields_ = [("cbf_luma", C.c_uint8 * 4), ("cbf_chroma", C.c_uint8 * 4), ("sig_group", C.c_uint8 * 4),
+                ("sig_luma", C.c_uint8 * 27), ("sig_chroma", C.c_uint8 * 15),
+                ("last_y_luma", C.c_uint8 * 15), ("last_y_chroma", C.c_uint8 * 15),
+                ("last_x_luma", C.c_uint8 * 15), ("last_x_chroma", C.c_uint8 * 15),
+                ("one_luma", C.c_uint8 * 16), ("one_chroma", C.c_uint8 * 8),
+                ("abs_luma", C.c_uint8 * 4), ("abs_chroma", C.c_uint8 * 2),
+                ("root_cbf", C.c_uint8), ("reserved", C.c_uint8 * 3)]
+
+
+assert C.sizeof(RdoqCtx) == 148
+
+
+def random_rdoq_ctx(rs):
+    """context states drawn uniformly from the 128 (state, MPS) pairs"""
+    raw = rs.integers(0, 128, 148, dtype=np.uint8)
+    raw[145:] = 0
+    return RdoqCtx.from_buffer_copy(raw.tobytes())
+
+
 def ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
