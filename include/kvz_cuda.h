@@ -312,6 +312,45 @@ KVZ_CUDA_API int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, cons
                                              void *d_rec, int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs,
                                              int n_jobs, uint8_t *d_has_coeffs, void *stream);
 
+/* ---- A15: rate-distortion optimised quantisation ---- */
+
+/* The CABAC context states (cabac_ctx_t.uc_state, cabac.h:36-39) that kvz_rdoq reads from
+ * state->cabac.ctx (cabac.h:53-90).  The host snapshots them once per CTU / wavefront step; any
+ * number of blocks may share a snapshot. */
+typedef struct kvz_cuda_rdoq_ctx {
+  uint8_t cbf_luma[4], cbf_chroma[4];            /* qt_cbf_model_luma / qt_cbf_model_chroma */
+  uint8_t sig_group[4];                          /* cu_sig_coeff_group_model */
+  uint8_t sig_luma[27], sig_chroma[15];          /* cu_sig_model_luma / _chroma */
+  uint8_t last_y_luma[15], last_y_chroma[15];    /* cu_ctx_last_y_luma / _chroma */
+  uint8_t last_x_luma[15], last_x_chroma[15];    /* cu_ctx_last_x_luma / _chroma */
+  uint8_t one_luma[16], one_chroma[8];           /* cu_one_model_luma / _chroma */
+  uint8_t abs_luma[4], abs_chroma[2];            /* cu_abs_model_luma / _chroma */
+  uint8_t root_cbf;                              /* cu_qt_root_cbf_model */
+  uint8_t reserved[3];
+} kvz_cuda_rdoq_ctx;                             /* 148 bytes */
+
+/* one kvz_rdoq() call (rdo.c:548-551) */
+typedef struct kvz_cuda_rdoq_job {
+  uint32_t coef_offset;               /* element offset of the width*width block in d_coef and in d_q_coef */
+  uint32_t ctx_index;                 /* entry of d_ctx holding state->cabac.ctx for this block */
+  double lambda;                      /* state->lambda */
+  uint8_t width;                      /* 4, 8, 16, 32 (height == width) */
+  uint8_t type;                       /* 0 luma, 2 chroma */
+  uint8_t scan_idx;                   /* coeff_scan_order_t; 1 and 2 only for width <= 8 (tables.h:72-77) */
+  uint8_t tr_depth;
+  int8_t qp;                          /* state->qp */
+  uint8_t cu_is_intra;                /* block_type == CU_INTRA */
+  uint8_t reserved[2];
+} kvz_cuda_rdoq_job;                  /* 24 bytes */
+
+/* kvz_rdoq (rdo.c:548-885) including kvz_rdoq_sign_hiding (rdo.c:405-540) for a batch of transform
+ * blocks: d_q_coef receives dest_coeff.  cfg supplies bitdepth and signhide; qp and cu_is_intra come
+ * from each job.  Flat scaling list.  All floating-point work is IEEE double in the reference's
+ * operation order (no FMA contraction), so the chosen levels are bit-identical. */
+KVZ_CUDA_API int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *d_ctx,
+                                      const int16_t *d_coef, int16_t *d_q_coef,
+                                      const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: fractional-sample interpolation  (rows A9, A10, A11, A12) */
 /* ------------------------------------------------------------------ */

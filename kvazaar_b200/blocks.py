@@ -118,6 +118,34 @@ def quantize_residuals(d_ref, d_pred, d_rec, d_coeff, jobs, slice_is_intra=False
     return has
 
 
+RDOQ_CTX_DT = np.dtype([("cbf_luma", "u1", (4,)), ("cbf_chroma", "u1", (4,)), ("sig_group", "u1", (4,)),
+                        ("sig_luma", "u1", (27,)), ("sig_chroma", "u1", (15,)),
+                        ("last_y_luma", "u1", (15,)), ("last_y_chroma", "u1", (15,)),
+                        ("last_x_luma", "u1", (15,)), ("last_x_chroma", "u1", (15,)),
+                        ("one_luma", "u1", (16,)), ("one_chroma", "u1", (8,)),
+                        ("abs_luma", "u1", (4,)), ("abs_chroma", "u1", (2,)),
+                        ("root_cbf", "u1"), ("reserved", "u1", (3,))])
+assert RDOQ_CTX_DT.itemsize == 148
+RDOQ_JOB_DT = np.dtype([("coef_offset", "<u4"), ("ctx_index", "<u4"), ("lambda", "<f8"), ("width", "u1"),
+                        ("type", "u1"), ("scan_idx", "u1"), ("tr_depth", "u1"), ("qp", "i1"),
+                        ("cu_is_intra", "u1"), ("reserved", "u1", (2,))])
+assert RDOQ_JOB_DT.itemsize == 24
+
+
+def rdoq_blocks(d_coef, ctxs, jobs, signhide=False, bitdepth=8):
+    """kvz_rdoq (rdo.c:548-885) for a batch of transform blocks.  d_coef: device int16 coefficients;
+    ctxs: numpy RDOQ_CTX_DT array of CABAC context snapshots; jobs: numpy RDOQ_JOB_DT array.
+    Returns the levels (device int16, same layout as d_coef)."""
+    capi.init(torch.cuda.current_device())
+    d_jobs, d_ctx = _dev(jobs), _dev(ctxs)
+    out = torch.zeros_like(d_coef)
+    cfg = _qcfg(0, bitdepth, False, signhide, False)
+    max_width = int(jobs["width"].max()) if len(jobs) else 4
+    capi.check(capi.lib().kvz_cuda_rdoq_blocks(C.byref(cfg), _p(d_ctx), _p(d_coef), _p(out), _p(d_jobs), len(jobs),
+                                               max_width, _stream()), "kvz_cuda_rdoq_blocks")
+    return out
+
+
 INTERP_PIXEL, INTERP_14BIT, INTERP_FME = 0, 1, 2
 INTERP_JOB_DT = np.dtype([("x", "<i4"), ("y", "<i4"), ("mv_x", "<i4"), ("mv_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                           ("chroma", "u1"), ("mode", "u1"), ("reserved", "u1", (2,)), ("dst_offset", "<u4"),

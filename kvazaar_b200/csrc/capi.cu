@@ -25,6 +25,8 @@ int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_id
 int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32_t *out, cudaStream_t stream);
 int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
                              const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream);
+int launch_rdoq_batch(const kvz_cuda_quant_cfg &cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
+                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, cudaStream_t stream);
 }
 namespace kvz {
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
@@ -297,6 +299,16 @@ int kvz_cuda_dequant_blocks(const kvz_cuda_quant_cfg *cfg, int n, int type, cons
   if (!check_qcfg(cfg, "kvz_cuda_dequant_blocks: bad cfg")) return 0;
   if (!d_coef || !d_q_coef || count < 0) return fail_msg("kvz_cuda_dequant_blocks: bad argument");
   return launch_quant_batch(*cfg, n, type, 0, 1, d_q_coef, d_coef, count, (cudaStream_t)stream);
+}
+
+int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
+                         int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_rdoq_blocks: bad cfg")) return 0;
+  if (!d_ctx || !d_coef || !d_q_coef || !d_jobs || n_jobs < 0) return fail_msg("kvz_cuda_rdoq_blocks: bad argument");
+  if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
+    return fail_msg("kvz_cuda_rdoq_blocks: max_width must be 4, 8, 16 or 32");
+  return launch_rdoq_batch(*cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs, max_width, (cudaStream_t)stream);
 }
 
 int kvz_cuda_coeff_abs_sums(const int16_t *d_coeffs, int per_block, int count, uint32_t *d_out, void *stream)
