@@ -351,6 +351,17 @@ KVZ_CUDA_API int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_c
                                       const int16_t *d_coef, int16_t *d_q_coef,
                                       const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, void *stream);
 
+/* kvz_quantize_residual (quant-generic.c:180-273) with cfg.rdoq_enable: residual -> transform -> kvz_rdoq ->
+ * dequant -> inverse transform -> reconstruction.  d_rdoq_jobs[i] describes the kvz_rdoq call of d_jobs[i]
+ * (same width; coef_offset == coeff_offset; type 0 for colour Y, 2 otherwise; tr_depth as computed at
+ * quant-generic.c:216-217).  d_work: scratch for the transform coefficients, as large as d_coeff.  With
+ * rdoq_skip != 0 the 4x4 blocks use the scalar quantiser (cfg.rdoq_skip, quant-generic.c:213-215). */
+KVZ_CUDA_API int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred,
+                                                  void *d_rec, int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs,
+                                                  int n_jobs, uint8_t *d_has_coeffs, const kvz_cuda_rdoq_ctx *d_ctx,
+                                                  const kvz_cuda_rdoq_job *d_rdoq_jobs, int max_width, int16_t *d_work,
+                                                  int rdoq_skip, void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: fractional-sample interpolation  (rows A9, A10, A11, A12) */
 /* ------------------------------------------------------------------ */

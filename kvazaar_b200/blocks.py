@@ -146,6 +146,22 @@ def rdoq_blocks(d_coef, ctxs, jobs, signhide=False, bitdepth=8):
     return out
 
 
+def quantize_residuals_rdoq(d_ref, d_pred, d_rec, d_coeff, jobs, ctxs, rdoq_jobs, slice_is_intra=False, signhide=False,
+                            rdoq_skip=False, bitdepth=8):
+    """kvz_quantize_residual with cfg.rdoq_enable (quant-generic.c:180-273 + rdo.c:548-885) for a batch of
+    transform blocks.  jobs: RESIDUAL_JOB_DT, rdoq_jobs: RDOQ_JOB_DT (paired), ctxs: RDOQ_CTX_DT."""
+    capi.init(torch.cuda.current_device())
+    d_jobs, d_rj, d_ctx = _dev(jobs), _dev(rdoq_jobs), _dev(ctxs)
+    has = torch.zeros(len(jobs), dtype=torch.uint8, device="cuda")
+    work = torch.empty_like(d_coeff)
+    cfg = _qcfg(0, bitdepth, slice_is_intra, signhide, False)
+    max_width = int(jobs["width"].max()) if len(jobs) else 4
+    capi.check(capi.lib().kvz_cuda_quantize_residuals_rdoq(
+        C.byref(cfg), _p(d_ref), _p(d_pred), _p(d_rec), _p(d_coeff), _p(d_jobs), len(jobs), _p(has), _p(d_ctx), _p(d_rj),
+        max_width, _p(work), int(rdoq_skip), _stream()), "kvz_cuda_quantize_residuals_rdoq")
+    return has
+
+
 INTERP_PIXEL, INTERP_14BIT, INTERP_FME = 0, 1, 2
 INTERP_JOB_DT = np.dtype([("x", "<i4"), ("y", "<i4"), ("mv_x", "<i4"), ("mv_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                           ("chroma", "u1"), ("mode", "u1"), ("reserved", "u1", (2,)), ("dst_offset", "<u4"),

@@ -26,7 +26,12 @@ int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32
 int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
                              const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream);
 int launch_rdoq_batch(const kvz_cuda_quant_cfg &cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
-                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, cudaStream_t stream);
+                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, int skip4,
+                      cudaStream_t stream);
+int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
+                                  const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs,
+                                  const kvz_cuda_rdoq_ctx *d_ctx, const kvz_cuda_rdoq_job *rdoq_jobs, int max_width,
+                                  int16_t *work, int rdoq_skip, cudaStream_t stream);
 }
 namespace kvz {
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
@@ -308,7 +313,23 @@ int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx 
   if (!d_ctx || !d_coef || !d_q_coef || !d_jobs || n_jobs < 0) return fail_msg("kvz_cuda_rdoq_blocks: bad argument");
   if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
     return fail_msg("kvz_cuda_rdoq_blocks: max_width must be 4, 8, 16 or 32");
-  return launch_rdoq_batch(*cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs, max_width, (cudaStream_t)stream);
+  return launch_rdoq_batch(*cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs, max_width, 0, (cudaStream_t)stream);
+}
+
+int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred, void *d_rec,
+                                     int16_t *d_coeff, const kvz_cuda_residual_job *d_jobs, int n_jobs,
+                                     uint8_t *d_has_coeffs, const kvz_cuda_rdoq_ctx *d_ctx,
+                                     const kvz_cuda_rdoq_job *d_rdoq_jobs, int max_width, int16_t *d_work, int rdoq_skip,
+                                     void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_quantize_residuals_rdoq: bad cfg")) return 0;
+  if (cfg->bitdepth != 8) return fail_msg("kvz_cuda_quantize_residuals_rdoq: only bitdepth 8 is implemented");
+  if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || !d_ctx || !d_rdoq_jobs || !d_work || n_jobs < 0)
+    return fail_msg("kvz_cuda_quantize_residuals_rdoq: bad argument");
+  if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
+    return fail_msg("kvz_cuda_quantize_residuals_rdoq: max_width must be 4, 8, 16 or 32");
+  return launch_quantize_residual_rdoq(*cfg, d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has_coeffs, d_ctx,
+                                       d_rdoq_jobs, max_width, d_work, rdoq_skip, (cudaStream_t)stream);
 }
 
 int kvz_cuda_coeff_abs_sums(const int16_t *d_coeffs, int per_block, int count, uint32_t *d_out, void *stream)

@@ -373,12 +373,13 @@ __device__ void hide_sign_in_group(const RdoqHead &H, const Arrays &A, int g, in
 
 __global__ void __launch_bounds__(32)
 rdoq_kernel(kvz_cuda_quant_cfg cfg, const kvz_cuda_rdoq_ctx *__restrict__ ctxs, const int16_t *__restrict__ coef_g,
-            int16_t *__restrict__ out_g, const kvz_cuda_rdoq_job *__restrict__ jobs, int n_jobs)
+            int16_t *__restrict__ out_g, const kvz_cuda_rdoq_job *__restrict__ jobs, int n_jobs, int skip4)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x;
   const kvz_cuda_rdoq_job jb = jobs[blockIdx.x];
   const int width = jb.width, lg = ilog2_pow2(width), nn = width * width;
+  if (skip4 && width == 4) return;          // cfg.rdoq_skip: 4x4 blocks keep the scalar quantiser's levels (quant-generic.c:213-215)
   RdoqHead &H = *reinterpret_cast<RdoqHead *>(smem_raw);
   Arrays A;
   {
@@ -474,12 +475,13 @@ rdoq_kernel(kvz_cuda_quant_cfg cfg, const kvz_cuda_rdoq_ctx *__restrict__ ctxs, 
 }  // namespace
 
 int launch_rdoq_batch(const kvz_cuda_quant_cfg &cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
-                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, cudaStream_t stream)
+                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, int skip4,
+                      cudaStream_t stream)
 {
   if (n_jobs == 0) return 1;
   const size_t smem = rdoq_smem_bytes(max_width * max_width);
   KVZ_CUDA_TRY(cudaFuncSetAttribute(rdoq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  rdoq_kernel<<<n_jobs, 32, smem, stream>>>(cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs);
+  rdoq_kernel<<<n_jobs, 32, smem, stream>>>(cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs, skip4);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

@@ -205,11 +205,17 @@ coeff_abs_sum_kernel(const int16_t *__restrict__ coeffs, int per_block, int coun
   if (lane == 0) out[blk] = s;
 }
 
-// kvz_quantize_residual (quant-generic.c:180-273) without RDOQ, one CTA per transform block
+// kvz_quantize_residual (quant-generic.c:180-273), one CTA per transform block.
+// STAGE 0: the whole function with the scalar quantiser (cfg.rdoq_enable == 0).
+// With RDOQ the function is three launches around rdoq_kernel (rdoq.cu):
+// STAGE 1: residual -> transform, coefficients to `work` (4x4 blocks under cfg.rdoq_skip are quantised here,
+//          quant-generic.c:213-215); STAGE 2: levels from coeff_out -> dequant -> inverse -> reconstruction.
+template <int STAGE>
 __global__ void __launch_bounds__(kThreads)
 quantize_residual_kernel(kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ pred,
                          uint8_t *__restrict__ rec, int16_t *__restrict__ coeff_out,
-                         const kvz_cuda_residual_job *__restrict__ jobs, int n_jobs, uint8_t *__restrict__ has_coeffs)
+                         const kvz_cuda_residual_job *__restrict__ jobs, int n_jobs, uint8_t *__restrict__ has_coeffs,
+                         int16_t *__restrict__ work, int rdoq_skip)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BlockSmem &sm = *reinterpret_cast<BlockSmem *>(smem_raw);
@@ -222,33 +228,45 @@ quantize_residual_kernel(kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, 
   c.cu_is_intra = jb.cu_is_intra;
   const bool dst4 = N == 4 && luma && jb.cu_is_intra;          // strategies-dct.c:59-113
   if (!jb.use_trskip) load_transform_matrix(sm.tt, N, dst4, tid, kThreads);
-  if (c.signhide) build_scan_table(sm.scan, jb.scan_idx, lg, tid, kThreads);
+  const bool scalar_quant = STAGE == 0 || (STAGE == 1 && N == 4 && rdoq_skip);
+  if (c.signhide && scalar_quant) build_scan_table(sm.scan, jb.scan_idx, lg, tid, kThreads);
   if (tid == 0) s_any = 0;
   const uint8_t *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
-  for (int i = tid; i < N * N; i += kThreads) {
-    const int y = i / N, x = i - y * N;
-    sm.a[y * P + x] = (int16_t)((int)rp[(size_t)y * jb.in_stride + x] - (int)pp[(size_t)y * jb.in_stride + x]);
-  }
-  __syncthreads();
   const int ts_shift = 15 - c.bitdepth - lg;
-  if (jb.use_trskip) {                                           // transform.c:151-161
+  int16_t *co = coeff_out + jb.coeff_offset;
+  if (STAGE != 2) {
     for (int i = tid; i < N * N; i += kThreads) {
-      int16_t &v = sm.a[(i / N) * P + (i % N)];
-      v = (int16_t)((int)v << ts_shift);
+      const int y = i / N, x = i - y * N;
+      sm.a[y * P + x] = (int16_t)((int)rp[(size_t)y * jb.in_stride + x] - (int)pp[(size_t)y * jb.in_stride + x]);
     }
     __syncthreads();
+    if (jb.use_trskip) {                                           // transform.c:151-161
+      for (int i = tid; i < N * N; i += kThreads) {
+        int16_t &v = sm.a[(i / N) * P + (i % N)];
+        v = (int16_t)((int)v << ts_shift);
+      }
+      __syncthreads();
+    } else {
+      forward2d(sm, N, c.bitdepth, tid);
+    }
+    if (!scalar_quant) {                                           // STAGE 1: the coefficients go to rdoq_kernel
+      int16_t *wo = work + jb.coeff_offset;
+      for (int i = tid; i < N * N; i += kThreads) wo[i] = sm.a[(i / N) * P + (i % N)];
+      return;
+    }
+    quant_block(sm, c, N, luma ? 0 : 2, tid);
+    __syncthreads();
   } else {
-    forward2d(sm, N, c.bitdepth, tid);
+    for (int i = tid; i < N * N; i += kThreads) sm.b[(i / N) * P + (i % N)] = co[i];
+    __syncthreads();
   }
-  quant_block(sm, c, N, luma ? 0 : 2, tid);
-  __syncthreads();
-  int16_t *co = coeff_out + jb.coeff_offset;
   int any = 0;
   for (int i = tid; i < N * N; i += kThreads) {
     const int16_t q = sm.b[(i / N) * P + (i % N)];
-    co[i] = q;
+    if (STAGE != 2) co[i] = q;
     any |= q != 0;
   }
+  if (STAGE == 1) return;
   if (any) s_any = 1;
   __syncthreads();
   uint8_t *op = rec + jb.rec_offset;
@@ -336,9 +354,33 @@ int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const
                              const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  if (!opt_in_smem(quantize_residual_kernel)) return 0;
-  quantize_residual_kernel<<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
-      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs);
+  if (!opt_in_smem(quantize_residual_kernel<0>)) return 0;
+  quantize_residual_kernel<0><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
+  return 1;
+}
+
+int launch_rdoq_batch(const kvz_cuda_quant_cfg &cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
+                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, int skip4,
+                      cudaStream_t stream);
+
+// kvz_quantize_residual with cfg.rdoq_enable: transform | RDOQ | reconstruction, three launches on one stream
+int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
+                                  const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs,
+                                  const kvz_cuda_rdoq_ctx *d_ctx, const kvz_cuda_rdoq_job *rdoq_jobs, int max_width,
+                                  int16_t *work, int rdoq_skip, cudaStream_t stream)
+{
+  if (n_jobs <= 0) return 1;
+  if (!opt_in_smem(quantize_residual_kernel<1>) || !opt_in_smem(quantize_residual_kernel<2>)) return 0;
+  quantize_residual_kernel<1><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
+  if (!launch_rdoq_batch(c, d_ctx, work, coeff, rdoq_jobs, n_jobs, max_width, rdoq_skip, stream)) return 0;
+  quantize_residual_kernel<2><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

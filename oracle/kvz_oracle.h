@@ -161,6 +161,12 @@ void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, con
                                    int use_trskip, int in_stride, int out_stride, \
                                    const PIX *ref_in, const PIX *pred_in, PIX *rec_out, \
                                    int16_t *coeff_out); \
+  /* the same with cfg.rdoq_enable (ctx != NULL): kvz_rdoq replaces kvz_quant, except for 4x4 under rdoq_skip */ \
+  int kvzo_quantize_residual_rdoq_##SFX(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, \
+                                        int rdoq_skip, int tr_depth, int width, int color, int scan_idx, \
+                                        int use_trskip, int in_stride, int out_stride, \
+                                        const PIX *ref_in, const PIX *pred_in, PIX *rec_out, \
+                                        int16_t *coeff_out); \
   /* test helper: SAD of one PU over the whole zero-centred window */ \
   void kvzo_dense_sad_map_##SFX(const PIX *pic, const PIX *ref, int W, int H, int x, int y, \
                                 int bw, int bh, int r, uint32_t *out); \

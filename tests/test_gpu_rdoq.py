@@ -7,6 +7,7 @@ import pytest
 
 import kvzlibs
 import rdoq_cases
+from kvzlibs import ptr
 from test_oracle_rdoq import run_oracle, run_ref
 
 pytestmark = pytest.mark.gpu
@@ -81,3 +82,57 @@ def test_rdoq_frame_batch_properties():
     assert np.all(np.abs(out.astype(np.int64)) <= top)
     assert np.all(np.sign(out) * np.sign(coef) >= 0)
     assert not out[::17].any() and out.any()
+
+
+@pytest.mark.parametrize("rdoq_skip", [0, 1])
+def test_fused_quantize_residual_with_rdoq(rdoq_skip):
+    """kvz_cuda_quantize_residuals_rdoq == kvz_quantize_residual with cfg.rdoq_enable (oracle, pinned on the reference)"""
+    import torch
+    from kvazaar_b200 import blocks
+    O = kvzlibs.oracle()
+    O.kvzo_quantize_residual_rdoq_8.argtypes = [C.c_void_p, C.c_double, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p] * 4
+    rs = np.random.default_rng(15 + rdoq_skip)
+    W, H = 256, 128
+    f = kvzlibs.synth_luma(9, W, H, 2)
+    ref, pred = f[1], f[0]
+    for signhide in (0, 1):
+        rows, rq, coff = [], [], 0
+        n_ctx = 5
+        ctx_list = [kvzlibs.random_rdoq_ctx(rs) for _ in range(n_ctx)]
+        ctxs = np.zeros(n_ctx, blocks.RDOQ_CTX_DT)
+        for i, cx in enumerate(ctx_list):
+            ctxs[i] = np.frombuffer(bytes(cx), blocks.RDOQ_CTX_DT)[0]
+        for _ in range(100):
+            n = int(rs.choice([4, 8, 16, 32]))
+            x, y = int(rs.integers(0, (W - n) // 4 + 1)) * 4, int(rs.integers(0, (H - n) // 4 + 1)) * 4
+            color = int(rs.integers(0, 3)) if n < 32 else 0
+            scan = int(rs.integers(0, 3)) if n <= 8 else 0
+            qp, intra = int(rs.integers(8, 48)), int(rs.integers(0, 2))
+            rows.append((y * W + x, y * W + x, y * W + x, coff, W, W, n, color, scan, int(n == 4 and rs.random() < 0.3),
+                         qp, intra, (0, 0)))
+            rq.append((coff, int(rs.integers(0, n_ctx)), float(0.57 * 2.0 ** ((qp - 12) / 3.0)), n, 0 if color == 0 else 2,
+                       scan, int(rs.integers(0, 3)), qp, intra, (0, 0)))
+            coff += n * n
+        jobs = np.array(rows, blocks.RESIDUAL_JOB_DT)
+        rjobs = np.array(rq, blocks.RDOQ_JOB_DT)
+        d_rec = torch.zeros((len(jobs), H, W), dtype=torch.uint8, device="cuda")
+        jobs["rec_offset"] += (np.arange(len(jobs)) * H * W).astype(np.uint32)
+        d_coeff = torch.zeros(coff, dtype=torch.int16, device="cuda")
+        has = blocks.quantize_residuals_rdoq(torch.from_numpy(ref).cuda(), torch.from_numpy(pred).cuda(), d_rec, d_coeff,
+                                             jobs, ctxs, rjobs, slice_is_intra=False, signhide=signhide,
+                                             rdoq_skip=rdoq_skip).cpu().numpy()
+        rec, coeff = d_rec.cpu().numpy(), d_coeff.cpu().numpy()
+        for i, (jb, rj) in enumerate(zip(jobs, rjobs)):
+            n = int(jb["width"])
+            oc = kvzlibs.OracleQCfg(int(jb["qp"]), 8, 0, signhide, int(jb["cu_is_intra"]))
+            rw = np.zeros((n, n), np.uint8); cw = np.zeros(n * n, np.int16)
+            off = int(jb["ref_offset"])
+            cx = ctx_list[int(rj["ctx_index"])]
+            hw = O.kvzo_quantize_residual_rdoq_8(C.addressof(oc), float(rj["lambda"]), C.addressof(cx), rdoq_skip,
+                                                 int(rj["tr_depth"]), n, int(jb["color"]), int(jb["scan_idx"]),
+                                                 int(jb["use_trskip"]), W, n, ptr(ref.reshape(-1)[off:]),
+                                                 ptr(pred.reshape(-1)[off:]), ptr(rw), ptr(cw))
+            y, x = off // W, off % W
+            assert has[i] == hw, i
+            assert np.array_equal(coeff[int(jb["coeff_offset"]):int(jb["coeff_offset"]) + n * n], cw), ("coeff", i, jb)
+            assert np.array_equal(rec[i, y:y + n, x:x + n], rw), ("rec", i, jb)

@@ -70,3 +70,38 @@ def test_rdoq_differs_from_plain_quant():
         O.kvzo_quant(C.byref(oc), ptr(case["coef"]), ptr(plain), case["width"], case["type"], case["scan_idx"])
         differ += int(not np.array_equal(plain, run_oracle(case, ctx)))
     assert differ > 5
+
+
+@needs_ref
+@pytest.mark.parametrize("rdoq_skip", [0, 1])
+def test_quantize_residual_with_rdoq_vs_reference(rdoq_skip):
+    """kvz_quantize_residual with cfg.rdoq_enable (quant-generic.c:211-221): transform -> kvz_rdoq -> reconstruction"""
+    L = kvzlibs.ref(1)
+    O = kvzlibs.oracle()
+    O.kvzo_quantize_residual_rdoq_8.argtypes = [C.c_void_p, C.c_double, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p] * 4
+    rs = np.random.default_rng(70 + rdoq_skip)
+    for n in (4, 8, 16, 32):
+        for it in range(16):
+            qp = int(rs.integers(10, 46))
+            color = int(rs.integers(0, 3)) if n < 32 else 0
+            intra = int(rs.integers(0, 2))
+            trskip = int(n == 4 and rs.random() < 0.3)
+            signhide = int(rs.integers(0, 2))
+            scan = int(rs.integers(0, 3)) if n <= 8 else 0
+            lam = float(0.57 * 2.0 ** ((qp - 12) / 3.0))
+            stride = n + 8 * int(rs.integers(0, 3))
+            ref_in = kvzlibs.aligned_copy(rs.integers(0, 256, (n, stride), dtype=np.uint8))
+            noise = rs.integers(-int(rs.integers(1, 40)), 40, (n, stride))
+            pred = kvzlibs.aligned_copy(np.clip(ref_in.astype(np.int64) + noise, 0, 255).astype(np.uint8))
+            rc = kvzlibs.RefQCfg(qp, intra, signhide, 1, rdoq_skip, intra, lam)
+            oc = kvzlibs.OracleQCfg(qp, 8, intra, signhide, intra)
+            ctx = kvzlibs.RdoqCtx()
+            L.ref_shim_init_rdoq_ctx(qp, intra, C.byref(ctx))
+            rec_w = kvzlibs.aligned((n, stride), np.uint8); rec_g = kvzlibs.aligned((n, stride), np.uint8)
+            co_w = kvzlibs.aligned((n * n,), np.int16); co_g = kvzlibs.aligned((n * n,), np.int16)
+            hw = L.ref_shim_quantize_residual(C.byref(rc), n, color, scan, trskip, stride, stride,
+                                              ptr(ref_in), ptr(pred), ptr(rec_w), ptr(co_w))
+            hg = O.kvzo_quantize_residual_rdoq_8(C.addressof(oc), lam, C.addressof(ctx), rdoq_skip, 0, n, color, scan,
+                                                 trskip, stride, stride, ptr(ref_in), ptr(pred), ptr(rec_g), ptr(co_g))
+            assert hg == hw and np.array_equal(co_g, co_w), ("coeff", n, it, qp, color, intra, trskip)
+            assert np.array_equal(rec_g[:, :n], rec_w[:, :n]), ("rec", n, it)
