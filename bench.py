@@ -298,7 +298,7 @@ def run_ours(args):
     n_sad = pipe.n_sad_launches
     achieved_ops = abs_diffs / (sad_ms * 1e-3)
     step_ms = ms / args.steps
-    kernel = "ime_sad_dense_kernel<0> (box)" if pipe.use_boxes else "ime_sad_dense_kernel<32>"
+    kernel = "ime_sad_multi_kernel (boxes of all references, one launch)" if pipe.use_boxes else "ime_sad_dense_kernel<32>"
     traffic = pipe.NCU_TRAFFIC_BYTES if (pipe.use_boxes and world >= 1) else None    # captured for the default (box) launches
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

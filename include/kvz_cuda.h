@@ -135,6 +135,19 @@ KVZ_CUDA_API int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d,
                                            uint16_t *d_sad8, uint16_t *d_sad16,
                                            uint32_t *d_sad32, uint32_t *d_sad64, void *stream);
 
+/* The box maps of up to 8 references of ONE current picture in a single launch (same results as one
+ * kvz_cuda_ime_sad_box_maps call per reference; the picture/tile fields of every desc must agree).  One grid
+ * instead of one per reference: no per-launch ramp and tail, heavy CTAs first. */
+#define KVZ_CUDA_IME_MAX_MULTI 8
+typedef struct kvz_cuda_ime_box_ref {
+  kvz_cuda_ime_box_desc desc;
+  const void *d_ref_padded;
+  uint16_t *d_sad8, *d_sad16;
+  uint32_t *d_sad32, *d_sad64;
+} kvz_cuda_ime_box_ref;
+KVZ_CUDA_API int kvz_cuda_ime_sad_box_maps_multi(const kvz_cuda_ime_box_ref *refs, int n_refs, const void *d_cur,
+                                                 void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: per-PU motion decision  (rows A3, A4, A5, A7-A10)         */
 /* ------------------------------------------------------------------ */

@@ -27,6 +27,7 @@ MAX_REFS = 16
 
 
 MAX_MAPSETS = 4
+IME_MAX_MULTI = 8
 
 
 class ImeBoxDesc(C.Structure):
@@ -35,6 +36,12 @@ class ImeBoxDesc(C.Structure):
                 ("tile_x", C.c_int32), ("tile_y", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
                 ("cur_pitch", C.c_int32), ("ref_pitch", C.c_int32), ("ref_pad", C.c_int32),
                 ("x0", C.c_int32), ("y0", C.c_int32), ("n_dx", C.c_int32), ("n_dy", C.c_int32)]
+
+
+class ImeBoxRef(C.Structure):
+    """kvz_cuda_ime_box_ref"""
+    _fields_ = [("desc", ImeBoxDesc), ("d_ref_padded", C.c_void_p), ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p),
+                ("d_sad32", C.c_void_p), ("d_sad64", C.c_void_p)]
 
 
 class MeMapSet(C.Structure):
@@ -91,6 +98,7 @@ SIGNATURES = {
     "kvz_cuda_ime_sad_maps": (C.c_int, [C.POINTER(ImeDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "kvz_cuda_ime_box_map_bytes": (C.c_size_t, [C.POINTER(ImeBoxDesc), C.c_int]),
     "kvz_cuda_ime_sad_box_maps": (C.c_int, [C.POINTER(ImeBoxDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "kvz_cuda_ime_sad_box_maps_multi": (C.c_int, [C.POINTER(ImeBoxRef), C.c_int, _VP, _VP]),
     "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

@@ -185,9 +185,9 @@ size_t kvz_cuda_ime_box_map_bytes(const kvz_cuda_ime_box_desc *d, int level)
   return ctus * n * n * (size_t)d->n_dy * (size_t)d->n_dx * (level < 2 ? 2 : 4);
 }
 
-int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur, const void *d_ref_padded,
-                              uint16_t *d_sad8, uint16_t *d_sad16, uint32_t *d_sad32, uint32_t *d_sad64,
-                              void *stream)
+// validates one box descriptor and fills the kernel parameters
+static int box_params(const kvz_cuda_ime_box_desc *d, const void *d_cur, const void *d_ref_padded, uint16_t *d_sad8,
+                      uint16_t *d_sad16, uint32_t *d_sad32, uint32_t *d_sad64, ImeSadParams &p)
 {
   if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
     return fail_msg("kvz_cuda_ime_sad_box_maps: null argument");
@@ -204,7 +204,6 @@ int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur,
   if ((d->width & 7) || (d->cur_pitch & 7) || (d->ref_pitch & 3) || (d->ref_pad & 3) ||
       (d->tile_x & 63) || (d->tile_y & 63) || (d->tile_w & 7) || (d->tile_h & 7))
     return fail_msg("kvz_cuda_ime_sad_box_maps: width/pitches/pad must be multiples of 8, tile origin of 64");
-  ImeSadParams p;
   p.cur = (const uint8_t *)d_cur;
   p.ref = (const uint8_t *)d_ref_padded;
   p.width = d->width; p.height = d->height;
@@ -213,7 +212,30 @@ int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur,
   p.ctus_x = (d->tile_w + 63) / 64; p.ctus_y = (d->tile_h + 63) / 64;
   p.map_pitch = d->n_dx;
   p.sad8 = d_sad8; p.sad16 = d_sad16; p.sad32 = d_sad32; p.sad64 = d_sad64;
+  return 1;
+}
+
+int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur, const void *d_ref_padded,
+                              uint16_t *d_sad8, uint16_t *d_sad16, uint32_t *d_sad32, uint32_t *d_sad64,
+                              void *stream)
+{
+  ImeSadParams p;
+  if (!box_params(d, d_cur, d_ref_padded, d_sad8, d_sad16, d_sad32, d_sad64, p)) return 0;
   return launch_ime_sad_box(p, d->x0, d->y0, d->n_dx, d->n_dy, (cudaStream_t)stream);
+}
+
+int kvz_cuda_ime_sad_box_maps_multi(const kvz_cuda_ime_box_ref *refs, int n_refs, const void *d_cur, void *stream)
+{
+  if (!refs || n_refs < 1 || n_refs > KVZ_CUDA_IME_MAX_MULTI)
+    return fail_msg("kvz_cuda_ime_sad_box_maps_multi: 1..8 references per call");
+  ImeSadParams ps[KVZ_CUDA_IME_MAX_MULTI];
+  int boxes[KVZ_CUDA_IME_MAX_MULTI][4];
+  for (int r = 0; r < n_refs; r++) {
+    const kvz_cuda_ime_box_ref &b = refs[r];
+    if (!box_params(&b.desc, d_cur, b.d_ref_padded, b.d_sad8, b.d_sad16, b.d_sad32, b.d_sad64, ps[r])) return 0;
+    boxes[r][0] = b.desc.x0; boxes[r][1] = b.desc.y0; boxes[r][2] = b.desc.n_dx; boxes[r][3] = b.desc.n_dy;
+  }
+  return launch_ime_sad_box_multi(ps, boxes, n_refs, (cudaStream_t)stream);
 }
 
 int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,

@@ -93,6 +93,9 @@ template <int PH, int S, int NJ>
 __device__ __forceinline__ void rows8(const uint32_t *trow, const uint32_t (&cur)[8][2], uint32_t (&acc)[8][4],
                                       uint16_t *stg /* &stage[0][blk][g] */)
 {
+#ifdef KVZ_SAD_EXP_NOCOMPUTE      // development: time the writer phase alone
+  if (PH >= 0) return;
+#endif
 #pragma unroll
   for (int u = 0; u < 8; u++) {
     if (PH == 0 && u < S) continue;
@@ -128,30 +131,53 @@ struct WriterPos {
   uint32_t o16, o32, o64;
   uint32_t src8;      // u16 index of the thread's 8 dx inside a ring slot
   uint32_t src16;     // u32 index of (first block of the 32x32 PU, dx pair) inside a ring slot
+  uint32_t rs;        // entries between consecutive dy rows of a PU
 };
 
-__device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, int chunk, int tid)
+// Two map layouts:
+//  * square window (chunk_major == 0): map[pu][row][map_pitch], chunk c owns columns 16c .. 16c+15 of every row;
+//  * box (chunk_major != 0): CHUNK-MAJOR, map[chunk][pu][row][nd] with nd = 16 (8 for a half last chunk): what one
+//    CTA writes for a PU is one contiguous run of n_dy * nd entries, and for the 64 blocks of its CTU one run of
+//    64 * n_dy * nd entries (147 KB at 1080p/full32) -- DRAM sees long sequential writes instead of 32-byte pieces
+//    a row pitch apart (measured: the writer phases alone 0.87 -> 0.52 ms per frame).
+__device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, int chunk, int tid, int nd)
 {
   const uint32_t PR = (uint32_t)p.pu_rows;
-  const uint32_t rs = (uint32_t)p.map_pitch;
   WriterPos w;
   const int blk = (tid >> 1) & 63, half = tid & 1;
-  w.o8 = ((uint32_t)ctu * 64 + blk) * PR * rs + chunk * kChunkDx + half * 8;
-  w.src8 = stage_slot(blk) * kChunkDx + half * 8;
   const int lane = tid & 31, p32 = lane >> 3, dxp = lane & 7;
-  const uint32_t col = chunk * kChunkDx + 2 * dxp;
-  w.o16 = ((uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2) * PR * rs + col;
-  w.o32 = ((uint32_t)ctu * 4 + p32) * PR * rs + col;
-  w.o64 = (uint32_t)ctu * PR * rs + col;
+  w.src8 = stage_slot(blk) * kChunkDx + half * 8;
   w.src16 = ((p32 >> 1) * 32 + (p32 & 1) * 4) * (kChunkDx / 2) + dxp;
+  const uint32_t pu8 = (uint32_t)ctu * 64 + blk, pu16 = (uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2,
+                 pu32 = (uint32_t)ctu * 4 + p32, pu64 = (uint32_t)ctu;
+  if (p.chunk_major) {
+    const uint32_t rs = (uint32_t)nd, nctu = (uint32_t)(p.ctus_x * p.ctus_y);
+    const uint32_t before = (uint32_t)chunk * kChunkDx * PR;        // entries per PU in the chunks before this one
+    w.rs = rs;
+    w.o8 = before * (nctu * 64) + pu8 * PR * rs + half * 8;
+    w.o16 = before * (nctu * 16) + pu16 * PR * rs + 2 * dxp;
+    w.o32 = before * (nctu * 4) + pu32 * PR * rs + 2 * dxp;
+    w.o64 = before * nctu + pu64 * PR * rs + 2 * dxp;
+  } else {
+    const uint32_t rs = (uint32_t)p.map_pitch;
+    const uint32_t col = chunk * kChunkDx + 2 * dxp;
+    w.rs = rs;
+    w.o8 = pu8 * PR * rs + chunk * kChunkDx + half * 8;
+    w.o16 = pu16 * PR * rs + col;
+    w.o32 = pu32 * PR * rs + col;
+    w.o64 = pu64 * PR * rs + col;
+  }
   return w;
 }
 
 // nd: displacement columns of this chunk (16 or 8)
 __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPos &wp, const uint16_t *stage, int m, int tid, int nd)
 {
+#ifdef KVZ_SAD_EXP_NOWRITE        // development: time the compute phase alone
+  if (p.skip >= 0) return;
+#endif
   const uint32_t PR = (uint32_t)p.pu_rows;
-  const uint32_t rs = (uint32_t)p.map_pitch;
+  const uint32_t rs = wp.rs;
   const int k0 = 8 * m - 7 - p.skip;              // map row of ring slot 0
   // (a) 8x8 map: thread = (block, half of the 16 dx), ring slots u0, u0+2, u0+4, u0+6
   {
@@ -287,94 +313,217 @@ __device__ __forceinline__ void last_column(const ImeSadParams &p, unsigned char
 #endif
 // one CTA = 16 dx (one chunk) x all dy of one CTU.  R > 0: square window, the first n_ctu CTAs do the last
 // column instead (they are short and latency bound: started first, they overlap the rest); R == 0: box
+// named barrier over `count` threads (count a multiple of 32); barrier 0 with the whole CTA == __syncthreads()
+__device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// Stages the reference tile of (ctu, chunk) as four byte-shifted copies and the current CTU; kThreads threads
+// (tid = 0..kThreads-1) that share named barrier `bar`.  `raw` is scratch for rows * kRawWords words.
+__device__ __forceinline__ void stage_tile(const ImeSadParams &p, const Geo &geo, uint32_t *tile, uint32_t *raw, uint8_t *cur_s,
+                                           int ctu, int chunk, int tid, int bar)
+{
+  const int CW = geo.copy_words;
+  const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
+  // tile rows ctu_y+y0 .., 84 bytes from column ctu_x+x0+16*chunk
+  const uint8_t *src = p.ref + (size_t)(ctu_y + p.y0 + p.pad) * p.ref_pitch + (ctu_x + p.x0 + kChunkDx * chunk + p.pad);
+  const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
+  const int sh = (int)(a0 & 3) * 8;
+  const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
+  // (1) raw rows (22 aligned words each) straight into shared memory, all copies in flight at once
+  for (int i = tid; i < geo.rows * kRawWords; i += kThreads) {
+    const int r = i / kRawWords, mw = i - r * kRawWords;
+    cp_async4(raw + i, src_al + (size_t)r * p.ref_pitch + 4 * mw);
+  }
+  stage_cur(p, cur_s, ctu_x, ctu_y, tid, kThreads);
+  cp_async_wait_all();
+  bar_sync(bar, kThreads);
+  // (2) the four byte-shifted copies
+  for (int i = tid; i < geo.rows * kRowWords; i += kThreads) {
+    const int r = i / kRowWords, mw = i - r * kRowWords;
+    const uint32_t *w = raw + r * kRawWords + mw;
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+    const uint32_t t0 = __funnelshift_r(w0, w1, sh), t1 = __funnelshift_r(w1, w2, sh);
+    tile[0 * CW + i] = t0;
+    tile[1 * CW + i] = __funnelshift_r(t0, t1, 8);
+    tile[2 * CW + i] = __funnelshift_r(t0, t1, 16);
+    tile[3 * CW + i] = __funnelshift_r(t0, t1, 24);
+  }
+  bar_sync(bar, kThreads);
+}
+
+template <int NJ>
+__device__ __forceinline__ void first_rows8(int skip, const uint32_t *trow, const uint32_t (&cur)[8][2], uint32_t (&acc)[8][4], uint16_t *stg)
+{
+  switch (skip) {
+    case 0: rows8<0, 0, NJ>(trow, cur, acc, stg); break;
+    case 1: rows8<0, 1, NJ>(trow, cur, acc, stg); break;
+    case 2: rows8<0, 2, NJ>(trow, cur, acc, stg); break;
+    case 3: rows8<0, 3, NJ>(trow, cur, acc, stg); break;
+    case 4: rows8<0, 4, NJ>(trow, cur, acc, stg); break;
+    case 5: rows8<0, 5, NJ>(trow, cur, acc, stg); break;
+    case 6: rows8<0, 6, NJ>(trow, cur, acc, stg); break;
+    default: rows8<0, 7, NJ>(trow, cur, acc, stg); break;
+  }
+}
+
+// one chunk CTA (kThreads threads): 16 (or 8) dx x all dy of one CTU; compute and writer phases alternate
+__device__ __forceinline__ void chunk_cta(const ImeSadParams &p, unsigned char *smem_raw, int ctu, int chunk)
+{
+  const int tid = threadIdx.x;
+  const Geo geo(p.n_dy);
+  const int CW = geo.copy_words;
+  uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
+  uint8_t *cur_s = smem_raw + (size_t)4 * CW * 4;
+  uint16_t *stage = reinterpret_cast<uint16_t *>(cur_s + 64 * 64);
+  stage_tile(p, geo, tile, reinterpret_cast<uint32_t *>(stage), cur_s, ctu, chunk, tid, 0);
+  const int warp = tid >> 5, lane = tid & 31;
+  const int by = warp, bx = lane >> 2, g = lane & 3, blk = by * 8 + bx;
+  uint32_t cur[8][2];
+#pragma unroll
+  for (int y = 0; y < 8; y++) {
+    const uint2 v = *reinterpret_cast<const uint2 *>(&cur_s[(by * 8 + y) * 64 + bx * 8]);
+    cur[y][0] = v.x; cur[y][1] = v.y;
+  }
+  uint32_t acc[8][4];
+  const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
+  uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
+  const int nd = chunk == p.n_chunks - 1 ? p.n_dx_last : kChunkDx;
+  const WriterPos wp = writer_pos(p, ctu, chunk, tid, nd);
+  auto run = [&](auto nj_tag) {
+    constexpr int NJ = decltype(nj_tag)::value;
+    first_rows8<NJ>(p.skip, trow, cur, acc, stg);
+    __syncthreads();
+    if (p.skip == 0) write_rows(p, wp, stage, 0, tid, nd);
+    __syncthreads();
+    for (int m = 1; m < geo.iters - 1; m++) {
+      rows8<1, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg);
+      __syncthreads();
+      write_rows(p, wp, stage, m, tid, nd);
+      __syncthreads();
+    }
+    rows8<2, 0, NJ>(trow + (geo.iters - 1) * 8 * kRowWords, cur, acc, stg);
+    __syncthreads();
+    write_rows(p, wp, stage, geo.iters - 1, tid, nd);
+  };
+  if (nd == kChunkDx) run(std::integral_constant<int, 4>());
+  else run(std::integral_constant<int, 2>());
+}
+
+// ---- warp-specialised chunk CTA: kThreads compute threads + kWriterThreads writer threads ----
+// Measured on B200 (1080p, four boxes): the compute phases alone take 0.80 ms per frame and the writer phases
+// alone 0.87 ms, but alternating them inside a CTA gives 1.05 ms even with two CTAs per SM: whenever both CTAs
+// write, the integer pipe idles.  Here the compute warps never stop: finished rows go to one of two ring
+// buffers, and two writer warps drain the other one (16-byte vectors of the 8x8 map, 16/32/64 sums) behind
+// named barriers.  full[b]: compute arrive -> writers wait; empty[b]: writers arrive -> compute wait.
+#ifndef KVZ_SAD_WRITERS
+#define KVZ_SAD_WRITERS 128
+#endif
+constexpr int kWriterThreads = KVZ_SAD_WRITERS;
+constexpr int kWsThreads = kThreads + kWriterThreads;
+constexpr int kRingEntries = 8 * 64 * kChunkDx;               // uint16 entries of one ring buffer
+enum { kBarCompute = 1, kBarFull0 = 2, kBarFull1 = 3, kBarEmpty0 = 4, kBarEmpty1 = 5 };
+
+__host__ __device__ inline size_t ws_smem_bytes(const Geo &geo)
+{
+  const size_t raw = (size_t)geo.rows * kRawWords * 4, ring = (size_t)2 * kRingEntries * 2;
+  return (size_t)4 * geo.copy_words * 4 + 64 * 64 + (raw > ring ? raw : ring);
+}
+
+__device__ __forceinline__ void chunk_cta_ws(const ImeSadParams &p, unsigned char *smem_raw, int ctu, int chunk)
+{
+  const int tid = threadIdx.x;
+  const Geo geo(p.n_dy);
+  const int CW = geo.copy_words;
+  uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
+  uint8_t *cur_s = smem_raw + (size_t)4 * CW * 4;
+  uint16_t *stage = reinterpret_cast<uint16_t *>(cur_s + 64 * 64);        // [2][kRingEntries]
+  const int nd = chunk == p.n_chunks - 1 ? p.n_dx_last : kChunkDx;
+  const int iters = geo.iters;
+  if (tid >= kThreads) {
+    // ---- writer warps: each thread stands in for four threads of the 256-thread writer layout ----
+    const int wt = tid - kThreads;
+    for (int m = 0; m < iters; m++) {
+      const int b = m & 1;
+      bar_sync(kBarFull0 + b, kWsThreads);
+      if (m > 0 || p.skip == 0) {
+#pragma unroll 1
+        for (int v = 0; v < kThreads / kWriterThreads; v++) {
+          const int vt = wt + v * kWriterThreads;
+          const WriterPos wp = writer_pos(p, ctu, chunk, vt, nd);
+          write_rows(p, wp, stage + b * kRingEntries, m, vt, nd);
+        }
+      }
+      if (m + 2 < iters) bar_arrive(kBarEmpty0 + b, kWsThreads);
+    }
+    return;
+  }
+  // ---- compute warps ----
+  stage_tile(p, geo, tile, reinterpret_cast<uint32_t *>(stage), cur_s, ctu, chunk, tid, kBarCompute);
+  const int warp = tid >> 5, lane = tid & 31;
+  const int by = warp, bx = lane >> 2, g = lane & 3, blk = by * 8 + bx;
+  uint32_t cur[8][2];
+#pragma unroll
+  for (int y = 0; y < 8; y++) {
+    const uint2 v = *reinterpret_cast<const uint2 *>(&cur_s[(by * 8 + y) * 64 + bx * 8]);
+    cur[y][0] = v.x; cur[y][1] = v.y;
+  }
+  uint32_t acc[8][4];
+  const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
+  uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
+  auto run = [&](auto nj_tag) {
+    constexpr int NJ = decltype(nj_tag)::value;
+    first_rows8<NJ>(p.skip, trow, cur, acc, stg);                 // the raw rows (overlaid on the ring) are dead by now
+    bar_arrive(kBarFull0, kWsThreads);
+    for (int m = 1; m < iters - 1; m++) {
+      const int b = m & 1;
+      if (m >= 2) bar_sync(kBarEmpty0 + b, kWsThreads);
+      rows8<1, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg + b * kRingEntries);
+      bar_arrive(kBarFull0 + b, kWsThreads);
+    }
+    if (iters > 1) {                                              // (a single iteration is complete after the first one)
+      const int m = iters - 1, b = m & 1;
+      if (m >= 2) bar_sync(kBarEmpty0 + b, kWsThreads);
+      rows8<2, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg + b * kRingEntries);
+      bar_arrive(kBarFull0 + b, kWsThreads);
+    }
+  };
+  if (nd == kChunkDx) run(std::integral_constant<int, 4>());
+  else run(std::integral_constant<int, 2>());
+}
+
 template <int R>
 __global__ void __launch_bounds__(kThreads, KVZ_SAD_MINB)
 ime_sad_dense_kernel(ImeSadParams p)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int tid = threadIdx.x;
-  const Geo geo(p.n_dy);
-  const int CW = geo.copy_words;
-  const int kChunks = p.n_chunks;
   const int n_ctu = R > 0 ? p.ctus_x * p.ctus_y : 0;
   if (R > 0 && (int)blockIdx.x < n_ctu) {
     if constexpr (R > 0) last_column<R>(p, smem_raw, blockIdx.x);
   } else {
     const int bid = blockIdx.x - n_ctu;
-    uint32_t *tile = reinterpret_cast<uint32_t *>(smem_raw);
-    uint8_t *cur_s = smem_raw + (size_t)4 * CW * 4;
-    uint16_t *stage = reinterpret_cast<uint16_t *>(cur_s + 64 * 64);
-    const int chunk = bid % kChunks, ctu = bid / kChunks;
-    const int ctu_x = p.tile_x + (ctu % p.ctus_x) * 64, ctu_y = p.tile_y + (ctu / p.ctus_x) * 64;
-    {
-      // tile rows ctu_y+y0 .., 84 bytes from column ctu_x+x0+16*chunk, as 4 byte-shifted copies
-      const uint8_t *src = p.ref + (size_t)(ctu_y + p.y0 + p.pad) * p.ref_pitch + (ctu_x + p.x0 + kChunkDx * chunk + p.pad);
-      const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
-      const int sh = (int)(a0 & 3) * 8;
-      const uint8_t *src_al = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)3);
-      // (1) raw rows (22 aligned words each) straight into shared memory, all copies in flight at once
-      uint32_t *raw = reinterpret_cast<uint32_t *>(stage);
-      for (int i = tid; i < geo.rows * kRawWords; i += kThreads) {
-        const int r = i / kRawWords, mw = i - r * kRawWords;
-        cp_async4(raw + i, src_al + (size_t)r * p.ref_pitch + 4 * mw);
-      }
-      stage_cur(p, cur_s, ctu_x, ctu_y, tid, kThreads);
-      cp_async_wait_all();
-      __syncthreads();
-      // (2) the four byte-shifted copies
-      for (int i = tid; i < geo.rows * kRowWords; i += kThreads) {
-        const int r = i / kRowWords, mw = i - r * kRowWords;
-        const uint32_t *w = raw + r * kRawWords + mw;
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-        const uint32_t t0 = __funnelshift_r(w0, w1, sh), t1 = __funnelshift_r(w1, w2, sh);
-        tile[0 * CW + i] = t0;
-        tile[1 * CW + i] = __funnelshift_r(t0, t1, 8);
-        tile[2 * CW + i] = __funnelshift_r(t0, t1, 16);
-        tile[3 * CW + i] = __funnelshift_r(t0, t1, 24);
-      }
-    }
-    __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31;
-    const int by = warp, bx = lane >> 2, g = lane & 3, blk = by * 8 + bx;
-    uint32_t cur[8][2];
-#pragma unroll
-    for (int y = 0; y < 8; y++) {
-      const uint2 v = *reinterpret_cast<const uint2 *>(&cur_s[(by * 8 + y) * 64 + bx * 8]);
-      cur[y][0] = v.x; cur[y][1] = v.y;
-    }
-    uint32_t acc[8][4];
-    const uint32_t *trow = tile + g * CW + (by * 8) * kRowWords + 2 * bx;
-    uint16_t *stg = stage + stage_slot(blk) * kChunkDx + g;
-    const WriterPos wp = writer_pos(p, ctu, chunk, tid);
-    const int nd = chunk == kChunks - 1 ? p.n_dx_last : kChunkDx;
-    auto run = [&](auto nj_tag) {
-      constexpr int NJ = decltype(nj_tag)::value;
-      switch (p.skip) {
-        case 0: rows8<0, 0, NJ>(trow, cur, acc, stg); break;
-        case 1: rows8<0, 1, NJ>(trow, cur, acc, stg); break;
-        case 2: rows8<0, 2, NJ>(trow, cur, acc, stg); break;
-        case 3: rows8<0, 3, NJ>(trow, cur, acc, stg); break;
-        case 4: rows8<0, 4, NJ>(trow, cur, acc, stg); break;
-        case 5: rows8<0, 5, NJ>(trow, cur, acc, stg); break;
-        case 6: rows8<0, 6, NJ>(trow, cur, acc, stg); break;
-        default: rows8<0, 7, NJ>(trow, cur, acc, stg); break;
-      }
-      __syncthreads();
-      if (p.skip == 0) write_rows(p, wp, stage, 0, tid, nd);
-      __syncthreads();
-      for (int m = 1; m < geo.iters - 1; m++) {
-        rows8<1, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg);
-        __syncthreads();
-        write_rows(p, wp, stage, m, tid, nd);
-        __syncthreads();
-      }
-      rows8<2, 0, NJ>(trow + (geo.iters - 1) * 8 * kRowWords, cur, acc, stg);
-      __syncthreads();
-      write_rows(p, wp, stage, geo.iters - 1, tid, nd);
-    };
-    if (nd == kChunkDx) run(std::integral_constant<int, 4>());
-    else run(std::integral_constant<int, 2>());
+    chunk_cta(p, smem_raw, bid / p.n_chunks, bid % p.n_chunks);
   }
+}
+
+// The box maps of SEVERAL references of one current picture in one launch: one grid instead of one per
+// reference removes the per-launch ramp and tail (8.6 waves each at 1080p), and the CTAs are ordered heavy
+// first -- the full 16-column chunks of every reference, then the 8-column remainders, which fill the tail.
+struct ImeSadMulti {
+  ImeSadParams p[kImeMaxMulti];
+  int full_end[kImeMaxMulti];     // cumulative CTA count after reference r
+  int n;
+};
+
+__global__ void __launch_bounds__(kWsThreads, 2)
+ime_sad_multi_kernel(const __grid_constant__ ImeSadMulti m)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int bid = blockIdx.x;
+  int r = 0;
+  while (bid >= m.full_end[r]) r++;
+  const int local = bid - (r ? m.full_end[r - 1] : 0);
+  const int ctu = local / m.p[r].n_chunks, chunk = local - ctu * m.p[r].n_chunks;
+  chunk_cta_ws(m.p[r], smem_raw, ctu, chunk);
 }
 
 // ---- replicate-pad a plane (image.c:320-452 == clamp-to-edge) ----
@@ -427,7 +576,7 @@ int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, 
 {
   p.x0 = center_x - range; p.y0 = center_y - range;
   p.n_dy = 2 * range + 1; p.n_chunks = range / 8; p.pu_rows = p.n_dy + 1;
-  p.skip = 0; p.n_dx_last = kChunkDx;
+  p.skip = 0; p.n_dx_last = kChunkDx; p.chunk_major = 0;
   switch (range) {
     case 8:  return launch_r<8>(p, stream);
     case 16: return launch_r<16>(p, stream);
@@ -437,14 +586,46 @@ int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, 
   }
 }
 
-int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream)
+static int box_geometry(ImeSadParams &p, int x0, int y0, int n_dx, int n_dy)
 {
   if (n_dx <= 0 || (n_dx & 7) || n_dy <= 0) return fail_msg("ime_sad_box: n_dx must be a positive multiple of 8, n_dy positive");
   // the kernel computes 8k + 1 rows; the surplus goes in front (alignment rows that are never written)
   p.skip = (8 - ((n_dy - 1) & 7)) & 7;
   p.x0 = x0; p.y0 = y0 - p.skip; p.n_dy = n_dy + p.skip; p.pu_rows = n_dy;
   p.n_chunks = (n_dx + 15) / 16; p.n_dx_last = n_dx - 16 * (p.n_chunks - 1);
+  p.chunk_major = 1;
+  return 1;
+}
+
+int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream)
+{
+  if (!box_geometry(p, x0, y0, n_dx, n_dy)) return 0;
   return launch_r<0>(p, stream);
+}
+
+int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream)
+{
+  if (n <= 0 || n > kImeMaxMulti) return fail_msg("ime_sad_box_multi: 1..8 references per launch");
+  ImeSadMulti m;
+  memset(&m, 0, sizeof(m));
+  m.n = n;
+  size_t smem = 0;
+  int total = 0;
+  for (int r = 0; r < n; r++) {
+    m.p[r] = ps[r];
+    if (!box_geometry(m.p[r], boxes[r][0], boxes[r][1], boxes[r][2], boxes[r][3])) return 0;
+    const size_t sb = ws_smem_bytes(Geo(m.p[r].n_dy));
+    if (sb > smem) smem = sb;
+    const int n_ctu = m.p[r].ctus_x * m.p[r].ctus_y;
+    total += n_ctu * m.p[r].n_chunks;
+    m.full_end[r] = total;
+  }
+  if (smem > 113 * 1024) return fail_msg("ime_sad: too many displacement rows for the shared-memory tile");
+  KVZ_CUDA_TRY(cudaFuncSetAttribute(ime_sad_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ime_sad_multi_kernel<<<total, kWsThreads, smem, stream>>>(m);
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
+  return 1;
 }
 
 }  // namespace kvz

@@ -20,11 +20,14 @@ struct ImeSadParams {
   int n_dx_last;           // columns of the last chunk: 16 or 8
   int pu_rows;             // map rows per PU: n_dy, or n_dy + 1 when row n_dy holds the column dx = x0 + 16*n_chunks
   int map_pitch;           // entries per map row
+  int chunk_major;         // box maps: map[chunk][pu][row][16 or 8] (see ime_sad.cu); 0: map[pu][row][map_pitch]
   uint16_t *sad8;          // [ctu*64 + by*8+bx][pu_rows][map_pitch]
   uint16_t *sad16;         // [ctu*16 + py*4+px][pu_rows][map_pitch]
   uint32_t *sad32;         // [ctu*4  + py*2+px][pu_rows][map_pitch]
   uint32_t *sad64;         // [ctu][pu_rows][map_pitch]
 };
+
+constexpr int kImeMaxMulti = 8;      // references per multi-reference launch
 
 int ime_map_pitch(int range);
 int launch_pad_plane(const void *src, int w, int h, int src_pitch, void *dst, int pad, int dst_pitch,
@@ -34,5 +37,8 @@ int launch_pad_plane(const void *src, int w, int h, int src_pitch, void *dst, in
 int launch_ime_sad_dense(ImeSadParams p, int range, int center_x, int center_y, cudaStream_t stream);
 // rectangular box: n_dx (multiple of 8) x n_dy displacements from (x0, y0), plain row-major maps
 int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaStream_t stream);
+
+// the boxes of n <= kImeMaxMulti references of one current picture in ONE launch; boxes[r] = {x0, y0, n_dx, n_dy}
+int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream);
 
 }  // namespace kvz

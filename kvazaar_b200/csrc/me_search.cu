@@ -528,25 +528,45 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     // Vectors of 8 entries in row-major order, 32 per step.  A lane streams its vectors through a ring in
     // shared memory with cp.async: kScanRing 16-byte pieces (8 vectors of uint16 entries, 4 of uint32) are
     // in flight per lane while one is priced -- the scan is bound by HBM latency, not by registers.
+    // Box maps are CHUNK-MAJOR (ime_sad.cu): map[chunk][pu][row][16], the last chunk 8 wide when n_dx is an odd
+    // multiple of 8.  Vector index i runs chunk by chunk, inside a chunk row-major (2 vectors per row, 1 in a half
+    // chunk): the vectors of a chunk are contiguous in memory.  The traversal order is free -- ties are settled
+    // by key, not by visiting order.
     const int total = n_dy * vpr;
-    const int srow = G / vpr, svec = G - srow * vpr;                // one step of 32 vectors in (row, vec)
-    int row = lane / vpr, vec = lane - row * vpr;
+    const int nch = (n_dx + 15) >> 4, last_vpc = (n_dx & 8) ? 1 : 2;
+    const int L = 2 * n_dy;                                         // vectors of a full chunk
+    const int pus_level = f.ctus_x * ((f.tile_h + 63) >> 6) * n * n;
     const bool wide = level >= 2;                                   // uint32 entries: two pieces per vector
-    const uint4 *mp = wide ? reinterpret_cast<const uint4 *>((level == 2 ? ms.sad32 : ms.sad64) + prow * (size_t)n_dy * n_dx)
-                           : reinterpret_cast<const uint4 *>((level == 0 ? ms.sad8 : ms.sad16) + prow * (size_t)n_dy * n_dx);
+    const uint4 *mp = wide ? reinterpret_cast<const uint4 *>(level == 2 ? ms.sad32 : ms.sad64)
+                           : reinterpret_cast<const uint4 *>(level == 0 ? ms.sad8 : ms.sad16);
     const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
-    auto issue = [&](int i, int slot) {
-      if (i < total) {
+    // cursor over the vectors of this lane: chunk c, index ic inside the chunk
+    struct Cursor { int c, ic; };
+    auto advance = [&](Cursor &k, int by) {
+      k.ic += by;
+      while (k.c < nch - 1 && k.ic >= L) { k.ic -= L; k.c++; }
+    };
+    auto vec_offset = [&](const Cursor &k) -> size_t {              // in vectors of 8 entries
+      const int vpc = k.c == nch - 1 ? last_vpc : 2;
+      return (size_t)k.c * 2 * pus_level * n_dy + (size_t)prow * n_dy * vpc + k.ic;
+    };
+    Cursor ci = { 0, 0 }, cc = { 0, 0 };                            // issue / consume
+    advance(ci, lane); advance(cc, lane);
+    int issued = lane;
+    auto issue = [&](int slot) {
+      if (issued < total) {
+        const size_t v = vec_offset(ci);
         if (wide) {
-          cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * i);
-          cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * i + 1);
+          cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * v);
+          cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * v + 1);
         } else {
-          cp_async16(&sm.ring[slot * 32 + lane], mp + i);
+          cp_async16(&sm.ring[slot * 32 + lane], mp + v);
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
+      issued += G; advance(ci, G);
     };
-    for (int t = 0; t < depth; t++) issue(lane + t * G, t);
+    for (int t = 0; t < depth; t++) issue(t);
     // Early rejection: the exact cost of a few likely candidates (the window centres and the two AMVP
     // predictors, where they are searched) bounds the minimum from above; a vector whose smallest SAD
     // already exceeds that bound (bit costs are >= 0) can hold neither the winner nor a tie with it.
@@ -560,7 +580,8 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
         const int col = sx - bx0, row = sy - by0;
         const uint32_t pos = ((uint32_t)row << 16) | (uint32_t)col;
         if (col >= 0 && col < n_dx && row >= 0 && row < n_dy && box_key(bc, pos) != 0xFFFFFFFFu) {
-          const size_t at = (prow * (size_t)n_dy + row) * n_dx + col;
+          const int sc = col >> 4, sw = (sc == nch - 1 && last_vpc == 1) ? 8 : 16;
+          const size_t at = (size_t)sc * 16 * pus_level * n_dy + (prow * (size_t)n_dy + row) * sw + (col - 16 * sc);
           const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + at) & 0xFFFFu
                                          : __ldg((level == 2 ? ms.sad32 : ms.sad64) + at);
           seed = box_price(bc, row, col, sad);
@@ -583,15 +604,15 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
         sad[0] = a.x & 0xFFFFu; sad[1] = a.x >> 16; sad[2] = a.y & 0xFFFFu; sad[3] = a.y >> 16;
         sad[4] = a.z & 0xFFFFu; sad[5] = a.z >> 16; sad[6] = a.w & 0xFFFFu; sad[7] = a.w >> 16;
       }
-      issue(i + depth * G, slot);                                   // the slot just read is free again
+      issue(slot);                                                  // the slot just read is free again
       slot = slot + 1 == depth ? 0 : slot + 1;
       const uint32_t smin = min(min(min(sad[0], sad[1]), min(sad[2], sad[3])), min(min(sad[4], sad[5]), min(sad[6], sad[7])));
       if (smin <= bound) {
-        price(row, vec, sad);
+        const bool half = cc.c == nch - 1 && last_vpc == 1;
+        price(half ? cc.ic : cc.ic >> 1, 2 * cc.c + (half ? 0 : (cc.ic & 1)), sad);
         bound = min(bound, wbest);
       }
-      row += srow; vec += svec;
-      if (vec >= vpr) { vec -= vpr; row++; }
+      advance(cc, G);
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | box_key(bc, wpos);

@@ -118,8 +118,9 @@ class ImeSearch:
 
 
 class ImeBoxSearch:
-    """Dense SAD maps over a rectangular box of displacements (kvz_cuda_ime_sad_box_maps):
-    map[level][pu][dy - y0][dx - x0], n_dx rounded up to a multiple of 8."""
+    """Dense SAD maps over a rectangular box of displacements (kvz_cuda_ime_sad_box_maps), n_dx rounded up to a
+    multiple of 8.  The device layout is CHUNK-MAJOR: map[level][chunk][pu][dy - y0][16] (a half last chunk is 8
+    wide); `maps[level]` is the flat buffer, `row_major(level)` reassembles [pu][dy - y0][dx - x0] for tests."""
 
     def __init__(self, width, height, box, tile=None, device="cuda"):
         capi.init(torch.cuda.current_device())
@@ -137,8 +138,21 @@ class ImeBoxSearch:
         for level in range(4):
             n = 8 >> level
             dt = torch.int16 if level < 2 else torch.int32
-            self.maps.append(torch.empty((n_ctu * n * n, n_dy, n_dx), dtype=dt, device=device))
+            self.maps.append(torch.empty(n_ctu * n * n * n_dy * n_dx, dtype=dt, device=device))
         self.desc = capi.ImeBoxDesc()
+
+    def row_major(self, level):
+        """host copy of one level as [pu][n_dy][n_dx] (numpy)"""
+        x0, y0, n_dx, n_dy = self.box
+        n = 8 >> level
+        pus = self.ctus_x * self.ctus_y * n * n
+        flat = self.maps[level].cpu().numpy()
+        parts, at = [], 0
+        for c0 in range(0, n_dx, 16):
+            w = min(16, n_dx - c0)
+            parts.append(flat[at:at + pus * n_dy * w].reshape(pus, n_dy, w))
+            at += pus * n_dy * w
+        return np.concatenate(parts, axis=2)
 
     pu_index = ImeSearch.pu_index
 
@@ -160,6 +174,27 @@ class ImeBoxSearch:
 
     def map_bytes(self):
         return sum(m.numel() * m.element_size() for m in self.maps)
+
+    def _fill_desc(self, d, cur, ref_padded):
+        d.width, d.height, d.bitdepth = self.width, self.height, 8
+        d.tile_x, d.tile_y, d.tile_w, d.tile_h = self.tile
+        d.cur_pitch = cur.stride(0) * cur.element_size()
+        d.ref_pitch, d.ref_pad = ref_padded.pitch_bytes, ref_padded.pad
+        d.x0, d.y0, d.n_dx, d.n_dy = self.box
+
+    @staticmethod
+    def run_many(searches, cur, refs_padded):
+        """kvz_cuda_ime_sad_box_maps_multi: the boxes of several references of one current picture in a
+        single launch (up to 8 per call)."""
+        for i0 in range(0, len(searches), capi.IME_MAX_MULTI):
+            grp = searches[i0:i0 + capi.IME_MAX_MULTI]
+            arr = (capi.ImeBoxRef * len(grp))()
+            for a, s, rp in zip(arr, grp, refs_padded[i0:i0 + capi.IME_MAX_MULTI]):
+                s._fill_desc(a.desc, cur, rp)
+                a.d_ref_padded = rp.data.data_ptr()
+                a.d_sad8, a.d_sad16, a.d_sad32, a.d_sad64 = (m.data_ptr() for m in s.maps)
+            capi.check(capi.lib().kvz_cuda_ime_sad_box_maps_multi(arr, len(grp), C.c_void_p(cur.data_ptr()), _stream_ptr()),
+                       "kvz_cuda_ime_sad_box_maps_multi")
 
 
 # numpy mirrors of the job structures of include/kvz_cuda.h

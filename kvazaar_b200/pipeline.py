@@ -91,6 +91,7 @@ class MePipeline:
         self.cur = torch.empty((height, width), dtype=torch.uint8, device=device)
         self.refs = [torch.empty((height, width), dtype=torch.uint8, device=device) for _ in range(n_refs)]
         self.use_boxes = use_boxes
+        self.multi_launch = True        # the boxes of all references in one launch (kvz_cuda_ime_sad_box_maps_multi)
         k = 2 * rng + 1
         n_pu = [(width // (8 << l)) * (height // (8 << l)) for l in range(4)]
         self.union_area = []
@@ -107,8 +108,8 @@ class MePipeline:
             pad = max(self.ime.pad, max(b.pad for b in self.boxes))
             self.padded = [PaddedPlane(width, height, pad, device=device) for _ in range(n_refs)]
             self.maps = [[(b.box, b.maps)] for b in self.boxes]
-            self.n_sad_launches = n_refs
-            sad_stage = ("ime_sad_box_maps x%d (one box per reference over the zero window and the frequent extra_mv / "
+            self.n_sad_launches = (n_refs + 7) // 8          # all references in one launch (up to 8 per launch)
+            sad_stage = ("ime_sad_box_maps_multi: %d boxes in one launch (one box per reference over the zero window and the frequent extra_mv / "
                          "merge windows: %s displacements)" % (n_refs, "+".join("%dx%d" % (b.box[2], b.box[3]) for b in self.boxes)))
         else:
             self.padded = [PaddedPlane(width, height, self.ime.pad, device=device) for _ in range(n_refs)]
@@ -153,6 +154,9 @@ class MePipeline:
 
     def sad_maps(self):
         """every dense SAD launch of one frame (planes already padded)"""
+        if self.use_boxes and self.multi_launch:
+            ImeBoxSearch.run_many(self.boxes, self.cur, self.padded)      # all references in one launch
+            return
         for r in range(self.n_refs):
             if self.use_boxes:
                 self.boxes[r].run(self.cur, self.padded[r])

@@ -124,8 +124,9 @@ def test_box_maps_small_frame(box):
     srch = kb.ImeBoxSearch(w, h, box)
     x0, y0, n_dx, n_dy = srch.box
     padded = kb.PaddedPlane(w, h, srch.pad).fill_from(torch.from_numpy(f[0]).cuda())
-    maps = [m.cpu().numpy() for m in srch.run(torch.from_numpy(f[1]).cuda(), padded)]
+    srch.run(torch.from_numpy(f[1]).cuda(), padded)
     torch.cuda.synchronize()
+    maps = [srch.row_major(level) for level in range(4)]
     rs = np.random.default_rng(3)
     for level in range(4):
         size = 8 << level
@@ -139,3 +140,30 @@ def test_box_maps_small_frame(box):
                 for j in range(n_dx):
                     want[i, j] = O.kvzo_image_sad_8(ptr(f[1]), ptr(f[0]), w, h, x, y, x + x0 + j, y + y0 + i, size, size)
             assert np.array_equal(got, want), (level, x, y)
+
+
+def test_box_maps_multi_equals_single():
+    """kvz_cuda_ime_sad_box_maps_multi (all references in one launch, heavy CTAs first) writes exactly the maps
+    of one kvz_cuda_ime_sad_box_maps call per reference: full and half last chunks, different n_dy per box."""
+    import torch
+    import kvazaar_b200 as kb
+    w, h = 328, 200                       # partial CTUs on both edges
+    f = kvzlibs.synth_luma(23, w, h, 6)
+    boxes = [(-8, -8, 32, 17), (-20, 3, 40, 25), (5, -30, 16, 41), (-9, -7, 24, 12), (-16, -5, 72, 19)]
+    cur = torch.from_numpy(f[5]).cuda()
+    single = [kb.ImeBoxSearch(w, h, b) for b in boxes]
+    multi = [kb.ImeBoxSearch(w, h, b) for b in boxes]
+    pad = max(s.pad for s in single)
+    padded = [kb.PaddedPlane(w, h, pad).fill_from(torch.from_numpy(f[r]).cuda()) for r in range(len(boxes))]
+    for s, p in zip(single, padded):
+        s.run(cur, p)
+    for s in multi:
+        for m in s.maps:
+            m.fill_(-1)
+    kb.ImeBoxSearch.run_many(multi, cur, padded)
+    torch.cuda.synchronize()
+    n_ctu = ((w + 63) // 64) * ((h + 63) // 64)
+    for r, (a, b) in enumerate(zip(single, multi)):
+        for level in range(4):
+            assert a.maps[level].numel() == n_ctu * (8 >> level) ** 2 * a.box[2] * a.box[3]
+            assert torch.equal(a.maps[level], b.maps[level]), (r, level)
