@@ -132,6 +132,7 @@ struct WriterPos {
   uint32_t src8;      // u16 index of the thread's 8 dx inside a ring slot
   uint32_t src16;     // u32 index of (first block of the 32x32 PU, dx pair) inside a ring slot
   uint32_t rs;        // entries between consecutive dy rows of a PU
+  uint32_t sx[4];     // u32 offset of block (i ^ swizzle) inside a group of four ring blocks, i = 0..3
 };
 
 // Two map layouts:
@@ -148,6 +149,8 @@ __device__ __forceinline__ WriterPos writer_pos(const ImeSadParams &p, int ctu, 
   const int lane = tid & 31, p32 = lane >> 3, dxp = lane & 7;
   w.src8 = stage_slot(blk) * kChunkDx + half * 8;
   w.src16 = ((p32 >> 1) * 32 + (p32 & 1) * 4) * (kChunkDx / 2) + dxp;
+#pragma unroll
+  for (int i = 0; i < 4; i++) w.sx[i] = (uint32_t)((i ^ p32) * (kChunkDx / 2));     // stage_slot() of the PU's blocks: low two bits ^ p32
   const uint32_t pu8 = (uint32_t)ctu * 64 + blk, pu16 = (uint32_t)ctu * 16 + (p32 >> 1) * 8 + (p32 & 1) * 2,
                  pu32 = (uint32_t)ctu * 4 + p32, pu64 = (uint32_t)ctu;
   if (p.chunk_major) {
@@ -196,15 +199,16 @@ __device__ __forceinline__ void write_rows(const ImeSadParams &p, const WriterPo
     const int k = k0 + u;
     if (k >= 0) {                                   // uniform per warp
       const uint32_t *st = reinterpret_cast<const uint32_t *>(stage) + u * (64 * kChunkDx / 2) + wp.src16;
-      const int sw = p32;                           // stage_slot() of the PU's blocks: low two bits ^ p32
       const bool wr = 2 * (tid & 7) < nd;           // this pair of displacement columns exists
       uint32_t lo = 0, hi = 0;
 #pragma unroll
       for (int q = 0; q < 4; q++) {
-        // 16x16 PU q of the 32x32 PU: blocks (2(q>>1), 2(q&1)) + {0,1}x{0,1}
+        // 16x16 PU q of the 32x32 PU: blocks (2(q>>1), 2(q&1)) + {0,1}x{0,1}; the swizzled low two bits of a
+        // block index come from wp.sx, the rest is an immediate offset
         const int b = (q >> 1) * 16 + (q & 1) * 2;
+        auto at = [&](int blk) { return st[(blk & ~3) * (kChunkDx / 2) + wp.sx[blk & 3]]; };
         // packed u16 pairs: 4 x 16320 < 65536, no carry between the halves
-        const uint32_t s16 = st[((b) ^ sw) * 8] + st[((b + 1) ^ sw) * 8] + st[((b + 8) ^ sw) * 8] + st[((b + 9) ^ sw) * 8];
+        const uint32_t s16 = at(b) + at(b + 1) + at(b + 8) + at(b + 9);
         if (wr) *reinterpret_cast<uint32_t *>(p.sad16 + wp.o16 + ((uint32_t)((q >> 1) * 4 + (q & 1)) * PR + (uint32_t)k) * rs) = s16;
         lo += s16 & 0xFFFFu;
         hi += s16 >> 16;
@@ -421,11 +425,15 @@ __device__ __forceinline__ void chunk_cta(const ImeSadParams &p, unsigned char *
 constexpr int kWriterThreads = KVZ_SAD_WRITERS;
 constexpr int kWsThreads = kThreads + kWriterThreads;
 constexpr int kRingEntries = 8 * 64 * kChunkDx;               // uint16 entries of one ring buffer
-enum { kBarCompute = 1, kBarFull0 = 2, kBarFull1 = 3, kBarEmpty0 = 4, kBarEmpty1 = 5 };
+#ifndef KVZ_SAD_RING
+#define KVZ_SAD_RING 2
+#endif
+constexpr int kRing = KVZ_SAD_RING;                           // ring buffers between compute and writer warps
+enum { kBarCompute = 1, kBarFull0 = 2, kBarEmpty0 = 2 + kRing };
 
 __host__ __device__ inline size_t ws_smem_bytes(const Geo &geo)
 {
-  const size_t raw = (size_t)geo.rows * kRawWords * 4, ring = (size_t)2 * kRingEntries * 2;
+  const size_t raw = (size_t)geo.rows * kRawWords * 4, ring = (size_t)kRing * kRingEntries * 2;
   return (size_t)4 * geo.copy_words * 4 + 64 * 64 + (raw > ring ? raw : ring);
 }
 
@@ -442,18 +450,17 @@ __device__ __forceinline__ void chunk_cta_ws(const ImeSadParams &p, unsigned cha
   if (tid >= kThreads) {
     // ---- writer warps: each thread stands in for four threads of the 256-thread writer layout ----
     const int wt = tid - kThreads;
-    for (int m = 0; m < iters; m++) {
-      const int b = m & 1;
+    constexpr int kV = kThreads / kWriterThreads;
+    WriterPos wp[kV];
+#pragma unroll
+    for (int v = 0; v < kV; v++) wp[v] = writer_pos(p, ctu, chunk, wt + v * kWriterThreads, nd);
+    for (int m = 0, b = 0; m < iters; m++, b = b + 1 == kRing ? 0 : b + 1) {
       bar_sync(kBarFull0 + b, kWsThreads);
       if (m > 0 || p.skip == 0) {
-#pragma unroll 1
-        for (int v = 0; v < kThreads / kWriterThreads; v++) {
-          const int vt = wt + v * kWriterThreads;
-          const WriterPos wp = writer_pos(p, ctu, chunk, vt, nd);
-          write_rows(p, wp, stage + b * kRingEntries, m, vt, nd);
-        }
+#pragma unroll
+        for (int v = 0; v < kV; v++) write_rows(p, wp[v], stage + b * kRingEntries, m, wt + v * kWriterThreads, nd);
       }
-      if (m + 2 < iters) bar_arrive(kBarEmpty0 + b, kWsThreads);
+      if (m + kRing < iters) bar_arrive(kBarEmpty0 + b, kWsThreads);
     }
     return;
   }
@@ -474,15 +481,16 @@ __device__ __forceinline__ void chunk_cta_ws(const ImeSadParams &p, unsigned cha
     constexpr int NJ = decltype(nj_tag)::value;
     first_rows8<NJ>(p.skip, trow, cur, acc, stg);                 // the raw rows (overlaid on the ring) are dead by now
     bar_arrive(kBarFull0, kWsThreads);
+    int b = kRing > 1 ? 1 : 0;
     for (int m = 1; m < iters - 1; m++) {
-      const int b = m & 1;
-      if (m >= 2) bar_sync(kBarEmpty0 + b, kWsThreads);
+      if (m >= kRing) bar_sync(kBarEmpty0 + b, kWsThreads);
       rows8<1, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg + b * kRingEntries);
       bar_arrive(kBarFull0 + b, kWsThreads);
+      b = b + 1 == kRing ? 0 : b + 1;
     }
     if (iters > 1) {                                              // (a single iteration is complete after the first one)
-      const int m = iters - 1, b = m & 1;
-      if (m >= 2) bar_sync(kBarEmpty0 + b, kWsThreads);
+      const int m = iters - 1;
+      if (m >= kRing) bar_sync(kBarEmpty0 + b, kWsThreads);
       rows8<2, 0, NJ>(trow + m * 8 * kRowWords, cur, acc, stg + b * kRingEntries);
       bar_arrive(kBarFull0 + b, kWsThreads);
     }

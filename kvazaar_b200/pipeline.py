@@ -72,10 +72,10 @@ def window_centres(pus, jobs, n_refs, max_sets=3):
 
 
 class MePipeline:
-    # dram__bytes_read.sum + dram__bytes_write.sum of the dense SAD launches of one step (the four box launches
-    # of the default 1080p / full32 / 4-reference workload), from profiles/r01d_prof_sad_summary.txt
-    # (ncu --set full): 431.5 + 472.8 + 494.3 + 626.1 MB
-    NCU_TRAFFIC_BYTES = 2024653000
+    # dram__bytes_read.sum + dram__bytes_write.sum of the dense SAD launch of one step (ime_sad_multi_kernel, the four
+    # boxes of the default 1080p / full32 / 4-reference workload), from profiles/r01e_prof_sad_summary.txt
+    # (ncu --set full): 17.9 MB read + 2082.6 MB written
+    NCU_TRAFFIC_BYTES = 2100454000
 
     def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda", use_boxes=True):
         """use_boxes: one box of displacements per reference that covers the zero window and the frequent

@@ -22,7 +22,7 @@ if [[ " $* " != *" noncu "* ]]; then
       --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
   echo "ncu list exit $?"
   timeout 300 $CMD > gpurun_out/plain2.log 2>&1 &&
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:ime_sad_dense -s 4 -c 4 \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:ime_sad_multi -s 4 -c 1 \
       -f -o gpurun_out/prof_sad $CMD > gpurun_out/ncu_full.log 2>&1
   echo "ncu full exit $?"
 fi
