@@ -234,7 +234,8 @@ class MeSearch:
     def set_current(self, cur):
         self.frame.d_cur = cur.data_ptr()
         self.frame.cur_pitch = cur.stride(0) * cur.element_size()
-        self._keep.append(cur)
+        if not any(k is cur for k in self._keep):
+            self._keep.append(cur)
 
     def set_refs(self, padded_planes, maps=None):
         """padded_planes: list of PaddedPlane; maps: per reference either the 4 zero-window map

@@ -172,6 +172,75 @@ class MePipeline:
         self.host_results.copy_(self.d_results, non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
+    # ---- the same step as a software pipeline over two input/result buffer sets ----
+    def _make_sets(self):
+        dev = self.cur.device
+        self._sets = []
+        for i in range(2):
+            st = {
+                "cur": self.cur if i == 0 else torch.empty_like(self.cur),
+                "refs": self.refs if i == 0 else [torch.empty_like(r) for r in self.refs],
+                "pus": self.d_pus if i == 0 else torch.empty_like(self.d_pus),
+                "jobs": self.d_jobs if i == 0 else torch.empty_like(self.d_jobs),
+                "res": self.d_results if i == 0 else torch.empty_like(self.d_results),
+                "host_res": self.host_results if i == 0 else torch.zeros_like(self.host_results).pin_memory(),
+                "uploaded": torch.cuda.Event(), "computed": torch.cuda.Event(), "downloaded": torch.cuda.Event(),
+                "used": False,
+            }
+            self._sets.append(st)
+        self._h2d, self._d2h = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        self._k = 0
+
+    def step_from_host_pipelined(self, host_cur, host_refs):
+        """One step from HOST buffers, overlapped with its neighbours: the inputs of step k are copied on an
+        H2D stream while step k-1 computes, its results come back on a D2H stream while step k+1 computes.
+        Every step still uploads all its inputs and downloads all its results; `flush_pipelined()` (or a device
+        synchronize) completes the last one.  Returns the host results of the step before this one, or None."""
+        if not hasattr(self, "_sets"):
+            self._make_sets()
+        st, prev = self._sets[self._k & 1], self._sets[(self._k & 1) ^ 1]
+        self._k += 1
+        comp = torch.cuda.current_stream()
+        with torch.cuda.stream(self._h2d):
+            if st["used"]:
+                self._h2d.wait_event(st["computed"])        # the set's previous step has finished reading it
+            st["cur"].copy_(host_cur, non_blocking=True)
+            for d, h in zip(st["refs"], host_refs):
+                d.copy_(h, non_blocking=True)
+            st["pus"].copy_(self.host_pus, non_blocking=True)
+            st["jobs"].copy_(self.host_jobs, non_blocking=True)
+            st["uploaded"].record(self._h2d)
+        comp.wait_event(st["uploaded"])
+        if st["used"]:
+            comp.wait_event(st["downloaded"])               # its previous results have left the device
+        for r in range(self.n_refs):
+            self.padded[r].fill_from(st["refs"][r])
+        if self.use_boxes and self.multi_launch:
+            ImeBoxSearch.run_many(self.boxes, st["cur"], self.padded)
+        else:
+            cur_saved, self.cur = self.cur, st["cur"]
+            self.sad_maps()
+            self.cur = cur_saved
+        self.search.set_current(st["cur"])
+        self.search.run(st["pus"], self.n_pus, st["jobs"], st["res"])
+        st["computed"].record(comp)
+        with torch.cuda.stream(self._d2h):
+            self._d2h.wait_event(st["computed"])
+            st["host_res"].copy_(st["res"], non_blocking=True)
+            st["downloaded"].record(self._d2h)
+        st["used"] = True
+        if prev["used"]:
+            prev["downloaded"].synchronize()
+            return prev["host_res"]
+        return None
+
+    def flush_pipelined(self):
+        """host results of the last pipelined step"""
+        st = self._sets[(self._k - 1) & 1]
+        st["downloaded"].synchronize()
+        self.search.set_current(self.cur)
+        return st["host_res"]
+
     def results(self):
         """kvz_cuda_me_result per job, as a numpy structured array (after step_from_host)"""
         return self.host_results.numpy().view(ME_RESULT_DT)

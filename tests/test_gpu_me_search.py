@@ -98,3 +98,29 @@ def test_box_map_sets_with_restrictions_and_ties():
         got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, 4, 20, box=(-16, -16, 48, 33), **kw)
         want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, 4, 20, **kw)
         me_oracle.assert_results_equal(got, want, pus)
+
+
+def test_pipelined_host_steps_equal_serial():
+    """MePipeline.step_from_host_pipelined (copies of neighbouring steps overlapped with the kernels, two buffer
+    sets) returns the results of MePipeline.step_from_host for every step, also when the inputs change per step."""
+    import torch
+    from kvazaar_b200.pipeline import MePipeline
+    w, h, n_refs = 416, 240, 2
+    f = kvzlibs.synth_luma(31, w, h, 6)
+    pipe = MePipeline(w, h, 16, n_refs)
+    steps = [(torch.from_numpy(f[k + 2]).pin_memory(), [torch.from_numpy(f[k + 1 - i]).pin_memory() for i in range(n_refs)])
+             for k in range(4)]
+    want = []
+    for cur, refs in steps:
+        pipe.step_from_host(cur, refs)
+        want.append(pipe.host_results.clone())
+    got = []
+    for cur, refs in steps:
+        r = pipe.step_from_host_pipelined(cur, refs)
+        if r is not None:
+            got.append(r.clone())
+    got.append(pipe.flush_pipelined().clone())
+    assert len(got) == len(want)
+    for k, (a, b) in enumerate(zip(got, want)):
+        assert torch.equal(a, b), k
+    assert not torch.equal(want[0], want[1])
