@@ -21,38 +21,49 @@ constexpr int P = 34;                 // int16 row pitch of a block in shared me
 __device__ __constant__ int32_t c_quant_scale[6] = { 26214, 23302, 20560, 18396, 16384, 14564 };   // scalinglist.c:66
 __device__ __constant__ int32_t c_inv_quant_scale[6] = { 40, 45, 51, 57, 64, 72 };                 // scalinglist.c:67
 
-struct BlockSmem {
-  int16_t a[32 * P];
-  int16_t b[32 * P];
-  int32_t delta[32 * 32];
-  TransformTables tt;
-  ScanTable scan;
+// what one thread group needs for a transform block of up to MAXN x MAXN: 13 KB for 32 (a CTA of kThreads
+// threads), 2.1 KB for 8 (one warp: blocks of 4x4 and 8x8 are processed one per WARP, four per CTA)
+template <int MAXN>
+struct BlockSmemT {
+  int16_t a[MAXN * P];
+  int16_t b[MAXN * P];
+  int32_t delta[MAXN * MAXN];
+  TransformTablesT<MAXN> tt;
+  ScanTableT<MAXN> scan;
   uint32_t acc;
   int last_cg;
+  int any;
 };
+using BlockSmem = BlockSmemT<32>;
+using SmallSmem = BlockSmemT<8>;
+constexpr int kSmallN = 8;            // largest block of the warp-per-block path
+constexpr int kWarps = kThreads / 32;
 
-__device__ void forward2d(BlockSmem &sm, int N, int bitdepth, int tid)
+template <int T, typename SM>
+__device__ void forward2d(SM &sm, int N, int bitdepth, int tid)
 {
   // a -> b -> a      (dct-generic.c:571-572)
   const int lg = ilog2_pow2(N);
-  fwd_pass_smem<P>(sm.tt, N, sm.a, sm.b, lg - 1 + (bitdepth - 8), tid, kThreads);
-  __syncthreads();
-  fwd_pass_smem<P>(sm.tt, N, sm.b, sm.a, lg + 6, tid, kThreads);
-  __syncthreads();
+  fwd_pass_smem<P>(sm.tt, N, sm.a, sm.b, lg - 1 + (bitdepth - 8), tid, T);
+  group_sync<T>();
+  fwd_pass_smem<P>(sm.tt, N, sm.b, sm.a, lg + 6, tid, T);
+  group_sync<T>();
 }
 
-__device__ void inverse2d(BlockSmem &sm, int N, int bitdepth, int tid)
+template <int T, typename SM>
+__device__ void inverse2d(SM &sm, int N, int bitdepth, int tid)
 {
   // a -> b -> a      (dct-generic.c:582-583)
-  inv_pass_smem<P>(sm.tt, N, sm.a, sm.b, 7, tid, kThreads);
-  __syncthreads();
-  inv_pass_smem<P>(sm.tt, N, sm.b, sm.a, 12 - (bitdepth - 8), tid, kThreads);
-  __syncthreads();
+  inv_pass_smem<P>(sm.tt, N, sm.a, sm.b, 7, tid, T);
+  group_sync<T>();
+  inv_pass_smem<P>(sm.tt, N, sm.b, sm.a, 12 - (bitdepth - 8), tid, T);
+  group_sync<T>();
 }
 
 // kvz_quant (quant-generic.c:37-163): coefficients in sm.a, levels to sm.b.
 // The scan table must have been built when cfg.signhide is set.
-__device__ void quant_block(BlockSmem &sm, const kvz_cuda_quant_cfg &c, int N, int type, int tid)
+template <int T, typename SM>
+__device__ void quant_block(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type, int tid)
 {
   const int lg = ilog2_pow2(N);
   const int qp_s = scaled_qp(type, c.qp, (c.bitdepth - 8) * 6);
@@ -60,9 +71,9 @@ __device__ void quant_block(BlockSmem &sm, const kvz_cuda_quant_cfg &c, int N, i
   const int q_bits = 14 + qp_s / 6 + (15 - c.bitdepth - lg);
   const int add = (c.slice_is_intra ? 171 : 85) << (q_bits - 9);
   if (tid == 0) { sm.acc = 0; sm.last_cg = -1; }
-  __syncthreads();
+  group_sync<T>();
   uint32_t my_sum = 0;
-  for (int i = tid; i < N * N; i += kThreads) {
+  for (int i = tid; i < N * N; i += T) {
     const int y = i / N, x = i - y * N;
     const int cf = sm.a[y * P + x];
     const long long prod = (long long)abs(cf) * qc;
@@ -75,20 +86,20 @@ __device__ void quant_block(BlockSmem &sm, const kvz_cuda_quant_cfg &c, int N, i
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) my_sum += __shfl_xor_sync(0xffffffffu, my_sum, o);
   if ((tid & 31) == 0) atomicAdd(&sm.acc, my_sum);
-  __syncthreads();
+  group_sync<T>();
   if (!c.signhide || sm.acc < 2) return;          // uniform
 
   // sign-bit hiding: one thread per 16-coefficient group (quant-generic.c:69-162)
   const int n_cg = (N * N) >> 4;
   auto q_at = [&](int pos) -> int16_t & { return sm.b[(pos / N) * P + (pos % N)]; };
   auto c_at = [&](int pos) -> int { return sm.a[(pos / N) * P + (pos % N)]; };
-  for (int g = tid; g < n_cg; g += kThreads) {
+  for (int g = tid; g < n_cg; g += T) {
     bool any = false;
     for (int n = 0; n < 16; n++) any |= q_at(sm.scan.pos[g * 16 + n]) != 0;
     if (any) atomicMax(&sm.last_cg, g);
   }
-  __syncthreads();
-  for (int g = tid; g < n_cg; g += kThreads) {
+  group_sync<T>();
+  for (int g = tid; g < n_cg; g += T) {
     const uint16_t *sc = sm.scan.pos + g * 16;
     int first = 16, last = -1, sum = 0;
     for (int n = 15; n >= 0; n--) if (q_at(sc[n])) { last = n; break; }
@@ -119,52 +130,91 @@ __device__ void quant_block(BlockSmem &sm, const kvz_cuda_quant_cfg &c, int N, i
     if (qq == 32767 || qq == -32768) change = -1;
     qq = (int16_t)(c_at(pos) >= 0 ? qq + change : qq - change);
   }
-  __syncthreads();
+  group_sync<T>();
 }
 
 // kvz_dequant (quant-generic.c:279-321, flat list): levels in sm.b -> coefficients in sm.a
-__device__ void dequant_block(BlockSmem &sm, const kvz_cuda_quant_cfg &c, int N, int type, int tid)
+template <int T, typename SM>
+__device__ void dequant_block(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type, int tid)
 {
   const int lg = ilog2_pow2(N);
   const int qp_s = scaled_qp(type, c.qp, (c.bitdepth - 8) * 6);
   const int shift = 20 - 14 - (15 - c.bitdepth - lg);
   const int scale = c_inv_quant_scale[qp_s % 6] << (qp_s / 6);
   const int add = 1 << (shift - 1);
-  for (int i = tid; i < N * N; i += kThreads) {
+  for (int i = tid; i < N * N; i += T) {
     const int y = i / N, x = i - y * N;
     const int v = ((int)sm.b[y * P + x] * scale + add) >> shift;
     sm.a[y * P + x] = (int16_t)clampi(v, -32768, 32767);
   }
-  __syncthreads();
+  group_sync<T>();
 }
 
+template <int T>
 __device__ __forceinline__ void load_block(int16_t *dst, const int16_t *src, int N, int tid)
 {
-  for (int i = tid; i < N * N; i += kThreads) dst[(i / N) * P + (i % N)] = src[i];
+  for (int i = tid; i < N * N; i += T) dst[(i / N) * P + (i % N)] = src[i];
 }
 
+template <int T>
 __device__ __forceinline__ void store_block(int16_t *dst, const int16_t *src, int N, int tid)
 {
-  for (int i = tid; i < N * N; i += kThreads) dst[i] = src[(i / N) * P + (i % N)];
+  for (int i = tid; i < N * N; i += T) dst[i] = src[(i / N) * P + (i % N)];
 }
 
 // ---- batch kernels ----
+// Blocks of 16x16 and 32x32 get the whole CTA (kThreads threads); blocks of 4x4 and 8x8 get one WARP each, four
+// per CTA, with a 2 KB shared-memory record per warp and warp barriers only -- a CTA per 16-sample block would
+// spend its time on barriers and idle lanes (measured: 129600 4x4 DCTs 0.24 ms with a CTA per block).
 
 __global__ void __launch_bounds__(kThreads)
 transform_batch_kernel(int N, int dst4, int inverse, int bitdepth, const int16_t *__restrict__ in,
                        int16_t *__restrict__ out, int count)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (N <= kSmallN) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    SmallSmem &sm = reinterpret_cast<SmallSmem *>(smem_raw)[warp];
+    load_transform_matrix(sm.tt, N, dst4 != 0, lane, 32);
+    for (int blk = blockIdx.x * kWarps + warp; blk < count; blk += gridDim.x * kWarps) {
+      __syncwarp();
+      load_block<32>(sm.a, in + (size_t)blk * N * N, N, lane);
+      __syncwarp();
+      if (inverse) inverse2d<32>(sm, N, bitdepth, lane);
+      else forward2d<32>(sm, N, bitdepth, lane);
+      store_block<32>(out + (size_t)blk * N * N, sm.a, N, lane);
+    }
+    return;
+  }
   BlockSmem &sm = *reinterpret_cast<BlockSmem *>(smem_raw);
   const int tid = threadIdx.x;
   load_transform_matrix(sm.tt, N, dst4 != 0, tid, kThreads);
   for (int blk = blockIdx.x; blk < count; blk += gridDim.x) {
     __syncthreads();
-    load_block(sm.a, in + (size_t)blk * N * N, N, tid);
+    load_block<kThreads>(sm.a, in + (size_t)blk * N * N, N, tid);
     __syncthreads();
-    if (inverse) inverse2d(sm, N, bitdepth, tid);
-    else forward2d(sm, N, bitdepth, tid);
-    store_block(out + (size_t)blk * N * N, sm.a, N, tid);
+    if (inverse) inverse2d<kThreads>(sm, N, bitdepth, tid);
+    else forward2d<kThreads>(sm, N, bitdepth, tid);
+    store_block<kThreads>(out + (size_t)blk * N * N, sm.a, N, tid);
+  }
+}
+
+template <int T, typename SM>
+__device__ __forceinline__ void quant_one(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type, int dequant,
+                                          const int16_t *in, int16_t *out, int tid)
+{
+  group_sync<T>();
+  if (dequant) {
+    load_block<T>(sm.b, in, N, tid);
+    group_sync<T>();
+    dequant_block<T>(sm, c, N, type, tid);
+    store_block<T>(out, sm.a, N, tid);
+  } else {
+    load_block<T>(sm.a, in, N, tid);
+    group_sync<T>();
+    quant_block<T>(sm, c, N, type, tid);
+    group_sync<T>();
+    store_block<T>(out, sm.b, N, tid);
   }
 }
 
@@ -173,24 +223,19 @@ quant_batch_kernel(kvz_cuda_quant_cfg c, int N, int type, int scan_idx, int dequ
                    int16_t *__restrict__ out, int count)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (N <= kSmallN) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    SmallSmem &sm = reinterpret_cast<SmallSmem *>(smem_raw)[warp];
+    if (!dequant && c.signhide) build_scan_table_t<32>(sm.scan, scan_idx, ilog2_pow2(N), lane);
+    for (int blk = blockIdx.x * kWarps + warp; blk < count; blk += gridDim.x * kWarps)
+      quant_one<32>(sm, c, N, type, dequant, in + (size_t)blk * N * N, out + (size_t)blk * N * N, lane);
+    return;
+  }
   BlockSmem &sm = *reinterpret_cast<BlockSmem *>(smem_raw);
   const int tid = threadIdx.x;
-  if (!dequant && c.signhide) build_scan_table(sm.scan, scan_idx, ilog2_pow2(N), tid, kThreads);
-  for (int blk = blockIdx.x; blk < count; blk += gridDim.x) {
-    __syncthreads();
-    if (dequant) {
-      load_block(sm.b, in + (size_t)blk * N * N, N, tid);
-      __syncthreads();
-      dequant_block(sm, c, N, type, tid);
-      store_block(out + (size_t)blk * N * N, sm.a, N, tid);
-    } else {
-      load_block(sm.a, in + (size_t)blk * N * N, N, tid);
-      __syncthreads();
-      quant_block(sm, c, N, type, tid);
-      __syncthreads();
-      store_block(out + (size_t)blk * N * N, sm.b, N, tid);
-    }
-  }
+  if (!dequant && c.signhide) build_scan_table_t<kThreads>(sm.scan, scan_idx, ilog2_pow2(N), tid);
+  for (int blk = blockIdx.x; blk < count; blk += gridDim.x)
+    quant_one<kThreads>(sm, c, N, type, dequant, in + (size_t)blk * N * N, out + (size_t)blk * N * N, tid);
 }
 
 __global__ void __launch_bounds__(256)
@@ -205,11 +250,102 @@ coeff_abs_sum_kernel(const int16_t *__restrict__ coeffs, int per_block, int coun
   if (lane == 0) out[blk] = s;
 }
 
-// kvz_quantize_residual (quant-generic.c:180-273), one CTA per transform block.
+// One kvz_quantize_residual call (quant-generic.c:180-273) by a group of T threads.
 // STAGE 0: the whole function with the scalar quantiser (cfg.rdoq_enable == 0).
 // With RDOQ the function is three launches around rdoq_kernel (rdoq.cu):
 // STAGE 1: residual -> transform, coefficients to `work` (4x4 blocks under cfg.rdoq_skip are quantised here,
 //          quant-generic.c:213-215); STAGE 2: levels from coeff_out -> dequant -> inverse -> reconstruction.
+template <int STAGE, int T, typename SM>
+__device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ pred,
+                             uint8_t *__restrict__ rec, int16_t *__restrict__ coeff_out, const kvz_cuda_residual_job &jb,
+                             uint8_t *has_coeff, int16_t *__restrict__ work, int rdoq_skip, int tid, int &tt_key,
+                             int &scan_key)
+{
+  const int N = jb.width, lg = ilog2_pow2(N);
+  const bool luma = jb.color == 0;
+  c.qp = jb.qp;
+  c.cu_is_intra = jb.cu_is_intra;
+  const bool dst4 = N == 4 && luma && jb.cu_is_intra;          // strategies-dct.c:59-113
+  group_sync<T>();                                             // the group's previous job is done with sm
+  // the transform matrix and the scan table stay in shared memory while consecutive jobs of the group use the same
+  if (!jb.use_trskip && tt_key != (N | (dst4 ? 64 : 0))) {
+    load_transform_matrix(sm.tt, N, dst4, tid, T);
+    tt_key = N | (dst4 ? 64 : 0);
+  }
+  const bool scalar_quant = STAGE == 0 || (STAGE == 1 && N == 4 && rdoq_skip);
+  if (c.signhide && scalar_quant && scan_key != (N | (jb.scan_idx << 8))) {
+    build_scan_table_t<T>(sm.scan, jb.scan_idx, lg, tid);
+    scan_key = N | (jb.scan_idx << 8);
+  }
+  if (tid == 0) sm.any = 0;
+  const uint8_t *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
+  const int ts_shift = 15 - c.bitdepth - lg;
+  int16_t *co = coeff_out + jb.coeff_offset;
+  if (STAGE != 2) {
+    for (int i = tid; i < N * N; i += T) {
+      const int y = i / N, x = i - y * N;
+      sm.a[y * P + x] = (int16_t)((int)rp[(size_t)y * jb.in_stride + x] - (int)pp[(size_t)y * jb.in_stride + x]);
+    }
+    group_sync<T>();
+    if (jb.use_trskip) {                                           // transform.c:151-161
+      for (int i = tid; i < N * N; i += T) {
+        int16_t &v = sm.a[(i / N) * P + (i % N)];
+        v = (int16_t)((int)v << ts_shift);
+      }
+      group_sync<T>();
+    } else {
+      forward2d<T>(sm, N, c.bitdepth, tid);
+    }
+    if (!scalar_quant) {                                           // STAGE 1: the coefficients go to rdoq_kernel
+      int16_t *wo = work + jb.coeff_offset;
+      for (int i = tid; i < N * N; i += T) wo[i] = sm.a[(i / N) * P + (i % N)];
+      return;
+    }
+    quant_block<T>(sm, c, N, luma ? 0 : 2, tid);
+    group_sync<T>();
+  } else {
+    for (int i = tid; i < N * N; i += T) sm.b[(i / N) * P + (i % N)] = co[i];
+    group_sync<T>();
+  }
+  int any = 0;
+  for (int i = tid; i < N * N; i += T) {
+    const int16_t q = sm.b[(i / N) * P + (i % N)];
+    if (STAGE != 2) co[i] = q;
+    any |= q != 0;
+  }
+  if (STAGE == 1) return;
+  if (any) sm.any = 1;
+  group_sync<T>();
+  uint8_t *op = rec + jb.rec_offset;
+  const int has = sm.any;
+  if (has) {
+    dequant_block<T>(sm, c, N, luma ? 0 : (jb.color == 1 ? 2 : 3), tid);
+    if (jb.use_trskip) {                                         // transform.c:169-181
+      const int off = 1 << (ts_shift - 1);
+      for (int i = tid; i < N * N; i += T) {
+        int16_t &v = sm.a[(i / N) * P + (i % N)];
+        v = (int16_t)(((int)v + off) >> ts_shift);
+      }
+      group_sync<T>();
+    } else {
+      inverse2d<T>(sm, N, c.bitdepth, tid);
+    }
+    const int pix_max = (1 << c.bitdepth) - 1;
+    for (int i = tid; i < N * N; i += T) {
+      const int y = i / N, x = i - y * N;
+      const int16_t val = (int16_t)((int)sm.a[y * P + x] + (int)pp[(size_t)y * jb.in_stride + x]);
+      op[(size_t)y * jb.out_stride + x] = (uint8_t)clampi(val, 0, pix_max);
+    }
+  } else {
+    for (int i = tid; i < N * N; i += T) {
+      const int y = i / N, x = i - y * N;
+      op[(size_t)y * jb.out_stride + x] = pp[(size_t)y * jb.in_stride + x];
+    }
+  }
+  if (tid == 0) *has_coeff = (uint8_t)has;
+}
+
+// a CTA takes kWarps consecutive jobs: one per warp when all of them are 4x4 / 8x8, else one after the other
 template <int STAGE>
 __global__ void __launch_bounds__(kThreads)
 quantize_residual_kernel(kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ pred,
@@ -218,83 +354,28 @@ quantize_residual_kernel(kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, 
                          int16_t *__restrict__ work, int rdoq_skip)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  BlockSmem &sm = *reinterpret_cast<BlockSmem *>(smem_raw);
-  __shared__ int s_any;
-  const int tid = threadIdx.x;
-  const kvz_cuda_residual_job jb = jobs[blockIdx.x];
-  const int N = jb.width, lg = ilog2_pow2(N);
-  const bool luma = jb.color == 0;
-  c.qp = jb.qp;
-  c.cu_is_intra = jb.cu_is_intra;
-  const bool dst4 = N == 4 && luma && jb.cu_is_intra;          // strategies-dct.c:59-113
-  if (!jb.use_trskip) load_transform_matrix(sm.tt, N, dst4, tid, kThreads);
-  const bool scalar_quant = STAGE == 0 || (STAGE == 1 && N == 4 && rdoq_skip);
-  if (c.signhide && scalar_quant) build_scan_table(sm.scan, jb.scan_idx, lg, tid, kThreads);
-  if (tid == 0) s_any = 0;
-  const uint8_t *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
-  const int ts_shift = 15 - c.bitdepth - lg;
-  int16_t *co = coeff_out + jb.coeff_offset;
-  if (STAGE != 2) {
-    for (int i = tid; i < N * N; i += kThreads) {
-      const int y = i / N, x = i - y * N;
-      sm.a[y * P + x] = (int16_t)((int)rp[(size_t)y * jb.in_stride + x] - (int)pp[(size_t)y * jb.in_stride + x]);
-    }
-    __syncthreads();
-    if (jb.use_trskip) {                                           // transform.c:151-161
-      for (int i = tid; i < N * N; i += kThreads) {
-        int16_t &v = sm.a[(i / N) * P + (i % N)];
-        v = (int16_t)((int)v << ts_shift);
+  int tt_small = -1, scan_small = -1, tt_big = -1, scan_big = -1;     // what the warp's / the CTA's tables hold
+  for (int j0 = blockIdx.x * kWarps; j0 < n_jobs; j0 += gridDim.x * kWarps) {
+    const int nj = min(kWarps, n_jobs - j0);
+    bool small = true;
+    for (int q = 0; q < nj; q++) small &= jobs[j0 + q].width <= kSmallN;
+    __syncthreads();                            // the two paths overlay the same shared memory
+    if (small) {
+      const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      tt_big = scan_big = -1;
+      if (warp < nj) {
+        SmallSmem &sm = reinterpret_cast<SmallSmem *>(smem_raw)[warp];
+        residual_job<STAGE, 32>(sm, c, ref, pred, rec, coeff_out, jobs[j0 + warp], has_coeffs + j0 + warp, work, rdoq_skip,
+                                lane, tt_small, scan_small);
       }
-      __syncthreads();
     } else {
-      forward2d(sm, N, c.bitdepth, tid);
-    }
-    if (!scalar_quant) {                                           // STAGE 1: the coefficients go to rdoq_kernel
-      int16_t *wo = work + jb.coeff_offset;
-      for (int i = tid; i < N * N; i += kThreads) wo[i] = sm.a[(i / N) * P + (i % N)];
-      return;
-    }
-    quant_block(sm, c, N, luma ? 0 : 2, tid);
-    __syncthreads();
-  } else {
-    for (int i = tid; i < N * N; i += kThreads) sm.b[(i / N) * P + (i % N)] = co[i];
-    __syncthreads();
-  }
-  int any = 0;
-  for (int i = tid; i < N * N; i += kThreads) {
-    const int16_t q = sm.b[(i / N) * P + (i % N)];
-    if (STAGE != 2) co[i] = q;
-    any |= q != 0;
-  }
-  if (STAGE == 1) return;
-  if (any) s_any = 1;
-  __syncthreads();
-  uint8_t *op = rec + jb.rec_offset;
-  if (s_any) {
-    dequant_block(sm, c, N, luma ? 0 : (jb.color == 1 ? 2 : 3), tid);
-    if (jb.use_trskip) {                                         // transform.c:169-181
-      const int off = 1 << (ts_shift - 1);
-      for (int i = tid; i < N * N; i += kThreads) {
-        int16_t &v = sm.a[(i / N) * P + (i % N)];
-        v = (int16_t)(((int)v + off) >> ts_shift);
-      }
-      __syncthreads();
-    } else {
-      inverse2d(sm, N, c.bitdepth, tid);
-    }
-    const int pix_max = (1 << c.bitdepth) - 1;
-    for (int i = tid; i < N * N; i += kThreads) {
-      const int y = i / N, x = i - y * N;
-      const int16_t val = (int16_t)((int)sm.a[y * P + x] + (int)pp[(size_t)y * jb.in_stride + x]);
-      op[(size_t)y * jb.out_stride + x] = (uint8_t)clampi(val, 0, pix_max);
-    }
-  } else {
-    for (int i = tid; i < N * N; i += kThreads) {
-      const int y = i / N, x = i - y * N;
-      op[(size_t)y * jb.out_stride + x] = pp[(size_t)y * jb.in_stride + x];
+      BlockSmem &sm = *reinterpret_cast<BlockSmem *>(smem_raw);
+      tt_small = scan_small = -1;
+      for (int q = 0; q < nj; q++)
+        residual_job<STAGE, kThreads>(sm, c, ref, pred, rec, coeff_out, jobs[j0 + q], has_coeffs + j0 + q, work, rdoq_skip,
+                                      threadIdx.x, tt_big, scan_big);
     }
   }
-  if (tid == 0) has_coeffs[blockIdx.x] = (uint8_t)s_any;
 }
 
 bool valid_n(int n) { return n == 4 || n == 8 || n == 16 || n == 32; }
@@ -306,6 +387,20 @@ static int sm_count()
 {
   if (!g_sms) { int d = 0; cudaGetDevice(&d); cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, d); }
   return g_sms;
+}
+
+// persistent CTAs: 4 per SM; a CTA serves kWarps blocks at a time when they are 4x4 / 8x8
+static int batch_grid(int n, int count)
+{
+  const int units = n <= kSmallN ? (count + kWarps - 1) / kWarps : count;
+  return units < sm_count() * 4 ? units : sm_count() * 4;
+}
+
+// persistent CTAs over groups of kWarps jobs, 8 per SM
+static int residual_grid(int n_jobs)
+{
+  const int groups = (n_jobs + kWarps - 1) / kWarps;
+  return groups < sm_count() * 8 ? groups : sm_count() * 8;
 }
 
 template <typename K>
@@ -321,7 +416,7 @@ int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int
   if (!valid_n(n) || (dst4 && n != 4)) return fail_msg("transform: n must be 4, 8, 16 or 32 (DST only for 4)");
   if (count <= 0) return 1;
   if (!opt_in_smem(transform_batch_kernel)) return 0;
-  const int grid = count < sm_count() * 4 ? count : sm_count() * 4;      // persistent CTAs, 4 per SM
+  const int grid = batch_grid(n, count);
   transform_batch_kernel<<<grid, kThreads, sizeof(BlockSmem), stream>>>(n, dst4, inverse, bitdepth, in, out, count);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
@@ -334,7 +429,7 @@ int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_id
   if (!valid_n(n)) return fail_msg("quant: n must be 4, 8, 16 or 32");
   if (count <= 0) return 1;
   if (!opt_in_smem(quant_batch_kernel)) return 0;
-  const int grid = count < sm_count() * 4 ? count : sm_count() * 4;
+  const int grid = batch_grid(n, count);
   quant_batch_kernel<<<grid, kThreads, sizeof(BlockSmem), stream>>>(c, n, type, scan_idx, dequant, in, out, count);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
@@ -355,7 +450,7 @@ int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const
 {
   if (n_jobs <= 0) return 1;
   if (!opt_in_smem(quantize_residual_kernel<0>)) return 0;
-  quantize_residual_kernel<0><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+  quantize_residual_kernel<0><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
       c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
@@ -374,12 +469,12 @@ int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, 
 {
   if (n_jobs <= 0) return 1;
   if (!opt_in_smem(quantize_residual_kernel<1>) || !opt_in_smem(quantize_residual_kernel<2>)) return 0;
-  quantize_residual_kernel<1><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+  quantize_residual_kernel<1><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
       c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   if (!launch_rdoq_batch(c, d_ctx, work, coeff, rdoq_jobs, n_jobs, max_width, rdoq_skip, stream)) return 0;
-  quantize_residual_kernel<2><<<n_jobs, kThreads, sizeof(BlockSmem), stream>>>(
+  quantize_residual_kernel<2><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
       c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();

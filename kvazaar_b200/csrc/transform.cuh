@@ -18,12 +18,22 @@ static __device__ __constant__ int8_t c_hevc_cos_q[33] = {
 static __device__ __constant__ int8_t c_dst4[4][4] = {           // dct-generic.c:26-32 (kvz_g_dst_4)
   { 29, 55, 74, 84 }, { 74, 74, 0, -74 }, { 84, -29, -74, 55 }, { 55, -84, 74, -29 } };
 
-struct TransformTables {
-  int16_t m[32 * 33];      // M_N[k][n] at m[k * 33 + n] for the N of this CTA (pitch 33: conflict-free columns)
+// A group of T threads working on one transform block: the whole CTA (T = blockDim.x) or one warp (T = 32)
+template <int T>
+__device__ __forceinline__ void group_sync()
+{
+  if (T == 32) __syncwarp(); else __syncthreads();
+}
+
+template <int MAXN>
+struct TransformTablesT {
+  int16_t m[MAXN * 33];    // M_N[k][n] at m[k * 33 + n] for the N of this group (pitch 33: conflict-free columns)
 };
+using TransformTables = TransformTablesT<32>;
 
 // fills t.m with the NxN matrix: M_N[k][n] = cos((32/N) k (2n+1) pi/64) scaled, or the 4x4 DST
-__device__ inline void load_transform_matrix(TransformTables &t, int N, bool dst4, int tid, int nthreads)
+template <typename TT>
+__device__ inline void load_transform_matrix(TT &t, int N, bool dst4, int tid, int nthreads)
 {
   for (int i = tid; i < N * N; i += nthreads) {
     const int k = i / N, n = i - k * N;
@@ -40,8 +50,8 @@ __device__ inline void load_transform_matrix(TransformTables &t, int N, bool dst
 
 // One forward pass over a block held in shared memory with row pitch P (int16):
 //   out[k * P + j] = (int16)((sum_n M[k][n] * in[j * P + n] + rnd) >> shift)      (dct-generic.c:258, 571-572)
-template <int P>
-__device__ __forceinline__ void fwd_pass_smem(const TransformTables &t, int N, const int16_t *in, int16_t *out, int shift,
+template <int P, typename TT>
+__device__ __forceinline__ void fwd_pass_smem(const TT &t, int N, const int16_t *in, int16_t *out, int shift,
                                               int tid, int nthreads)
 {
   const int rnd = 1 << (shift - 1);
@@ -54,8 +64,8 @@ __device__ __forceinline__ void fwd_pass_smem(const TransformTables &t, int N, c
 }
 
 // One inverse pass:  out[j * P + n] = clip16((sum_k M[k][n] * in[k * P + j] + rnd) >> shift)   (dct-generic.c:582-583)
-template <int P>
-__device__ __forceinline__ void inv_pass_smem(const TransformTables &t, int N, const int16_t *in, int16_t *out, int shift,
+template <int P, typename TT>
+__device__ __forceinline__ void inv_pass_smem(const TT &t, int N, const int16_t *in, int16_t *out, int shift,
                                               int tid, int nthreads)
 {
   const int rnd = 1 << (shift - 1);
@@ -86,10 +96,12 @@ __device__ inline int scaled_qp(int type, int qp, int qp_offset)
 // Scan tables of a (1 << lg)^2 block in shared memory: pos[i] = raster position of scan index i,
 // kvz_g_sig_last_scan[scan_idx][lg - 1] (tables.c): 4x4 coefficient groups, the groups and the
 // samples inside a group both in `scan_idx` order (0 up-right diagonal, 1 horizontal, 2 vertical).
-struct ScanTable {
-  uint16_t pos[32 * 32];
-  uint8_t gx[64], gy[64], px[16], py[16];
+template <int MAXN>
+struct ScanTableT {
+  uint16_t pos[MAXN * MAXN];
+  uint8_t gx[(MAXN / 4) * (MAXN / 4)], gy[(MAXN / 4) * (MAXN / 4)], px[16], py[16];
 };
+using ScanTable = ScanTableT<32>;
 
 __device__ inline void square_scan(int scan_idx, int n, uint8_t *xs, uint8_t *ys)
 {
@@ -104,18 +116,26 @@ __device__ inline void square_scan(int scan_idx, int n, uint8_t *xs, uint8_t *ys
   }
 }
 
-// all threads of the CTA call this; contains two barriers
-__device__ inline void build_scan_table(ScanTable &t, int scan_idx, int lg, int tid, int nthreads)
+// all T threads of the group call this; contains two group barriers
+template <int T, typename ST>
+__device__ inline void build_scan_table_t(ST &t, int scan_idx, int lg, int tid)
 {
   const int n = 1 << lg;
   if (tid == 0) square_scan(scan_idx, n >> 2, t.gx, t.gy);
-  if (tid == 32 % nthreads) square_scan(scan_idx, 4, t.px, t.py);
-  __syncthreads();
-  for (int i = tid; i < n * n; i += nthreads) {
+  if (tid == 32 % T) square_scan(scan_idx, 4, t.px, t.py);
+  group_sync<T>();
+  for (int i = tid; i < n * n; i += T) {
     const int g = i >> 4, k = i & 15;
     t.pos[i] = (uint16_t)((t.gy[g] * 4 + t.py[k]) * n + t.gx[g] * 4 + t.px[k]);
   }
-  __syncthreads();
+  group_sync<T>();
+}
+
+// CTA-wide form (nthreads == blockDim.x, 32 or 128)
+__device__ inline void build_scan_table(ScanTable &t, int scan_idx, int lg, int tid, int nthreads)
+{
+  if (nthreads == 32) build_scan_table_t<32>(t, scan_idx, lg, tid);
+  else build_scan_table_t<128>(t, scan_idx, lg, tid);
 }
 
 }  // namespace kvz

@@ -1,0 +1,85 @@
+"""Frame-scale device timings of the batch kernels beside the ME stage (rows A13-A17 of SURVEY.md 8a): one 1080p
+frame's worth of blocks per launch, CUDA events on the launching stream, inputs resident.  Prints one JSON object;
+bytes are the algorithmic bytes of DESIGN.md section 4."""
+import json, os, sys
+R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
+import numpy as np
+import torch
+import kvzlibs
+from kvazaar_b200 import blocks
+
+W, H = 1920, 1080
+f = kvzlibs.synth_luma(2, W, H, 2)
+d_src, d_pred = torch.from_numpy(f[1]).cuda(), torch.from_numpy(f[0]).cuda()
+rs = np.random.default_rng(1)
+try:
+    HBM = float(json.load(open(os.path.join(R, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+except Exception:
+    HBM = 6650.0
+
+
+def timed(fn, iters=10):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+out = {"frame": "1920x1080 8-bit, every aligned block of the size", "hbm_peak_gbs": HBM, "stages": {}}
+
+
+def put(name, ms, n_blocks, bytes_, note=""):
+    out["stages"][name] = {"blocks": n_blocks, "ms": round(ms, 4), "Mblocks_per_s": round(n_blocks / ms / 1e3, 1),
+                           "algorithmic_GB_per_s": round(bytes_ / ms / 1e6, 1), "frac_of_hbm": round(bytes_ / ms / 1e6 / HBM, 3), "note": note}
+
+
+for n in (4, 8, 16, 32):
+    cnt = (W // n) * (H // n)
+    resid = torch.from_numpy(rs.integers(-60, 61, cnt * n * n).astype(np.int16)).cuda()
+    put(f"dct{n}", timed(lambda: blocks.transform_blocks(resid, n)), cnt, cnt * n * n * 4)
+    coef = blocks.transform_blocks(resid, n)
+    put(f"idct{n}", timed(lambda: blocks.transform_blocks(coef, n, inverse=True)), cnt, cnt * n * n * 4)
+    put(f"quant{n}_signhide", timed(lambda: blocks.quant_blocks(coef, n, 32, signhide=True)), cnt, cnt * n * n * 4)
+    # fused residual coding: scalar quantiser and RDOQ
+    ys, xs = np.mgrid[0:H // n, 0:W // n]
+    off = (ys.reshape(-1) * n * W + xs.reshape(-1) * n).astype(np.uint32)
+    jobs = np.zeros(cnt, blocks.RESIDUAL_JOB_DT)
+    jobs["ref_offset"] = jobs["pred_offset"] = jobs["rec_offset"] = off
+    jobs["coeff_offset"] = np.arange(cnt, dtype=np.uint32) * n * n
+    jobs["in_stride"] = jobs["out_stride"] = W
+    jobs["width"], jobs["qp"], jobs["cu_is_intra"] = n, 32, 1
+    d_rec = torch.zeros((H, W), dtype=torch.uint8, device="cuda")
+    d_co = torch.zeros(cnt * n * n, dtype=torch.int16, device="cuda")
+    put(f"quantize_residual{n}", timed(lambda: blocks.quantize_residuals(d_src, d_pred, d_rec, d_co, jobs, True, True)), cnt,
+        cnt * n * n * 5, "residual -> T -> Q -> Q^-1 -> T^-1 -> recon, one launch")
+    rj = np.zeros(cnt, blocks.RDOQ_JOB_DT)
+    rj["coef_offset"] = jobs["coeff_offset"]; rj["ctx_index"] = np.arange(cnt) % 64; rj["lambda"] = 40.0
+    rj["width"], rj["qp"], rj["cu_is_intra"] = n, 32, 1
+    ctxs = np.frombuffer(rs.integers(0, 128, 64 * 148, dtype=np.uint8).tobytes(), blocks.RDOQ_CTX_DT).copy()
+    put(f"quantize_residual{n}_rdoq", timed(lambda: blocks.quantize_residuals_rdoq(d_src, d_pred, d_rec, d_co, jobs, ctxs, rj, True, True)),
+        cnt, cnt * n * n * 9, "transform | kvz_rdoq | reconstruction, three launches (latency-bound serial chain per block)")
+
+# intra: 35 predictions + SATD/SAD per PU
+for lg in (2, 3, 4, 5):
+    n = 1 << lg
+    cnt = (W // n) * (H // n)
+    refs = rs.integers(0, 256, cnt * 2 * (2 * n + 1), dtype=np.uint8)
+    ys, xs = np.mgrid[0:H // n, 0:W // n]
+    jobs = np.zeros(cnt, blocks.INTRA_JOB_DT)
+    jobs["ref_offset"] = np.arange(cnt, dtype=np.uint32) * 2 * (2 * n + 1)
+    jobs["orig_offset"] = (ys.reshape(-1) * n * W + xs.reshape(-1) * n).astype(np.uint32)
+    jobs["orig_stride"] = W
+    jobs["log2_width"], jobs["filter_boundary"] = lg, 1
+    jobs[jobs.dtype.names[-1]] = 1
+    d_refs = torch.from_numpy(refs).cuda()
+    ms = timed(lambda: blocks.intra_mode_costs(d_refs, d_src, jobs), 5)
+    out["stages"][f"intra_costs{n}"] = {"blocks": cnt, "ms": round(ms, 4), "Mblocks_per_s": round(cnt / ms / 1e3, 1),
+                                        "predicted_Gsamples_per_s": round(cnt * 35 * n * n / ms / 1e6, 1),
+                                        "note": "35 predictions + SATD + SAD per PU (ALU / latency bound)"}
+print(json.dumps(out))
