@@ -204,6 +204,8 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback on the hot path)")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     kb.init(local)
 
