@@ -124,7 +124,10 @@ __device__ __forceinline__ void make_ctx(JobCtx &j, const MeFrame &f, const kvz_
 }
 
 // fracmv_within_tile (search_inter.c:87-172); x,y quarter-pel
-__device__ __noinline__ bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
+#ifndef KVZ_WT_INLINE
+#define KVZ_WT_INLINE __noinline__
+#endif
+__device__ KVZ_WT_INLINE bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
 {
   const bool frac_luma = (x % 4 != 0) || (y % 4 != 0);
   const bool frac_chroma = (x % 8 != 0) || (y % 8 != 0);
@@ -287,6 +290,9 @@ __device__ __noinline__ uint32_t exact_cost(const WinCtx &w, int row, int col, u
   return sad + mvd;
 }
 
+#ifndef KVZ_BOX_INLINE
+#define KVZ_BOX_INLINE __forceinline__
+#endif
 // union scan of a box: what the rare paths need
 struct BoxCtx {
   const MeFrame *f;
@@ -299,7 +305,7 @@ struct BoxCtx {
 };
 
 // exact cost of the box entry (row, col): tile restriction and merge override included; ~0u if excluded
-__device__ __noinline__ uint32_t box_price(const BoxCtx &b, int row, int col, uint32_t sad)
+__device__ KVZ_BOX_INLINE uint32_t box_price(const BoxCtx &b, int row, int col, uint32_t sad)
 {
   const int dx = b.bx0 + col, dy = b.by0 + row;
   if (!b.free_mv && !within_tile(*b.f, *b.j, dx * 4, dy * 4)) return 0xFFFFFFFFu;
@@ -311,7 +317,7 @@ __device__ __noinline__ uint32_t box_price(const BoxCtx &b, int row, int col, ui
 }
 
 // (first covering window << 16) | position inside that window, of the box entry pos = row << 16 | col
-__device__ __noinline__ uint32_t box_key(const BoxCtx &b, uint32_t pos)
+__device__ KVZ_BOX_INLINE uint32_t box_key(const BoxCtx &b, uint32_t pos)
 {
   const int dx = b.bx0 + (int)(pos & 0xFFFFu), dy = b.by0 + (int)(pos >> 16);
   for (int w = 0; w < b.nwin; w++)
@@ -321,7 +327,7 @@ __device__ __noinline__ uint32_t box_key(const BoxCtx &b, uint32_t pos)
 }
 
 // two box entries of equal cost: the one search_mv_full meets first
-__device__ __noinline__ uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint32_t pos_b)
+__device__ KVZ_BOX_INLINE uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint32_t pos_b)
 {
   return box_key(b, pos_b) < box_key(b, pos_a) ? pos_b : pos_a;
 }
