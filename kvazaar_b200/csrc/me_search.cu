@@ -546,22 +546,25 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     const uint4 *mp = wide ? reinterpret_cast<const uint4 *>(level == 2 ? ms.sad32 : ms.sad64)
                            : reinterpret_cast<const uint4 *>(level == 0 ? ms.sad8 : ms.sad16);
     const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
-    // cursor over the vectors of this lane: chunk c, index ic inside the chunk
-    struct Cursor { int c, ic; };
+    // cursor over the vectors of this lane: chunk c, index ic inside the chunk, off = position in the map (in
+    // vectors of 8 entries): off advances with ic and jumps to the next chunk's run when ic passes L
+    struct Cursor { int c, ic; size_t off; };
+    const size_t chunk_stride = (size_t)2 * pus_level * n_dy;      // vectors of a full chunk, all PUs
+    const size_t pu_run = (size_t)prow * n_dy;                     // this PU's run inside a chunk starts at pu_run * vpc
     auto advance = [&](Cursor &k, int by) {
-      k.ic += by;
-      while (k.c < nch - 1 && k.ic >= L) { k.ic -= L; k.c++; }
+      k.ic += by; k.off += by;
+      while (k.c < nch - 1 && k.ic >= L) {
+        k.ic -= L; k.c++;
+        k.off += chunk_stride - L;
+        if (k.c == nch - 1 && last_vpc == 1) k.off -= pu_run;      // a half chunk has one vector per row
+      }
     };
-    auto vec_offset = [&](const Cursor &k) -> size_t {              // in vectors of 8 entries
-      const int vpc = k.c == nch - 1 ? last_vpc : 2;
-      return (size_t)k.c * 2 * pus_level * n_dy + (size_t)prow * n_dy * vpc + k.ic;
-    };
-    Cursor ci = { 0, 0 }, cc = { 0, 0 };                            // issue / consume
+    Cursor ci = { 0, 0, pu_run * (nch == 1 ? last_vpc : 2) }, cc = ci;      // issue / consume
     advance(ci, lane); advance(cc, lane);
     int issued = lane;
     auto issue = [&](int slot) {
       if (issued < total) {
-        const size_t v = vec_offset(ci);
+        const size_t v = ci.off;
         if (wide) {
           cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * v);
           cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * v + 1);
