@@ -119,7 +119,12 @@ KVZ_CUDA_API int kvz_cuda_ime_sad_maps(const kvz_cuda_ime_desc *d,
 /* The same for a rectangular box of displacements, dx in [x0, x0+n_dx), dy in [y0, y0+n_dy): one box that
  * covers all the windows search_mv_full visits for a reference (zero window, extra_mv window, merge-candidate
  * windows; search_inter.c:891-955) computes every displacement once, where separate windows overlap.
- *   map[level][p][dy - y0][dx - x0],  rows n_dx entries apart (plain row-major, no extra row).
+ * The maps are CHUNK-MAJOR: a chunk is 16 displacement columns (the last one 8 when n_dx is an odd multiple
+ * of 8), and with P = PUs of the level, w_c = width of chunk c:
+ *   entry (p, dy, dx) of a level lives at   16 * c * P * n_dy + (p * n_dy + (dy - y0)) * w_c + ((dx - x0) - 16 * c),
+ *   c = (dx - x0) / 16   -- i.e. map[chunk][p][dy - y0][w_c]; each map holds exactly P * n_dy * n_dx entries.
+ * (One CTA computes one (CTU, chunk): its output is one contiguous run per level; kvz_cuda_me_search reads a
+ * PU's map as n_chunks contiguous runs.)
  * n_dx must be a multiple of 8 (round the box up: entries no window covers are ignored by
  * kvz_cuda_me_search), n_dy is free; both at most 272.
  * ref_pad must be >= 104 + max(|x0|, |x0+n_dx|, |y0|, |y0+n_dy|). */
@@ -246,7 +251,8 @@ enum kvz_cuda_cost_kind {
 };
 
 typedef struct kvz_cuda_block_job {
-  uint32_t a_offset, b_offset;  /* byte offsets of the two blocks in the buffers d_a, d_b */
+  uint32_t a_offset, b_offset;  /* offsets of the two blocks in the buffers d_a, d_b, in SAMPLES (bytes at 8 bits;
+                                   at bitdepth 10 the buffers hold uint16_t samples and strides count samples too) */
   int32_t a_stride, b_stride;   /* samples per row */
   int16_t w, h;
   int32_t kind;                 /* enum kvz_cuda_cost_kind */

@@ -37,15 +37,16 @@ __device__ uint32_t warp_satd_any(const FA &a, const FB &b, int w, int h, int la
   return s;
 }
 
+template <typename PIX>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-block_cost_kernel(const uint8_t *__restrict__ base_a, const uint8_t *__restrict__ base_b,
+block_cost_kernel(const PIX *__restrict__ base_a, const PIX *__restrict__ base_b,
                   const kvz_cuda_block_job *__restrict__ jobs, int n_jobs, int bitdepth, uint32_t *__restrict__ out)
 {
   const int ji = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (ji >= n_jobs) return;
   const kvz_cuda_block_job jb = jobs[ji];
-  const StridedBlock a{ base_a + jb.a_offset, jb.a_stride }, b{ base_b + jb.b_offset, jb.b_stride };
+  const StridedBlockT<PIX> a{ base_a + jb.a_offset, jb.a_stride }, b{ base_b + jb.b_offset, jb.b_stride };
   const int sh = bitdepth - 8;
   uint32_t r = 0;
   switch (jb.kind) {
@@ -62,8 +63,9 @@ block_cost_kernel(const uint8_t *__restrict__ base_a, const uint8_t *__restrict_
   if (lane == 0) out[ji] = r;
 }
 
+template <typename PIX>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-image_cost_kernel(const uint8_t *__restrict__ pic, int pic_pitch, const uint8_t *__restrict__ ref, int ref_pitch,
+image_cost_kernel(const PIX *__restrict__ pic, int pic_pitch, const PIX *__restrict__ ref, int ref_pitch,
                   int width, int height, const kvz_cuda_image_cost_job *__restrict__ jobs, int n_jobs,
                   int bitdepth, uint32_t *__restrict__ out)
 {
@@ -71,8 +73,8 @@ image_cost_kernel(const uint8_t *__restrict__ pic, int pic_pitch, const uint8_t 
   const int lane = threadIdx.x & 31;
   if (ji >= n_jobs) return;
   const kvz_cuda_image_cost_job jb = jobs[ji];
-  const StridedBlock a{ pic + (size_t)jb.pic_y * pic_pitch + jb.pic_x, pic_pitch };
-  const ClampedPlane b{ ref, ref_pitch, width, height, jb.ref_x, jb.ref_y };
+  const StridedBlockT<PIX> a{ pic + (size_t)jb.pic_y * pic_pitch + jb.pic_x, pic_pitch };
+  const ClampedPlaneT<PIX> b{ ref, ref_pitch, width, height, jb.ref_x, jb.ref_y };
   const int sh = bitdepth - 8;
   uint32_t r;
   if (jb.kind == KVZ_CUDA_IMAGE_SAD) r = warp_sad(a, b, jb.w, jb.h, lane) >> sh;                 // image.c:474-477
@@ -86,8 +88,13 @@ int launch_block_cost(const void *base_a, const void *base_b, const kvz_cuda_blo
                       int bitdepth, uint32_t *out, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  block_cost_kernel<<<(n_jobs + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, stream>>>(
-      (const uint8_t *)base_a, (const uint8_t *)base_b, jobs, n_jobs, bitdepth, out);
+  const int grid = (n_jobs + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (bitdepth == 8)
+    block_cost_kernel<uint8_t><<<grid, kWarpsPerCta * 32, 0, stream>>>((const uint8_t *)base_a, (const uint8_t *)base_b, jobs,
+                                                                       n_jobs, bitdepth, out);
+  else   // 10-bit build: uint16_t samples, offsets and strides in samples
+    block_cost_kernel<uint16_t><<<grid, kWarpsPerCta * 32, 0, stream>>>((const uint16_t *)base_a, (const uint16_t *)base_b, jobs,
+                                                                        n_jobs, bitdepth, out);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
@@ -97,8 +104,13 @@ int launch_image_cost(const void *pic, int pic_pitch, const void *ref, int ref_p
                       const kvz_cuda_image_cost_job *jobs, int n_jobs, int bitdepth, uint32_t *out, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  image_cost_kernel<<<(n_jobs + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, stream>>>(
-      (const uint8_t *)pic, pic_pitch, (const uint8_t *)ref, ref_pitch, width, height, jobs, n_jobs, bitdepth, out);
+  const int grid = (n_jobs + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (bitdepth == 8)
+    image_cost_kernel<uint8_t><<<grid, kWarpsPerCta * 32, 0, stream>>>((const uint8_t *)pic, pic_pitch, (const uint8_t *)ref,
+                                                                       ref_pitch, width, height, jobs, n_jobs, bitdepth, out);
+  else   // pitches in samples
+    image_cost_kernel<uint16_t><<<grid, kWarpsPerCta * 32, 0, stream>>>((const uint16_t *)pic, pic_pitch, (const uint16_t *)ref,
+                                                                        ref_pitch, width, height, jobs, n_jobs, bitdepth, out);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

@@ -191,7 +191,7 @@ static int box_params(const kvz_cuda_ime_box_desc *d, const void *d_cur, const v
 {
   if (!d || !d_cur || !d_ref_padded || !d_sad8 || !d_sad16 || !d_sad32 || !d_sad64)
     return fail_msg("kvz_cuda_ime_sad_box_maps: null argument");
-  if (d->bitdepth != 8) return fail_msg("kvz_cuda_ime_sad_box_maps: only bitdepth 8 is implemented");
+  if (d->bitdepth != 8 && d->bitdepth != 10) return fail_msg("kvz_cuda_ime_sad_box_maps: bitdepth must be 8 or 10");
   if (d->n_dx <= 0 || (d->n_dx & 7) || d->n_dy <= 0 || d->n_dx > kMeMaxBox || d->n_dy > kMeMaxBox)
     return fail_msg("kvz_cuda_ime_sad_box_maps: n_dx must be a multiple of 8; both sides 1..272");
   {
@@ -221,6 +221,7 @@ int kvz_cuda_ime_sad_box_maps(const kvz_cuda_ime_box_desc *d, const void *d_cur,
 {
   ImeSadParams p;
   if (!box_params(d, d_cur, d_ref_padded, d_sad8, d_sad16, d_sad32, d_sad64, p)) return 0;
+  if (d->bitdepth != 8) return launch_ime_sad10_box(p, d->x0, d->y0, d->n_dx, d->n_dy, d->bitdepth, (cudaStream_t)stream);
   return launch_ime_sad_box(p, d->x0, d->y0, d->n_dx, d->n_dy, (cudaStream_t)stream);
 }
 
@@ -234,6 +235,12 @@ int kvz_cuda_ime_sad_box_maps_multi(const kvz_cuda_ime_box_ref *refs, int n_refs
     const kvz_cuda_ime_box_ref &b = refs[r];
     if (!box_params(&b.desc, d_cur, b.d_ref_padded, b.d_sad8, b.d_sad16, b.d_sad32, b.d_sad64, ps[r])) return 0;
     boxes[r][0] = b.desc.x0; boxes[r][1] = b.desc.y0; boxes[r][2] = b.desc.n_dx; boxes[r][3] = b.desc.n_dy;
+  }
+  if (refs[0].desc.bitdepth != 8) {                 // 10-bit: one launch per reference (ime_sad10.cu)
+    for (int r = 0; r < n_refs; r++)
+      if (!launch_ime_sad10_box(ps[r], boxes[r][0], boxes[r][1], boxes[r][2], boxes[r][3], refs[r].desc.bitdepth,
+                                (cudaStream_t)stream)) return 0;
+    return 1;
   }
   return launch_ime_sad_box_multi(ps, boxes, n_refs, (cudaStream_t)stream);
 }
@@ -283,7 +290,7 @@ int kvz_cuda_block_costs(const void *d_a, const void *d_b, const kvz_cuda_block_
                          int bitdepth, uint32_t *d_out, void *stream)
 {
   if (!d_a || !d_b || !d_jobs || !d_out || n_jobs < 0) return fail_msg("kvz_cuda_block_costs: bad argument");
-  if (bitdepth != 8) return fail_msg("kvz_cuda_block_costs: only bitdepth 8 is implemented");
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_block_costs: bitdepth must be 8 or 10");
   return launch_block_cost(d_a, d_b, d_jobs, n_jobs, bitdepth, d_out, (cudaStream_t)stream);
 }
 
@@ -292,7 +299,7 @@ int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const void *d_ref, in
 {
   if (!d_pic || !d_ref || !d_jobs || !d_out || n_jobs < 0 || width <= 0 || height <= 0)
     return fail_msg("kvz_cuda_image_costs: bad argument");
-  if (bitdepth != 8) return fail_msg("kvz_cuda_image_costs: only bitdepth 8 is implemented");
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_image_costs: bitdepth must be 8 or 10");
   return launch_image_cost(d_pic, pic_pitch, d_ref, ref_pitch, width, height, d_jobs, n_jobs, bitdepth, d_out,
                            (cudaStream_t)stream);
 }

@@ -83,20 +83,25 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v)
 }
 
 // pixel fetchers: plain strided block, or plane with the coordinate clamped into it
-struct StridedBlock {
-  const uint8_t *p;
+// (PIX = uint8_t for the 8-bit build of the reference, uint16_t for KVZ_BIT_DEPTH 10; strides in samples)
+template <typename PIX>
+struct StridedBlockT {
+  const PIX *p;
   int stride;
   __device__ __forceinline__ int operator()(int x, int y) const { return p[(size_t)y * stride + x]; }
 };
+using StridedBlock = StridedBlockT<uint8_t>;
 
-struct ClampedPlane {
-  const uint8_t *p;
+template <typename PIX>
+struct ClampedPlaneT {
+  const PIX *p;
   int pitch, w, h, x0, y0;
   __device__ __forceinline__ int operator()(int x, int y) const
   {
     return p[(size_t)clampi(y0 + y, 0, h - 1) * pitch + clampi(x0 + x, 0, w - 1)];
   }
 };
+using ClampedPlane = ClampedPlaneT<uint8_t>;
 
 template <typename FA, typename FB>
 __device__ inline uint32_t warp_sad(const FA &a, const FB &b, int w, int h, int lane)

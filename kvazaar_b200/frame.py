@@ -122,9 +122,9 @@ class ImeBoxSearch:
     multiple of 8.  The device layout is CHUNK-MAJOR: map[level][chunk][pu][dy - y0][16] (a half last chunk is 8
     wide); `maps[level]` is the flat buffer, `row_major(level)` reassembles [pu][dy - y0][dx - x0] for tests."""
 
-    def __init__(self, width, height, box, tile=None, device="cuda"):
+    def __init__(self, width, height, box, tile=None, device="cuda", bitdepth=8):
         capi.init(torch.cuda.current_device())
-        self.width, self.height = width, height
+        self.width, self.height, self.bitdepth = width, height, bitdepth
         self.tile = tile or (0, 0, width, height)
         x0, y0, n_dx, n_dy = box
         n_dx = (n_dx + 7) & ~7
@@ -160,11 +160,7 @@ class ImeBoxSearch:
         if maps is not None:
             self.maps = maps
         d = self.desc
-        d.width, d.height, d.bitdepth = self.width, self.height, 8
-        d.tile_x, d.tile_y, d.tile_w, d.tile_h = self.tile
-        d.cur_pitch = cur.stride(0) * cur.element_size()
-        d.ref_pitch, d.ref_pad = ref_padded.pitch_bytes, ref_padded.pad
-        d.x0, d.y0, d.n_dx, d.n_dy = self.box
+        self._fill_desc(d, cur, ref_padded)
         capi.check(capi.lib().kvz_cuda_ime_sad_box_maps(
             C.byref(d), C.c_void_p(cur.data_ptr()), C.c_void_p(ref_padded.data.data_ptr()),
             C.c_void_p(self.maps[0].data_ptr()), C.c_void_p(self.maps[1].data_ptr()),
@@ -176,7 +172,7 @@ class ImeBoxSearch:
         return sum(m.numel() * m.element_size() for m in self.maps)
 
     def _fill_desc(self, d, cur, ref_padded):
-        d.width, d.height, d.bitdepth = self.width, self.height, 8
+        d.width, d.height, d.bitdepth = self.width, self.height, self.bitdepth
         d.tile_x, d.tile_y, d.tile_w, d.tile_h = self.tile
         d.cur_pitch = cur.stride(0) * cur.element_size()
         d.ref_pitch, d.ref_pad = ref_padded.pitch_bytes, ref_padded.pad

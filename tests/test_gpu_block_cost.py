@@ -124,3 +124,62 @@ def test_image_costs_vs_oracle_1080p():
     got = blocks.image_costs(torch.from_numpy(pic).cuda(), torch.from_numpy(ref).cuda(),
                              np.array(rows, blocks.IMAGE_JOB_DT)).cpu().numpy().astype(np.uint32)
     assert got.tolist() == want
+
+
+def test_10bit_blocks_and_image_costs_vs_oracle():
+    """bitdepth 10 (uint16 samples, KVZ_BIT_DEPTH=10 build of the reference): block costs incl. the >> (BD-8)
+    of the NxN / any-size / SSD flavours, and the clamped picture-level SAD / SATD (shifted twice, image.c:507-512)"""
+    import torch
+    from kvazaar_b200 import blocks
+    O = kvzlibs.oracle()
+    rs = np.random.default_rng(10)
+    a = rs.integers(0, 1024, (80, 96), dtype=np.uint16)
+    b = rs.integers(0, 1024, (72, 112), dtype=np.uint16)
+    a[:8, :8], b[:8, :8] = 0, 1023                                  # extremes: 0 vs PIXEL_MAX
+    shapes = [(8, 8), (16, 16), (32, 32), (64, 64), (16, 8), (64, 32), (12, 16), (4, 8), (24, 32), (4, 4), (48, 64)]
+    jobs, want = [], []
+    for (w, h) in shapes:
+        for kind in (blocks.COST_REG_SAD, blocks.COST_SATD_ANY, blocks.COST_SSD):
+            ox, oy = (0, 0) if (w, h) == (8, 8) else (int(rs.integers(0, 8)), int(rs.integers(0, 8)))
+            ao, bo = oy * 96 + ox, oy * 112 + ox
+            jobs.append((ao, bo, 96, 112, w, h, kind))
+            av, bv = a.reshape(-1)[ao:], b.reshape(-1)[bo:]
+            if kind == blocks.COST_REG_SAD:
+                want.append(O.kvzo_reg_sad_10(ptr(av), ptr(bv), w, h, 96, 112))
+            elif kind == blocks.COST_SATD_ANY:
+                want.append(O.kvzo_satd_any_size_10(w, h, ptr(av), 96, ptr(bv), 112))
+            else:
+                want.append(O.kvzo_ssd_10(ptr(av), ptr(bv), 96, 112, w))
+    got = blocks.block_costs(torch.from_numpy(a.view(np.int16)).cuda(), torch.from_numpy(b.view(np.int16)).cuda(),
+                             np.array(jobs, blocks.BLOCK_JOB_DT), bitdepth=10).cpu().numpy().astype(np.uint32)
+    assert got.tolist() == want
+    for n in (4, 8, 16, 32, 64):
+        x = rs.integers(0, 1024, (4, n * n), dtype=np.uint16)
+        y = rs.integers(0, 1024, (4, n * n), dtype=np.uint16)
+        jb = np.zeros(8, blocks.BLOCK_JOB_DT)
+        jb["a_stride"] = jb["b_stride"] = jb["w"] = jb["h"] = n
+        jb["a_offset"] = jb["b_offset"] = np.tile(np.arange(4) * n * n, 2)
+        jb["kind"][:4], jb["kind"][4:] = blocks.COST_SAD_NXN, blocks.COST_SATD_NXN
+        got = blocks.block_costs(torch.from_numpy(x.view(np.int16)).cuda(), torch.from_numpy(y.view(np.int16)).cuda(), jb,
+                                 bitdepth=10).cpu().numpy().astype(np.uint32)
+        want = [O.kvzo_sad_nxn_10(n, ptr(x[i]), ptr(y[i])) for i in range(4)] + \
+               [O.kvzo_satd_nxn_10(n, ptr(x[i]), ptr(y[i])) for i in range(4)]
+        assert got.tolist() == want, n
+    # picture-level costs with the reference block partly / wholly outside the frame
+    W, H = 96, 72
+    pic = rs.integers(0, 1024, (H, W), dtype=np.uint16)
+    ref = rs.integers(0, 1024, (H, W), dtype=np.uint16)
+    rows = []
+    for _ in range(60):
+        w = int(rs.choice([8, 16, 32, 64])); h = int(rs.choice([8, 16, 32, 64]))
+        if w > W or h > H:
+            continue
+        px, py = int(rs.integers(0, (W - w) // 8 + 1)) * 8, int(rs.integers(0, (H - h) // 8 + 1)) * 8
+        rows.append((px, py, int(rs.integers(-70, W + 10)), int(rs.integers(-70, H + 10)), w, h, int(rs.integers(0, 2))))
+    ij = np.array(rows, blocks.IMAGE_JOB_DT)
+    got = blocks.image_costs(torch.from_numpy(pic.view(np.int16)).cuda(), torch.from_numpy(ref.view(np.int16)).cuda(), ij,
+                             bitdepth=10).cpu().numpy().astype(np.uint32)
+    for g, r in zip(got, ij):
+        fn = O.kvzo_image_sad_10 if r["kind"] == 0 else O.kvzo_image_satd_10
+        assert g == fn(ptr(pic), ptr(ref), W, H, int(r["pic_x"]), int(r["pic_y"]), int(r["ref_x"]), int(r["ref_y"]),
+                       int(r["w"]), int(r["h"])), r

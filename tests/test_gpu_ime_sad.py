@@ -167,3 +167,35 @@ def test_box_maps_multi_equals_single():
         for level in range(4):
             assert a.maps[level].numel() == n_ctu * (8 >> level) ** 2 * a.box[2] * a.box[3]
             assert torch.equal(a.maps[level], b.maps[level]), (r, level)
+
+
+@pytest.mark.parametrize("box", [(-8, -8, 32, 17), (-20, 3, 40, 9), (5, -12, 16, 21), (-3, -3, 8, 7)])
+def test_box_maps_10bit(box):
+    """bitdepth 10 (uint16 samples): kvz_cuda_ime_sad_box_maps vs the oracle's kvz_image_calc_sad of the 10-bit build
+    (clamped reference, >> (BD - 8)), all four PU levels, partial CTUs, full and half last chunks, extreme samples."""
+    import torch
+    import kvazaar_b200 as kb
+    w, h = 200, 136
+    rs = np.random.default_rng(41)
+    f8 = np.stack(kvzlibs.synth_luma(19, w, h, 2)).astype(np.uint16)
+    f = (f8 * 4 + rs.integers(0, 4, f8.shape)).astype(np.uint16)           # 10-bit texture
+    f[0, :16, :16], f[1, :16, :16] = 1023, 0                                # PIXEL_MAX vs 0
+    O = kvzlibs.oracle()
+    srch = kb.ImeBoxSearch(w, h, box, bitdepth=10)
+    x0, y0, n_dx, n_dy = srch.box
+    padded = kb.PaddedPlane(w, h, srch.pad, bitdepth=10).fill_from(torch.from_numpy(f[0].view(np.int16)).cuda())
+    srch.run(torch.from_numpy(f[1].view(np.int16)).cuda(), padded)
+    torch.cuda.synchronize()
+    maps = [srch.row_major(level) for level in range(4)]
+    for level in range(4):
+        size = 8 << level
+        pus = [(x, y) for y in range(0, h - size + 1, size) for x in range(0, w - size + 1, size)]
+        if len(pus) > 14:
+            pus = [pus[0], pus[-1]] + [pus[i] for i in rs.choice(len(pus), 12, replace=False)]
+        for (x, y) in pus:
+            got = maps[level][srch.pu_index(level, x, y)].astype(np.uint32) & (0xFFFF if level < 2 else 0xFFFFFFFF)
+            want = np.zeros((n_dy, n_dx), np.uint32)
+            for i in range(n_dy):
+                for j in range(n_dx):
+                    want[i, j] = O.kvzo_image_sad_10(ptr(f[1]), ptr(f[0]), w, h, x, y, x + x0 + j, y + y0 + i, size, size)
+            assert np.array_equal(got, want), (level, x, y)
