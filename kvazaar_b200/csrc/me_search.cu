@@ -124,10 +124,10 @@ __device__ __forceinline__ void make_ctx(JobCtx &j, const MeFrame &f, const kvz_
 }
 
 // fracmv_within_tile (search_inter.c:87-172); x,y quarter-pel
-#ifndef KVZ_WT_INLINE
-#define KVZ_WT_INLINE __noinline__
+#ifndef KVZ_REFINE_WT
+#define KVZ_REFINE_WT within_tile
 #endif
-__device__ KVZ_WT_INLINE bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y)
+__device__ __forceinline__ bool within_tile_inl(const MeFrame &f, const JobCtx &j, int x, int y)
 {
   const bool frac_luma = (x % 4 != 0) || (y % 4 != 0);
   const bool frac_chroma = (x % 8 != 0) || (y % 8 != 0);
@@ -149,6 +149,9 @@ __device__ KVZ_WT_INLINE bool within_tile(const MeFrame &f, const JobCtx &j, int
   const int from_bottom = (f.tile_h << 2) - (ay + (j.h << 2));
   return ax >= margin && ay >= margin && from_right >= margin && from_bottom >= margin;
 }
+
+// out-of-line form for the integer scan, where the check is rare and inlining it costs registers
+__device__ __noinline__ bool within_tile(const MeFrame &f, const JobCtx &j, int x, int y) { return within_tile_inl(f, j, x, y); }
 
 // calc_mvd_cost (search_inter.c:373-412): bits for vector (x,y) << mv_shift
 __device__ __forceinline__ uint32_t mvd_cost_bits(const JobCtx &j, int x, int y, int mv_shift)
@@ -1085,7 +1088,7 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
         {
           const int k = g.tid & 3;
           const int cxk = mvx + sqx[i + k], cyk = mvy + sqy[i + k];
-          const bool okk = free_mv || within_tile(f, j, cxk * (1 << mv_shift), cyk * (1 << mv_shift));
+          const bool okk = free_mv || KVZ_REFINE_WT(f, j, cxk * (1 << mv_shift), cyk * (1 << mv_shift));
           uint32_t ck = sm.cost4[k], bk = 0;
           if (okk) {
             bk = mvd_cost_bits(j, cxk, cyk, mv_shift);
