@@ -109,3 +109,38 @@ def test_cuda_transform_quant_match_reference_vectors(n, dst):
     assert np.array_equal(q.cpu().numpy()[0], G[k + "q"])
     dq = blocks.dequant_blocks(q, n, 27, type_=0)
     assert np.array_equal(dq.cpu().numpy()[0], G[k + "dq"])
+
+
+# ---- A15: RDOQ vectors of the compiled reference (tests/golden/make_golden_rdoq.py) ----
+RDOQ_PARAMS = ("width", "type", "scan_idx", "cu_is_intra", "tr_depth", "qp", "signhide", "slice_is_intra")
+
+
+def _rdoq_cases():
+    import kvzlibs as kl
+    v = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rdoq_vectors.npz"))
+    at = 0
+    for prm, lam, ctx in zip(v["params"], v["lam"], v["ctx"]):
+        case = dict(zip(RDOQ_PARAMS, (int(x) for x in prm)))
+        nn = case["width"] ** 2
+        case["lam"], case["coef"] = float(lam), v["coef"][at:at + nn].copy()
+        yield case, kl.RdoqCtx.from_buffer_copy(ctx.tobytes()), v["levels"][at:at + nn]
+        at += nn
+
+
+def test_oracle_rdoq_matches_reference_vectors(oracle_lib):
+    from test_oracle_rdoq import run_oracle
+    n = 0
+    for case, ctx, want in _rdoq_cases():
+        assert np.array_equal(run_oracle(case, ctx), want), {k: v for k, v in case.items() if k != "coef"}
+        n += 1
+    assert n > 60
+
+
+@pytest.mark.gpu
+def test_cuda_rdoq_matches_reference_vectors():
+    from test_gpu_rdoq import gpu_rdoq
+    for sh in (0, 1):
+        sel = [(c, x, w) for c, x, w in _rdoq_cases() if c["signhide"] == sh]
+        got = gpu_rdoq([c for c, _, _ in sel], [x for _, x, _ in sel], sh)
+        for (c, _, want), g in zip(sel, got):
+            assert np.array_equal(g, want), {k: v for k, v in c.items() if k != "coef"}
