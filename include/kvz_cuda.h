@@ -227,7 +227,18 @@ typedef struct kvz_cuda_me_frame {
   uint8_t ref_LX[2][16];        /* state->frame->ref_LX */
   int32_t n_refs;
   kvz_cuda_me_ref refs[KVZ_CUDA_MAX_REFS];   /* indexed by ref_idx */
+  /* integer search algorithm (cfg.ime_algorithm, search_inter.c:1208-1235); appended, 0 keeps the full search */
+  int32_t ime_search;           /* enum kvz_cuda_ime_search */
+  int32_t me_early_termination; /* cfg.me_early_termination: 0 off, 1 on, 2 sensitive (search_inter.c:415-460) */
+  int32_t me_max_steps;         /* cfg.me_max_steps, -1 = unlimited (search_inter.c:715, 828) */
 } kvz_cuda_me_frame;
+
+enum kvz_cuda_ime_search {
+  KVZ_CUDA_IME_FULL = 0,        /* search_mv_full over [-range, range]^2 windows (dense maps where present) */
+  KVZ_CUDA_IME_HEXBS = 1,       /* hexagon_search (search_inter.c:690-778); probes are evaluated on demand, no maps */
+  KVZ_CUDA_IME_DIA = 2,         /* diamond_search (search_inter.c:796-883) */
+  KVZ_CUDA_IME_TZ = 3           /* tz_search (search_inter.c:595-671) with the reference's compiled-in parameters */
+};
 
 /* For each PU and each of its jobs: integer full search (search_mv_full), then fractional
  * refinement (search_frac) or SATD at the integer vector, the merge-index match and the AMVP

@@ -65,7 +65,8 @@ class MeFrame(C.Structure):
                 ("deblock_enable", C.c_int32), ("mv_constraint", C.c_int32),
                 ("max_ref_lcu_right", C.c_int32), ("max_ref_lcu_down", C.c_int32),
                 ("ref_LX", (C.c_uint8 * 16) * 2), ("n_refs", C.c_int32),
-                ("refs", MeRef * MAX_REFS)]
+                ("refs", MeRef * MAX_REFS),
+                ("ime_search", C.c_int32), ("me_early_termination", C.c_int32), ("me_max_steps", C.c_int32)]
 
 
 class QuantCfg(C.Structure):

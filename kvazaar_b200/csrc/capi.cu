@@ -261,6 +261,8 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
   f.tile_x = fr->tile_x; f.tile_y = fr->tile_y; f.tile_w = fr->tile_w; f.tile_h = fr->tile_h;
   f.ctus_x = (fr->tile_w + 63) / 64;
   f.range = fr->range; f.map_pitch = ime_map_pitch(fr->range);
+  if (fr->ime_search < 0 || fr->ime_search > KVZ_CUDA_IME_TZ) return fail_msg("kvz_cuda_me_search: ime_search must be 0 (full), 1 (hexbs), 2 (dia) or 3 (tz)");
+  f.ime_search = fr->ime_search; f.me_early_termination = fr->me_early_termination; f.me_max_steps = fr->me_max_steps;
   f.lambda_sqrt_i = fr->lambda_sqrt_i;
   f.fme_level = fr->fme_level; f.owf = fr->owf; f.wpp = fr->wpp; f.sao_type = fr->sao_type;
   f.deblock_enable = fr->deblock_enable; f.mv_constraint = fr->mv_constraint;

@@ -335,6 +335,183 @@ __device__ KVZ_BOX_INLINE uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint
   return box_key(b, pos_b) < box_key(b, pos_a) ? pos_b : pos_a;
 }
 
+// ======================================================================================
+// heuristic integer searches (hexagon_search search_inter.c:690-778, diamond_search :796-883,
+// select_starting_point :282-307, early_terminate :415-460): one warp per (PU, reference) job.
+// The probes of one step are independent candidates, so lane i evaluates probe i and the step's
+// outcome -- check_mv_cost's strict '<' over the probes in order -- is the (cost, index) minimum.
+// ======================================================================================
+struct HeurState {
+  uint32_t best_cost, best_bits;
+  int mvx, mvy;                     // whole samples
+};
+
+// Lane i < n evaluates candidate (px, py) (its own); returns the index of the candidate that became the new
+// best, or -1 if none beats the current best (all lanes return the same value).
+__device__ int probe_set(const MeFrame &f, const MeRef &ref, const JobCtx &j, const uint8_t *cur, int fx0, int fy0,
+                         bool free_mv, int lane, int n, int px, int py, HeurState &h)
+{
+  uint32_t cost = 0xFFFFFFFFu, bits = 0;
+  if (lane < n && (free_mv || within_tile(f, j, px * 4, py * 4))) {
+    const uint32_t sad = sad_on_demand(f, ref, cur, f.cur_pitch, j.w, j.h, fx0 + px, fy0 + py);
+    if (sad < h.best_cost) {                                   // check_mv_cost (search_inter.c:211)
+      bits = mvd_cost_bits(j, px, py, 2);
+      cost = sad + bits * (uint32_t)j.lambda;
+    }
+  }
+  unsigned long long key = ((unsigned long long)cost << 8) | (unsigned)lane;
+  key = warp_min(key);
+  const uint32_t wcost = (uint32_t)(key >> 8);
+  const int win = (int)(key & 0xFFu);
+  if (wcost >= h.best_cost) return -1;
+  h.best_cost = wcost;
+  h.best_bits = __shfl_sync(0xffffffffu, bits, win);
+  h.mvx = __shfl_sync(0xffffffffu, px, win);
+  h.mvy = __shfl_sync(0xffffffffu, py, win);
+  return win;
+}
+
+__device__ void heuristic_job(int lane, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                              const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
+{
+  JobCtx j;
+  make_ctx(j, f, pu, merge, job);
+  const MeRef &ref = f.refs[job.ref_idx];
+  const bool free_mv = !(f.owf && f.wpp) && f.mv_constraint == 0;
+  const int fx0 = f.tile_x + j.x, fy0 = f.tile_y + j.y;
+  const uint8_t *cur = f.cur + (size_t)fy0 * f.cur_pitch + fx0;
+  HeurState h = { 0xFFFFFFFFu, 0u, 0, 0 };
+
+  // ---- select_starting_point: zero vector, extra_mv, rounded uni-directional merge candidates ----
+  {
+    int n = 1, mx = 0, my = 0;                                 // lane 0: (0, 0)
+    const int ex = job.extra_mv[0] >> 2, ey = job.extra_mv[1] >> 2;
+    bool in_merge = false;
+    for (int i = 0; i < pu.num_merge_cand; i++) {
+      const kvz_cuda_merge_cand &m = merge[i];
+      if (m.dir == 3) continue;
+      in_merge |= ((m.mv[m.dir - 1][0] + 2) >> 2) == ex && ((m.mv[m.dir - 1][1] + 2) >> 2) == ey;
+    }
+    if ((ex != 0 || ey != 0) && !in_merge) { if (lane == n) { mx = ex; my = ey; } n++; }
+    for (int i = 0; i < pu.num_merge_cand; i++) {
+      const kvz_cuda_merge_cand &m = merge[i];
+      if (m.dir == 3) continue;
+      const int x = (m.mv[m.dir - 1][0] + 2) >> 2, y = (m.mv[m.dir - 1][1] + 2) >> 2;
+      if (x == 0 && y == 0) continue;
+      if (lane == n) { mx = x; my = y; }
+      n++;
+    }
+    probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, n, mx, my, h);
+  }
+
+  bool done = false;
+  // ---- early_terminate: two rounds of a 4- then 3-point cross ----
+  if (f.me_early_termination) {
+    const int ptx[7] = { 0, -1, 0, 1, 0, -1, 0 }, pty[7] = { -1, 0, 1, 0, -1, 0, 0 };
+    int cx = h.mvx, cy = h.mvy, first = 0, last = 3;
+    for (int k = 0; k < 2 && !done; k++) {
+      const double threshold = f.me_early_termination == 2 ? (double)h.best_cost * 0.95 : (double)h.best_cost;
+      const int idx = min(first + lane, 6);
+      const int w = probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, last - first + 1, cx + ptx[idx], cy + pty[idx], h);
+      const int best = w < 0 ? 6 : first + w;
+      cx += ptx[best]; cy += pty[best];
+      if ((double)h.best_cost >= threshold) done = true;
+      first = (best + 3) % 4;
+      last = first + 2;
+    }
+  }
+
+  if (!done && f.ime_search == KVZ_CUDA_IME_HEXBS) {
+    const int bx[9] = { 0, 1, 2, 1, -1, -2, -1, 1, 2 }, by[9] = { 0, -2, 0, 2, 2, 0, -2, -2, 0 };
+    const int sx[9] = { 0, 0, -1, 1, 0, -1, 1, -1, 1 }, sy[9] = { 0, -1, 0, 0, 1, -1, -1, 1, 1 };
+    uint32_t steps = (uint32_t)f.me_max_steps;
+    int cx = h.mvx, cy = h.mvy;
+    int li = min(lane + 1, 8);
+    int w = probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, 6, cx + bx[li], cy + by[li], h);
+    int best = w < 0 ? 0 : w + 1;
+    while (best != 0 && steps != 0) {
+      if (steps > 0) steps -= 1;
+      const int start = best == 1 ? 6 : (best == 8 ? 1 : best - 1);
+      cx += bx[best]; cy += by[best];
+      li = min(start + lane, 8);
+      w = probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, 3, cx + bx[li], cy + by[li], h);
+      best = w < 0 ? 0 : start + w;
+    }
+    li = min(lane + 1, 8);
+    probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, 8, cx + sx[li], cy + sy[li], h);
+  } else if (!done && f.ime_search == KVZ_CUDA_IME_TZ) {
+    // tz_search (search_inter.c:595-671) with its compiled-in parameters: range 96, 8-point diamond
+    // patterns (4 points at distance 1, tz_pattern_search :463-577), no raster step, star refinement
+    const int range = 96;
+    int best_dist = 0;
+    auto pattern = [&](int dist, int cx, int cy) {
+      const int hd = dist / 2, k = lane & 7;
+      const int ox = k == 1 ? dist : k == 3 ? -dist : k == 4 || k == 5 ? hd : k >= 6 ? -hd : 0;
+      const int oy = k == 0 ? dist : k == 2 ? -dist : k == 4 || k == 7 ? hd : k == 5 || k == 6 ? -hd : 0;
+      if (probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, dist == 1 ? 4 : 8, cx + ox, cy + oy, h) >= 0) best_dist = dist;
+    };
+    int sx = h.mvx, sy = h.mvy, idle = 0;
+    for (int d = 1; d <= range; d *= 2) {
+      pattern(d, sx, sy);
+      if (best_dist != d) idle++;
+      if (idle >= 3) break;
+    }
+    if (sx != 0 || sy != 0) {
+      idle = 0;
+      for (int d = 1; d <= range / 2; d *= 2) {
+        pattern(d, 0, 0);
+        if (best_dist != d) idle++;
+        if (idle >= 3) break;
+      }
+    }
+    while (best_dist > 0) {
+      best_dist = 0;
+      sx = h.mvx; sy = h.mvy;
+      for (int d = 1; d <= range; d *= 2) pattern(d, sx, sy);
+    }
+  } else if (!done) {
+    const int dx[5] = { 0, 1, 0, -1, 0 }, dy[5] = { -1, 0, 1, 0, 0 };
+    uint32_t steps = (uint32_t)f.me_max_steps;
+    int cx = h.mvx, cy = h.mvy;
+    int li = min(lane, 4);
+    int w = probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, 5, cx + dx[li], cy + dy[li], h);
+    int best = w < 0 ? 4 : w;
+    if (best != 4) {
+      cx += dx[best]; cy += dy[best];
+      int from = 4;
+      bool better;
+      do {
+        better = false;
+        if (steps > 0) steps -= 1;
+        // the three points that are not where the search came from, in index order
+        int k = lane, idx = -1;
+        for (int i = 0; i < 4; i++) {
+          if (i == from) continue;
+          if (k == 0 && idx < 0) idx = i;
+          k--;
+        }
+        const int n = from == 4 ? 4 : 3;
+        if (idx < 0) idx = 4;
+        w = probe_set(f, ref, j, cur, fx0, fy0, free_mv, lane, n, cx + dx[idx], cy + dy[idx], h);
+        if (w >= 0) {
+          best = __shfl_sync(0xffffffffu, idx, w);
+          better = true;
+          cx += dx[best]; cy += dy[best];
+          from = best ^ 3;                                     // search_inter.c:874 (as the oracle restates it)
+        }
+      } while (better && steps != 0);
+    }
+  }
+
+  if (lane == 0) {
+    kvz_cuda_me_result r;
+    r.mv[0] = (int16_t)(h.mvx * 4); r.mv[1] = (int16_t)(h.mvy * 4);
+    r.cost = h.best_cost; r.bitcost = h.best_bits;
+    r.merged = 0; r.merge_idx = 0; r.mv_cand_idx = 0; r.took = 0;
+    *out = r;
+  }
+}
+
 template <bool BOX>
 __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
                          const kvz_cuda_me_job &job, kvz_cuda_me_result *out, bool after_box)
@@ -879,8 +1056,10 @@ me_scan_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__restri
       scan_job<true>(lane, sm, f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q, false);
   } else {
     __shared__ ScanSmemT<false> sm[kScanWarps];
-    for (int q = warp; q < pu.num_jobs; q += kScanWarps)
-      scan_job<false>(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q, box_dx > 0);
+    for (int q = warp; q < pu.num_jobs; q += kScanWarps) {
+      if (f.ime_search != KVZ_CUDA_IME_FULL) heuristic_job(lane, f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q);
+      else scan_job<false>(lane, sm[warp], f, pu, merge, jobs[pu.first_job + q], results + pu.first_job + q, box_dx > 0);
+    }
   }
 }
 
@@ -1192,6 +1371,7 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
       if (f.refs[r].sets[m].n_dx > box_dx) box_dx = f.refs[r].sets[m].n_dx;
       if (f.refs[r].sets[m].n_dy > box_dy) box_dy = f.refs[r].sets[m].n_dy;
     }
+  if (f.ime_search != KVZ_CUDA_IME_FULL) box_dx = box_dy = 0;      // heuristic searches evaluate their probes on demand
   if (box_dx > 0) {
     const size_t smem = kScanWarps * box_scan_warp_bytes(box_dx, box_dy);
     auto kern = me_scan_kernel<true>;

@@ -29,6 +29,7 @@ struct MeFrame {
   int tile_x, tile_y, tile_w, tile_h;
   int ctus_x;
   int range, map_pitch;
+  int ime_search, me_early_termination, me_max_steps;   // kvz_cuda_ime_search; cfg.me_early_termination / me_max_steps
   int lambda_sqrt_i;
   int fme_level, owf, wpp, sao_type, deblock_enable, mv_constraint, max_ref_lcu_right, max_ref_lcu_down;
   int n_refs;

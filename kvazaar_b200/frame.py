@@ -212,9 +212,12 @@ class MeSearch:
     references; mirrors the reference loop of search_pu_inter (search_inter.c:1451-1524)."""
 
     def __init__(self, width, height, rng=32, fme_level=4, lambda_sqrt=27.0, tile=None, owf=0, wpp=0,
-                 sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu=(1, 1), ref_LX=None):
+                 sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu=(1, 1), ref_LX=None,
+                 ime_search=0, me_early_termination=0, me_max_steps=-1):
+        """ime_search: 0 full search (dense maps), 1 hexbs, 2 diamond, 3 tz (probes evaluated on demand)"""
         capi.init(torch.cuda.current_device())
         fr = capi.MeFrame()
+        fr.ime_search, fr.me_early_termination, fr.me_max_steps = ime_search, me_early_termination, me_max_steps
         fr.width, fr.height, fr.bitdepth, fr.range = width, height, 8, rng
         fr.tile_x, fr.tile_y, fr.tile_w, fr.tile_h = tile or (0, 0, width, height)
         fr.lambda_sqrt_i = int(lambda_sqrt + 0.5)

@@ -48,7 +48,8 @@ def random_pus(rs, width, height, n_refs, count, sizes=(8, 16, 32, 64), mv_span=
 
 
 def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, owf=0, wpp=0,
-                  sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu=(1, 1), ref_LX=None):
+                  sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu=(1, 1), ref_LX=None,
+                  ime_search=0, me_early_termination=0, me_max_steps=-1):
     """Runs kvzo_ime / kvzo_fme / kvzo_int_satd with *inter_cost carried over each PU's jobs
     and returns a result array in the layout of kvz_cuda_me_result."""
     from kvazaar_b200.frame import ME_RESULT_DT
@@ -81,8 +82,9 @@ def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sq
             j.lambda_sqrt_i = lambda_sqrt_i
             j.owf, j.wpp, j.sao_type, j.deblock_enable, j.mv_constraint = owf, wpp, sao_type, deblock_enable, mv_constraint
             j.max_ref_lcu_right, j.max_ref_lcu_down = max_ref_lcu
-            j.fme_level, j.me_early_termination, j.me_max_steps = fme_level, 0, -1
-            j.ime_algorithm = ALGO_OF_RANGE[rng]
+            j.fme_level, j.me_early_termination, j.me_max_steps = fme_level, me_early_termination, me_max_steps
+            # kvz_cuda_ime_search: 0 full (by range), 1 hexbs (KVZ_IME_HEXBS = 0), 2 dia (KVZ_IME_DIA = 7), 3 tz (KVZ_IME_TZ = 1)
+            j.ime_algorithm = (ALGO_OF_RANGE[rng], 0, 7, 1)[ime_search]
             ref = refs[j.ref_idx]
             O.kvzo_ime_8(C.byref(j), ptr(cur), ptr(ref))
             if fme_level > 0 and j.best_cost < inter_cost:

@@ -55,6 +55,24 @@ def test_without_dense_maps():
     _run(200, 136, 8, 4, 2, 24, 12, use_maps=False)
 
 
+@pytest.mark.parametrize("algo", [1, 2, 3])
+@pytest.mark.parametrize("early", [0, 1, 2])
+def test_heuristic_integer_search(algo, early):
+    # hexagon_search / diamond_search / tz_search (search_inter.c:595-883) with the early_terminate variants
+    _run(256, 192, 16, 4, 2, 64, 40 + 3 * algo + early, use_maps=False, ime_search=algo, me_early_termination=early)
+
+
+def test_heuristic_integer_search_step_limit_and_restrictions():
+    _run(256, 192, 16, 2, 3, 48, 50, use_maps=False, ime_search=1, me_max_steps=2)
+    _run(256, 192, 16, 0, 2, 48, 51, use_maps=False, ime_search=2, me_max_steps=1)
+    _run(256, 192, 16, 4, 2, 48, 52, use_maps=False, ime_search=1, owf=1, wpp=1)
+    _run(200, 136, 8, 4, 2, 40, 53, use_maps=False, ime_search=2, mv_constraint=4, me_early_termination=2)
+    _run(256, 192, 16, 4, 2, 48, 55, use_maps=False, ime_search=3, owf=1, wpp=1)
+    _run(200, 136, 8, 2, 2, 40, 56, use_maps=False, ime_search=3, mv_constraint=4)
+    # dense maps present: the heuristic searches ignore them
+    _run(200, 136, 8, 4, 2, 24, 54, use_maps=True, ime_search=1)
+
+
 def test_cached_window_centres():
     # windows round extra_mv / merge candidates served from centred dense maps, the rest on demand
     _run(256, 192, 16, 4, 2, 48, 14, centres=[(5, 3), (-7, 10)])
