@@ -290,6 +290,29 @@ KVZ_CUDA_API int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const vo
                                       int n_jobs, int bitdepth, uint32_t *d_out, void *stream);
 
 /* ------------------------------------------------------------------ */
+/* BATCH face: picture-level reductions              */
+/* ------------------------------------------------------------------ */
+
+typedef struct kvz_cuda_plane {
+  const void *d_data;           /* first sample of the plane (device) */
+  int32_t width, height;        /* samples */
+  int32_t pitch;                /* bytes per row */
+} kvz_cuda_plane;
+
+/* Picture-hash SEI checksum of up to 3 planes in one launch: d_checksums[p] = what array_checksum_func
+ * kvz_array_checksum (strategies/strategies-nal.h:42-47, strategies/generic/nal-generic.c:58-82; caller
+ * kvz_image_checksum nal.c:60-76) computes for plane p before it unpacks the sum big-endian into
+ * checksum_out[0..3] -- the host glue does that unpacking.  bitdepth 8: uint8 samples; > 8: uint16 samples,
+ * both bytes hashed.  kvz_array_md5 is a serial chain over the plane and stays on the host. */
+KVZ_CUDA_API int kvz_cuda_picture_checksum(const kvz_cuda_plane *planes, int n_planes, int bitdepth,
+                                           uint32_t *d_checksums, void *stream);
+
+/* d_sse[p] = sum over plane p of (src - rec)^2, the sums compute_psnr (encmain.c:101-131) turns into
+ * 10 * log10(num_pixels * PIXEL_MAX^2 / sse) on the host; planes of src and rec must have equal sizes. */
+KVZ_CUDA_API int kvz_cuda_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_plane *rec, int n_planes,
+                                      int bitdepth, uint64_t *d_sse, void *stream);
+
+/* ------------------------------------------------------------------ */
 /* BATCH face: transforms and quantisation  (rows A13, A14)              */
 /* ------------------------------------------------------------------ */
 

@@ -35,6 +35,7 @@ KVZ_CUDA_API int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth, 
 KVZ_CUDA_API int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 KVZ_CUDA_API int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 KVZ_CUDA_API int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 
 /* ---- picture: strategies-picture.h:102-136 ---- */
 /* reg_sad_func */
@@ -127,6 +128,12 @@ KVZ_CUDA_API void kvz_cuda_filter_hpel_blocks_hor_ver_luma(KVZ_CUDA_IPOL_BLOCKS_
 KVZ_CUDA_API void kvz_cuda_filter_hpel_blocks_diag_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS);
 KVZ_CUDA_API void kvz_cuda_filter_qpel_blocks_hor_ver_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS);
 KVZ_CUDA_API void kvz_cuda_filter_qpel_blocks_diag_luma(KVZ_CUDA_IPOL_BLOCKS_ARGS);
+
+/* ---- nal: strategies-nal.h:42-47 ---- */
+/* array_checksum_func kvz_array_checksum (checksum_out is SEI_HASH_MAX_LENGTH = 16 bytes, the first four are
+ * written, nal-generic.c:76-81); the plane is uploaded in strips of rows.  kvz_array_md5 is not replaced. */
+KVZ_CUDA_API void kvz_cuda_array_checksum(const kvz_cuda_px *data, const int height, const int width, const int stride,
+                                          unsigned char checksum_out[16], const uint8_t bitdepth);
 
 #ifdef __cplusplus
 }

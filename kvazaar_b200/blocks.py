@@ -54,6 +54,37 @@ def image_costs(d_pic, d_ref, jobs, bitdepth=8):
     return out
 
 
+def _planes(tensors):
+    arr = (capi.Plane * len(tensors))()
+    for a, t in zip(arr, tensors):
+        assert t.dim() == 2 and t.stride(1) == 1
+        a.d_data, a.height, a.width = t.data_ptr(), t.shape[0], t.shape[1]
+        a.pitch = t.stride(0) * t.element_size()
+    return arr
+
+
+def picture_checksum(planes, bitdepth=8):
+    """planes: up to 3 (H, W) device tensors (uint8, or int16/uint16 samples at bitdepth > 8; row-strided views
+    allowed).  Returns a device int32 tensor: per plane the 32-bit sum of kvz_array_checksum
+    (nal-generic.c:58-82) before the reference unpacks it big-endian."""
+    capi.init(torch.cuda.current_device())
+    out = torch.empty(len(planes), dtype=torch.int32, device="cuda")
+    arr = _planes(planes)
+    capi.check(capi.lib().kvz_cuda_picture_checksum(C.addressof(arr), len(planes), bitdepth, _p(out), _stream()),
+               "kvz_cuda_picture_checksum")
+    return out
+
+
+def picture_sse(src_planes, rec_planes, bitdepth=8):
+    """Per plane the sum of squared differences compute_psnr (encmain.c:101-131) accumulates; device int64 tensor."""
+    capi.init(torch.cuda.current_device())
+    out = torch.empty(len(src_planes), dtype=torch.int64, device="cuda")
+    a, b = _planes(src_planes), _planes(rec_planes)
+    capi.check(capi.lib().kvz_cuda_picture_sse(C.addressof(a), C.addressof(b), len(src_planes), bitdepth, _p(out), _stream()),
+               "kvz_cuda_picture_sse")
+    return out
+
+
 RESIDUAL_JOB_DT = np.dtype([("ref_offset", "<u4"), ("pred_offset", "<u4"), ("rec_offset", "<u4"),
                             ("coeff_offset", "<u4"), ("in_stride", "<i4"), ("out_stride", "<i4"),
                             ("width", "u1"), ("color", "u1"), ("scan_idx", "u1"), ("use_trskip", "u1"),

@@ -38,6 +38,11 @@ class ImeBoxDesc(C.Structure):
                 ("x0", C.c_int32), ("y0", C.c_int32), ("n_dx", C.c_int32), ("n_dy", C.c_int32)]
 
 
+class Plane(C.Structure):
+    """kvz_cuda_plane"""
+    _fields_ = [("d_data", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("pitch", C.c_int32)]
+
+
 class ImeBoxRef(C.Structure):
     """kvz_cuda_ime_box_ref"""
     _fields_ = [("desc", ImeBoxDesc), ("d_ref_padded", C.c_void_p), ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p),
@@ -101,6 +106,8 @@ SIGNATURES = {
     "kvz_cuda_ime_sad_box_maps": (C.c_int, [C.POINTER(ImeBoxDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "kvz_cuda_ime_sad_box_maps_multi": (C.c_int, [C.POINTER(ImeBoxRef), C.c_int, _VP, _VP]),
     "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_picture_checksum": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_picture_sse": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

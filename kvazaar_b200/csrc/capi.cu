@@ -18,6 +18,12 @@ int launch_image_cost(const void *pic, int pic_pitch, const void *ref, int ref_p
                       const kvz_cuda_image_cost_job *jobs, int n_jobs, int bitdepth, uint32_t *out, cudaStream_t stream);
 }
 namespace kvz {
+int launch_picture_checksum(const kvz_cuda_plane *planes, int n_planes, int bitdepth, uint32_t *d_out, cudaStream_t stream, int y0);
+int launch_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_plane *rec, int n_planes, int bitdepth,
+                       unsigned long long *d_out, cudaStream_t stream);
+}
+
+namespace kvz {
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
@@ -304,6 +310,21 @@ int kvz_cuda_image_costs(const void *d_pic, int pic_pitch, const void *d_ref, in
   if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_image_costs: bitdepth must be 8 or 10");
   return launch_image_cost(d_pic, pic_pitch, d_ref, ref_pitch, width, height, d_jobs, n_jobs, bitdepth, d_out,
                            (cudaStream_t)stream);
+}
+
+int kvz_cuda_picture_checksum(const kvz_cuda_plane *planes, int n_planes, int bitdepth, uint32_t *d_checksums, void *stream)
+{
+  if (!planes || !d_checksums) return fail_msg("kvz_cuda_picture_checksum: bad argument");
+  if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_picture_checksum: bitdepth must be 8..16");
+  return launch_picture_checksum(planes, n_planes, bitdepth, d_checksums, (cudaStream_t)stream, 0);
+}
+
+int kvz_cuda_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_plane *rec, int n_planes, int bitdepth,
+                         uint64_t *d_sse, void *stream)
+{
+  if (!src || !rec || !d_sse) return fail_msg("kvz_cuda_picture_sse: bad argument");
+  if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_picture_sse: bitdepth must be 8..16");
+  return launch_picture_sse(src, rec, n_planes, bitdepth, reinterpret_cast<unsigned long long *>(d_sse), (cudaStream_t)stream);
 }
 
 int kvz_cuda_transform_blocks(int n, int dst4, int inverse, int bitdepth, const int16_t *d_in, int16_t *d_out,

@@ -20,6 +20,7 @@ int launch_block_cost(const void *base_a, const void *base_b, const kvz_cuda_blo
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32_t *out, cudaStream_t stream);
+int launch_picture_checksum(const kvz_cuda_plane *planes, int n_planes, int bitdepth, uint32_t *d_out, cudaStream_t stream, int y0);
 int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
                        uint32_t *costs, void *preds, cudaStream_t stream);
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
@@ -521,6 +522,40 @@ int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_reg
   KVZ_REG("sample_14bit_quarterpel_luma", kvz_cuda_sample_14bit_quarterpel_luma);
   KVZ_REG("sample_14bit_octpel_chroma", kvz_cuda_sample_14bit_octpel_chroma);
   // get_extended_block stays with the host's generic strategy: it only copies memory
+  return ok;
+}
+
+// ---------------- nal ----------------
+void kvz_cuda_array_checksum(const kvz_cuda_px *data, const int height, const int width, const int stride,
+                             unsigned char checksum_out[16], const uint8_t bitdepth)
+{
+  const char *who = "kvz_cuda_array_checksum";
+  if (bitdepth != 8 || width <= 0 || height <= 0 || (size_t)width + 64 > kStage) { fail_msg("kvz_cuda_array_checksum: bad argument"); die(who); }
+  uint32_t sum = 0;                                           // the checksum is a sum: strips of rows add up
+  const int rows_per = (int)((kStage - 64) / (size_t)width);
+  for (int y0 = 0; y0 < height; y0 += rows_per) {
+    const int rows = height - y0 < rows_per ? height - y0 : rows_per;
+    Stage st(who);
+    uint8_t *in = st.in<uint8_t>((size_t)rows * width);
+    pack_rows(in, data + (size_t)y0 * stride, width, rows, (size_t)stride);
+    uint32_t *out = st.out<uint32_t>(1);
+    st.upload(who);
+    kvz_cuda_plane pl = { st.dev(in), width, rows, width };
+    if (!launch_picture_checksum(&pl, 1, 8, st.dev(out), g_pc.stream, y0)) die(who);
+    st.download(who);
+    sum += *out;
+  }
+  checksum_out[0] = (unsigned char)(sum >> 24); checksum_out[1] = (unsigned char)(sum >> 16);
+  checksum_out[2] = (unsigned char)(sum >> 8); checksum_out[3] = (unsigned char)sum;
+}
+
+int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  KVZ_REG("array_checksum", kvz_cuda_array_checksum);
   return ok;
 }
 

@@ -167,6 +167,11 @@ void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, con
                                         int use_trskip, int in_stride, int out_stride, \
                                         const PIX *ref_in, const PIX *pred_in, PIX *rec_out, \
                                         int16_t *coeff_out); \
+  /* picture hash checksum (strategies/generic/nal-generic.c:58-82), the 32-bit sum before it is unpacked \
+   * big-endian; stride in samples.  At KVZ_BIT_DEPTH > 8 both bytes of a sample are hashed. */ \
+  uint32_t kvzo_array_checksum_##SFX(const PIX *data, int height, int width, int stride); \
+  /* the per-plane sum of compute_psnr (encmain.c:101-131) */ \
+  uint64_t kvzo_plane_sse_##SFX(const PIX *src, const PIX *rec, int width, int height, int src_stride, int rec_stride); \
   /* test helper: SAD of one PU over the whole zero-centred window */ \
   void kvzo_dense_sad_map_##SFX(const PIX *pic, const PIX *ref, int W, int H, int x, int y, \
                                 int bw, int bh, int r, uint32_t *out); \

@@ -153,6 +153,21 @@ def test_intra_and_ipol_strategies():
                 assert np.array_equal(filt.reshape(4, 64, 64)[:, :h, :w], wantb[:, :h, :w]), (nm, w)
 
 
+def test_nal_checksum_strategy():
+    # array_checksum_func (strategies-nal.h:42-47) on host planes, larger than one staging strip
+    from test_oracle_picture_stats import oracle_checksum
+    L = _lib()
+    L.kvz_cuda_array_checksum.restype = None
+    L.kvz_cuda_array_checksum.argtypes = [PX, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_ubyte), C.c_uint8]
+    rs = np.random.default_rng(3)
+    for h, w, pad in ((1, 1, 0), (68, 100, 12), (1080, 1920, 0), (540, 960, 64), (2160, 3840, 0)):
+        big = rs.integers(0, 256, (h, w + pad), dtype=np.uint8)
+        out = (C.c_ubyte * 16)()
+        L.kvz_cuda_array_checksum(_p8(big), h, w, w + pad, out, 8)
+        got = (out[0] << 24) | (out[1] << 16) | (out[2] << 8) | out[3]
+        assert got == oracle_checksum(big[:, :w]), (h, w)
+
+
 def test_registers_into_the_reference_strategy_list(ref_lib):
     L = _lib()
 
@@ -161,11 +176,11 @@ def test_registers_into_the_reference_strategy_list(ref_lib):
 
     reg = C.cast(ref_lib.kvz_strategyselector_register, C.c_void_p)
     total = 0
-    for fam, n in (("picture", 24), ("dct", 10), ("quant", 1), ("intra", 2), ("ipol", 8)):
+    for fam, n in (("picture", 24), ("dct", 10), ("quant", 1), ("intra", 2), ("ipol", 8), ("nal", 1)):
         fn = getattr(L, f"kvz_strategy_register_{fam}_cuda")
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_uint8, C.c_void_p]
         lst = StrategyList()
         assert fn(C.byref(lst), 8, reg) == 1
         assert lst.count == n, (fam, lst.count)
         total += lst.count
-    assert total == 45
+    assert total == 46

@@ -82,4 +82,15 @@ for lg in (2, 3, 4, 5):
     out["stages"][f"intra_costs{n}"] = {"blocks": cnt, "ms": round(ms, 4), "Mblocks_per_s": round(cnt / ms / 1e3, 1),
                                         "predicted_Gsamples_per_s": round(cnt * 35 * n * n / ms / 1e6, 1),
                                         "note": "35 predictions + SATD + SAD per PU (ALU / latency bound)"}
+# picture-level reductions: 4:2:0 pictures, all three planes in one launch
+for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (3840, 2160), 10)):
+    dt, top = (np.uint8, 256) if bd == 8 else (np.int16, 1024)
+    mk = lambda: [torch.from_numpy(rs.integers(0, top, s).astype(dt)).cuda() for s in ((ph, pw), (ph // 2, pw // 2), (ph // 2, pw // 2))]
+    a, b = mk(), mk()
+    nbytes = sum(t.numel() * t.element_size() for t in a)
+    for label, fn, rd in (("picture_checksum", lambda: blocks.picture_checksum(a, bd), 1), ("picture_sse", lambda: blocks.picture_sse(a, b, bd), 2)):
+        ms = timed(fn, 20)
+        out["stages"][f"{label}_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(rd * nbytes / ms / 1e6, 1),
+                                            "frac_of_hbm": round(rd * nbytes / ms / 1e6 / HBM, 3),
+                                            "note": "one launch + one memset per picture; the planes fit in L2, so this is launch latency, not HBM"}
 print(json.dumps(out))
