@@ -71,6 +71,14 @@ int kvzo_select_mv_cand(const int16_t mv_cand[2][2], int mv_x, int mv_y);
 void kvzo_fwd_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
 void kvzo_inv_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
 
+/* the fields of sao_info_t (sao.h:43-51) the SAO filters and distortion functions read */
+typedef struct {
+  int32_t type;             /* 0 SAO_TYPE_NONE, 1 SAO_TYPE_BAND, 2 SAO_TYPE_EDGE */
+  int32_t eo_class;         /* 0 horizontal, 1 vertical, 2 diagonal 135, 3 diagonal 45 (sao.h:59-64) */
+  int32_t band_position[2]; /* [0] Y or U, [1] V */
+  int32_t offsets[10];      /* [cat] for Y / U, [5 + cat] for V */
+} kvzo_sao_info;
+
 typedef struct {
   int32_t qp;             /* state->qp (luma QP of the CTU) */
   int32_t bitdepth;
@@ -172,6 +180,17 @@ void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, con
   uint32_t kvzo_array_checksum_##SFX(const PIX *data, int height, int width, int stride); \
   /* the per-plane sum of compute_psnr (encmain.c:101-131) */ \
   uint64_t kvzo_plane_sse_##SFX(const PIX *src, const PIX *rec, int width, int height, int src_stride, int rec_stride); \
+  /* SAO strategies (strategies/generic/sao-generic.c:50-182) and calc_sao_bands (sao.c:245-260) on contiguous \
+   * block_width x block_height blocks; kvzo_sao_reconstruct = kvz_sao_reconstruct (sao.c:277-337) on whole planes \
+   * of stride == frame width: `pre` holds the deblocked samples, `out` the filtered ones */ \
+  int kvzo_sao_edge_ddistortion_##SFX(const PIX *orig, const PIX *rec, int bw, int bh, int eo_class, const int *offsets); \
+  void kvzo_calc_sao_edge_dir_##SFX(const PIX *orig, const PIX *rec, int eo_class, int bw, int bh, int *cat_sum_cnt); \
+  int kvzo_sao_band_ddistortion_##SFX(const PIX *orig, const PIX *rec, int bw, int bh, int band_pos, const int *sao_bands); \
+  void kvzo_calc_sao_bands_##SFX(const PIX *orig, const PIX *rec, int bw, int bh, int *sao_bands); \
+  void kvzo_sao_reconstruct_color_##SFX(const PIX *rec, PIX *new_rec, const kvzo_sao_info *sao, int stride, \
+                                        int new_stride, int bw, int bh, int color); \
+  void kvzo_sao_reconstruct_##SFX(const PIX *pre, PIX *out, int frame_w, int frame_h, int x, int y, int w, int h, \
+                                  const kvzo_sao_info *sao, int color); \
   /* test helper: SAD of one PU over the whole zero-centred window */ \
   void kvzo_dense_sad_map_##SFX(const PIX *pic, const PIX *ref, int W, int H, int x, int y, \
                                 int bw, int bh, int r, uint32_t *out); \

@@ -474,3 +474,64 @@ int ref_shim_intra_predict(const kvz_pixel *ref_top, const kvz_pixel *ref_left, 
   kvz_intra_predict(&refs, log2_width, mode, (color_t)color, dst, filter_boundary);
   return 1;
 }
+
+/* ---- SAO: the strategies that read encoder state, and kvz_sao_reconstruct (sao.c:277-337) on a fake frame ---- */
+#include "sao.h"
+#include "strategies/strategies-sao.h"
+
+typedef struct {
+  int32_t type, eo_class, band_position[2], offsets[10];
+} ref_sao_info;
+
+static void sao_from_plain(sao_info_t *s, const ref_sao_info *p)
+{
+  memset(s, 0, sizeof(*s));
+  s->type = (sao_type)p->type;
+  s->eo_class = (sao_eo_class)p->eo_class;
+  s->band_position[0] = p->band_position[0]; s->band_position[1] = p->band_position[1];
+  for (int i = 0; i < 10; i++) s->offsets[i] = p->offsets[i];
+}
+
+int ref_shim_sao_band_ddistortion(const kvz_pixel *orig, const kvz_pixel *rec, int bw, int bh, int band_pos, int *bands)
+{
+  fake_env *e = calloc(1, sizeof(*e));
+  e->state.encoder_control = &e->ctrl;
+  e->ctrl.bitdepth = KVZ_BIT_DEPTH;
+  int r = kvz_sao_band_ddistortion(&e->state, orig, rec, bw, bh, band_pos, bands);
+  free(e);
+  return r;
+}
+
+int ref_shim_sao_reconstruct_color(const kvz_pixel *rec, kvz_pixel *new_rec, const ref_sao_info *p, int stride,
+                                   int new_stride, int bw, int bh, int color)
+{
+  encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+  ctrl->bitdepth = KVZ_BIT_DEPTH;
+  sao_info_t s;
+  sao_from_plain(&s, p);
+  kvz_sao_reconstruct_color(ctrl, rec, new_rec, &s, stride, new_stride, bw, bh, (color_t)color);
+  free(ctrl);
+  return 1;
+}
+
+/* pre: deblocked plane of this colour (stride == its width); out: the frame's rec plane of this colour, which
+ * kvz_sao_reconstruct writes at (x, y); luma_w / luma_h: frame size in luma samples */
+int ref_shim_sao_reconstruct(const kvz_pixel *pre, kvz_pixel *out, int luma_w, int luma_h, int x, int y, int w, int h,
+                             const ref_sao_info *p, int color)
+{
+  fake_env *e = calloc(1, sizeof(*e));
+  e->state.encoder_control = &e->ctrl;
+  e->state.tile = &e->tile;
+  e->tile.frame = &e->vframe;
+  e->ctrl.bitdepth = KVZ_BIT_DEPTH;
+  e->vframe.width = luma_w; e->vframe.height = luma_h;
+  e->vframe.rec = &e->pic;
+  e->pic.width = luma_w; e->pic.height = luma_h; e->pic.stride = luma_w;
+  e->pic.data[color] = out;
+  const int plane_w = color ? luma_w >> 1 : luma_w;
+  sao_info_t s;
+  sao_from_plain(&s, p);
+  kvz_sao_reconstruct(&e->state, pre + (size_t)y * plane_w + x, plane_w, x, y, w, h, &s, (color_t)color);
+  free(e);
+  return 1;
+}
