@@ -313,6 +313,48 @@ KVZ_CUDA_API int kvz_cuda_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_
                                       int bitdepth, uint64_t *d_sse, void *stream);
 
 /* ------------------------------------------------------------------ */
+/* BATCH face: sample adaptive offset                */
+/* ------------------------------------------------------------------ */
+
+/* The fields of sao_info_t (sao.h:43-51) the filter reads, per CTU; luma CTUs and chroma CTUs have one array
+ * each (frame->sao_luma / frame->sao_chroma), raster order over the picture's CTUs. */
+typedef struct kvz_cuda_sao_params {
+  int8_t type;                  /* sao_type: 0 none, 1 band, 2 edge */
+  int8_t eo_class;              /* sao_eo_class 0..3 (neighbour offsets sao.h:59-64) */
+  int8_t band_position[2];      /* [0] Y / U, [1] V */
+  int8_t offsets[10];           /* [category] for Y / U, [5 + category] for V; band offsets at [1..4] / [6..9] */
+  int8_t reserved[2];
+} kvz_cuda_sao_params;          /* 16 bytes */
+
+/* What the SAO search asks the pixels of one CTU of one colour plane for. */
+typedef struct kvz_cuda_sao_stats {
+  int32_t edge[4][2][5];        /* [eo_class]: cat_sum_cnt of calc_sao_edge_dir (sao-generic.c:90-117):
+                                   [0][cat] = sum of (orig - rec), [1][cat] = count, block-interior samples */
+  int32_t band[2][32];          /* sao_bands of calc_sao_bands (sao.c:245-260): [0][band] sum, [1][band] count */
+} kvz_cuda_sao_stats;           /* 416 bytes */
+
+/* One pass over the source (`orig`) and the deblocked reconstruction (`rec`) of a picture: plane 0 luma with
+ * 64x64 CTUs, planes 1..2 chroma of a 4:2:0 picture with 32x32 CTUs (partial CTUs at the right / bottom, as
+ * sao_search_luma / sao_search_chroma clip them, sao.c:577-637).  d_stats holds the records of plane 0's CTUs in
+ * raster order, then plane 1's, then plane 2's.  Replaces the calls of calc_sao_edge_dir_func kvz_calc_sao_edge_dir
+ * and calc_sao_bands in sao_search_edge_sao / sao_search_band_sao (sao.c:337-455) and, because
+ *   kvz_sao_edge_ddistortion(eo_class, offsets) = sum_cat  n[cat] * h[cat]^2 - 2 * h[cat] * E[cat]   (h != 0)
+ *   kvz_sao_band_ddistortion(pos, bands)       = sum_b<4  n[pos+b] * h[b]^2 - 2 * h[b] * E[pos+b]    (h != 0)
+ * exactly (sao-generic.c:51-81, :158-182; the formula of sao.c:381-388), every sao_edge_ddistortion_func /
+ * sao_band_ddistortion_func call of sao_search_best_mode (sao.c:465-575) as well. */
+KVZ_CUDA_API int kvz_cuda_sao_ctu_stats(const kvz_cuda_plane *orig, const kvz_cuda_plane *rec, int n_planes,
+                                        int bitdepth, kvz_cuda_sao_stats *d_stats, void *stream);
+
+/* kvz_sao_reconstruct (sao.c:277-337) with sao_reconstruct_color_func kvz_sao_reconstruct_color
+ * (sao-generic.c:120-155) for every CTU of the picture, i.e. the picture encoder_sao_reconstruct
+ * (encoderstate.c:245-441) leaves once every LCU has been through it: rec_out = SAO(rec_in), each sample with the
+ * parameters of the CTU containing it, neighbours read from rec_in, samples whose edge neighbour lies outside
+ * the picture copied.  rec_out must not alias rec_in.  Plane / CTU conventions as above. */
+KVZ_CUDA_API int kvz_cuda_sao_reconstruct(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out, int n_planes,
+                                          int bitdepth, const kvz_cuda_sao_params *d_luma,
+                                          const kvz_cuda_sao_params *d_chroma, void *stream);
+
+/* ------------------------------------------------------------------ */
 /* BATCH face: transforms and quantisation  (rows A13, A14)              */
 /* ------------------------------------------------------------------ */
 

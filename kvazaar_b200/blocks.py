@@ -85,6 +85,40 @@ def picture_sse(src_planes, rec_planes, bitdepth=8):
     return out
 
 
+SAO_PARAMS_DT = np.dtype([("type", "i1"), ("eo_class", "i1"), ("band_position", "i1", (2,)), ("offsets", "i1", (10,)),
+                          ("reserved", "i1", (2,))])
+SAO_STATS_DT = np.dtype([("edge", "<i4", (4, 2, 5)), ("band", "<i4", (2, 32))])
+assert SAO_PARAMS_DT.itemsize == 16 and SAO_STATS_DT.itemsize == 416
+
+
+def sao_ctu_counts(planes):
+    """CTUs per plane: 64x64 for plane 0, 32x32 for the chroma planes of a 4:2:0 picture"""
+    return [((t.shape[0] + c - 1) // c) * ((t.shape[1] + c - 1) // c) for t, c in zip(planes, (64, 32, 32))]
+
+
+def sao_ctu_stats(orig_planes, rec_planes, bitdepth=8):
+    """kvz_cuda_sao_ctu_stats: device uint8 tensor holding SAO_STATS_DT records, plane-major, CTUs in raster order"""
+    capi.init(torch.cuda.current_device())
+    n = sum(sao_ctu_counts(orig_planes))
+    out = torch.empty(n * SAO_STATS_DT.itemsize, dtype=torch.uint8, device="cuda")
+    a, b = _planes(orig_planes), _planes(rec_planes)
+    capi.check(capi.lib().kvz_cuda_sao_ctu_stats(C.addressof(a), C.addressof(b), len(orig_planes), bitdepth, _p(out), _stream()),
+               "kvz_cuda_sao_ctu_stats")
+    return out
+
+
+def sao_reconstruct(rec_planes, out_planes, luma_params, chroma_params, bitdepth=8):
+    """kvz_cuda_sao_reconstruct: *_params are numpy SAO_PARAMS_DT arrays (one record per CTU) or device tensors"""
+    capi.init(torch.cuda.current_device())
+    d_l = _dev(luma_params) if isinstance(luma_params, np.ndarray) else luma_params
+    d_c = (_dev(chroma_params) if isinstance(chroma_params, np.ndarray) else chroma_params) if chroma_params is not None else None
+    a, b = _planes(rec_planes), _planes(out_planes)
+    capi.check(capi.lib().kvz_cuda_sao_reconstruct(C.addressof(a), C.addressof(b), len(rec_planes), bitdepth, _p(d_l),
+                                                   _p(d_c) if d_c is not None else None, _stream()),
+               "kvz_cuda_sao_reconstruct")
+    return out_planes
+
+
 RESIDUAL_JOB_DT = np.dtype([("ref_offset", "<u4"), ("pred_offset", "<u4"), ("rec_offset", "<u4"),
                             ("coeff_offset", "<u4"), ("in_stride", "<i4"), ("out_stride", "<i4"),
                             ("width", "u1"), ("color", "u1"), ("scan_idx", "u1"), ("use_trskip", "u1"),

@@ -108,6 +108,8 @@ SIGNATURES = {
     "kvz_cuda_block_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_picture_checksum": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_picture_sse": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_sao_ctu_stats": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_sao_reconstruct": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

@@ -24,6 +24,13 @@ int launch_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_plane *rec, int
 }
 
 namespace kvz {
+int launch_sao_stats(const kvz_cuda_plane *orig, const kvz_cuda_plane *rec, int n_planes, int bitdepth,
+                     kvz_cuda_sao_stats *d_stats, cudaStream_t stream);
+int launch_sao_apply(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out, int n_planes, int bitdepth,
+                     const kvz_cuda_sao_params *d_luma, const kvz_cuda_sao_params *d_chroma, cudaStream_t stream);
+}
+
+namespace kvz {
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
@@ -325,6 +332,22 @@ int kvz_cuda_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_plane *rec, i
   if (!src || !rec || !d_sse) return fail_msg("kvz_cuda_picture_sse: bad argument");
   if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_picture_sse: bitdepth must be 8..16");
   return launch_picture_sse(src, rec, n_planes, bitdepth, reinterpret_cast<unsigned long long *>(d_sse), (cudaStream_t)stream);
+}
+
+int kvz_cuda_sao_ctu_stats(const kvz_cuda_plane *orig, const kvz_cuda_plane *rec, int n_planes, int bitdepth,
+                           kvz_cuda_sao_stats *d_stats, void *stream)
+{
+  if (!orig || !rec || !d_stats) return fail_msg("kvz_cuda_sao_ctu_stats: bad argument");
+  if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_sao_ctu_stats: bitdepth must be 8..16");
+  return launch_sao_stats(orig, rec, n_planes, bitdepth, d_stats, (cudaStream_t)stream);
+}
+
+int kvz_cuda_sao_reconstruct(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out, int n_planes, int bitdepth,
+                             const kvz_cuda_sao_params *d_luma, const kvz_cuda_sao_params *d_chroma, void *stream)
+{
+  if (!rec_in || !rec_out || !d_luma || (n_planes > 1 && !d_chroma)) return fail_msg("kvz_cuda_sao_reconstruct: bad argument");
+  if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_sao_reconstruct: bitdepth must be 8..16");
+  return launch_sao_apply(rec_in, rec_out, n_planes, bitdepth, d_luma, d_chroma, (cudaStream_t)stream);
 }
 
 int kvz_cuda_transform_blocks(int n, int dst4, int inverse, int bitdepth, const int16_t *d_in, int16_t *d_out,

@@ -93,4 +93,20 @@ for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (384
         out["stages"][f"{label}_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(rd * nbytes / ms / 1e6, 1),
                                             "frac_of_hbm": round(rd * nbytes / ms / 1e6 / HBM, 3),
                                             "note": "one launch + one memset per picture; the planes fit in L2, so this is launch latency, not HBM"}
+    # SAO: statistics pass and reconstruction of the whole picture
+    st_fn = lambda: blocks.sao_ctu_stats(a, b, bd)
+    ms = timed(st_fn, 20)
+    out["stages"][f"sao_ctu_stats_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(2 * nbytes / ms / 1e6, 1),
+                                              "frac_of_hbm": round(2 * nbytes / ms / 1e6 / HBM, 3),
+                                              "note": "all 4 edge classes + 32 bands per CTU and plane, one launch"}
+    counts = blocks.sao_ctu_counts(a)
+    prm = np.zeros(counts[0], blocks.SAO_PARAMS_DT); prm["type"] = 2; prm["eo_class"] = np.arange(counts[0]) % 4
+    prm["offsets"] = (0, 2, 1, -1, -2, 0, 2, 1, -1, -2)
+    prc = prm[:counts[1]].copy()
+    d_l, d_c = blocks._dev(prm), blocks._dev(prc)
+    outp = [torch.empty_like(t) for t in a]
+    ms = timed(lambda: blocks.sao_reconstruct(b, outp, d_l, d_c, bd), 20)
+    out["stages"][f"sao_reconstruct_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(2 * nbytes / ms / 1e6, 1),
+                                                "frac_of_hbm": round(2 * nbytes / ms / 1e6 / HBM, 3),
+                                                "note": "edge offsets in every CTU, one launch"}
 print(json.dumps(out))
