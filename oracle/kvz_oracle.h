@@ -71,6 +71,29 @@ int kvzo_select_mv_cand(const int16_t mv_cand[2][2], int mv_x, int mv_y);
 void kvzo_fwd_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
 void kvzo_inv_transform(int n, int dst4, int bitdepth, const int16_t *in, int16_t *out);
 
+/* the fields of cu_info_t (cu.h:134-175) the deblocking filter reads, one record per 4x4 SCU, raster order */
+typedef struct {
+  uint8_t type;             /* cu_type_t: 1 intra, 2 inter */
+  uint8_t depth, tr_depth;  /* CU and TU quadtree depths (CU width = 64 >> depth) */
+  uint8_t part_size;        /* part_mode_t 0..7 */
+  uint8_t cbf_y;            /* cbf_is_set(cbf, tr_depth, COLOR_Y) */
+  uint8_t mv_dir;           /* inter.mv_dir: 1 L0, 2 L1, 3 both */
+  uint8_t mv_ref[2];        /* inter.mv_ref */
+  int16_t mv[2][2];         /* inter.mv, quarter-pel */
+  int8_t qp;
+  uint8_t reserved[3];
+} kvzo_scu;                 /* 20 bytes */
+
+typedef struct {
+  int32_t width, height;    /* frame (tile) size in luma samples, multiples of 8 */
+  int32_t qp;               /* state->qp */
+  int32_t cu_qp;            /* encoder_control->max_qp_delta_depth >= 0: QP averaged over the two CUs */
+  int32_t beta_offset_div2, tc_offset_div2;   /* cfg.deblock_beta, cfg.deblock_tc */
+  int32_t slice_b;          /* frame->slicetype == KVZ_SLICE_B */
+  int32_t chroma;           /* chroma_format != KVZ_CSP_400 */
+  uint8_t ref_LX[2][16];    /* frame->ref_LX */
+} kvzo_deblock_cfg;
+
 /* the fields of sao_info_t (sao.h:43-51) the SAO filters and distortion functions read */
 typedef struct {
   int32_t type;             /* 0 SAO_TYPE_NONE, 1 SAO_TYPE_BAND, 2 SAO_TYPE_EDGE */
@@ -191,6 +214,9 @@ void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, con
                                         int new_stride, int bw, int bh, int color); \
   void kvzo_sao_reconstruct_##SFX(const PIX *pre, PIX *out, int frame_w, int frame_h, int x, int y, int w, int h, \
                                   const kvzo_sao_info *sao, int color); \
+  /* kvz_filter_deblock_lcu (filter.c:770-779) for every LCU of the picture in raster order, in place; \
+   * luma stride == width, chroma stride == width / 2 */ \
+  void kvzo_deblock_picture_##SFX(const kvzo_deblock_cfg *c, const kvzo_scu *scus, PIX *y, PIX *u, PIX *v); \
   /* test helper: SAD of one PU over the whole zero-centred window */ \
   void kvzo_dense_sad_map_##SFX(const PIX *pic, const PIX *ref, int W, int H, int x, int y, \
                                 int bw, int bh, int r, uint32_t *out); \

@@ -535,3 +535,63 @@ int ref_shim_sao_reconstruct(const kvz_pixel *pre, kvz_pixel *out, int luma_w, i
   free(e);
   return 1;
 }
+
+/* ---- deblocking: kvz_filter_deblock_lcu (filter.c:770-779) over a whole picture on a fake frame ---- */
+#include "filter.h"
+#include "cu.h"
+
+typedef struct {
+  uint8_t type, depth, tr_depth, part_size, cbf_y, mv_dir, mv_ref[2];
+  int16_t mv[2][2];
+  int8_t qp;
+  uint8_t reserved[3];
+} ref_scu;
+
+typedef struct {
+  int32_t width, height, qp, cu_qp, beta_offset_div2, tc_offset_div2, slice_b, chroma;
+  uint8_t ref_LX[2][16];
+} ref_deblock_cfg;
+
+int ref_shim_deblock_picture(const ref_deblock_cfg *c, const ref_scu *scus, kvz_pixel *y, kvz_pixel *u, kvz_pixel *v)
+{
+  fake_env *e = calloc(1, sizeof(*e));
+  e->state.encoder_control = &e->ctrl;
+  e->state.tile = &e->tile;
+  e->state.frame = &e->frame;
+  e->tile.frame = &e->vframe;
+  e->ctrl.bitdepth = KVZ_BIT_DEPTH;
+  e->ctrl.chroma_format = c->chroma ? KVZ_CSP_420 : KVZ_CSP_400;
+  e->ctrl.max_qp_delta_depth = c->cu_qp ? 0 : -1;
+  e->ctrl.cfg.deblock_beta = c->beta_offset_div2;
+  e->ctrl.cfg.deblock_tc = c->tc_offset_div2;
+  e->state.qp = (int8_t)c->qp;
+  e->frame.QP = (int8_t)c->qp;
+  e->frame.slicetype = c->slice_b ? KVZ_SLICE_B : KVZ_SLICE_P;
+  memcpy(e->frame.ref_LX, c->ref_LX, sizeof(c->ref_LX));
+  e->vframe.width = c->width; e->vframe.height = c->height;
+  e->vframe.width_in_lcu = (c->width + 63) / 64; e->vframe.height_in_lcu = (c->height + 63) / 64;
+  e->vframe.rec = &e->pic;
+  e->pic.width = c->width; e->pic.height = c->height; e->pic.stride = c->width;
+  e->pic.y = e->pic.data[0] = y; e->pic.u = e->pic.data[1] = u; e->pic.v = e->pic.data[2] = v;
+  e->pic.chroma_format = e->ctrl.chroma_format;
+  e->vframe.cu_array = kvz_cu_array_alloc(c->width, c->height);
+  for (int sy = 0; sy < c->height / 4; sy++)
+    for (int sx = 0; sx < c->width / 4; sx++) {
+      const ref_scu *s = &scus[sy * (c->width / 4) + sx];
+      cu_info_t *cu = kvz_cu_array_at(e->vframe.cu_array, sx * 4, sy * 4);
+      memset(cu, 0, sizeof(*cu));
+      cu->type = s->type; cu->depth = s->depth; cu->tr_depth = s->tr_depth; cu->part_size = s->part_size;
+      cu->qp = (uint8_t)s->qp;
+      if (s->cbf_y) cbf_set(&cu->cbf, s->tr_depth, COLOR_Y);
+      if (s->type == CU_INTER) {
+        cu->inter.mv_dir = s->mv_dir;
+        cu->inter.mv_ref[0] = s->mv_ref[0]; cu->inter.mv_ref[1] = s->mv_ref[1];
+        memcpy(cu->inter.mv, s->mv, sizeof(s->mv));
+      }
+    }
+  for (int ly = 0; ly < c->height; ly += 64)
+    for (int lx = 0; lx < c->width; lx += 64) kvz_filter_deblock_lcu(&e->state, lx, ly);
+  kvz_cu_array_free(&e->vframe.cu_array);
+  free(e);
+  return 1;
+}
