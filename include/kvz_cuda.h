@@ -313,6 +313,40 @@ KVZ_CUDA_API int kvz_cuda_picture_sse(const kvz_cuda_plane *src, const kvz_cuda_
                                       int bitdepth, uint64_t *d_sse, void *stream);
 
 /* ------------------------------------------------------------------ */
+/* BATCH face: deblocking filter                     */
+/* ------------------------------------------------------------------ */
+
+/* The fields of cu_info_t (cu.h:134-175) the filter reads; one record per 4x4 SCU of the frame (tile), raster
+ * order, width / 4 records per row -- the device-side mirror of frame->cu_array. */
+typedef struct kvz_cuda_scu {
+  uint8_t type;                 /* cu_type_t: 1 CU_INTRA, 2 CU_INTER */
+  uint8_t depth, tr_depth;      /* CU width = 64 >> depth, TU width = 64 >> tr_depth */
+  uint8_t part_size;            /* part_mode_t 0..7 */
+  uint8_t cbf_y;                /* cbf_is_set(cu->cbf, cu->tr_depth, COLOR_Y) */
+  uint8_t mv_dir;               /* inter.mv_dir */
+  uint8_t mv_ref[2];            /* inter.mv_ref */
+  int16_t mv[2][2];             /* inter.mv */
+  int8_t qp;                    /* cu->qp (read when cu_qp != 0) */
+  uint8_t reserved[3];
+} kvz_cuda_scu;                 /* 20 bytes */
+
+typedef struct kvz_cuda_deblock_cfg {
+  int32_t width, height;        /* state->tile->frame size in luma samples, multiples of 8 */
+  int32_t qp;                   /* state->qp */
+  int32_t cu_qp;                /* encoder_control->max_qp_delta_depth >= 0 (get_qp_y_pred, filter.c:263-285) */
+  int32_t beta_offset_div2, tc_offset_div2;   /* cfg.deblock_beta, cfg.deblock_tc */
+  int32_t slice_b;              /* state->frame->slicetype == KVZ_SLICE_B */
+  int32_t reserved;
+  uint8_t ref_LX[2][16];        /* state->frame->ref_LX (B-slice strength rule, filter.c:436-441) */
+} kvz_cuda_deblock_cfg;
+
+/* kvz_filter_deblock_lcu (filter.c:770-779) for every LCU of the picture: planes[0] luma and, with n_planes == 3,
+ * the two chroma planes of a 4:2:0 picture, filtered IN PLACE.  Two launches: all vertical edges, then all
+ * horizontal edges (the order the reference's LCU walk and its postponed rightmost columns implement). */
+KVZ_CUDA_API int kvz_cuda_deblock_picture(const kvz_cuda_deblock_cfg *cfg, const kvz_cuda_scu *d_scus,
+                                          const kvz_cuda_plane *planes, int n_planes, int bitdepth, void *stream);
+
+/* ------------------------------------------------------------------ */
 /* BATCH face: sample adaptive offset                */
 /* ------------------------------------------------------------------ */
 

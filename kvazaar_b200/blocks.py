@@ -119,6 +119,28 @@ def sao_reconstruct(rec_planes, out_planes, luma_params, chroma_params, bitdepth
     return out_planes
 
 
+SCU_DT = np.dtype([("type", "u1"), ("depth", "u1"), ("tr_depth", "u1"), ("part_size", "u1"), ("cbf_y", "u1"),
+                   ("mv_dir", "u1"), ("mv_ref", "u1", (2,)), ("mv", "<i2", (2, 2)), ("qp", "i1"), ("reserved", "u1", (3,))])
+assert SCU_DT.itemsize == 20
+
+
+def deblock_picture(planes, scus, qp, cu_qp=0, beta_offset_div2=0, tc_offset_div2=0, slice_b=0, ref_LX=None, bitdepth=8):
+    """kvz_cuda_deblock_picture: planes = [luma] or [luma, u, v] device tensors, filtered in place;
+    scus: numpy SCU_DT array (height / 4, width / 4) or a device tensor of its bytes"""
+    capi.init(torch.cuda.current_device())
+    cfg = capi.DeblockCfg()
+    cfg.height, cfg.width = planes[0].shape
+    cfg.qp, cfg.cu_qp, cfg.beta_offset_div2, cfg.tc_offset_div2, cfg.slice_b = qp, cu_qp, beta_offset_div2, tc_offset_div2, slice_b
+    for l in range(2):
+        for i in range(16):
+            cfg.ref_LX[l][i] = ref_LX[l][i] if ref_LX is not None else i
+    d_scus = _dev(scus) if isinstance(scus, np.ndarray) else scus
+    arr = _planes(planes)
+    capi.check(capi.lib().kvz_cuda_deblock_picture(C.byref(cfg), _p(d_scus), C.addressof(arr), len(planes), bitdepth, _stream()),
+               "kvz_cuda_deblock_picture")
+    return planes
+
+
 RESIDUAL_JOB_DT = np.dtype([("ref_offset", "<u4"), ("pred_offset", "<u4"), ("rec_offset", "<u4"),
                             ("coeff_offset", "<u4"), ("in_stride", "<i4"), ("out_stride", "<i4"),
                             ("width", "u1"), ("color", "u1"), ("scan_idx", "u1"), ("use_trskip", "u1"),

@@ -43,6 +43,13 @@ class Plane(C.Structure):
     _fields_ = [("d_data", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("pitch", C.c_int32)]
 
 
+class DeblockCfg(C.Structure):
+    """kvz_cuda_deblock_cfg"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("qp", C.c_int32), ("cu_qp", C.c_int32),
+                ("beta_offset_div2", C.c_int32), ("tc_offset_div2", C.c_int32), ("slice_b", C.c_int32),
+                ("reserved", C.c_int32), ("ref_LX", (C.c_uint8 * 16) * 2)]
+
+
 class ImeBoxRef(C.Structure):
     """kvz_cuda_ime_box_ref"""
     _fields_ = [("desc", ImeBoxDesc), ("d_ref_padded", C.c_void_p), ("d_sad8", C.c_void_p), ("d_sad16", C.c_void_p),
@@ -110,6 +117,7 @@ SIGNATURES = {
     "kvz_cuda_picture_sse": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_sao_ctu_stats": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_sao_reconstruct": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),
+    "kvz_cuda_deblock_picture": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

@@ -31,6 +31,11 @@ int launch_sao_apply(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out
 }
 
 namespace kvz {
+int launch_deblock_picture(const kvz_cuda_deblock_cfg &cfg, const kvz_cuda_scu *d_scus, const kvz_cuda_plane *planes,
+                           int n_planes, int bitdepth, cudaStream_t stream);
+}
+
+namespace kvz {
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
@@ -348,6 +353,17 @@ int kvz_cuda_sao_reconstruct(const kvz_cuda_plane *rec_in, const kvz_cuda_plane 
   if (!rec_in || !rec_out || !d_luma || (n_planes > 1 && !d_chroma)) return fail_msg("kvz_cuda_sao_reconstruct: bad argument");
   if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_sao_reconstruct: bitdepth must be 8..16");
   return launch_sao_apply(rec_in, rec_out, n_planes, bitdepth, d_luma, d_chroma, (cudaStream_t)stream);
+}
+
+int kvz_cuda_deblock_picture(const kvz_cuda_deblock_cfg *cfg, const kvz_cuda_scu *d_scus, const kvz_cuda_plane *planes,
+                             int n_planes, int bitdepth, void *stream)
+{
+  if (!cfg || !d_scus || !planes || (n_planes != 1 && n_planes != 3)) return fail_msg("kvz_cuda_deblock_picture: bad argument");
+  if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_deblock_picture: bitdepth must be 8..16");
+  if (cfg->width < 8 || cfg->height < 8 || (cfg->width & 7) || (cfg->height & 7))
+    return fail_msg("kvz_cuda_deblock_picture: width and height must be positive multiples of 8");
+  if (cfg->qp < 0 || cfg->qp > 51) return fail_msg("kvz_cuda_deblock_picture: qp must be 0..51");
+  return launch_deblock_picture(*cfg, d_scus, planes, n_planes, bitdepth, (cudaStream_t)stream);
 }
 
 int kvz_cuda_transform_blocks(int n, int dst4, int inverse, int bitdepth, const int16_t *d_in, int16_t *d_out,

@@ -109,4 +109,14 @@ for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (384
     out["stages"][f"sao_reconstruct_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(2 * nbytes / ms / 1e6, 1),
                                                 "frac_of_hbm": round(2 * nbytes / ms / 1e6 / HBM, 3),
                                                 "note": "edge offsets in every CTU, one launch"}
+# deblocking: whole 4:2:0 pictures, random CU quadtrees, two launches per picture
+import deblock_oracle as dbo
+for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (3840, 2160), 10)):
+    scus = blocks._dev(dbo.random_scus(rs, pw, ph, p_intra=0.3).view(blocks.SCU_DT))
+    pl = [torch.from_numpy(p.view(np.int16) if bd > 8 else p).cuda() for p in dbo.picture(rs, pw, ph, bd)]
+    nbytes = sum(t.numel() * t.element_size() for t in pl)
+    ms = timed(lambda: blocks.deblock_picture(pl, scus, 32, bitdepth=bd), 20)
+    out["stages"][f"deblock_picture_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(2 * nbytes / ms / 1e6, 1),
+                                                "frac_of_hbm": round(2 * nbytes / ms / 1e6 / HBM, 3),
+                                                "note": "vertical-edge pass + horizontal-edge pass, in place; one thread per 4-sample edge segment"}
 print(json.dumps(out))
