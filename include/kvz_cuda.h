@@ -455,7 +455,8 @@ typedef struct kvz_cuda_rdoq_ctx {
   uint8_t one_luma[16], one_chroma[8];           /* cu_one_model_luma / _chroma */
   uint8_t abs_luma[4], abs_chroma[2];            /* cu_abs_model_luma / _chroma */
   uint8_t root_cbf;                              /* cu_qt_root_cbf_model */
-  uint8_t reserved[3];
+  uint8_t trskip_luma, trskip_chroma;               /* transform_skip_model_luma / _chroma (kvz_cuda_coeff_bits only) */
+  uint8_t reserved;
 } kvz_cuda_rdoq_ctx;                             /* 148 bytes */
 
 /* one kvz_rdoq() call (rdo.c:548-551) */

@@ -211,7 +211,7 @@ RDOQ_CTX_DT = np.dtype([("cbf_luma", "u1", (4,)), ("cbf_chroma", "u1", (4,)), ("
                         ("last_x_luma", "u1", (15,)), ("last_x_chroma", "u1", (15,)),
                         ("one_luma", "u1", (16,)), ("one_chroma", "u1", (8,)),
                         ("abs_luma", "u1", (4,)), ("abs_chroma", "u1", (2,)),
-                        ("root_cbf", "u1"), ("reserved", "u1", (3,))])
+                        ("root_cbf", "u1"), ("trskip_luma", "u1"), ("trskip_chroma", "u1"), ("reserved", "u1")])
 assert RDOQ_CTX_DT.itemsize == 148
 RDOQ_JOB_DT = np.dtype([("coef_offset", "<u4"), ("ctx_index", "<u4"), ("lambda", "<f8"), ("width", "u1"),
                         ("type", "u1"), ("scan_idx", "u1"), ("tr_depth", "u1"), ("qp", "i1"),

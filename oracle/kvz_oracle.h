@@ -134,8 +134,15 @@ typedef struct {
   uint8_t one_luma[16], one_chroma[8];           /* cu_one_model_* */
   uint8_t abs_luma[4], abs_chroma[2];            /* cu_abs_model_* */
   uint8_t root_cbf;                              /* cu_qt_root_cbf_model */
-  uint8_t reserved[3];
+  uint8_t trskip_luma, trskip_chroma;            /* transform_skip_model_luma / _chroma */
+  uint8_t reserved;
 } kvzo_rdoq_ctx;                                 /* 148 bytes */
+
+/* get_coeff_cabac_cost (rdo.c:158-197): bits kvz_encode_coeff_nxn (encode_coding_tree.c:103-345) spends on the
+ * block in counting mode, starting from the coder range `range` (state->cabac.range) and the context states of
+ * `ctx` (not modified).  0 for an all-zero block. */
+uint32_t kvzo_coeff_cabac_bits(const kvzo_rdoq_ctx *ctx, uint32_t range, const int16_t *coeff, int width, int type,
+                               int scan_mode, int signhide, int trskip_enable);
 
 /* kvz_rdoq (rdo.c:548-885) + kvz_rdoq_sign_hiding (rdo.c:405-540), flat scaling list.
  * type 0 luma / 2 chroma, scan_idx 0 diag / 1 hor / 2 ver (hor/ver only for width <= 8).

@@ -420,3 +420,182 @@ void kvzo_rdoq(const kvzo_q_cfg *c, double lambda, const kvzo_rdoq_ctx *ctx, con
   if (c->signhide && abs_sum >= 2)
     hide_signs(lambda, c->bitdepth, qp_scaled, scan, hr, coded_end, coef, dest);
 }
+
+/* ======================================================================================
+ * kvz_get_coeff_cost's CABAC path (rdo.c:158-197): the bits kvz_encode_coeff_nxn
+ * (encode_coding_tree.c:103-345) spends on a block when run on a copy of the CABAC state in counting mode.
+ * In that mode kvz_cabac_write only counts bytes (cabac.c:128-137), so
+ *   (23 - bits_left) + 8 * num_buffered_bytes  ==  the total of all renormalisation shifts,
+ * a function of the coder's `range` and the context states only (`low` never matters).
+ * ====================================================================================== */
+
+/* HEVC table 9-46 (rangeTabLps), cabac.c:52-67 */
+static const uint8_t k_range_lps[64][4] = {
+  {128, 176, 208, 240}, {128, 167, 197, 227}, {128, 158, 187, 216}, {123, 150, 178, 205}, {116, 142, 169, 195},
+  {111, 135, 160, 185}, {105, 128, 152, 175}, {100, 122, 144, 166}, { 95, 116, 137, 158}, { 90, 110, 130, 150},
+  { 85, 104, 123, 142}, { 81,  99, 117, 135}, { 77,  94, 111, 128}, { 73,  89, 105, 122}, { 69,  85, 100, 116},
+  { 66,  80,  95, 110}, { 62,  76,  90, 104}, { 59,  72,  86,  99}, { 56,  69,  81,  94}, { 53,  65,  77,  89},
+  { 51,  62,  73,  85}, { 48,  59,  69,  80}, { 46,  56,  66,  76}, { 43,  53,  63,  72}, { 41,  50,  59,  69},
+  { 39,  48,  56,  65}, { 37,  45,  54,  62}, { 35,  43,  51,  59}, { 33,  41,  48,  56}, { 32,  39,  46,  53},
+  { 30,  37,  43,  50}, { 29,  35,  41,  48}, { 27,  33,  39,  45}, { 26,  31,  37,  43}, { 24,  30,  35,  41},
+  { 23,  28,  33,  39}, { 22,  27,  32,  37}, { 21,  26,  30,  35}, { 20,  24,  29,  33}, { 19,  23,  27,  31},
+  { 18,  22,  26,  30}, { 17,  21,  25,  28}, { 16,  20,  23,  27}, { 15,  19,  22,  25}, { 14,  18,  21,  24},
+  { 14,  17,  20,  23}, { 13,  16,  19,  22}, { 12,  15,  18,  21}, { 12,  14,  17,  20}, { 11,  14,  16,  19},
+  { 11,  13,  15,  18}, { 10,  12,  15,  17}, { 10,  12,  14,  16}, {  9,  11,  13,  15}, {  9,  11,  12,  14},
+  {  8,  10,  12,  14}, {  8,   9,  11,  13}, {  7,   9,  11,  12}, {  7,   9,  10,  12}, {  7,   8,  10,  11},
+  {  6,   8,   9,  11}, {  6,   7,   9,  10}, {  6,   7,   8,   9}, {  2,   2,   2,   2} };
+/* HEVC table 9-47 (transIdxLps); the MPS transition is state + 1 up to 62 */
+static const uint8_t k_next_lps[64] = { 0, 0, 1, 2, 2, 4, 4, 5, 6, 7, 8, 9, 9, 11, 11, 12, 13, 13, 15, 15, 16, 16, 18, 18,
+  19, 19, 21, 21, 22, 22, 23, 24, 24, 25, 26, 26, 27, 27, 28, 29, 29, 30, 30, 30, 31, 32, 32, 33, 33, 33, 34, 34, 35,
+  35, 35, 36, 36, 36, 37, 37, 37, 38, 38, 63 };
+static const uint8_t k_min_in_group[10] = { 0, 1, 2, 3, 4, 6, 8, 12, 16, 24 };      /* encoderstate.h:351 */
+
+typedef struct { uint32_t range; uint32_t bits; } bit_counter;
+
+static int log2_of(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
+
+/* kvz_cabac_encode_bin (cabac.c:91-120) without `low`; state = (pStateIdx << 1) | valMps as in cabac_ctx_t */
+static void count_bin(bit_counter *b, uint8_t *state, int bin)
+{
+  const uint32_t lps = k_range_lps[*state >> 1][(b->range >> 6) & 3];
+  b->range -= lps;
+  if ((bin ? 1 : 0) != (*state & 1)) {
+    /* kvz_g_auc_renorm_table[lps >> 3] (cabac.c:69-73): the shift that brings lps back to >= 256 (state 63's
+     * lps of 2 is only ever used by the terminating bin, its table entry is 6 like any lps < 8) */
+    static const uint8_t renorm[32] = { 6, 5, 4, 4, 3, 3, 3, 3, 2, 2, 2, 2, 2, 2, 2, 2,
+                                        1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1 };
+    const int shift = renorm[lps >> 3];
+    b->range = lps << shift;
+    b->bits += shift;
+    const int st = *state >> 1;
+    *state = st == 0 ? (uint8_t)(*state ^ 1) : (uint8_t)((k_next_lps[st] << 1) | (*state & 1));
+  } else {
+    if ((*state >> 1) < 62) *state += 2;
+    if (b->range < 256) { b->range <<= 1; b->bits += 1; }
+  }
+}
+
+static void count_remaining(bit_counter *b, uint32_t symbol, uint32_t rice)
+{
+  /* kvz_cabac_write_coeff_remain (cabac.c:317-337): bypass bins only */
+  if (symbol < (3u << rice)) {
+    b->bits += (symbol >> rice) + 1 + rice;
+  } else {
+    uint32_t length = rice, code = symbol - (3u << rice);
+    while (code >= (1u << length)) { code -= 1u << length; length++; }
+    b->bits += (3 + length + 1 - rice) + length;
+  }
+}
+
+uint32_t kvzo_coeff_cabac_bits(const kvzo_rdoq_ctx *ctx_in, uint32_t range, const int16_t *coeff, int width, int type,
+                               int scan_mode, int signhide, int trskip_enable)
+{
+  const int nn = width * width, lg = log2_of(width), side = width >> 2, is_chroma = type != 0;
+  int any = 0;
+  for (int i = 0; i < nn; i++) any |= coeff[i] != 0;
+  if (!any) return 0;                                         /* rdo.c:166-173 */
+
+  kvzo_rdoq_ctx ctx = *ctx_in;                                /* the coder updates its copy of the contexts */
+  bit_counter b = { range, 0 };
+  uint32_t scan[32 * 32], scan_cg[64];
+  kvzo_scan_order(scan_mode, lg, scan);
+  for (int g = 0; g < side * side; g++) {                     /* group order = where each 16-run of the scan lies */
+    const uint32_t bp = scan[g * 16];
+    scan_cg[g] = ((bp >> lg) >> 2) * side + ((bp & (width - 1)) >> 2);
+  }
+  uint8_t group_sig[64];
+  memset(group_sig, 0, sizeof(group_sig));
+  for (int i = 0; i < nn; i++)
+    if (coeff[i]) group_sig[((i >> lg) >> 2) * side + ((i & (width - 1)) >> 2)] = 1;
+
+  int cg_last = side * side - 1;
+  while (!group_sig[scan_cg[cg_last]]) cg_last--;
+  int pos_last_scan = cg_last * 16 + 15;
+  while (!coeff[scan[pos_last_scan]]) pos_last_scan--;
+  const int pos_last = scan[pos_last_scan];
+
+  if (width == 4 && trskip_enable) count_bin(&b, is_chroma ? &ctx.trskip_chroma : &ctx.trskip_luma, 0);
+
+  {
+    /* encode_last_significant_xy (encode_coding_tree.c:49-101) */
+    int lx = pos_last & (width - 1), ly = pos_last >> lg;
+    const int index = lg - 2;
+    const int ctx_offset = is_chroma ? 0 : index * 3 + (index + 1) / 4;
+    const int shift = is_chroma ? index : (index + 3) / 4;
+    uint8_t *mx = is_chroma ? ctx.last_x_chroma : ctx.last_x_luma, *my = is_chroma ? ctx.last_y_chroma : ctx.last_y_luma;
+    if (scan_mode == 2) { const int t = lx; lx = ly; ly = t; }
+    const int gx = k_last_group[lx], gy = k_last_group[ly], gmax = k_last_group[width - 1];
+    for (int i = 0; i < gx; i++) count_bin(&b, &mx[ctx_offset + (i >> shift)], 1);
+    if (gx < gmax) count_bin(&b, &mx[ctx_offset + (gx >> shift)], 0);
+    for (int i = 0; i < gy; i++) count_bin(&b, &my[ctx_offset + (i >> shift)], 1);
+    if (gy < gmax) count_bin(&b, &my[ctx_offset + (gy >> shift)], 0);
+    if (gx > 3) b.bits += (gx - 2) / 2;
+    if (gy > 3) b.bits += (gy - 2) / 2;
+    (void)k_min_in_group;                                     /* the suffix VALUE does not change the bit count */
+  }
+
+  uint8_t *sig_models = is_chroma ? ctx.sig_chroma : ctx.sig_luma;
+  int c1 = 1, scan_pos = pos_last_scan;
+  for (int g = cg_last; g >= 0; g--) {
+    const int sub_pos = g << 4, cg_blk = scan_cg[g], cgy = cg_blk / side, cgx = cg_blk - cgy * side;
+    int abs_coeff[16], n_nz = 0, last_nz = -1, first_nz = 16;
+    uint32_t rice = 0;
+    if (scan_pos == pos_last_scan) {
+      abs_coeff[0] = abs(coeff[pos_last]);
+      n_nz = 1; last_nz = first_nz = scan_pos;
+      scan_pos--;
+    }
+    if (g == cg_last || g == 0) {
+      group_sig[cg_blk] = 1;
+    } else {
+      const int nb = neighbour_groups(group_sig, cgx, cgy, side);
+      count_bin(&b, &ctx.sig_group[type + (nb != 0)], group_sig[cg_blk] != 0);   /* &cu_sig_coeff_group_model[type] */
+    }
+    if (group_sig[cg_blk]) {
+      const int pattern = width == 4 ? -1 : neighbour_groups(group_sig, cgx, cgy, side);
+      for (; scan_pos >= sub_pos; scan_pos--) {
+        const uint32_t bp = scan[scan_pos];
+        const int py = bp >> lg, px = bp - (py << lg), sig = coeff[bp] != 0;
+        if (scan_pos > sub_pos || g == 0 || n_nz)
+          count_bin(&b, &sig_models[sig_ctx_inc(pattern, scan_mode, px, py, lg, is_chroma)], sig);
+        if (sig) {
+          abs_coeff[n_nz++] = abs(coeff[bp]);
+          if (last_nz == -1) last_nz = scan_pos;
+          first_nz = scan_pos;
+        }
+      }
+    } else {
+      scan_pos = sub_pos - 1;
+    }
+    if (n_nz > 0) {
+      const int sign_hidden = last_nz - first_nz >= 4;
+      int ctx_set = (g > 0 && !is_chroma) ? 2 : 0;
+      if (c1 == 0) ctx_set++;
+      c1 = 1;
+      uint8_t *one = (is_chroma ? ctx.one_chroma : ctx.one_luma) + 4 * ctx_set;
+      const int n_c1 = n_nz < 8 ? n_nz : 8;                   /* C1FLAG_NUMBER */
+      int first_c2 = -1;
+      for (int i = 0; i < n_c1; i++) {
+        const int sym = abs_coeff[i] > 1;
+        count_bin(&b, &one[c1], sym);
+        if (sym) { c1 = 0; if (first_c2 == -1) first_c2 = i; }
+        else if (c1 < 3 && c1 > 0) c1++;
+      }
+      if (c1 == 0 && first_c2 != -1)
+        count_bin(&b, &(is_chroma ? ctx.abs_chroma : ctx.abs_luma)[ctx_set], abs_coeff[first_c2] > 2);
+      b.bits += (signhide && sign_hidden) ? n_nz - 1 : n_nz;  /* coeff_sign_flag, bypass */
+      if (c1 == 0 || n_nz > 8) {
+        int first_coeff2 = 1;
+        for (int i = 0; i < n_nz; i++) {
+          const int base = i < 8 ? 2 + first_coeff2 : 1;
+          if (abs_coeff[i] >= base) {
+            count_remaining(&b, abs_coeff[i] - base, rice);
+            if (abs_coeff[i] > 3 * (1 << rice)) rice = rice + 1 < 4 ? rice + 1 : 4;
+          }
+          if (abs_coeff[i] >= 2) first_coeff2 = 0;
+        }
+      }
+    }
+  }
+  return b.bits;
+}

@@ -384,7 +384,7 @@ typedef struct {
   uint8_t one_luma[16], one_chroma[8];
   uint8_t abs_luma[4], abs_chroma[2];
   uint8_t root_cbf;
-  uint8_t reserved[3];
+  uint8_t trskip_luma, trskip_chroma, reserved;
 } ref_rdoq_ctx;
 
 #define CTX_COPY(dir, field, member, n) \
@@ -408,6 +408,13 @@ static void ctx_transfer(int to_cabac, cabac_data_t *cab, ref_rdoq_ctx *s)
   CTX_COPY(to_cabac, abs_chroma, cu_abs_model_chroma, 2)
   if (to_cabac) cab->ctx.cu_qt_root_cbf_model.uc_state = s->root_cbf;
   else s->root_cbf = cab->ctx.cu_qt_root_cbf_model.uc_state;
+  if (to_cabac) {
+    cab->ctx.transform_skip_model_luma.uc_state = s->trskip_luma;
+    cab->ctx.transform_skip_model_chroma.uc_state = s->trskip_chroma;
+  } else {
+    s->trskip_luma = cab->ctx.transform_skip_model_luma.uc_state;
+    s->trskip_chroma = cab->ctx.transform_skip_model_chroma.uc_state;
+  }
 }
 
 /* the states kvz_init_contexts (context.c:209-300) gives a slice of this QP and type */
@@ -594,4 +601,21 @@ int ref_shim_deblock_picture(const ref_deblock_cfg *c, const ref_scu *scus, kvz_
   kvz_cu_array_free(&e->vframe.cu_array);
   free(e);
   return 1;
+}
+
+/* kvz_get_coeff_cost (rdo.c:208-222) on its CABAC path with caller-chosen context states and coder range */
+uint32_t ref_shim_coeff_cost(const ref_rdoq_ctx *ctx, uint32_t range, const coeff_t *coeff, int width, int type,
+                             int scan_mode, int signhide, int trskip_enable)
+{
+  ref_q_cfg c; memset(&c, 0, sizeof(c));
+  c.qp = 30; c.rdoq = 1; c.signhide = signhide;
+  fake_qenv *e = qenv_make(&c);
+  ref_rdoq_ctx tmp = *ctx;
+  ctx_transfer(1, &e->state.cabac, &tmp);
+  e->state.cabac.range = range;
+  e->ctrl.cfg.fast_residual_cost_limit = 0;
+  e->ctrl.cfg.trskip_enable = trskip_enable;
+  uint32_t bits = kvz_get_coeff_cost(&e->state, coeff, width, type, (int8_t)scan_mode);
+  qenv_free(e);
+  return bits;
 }

@@ -91,7 +91,7 @@ class RdoqCtx(C.Structure):
                 ("last_x_luma", C.c_uint8 * 15), ("last_x_chroma", C.c_uint8 * 15),
                 ("one_luma", C.c_uint8 * 16), ("one_chroma", C.c_uint8 * 8),
                 ("abs_luma", C.c_uint8 * 4), ("abs_chroma", C.c_uint8 * 2),
-                ("root_cbf", C.c_uint8), ("reserved", C.c_uint8 * 3)]
+                ("root_cbf", C.c_uint8), ("trskip_luma", C.c_uint8), ("trskip_chroma", C.c_uint8), ("reserved", C.c_uint8)]
 
 
 assert C.sizeof(RdoqCtx) == 148
@@ -100,7 +100,7 @@ assert C.sizeof(RdoqCtx) == 148
 def random_rdoq_ctx(rs):
     """context states drawn uniformly from the 128 (state, MPS) pairs"""
     raw = rs.integers(0, 128, 148, dtype=np.uint8)
-    raw[145:] = 0
+    raw[147:] = 0
     return RdoqCtx.from_buffer_copy(raw.tobytes())
 
 
