@@ -481,6 +481,28 @@ KVZ_CUDA_API int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_c
                                       const int16_t *d_coef, int16_t *d_q_coef,
                                       const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, void *stream);
 
+typedef struct kvz_cuda_coeff_job {
+  uint32_t coef_offset;               /* first coefficient of the block in d_coeffs, in int16 units */
+  uint32_t ctx_index;                 /* which snapshot of d_ctx */
+  uint16_t range;                     /* state->cabac.range when the cost is asked for (256..510) */
+  uint8_t width;                      /* 4, 8, 16, 32 */
+  uint8_t type;                       /* 0 luma, 2 chroma */
+  uint8_t scan_idx;                   /* coeff_scan_order_t */
+  uint8_t reserved[3];
+} kvz_cuda_coeff_job;                 /* 16 bytes */
+
+/* kvz_get_coeff_cost (rdo.c:208-222) on its CABAC path (state->qp >= cfg.fast_residual_cost_limit):
+ * d_bits[i] = the bits kvz_encode_coeff_nxn (encode_coding_tree.c:103-345) spends on block i when run in counting
+ * mode on a copy of the CABAC state, i.e. get_coeff_cabac_cost (rdo.c:158-197); 0 for an all-zero block.  The
+ * count depends on the coder's range and the context states only (cabac.c:128-137 counts bytes and never looks at
+ * `low`), both supplied per job; the snapshots are not modified.  signhide = cfg.signhide_enable,
+ * trskip_enable = cfg.trskip_enable (the transform_skip_flag of 4x4 blocks, always coded as 0 here as in
+ * rdo.c:188-194).  The fast estimate for low QPs, sum * (qp * COEFF_COST_QP_FACTOR + COEFF_COST_BIAS), is
+ * kvz_cuda_coeff_abs_sums plus one multiplication on the host. */
+KVZ_CUDA_API int kvz_cuda_coeff_bits(const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coeffs,
+                                     const kvz_cuda_coeff_job *d_jobs, int n_jobs, int max_width, int signhide,
+                                     int trskip_enable, uint32_t *d_bits, void *stream);
+
 /* kvz_quantize_residual (quant-generic.c:180-273) with cfg.rdoq_enable: residual -> transform -> kvz_rdoq ->
  * dequant -> inverse transform -> reconstruction.  d_rdoq_jobs[i] describes the kvz_rdoq call of d_jobs[i]
  * (same width; coef_offset == coeff_offset; type 0 for colour Y, 2 otherwise; tr_depth as computed at

@@ -233,6 +233,24 @@ def rdoq_blocks(d_coef, ctxs, jobs, signhide=False, bitdepth=8):
     return out
 
 
+COEFF_JOB_DT = np.dtype([("coef_offset", "<u4"), ("ctx_index", "<u4"), ("range", "<u2"), ("width", "u1"), ("type", "u1"),
+                         ("scan_idx", "u1"), ("reserved", "u1", (3,))])
+assert COEFF_JOB_DT.itemsize == 16
+
+
+def coeff_bits(d_coeffs, ctxs, jobs, signhide=False, trskip_enable=False):
+    """kvz_get_coeff_cost's CABAC path (rdo.c:158-197) for a batch of coefficient blocks.  d_coeffs: device int16;
+    ctxs: numpy RDOQ_CTX_DT snapshots (or a device tensor of them); jobs: numpy COEFF_JOB_DT.  Returns device int32 bits."""
+    capi.init(torch.cuda.current_device())
+    d_jobs = _dev(jobs)
+    d_ctx = _dev(ctxs) if isinstance(ctxs, np.ndarray) else ctxs
+    out = torch.zeros(len(jobs), dtype=torch.int32, device="cuda")
+    max_width = int(jobs["width"].max()) if len(jobs) else 4
+    capi.check(capi.lib().kvz_cuda_coeff_bits(_p(d_ctx), _p(d_coeffs), _p(d_jobs), len(jobs), max_width, int(signhide),
+                                              int(trskip_enable), _p(out), _stream()), "kvz_cuda_coeff_bits")
+    return out
+
+
 def quantize_residuals_rdoq(d_ref, d_pred, d_rec, d_coeff, jobs, ctxs, rdoq_jobs, slice_is_intra=False, signhide=False,
                             rdoq_skip=False, bitdepth=8):
     """kvz_quantize_residual with cfg.rdoq_enable (quant-generic.c:180-273 + rdo.c:548-885) for a batch of

@@ -118,6 +118,7 @@ SIGNATURES = {
     "kvz_cuda_sao_ctu_stats": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_sao_reconstruct": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_deblock_picture": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP]),
+    "kvz_cuda_coeff_bits": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

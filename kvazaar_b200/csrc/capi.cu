@@ -36,6 +36,11 @@ int launch_deblock_picture(const kvz_cuda_deblock_cfg &cfg, const kvz_cuda_scu *
 }
 
 namespace kvz {
+int launch_coeff_bits(const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coeffs, const kvz_cuda_coeff_job *d_jobs,
+                      int n_jobs, int max_width, int signhide, int trskip_enable, uint32_t *d_bits, cudaStream_t stream);
+}
+
+namespace kvz {
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
@@ -405,6 +410,16 @@ int kvz_cuda_rdoq_blocks(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx 
   if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
     return fail_msg("kvz_cuda_rdoq_blocks: max_width must be 4, 8, 16 or 32");
   return launch_rdoq_batch(*cfg, d_ctx, d_coef, d_q_coef, d_jobs, n_jobs, max_width, 0, (cudaStream_t)stream);
+}
+
+int kvz_cuda_coeff_bits(const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coeffs, const kvz_cuda_coeff_job *d_jobs,
+                        int n_jobs, int max_width, int signhide, int trskip_enable, uint32_t *d_bits, void *stream)
+{
+  if (!d_ctx || !d_coeffs || !d_jobs || !d_bits || n_jobs < 0) return fail_msg("kvz_cuda_coeff_bits: bad argument");
+  if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
+    return fail_msg("kvz_cuda_coeff_bits: max_width must be 4, 8, 16 or 32");
+  return launch_coeff_bits(d_ctx, d_coeffs, d_jobs, n_jobs, max_width, signhide != 0, trskip_enable != 0, d_bits,
+                           (cudaStream_t)stream);
 }
 
 int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred, void *d_rec,

@@ -82,6 +82,19 @@ for lg in (2, 3, 4, 5):
     out["stages"][f"intra_costs{n}"] = {"blocks": cnt, "ms": round(ms, 4), "Mblocks_per_s": round(cnt / ms / 1e3, 1),
                                         "predicted_Gsamples_per_s": round(cnt * 35 * n * n / ms / 1e6, 1),
                                         "note": "35 predictions + SATD + SAD per PU (ALU / latency bound)"}
+# CABAC-exact coefficient bit cost: every block of the frame, quantised on device first
+for n in (4, 8, 16, 32):
+    cnt = (W // n) * (H // n)
+    resid = torch.from_numpy(rs.integers(-40, 41, cnt * n * n).astype(np.int16)).cuda()
+    lv = blocks.quant_blocks(blocks.transform_blocks(resid, n), n, 32, signhide=True)
+    cj = np.zeros(cnt, blocks.COEFF_JOB_DT)
+    cj["coef_offset"] = np.arange(cnt, dtype=np.uint32) * n * n
+    cj["ctx_index"] = np.arange(cnt) % 64
+    cj["range"], cj["width"] = 400, n
+    cctx = blocks._dev(np.frombuffer(rs.integers(0, 126, 64 * 148, dtype=np.uint8).tobytes(), blocks.RDOQ_CTX_DT).copy())
+    put(f"coeff_bits{n}", timed(lambda: blocks.coeff_bits(lv, cctx, cj, True, False)), cnt, cnt * n * n * 2,
+        "kvz_get_coeff_cost CABAC path, one warp per block (serial context chain per block)")
+
 # picture-level reductions: 4:2:0 pictures, all three planes in one launch
 for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (3840, 2160), 10)):
     dt, top = (np.uint8, 256) if bd == 8 else (np.int16, 1024)
