@@ -94,6 +94,28 @@ typedef struct {
   uint8_t ref_LX[2][16];    /* frame->ref_LX */
 } kvzo_deblock_cfg;
 
+/* what the inter candidate derivation reads of the frame (A18) */
+typedef struct {
+  int32_t width, height;          /* state->tile->frame size, luma samples */
+  int32_t in_width, in_height;    /* encoder_control->in.width / height */
+  int32_t tile_offset_x, tile_offset_y;
+  int32_t poc;                    /* state->frame->poc */
+  int32_t slice_b, tmvp_enable;
+  int32_t n_refs;                 /* state->frame->ref->used_size */
+  int32_t ref_pocs[16];           /* state->frame->ref->pocs */
+  int32_t col_ref_pocs[2][16];    /* images[c]->ref_pocs[ref_LXs[c][list][idx]] for c = ref_LX[0][0] */
+  uint8_t ref_LX[2][16];
+  uint8_t ref_LX_size[2];
+  uint8_t reserved[2];
+  int32_t ref_scu_pitch;          /* SCU records per row of the reference pictures' arrays */
+  const kvzo_scu *scus;           /* this frame (tile), width / 4 records per row */
+  const kvzo_scu *ref_scus[16];   /* state->frame->ref->cu_arrays */
+} kvzo_cand_frame;
+
+void kvzo_inter_mv_cand(const kvzo_cand_frame *f, int x, int y, int w, int h, int reflist, int lx_idx, int16_t mv_cand[2][2]);
+int kvzo_inter_merge_cand(const kvzo_cand_frame *f, int x, int y, int w, int h, int use_a1, int use_b1, kvzo_merge_cand out[5]);
+void kvzo_colocated_start_mv(const kvzo_cand_frame *f, int x, int y, int w, int h, int ref_idx, int16_t mv[2]);
+
 /* the fields of sao_info_t (sao.h:43-51) the SAO filters and distortion functions read */
 typedef struct {
   int32_t type;             /* 0 SAO_TYPE_NONE, 1 SAO_TYPE_BAND, 2 SAO_TYPE_EDGE */

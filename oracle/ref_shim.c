@@ -619,3 +619,125 @@ uint32_t ref_shim_coeff_cost(const ref_rdoq_ctx *ctx, uint32_t range, const coef
   qenv_free(e);
   return bits;
 }
+
+/* ---- inter candidate derivation (A18): kvz_inter_get_merge_cand / kvz_inter_get_mv_cand on a fake frame ---- */
+#include "inter.h"
+#include "imagelist.h"
+
+typedef struct {
+  int32_t width, height, in_width, in_height, tile_offset_x, tile_offset_y, poc, slice_b, tmvp_enable, n_refs;
+  int32_t ref_pocs[16];
+  int32_t col_ref_pocs[2][16];
+  uint8_t ref_LX[2][16];
+  uint8_t ref_LX_size[2];
+  uint8_t reserved[2];
+  int32_t ref_scu_pitch;
+  const ref_scu *scus;
+  const ref_scu *ref_scus[16];
+} ref_cand_frame;
+
+typedef struct {
+  fake_env env;
+  image_list_t list;
+  kvz_picture *images[16];
+  kvz_picture pics[16];
+  cu_array_t *cuas[16];
+  int32_t pocs[16];
+  uint8_t ref_LXs[16][2][16];
+  lcu_t lcu;
+} cand_env;
+
+static void cu_from_scu(cu_info_t *cu, const ref_scu *s)
+{
+  memset(cu, 0, sizeof(*cu));
+  cu->type = s->type; cu->depth = s->depth; cu->tr_depth = s->tr_depth; cu->part_size = s->part_size;
+  if (s->type == CU_INTER) {
+    cu->inter.mv_dir = s->mv_dir;
+    cu->inter.mv_ref[0] = s->mv_ref[0]; cu->inter.mv_ref[1] = s->mv_ref[1];
+    memcpy(cu->inter.mv, s->mv, sizeof(s->mv));
+  }
+}
+
+static cand_env *cand_env_make(const ref_cand_frame *f, int x, int y)
+{
+  cand_env *e = calloc(1, sizeof(*e));
+  e->env.state.encoder_control = &e->env.ctrl;
+  e->env.state.tile = &e->env.tile;
+  e->env.state.frame = &e->env.frame;
+  e->env.tile.frame = &e->env.vframe;
+  e->env.tile.offset_x = f->tile_offset_x; e->env.tile.offset_y = f->tile_offset_y;
+  e->env.ctrl.in.width = f->in_width; e->env.ctrl.in.height = f->in_height;
+  e->env.ctrl.cfg.tmvp_enable = f->tmvp_enable;
+  e->env.vframe.width = f->width; e->env.vframe.height = f->height;
+  e->env.frame.poc = f->poc;
+  e->env.frame.slicetype = f->slice_b ? KVZ_SLICE_B : KVZ_SLICE_P;
+  memcpy(e->env.frame.ref_LX, f->ref_LX, sizeof(f->ref_LX));
+  e->env.frame.ref_LX_size[0] = f->ref_LX_size[0]; e->env.frame.ref_LX_size[1] = f->ref_LX_size[1];
+  e->env.frame.ref = &e->list;
+  e->list.images = e->images; e->list.cu_arrays = e->cuas; e->list.pocs = e->pocs; e->list.ref_LXs = e->ref_LXs;
+  e->list.size = 16; e->list.used_size = f->n_refs;
+  const int rows = (f->in_height + 3) / 4;
+  for (int r = 0; r < f->n_refs; r++) {
+    e->images[r] = &e->pics[r];
+    e->pocs[r] = f->ref_pocs[r];
+    e->cuas[r] = kvz_cu_array_alloc(f->ref_scu_pitch * 4, rows * 4);
+    for (int sy = 0; sy < rows; sy++)
+      for (int sx = 0; sx < f->ref_scu_pitch; sx++)
+        cu_from_scu(kvz_cu_array_at(e->cuas[r], sx * 4, sy * 4), &f->ref_scus[r][sy * f->ref_scu_pitch + sx]);
+    /* the colocated picture's own lists: identity index lists over its ref_pocs, which carry col_ref_pocs */
+    for (int l = 0; l < 2; l++)
+      for (int i = 0; i < 16; i++) e->ref_LXs[r][l][i] = (uint8_t)i;
+  }
+  if (f->n_refs && f->ref_LX_size[0]) {
+    /* ref_pocs is indexed through ref_LXs[c][list][idx]; give list 1 the indices 8..15 so both tables fit */
+    const int c = f->ref_LX[0][0];
+    for (int i = 0; i < 8; i++) {
+      e->ref_LXs[c][0][i] = (uint8_t)i;       e->pics[c].ref_pocs[i] = f->col_ref_pocs[0][i];
+      e->ref_LXs[c][1][i] = (uint8_t)(8 + i); e->pics[c].ref_pocs[8 + i] = f->col_ref_pocs[1][i];
+    }
+  }
+  /* the working LCU around (x, y): its own SCUs, the column to the left, the row above, the top-right SCU */
+  const int lx = x & ~63, ly = y & ~63, per_row = f->width / 4;
+  for (int sy = -1; sy < 16; sy++)
+    for (int sx = -1; sx < 16; sx++) {
+      const int px = lx + sx * 4, py = ly + sy * 4;
+      if (px < 0 || py < 0 || px >= f->width || py >= f->height) continue;
+      cu_from_scu(LCU_GET_CU_AT_PX(&e->lcu, sx * 4, sy * 4), &f->scus[(py / 4) * per_row + px / 4]);
+    }
+  if (ly > 0 && lx + 64 < f->width) cu_from_scu(LCU_GET_TOP_RIGHT_CU(&e->lcu), &f->scus[((ly - 4) / 4) * per_row + (lx + 64) / 4]);
+  return e;
+}
+
+static void cand_env_free(cand_env *e, const ref_cand_frame *f)
+{
+  for (int r = 0; r < f->n_refs; r++) kvz_cu_array_free(&e->cuas[r]);
+  free(e);
+}
+
+typedef struct { uint8_t dir, ref[2], reserved; int16_t mv[2][2]; } ref_merge_out;
+
+int ref_shim_merge_cand(const ref_cand_frame *f, int x, int y, int w, int h, int use_a1, int use_b1, ref_merge_out out[5])
+{
+  cand_env *e = cand_env_make(f, x, y);
+  inter_merge_cand_t mc[MRG_MAX_NUM_CANDS];
+  memset(mc, 0, sizeof(mc));
+  int n = kvz_inter_get_merge_cand(&e->env.state, x, y, w, h, use_a1, use_b1, mc, &e->lcu);
+  for (int i = 0; i < 5; i++) {
+    out[i].dir = mc[i].dir; out[i].ref[0] = mc[i].ref[0]; out[i].ref[1] = mc[i].ref[1]; out[i].reserved = 0;
+    memcpy(out[i].mv, mc[i].mv, sizeof(out[i].mv));
+  }
+  cand_env_free(e, f);
+  return n;
+}
+
+int ref_shim_mv_cand(const ref_cand_frame *f, int x, int y, int w, int h, int reflist, int lx_idx, int16_t mv_cand[2][2])
+{
+  cand_env *e = cand_env_make(f, x, y);
+  cu_info_t cur;
+  memset(&cur, 0, sizeof(cur));
+  cur.type = CU_INTER;
+  cur.inter.mv_ref[reflist] = (uint8_t)lx_idx;
+  kvz_inter_get_mv_cand(&e->env.state, x, y, w, h, mv_cand, &cur, &e->lcu, (int8_t)reflist);
+  cand_env_free(e, f);
+  return 1;
+}
