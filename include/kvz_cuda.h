@@ -347,6 +347,40 @@ KVZ_CUDA_API int kvz_cuda_deblock_picture(const kvz_cuda_deblock_cfg *cfg, const
                                           const kvz_cuda_plane *planes, int n_planes, int bitdepth, void *stream);
 
 /* ------------------------------------------------------------------ */
+/* BATCH face: inter candidate derivation  (row A18)                     */
+/* ------------------------------------------------------------------ */
+
+typedef struct kvz_cuda_cand_frame {
+  int32_t width, height;          /* state->tile->frame size in luma samples (spatial candidates) */
+  int32_t in_width, in_height;    /* encoder_control->in.width / height (temporal candidate availability) */
+  int32_t tile_offset_x, tile_offset_y;   /* state->tile->offset_x / y (colocated start vector) */
+  int32_t poc;                    /* state->frame->poc */
+  int32_t slice_b;                /* state->frame->slicetype == KVZ_SLICE_B */
+  int32_t tmvp_enable;            /* cfg.tmvp_enable */
+  int32_t n_refs;                 /* state->frame->ref->used_size */
+  int32_t ref_pocs[16];           /* state->frame->ref->pocs */
+  int32_t col_ref_pocs[2][16];    /* for c = ref_LX[0][0]: ref->images[c]->ref_pocs[ref->ref_LXs[c][list][idx]]
+                                     (add_temporal_candidate, inter.c:1058-1066) */
+  uint8_t ref_LX[2][16];          /* state->frame->ref_LX */
+  uint8_t ref_LX_size[2];
+  uint8_t reserved[2];
+  int32_t ref_scu_pitch;          /* records per row of the references' SCU arrays (ref_cu_array->width / 4) */
+  const kvz_cuda_scu *d_scus;     /* this frame (tile): width / 4 records per row, what is coded so far */
+  const kvz_cuda_scu *d_ref_scus[16];   /* state->frame->ref->cu_arrays, indexed like ref_pocs */
+} kvz_cuda_cand_frame;
+
+/* For each PU d_pus[i] (in: x, y, w, h, first_job, num_jobs) fills merge_cand[5] / num_merge_cand like
+ * kvz_inter_get_merge_cand (inter.c:1314-1446; the unused list of a uni-directional candidate reads mv 0 / ref 255
+ * as inter_clear_cu_unused leaves it) and, for each of its jobs (in: ref_idx), mv_cand like kvz_inter_get_mv_cand
+ * (inter.c:1209-1228) for the list and index that hold ref_idx (search_inter.c:1142-1162) and extra_mv like
+ * search_pu_inter_ref (search_inter.c:1188-1206).  d_pu_flags (may be NULL): bit 0 = merge candidate A1 must not be
+ * used, bit 1 = B1 must not be used (second PUs of Nx2N.. / 2NxN.., search_inter.c:1472-1477).  The neighbours are
+ * read from d_scus at the picture positions the reference reads through the working lcu_t, so the array must hold
+ * the decisions of every CU coded before the PU. */
+KVZ_CUDA_API int kvz_cuda_inter_candidates(const kvz_cuda_cand_frame *frame, kvz_cuda_me_pu *d_pus, int n_pus,
+                                           const uint8_t *d_pu_flags, kvz_cuda_me_job *d_jobs, void *stream);
+
+/* ------------------------------------------------------------------ */
 /* BATCH face: sample adaptive offset                */
 /* ------------------------------------------------------------------ */
 

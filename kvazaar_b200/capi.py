@@ -43,6 +43,16 @@ class Plane(C.Structure):
     _fields_ = [("d_data", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("pitch", C.c_int32)]
 
 
+class CandFrame(C.Structure):
+    """kvz_cuda_cand_frame"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("in_width", C.c_int32), ("in_height", C.c_int32),
+                ("tile_offset_x", C.c_int32), ("tile_offset_y", C.c_int32), ("poc", C.c_int32), ("slice_b", C.c_int32),
+                ("tmvp_enable", C.c_int32), ("n_refs", C.c_int32), ("ref_pocs", C.c_int32 * 16),
+                ("col_ref_pocs", (C.c_int32 * 16) * 2), ("ref_LX", (C.c_uint8 * 16) * 2), ("ref_LX_size", C.c_uint8 * 2),
+                ("reserved", C.c_uint8 * 2), ("ref_scu_pitch", C.c_int32), ("d_scus", C.c_void_p),
+                ("d_ref_scus", C.c_void_p * 16)]
+
+
 class DeblockCfg(C.Structure):
     """kvz_cuda_deblock_cfg"""
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("qp", C.c_int32), ("cu_qp", C.c_int32),
@@ -119,6 +129,7 @@ SIGNATURES = {
     "kvz_cuda_sao_reconstruct": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_deblock_picture": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP]),
     "kvz_cuda_coeff_bits": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP]),
+    "kvz_cuda_inter_candidates": (C.c_int, [_VP, _VP, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_image_costs": (C.c_int, [_VP, C.c_int, _VP, C.c_int, C.c_int, C.c_int, _VP, C.c_int, C.c_int, _VP, _VP]),
     "kvz_cuda_transform_blocks": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),
     "kvz_cuda_quant_blocks": (C.c_int, [C.POINTER(QuantCfg), C.c_int, C.c_int, C.c_int, _VP, _VP, C.c_int, _VP]),

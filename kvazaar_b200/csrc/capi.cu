@@ -41,6 +41,11 @@ int launch_coeff_bits(const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coeffs, c
 }
 
 namespace kvz {
+int launch_inter_candidates(const kvz_cuda_cand_frame &f, kvz_cuda_me_pu *d_pus, int n_pus, const uint8_t *d_pu_flags,
+                            kvz_cuda_me_job *d_jobs, cudaStream_t stream);
+}
+
+namespace kvz {
 int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int16_t *in, int16_t *out, int count,
                            cudaStream_t stream);
 int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_idx, int dequant, const int16_t *in,
@@ -358,6 +363,18 @@ int kvz_cuda_sao_reconstruct(const kvz_cuda_plane *rec_in, const kvz_cuda_plane 
   if (!rec_in || !rec_out || !d_luma || (n_planes > 1 && !d_chroma)) return fail_msg("kvz_cuda_sao_reconstruct: bad argument");
   if (bitdepth < 8 || bitdepth > 16) return fail_msg("kvz_cuda_sao_reconstruct: bitdepth must be 8..16");
   return launch_sao_apply(rec_in, rec_out, n_planes, bitdepth, d_luma, d_chroma, (cudaStream_t)stream);
+}
+
+int kvz_cuda_inter_candidates(const kvz_cuda_cand_frame *frame, kvz_cuda_me_pu *d_pus, int n_pus, const uint8_t *d_pu_flags,
+                              kvz_cuda_me_job *d_jobs, void *stream)
+{
+  if (!frame || !d_pus || !d_jobs || n_pus < 0 || !frame->d_scus) return fail_msg("kvz_cuda_inter_candidates: bad argument");
+  if (frame->width <= 0 || frame->height <= 0 || (frame->width & 3) || (frame->height & 3) || frame->n_refs < 0 ||
+      frame->n_refs > 16 || frame->ref_LX_size[0] > 16 || frame->ref_LX_size[1] > 16 || frame->ref_scu_pitch <= 0)
+    return fail_msg("kvz_cuda_inter_candidates: bad frame description");
+  for (int r = 0; r < frame->n_refs; r++)
+    if (!frame->d_ref_scus[r]) return fail_msg("kvz_cuda_inter_candidates: missing reference SCU array");
+  return launch_inter_candidates(*frame, d_pus, n_pus, d_pu_flags, d_jobs, (cudaStream_t)stream);
 }
 
 int kvz_cuda_deblock_picture(const kvz_cuda_deblock_cfg *cfg, const kvz_cuda_scu *d_scus, const kvz_cuda_plane *planes,

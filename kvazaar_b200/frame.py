@@ -265,3 +265,30 @@ class MeSearch:
             C.byref(self.frame), C.c_void_p(d_pus.data_ptr()), n_pus, C.c_void_p(d_jobs.data_ptr()),
             C.c_void_p(d_results.data_ptr()), _stream_ptr()), "kvz_cuda_me_search")
         return d_results
+
+
+def inter_candidates(scene, d_scus, d_ref_scus, d_pus, n_pus, d_jobs, d_pu_flags=None):
+    """kvz_cuda_inter_candidates: `scene` supplies the frame bookkeeping (width, height, poc, slice_b, tmvp,
+    ref_pocs, col_ref_pocs, lists = [L0 picture indices, L1 picture indices]); d_scus / d_ref_scus are device uint8
+    tensors of kvz_cuda_scu records; d_pus / d_jobs are filled in place (merge lists, AMVP predictors, extra_mv)."""
+    capi.init(torch.cuda.current_device())
+    f = capi.CandFrame()
+    f.width = f.in_width = scene.width
+    f.height = f.in_height = scene.height
+    f.poc, f.slice_b, f.tmvp_enable, f.n_refs = scene.poc, int(scene.slice_b), int(scene.tmvp), len(d_ref_scus)
+    for i, p in enumerate(scene.ref_pocs):
+        f.ref_pocs[i] = p
+    for l in range(2):
+        f.ref_LX_size[l] = len(scene.lists[l])
+        for i, r in enumerate(scene.lists[l]):
+            f.ref_LX[l][i] = r
+        for i in range(16):
+            f.col_ref_pocs[l][i] = scene.col_ref_pocs[l][i]
+    f.ref_scu_pitch = scene.width // 4
+    f.d_scus = d_scus.data_ptr()
+    for i, r in enumerate(d_ref_scus):
+        f.d_ref_scus[i] = r.data_ptr()
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check(capi.lib().kvz_cuda_inter_candidates(C.byref(f), C.c_void_p(d_pus.data_ptr()), n_pus,
+                                                    C.c_void_p(d_pu_flags.data_ptr()) if d_pu_flags is not None else None,
+                                                    C.c_void_p(d_jobs.data_ptr()), stream), "kvz_cuda_inter_candidates")

@@ -38,6 +38,9 @@ class Scene:
         self.ref_pocs = pocs
         # POCs the colocated picture's own references had, per list and index
         self.col_ref_pocs = [[int(v) for v in rs.integers(poc - 12, poc + 6, 16)] for _ in range(2)]
+        # a picture never references itself (the POC distance is a divisor, inter.c:975)
+        col_poc = pocs[self.lists[0][0]]
+        self.col_ref_pocs = [[v if v != col_poc else col_poc - 3 for v in l] for l in self.col_ref_pocs]
         # mv_ref of the current picture's SCUs must index the lists
         for l in range(2):
             n = max(1, len(self.lists[l]))
