@@ -122,6 +122,22 @@ for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (384
     out["stages"][f"sao_reconstruct_{name}"] = {"ms": round(ms, 4), "algorithmic_GB_per_s": round(2 * nbytes / ms / 1e6, 1),
                                                 "frac_of_hbm": round(2 * nbytes / ms / 1e6 / HBM, 3),
                                                 "note": "edge offsets in every CTU, one launch"}
+# inter candidate derivation (row A18): every 2Nx2N PU of the frame x 4 references
+import cand_oracle as cdo
+from kvazaar_b200.frame import ME_PU_DT, ME_JOB_DT, inter_candidates
+sc = cdo.Scene(rs, W, H - H % 8, slice_b=False, n_refs=4)
+pl_ = [(x, y, sz) for sz in (8, 16, 32, 64) for y in range(0, sc.height - sz + 1, sz) for x in range(0, sc.width - sz + 1, sz)]
+P = np.zeros(len(pl_), ME_PU_DT); J = np.zeros(len(pl_) * 4, ME_JOB_DT)
+P["x"], P["y"] = [p[0] for p in pl_], [p[1] for p in pl_]
+P["w"] = P["h"] = [p[2] for p in pl_]
+P["first_job"], P["num_jobs"] = np.arange(len(pl_)) * 4, 4
+J["ref_idx"] = np.tile(np.arange(4), len(pl_))
+d_P, d_J, d_S = blocks._dev(P), blocks._dev(J), blocks._dev(sc.scus)
+d_R = [blocks._dev(r) for r in sc.ref_scus]
+ms = timed(lambda: inter_candidates(sc, d_S, d_R, d_P, len(P), d_J), 20)
+out["stages"]["inter_candidates_1080p"] = {"pus": len(P), "jobs": len(J), "ms": round(ms, 4), "Mpus_per_s": round(len(P) / ms / 1e3, 1),
+                                           "note": "merge list + AMVP x4 references + colocated start vector per PU, one thread per PU"}
+
 # deblocking: whole 4:2:0 pictures, random CU quadtrees, two launches per picture
 import deblock_oracle as dbo
 for name, (pw, ph), bd in (("1080p_8bit", (1920, 1080), 8), ("2160p_10bit", (3840, 2160), 10)):
