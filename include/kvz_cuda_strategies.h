@@ -36,6 +36,7 @@ KVZ_CUDA_API int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth
 KVZ_CUDA_API int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 KVZ_CUDA_API int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 KVZ_CUDA_API int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
 
 /* ---- picture: strategies-picture.h:102-136 ---- */
 /* reg_sad_func */
@@ -134,6 +135,21 @@ KVZ_CUDA_API void kvz_cuda_filter_qpel_blocks_diag_luma(KVZ_CUDA_IPOL_BLOCKS_ARG
  * written, nal-generic.c:76-81); the plane is uploaded in strips of rows.  kvz_array_md5 is not replaced. */
 KVZ_CUDA_API void kvz_cuda_array_checksum(const kvz_cuda_px *data, const int height, const int width, const int stride,
                                           unsigned char checksum_out[16], const uint8_t bitdepth);
+
+/* ---- sao: strategies-sao.h:37-60 ---- */
+/* sao_edge_ddistortion_func, calc_sao_edge_dir_func: contiguous block_width x block_height blocks, at most 64x64
+ * (NUM_SAO_EDGE_CATEGORIES = 5; cat_sum_cnt is accumulated into, as sao-generic.c:110-111 does) */
+KVZ_CUDA_API int kvz_cuda_sao_edge_ddistortion(const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data, int block_width,
+                                               int block_height, int eo_class, int offsets[5]);
+KVZ_CUDA_API void kvz_cuda_calc_sao_edge_dir(const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data, int eo_class,
+                                             int block_width, int block_height, int cat_sum_cnt[2][5]);
+/* sao_band_ddistortion_func / sao_reconstruct_color_func take encoder_state_t / encoder_control_t / sao_info_t:
+ * the glue's wrappers pass encoder_control->bitdepth and the sao_info_t fields packed as kvz_cuda_sao_params */
+KVZ_CUDA_API int kvz_cuda_sao_band_ddistortion_host(int bitdepth, const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data,
+                                                    int block_width, int block_height, int band_pos, const int sao_bands[4]);
+KVZ_CUDA_API void kvz_cuda_sao_reconstruct_color_host(int bitdepth, const kvz_cuda_px *rec_data, kvz_cuda_px *new_rec_data,
+                                                      const kvz_cuda_sao_params *sao, int stride, int new_stride,
+                                                      int block_width, int block_height, int color_i);
 
 #ifdef __cplusplus
 }

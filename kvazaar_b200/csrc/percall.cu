@@ -21,6 +21,10 @@ int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int
                            cudaStream_t stream);
 int launch_coeff_abs_sum(const int16_t *coeffs, int per_block, int count, uint32_t *out, cudaStream_t stream);
 int launch_picture_checksum(const kvz_cuda_plane *planes, int n_planes, int bitdepth, uint32_t *d_out, cudaStream_t stream, int y0);
+int launch_sao_stats(const kvz_cuda_plane *orig, const kvz_cuda_plane *rec, int n_planes, int bitdepth,
+                     kvz_cuda_sao_stats *d_stats, cudaStream_t stream);
+int launch_sao_apply(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out, int n_planes, int bitdepth,
+                     const kvz_cuda_sao_params *d_luma, const kvz_cuda_sao_params *d_chroma, cudaStream_t stream);
 int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
                        uint32_t *costs, void *preds, cudaStream_t stream);
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
@@ -556,6 +560,109 @@ int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_regi
   if (!cuda_usable()) return 0;
   int ok = 1;
   KVZ_REG("array_checksum", kvz_cuda_array_checksum);
+  return ok;
+}
+
+// ---------------- sao ----------------
+// the statistics of one contiguous block_width x block_height block (<= 64x64, one CTU of the statistics kernel)
+static void sao_block_stats(const char *who, const kvz_cuda_px *orig, const kvz_cuda_px *rec, int bw, int bh, int bitdepth,
+                            kvz_cuda_sao_stats *result)
+{
+  if (bw <= 0 || bh <= 0 || bw > 64 || bh > 64) { fail_msg("SAO block larger than an LCU"); die(who); }
+  Stage st(who);
+  uint8_t *o = st.in<uint8_t>((size_t)bw * bh), *r = st.in<uint8_t>((size_t)bw * bh);
+  memcpy(o, orig, (size_t)bw * bh);
+  memcpy(r, rec, (size_t)bw * bh);
+  kvz_cuda_sao_stats *out = st.out<kvz_cuda_sao_stats>(1);
+  st.upload(who);
+  kvz_cuda_plane po = { st.dev(o), bw, bh, bw }, pr = { st.dev(r), bw, bh, bw };
+  if (!launch_sao_stats(&po, &pr, 1, bitdepth, st.dev(out), g_pc.stream)) die(who);
+  st.download(who);
+  *result = *out;
+}
+
+int kvz_cuda_sao_edge_ddistortion(const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data, int block_width, int block_height,
+                                  int eo_class, int offsets[5])
+{
+  kvz_cuda_sao_stats s;
+  sao_block_stats("kvz_cuda_sao_edge_ddistortion", orig_data, rec_data, block_width, block_height, 8, &s);
+  int sum = 0;                                                // n * h^2 - 2 * h * E per category == sao-generic.c:51-81
+  for (int c = 0; c < 5; c++) sum += s.edge[eo_class & 3][1][c] * offsets[c] * offsets[c] - 2 * offsets[c] * s.edge[eo_class & 3][0][c];
+  return sum;
+}
+
+void kvz_cuda_calc_sao_edge_dir(const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data, int eo_class, int block_width,
+                                int block_height, int cat_sum_cnt[2][5])
+{
+  kvz_cuda_sao_stats s;
+  sao_block_stats("kvz_cuda_calc_sao_edge_dir", orig_data, rec_data, block_width, block_height, 8, &s);
+  for (int k = 0; k < 2; k++)
+    for (int c = 0; c < 5; c++) cat_sum_cnt[k][c] += s.edge[eo_class & 3][k][c];      // the reference accumulates
+}
+
+int kvz_cuda_sao_band_ddistortion_host(int bitdepth, const kvz_cuda_px *orig_data, const kvz_cuda_px *rec_data, int block_width,
+                                       int block_height, int band_pos, const int sao_bands[4])
+{
+  if (bitdepth != 8) { fail_msg("kvz_cuda_sao_band_ddistortion_host: the per-call face is 8-bit"); die("kvz_cuda_sao_band_ddistortion_host"); }
+  kvz_cuda_sao_stats s;
+  sao_block_stats("kvz_cuda_sao_band_ddistortion_host", orig_data, rec_data, block_width, block_height, 8, &s);
+  int sum = 0;
+  for (int b = 0; b < 4; b++) {
+    const int band = band_pos + b;
+    if (band < 0 || band > 31) continue;
+    sum += s.band[1][band] * sao_bands[b] * sao_bands[b] - 2 * sao_bands[b] * s.band[0][band];
+  }
+  return sum;
+}
+
+void kvz_cuda_sao_reconstruct_color_host(int bitdepth, const kvz_cuda_px *rec_data, kvz_cuda_px *new_rec_data,
+                                         const kvz_cuda_sao_params *sao, int stride, int new_stride, int block_width,
+                                         int block_height, int color_i)
+{
+  const char *who = "kvz_cuda_sao_reconstruct_color_host";
+  if (bitdepth != 8 || !sao || block_width <= 0 || block_height <= 0 || block_width > 66 || block_height > 66 || color_i < 0 || color_i > 2) {
+    fail_msg("kvz_cuda_sao_reconstruct_color_host: bad argument"); die(who);
+  }
+  // The filter reads one sample beyond the block on every side for the edge type (the caller owns that border,
+  // sao-generic.c:138-148); stage the block with its border, filter the bordered plane as one CTU of a 1-CTU
+  // picture and return the interior.  A band offset reads no neighbours.
+  const int edge = sao->type == 2, b = edge ? 1 : 0, w = block_width + 2 * b, h = block_height + 2 * b;
+  if (w > 64 || h > 64) {
+    // larger than one CTU of the kernel with its border: filter row strips of up to 62 x 62
+    for (int y0 = 0; y0 < block_height; y0 += 62)
+      for (int x0 = 0; x0 < block_width; x0 += 62)
+        kvz_cuda_sao_reconstruct_color_host(bitdepth, rec_data + (size_t)y0 * stride + x0, new_rec_data + (size_t)y0 * new_stride + x0,
+                                            sao, stride, new_stride, block_width - x0 < 62 ? block_width - x0 : 62,
+                                            block_height - y0 < 62 ? block_height - y0 : 62, color_i);
+    return;
+  }
+  Stage st(who);
+  uint8_t *in = st.in<uint8_t>((size_t)w * h);
+  pack_rows(in, rec_data - (ptrdiff_t)b * stride - b, w, h, (size_t)stride);
+  kvz_cuda_sao_params *prm = st.in<kvz_cuda_sao_params>(1);
+  *prm = *sao;
+  if (color_i == 2) {                                         // the kernel picks the V fields for its third plane only
+    prm->band_position[0] = sao->band_position[1];
+    for (int c = 0; c < 5; c++) prm->offsets[c] = sao->offsets[5 + c];
+  }
+  uint8_t *out = st.out<uint8_t>((size_t)w * h);
+  st.upload(who);
+  kvz_cuda_plane pi = { st.dev(in), w, h, w }, po = { st.dev(out), w, h, w };
+  if (!launch_sao_apply(&pi, &po, 1, 8, st.dev(prm), nullptr, g_pc.stream)) die(who);
+  st.download(who);
+  for (int y = 0; y < block_height; y++) memcpy(new_rec_data + (size_t)y * new_stride, out + (size_t)(y + b) * w + b, (size_t)block_width);
+}
+
+int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+{
+  if (!register_fn) return 0;
+  if (bitdepth != 8) return 1;
+  if (!cuda_usable()) return 0;
+  int ok = 1;
+  // sao_reconstruct_color / sao_band_ddistortion read encoder structures: their one-line wrappers live in the glue
+  //  and call kvz_cuda_sao_{reconstruct_color,band_ddistortion}_host
+  KVZ_REG("sao_edge_ddistortion", kvz_cuda_sao_edge_ddistortion);
+  KVZ_REG("calc_sao_edge_dir", kvz_cuda_calc_sao_edge_dir);
   return ok;
 }
 

@@ -168,6 +168,52 @@ def test_nal_checksum_strategy():
         assert got == oracle_checksum(big[:, :w]), (h, w)
 
 
+def test_sao_strategies():
+    # strategies-sao.h:37-60 on host blocks, against the oracle (which is pinned on the reference's strategies)
+    import sao_oracle as so
+    from sao_oracle import _pp, ints
+    L = _lib()
+    O = kvzlibs.oracle()
+    IP = C.POINTER(C.c_int)
+    L.kvz_cuda_sao_edge_ddistortion.restype = C.c_int
+    L.kvz_cuda_sao_edge_ddistortion.argtypes = [PX, PX, C.c_int, C.c_int, C.c_int, IP]
+    L.kvz_cuda_calc_sao_edge_dir.restype = None
+    L.kvz_cuda_calc_sao_edge_dir.argtypes = [PX, PX, C.c_int, C.c_int, C.c_int, IP]
+    L.kvz_cuda_sao_band_ddistortion_host.restype = C.c_int
+    L.kvz_cuda_sao_band_ddistortion_host.argtypes = [C.c_int, PX, PX, C.c_int, C.c_int, C.c_int, IP]
+    L.kvz_cuda_sao_reconstruct_color_host.restype = None
+    L.kvz_cuda_sao_reconstruct_color_host.argtypes = [C.c_int, PX, PX, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    rs = np.random.default_rng(8)
+    for bw, bh in ((64, 64), (32, 32), (40, 24), (8, 8)):
+        base = rs.integers(0, 256, (bh, bw)).astype(np.int32)
+        base = (base + np.roll(base, 1, 0) + np.roll(base, 1, 1)) // 3
+        orig = base.astype(np.uint8)
+        rec = np.clip(base + rs.integers(-8, 9, base.shape), 0, 255).astype(np.uint8)
+        for e in range(4):
+            offs = [0] + [int(v) for v in rs.integers(-7, 8, 4)]
+            assert L.kvz_cuda_sao_edge_ddistortion(_p8(orig), _p8(rec), bw, bh, e, ints(offs)) == \
+                O.kvzo_sao_edge_ddistortion_8(_pp(orig), _pp(rec), bw, bh, e, ints(offs))
+            a, b = (C.c_int * 10)(*range(10)), (C.c_int * 10)(*range(10))      # accumulated into
+            L.kvz_cuda_calc_sao_edge_dir(_p8(orig), _p8(rec), e, bw, bh, a)
+            O.kvzo_calc_sao_edge_dir_8(_pp(orig), _pp(rec), e, bw, bh, b)
+            assert a[:] == b[:]
+        for pos in (0, 11, 28):
+            bands = [int(v) for v in rs.integers(-7, 8, 4)]
+            assert L.kvz_cuda_sao_band_ddistortion_host(8, _p8(orig), _p8(rec), bw, bh, pos, ints(bands)) == \
+                O.kvzo_sao_band_ddistortion_8(_pp(orig), _pp(rec), bw, bh, pos, ints(bands))
+        # reconstruct_color on a block inside a larger buffer (the caller owns a one-sample border)
+        plane = np.clip(np.pad(base, 1, mode="edge") + rs.integers(-20, 21, (bh + 2, bw + 2)), 0, 255).astype(np.uint8)
+        for prm in so.random_params(rs, 6, p_none=0.0):
+            for color in (0, 1, 2):
+                got, want = np.zeros((bh, bw), np.uint8), np.zeros((bh, bw), np.uint8)
+                src = plane[1:, 1:]
+                p16 = np.zeros(1, so.SAO_PARAMS_DT); p16[0] = prm
+                L.kvz_cuda_sao_reconstruct_color_host(8, _p8(src), _p8(got), p16.ctypes.data_as(C.c_void_p), bw + 2, bw, bw, bh, color)
+                s_ = so.info_of(prm)
+                O.kvzo_sao_reconstruct_color_8(_pp(src), _pp(want), C.byref(s_), bw + 2, bw, bw, bh, color)
+                assert np.array_equal(got, want), (bw, bh, prm, color)
+
+
 def test_registers_into_the_reference_strategy_list(ref_lib):
     L = _lib()
 
@@ -176,11 +222,11 @@ def test_registers_into_the_reference_strategy_list(ref_lib):
 
     reg = C.cast(ref_lib.kvz_strategyselector_register, C.c_void_p)
     total = 0
-    for fam, n in (("picture", 24), ("dct", 10), ("quant", 1), ("intra", 2), ("ipol", 8), ("nal", 1)):
+    for fam, n in (("picture", 24), ("dct", 10), ("quant", 1), ("intra", 2), ("ipol", 8), ("nal", 1), ("sao", 2)):
         fn = getattr(L, f"kvz_strategy_register_{fam}_cuda")
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_uint8, C.c_void_p]
         lst = StrategyList()
         assert fn(C.byref(lst), 8, reg) == 1
         assert lst.count == n, (fam, lst.count)
         total += lst.count
-    assert total == 46
+    assert total == 48
