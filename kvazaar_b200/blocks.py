@@ -281,14 +281,14 @@ def interp_blocks(d_plane, jobs, d_dst8=None, d_dst16=None, bitdepth=8):
     h, w = d_plane.shape
     d_jobs = _dev(jobs)
     capi.check(capi.lib().kvz_cuda_interp_blocks(
-        _p(d_plane), d_plane.stride(0), w, h, bitdepth, _p(d_jobs), len(jobs),
+        _p(d_plane), d_plane.stride(0) * d_plane.element_size(), w, h, bitdepth, _p(d_jobs), len(jobs),
         _p(d_dst8) if d_dst8 is not None else None, _p(d_dst16) if d_dst16 is not None else None, _stream()),
         "kvz_cuda_interp_blocks")
 
 
 def bipred_blend(d_s0, d_s1, bitdepth=8):
     capi.init(torch.cuda.current_device())
-    out = torch.empty(d_s0.shape, dtype=torch.uint8, device="cuda")
+    out = torch.empty(d_s0.shape, dtype=torch.uint8 if bitdepth == 8 else torch.int16, device="cuda")
     capi.check(capi.lib().kvz_cuda_bipred_blend(_p(d_s0), _p(d_s1), d_s0.numel(), bitdepth, _p(out), _stream()),
                "kvz_cuda_bipred_blend")
     return out

@@ -477,14 +477,14 @@ int kvz_cuda_interp_blocks(const void *d_plane, int pitch, int width, int height
 {
   if (!d_plane || !d_jobs || n_jobs < 0 || width <= 0 || height <= 0 || (!d_dst8 && !d_dst16))
     return fail_msg("kvz_cuda_interp_blocks: bad argument");
-  if (bitdepth != 8) return fail_msg("kvz_cuda_interp_blocks: only bitdepth 8 is implemented");
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_interp_blocks: bitdepth must be 8 or 10");
   return launch_interp(d_plane, pitch, width, height, bitdepth, d_jobs, n_jobs, d_dst8, d_dst16, (cudaStream_t)stream);
 }
 
 int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1, size_t n, int bitdepth, void *d_dst, void *stream)
 {
   if (!d_s0 || !d_s1 || !d_dst) return fail_msg("kvz_cuda_bipred_blend: null argument");
-  if (bitdepth != 8) return fail_msg("kvz_cuda_bipred_blend: only bitdepth 8 is implemented");
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_bipred_blend: bitdepth must be 8 or 10");
   return launch_bipred_blend(d_s0, d_s1, n, bitdepth, d_dst, (cudaStream_t)stream);
 }
 

@@ -23,14 +23,16 @@ __device__ __constant__ int8_t c_chroma[8][4] = {        // kvz_g_chroma_filter 
   { 0, 64, 0, 0 }, { -2, 58, 10, -2 }, { -4, 54, 16, -2 }, { -6, 46, 28, -4 },
   { -4, 36, 36, -4 }, { -4, 28, 46, -6 }, { -2, 16, 54, -4 }, { -2, 10, 58, -2 } };
 
+template <typename PIX>
 struct Smem {
-  uint8_t win[71 * 72];          // (h + taps - 1) x (w + taps - 1), pitch 72
+  PIX win[71 * 72];              // (h + taps - 1) x (w + taps - 1), pitch 72
   int16_t hor[71 * 64];          // horizontally filtered rows, pitch w
 };
 
-template <int TAPS>
-__device__ void interp_block(Smem &sm, const kvz_cuda_interp_job &jb, const uint8_t *plane, int pitch, int W, int H,
-                             int bitdepth, uint8_t *dst8, int16_t *dst16)
+// PIX = kvz_pixel of the build: uint8_t, or uint16_t for KVZ_BIT_DEPTH > 8 (pitch in bytes either way)
+template <int TAPS, typename PIX>
+__device__ void interp_block(Smem<PIX> &sm, const kvz_cuda_interp_job &jb, const uint8_t *plane_bytes, int pitch, int W, int H,
+                             int bitdepth, PIX *dst8, int16_t *dst16)
 {
   constexpr int before = TAPS / 2 - 1;
   constexpr int fshift = TAPS == 8 ? 2 : 3;                 // quarter- / eighth-pel
@@ -42,7 +44,7 @@ __device__ void interp_block(Smem &sm, const kvz_cuda_interp_job &jb, const uint
   const int ww = w + TAPS - 1, wh = h + TAPS - 1;
   for (int i = tid; i < ww * wh; i += kThreads) {
     const int r = i / ww, c = i - r * ww;
-    sm.win[r * 72 + c] = plane[(size_t)clampi(by - before + r, 0, H - 1) * pitch + clampi(bx - before + c, 0, W - 1)];
+    sm.win[r * 72 + c] = reinterpret_cast<const PIX *>(plane_bytes + (size_t)clampi(by - before + r, 0, H - 1) * pitch)[clampi(bx - before + c, 0, W - 1)];
   }
   __syncthreads();
   const int8_t *fh = TAPS == 8 ? c_luma[fx] : c_chroma[fx];
@@ -66,27 +68,29 @@ __device__ void interp_block(Smem &sm, const kvz_cuda_interp_job &jb, const uint
       dst16[(size_t)jb.dst_offset + (size_t)y * jb.dst_stride + x] = (int16_t)s;
     } else {
       if (jb.mode == KVZ_CUDA_INTERP_FME) s = (int16_t)s;      // int16 store of the block filters (ipol-generic.c:285)
-      dst8[(size_t)jb.dst_offset + (size_t)y * jb.dst_stride + x] = (uint8_t)clampi((s + off) >> sh, 0, pix_max);
+      dst8[(size_t)jb.dst_offset + (size_t)y * jb.dst_stride + x] = (PIX)clampi((s + off) >> sh, 0, pix_max);
     }
   }
 }
 
+template <typename PIX>
 __global__ void __launch_bounds__(kThreads)
 interp_kernel(const uint8_t *__restrict__ plane, int pitch, int W, int H, int bitdepth,
-              const kvz_cuda_interp_job *__restrict__ jobs, uint8_t *dst8, int16_t *dst16)
+              const kvz_cuda_interp_job *__restrict__ jobs, PIX *dst8, int16_t *dst16)
 {
-  __shared__ Smem sm;
+  __shared__ Smem<PIX> sm;
   const kvz_cuda_interp_job jb = jobs[blockIdx.x];
-  if (jb.chroma) interp_block<4>(sm, jb, plane, pitch, W, H, bitdepth, dst8, dst16);
-  else interp_block<8>(sm, jb, plane, pitch, W, H, bitdepth, dst8, dst16);
+  if (jb.chroma) interp_block<4, PIX>(sm, jb, plane, pitch, W, H, bitdepth, dst8, dst16);
+  else interp_block<8, PIX>(sm, jb, plane, pitch, W, H, bitdepth, dst8, dst16);
 }
 
+template <typename PIX>
 __global__ void bipred_blend_kernel(const int16_t *__restrict__ s0, const int16_t *__restrict__ s1, size_t n,
-                                    int bitdepth, uint8_t *__restrict__ dst)
+                                    int bitdepth, PIX *__restrict__ dst)
 {
   const int sh = 15 - bitdepth, off = 1 << (sh - 1), pix_max = (1 << bitdepth) - 1;   // picture-generic.c:553-570
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    dst[i] = (uint8_t)clampi(((int)s0[i] + (int)s1[i] + off) >> sh, 0, pix_max);
+    dst[i] = (PIX)clampi(((int)s0[i] + (int)s1[i] + off) >> sh, 0, pix_max);
 }
 
 }  // namespace
@@ -95,7 +99,8 @@ int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, cons
                   void *dst8, int16_t *dst16, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  interp_kernel<<<n_jobs, kThreads, 0, stream>>>((const uint8_t *)plane, pitch, W, H, bitdepth, jobs, (uint8_t *)dst8, dst16);
+  if (bitdepth > 8) interp_kernel<uint16_t><<<n_jobs, kThreads, 0, stream>>>((const uint8_t *)plane, pitch, W, H, bitdepth, jobs, (uint16_t *)dst8, dst16);
+  else interp_kernel<uint8_t><<<n_jobs, kThreads, 0, stream>>>((const uint8_t *)plane, pitch, W, H, bitdepth, jobs, (uint8_t *)dst8, dst16);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
@@ -105,7 +110,8 @@ int launch_bipred_blend(const int16_t *s0, const int16_t *s1, size_t n, int bitd
 {
   if (n == 0) return 1;
   const int grid = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-  bipred_blend_kernel<<<grid, 256, 0, stream>>>(s0, s1, n, bitdepth, (uint8_t *)dst);
+  if (bitdepth > 8) bipred_blend_kernel<uint16_t><<<grid, 256, 0, stream>>>(s0, s1, n, bitdepth, (uint16_t *)dst);
+  else bipred_blend_kernel<uint8_t><<<grid, 256, 0, stream>>>(s0, s1, n, bitdepth, (uint8_t *)dst);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

@@ -9,7 +9,7 @@ from kvzlibs import ptr
 pytestmark = pytest.mark.gpu
 
 
-def _run(W, H, ref, count, seed, hostile=False):
+def _run(W, H, ref, count, seed, hostile=False, bitdepth=8):
     import torch
     from kvazaar_b200 import blocks
     O = kvzlibs.oracle()
@@ -31,26 +31,29 @@ def _run(W, H, ref, count, seed, hostile=False):
         else:
             rows.append((x, y, mvx, mvy, w, h, chroma, mode, (0, 0), off8, w)); off8 += w * h
     jobs = np.array(rows, blocks.INTERP_JOB_DT)
-    d8 = torch.zeros(max(off8, 1), dtype=torch.uint8, device="cuda")
+    sfx = "8" if bitdepth == 8 else "10"
+    pix = np.uint8 if bitdepth == 8 else np.uint16
+    d8 = torch.zeros(max(off8, 1), dtype=torch.uint8 if bitdepth == 8 else torch.int16, device="cuda")
     d16 = torch.zeros(max(off16, 1), dtype=torch.int16, device="cuda")
-    blocks.interp_blocks(torch.from_numpy(ref).cuda(), jobs, d8, d16)
-    g8, g16 = d8.cpu().numpy(), d16.cpu().numpy()
+    blocks.interp_blocks(torch.from_numpy(ref if bitdepth == 8 else ref.view(np.int16)).cuda(), jobs, d8, d16, bitdepth)
+    g8, g16 = d8.cpu().numpy().view(pix), d16.cpu().numpy()
     for jb in jobs:
         w, h, o = int(jb["w"]), int(jb["h"]), int(jb["dst_offset"])
         args = (ptr(ref), W, H, int(jb["x"]), int(jb["y"]), int(jb["mv_x"]), int(jb["mv_y"]), w, h)
         if jb["mode"] == 1:
             want = np.zeros((h, w), np.int16)
-            (O.kvzo_interp_chroma14_8 if jb["chroma"] else O.kvzo_interp_luma14_8)(*args, ptr(want), w)
+            getattr(O, ("kvzo_interp_chroma14_" if jb["chroma"] else "kvzo_interp_luma14_") + sfx)(*args, ptr(want), w)
             got = g16[o:o + w * h].reshape(h, w)
         elif jb["mode"] == 0:
-            want = np.zeros((h, w), np.uint8)
-            (O.kvzo_interp_chroma_8 if jb["chroma"] else O.kvzo_interp_luma_8)(*args, ptr(want), w)
+            want = np.zeros((h, w), pix)
+            getattr(O, ("kvzo_interp_chroma_" if jb["chroma"] else "kvzo_interp_luma_") + sfx)(*args, ptr(want), w)
             got = g8[o:o + w * h].reshape(h, w)
         else:
             # FME candidate = 14-bit (int16-wrapped) value rounded to a pixel, ipol-generic.c:285-300
             w14 = np.zeros((h, w), np.int16)
-            O.kvzo_interp_luma14_8(*args, ptr(w14), w)
-            want = np.clip((w14.astype(np.int32) + 32) >> 6, 0, 255).astype(np.uint8)
+            getattr(O, "kvzo_interp_luma14_" + sfx)(*args, ptr(w14), w)
+            sh = 14 - bitdepth
+            want = np.clip((w14.astype(np.int32) + (1 << (sh - 1))) >> sh, 0, (1 << bitdepth) - 1).astype(pix)
             got = g8[o:o + w * h].reshape(h, w)
         assert np.array_equal(got, want), jb
 
@@ -58,6 +61,16 @@ def _run(W, H, ref, count, seed, hostile=False):
 def test_interp_textured():
     W, H = 160, 96
     _run(W, H, kvzlibs.synth_luma(21, W, H, 1)[0], 150, 1)
+
+
+def test_interp_10bit():
+    W, H = 160, 96
+    ref = (kvzlibs.synth_luma(23, W, H, 1)[0].astype(np.uint16) << 2) | np.random.default_rng(5).integers(0, 4, (H, W), dtype=np.uint16)
+    _run(W, H, np.ascontiguousarray(ref), 150, 6, bitdepth=10)
+    hostile = np.zeros((64, 128), np.uint16)
+    hostile[:, ::2] = 1023
+    hostile[::2, :] ^= 1023
+    _run(128, 64, hostile, 120, 7, bitdepth=10)
 
 
 def test_interp_hostile_pattern():
@@ -109,3 +122,7 @@ def test_bipred_blend():
     want = np.zeros(s0.size, np.uint8)
     O.kvzo_bipred_blend_8(ptr(s0), ptr(s1), s0.size, ptr(want))
     assert np.array_equal(got, want)
+    got10 = blocks.bipred_blend(torch.from_numpy(s0).cuda(), torch.from_numpy(s1).cuda(), 10).cpu().numpy().view(np.uint16)
+    want10 = np.zeros(s0.size, np.uint16)
+    O.kvzo_bipred_blend_10(ptr(s0), ptr(s1), s0.size, ptr(want10))
+    assert np.array_equal(got10, want10)
