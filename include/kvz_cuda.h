@@ -587,11 +587,11 @@ KVZ_CUDA_API int kvz_cuda_bipred_blend(const int16_t *d_s0, const int16_t *d_s1,
 /* ------------------------------------------------------------------ */
 
 typedef struct kvz_cuda_intra_job {
-  uint32_t ref_offset;          /* byte offset in d_refs of this PU's reference samples: top[2w+1] then left[2w+1],
+  uint32_t ref_offset;          /* offset in d_refs (in SAMPLES) of this PU's reference samples: top[2w+1] then left[2w+1],
                                    [0] = the top-left corner (kvz_intra_references.ref, intra.h) */
-  uint32_t orig_offset;         /* byte offset of the source block in d_orig */
+  uint32_t orig_offset;         /* offset (samples) of the source block in d_orig; orig_stride in samples */
   int32_t orig_stride;
-  uint32_t pred_offset;         /* byte offset in d_preds of this PU's 35 predictions (35 * w * w samples) */
+  uint32_t pred_offset;         /* offset (samples) in d_preds of this PU's 35 predictions (35 * w * w samples) */
   uint8_t log2_width;           /* 2..5 */
   uint8_t is_chroma;            /* color != COLOR_Y */
   uint8_t filter_boundary;      /* !(cfg->lossless && cfg->implicit_rdpcm), search_intra.c:420 */

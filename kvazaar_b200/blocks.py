@@ -308,7 +308,7 @@ def intra_mode_costs(d_refs, d_orig, jobs, want_preds=False, bitdepth=8):
     preds = None
     if want_preds:
         total = int(jobs["pred_offset"].max()) + 35 * (1 << (2 * int(jobs["log2_width"][np.argmax(jobs["pred_offset"])])))
-        preds = torch.zeros(total, dtype=torch.uint8, device="cuda")
+        preds = torch.zeros(total, dtype=torch.uint8 if bitdepth == 8 else torch.int16, device="cuda")
     capi.check(capi.lib().kvz_cuda_intra_mode_costs(
         _p(d_refs), _p(d_orig) if d_orig is not None else None, _p(d_jobs), len(jobs), bitdepth, _p(costs),
         _p(preds) if preds is not None else None, _stream()), "kvz_cuda_intra_mode_costs")

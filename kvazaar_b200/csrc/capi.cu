@@ -68,7 +68,7 @@ int launch_bipred_blend(const int16_t *s0, const int16_t *s1, size_t n, int bitd
 }
 namespace kvz {
 int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
-                       uint32_t *costs, void *preds, cudaStream_t stream);
+                       uint32_t *costs, void *preds, cudaStream_t stream, int bitdepth);
 }
 namespace kvz { int measure_vabsdiff4_peak(double *abs_diffs_per_s, cudaStream_t stream); }
 
@@ -446,7 +446,7 @@ int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg, const void *
                                      void *stream)
 {
   if (!check_qcfg(cfg, "kvz_cuda_quantize_residuals_rdoq: bad cfg")) return 0;
-  if (cfg->bitdepth != 8) return fail_msg("kvz_cuda_quantize_residuals_rdoq: only bitdepth 8 is implemented");
+
   if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || !d_ctx || !d_rdoq_jobs || !d_work || n_jobs < 0)
     return fail_msg("kvz_cuda_quantize_residuals_rdoq: bad argument");
   if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
@@ -466,7 +466,7 @@ int kvz_cuda_quantize_residuals(const kvz_cuda_quant_cfg *cfg, const void *d_ref
                                 uint8_t *d_has_coeffs, void *stream)
 {
   if (!check_qcfg(cfg, "kvz_cuda_quantize_residuals: bad cfg")) return 0;
-  if (cfg->bitdepth != 8) return fail_msg("kvz_cuda_quantize_residuals: only bitdepth 8 is implemented");
+
   if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || n_jobs < 0)
     return fail_msg("kvz_cuda_quantize_residuals: bad argument");
   return launch_quantize_residual(*cfg, d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has_coeffs, (cudaStream_t)stream);
@@ -492,8 +492,8 @@ int kvz_cuda_intra_mode_costs(const void *d_refs, const void *d_orig, const kvz_
                               int bitdepth, uint32_t *d_costs, void *d_preds, void *stream)
 {
   if (!d_refs || !d_jobs || n_jobs < 0 || (!d_costs && !d_preds)) return fail_msg("kvz_cuda_intra_mode_costs: bad argument");
-  if (bitdepth != 8) return fail_msg("kvz_cuda_intra_mode_costs: only bitdepth 8 is implemented");
-  return launch_intra_costs(d_refs, d_orig, d_jobs, n_jobs, d_costs, d_preds, (cudaStream_t)stream);
+  if (bitdepth != 8 && bitdepth != 10) return fail_msg("kvz_cuda_intra_mode_costs: bitdepth must be 8 or 10");
+  return launch_intra_costs(d_refs, d_orig, d_jobs, n_jobs, d_costs, d_preds, (cudaStream_t)stream, bitdepth);
 }
 
 }  // extern "C"

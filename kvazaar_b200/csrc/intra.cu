@@ -20,10 +20,12 @@ namespace {
 
 constexpr int kWarps = 4;
 
+// PIX = kvz_pixel of the build: uint8_t, or uint16_t for KVZ_BIT_DEPTH > 8
+template <typename PIX>
 struct Smem {
-  uint8_t top[65], left[65], ftop[65], fleft[65];
-  alignas(16) uint8_t orig[32 * 32];
-  alignas(16) uint8_t pred[kWarps][32 * 32];
+  PIX top[65], left[65], ftop[65], fleft[65];
+  alignas(16) PIX orig[32 * 32];
+  alignas(16) PIX pred[kWarps][32 * 32];
 };
 
 __device__ __constant__ int8_t c_disp[9] = { 0, 2, 5, 9, 13, 17, 21, 26, 32 };
@@ -31,12 +33,14 @@ __device__ __constant__ int16_t c_inv_disp[9] = { 0, 4096, 1638, 910, 630, 482, 
 
 // sample i (block coordinate, >= most negative index) of the main reference after the side
 // reference has been projected onto its negative half (intra-generic.c:73-95)
-__device__ __forceinline__ int main_ref(const uint8_t *main_in, const uint8_t *side_in, int i, int inv)
+template <typename PIX>
+__device__ __forceinline__ int main_ref(const PIX *main_in, const PIX *side_in, int i, int inv)
 {
   return i >= -1 ? main_in[i + 1] : side_in[(128 + inv * (-i - 1)) >> 8];
 }
 
-__device__ void predict_mode(const Smem &sm, int lg, int mode, bool chroma, bool filter_boundary, uint8_t *dst, int lane)
+template <typename PIX>
+__device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma, bool filter_boundary, PIX *dst, int lane, int pix_max)
 {
   const int w = 1 << lg;
   // which reference (intra.c:291-310)
@@ -48,7 +52,7 @@ __device__ void predict_mode(const Smem &sm, int lg, int mode, bool chroma, bool
       filtered = min(abs(mode - 26), abs(mode - 10)) > thres;
     }
   }
-  const uint8_t *top = filtered ? sm.ftop : sm.top, *left = filtered ? sm.fleft : sm.left;
+  const PIX *top = filtered ? sm.ftop : sm.top, *left = filtered ? sm.fleft : sm.left;
 
   if (mode == 0) {
     const int tr = top[w + 1], bl = left[w + 1];
@@ -56,7 +60,7 @@ __device__ void predict_mode(const Smem &sm, int lg, int mode, bool chroma, bool
       const int y = i >> lg, x = i & (w - 1);
       const int hor = (w - 1 - x) * left[y + 1] + (x + 1) * tr;
       const int ver = (w - 1 - y) * top[x + 1] + (y + 1) * bl;
-      dst[i] = (uint8_t)((hor + ver + w) >> (lg + 1));
+      dst[i] = (PIX)((hor + ver + w) >> (lg + 1));
     }
   } else if (mode == 1) {
     int sum = 0;
@@ -72,14 +76,14 @@ __device__ void predict_mode(const Smem &sm, int lg, int mode, bool chroma, bool
         else if (y == 0) v = (top[x + 1] + 3 * dc + 2) / 4;
         else if (x == 0) v = (left[y + 1] + 3 * dc + 2) / 4;
       }
-      dst[i] = (uint8_t)v;
+      dst[i] = (PIX)v;
     }
   } else {
     const bool vertical = mode >= 18;
     const int md = vertical ? mode - 26 : 10 - mode;
     const int disp = (md < 0 ? -1 : 1) * c_disp[abs(md)];
     const int inv = c_inv_disp[abs(md)];
-    const uint8_t *main_in = vertical ? top : left, *side_in = vertical ? left : top;
+    const PIX *main_in = vertical ? top : left, *side_in = vertical ? left : top;
     const bool post = !chroma && w < 32 && filter_boundary && (mode == 10 || mode == 26);
     for (int i = lane; i < w * w; i += 32) {
       // (x, y) in the orientation of a vertical mode; horizontal modes are its transpose
@@ -94,46 +98,49 @@ __device__ void predict_mode(const Smem &sm, int lg, int mode, bool chroma, bool
         v = fr ? ((32 - fr) * a + fr * main_in[x + di + 2] + 16) >> 5 : a;
       }
       // pure horizontal / vertical: first row / column follows the gradient of the other edge (intra.c:195-207)
-      if (post && x == 0) v = clampi(v + ((side_in[y + 1] - side_in[0]) >> 1), 0, 255);
-      dst[vertical ? i : x * w + y] = (uint8_t)v;
+      if (post && x == 0) v = clampi(v + (((int)side_in[y + 1] - (int)side_in[0]) >> 1), 0, pix_max);
+      dst[vertical ? i : x * w + y] = (PIX)v;
     }
   }
 }
 
+template <typename PIX>
 __global__ void __launch_bounds__(kWarps * 32)
-intra_costs_kernel(const uint8_t *__restrict__ refs, const uint8_t *__restrict__ orig_base,
-                   const kvz_cuda_intra_job *__restrict__ jobs, uint32_t *__restrict__ costs, uint8_t *__restrict__ preds)
+intra_costs_kernel(const PIX *__restrict__ refs, const PIX *__restrict__ orig_base,
+                   const kvz_cuda_intra_job *__restrict__ jobs, uint32_t *__restrict__ costs, PIX *__restrict__ preds, int pix_max,
+                   int cost_shift)
 {
-  __shared__ Smem sm;
+  __shared__ Smem<PIX> sm;
   const kvz_cuda_intra_job jb = jobs[blockIdx.x];
   const int lg = jb.log2_width, w = 1 << lg, n = 2 * w + 1;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint8_t *rt = refs + jb.ref_offset, *rl = rt + n;
+  const PIX *rt = refs + jb.ref_offset, *rl = rt + n;
   for (int i = tid; i < n; i += kWarps * 32) { sm.top[i] = rt[i]; sm.left[i] = rl[i]; }
   if (jb.has_orig)
     for (int i = tid; i < w * w; i += kWarps * 32)
       sm.orig[i] = orig_base[jb.orig_offset + (size_t)(i >> lg) * jb.orig_stride + (i & (w - 1))];
   __syncthreads();
   for (int i = tid; i < n; i += kWarps * 32) {                // intra_filter_reference (intra.c:163-193)
-    if (i == 0) sm.ftop[0] = sm.fleft[0] = (uint8_t)((sm.left[1] + 2 * sm.left[0] + sm.top[1] + 2) / 4);
+    if (i == 0) sm.ftop[0] = sm.fleft[0] = (PIX)((sm.left[1] + 2 * sm.left[0] + sm.top[1] + 2) / 4);
     else if (i == n - 1) { sm.ftop[i] = sm.top[i]; sm.fleft[i] = sm.left[i]; }
     else {
-      sm.ftop[i] = (uint8_t)((sm.top[i - 1] + 2 * sm.top[i] + sm.top[i + 1] + 2) / 4);
-      sm.fleft[i] = (uint8_t)((sm.left[i - 1] + 2 * sm.left[i] + sm.left[i + 1] + 2) / 4);
+      sm.ftop[i] = (PIX)((sm.top[i - 1] + 2 * sm.top[i] + sm.top[i + 1] + 2) / 4);
+      sm.fleft[i] = (PIX)((sm.left[i - 1] + 2 * sm.left[i] + sm.left[i + 1] + 2) / 4);
     }
   }
   __syncthreads();
-  uint8_t *dst = sm.pred[warp];
-  const StridedBlock a{ dst, w }, b{ sm.orig, w };
+  PIX *dst = sm.pred[warp];
+  const StridedBlockT<PIX> a{ dst, w }, b{ sm.orig, w };
   for (int mode = warp; mode < 35; mode += kWarps) {
     __syncwarp();
-    predict_mode(sm, lg, mode, jb.is_chroma != 0, jb.filter_boundary != 0, dst, lane);
+    predict_mode<PIX>(sm, lg, mode, jb.is_chroma != 0, jb.filter_boundary != 0, dst, lane, pix_max);
     __syncwarp();
     if (preds)
       for (int i = lane; i < w * w; i += 32) preds[(size_t)jb.pred_offset + (size_t)mode * w * w + i] = dst[i];
     if (jb.has_orig) {
-      const uint32_t satd = w == 4 ? warp_satd4_strip(a, b, 0, 0, 0, 0, 1, lane) : warp_satd8_area(a, b, 0, 0, w, w, lane);
-      const uint32_t sad = warp_sad(a, b, w, w, lane);
+      // satd_NxN / sad_NxN shift their result by KVZ_BIT_DEPTH - 8, satd_4x4 does not (picture-generic.c:189-196, :322-340)
+      const uint32_t satd = w == 4 ? warp_satd4_strip(a, b, 0, 0, 0, 0, 1, lane) : warp_satd8_area(a, b, 0, 0, w, w, lane) >> cost_shift;
+      const uint32_t sad = warp_sad(a, b, w, w, lane) >> cost_shift;
       if (lane == 0) {
         costs[((size_t)blockIdx.x * 35 + mode) * 2] = satd;
         costs[((size_t)blockIdx.x * 35 + mode) * 2 + 1] = sad;
@@ -144,12 +151,17 @@ intra_costs_kernel(const uint8_t *__restrict__ refs, const uint8_t *__restrict__
 
 }  // namespace
 
+// offsets of the jobs are in SAMPLES (bytes at 8 bits)
 int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
-                       uint32_t *costs, void *preds, cudaStream_t stream)
+                       uint32_t *costs, void *preds, cudaStream_t stream, int bitdepth)
 {
   if (n_jobs <= 0) return 1;
-  intra_costs_kernel<<<n_jobs, kWarps * 32, 0, stream>>>((const uint8_t *)refs, (const uint8_t *)orig, jobs, costs,
-                                                         (uint8_t *)preds);
+  if (bitdepth > 8)
+    intra_costs_kernel<uint16_t><<<n_jobs, kWarps * 32, 0, stream>>>((const uint16_t *)refs, (const uint16_t *)orig, jobs, costs,
+                                                                     (uint16_t *)preds, (1 << bitdepth) - 1, bitdepth - 8);
+  else
+    intra_costs_kernel<uint8_t><<<n_jobs, kWarps * 32, 0, stream>>>((const uint8_t *)refs, (const uint8_t *)orig, jobs, costs,
+                                                                    (uint8_t *)preds, 255, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

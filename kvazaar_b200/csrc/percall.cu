@@ -26,7 +26,7 @@ int launch_sao_stats(const kvz_cuda_plane *orig, const kvz_cuda_plane *rec, int 
 int launch_sao_apply(const kvz_cuda_plane *rec_in, const kvz_cuda_plane *rec_out, int n_planes, int bitdepth,
                      const kvz_cuda_sao_params *d_luma, const kvz_cuda_sao_params *d_chroma, cudaStream_t stream);
 int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_job *jobs, int n_jobs,
-                       uint32_t *costs, void *preds, cudaStream_t stream);
+                       uint32_t *costs, void *preds, cudaStream_t stream, int bitdepth);
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
                   void *dst8, int16_t *dst16, cudaStream_t stream);
 
@@ -321,7 +321,7 @@ static void intra_call(const char *who, int lg, int mode, const kvz_cuda_px *top
   jb->log2_width = (uint8_t)lg; jb->is_chroma = 1;
   uint8_t *preds = st.out<uint8_t>((size_t)35 * w * w);
   st.upload(who);
-  if (!launch_intra_costs(st.dev(refs), nullptr, st.dev(jb), 1, nullptr, st.dev(preds), g_pc.stream)) die(who);
+  if (!launch_intra_costs(st.dev(refs), nullptr, st.dev(jb), 1, nullptr, st.dev(preds), g_pc.stream, 8)) die(who);
   st.download(who);
   memcpy(dst, preds + (size_t)mode * w * w, (size_t)w * w);
 }

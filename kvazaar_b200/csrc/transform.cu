@@ -255,9 +255,10 @@ coeff_abs_sum_kernel(const int16_t *__restrict__ coeffs, int per_block, int coun
 // With RDOQ the function is three launches around rdoq_kernel (rdoq.cu):
 // STAGE 1: residual -> transform, coefficients to `work` (4x4 blocks under cfg.rdoq_skip are quantised here,
 //          quant-generic.c:213-215); STAGE 2: levels from coeff_out -> dequant -> inverse -> reconstruction.
-template <int STAGE, int T, typename SM>
-__device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ pred,
-                             uint8_t *__restrict__ rec, int16_t *__restrict__ coeff_out, const kvz_cuda_residual_job &jb,
+// PIX = kvz_pixel of the build (uint8_t, or uint16_t for KVZ_BIT_DEPTH > 8); job offsets and strides in samples
+template <int STAGE, int T, typename SM, typename PIX>
+__device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const PIX *__restrict__ ref, const PIX *__restrict__ pred,
+                             PIX *__restrict__ rec, int16_t *__restrict__ coeff_out, const kvz_cuda_residual_job &jb,
                              uint8_t *has_coeff, int16_t *__restrict__ work, int rdoq_skip, int tid, int &tt_key,
                              int &scan_key)
 {
@@ -278,7 +279,7 @@ __device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__rest
     scan_key = N | (jb.scan_idx << 8);
   }
   if (tid == 0) sm.any = 0;
-  const uint8_t *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
+  const PIX *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
   const int ts_shift = 15 - c.bitdepth - lg;
   int16_t *co = coeff_out + jb.coeff_offset;
   if (STAGE != 2) {
@@ -316,7 +317,7 @@ __device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__rest
   if (STAGE == 1) return;
   if (any) sm.any = 1;
   group_sync<T>();
-  uint8_t *op = rec + jb.rec_offset;
+  PIX *op = rec + jb.rec_offset;
   const int has = sm.any;
   if (has) {
     dequant_block<T>(sm, c, N, luma ? 0 : (jb.color == 1 ? 2 : 3), tid);
@@ -334,7 +335,7 @@ __device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__rest
     for (int i = tid; i < N * N; i += T) {
       const int y = i / N, x = i - y * N;
       const int16_t val = (int16_t)((int)sm.a[y * P + x] + (int)pp[(size_t)y * jb.in_stride + x]);
-      op[(size_t)y * jb.out_stride + x] = (uint8_t)clampi(val, 0, pix_max);
+      op[(size_t)y * jb.out_stride + x] = (PIX)clampi(val, 0, pix_max);
     }
   } else {
     for (int i = tid; i < N * N; i += T) {
@@ -346,10 +347,10 @@ __device__ void residual_job(SM &sm, kvz_cuda_quant_cfg c, const uint8_t *__rest
 }
 
 // a CTA takes kWarps consecutive jobs: one per warp when all of them are 4x4 / 8x8, else one after the other
-template <int STAGE>
+template <int STAGE, typename PIX>
 __global__ void __launch_bounds__(kThreads)
-quantize_residual_kernel(kvz_cuda_quant_cfg c, const uint8_t *__restrict__ ref, const uint8_t *__restrict__ pred,
-                         uint8_t *__restrict__ rec, int16_t *__restrict__ coeff_out,
+quantize_residual_kernel(kvz_cuda_quant_cfg c, const PIX *__restrict__ ref, const PIX *__restrict__ pred,
+                         PIX *__restrict__ rec, int16_t *__restrict__ coeff_out,
                          const kvz_cuda_residual_job *__restrict__ jobs, int n_jobs, uint8_t *__restrict__ has_coeffs,
                          int16_t *__restrict__ work, int rdoq_skip)
 {
@@ -449,9 +450,13 @@ int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const
                              const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  if (!opt_in_smem(quantize_residual_kernel<0>)) return 0;
-  quantize_residual_kernel<0><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
+  if (!opt_in_smem(quantize_residual_kernel<0, uint8_t>) || !opt_in_smem(quantize_residual_kernel<0, uint16_t>)) return 0;
+  if (c.bitdepth > 8)
+    quantize_residual_kernel<0, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
+  else
+    quantize_residual_kernel<0, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
@@ -468,14 +473,24 @@ int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, 
                                   int16_t *work, int rdoq_skip, cudaStream_t stream)
 {
   if (n_jobs <= 0) return 1;
-  if (!opt_in_smem(quantize_residual_kernel<1>) || !opt_in_smem(quantize_residual_kernel<2>)) return 0;
-  quantize_residual_kernel<1><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+  if (!opt_in_smem(quantize_residual_kernel<1, uint8_t>) || !opt_in_smem(quantize_residual_kernel<2, uint8_t>) ||
+      !opt_in_smem(quantize_residual_kernel<1, uint16_t>) || !opt_in_smem(quantize_residual_kernel<2, uint16_t>)) return 0;
+  const bool wide = c.bitdepth > 8;
+  if (wide)
+    quantize_residual_kernel<1, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+  else
+    quantize_residual_kernel<1, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   if (!launch_rdoq_batch(c, d_ctx, work, coeff, rdoq_jobs, n_jobs, max_width, rdoq_skip, stream)) return 0;
-  quantize_residual_kernel<2><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-      c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+  if (wide)
+    quantize_residual_kernel<2, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+  else
+    quantize_residual_kernel<2, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

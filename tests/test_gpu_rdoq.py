@@ -84,17 +84,25 @@ def test_rdoq_frame_batch_properties():
     assert not out[::17].any() and out.any()
 
 
+@pytest.mark.parametrize("bitdepth", [8, 10])
 @pytest.mark.parametrize("rdoq_skip", [0, 1])
-def test_fused_quantize_residual_with_rdoq(rdoq_skip):
+def test_fused_quantize_residual_with_rdoq(rdoq_skip, bitdepth):
     """kvz_cuda_quantize_residuals_rdoq == kvz_quantize_residual with cfg.rdoq_enable (oracle, pinned on the reference)"""
     import torch
     from kvazaar_b200 import blocks
     O = kvzlibs.oracle()
-    O.kvzo_quantize_residual_rdoq_8.argtypes = [C.c_void_p, C.c_double, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p] * 4
+    fn = O.kvzo_quantize_residual_rdoq_8 if bitdepth == 8 else O.kvzo_quantize_residual_rdoq_10
+    fn.argtypes = [C.c_void_p, C.c_double, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p] * 4
     rs = np.random.default_rng(15 + rdoq_skip)
     W, H = 256, 128
     f = kvzlibs.synth_luma(9, W, H, 2)
     ref, pred = f[1], f[0]
+    pix = np.uint8
+    if bitdepth > 8:
+        pix = np.uint16
+        ref = np.ascontiguousarray((ref.astype(np.uint16) << 2) | rs.integers(0, 4, ref.shape, dtype=np.uint16))
+        pred = np.ascontiguousarray((pred.astype(np.uint16) << 2) | rs.integers(0, 4, pred.shape, dtype=np.uint16))
+    dev = lambda a: torch.from_numpy(a.view(np.int16) if a.dtype == np.uint16 else a).cuda()
     for signhide in (0, 1):
         rows, rq, coff = [], [], 0
         n_ctx = 5
@@ -115,20 +123,20 @@ def test_fused_quantize_residual_with_rdoq(rdoq_skip):
             coff += n * n
         jobs = np.array(rows, blocks.RESIDUAL_JOB_DT)
         rjobs = np.array(rq, blocks.RDOQ_JOB_DT)
-        d_rec = torch.zeros((len(jobs), H, W), dtype=torch.uint8, device="cuda")
+        d_rec = torch.zeros((len(jobs), H, W), dtype=torch.uint8 if bitdepth == 8 else torch.int16, device="cuda")
         jobs["rec_offset"] += (np.arange(len(jobs)) * H * W).astype(np.uint32)
         d_coeff = torch.zeros(coff, dtype=torch.int16, device="cuda")
-        has = blocks.quantize_residuals_rdoq(torch.from_numpy(ref).cuda(), torch.from_numpy(pred).cuda(), d_rec, d_coeff,
+        has = blocks.quantize_residuals_rdoq(dev(ref), dev(pred), d_rec, d_coeff,
                                              jobs, ctxs, rjobs, slice_is_intra=False, signhide=signhide,
-                                             rdoq_skip=rdoq_skip).cpu().numpy()
-        rec, coeff = d_rec.cpu().numpy(), d_coeff.cpu().numpy()
+                                             rdoq_skip=rdoq_skip, bitdepth=bitdepth).cpu().numpy()
+        rec, coeff = d_rec.cpu().numpy().view(pix), d_coeff.cpu().numpy()
         for i, (jb, rj) in enumerate(zip(jobs, rjobs)):
             n = int(jb["width"])
-            oc = kvzlibs.OracleQCfg(int(jb["qp"]), 8, 0, signhide, int(jb["cu_is_intra"]))
-            rw = np.zeros((n, n), np.uint8); cw = np.zeros(n * n, np.int16)
+            oc = kvzlibs.OracleQCfg(int(jb["qp"]), bitdepth, 0, signhide, int(jb["cu_is_intra"]))
+            rw = np.zeros((n, n), pix); cw = np.zeros(n * n, np.int16)
             off = int(jb["ref_offset"])
             cx = ctx_list[int(rj["ctx_index"])]
-            hw = O.kvzo_quantize_residual_rdoq_8(C.addressof(oc), float(rj["lambda"]), C.addressof(cx), rdoq_skip,
+            hw = fn(C.addressof(oc), float(rj["lambda"]), C.addressof(cx), rdoq_skip,
                                                  int(rj["tr_depth"]), n, int(jb["color"]), int(jb["scan_idx"]),
                                                  int(jb["use_trskip"]), W, n, ptr(ref.reshape(-1)[off:]),
                                                  ptr(pred.reshape(-1)[off:]), ptr(rw), ptr(cw))

@@ -78,7 +78,8 @@ def test_coeff_abs_sum_known_answer():
     assert int(got[0]) == int(np.abs(c.astype(np.int64)).sum())
 
 
-def test_fused_quantize_residual():
+@pytest.mark.parametrize("bitdepth", [8, 10])
+def test_fused_quantize_residual(bitdepth):
     import torch
     from kvazaar_b200 import blocks
     O = kvzlibs.oracle()
@@ -86,6 +87,13 @@ def test_fused_quantize_residual():
     W, H = 256, 128
     f = kvzlibs.synth_luma(9, W, H, 2)
     ref, pred = f[1], f[0]
+    pix = np.uint8
+    if bitdepth > 8:
+        pix = np.uint16
+        ref = np.ascontiguousarray((ref.astype(np.uint16) << 2) | rs.integers(0, 4, ref.shape, dtype=np.uint16))
+        pred = np.ascontiguousarray((pred.astype(np.uint16) << 2) | rs.integers(0, 4, pred.shape, dtype=np.uint16))
+    dev = lambda a: torch.from_numpy(a.view(np.int16) if a.dtype == np.uint16 else a).cuda()
+    fn = O.kvzo_quantize_residual_8 if bitdepth == 8 else O.kvzo_quantize_residual_10
     for intra_slice in (0, 1):
         for signhide in (0, 1):
             rows, coff = [], 0
@@ -99,18 +107,17 @@ def test_fused_quantize_residual():
                 coff += n * n
             jobs = np.array(rows, blocks.RESIDUAL_JOB_DT)
             # overlapping rec blocks would race: give every job its own rec plane row band instead
-            d_rec = torch.zeros((len(jobs), H, W), dtype=torch.uint8, device="cuda")
+            d_rec = torch.zeros((len(jobs), H, W), dtype=torch.uint8 if bitdepth == 8 else torch.int16, device="cuda")
             jobs["rec_offset"] += (np.arange(len(jobs)) * H * W).astype(np.uint32)
             d_coeff = torch.zeros(coff, dtype=torch.int16, device="cuda")
-            has = blocks.quantize_residuals(torch.from_numpy(ref).cuda(), torch.from_numpy(pred).cuda(), d_rec,
-                                            d_coeff, jobs, intra_slice, signhide).cpu().numpy()
-            rec, coeff = d_rec.cpu().numpy(), d_coeff.cpu().numpy()
+            has = blocks.quantize_residuals(dev(ref), dev(pred), d_rec, d_coeff, jobs, intra_slice, signhide, bitdepth).cpu().numpy()
+            rec, coeff = d_rec.cpu().numpy().view(pix), d_coeff.cpu().numpy()
             for i, jb in enumerate(jobs):
                 n = int(jb["width"])
-                oc = kvzlibs.OracleQCfg(int(jb["qp"]), 8, intra_slice, signhide, int(jb["cu_is_intra"]))
-                rw = np.zeros((n, n), np.uint8); cw = np.zeros(n * n, np.int16)
+                oc = kvzlibs.OracleQCfg(int(jb["qp"]), bitdepth, intra_slice, signhide, int(jb["cu_is_intra"]))
+                rw = np.zeros((n, n), pix); cw = np.zeros(n * n, np.int16)
                 off = int(jb["ref_offset"])
-                hw = O.kvzo_quantize_residual_8(C.byref(oc), n, int(jb["color"]), int(jb["scan_idx"]),
+                hw = fn(C.byref(oc), n, int(jb["color"]), int(jb["scan_idx"]),
                                                 int(jb["use_trskip"]), W, n, ptr(ref.reshape(-1)[off:]),
                                                 ptr(pred.reshape(-1)[off:]), ptr(rw), ptr(cw))
                 y, x = off // W, off % W
