@@ -394,10 +394,30 @@ def main():
     ap.add_argument("--separate-windows", action="store_true",
                     help="one square-window SAD map set per window centre instead of one box per reference")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly ONE JSON line: whatever libraries write to file descriptor 1 while the bench runs (NCCL's
+    # version banner, for one) goes to stderr instead; the result line is written to the real stdout at the end
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    lines = []
+    global print
+    builtin_print = print
+
+    def print(*a, **k):                      # noqa: A001 -- the two result prints of this file
+        lines.append(" ".join(str(x) for x in a))
+
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        print = builtin_print
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    for ln in lines:
+        builtin_print(ln, flush=True)
 
 
 if __name__ == "__main__":
