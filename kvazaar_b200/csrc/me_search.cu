@@ -204,6 +204,37 @@ __device__ __noinline__ uint32_t sad_on_demand(const MeFrame &f, const MeRef &r,
   return acc;
 }
 
+// the same over the rows row0, row0 + rstep, ... only (a lane group shares one candidate)
+__device__ __noinline__ uint32_t sad_on_demand_rows(const MeFrame &f, const MeRef &r, const uint8_t *cur, int cur_pitch, int w, int h,
+                                                    int rx, int ry, int row0, int rstep)
+{
+  rx = clampi(rx, -r.pad, f.width + r.pad - w);
+  ry = clampi(ry, -r.pad, f.height + r.pad - h);
+  const uint8_t *p = r.plane + (size_t)(ry + r.pad + row0) * r.pitch + (rx + r.pad);
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const int sh = (int)(a & 3) * 8;
+  const uint32_t *rw = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+  const int wpitch = r.pitch >> 2;
+  uint32_t acc = 0;
+  for (int yy = row0; yy < h; yy += rstep) {
+    const uint32_t *cw = reinterpret_cast<const uint32_t *>(cur + (size_t)yy * cur_pitch);
+    uint32_t prev = __ldg(rw);
+    for (int c = 0; c < (w >> 2); c++) {
+      uint32_t v = prev;
+      if (sh) {
+        const uint32_t nxt = __ldg(rw + c + 1);
+        v = __funnelshift_r(prev, nxt, sh);
+        prev = nxt;
+      } else if (c + 1 < (w >> 2)) {
+        prev = __ldg(rw + c + 1);
+      }
+      acc = sad4(__ldg(cw + c), v, acc);
+    }
+    rw += wpitch * rstep;
+  }
+  return acc;
+}
+
 __device__ __forceinline__ unsigned long long warp_min(unsigned long long v)
 {
 #pragma unroll
@@ -346,26 +377,30 @@ struct HeurState {
   int mvx, mvy;                     // whole samples
 };
 
-// Lane i < n evaluates candidate (px, py) (its own); returns the index of the candidate that became the new
-// best, or -1 if none beats the current best (all lanes return the same value).
+// Lane i < n HOLDS candidate i = (px, py); the warp is cut into groups of 32 / 8 = 4 lanes (8 lanes when n <= 4),
+// group g evaluates candidate g with its lanes taking every 4th (8th) row of the PU.  Returns the index of the
+// candidate that became the new best, or -1 if none beats the current best (all lanes return the same value).
 __device__ int probe_set(const MeFrame &f, const MeRef &ref, const JobCtx &j, const uint8_t *cur, int fx0, int fy0,
                          bool free_mv, int lane, int n, int px, int py, HeurState &h)
 {
+  const int gl = n <= 4 ? 3 : 2, G = 1 << gl;                  // log2 of the lanes per candidate
+  const int pr = lane >> gl, sub = lane & (G - 1);
+  const int qx = __shfl_sync(0xffffffffu, px, pr), qy = __shfl_sync(0xffffffffu, py, pr);
+  const bool live = pr < n && (free_mv || within_tile(f, j, qx * 4, qy * 4));
+  uint32_t sad = live ? sad_on_demand_rows(f, ref, cur, f.cur_pitch, j.w, j.h, fx0 + qx, fy0 + qy, sub, G) : 0u;
+  for (int o = G >> 1; o > 0; o >>= 1) sad += __shfl_xor_sync(0xffffffffu, sad, o);
   uint32_t cost = 0xFFFFFFFFu, bits = 0;
-  if (lane < n && (free_mv || within_tile(f, j, px * 4, py * 4))) {
-    const uint32_t sad = sad_on_demand(f, ref, cur, f.cur_pitch, j.w, j.h, fx0 + px, fy0 + py);
-    if (sad < h.best_cost) {                                   // check_mv_cost (search_inter.c:211)
-      bits = mvd_cost_bits(j, px, py, 2);
-      cost = sad + bits * (uint32_t)j.lambda;
-    }
+  if (live && sad < h.best_cost) {                             // check_mv_cost (search_inter.c:211)
+    bits = mvd_cost_bits(j, qx, qy, 2);
+    cost = sad + bits * (uint32_t)j.lambda;
   }
-  unsigned long long key = ((unsigned long long)cost << 8) | (unsigned)lane;
+  unsigned long long key = ((unsigned long long)cost << 8) | (unsigned)pr;
   key = warp_min(key);
   const uint32_t wcost = (uint32_t)(key >> 8);
   const int win = (int)(key & 0xFFu);
   if (wcost >= h.best_cost) return -1;
   h.best_cost = wcost;
-  h.best_bits = __shfl_sync(0xffffffffu, bits, win);
+  h.best_bits = __shfl_sync(0xffffffffu, bits, win << gl);
   h.mvx = __shfl_sync(0xffffffffu, px, win);
   h.mvy = __shfl_sync(0xffffffffu, py, win);
   return win;
