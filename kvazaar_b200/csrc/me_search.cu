@@ -369,7 +369,7 @@ __device__ KVZ_BOX_INLINE uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint
 // ======================================================================================
 // heuristic integer searches (hexagon_search search_inter.c:690-778, diamond_search :796-883,
 // select_starting_point :282-307, early_terminate :415-460): one warp per (PU, reference) job.
-// The probes of one step are independent candidates, so lane i evaluates probe i and the step's
+// The probes of one step are independent candidates, so a lane group evaluates probe i (lane i holds its coordinates) and the step's
 // outcome -- check_mv_cost's strict '<' over the probes in order -- is the (cost, index) minimum.
 // ======================================================================================
 struct HeurState {
