@@ -238,11 +238,12 @@ COEFF_JOB_DT = np.dtype([("coef_offset", "<u4"), ("ctx_index", "<u4"), ("range",
 assert COEFF_JOB_DT.itemsize == 16
 
 
-def coeff_bits(d_coeffs, ctxs, jobs, signhide=False, trskip_enable=False):
+def coeff_bits(d_coeffs, ctxs, jobs, signhide=False, trskip_enable=False, d_jobs=None):
     """kvz_get_coeff_cost's CABAC path (rdo.c:158-197) for a batch of coefficient blocks.  d_coeffs: device int16;
-    ctxs: numpy RDOQ_CTX_DT snapshots (or a device tensor of them); jobs: numpy COEFF_JOB_DT.  Returns device int32 bits."""
+    ctxs: numpy RDOQ_CTX_DT snapshots (or a device tensor of them); jobs: numpy COEFF_JOB_DT (d_jobs: the same array
+    already on the device).  Returns device int32 bits."""
     capi.init(torch.cuda.current_device())
-    d_jobs = _dev(jobs)
+    d_jobs = d_jobs if d_jobs is not None else _dev(jobs)
     d_ctx = _dev(ctxs) if isinstance(ctxs, np.ndarray) else ctxs
     out = torch.zeros(len(jobs), dtype=torch.int32, device="cuda")
     max_width = int(jobs["width"].max()) if len(jobs) else 4

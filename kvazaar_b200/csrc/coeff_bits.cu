@@ -12,6 +12,7 @@
 // nobody looks at afterwards), so lanes also precompute every position's significance context.  Lane 0 then
 // runs the chain the reference runs: the context-coded bins in coding order, each updating `range` and its
 // context state; bypass bins only add their count.
+#include <cstdlib>
 #include "common.cuh"
 #include "transform.cuh"
 #include "../../include/kvz_cuda.h"
@@ -45,18 +46,24 @@ __device__ __constant__ uint8_t c_cb_last_group[32] = { 0, 1, 2, 3, 4, 4, 5, 5, 
                                                         8, 8, 8, 8, 8, 8, 8, 8, 9, 9, 9, 9, 9, 9, 9, 9 };
 __device__ __constant__ uint8_t c_cb_sig_map4x4[16] = { 0, 1, 4, 5, 2, 3, 4, 5, 6, 6, 8, 8, 7, 7, 8, 8 };   // context.c:357-363
 
-struct Counter { uint32_t range, bits; };
+// `range`, the bit count, and where the coder's tables live: constant memory for the warp-per-block kernel (one lane
+// reads them), a shared-memory copy for the thread-per-block kernel (32 lanes read 32 different entries, which
+// the constant cache would serialise)
+struct Counter {
+  uint32_t range, bits;
+  const uint8_t *lps, *next, *renorm;
+};
 
 // kvz_cabac_encode_bin (cabac.c:91-120) without `low`; state = (pStateIdx << 1) | valMps
 __device__ __forceinline__ void count_bin(Counter &b, uint8_t &state, int bin)
 {
-  const uint32_t st = state >> 1, lps = c_range_lps[st][(b.range >> 6) & 3];
+  const uint32_t st = state >> 1, lps = b.lps[st * 4 + ((b.range >> 6) & 3)];
   b.range -= lps;
   if (bin != (int)(state & 1)) {
-    const int shift = c_renorm[lps >> 3];
+    const int shift = b.renorm[lps >> 3];
     b.range = lps << shift;
     b.bits += shift;
-    state = st == 0 ? (uint8_t)(state ^ 1) : (uint8_t)((c_next_lps[st] << 1) | (state & 1));
+    state = st == 0 ? (uint8_t)(state ^ 1) : (uint8_t)((b.next[st] << 1) | (state & 1));
   } else {
     if (st < 62) state += 2;
     if (b.range < 256) { b.range <<= 1; b.bits += 1; }
@@ -64,10 +71,10 @@ __device__ __forceinline__ void count_bin(Counter &b, uint8_t &state, int bin)
 }
 
 // context.c:354-385
-__device__ int cb_sig_ctx_inc(int pattern, int scan_idx, int x, int y, int lg, bool chroma)
+__device__ int cb_sig_ctx_inc(int pattern, int scan_idx, int x, int y, int lg, bool chroma, const uint8_t *map4 = c_cb_sig_map4x4)
 {
   if (x + y == 0) return 0;
-  if (lg == 2) return c_cb_sig_map4x4[4 * y + x];
+  if (lg == 2) return map4[4 * y + x];
   const int base = lg == 3 ? (scan_idx == 0 ? 9 : 15) : (chroma ? 12 : 21);
   const int xs = x & 3, ys = y & 3;
   int cnt;
@@ -141,7 +148,7 @@ coeff_bits_kernel(const kvz_cuda_rdoq_ctx *__restrict__ ctxs, const int16_t *__r
   if (lane != 0) return;
 
   // ---- lane 0: the chain ----
-  Counter b = { jb.range, 0 };
+  Counter b = { jb.range, 0, &c_range_lps[0][0], c_next_lps, c_renorm };
   kvz_cuda_rdoq_ctx &ctx = H.ctx;
   const int cg_last = last_scan >> 4, pos_last = H.scan.pos[last_scan];
   if (width == 4 && trskip_enable) count_bin(b, chroma ? ctx.trskip_chroma : ctx.trskip_luma, 0);
@@ -236,12 +243,194 @@ coeff_bits_kernel(const kvz_cuda_rdoq_ctx *__restrict__ ctxs, const int16_t *__r
   bits_out[blockIdx.x] = b.bits;
 }
 
+// ---- blocks up to 8x8: one THREAD per block ----
+// The chain is serial per block whatever the width; a warp per block leaves 31 lanes idle during it.  For 4x4 and
+// 8x8 blocks (the bulk of a frame) every lane runs the chain of its own block: coefficients in registers / local
+// memory, its private copy of the context snapshot in shared memory (the chain updates it), scan order from a
+// constant table filled by the host on first use.
+constexpr int kSmallT = 64;
+__device__ __constant__ uint8_t c_small_scan[2][3][64];       // [log2 width - 2][scan_idx][scan position] -> block position
+
+__global__ void __launch_bounds__(kSmallT)
+coeff_bits_small_kernel(const kvz_cuda_rdoq_ctx *__restrict__ ctxs, const int16_t *__restrict__ coef_g,
+                        const kvz_cuda_coeff_job *__restrict__ jobs, int n_jobs, int signhide, int trskip_enable,
+                        uint32_t *__restrict__ bits_out)
+{
+  __shared__ kvz_cuda_rdoq_ctx s_ctx[kSmallT];
+  __shared__ uint8_t s_lps[256], s_next[64], s_renorm[32], s_last_group[32], s_map4[16], s_scan[2 * 3 * 64];
+  for (int i = threadIdx.x; i < 256; i += kSmallT) s_lps[i] = (&c_range_lps[0][0])[i];
+  for (int i = threadIdx.x; i < 64; i += kSmallT) s_next[i] = c_next_lps[i];
+  for (int i = threadIdx.x; i < 32; i += kSmallT) { s_renorm[i] = c_renorm[i]; s_last_group[i] = c_cb_last_group[i]; }
+  for (int i = threadIdx.x; i < 16; i += kSmallT) s_map4[i] = c_cb_sig_map4x4[i];
+  for (int i = threadIdx.x; i < 2 * 3 * 64; i += kSmallT) s_scan[i] = (&c_small_scan[0][0][0])[i];
+  __syncthreads();
+  const int ji = blockIdx.x * kSmallT + threadIdx.x;
+  if (ji >= n_jobs) return;
+  const kvz_cuda_coeff_job jb = jobs[ji];
+  const int width = jb.width, lg = ilog2_pow2(width), nn = width * width, side = width >> 2;
+  const bool chroma = jb.type != 0;
+  const uint8_t *scan = s_scan + ((lg - 2) * 3 + jb.scan_idx) * 64;
+  alignas(8) int16_t coef[64];
+  {
+    const int16_t *src16 = coef_g + jb.coef_offset;
+    if ((reinterpret_cast<uintptr_t>(src16) & 7) == 0) {       // the usual case: blocks packed back to back
+      const uint2 *src = reinterpret_cast<const uint2 *>(src16);
+      uint2 *dst = reinterpret_cast<uint2 *>(coef);
+      for (int i = 0; i < nn / 4; i++) dst[i] = src[i];
+    } else {
+      for (int i = 0; i < nn; i++) coef[i] = src16[i];
+    }
+  }
+  unsigned group_sig = 0;                                     // bit gy * side + gx
+  int last_scan = -1;
+  for (int sp = 0; sp < nn; sp++) {
+    const int bp = scan[sp];
+    if (coef[bp] != 0) { last_scan = sp; group_sig |= 1u << (((bp >> lg) >> 2) * side + ((bp & (width - 1)) >> 2)); }
+  }
+  if (last_scan < 0) { bits_out[ji] = 0; return; }
+  kvz_cuda_rdoq_ctx &ctx = s_ctx[threadIdx.x];
+  {
+    const uint32_t *cs = reinterpret_cast<const uint32_t *>(ctxs + jb.ctx_index);
+    uint32_t *cd = reinterpret_cast<uint32_t *>(&ctx);
+    for (int i = 0; i < (int)(sizeof(kvz_cuda_rdoq_ctx) / 4); i++) cd[i] = cs[i];
+  }
+  Counter b = { jb.range, 0, s_lps, s_next, s_renorm };
+  const int cg_last = last_scan >> 4, pos_last = scan[last_scan];
+  if (width == 4 && trskip_enable) count_bin(b, chroma ? ctx.trskip_chroma : ctx.trskip_luma, 0);
+  {
+    int lx = pos_last & (width - 1), ly = pos_last >> lg;
+    const int index = lg - 2;
+    const int ctx_offset = chroma ? 0 : index * 3 + (index + 1) / 4;
+    const int shift = chroma ? index : (index + 3) / 4;
+    uint8_t *mx = chroma ? ctx.last_x_chroma : ctx.last_x_luma, *my = chroma ? ctx.last_y_chroma : ctx.last_y_luma;
+    if (jb.scan_idx == 2) { const int t = lx; lx = ly; ly = t; }
+    const int gx = s_last_group[lx], gy = s_last_group[ly], gmax = s_last_group[width - 1];
+    for (int i = 0; i < gx; i++) count_bin(b, mx[ctx_offset + (i >> shift)], 1);
+    if (gx < gmax) count_bin(b, mx[ctx_offset + (gx >> shift)], 0);
+    for (int i = 0; i < gy; i++) count_bin(b, my[ctx_offset + (i >> shift)], 1);
+    if (gy < gmax) count_bin(b, my[ctx_offset + (gy >> shift)], 0);
+    if (gx > 3) b.bits += (gx - 2) / 2;
+    if (gy > 3) b.bits += (gy - 2) / 2;
+  }
+  uint8_t *sig_models = chroma ? ctx.sig_chroma : ctx.sig_luma;
+  int c1 = 1, scan_pos = last_scan;
+  for (int g = cg_last; g >= 0; g--) {
+    const int sub_pos = g << 4, gbp = scan[sub_pos];
+    const int cgx = (gbp & (width - 1)) >> 2, cgy = (gbp >> lg) >> 2;
+    int abs_coeff[16], n_nz = 0, last_nz = -1, first_nz = 16;
+    uint32_t rice = 0;
+    if (scan_pos == last_scan) {
+      abs_coeff[0] = abs((int)coef[pos_last]);
+      n_nz = 1; last_nz = first_nz = scan_pos;
+      scan_pos--;
+    }
+    const int r = cgx < side - 1 ? (group_sig >> (cgy * side + cgx + 1)) & 1 : 0;
+    const int d = cgy < side - 1 ? (group_sig >> ((cgy + 1) * side + cgx)) & 1 : 0;
+    bool coded = (group_sig >> (cgy * side + cgx)) & 1;
+    if (g == cg_last || g == 0) coded = true;
+    else count_bin(b, ctx.sig_group[jb.type + ((r | d) != 0)], coded);
+    if (coded) {
+      const int pattern = width == 4 ? -1 : r + (d << 1);
+      for (; scan_pos >= sub_pos; scan_pos--) {
+        const int bp = scan[scan_pos], level = coef[bp], sig = level != 0;
+        if (scan_pos > sub_pos || g == 0 || n_nz)
+          count_bin(b, sig_models[cb_sig_ctx_inc(pattern, jb.scan_idx, bp & (width - 1), bp >> lg, lg, chroma, s_map4)], sig);
+        if (sig) {
+          abs_coeff[n_nz++] = abs(level);
+          if (last_nz == -1) last_nz = scan_pos;
+          first_nz = scan_pos;
+        }
+      }
+    } else {
+      scan_pos = sub_pos - 1;
+    }
+    if (n_nz > 0) {
+      const bool sign_hidden = last_nz - first_nz >= 4;
+      int ctx_set = (g > 0 && !chroma) ? 2 : 0;
+      if (c1 == 0) ctx_set++;
+      c1 = 1;
+      uint8_t *one = (chroma ? ctx.one_chroma : ctx.one_luma) + 4 * ctx_set;
+      const int n_c1 = min(n_nz, 8);
+      int first_c2 = -1;
+      for (int i = 0; i < n_c1; i++) {
+        const int sym = abs_coeff[i] > 1;
+        count_bin(b, one[c1], sym);
+        if (sym) { c1 = 0; if (first_c2 == -1) first_c2 = i; }
+        else if (c1 < 3 && c1 > 0) c1++;
+      }
+      if (c1 == 0 && first_c2 != -1)
+        count_bin(b, (chroma ? ctx.abs_chroma : ctx.abs_luma)[ctx_set], abs_coeff[first_c2] > 2);
+      b.bits += (signhide && sign_hidden) ? n_nz - 1 : n_nz;
+      if (c1 == 0 || n_nz > 8) {
+        int first_coeff2 = 1;
+        for (int i = 0; i < n_nz; i++) {
+          const int base = i < 8 ? 2 + first_coeff2 : 1;
+          if (abs_coeff[i] >= base) {
+            const uint32_t symbol = (uint32_t)(abs_coeff[i] - base);
+            if (symbol < (3u << rice)) {
+              b.bits += (symbol >> rice) + 1 + rice;
+            } else {
+              uint32_t length = rice, code = symbol - (3u << rice);
+              while (code >= (1u << length)) { code -= 1u << length; length++; }
+              b.bits += (3 + length + 1 - rice) + length;
+            }
+            if (abs_coeff[i] > 3 * (1 << rice)) rice = min(rice + 1, 4u);
+          }
+          if (abs_coeff[i] >= 2) first_coeff2 = 0;
+        }
+      }
+    }
+  }
+  bits_out[ji] = b.bits;
+}
+
+// the scan orders of 4x4 and 8x8 blocks, as build_scan_table_t (transform.cuh) makes them
+void host_small_scans(uint8_t out[2][3][64])
+{
+  for (int lgi = 0; lgi < 2; lgi++)
+    for (int scan = 0; scan < 3; scan++) {
+      const int n = 4 << lgi, gs = n >> 2;
+      uint8_t gx[4], gy[4], px[16], py[16];
+      auto square = [](int scan_idx, int m, uint8_t *xs, uint8_t *ys) {
+        int c = 0;
+        if (scan_idx == 0) {
+          for (int d = 0; d <= 2 * (m - 1); d++)
+            for (int x = (d - (m - 1) > 0 ? d - (m - 1) : 0); x <= (d < m - 1 ? d : m - 1); x++) { xs[c] = (uint8_t)x; ys[c] = (uint8_t)(d - x); c++; }
+        } else if (scan_idx == 1) {
+          for (int y = 0; y < m; y++) for (int x = 0; x < m; x++) { xs[c] = (uint8_t)x; ys[c] = (uint8_t)y; c++; }
+        } else {
+          for (int x = 0; x < m; x++) for (int y = 0; y < m; y++) { xs[c] = (uint8_t)x; ys[c] = (uint8_t)y; c++; }
+        }
+      };
+      square(scan, gs, gx, gy);
+      square(scan, 4, px, py);
+      for (int i = 0; i < n * n; i++) {
+        const int g = i >> 4, k = i & 15;
+        out[lgi][scan][i] = (uint8_t)((gy[g] * 4 + py[k]) * n + gx[g] * 4 + px[k]);
+      }
+    }
+}
+
 }  // namespace
 
 int launch_coeff_bits(const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coeffs, const kvz_cuda_coeff_job *d_jobs,
                       int n_jobs, int max_width, int signhide, int trskip_enable, uint32_t *d_bits, cudaStream_t stream)
 {
   if (n_jobs == 0) return 1;
+  if (max_width <= 8 && !getenv("KVZ_COEFF_BITS_WARP")) {
+    static bool scans_ready = false;
+    if (!scans_ready) {
+      uint8_t tab[2][3][64] = {};
+      host_small_scans(tab);
+      KVZ_CUDA_TRY(cudaMemcpyToSymbol(c_small_scan, tab, sizeof(tab)));
+      scans_ready = true;
+    }
+    coeff_bits_small_kernel<<<(n_jobs + kSmallT - 1) / kSmallT, kSmallT, 0, stream>>>(d_ctx, d_coeffs, d_jobs, n_jobs, signhide,
+                                                                                    trskip_enable, d_bits);
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+    return 1;
+  }
   const size_t smem = coeff_bits_smem(max_width * max_width);
   KVZ_CUDA_TRY(cudaFuncSetAttribute(coeff_bits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   coeff_bits_kernel<<<n_jobs, 32, smem, stream>>>(d_ctx, d_coeffs, d_jobs, signhide, trskip_enable, d_bits);

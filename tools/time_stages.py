@@ -92,7 +92,8 @@ for n in (4, 8, 16, 32):
     cj["ctx_index"] = np.arange(cnt) % 64
     cj["range"], cj["width"] = 400, n
     cctx = blocks._dev(np.frombuffer(rs.integers(0, 126, 64 * 148, dtype=np.uint8).tobytes(), blocks.RDOQ_CTX_DT).copy())
-    put(f"coeff_bits{n}", timed(lambda: blocks.coeff_bits(lv, cctx, cj, True, False)), cnt, cnt * n * n * 2,
+    d_cj = blocks._dev(cj)
+    put(f"coeff_bits{n}", timed(lambda: blocks.coeff_bits(lv, cctx, cj, True, False, d_jobs=d_cj)), cnt, cnt * n * n * 2,
         "kvz_get_coeff_cost CABAC path, one warp per block (serial context chain per block)")
 
 # picture-level reductions: 4:2:0 pictures, all three planes in one launch
