@@ -1,6 +1,6 @@
 """Frame-scale device timings of the batch kernels beside the ME stage (rows A13-A17 of SURVEY.md 8a): one 1080p
 frame's worth of blocks per launch, CUDA events on the launching stream, inputs resident.  Prints one JSON object;
-bytes are the algorithmic bytes of DESIGN.md section 4."""
+bytes are the algorithmic bytes of DESIGN.md section 4.  Job / parameter arrays are uploaded once (blocks.keep_on_device), not per timed call."""
 import json, os, sys
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
@@ -54,6 +54,7 @@ for n in (4, 8, 16, 32):
     jobs["coeff_offset"] = np.arange(cnt, dtype=np.uint32) * n * n
     jobs["in_stride"] = jobs["out_stride"] = W
     jobs["width"], jobs["qp"], jobs["cu_is_intra"] = n, 32, 1
+    blocks.keep_on_device(jobs)
     d_rec = torch.zeros((H, W), dtype=torch.uint8, device="cuda")
     d_co = torch.zeros(cnt * n * n, dtype=torch.int16, device="cuda")
     put(f"quantize_residual{n}", timed(lambda: blocks.quantize_residuals(d_src, d_pred, d_rec, d_co, jobs, True, True)), cnt,
@@ -62,6 +63,7 @@ for n in (4, 8, 16, 32):
     rj["coef_offset"] = jobs["coeff_offset"]; rj["ctx_index"] = np.arange(cnt) % 64; rj["lambda"] = 40.0
     rj["width"], rj["qp"], rj["cu_is_intra"] = n, 32, 1
     ctxs = np.frombuffer(rs.integers(0, 128, 64 * 148, dtype=np.uint8).tobytes(), blocks.RDOQ_CTX_DT).copy()
+    blocks.keep_on_device(rj); blocks.keep_on_device(ctxs)
     put(f"quantize_residual{n}_rdoq", timed(lambda: blocks.quantize_residuals_rdoq(d_src, d_pred, d_rec, d_co, jobs, ctxs, rj, True, True)),
         cnt, cnt * n * n * 9, "transform | kvz_rdoq | reconstruction, three launches (latency-bound serial chain per block)")
 
@@ -78,6 +80,7 @@ for lg in (2, 3, 4, 5):
     jobs["log2_width"], jobs["filter_boundary"] = lg, 1
     jobs[jobs.dtype.names[-1]] = 1
     d_refs = torch.from_numpy(refs).cuda()
+    blocks.keep_on_device(jobs)
     ms = timed(lambda: blocks.intra_mode_costs(d_refs, d_src, jobs), 5)
     out["stages"][f"intra_costs{n}"] = {"blocks": cnt, "ms": round(ms, 4), "Mblocks_per_s": round(cnt / ms / 1e3, 1),
                                         "predicted_Gsamples_per_s": round(cnt * 35 * n * n / ms / 1e6, 1),
