@@ -93,6 +93,59 @@ __device__ void quant_block(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type
   const int n_cg = (N * N) >> 4;
   auto q_at = [&](int pos) -> int16_t & { return sm.b[(pos / N) * P + (pos % N)]; };
   auto c_at = [&](int pos) -> int { return sm.a[(pos / N) * P + (pos % N)]; };
+  if constexpr (T == 32) {
+    // a warp owns the block (4x4 / 8x8: 1 or 4 groups): lanes 0..15 take the 16 scan positions of a group, the
+    // reference's backward walk with its strict '<' (the first minimum met coming down from the top wins) becomes an
+    // arg-min over (cost, 15 - n)
+    const int n = tid & 15;
+    const bool act = tid < 16;
+    int last_cg = -1;
+    for (int g = 0; g < n_cg; g++)
+      if (__ballot_sync(0xffffffffu, act && q_at(sm.scan.pos[g * 16 + n]) != 0)) last_cg = g;
+    for (int g = 0; g < n_cg; g++) {
+      const int p = sm.scan.pos[g * 16 + n];
+      const int q = q_at(p), dl = sm.delta[p], cf = c_at(p);
+      const unsigned nz = __ballot_sync(0xffffffffu, act && q != 0);
+      if (!nz) continue;
+      const int first = __ffs(nz) - 1, last = 31 - __clz(nz);
+      if (last - first < 4) continue;
+      int sum = act && n >= first && n <= last ? q : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      const int signbit = __shfl_sync(0xffffffffu, q, first) > 0 ? 0 : 1;
+      if (signbit == (sum & 1)) continue;
+      const int top = g == last_cg ? last : 15;
+      int cost = 0x7FFFFFFF, cur_change = 0;
+      if (act && n <= top) {
+        if (q != 0) {
+          if (dl > 0) { cost = -dl; cur_change = 1; }
+          else if (n == first && abs(q) == 1) { cost = 0x7FFFFFFF; }
+          else { cost = dl; cur_change = -1; }
+        } else if (n < first && ((cf >= 0) ? 0 : 1) != signbit) {
+          cost = 0x7FFFFFFF;
+        } else {
+          cost = -dl; cur_change = 1;
+        }
+      }
+      long long key = (long long)cost * 256 + (15 - n) + (act ? 0 : 64);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const long long t = __shfl_xor_sync(0xffffffffu, key, o);
+        key = t < key ? t : key;
+      }
+      const int wn = 15 - (int)(key & 63);                       // (cost * 256 + r) & 63 == r for r < 64, any sign of cost
+      const int best = __shfl_sync(0xffffffffu, cost, wn);
+      if (best == 0x7FFFFFFF) continue;
+      if (tid == wn) {
+        int change = cur_change;
+        int16_t &qq = q_at(p);
+        if (qq == 32767 || qq == -32768) change = -1;
+        qq = (int16_t)(cf >= 0 ? qq + change : qq - change);
+      }
+    }
+    group_sync<T>();
+    return;
+  }
   for (int g = tid; g < n_cg; g += T) {
     bool any = false;
     for (int n = 0; n < 16; n++) any |= q_at(sm.scan.pos[g * 16 + n]) != 0;
