@@ -39,8 +39,10 @@ __device__ __forceinline__ int main_ref(const PIX *main_in, const PIX *side_in, 
   return i >= -1 ? main_in[i + 1] : side_in[(128 + inv * (-i - 1)) >> 8];
 }
 
+// the calling group strides the samples by `step`: 32 lanes of a warp, or 1 = a single thread predicts the block
 template <typename PIX>
-__device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma, bool filter_boundary, PIX *dst, int lane, int pix_max)
+__device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma, bool filter_boundary, PIX *dst, int lane, int pix_max,
+                             int step = 32)
 {
   const int w = 1 << lg;
   // which reference (intra.c:291-310)
@@ -56,7 +58,7 @@ __device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma,
 
   if (mode == 0) {
     const int tr = top[w + 1], bl = left[w + 1];
-    for (int i = lane; i < w * w; i += 32) {
+    for (int i = lane; i < w * w; i += step) {
       const int y = i >> lg, x = i & (w - 1);
       const int hor = (w - 1 - x) * left[y + 1] + (x + 1) * tr;
       const int ver = (w - 1 - y) * top[x + 1] + (y + 1) * bl;
@@ -64,11 +66,11 @@ __device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma,
     }
   } else if (mode == 1) {
     int sum = 0;
-    for (int i = lane; i < w; i += 32) sum += top[i + 1] + left[i + 1];
-    sum = (int)warp_sum((uint32_t)sum);
+    for (int i = lane; i < w; i += step) sum += top[i + 1] + left[i + 1];
+    if (step == 32) sum = (int)warp_sum((uint32_t)sum);
     const int dc = (sum + w) >> (lg + 1);
     const bool edge = !chroma && w < 32;                     // intra_pred_filtered_dc (intra.c:246-279)
-    for (int i = lane; i < w * w; i += 32) {
+    for (int i = lane; i < w * w; i += step) {
       const int y = i >> lg, x = i & (w - 1);
       int v = dc;
       if (edge) {
@@ -85,7 +87,7 @@ __device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma,
     const int inv = c_inv_disp[abs(md)];
     const PIX *main_in = vertical ? top : left, *side_in = vertical ? left : top;
     const bool post = !chroma && w < 32 && filter_boundary && (mode == 10 || mode == 26);
-    for (int i = lane; i < w * w; i += 32) {
+    for (int i = lane; i < w * w; i += step) {
       // (x, y) in the orientation of a vertical mode; horizontal modes are its transpose
       const int y = i >> lg, x = i & (w - 1);
       const int pos = (y + 1) * disp, di = pos >> 5, fr = pos & 31;
@@ -129,6 +131,26 @@ intra_costs_kernel(const PIX *__restrict__ refs, const PIX *__restrict__ orig_ba
     }
   }
   __syncthreads();
+  if (lg == 2) {
+    // 4x4: one THREAD per mode (a warp per mode would leave 31 lanes idle in the 4x4 Hadamard): 35 threads predict
+    // their 16 samples, transform and sum on their own
+    if (tid < 35) {
+      const int mode = tid;
+      PIX *mine = &sm.pred[0][0] + mode * 16;
+      predict_mode<PIX>(sm, lg, mode, jb.is_chroma != 0, jb.filter_boundary != 0, mine, 0, pix_max, 1);
+      if (preds)
+        for (int i = 0; i < 16; i++) preds[(size_t)jb.pred_offset + (size_t)mode * 16 + i] = mine[i];
+      if (jb.has_orig) {
+        int d[16];
+        uint32_t sad = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) { d[i] = (int)mine[i] - (int)sm.orig[i]; sad += (uint32_t)abs(d[i]); }
+        costs[((size_t)blockIdx.x * 35 + mode) * 2] = satd4_thread(d);          // satd_4x4: not shifted
+        costs[((size_t)blockIdx.x * 35 + mode) * 2 + 1] = sad >> cost_shift;
+      }
+    }
+    return;
+  }
   PIX *dst = sm.pred[warp];
   const StridedBlockT<PIX> a{ dst, w }, b{ sm.orig, w };
   for (int mode = warp; mode < 35; mode += kWarps) {
