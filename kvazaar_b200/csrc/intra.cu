@@ -68,6 +68,10 @@ __device__ void predict_mode(const Smem<PIX> &sm, int lg, int mode, bool chroma,
     int sum = 0;
     for (int i = lane; i < w; i += step) sum += top[i + 1] + left[i + 1];
     if (step == 32) sum = (int)warp_sum((uint32_t)sum);
+    else if (step == 8) {                                     // the 8 lanes that share this mode (other groups of the warp are elsewhere)
+      const unsigned gm = 0xFFu << ((threadIdx.x & 31) & ~7);
+      sum += __shfl_xor_sync(gm, sum, 4); sum += __shfl_xor_sync(gm, sum, 2); sum += __shfl_xor_sync(gm, sum, 1);
+    }
     const int dc = (sum + w) >> (lg + 1);
     const bool edge = !chroma && w < 32;                     // intra_pred_filtered_dc (intra.c:246-279)
     for (int i = lane; i < w * w; i += step) {
@@ -147,6 +151,36 @@ intra_costs_kernel(const PIX *__restrict__ refs, const PIX *__restrict__ orig_ba
         for (int i = 0; i < 16; i++) { d[i] = (int)mine[i] - (int)sm.orig[i]; sad += (uint32_t)abs(d[i]); }
         costs[((size_t)blockIdx.x * 35 + mode) * 2] = satd4_thread(d);          // satd_4x4: not shifted
         costs[((size_t)blockIdx.x * 35 + mode) * 2 + 1] = sad >> cost_shift;
+      }
+    }
+    return;
+  }
+  if (lg == 3) {
+    // 8x8: four modes per warp, EIGHT lanes per mode (one row of the block each: what the 8x8 Hadamard needs)
+    const int sub = lane >> 3, lane8 = lane & 7;
+    PIX *mine = sm.pred[warp] + sub * 64;
+    for (int base = 0; base < 35; base += 4 * kWarps) {
+      const int mode = base + warp * 4 + sub;
+      const bool on = mode < 35;
+      __syncwarp();
+      if (on) predict_mode<PIX>(sm, lg, mode, jb.is_chroma != 0, jb.filter_boundary != 0, mine, lane8, pix_max, 8);
+      __syncwarp();
+      if (on && preds)
+        for (int i = lane8; i < 64; i += 8) preds[(size_t)jb.pred_offset + (size_t)mode * 64 + i] = mine[i];
+      if (jb.has_orig) {
+        int d[8];
+        uint32_t sad = 0;
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+          d[x] = on ? (int)mine[lane8 * 8 + x] - (int)sm.orig[lane8 * 8 + x] : 0;
+          sad += (uint32_t)abs(d[x]);
+        }
+        const uint32_t satd = satd8_rows(d, lane8);            // all 32 lanes take part
+        sad += __shfl_xor_sync(0xffffffffu, sad, 1); sad += __shfl_xor_sync(0xffffffffu, sad, 2); sad += __shfl_xor_sync(0xffffffffu, sad, 4);
+        if (on && lane8 == 0) {
+          costs[((size_t)blockIdx.x * 35 + mode) * 2] = satd >> cost_shift;
+          costs[((size_t)blockIdx.x * 35 + mode) * 2 + 1] = sad >> cost_shift;
+        }
       }
     }
     return;
