@@ -96,3 +96,25 @@ def test_frame_of_pus_feeds_me_search():
     for k, i in enumerate(pick):
         assert got_p[i]["merge_cand"].tobytes() == sp[k]["merge_cand"].tobytes()
         assert np.array_equal(got_j[i * len(refs):(i + 1) * len(refs)]["mv_cand"], sj[k * len(refs):(k + 1) * len(refs)]["mv_cand"])
+
+
+def test_device_candidates_drive_me_search_to_the_oracle_decisions():
+    """A18 -> A3-A5 composed on the device: candidates derived by kvz_cuda_inter_candidates, then kvz_cuda_me_search
+    on those records, against the oracle's candidate derivation followed by the oracle's search"""
+    import me_oracle
+    W, H, n_refs, rng = 200, 136, 2, 8
+    rs = np.random.default_rng(91)
+    sc = co.Scene(rs, W, H, slice_b=False, n_refs=n_refs, p_intra=0.2)
+    f = sc.frame()
+    pus = [p for p in sc.pus(rs, 160) if p[2] % 8 == 0 and p[3] % 8 == 0][:60]
+    P, J, flags, refs = _records(sc, pus)
+    want_p, want_j = P.copy(), J.copy()
+    _oracle_fill(sc, f, pus, want_p, want_j, refs)
+    got_p, got_j = _gpu_fill(sc, P, J, flags)
+    frames = kvzlibs.synth_luma(17, W, H, n_refs + 1)
+    cur, planes = frames[n_refs], [frames[n_refs - 1 - i] for i in range(n_refs)]
+    ref_LX = [[i % n_refs for i in range(16)], [0] * 16]
+    got = me_oracle.gpu_search(got_p, got_j, cur, planes, W, H, rng, 4, 20, use_maps=False, ref_LX=ref_LX)
+    want = me_oracle.oracle_search(want_p, want_j, cur, planes, W, H, rng, 4, 20, ref_LX=ref_LX)
+    me_oracle.assert_results_equal(got, want, want_p)
+    assert got["merged"].any() or (got["mv"] != 0).any()
