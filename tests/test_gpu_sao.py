@@ -107,3 +107,38 @@ def test_reconstruct_luma_only_strided_and_rejects_aliasing():
     assert int(out[:, :16].sum()) == 0 and int(out[:, 216:].sum()) == 0
     with pytest.raises(KvzCudaError):
         blocks.sao_reconstruct([big[:, 8:208]], [big[:, 8:208]], luma.view(blocks.SAO_PARAMS_DT), None)
+
+
+def test_in_loop_filter_chain_on_resident_planes():
+    """deblock -> SAO statistics -> SAO reconstruction -> picture checksum / SSE, every step on the planes the step
+    before left on the device, against the same chain of oracle calls"""
+    import torch
+    import deblock_oracle as do
+    from kvazaar_b200 import blocks
+    from test_oracle_deblock import oracle_deblock
+    from test_oracle_picture_stats import oracle_checksum, oracle_sse
+    rs = np.random.default_rng(55)
+    w, h, qp = 264, 200, 34
+    src = do.picture(rs, w, h, blockiness=0)
+    rec = [np.clip(p.astype(np.int32) + np.kron(rs.integers(-10, 11, ((p.shape[0] + 7) // 8, (p.shape[1] + 7) // 8)),
+                                                np.ones((8, 8), np.int32))[:p.shape[0], :p.shape[1]], 0, 255).astype(np.uint8) for p in src]
+    scus = do.random_scus(rs, w, h, p_intra=0.4, qp=qp)
+    ref_LX = [[i for i in range(16)], [(i + 1) % 4 for i in range(16)]]
+    # oracle chain
+    o_db = oracle_deblock(do.make_cfg(w, h, qp=qp, ref_LX=ref_LX), scus, rec)
+    o_stats = np.concatenate(so.oracle_ctu_stats(src, o_db))
+    counts = [len(list(so.ctu_blocks(p, c))) for p, c in zip(src, (64, 32, 32))]
+    luma, chroma = so.random_params(rs, counts[0]), so.random_params(rs, counts[1])
+    o_out = so.oracle_reconstruct(o_db, luma, chroma)
+    # device chain
+    d_src, d_rec = [_dev(p) for p in src], [_dev(p) for p in rec]
+    blocks.deblock_picture(d_rec, scus.view(blocks.SCU_DT), qp, ref_LX=ref_LX)
+    st = blocks.sao_ctu_stats(d_src, d_rec).cpu().numpy().view(blocks.SAO_STATS_DT)
+    assert np.array_equal(st["edge"], o_stats["edge"]) and np.array_equal(st["band"], o_stats["band"])
+    d_out = [torch.empty_like(t) for t in d_rec]
+    blocks.sao_reconstruct(d_rec, d_out, luma.view(blocks.SAO_PARAMS_DT), chroma.view(blocks.SAO_PARAMS_DT))
+    ck = blocks.picture_checksum(d_out).cpu().numpy().view(np.uint32)
+    sse = blocks.picture_sse(d_src, d_out).cpu().numpy()
+    assert ck.tolist() == [oracle_checksum(p) for p in o_out]
+    assert sse.tolist() == [oracle_sse(a, b) for a, b in zip(src, o_out)]
+    assert not np.array_equal(o_out[0], rec[0])
