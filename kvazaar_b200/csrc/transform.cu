@@ -144,8 +144,7 @@ __device__ void quant_block(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type
       }
     }
     group_sync<T>();
-    return;
-  }
+  } else {
   for (int g = tid; g < n_cg; g += T) {
     bool any = false;
     for (int n = 0; n < 16; n++) any |= q_at(sm.scan.pos[g * 16 + n]) != 0;
@@ -184,6 +183,7 @@ __device__ void quant_block(SM &sm, const kvz_cuda_quant_cfg &c, int N, int type
     qq = (int16_t)(c_at(pos) >= 0 ? qq + change : qq - change);
   }
   group_sync<T>();
+  }
 }
 
 // kvz_dequant (quant-generic.c:279-321, flat list): levels in sm.b -> coefficients in sm.a
