@@ -548,6 +548,23 @@ KVZ_CUDA_API int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg,
                                                   const kvz_cuda_rdoq_job *d_rdoq_jobs, int max_width, int16_t *d_work,
                                                   int rdoq_skip, void *stream);
 
+/* The same without any allocation and without a caller-supplied d_work.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The transform-coefficient scratch is a file-scope device array of
+ * KVZ_CUDA_NOALLOC_MAX_COEFFS int16 (2 MiB, held by every GPU that loads the library until exit); `coeff_elems` is the
+ * number of int16 elements of d_coeff the jobs address (max over jobs of coeff_offset + width * width) and the call
+ * fails with a clear kvz_cuda_last_error() when it exceeds that maximum.  The call makes no cudaMalloc / cudaFree and
+ * uses no allocating library routine; inputs and outputs are still the caller's.  Every call shares the scratch, which
+ * keeps the previous call's contents (nothing in it needs to start at zero: the first stage writes every coefficient
+ * the RDOQ stage reads), so calls that OVERLAP ON THE GPU -- two streams, two host threads -- race; order them. */
+#define KVZ_CUDA_NOALLOC_MAX_COEFFS (1u << 20)
+KVZ_CUDA_API int kvz_cuda_quantize_residuals_rdoq_noalloc(const kvz_cuda_quant_cfg *cfg, const void *d_ref,
+                                                          const void *d_pred, void *d_rec, int16_t *d_coeff,
+                                                          size_t coeff_elems, const kvz_cuda_residual_job *d_jobs,
+                                                          int n_jobs, uint8_t *d_has_coeffs, const kvz_cuda_rdoq_ctx *d_ctx,
+                                                          const kvz_cuda_rdoq_job *d_rdoq_jobs, int max_width,
+                                                          int rdoq_skip, void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: fractional-sample interpolation  (rows A9, A10, A11, A12) */
 /* ------------------------------------------------------------------ */

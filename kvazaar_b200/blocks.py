@@ -283,6 +283,21 @@ def quantize_residuals_rdoq(d_ref, d_pred, d_rec, d_coeff, jobs, ctxs, rdoq_jobs
     return has
 
 
+NOALLOC_MAX_COEFFS = 1 << 20      # KVZ_CUDA_NOALLOC_MAX_COEFFS (include/kvz_cuda.h)
+
+
+def quantize_residuals_rdoq_noalloc(d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has, d_ctx, d_rdoq_jobs, max_width,
+                                    slice_is_intra=False, signhide=False, rdoq_skip=False, bitdepth=8):
+    """kvz_cuda_quantize_residuals_rdoq_noalloc: the call above for callers that cannot allocate.  Every argument is a
+    tensor already on the device (this wrapper allocates nothing either); the transform-coefficient scratch is the
+    library's built-in device array of NOALLOC_MAX_COEFFS int16.  Calls that overlap on the GPU race on it."""
+    cfg = _qcfg(0, bitdepth, slice_is_intra, signhide, False)
+    capi.check(capi.lib().kvz_cuda_quantize_residuals_rdoq_noalloc(
+        C.byref(cfg), _p(d_ref), _p(d_pred), _p(d_rec), _p(d_coeff), d_coeff.numel(), _p(d_jobs), int(n_jobs), _p(d_has),
+        _p(d_ctx), _p(d_rdoq_jobs), int(max_width), int(rdoq_skip), _stream()), "kvz_cuda_quantize_residuals_rdoq_noalloc")
+    return d_has
+
+
 INTERP_PIXEL, INTERP_14BIT, INTERP_FME = 0, 1, 2
 INTERP_JOB_DT = np.dtype([("x", "<i4"), ("y", "<i4"), ("mv_x", "<i4"), ("mv_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                           ("chroma", "u1"), ("mode", "u1"), ("reserved", "u1", (2,)), ("dst_offset", "<u4"),

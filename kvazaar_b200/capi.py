@@ -139,6 +139,8 @@ SIGNATURES = {
     "kvz_cuda_rdoq_blocks": (C.c_int, [C.POINTER(QuantCfg), _VP, _VP, _VP, _VP, C.c_int, C.c_int, _VP]),
     "kvz_cuda_quantize_residuals_rdoq": (C.c_int, [C.POINTER(QuantCfg), _VP, _VP, _VP, _VP, _VP, C.c_int, _VP, _VP, _VP,
                                                    C.c_int, _VP, C.c_int, _VP]),
+    "kvz_cuda_quantize_residuals_rdoq_noalloc": (C.c_int, [C.POINTER(QuantCfg), _VP, _VP, _VP, _VP, C.c_size_t, _VP, C.c_int,
+                                                           _VP, _VP, _VP, C.c_int, C.c_int, _VP]),
     "kvz_cuda_interp_blocks": (C.c_int, [_VP, C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_bipred_blend": (C.c_int, [_VP, _VP, C.c_size_t, C.c_int, _VP, _VP]),
     "kvz_cuda_intra_mode_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),

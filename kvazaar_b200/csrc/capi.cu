@@ -60,6 +60,11 @@ int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, 
                                   const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs,
                                   const kvz_cuda_rdoq_ctx *d_ctx, const kvz_cuda_rdoq_job *rdoq_jobs, int max_width,
                                   int16_t *work, int rdoq_skip, cudaStream_t stream);
+int launch_quantize_residual_rdoq_noalloc(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec,
+                                          int16_t *coeff, size_t coeff_elems, const kvz_cuda_residual_job *jobs, int n_jobs,
+                                          uint8_t *has_coeffs, const kvz_cuda_rdoq_ctx *d_ctx,
+                                          const kvz_cuda_rdoq_job *rdoq_jobs, int max_width, int rdoq_skip,
+                                          cudaStream_t stream);
 }
 namespace kvz {
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
@@ -453,6 +458,21 @@ int kvz_cuda_quantize_residuals_rdoq(const kvz_cuda_quant_cfg *cfg, const void *
     return fail_msg("kvz_cuda_quantize_residuals_rdoq: max_width must be 4, 8, 16 or 32");
   return launch_quantize_residual_rdoq(*cfg, d_ref, d_pred, d_rec, d_coeff, d_jobs, n_jobs, d_has_coeffs, d_ctx,
                                        d_rdoq_jobs, max_width, d_work, rdoq_skip, (cudaStream_t)stream);
+}
+
+int kvz_cuda_quantize_residuals_rdoq_noalloc(const kvz_cuda_quant_cfg *cfg, const void *d_ref, const void *d_pred,
+                                             void *d_rec, int16_t *d_coeff, size_t coeff_elems,
+                                             const kvz_cuda_residual_job *d_jobs, int n_jobs, uint8_t *d_has_coeffs,
+                                             const kvz_cuda_rdoq_ctx *d_ctx, const kvz_cuda_rdoq_job *d_rdoq_jobs,
+                                             int max_width, int rdoq_skip, void *stream)
+{
+  if (!check_qcfg(cfg, "kvz_cuda_quantize_residuals_rdoq_noalloc: bad cfg")) return 0;
+  if (!d_ref || !d_pred || !d_rec || !d_coeff || !d_jobs || !d_has_coeffs || !d_ctx || !d_rdoq_jobs || n_jobs < 0)
+    return fail_msg("kvz_cuda_quantize_residuals_rdoq_noalloc: bad argument");
+  if (max_width != 4 && max_width != 8 && max_width != 16 && max_width != 32)
+    return fail_msg("kvz_cuda_quantize_residuals_rdoq_noalloc: max_width must be 4, 8, 16 or 32");
+  return launch_quantize_residual_rdoq_noalloc(*cfg, d_ref, d_pred, d_rec, d_coeff, coeff_elems, d_jobs, n_jobs, d_has_coeffs,
+                                               d_ctx, d_rdoq_jobs, max_width, rdoq_skip, (cudaStream_t)stream);
 }
 
 int kvz_cuda_coeff_abs_sums(const int16_t *d_coeffs, int per_block, int count, uint32_t *d_out, void *stream)

@@ -8,6 +8,8 @@
 //   * the fused kvz_quantize_residual                  (quant-generic.c:180-273): residual -> T -> Q ->
 //     Q^-1 -> T^-1 -> reconstruction, the block never leaving shared memory.
 // N <= 16 is HBM-bound; every block is read once and written once.
+#include <mutex>
+
 #include "common.cuh"
 #include "transform.cuh"
 #include "../../include/kvz_cuda.h"
@@ -547,6 +549,53 @@ int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, 
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
+}
+
+
+// ---- the same without any allocation: the scratch is a file-scope device array --------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).
+// No counterpart in the reference.
+//
+// g_noalloc_work is a host-side stand-in in host code, NOT a device address: its address on the current device
+// is fetched once per device with cudaGetSymbolAddress and that pointer is what the kernels receive.  Every GPU
+// that loads the library holds the array (kNoAllocMaxCoeffs * 2 bytes = 2 MiB) until exit.  All calls share it
+// and it keeps the last call's contents; nothing in it has to start at zero (stage 1 writes every coefficient
+// the RDOQ stage reads, see residual_job), so nothing is cleared.  Calls that overlap on the GPU race on it.
+constexpr size_t kNoAllocMaxCoeffs = (size_t)KVZ_CUDA_NOALLOC_MAX_COEFFS;
+static __device__ __align__(256) int16_t g_noalloc_work[kNoAllocMaxCoeffs];
+
+constexpr int kNoAllocMaxDevices = 64;
+static int16_t *g_noalloc_ptr[kNoAllocMaxDevices];     // device address of g_noalloc_work, per device
+static std::mutex g_noalloc_lock;
+
+int launch_quantize_residual_rdoq_noalloc(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec,
+                                          int16_t *coeff, size_t coeff_elems, const kvz_cuda_residual_job *jobs, int n_jobs,
+                                          uint8_t *has_coeffs, const kvz_cuda_rdoq_ctx *d_ctx,
+                                          const kvz_cuda_rdoq_job *rdoq_jobs, int max_width, int rdoq_skip,
+                                          cudaStream_t stream)
+{
+  if (coeff_elems > kNoAllocMaxCoeffs) {
+    snprintf(g_last_error, sizeof(g_last_error),
+             "kvz_cuda_quantize_residuals_rdoq_noalloc: %zu coefficients exceed the built-in scratch of %zu "
+             "(KVZ_CUDA_NOALLOC_MAX_COEFFS); split the batch or use kvz_cuda_quantize_residuals_rdoq with your own d_work",
+             coeff_elems, kNoAllocMaxCoeffs);
+    return 0;
+  }
+  int dev = -1;
+  KVZ_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail_msg("kvz_cuda_quantize_residuals_rdoq_noalloc: device index out of range");
+  int16_t *work = nullptr;
+  {
+    std::lock_guard<std::mutex> guard(g_noalloc_lock);
+    if (!g_noalloc_ptr[dev]) {                  // set-up, once per device, with that device current
+      void *p = nullptr;
+      KVZ_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_work));
+      g_noalloc_ptr[dev] = static_cast<int16_t *>(p);
+    }
+    work = g_noalloc_ptr[dev];
+  }
+  return launch_quantize_residual_rdoq(c, ref, pred, rec, coeff, jobs, n_jobs, has_coeffs, d_ctx, rdoq_jobs, max_width, work,
+                                       rdoq_skip, stream);
 }
 
 }  // namespace kvz
