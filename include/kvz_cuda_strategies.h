@@ -26,17 +26,33 @@ typedef uint8_t kvz_cuda_px;      /* kvz_pixel of the 8-bit build */
 typedef int16_t kvz_cuda_coeff;   /* coeff_t (src/global.h:99) */
 
 /* ---- registration (replaces nothing; added next to kvz_strategy_register_*_avx2, e.g.
- * src/strategies/strategies-picture.c:66-88).  `register_fn` is the host's
- * kvz_strategyselector_register (src/strategyselector.c:216-256): passing it in keeps this library
- * free of link-time dependencies on the encoder.  Strategy name "cuda", priority 50. ---- */
+ * src/strategies/strategies-picture.c:66-88).  Same form as the reference's per-ISA registration functions:
+ * int kvz_strategy_register_<family>_cuda(void *opaque, uint8_t bitdepth).  Strategy name "cuda", priority 50.
+ * The host's kvz_strategyselector_register (src/strategyselector.c:216-256) is looked up in the running process
+ * with dlsym(RTLD_DEFAULT, ...), which keeps this library free of link-time dependencies on the encoder; the
+ * *_with forms take it as an argument instead (hosts that hide the symbol, tests).
+ * Returns 1 on success; at bitdepth != 8 registers nothing and returns 1 (as avx2/picture-avx2.c:1230); without a
+ * usable B200 returns 0, which fails kvz_strategyselector_init and encoder_open -- there is no CPU fallback.
+ * The device is KVZ_CUDA_DEVICE, else LOCAL_RANK, else 0, unless kvz_cuda_init() already chose one. ---- */
 typedef int (*kvz_cuda_register_fn)(void *opaque, const char *type, const char *strategy_name, int priority, void *fptr);
-KVZ_CUDA_API int kvz_strategy_register_picture_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
-KVZ_CUDA_API int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_picture_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth);
+KVZ_CUDA_API int kvz_strategy_register_picture_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_dct_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_quant_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_intra_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_ipol_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_nal_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+KVZ_CUDA_API int kvz_strategy_register_sao_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn);
+
+/* calls this face has served since the library was loaded, per strategy family: [0] picture, [1] dct, [2] quant,
+ * [3] intra, [4] ipol, [5] sao, [6] nal -- parity runs read them to prove which implementation was the one called */
+KVZ_CUDA_API void kvz_cuda_percall_counts(unsigned long long counts[7]);
 
 /* ---- picture: strategies-picture.h:102-136 ---- */
 /* reg_sad_func */
@@ -99,6 +115,19 @@ KVZ_CUDA_API int kvz_cuda_quantize_residual_host(const kvz_cuda_quant_cfg *cfg, 
                                                  int use_trskip, int in_stride, int out_stride,
                                                  const kvz_cuda_px *ref_in, const kvz_cuda_px *pred_in,
                                                  kvz_cuda_px *rec_out, kvz_cuda_coeff *coeff_out);
+
+/* the same with cfg.rdoq_enable (quant-generic.c:211-221: kvz_rdoq instead of kvz_quant unless width == 4 and
+ * cfg.rdoq_skip): ctx = the CABAC context states kvz_rdoq reads from state->cabac.ctx, lambda = state->lambda,
+ * tr_depth = cur_cu->tr_depth - cur_cu->depth + (part_size == SIZE_NxN) */
+KVZ_CUDA_API int kvz_cuda_quantize_residual_rdoq_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *ctx, double lambda,
+                                                      int tr_depth, int rdoq_skip, int width, int color, int scan_order,
+                                                      int use_trskip, int in_stride, int out_stride,
+                                                      const kvz_cuda_px *ref_in, const kvz_cuda_px *pred_in,
+                                                      kvz_cuda_px *rec_out, kvz_cuda_coeff *coeff_out);
+/* kvz_rdoq (rdo.c:548-885) for one block of HOST coefficients; type 0 luma / 2 chroma */
+KVZ_CUDA_API int kvz_cuda_rdoq_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *ctx, double lambda,
+                                    const kvz_cuda_coeff *coef, kvz_cuda_coeff *dest_coeff, int width, int type,
+                                    int scan_idx, int tr_depth);
 
 /* ---- intra: angular_pred_func, intra_pred_planar_func (strategies-intra.h:32-43) ---- */
 KVZ_CUDA_API void kvz_cuda_angular_pred(const int_fast8_t log2_width, const int_fast8_t intra_mode,

@@ -8,7 +8,7 @@
 namespace kvz {
 thread_local char g_last_error[512] = "";
 unsigned long long g_launch_count = 0;
-static int g_device = -1;
+int g_device = -1;          // the device kvz_cuda_init() selected; read by every per-call function
 }  // namespace kvz
 
 namespace kvz {

@@ -41,9 +41,11 @@ inline int fail_msg(const char *what)
 
 constexpr int kLcuWidth = 64;   // global.h:137: CTU is fixed at 64x64
 
+extern int g_device;        // capi.cu: device selected by kvz_cuda_init(), -1 before
+
 // launch counter: bench.py reports gpu_launches from this
 extern unsigned long long g_launch_count;
-inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
+inline void count_launch(int n = 1) { __atomic_fetch_add(&g_launch_count, (unsigned long long)n, __ATOMIC_RELAXED); }   // any host thread
 
 // pixel traits: 8-bit build of the reference uses uint8_t, 10-bit uint16_t
 // (kvazaar.h:72-77)

@@ -1,0 +1,439 @@
+// kvazaar_b200/csrc/enc_session.cu -- the encoder-session face (include/kvz_cuda_enc.h).
+//
+// A Kvazaar host keeps its pictures in host memory and searches one PU at a time, in CTU wavefront order, from
+// all of its threadqueue workers (src/encoderstate.c:777-828, src/search_inter.c:1451-1524).  The session turns
+// that call pattern into the batch face's: per frame the source and the new reference are uploaded once, the
+// references are bordered and ONE launch produces the dense SAD maps of every PU of the frame against every
+// reference (ime_sad.cu); each per-PU call then only prices / scans those maps and refines the winner
+// (me_search.cu) on the calling thread's own stream, so the calls of the wavefront's CTU rows overlap on the GPU.
+#include <time.h>
+
+#include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <vector>
+
+#include "../../include/kvz_cuda_enc.h"
+#include "common.cuh"
+#include "ime_sad.cuh"
+#include "me_search.cuh"
+
+namespace kvz {
+namespace {
+
+constexpr int kPad = 240;             // border of the resident reference planes: 104 + kFar (ime_sad box kernels)
+constexpr int kFar = 136;             // largest |displacement| + 1 a box may reach
+constexpr int kMaxSlots = 24;         // resident reference planes (the DPB holds at most 16 + the one being uploaded)
+
+struct PlaneSlot {
+  uint64_t key = 0;
+  int poc = 0;
+  bool live = false;
+  uint8_t *d = nullptr;               // (w + 2 kPad) x (h + 2 kPad), pitch bytes per row
+};
+
+struct CurPlane {
+  uint64_t key = 0, frame_num = ~0ull;
+  uint8_t *d = nullptr;
+};
+
+struct FrameCtx {
+  uint64_t id = ~0ull;
+  MeFrame f;
+  uint8_t *maps = nullptr;
+  size_t map_bytes = 0;               // allocated
+  cudaEvent_t ready = nullptr;
+  std::atomic<int> inflight{0};
+  int box[KVZ_CUDA_MAX_REFS][4];      // x0, y0, n_dx, n_dy per reference
+};
+
+// per calling thread: a stream and the staging of one PU, its jobs and results
+struct Worker {
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  uint8_t *h = nullptr, *d = nullptr;
+  uint64_t seen_ctx = ~0ull;
+  const void *seen_enc = nullptr;
+};
+thread_local Worker t_worker;
+
+constexpr size_t kOffJobs = 128, kOffResults = kOffJobs + KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_job);
+constexpr size_t kStageBytes = kOffResults + KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result);
+static_assert(sizeof(kvz_cuda_me_pu) <= kOffJobs, "staging layout");
+
+}  // namespace
+}  // namespace kvz
+
+using namespace kvz;
+
+struct kvz_cuda_enc {
+  kvz_cuda_enc_cfg cfg;
+  int pitch = 0;                      // bytes per row of the bordered planes
+  size_t plane_bytes = 0;
+  std::mutex lock;
+  cudaStream_t stream = nullptr;      // frame-level work: uploads, borders, dense maps
+  uint8_t *d_tmp = nullptr;           // un-bordered upload of a reference
+  PlaneSlot slots[kMaxSlots];
+  CurPlane cur[4];
+  int cur_next = 0;
+  std::vector<FrameCtx *> ctxs;
+  std::atomic<unsigned long long> stats[8];
+  // KVZ_CUDA_STATS: wall time of kvz_cuda_enc_search_pu by PU size (8, 16, 32, 64) and by whether every window of
+  // every job lay inside its reference's box
+  bool timing = false;
+  std::atomic<unsigned long long> t_ns[4][2], t_calls[4][2];
+};
+
+namespace {
+
+int fail_enc(const char *what) { return fail_msg(what); }
+
+// One box per reference: the zero window plus the windows round the vectors the hints predict.  Hints are trimmed
+// to their 2nd..98th percentile per axis (a few wild vectors must not blow the box up) and the spread of the window
+// centres is capped so that the box stays inside +-kFar.
+void choose_box(int R, const int16_t *hints, int n_hints, int max_spread, int box[4])
+{
+  int lox = 0, hix = 0, loy = 0, hiy = 0;
+  if (hints && n_hints > 0) {
+    std::vector<int> xs(n_hints), ys(n_hints);
+    for (int i = 0; i < n_hints; i++) { xs[i] = hints[2 * i] >> 2; ys[i] = hints[2 * i + 1] >> 2; }
+    std::sort(xs.begin(), xs.end());
+    std::sort(ys.begin(), ys.end());
+    const int a = n_hints / 50, b = n_hints - 1 - n_hints / 50;
+    lox = std::min(0, xs[a]); hix = std::max(0, xs[b]);
+    loy = std::min(0, ys[a]); hiy = std::max(0, ys[b]);
+  }
+  // vectors round to the next whole sample in some window centres ((mv + 2) >> 2, search_inter.c:268): one sample of slack
+  hix += 1; hiy += 1;
+  const int cap = std::max(0, std::min(max_spread, kFar - 8 - R));
+  lox = std::max(lox, -cap); loy = std::max(loy, -cap);
+  hix = std::min(hix, cap); hiy = std::min(hiy, cap);
+  box[0] = lox - R; box[1] = loy - R;
+  box[2] = ((hix + R) - (lox - R) + 1 + 7) & ~7;
+  box[3] = (hiy + R) - (loy - R) + 1;
+}
+
+size_t level_entries(int tile_w, int tile_h, int level)
+{
+  const size_t ctus = (size_t)((tile_w + 63) / 64) * ((tile_h + 63) / 64);
+  const size_t n = 8 >> level;
+  return ctus * n * n;
+}
+
+size_t box_bytes(int tile_w, int tile_h, const int box[4])
+{
+  size_t b = 0;
+  for (int l = 0; l < 4; l++) {
+    size_t lb = level_entries(tile_w, tile_h, l) * (size_t)box[2] * box[3] * (l < 2 ? 2 : 4);
+    b += (lb + 255) & ~(size_t)255;
+  }
+  return b;
+}
+
+// the window centres search_mv_full visits for one job (search_inter.c:891-955; the list scan_job builds on the device):
+// true when all of them lie inside the reference's box, i.e. the job is served from the dense maps alone
+bool job_in_box(const FrameCtx &c, int R, const kvz_cuda_me_pu &pu, const kvz_cuda_me_job &job)
+{
+  const int *b = c.box[job.ref_idx];
+  int lox = 0, hix = 0, loy = 0, hiy = 0;
+  auto add = [&](int x, int y) { lox = std::min(lox, x); hix = std::max(hix, x); loy = std::min(loy, y); hiy = std::max(hiy, y); };
+  const int ex = job.extra_mv[0] >> 2, ey = job.extra_mv[1] >> 2;
+  bool in_merge = false;
+  for (int i = 0; i < pu.num_merge_cand; i++) {
+    const kvz_cuda_merge_cand &m = pu.merge_cand[i];
+    if (m.dir == 3) continue;
+    in_merge |= ((m.mv[m.dir - 1][0] + 2) >> 2) == ex && ((m.mv[m.dir - 1][1] + 2) >> 2) == ey;
+    add(m.mv[m.dir - 1][0] >> 2, m.mv[m.dir - 1][1] >> 2);
+  }
+  if (!in_merge) add(ex, ey);
+  return lox - R >= b[0] && hix + R < b[0] + b[2] && loy - R >= b[1] && hiy + R < b[1] + b[3];
+}
+
+bool worker_ready(kvz_cuda_enc *e)
+{
+  Worker &w = t_worker;
+  if (w.device == e->cfg.device && w.stream) return true;
+  if (cudaSetDevice(e->cfg.device) != cudaSuccess) return false;      // every calling thread binds the session's device
+  if (cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess) return false;
+  if (cudaHostAlloc(&w.h, kStageBytes, cudaHostAllocDefault) != cudaSuccess) return false;
+  if (cudaMalloc(&w.d, kStageBytes) != cudaSuccess) return false;
+  w.device = e->cfg.device;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+kvz_cuda_enc *kvz_cuda_enc_open(const kvz_cuda_enc_cfg *cfg)
+{
+  if (!cfg) { fail_enc("kvz_cuda_enc_open: null cfg"); return nullptr; }
+  if (cfg->bitdepth != 8) { fail_enc("kvz_cuda_enc_open: only bitdepth 8 is implemented on this face"); return nullptr; }
+  if (cfg->width <= 0 || cfg->height <= 0 || (cfg->width & 7) || (cfg->height & 7)) {
+    fail_enc("kvz_cuda_enc_open: width and height must be positive multiples of 8 (the CLI pads its input, encmain.c:80)");
+    return nullptr;
+  }
+  if (cfg->ime_search < KVZ_CUDA_IME_FULL || cfg->ime_search > KVZ_CUDA_IME_TZ) { fail_enc("kvz_cuda_enc_open: bad ime_search"); return nullptr; }
+  if (cfg->range != 8 && cfg->range != 16 && cfg->range != 32 && cfg->range != 64) { fail_enc("kvz_cuda_enc_open: range must be 8, 16, 32 or 64"); return nullptr; }
+  if (cfg->fme_level < 0 || cfg->fme_level > 4) { fail_enc("kvz_cuda_enc_open: fme_level must be 0..4"); return nullptr; }
+  if (!kvz_cuda_init(cfg->device)) return nullptr;
+  kvz_cuda_enc *e = new kvz_cuda_enc();
+  e->cfg = *cfg;
+  if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 32768;
+  for (auto &s : e->stats) s = 0;
+  for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) { e->t_ns[a][b] = 0; e->t_calls[a][b] = 0; }
+  e->timing = getenv("KVZ_CUDA_STATS") != nullptr;
+  e->pitch = (cfg->width + 2 * kPad + 63) & ~63;
+  e->plane_bytes = (size_t)e->pitch * (cfg->height + 2 * kPad);
+  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMalloc(&e->d_tmp, (size_t)cfg->width * cfg->height) != cudaSuccess) {
+    fail("kvz_cuda_enc_open", cudaGetLastError(), __FILE__, __LINE__);
+    delete e;
+    return nullptr;
+  }
+  return e;
+}
+
+void kvz_cuda_enc_close(kvz_cuda_enc *e)
+{
+  if (!e) return;
+  cudaSetDevice(e->cfg.device);
+  cudaDeviceSynchronize();
+  for (auto &s : e->slots) if (s.d) cudaFree(s.d);
+  for (auto &c : e->cur) if (c.d) cudaFree(c.d);
+  for (FrameCtx *c : e->ctxs) {
+    if (c->maps) cudaFree(c->maps);
+    if (c->ready) cudaEventDestroy(c->ready);
+    delete c;
+  }
+  if (e->d_tmp) cudaFree(e->d_tmp);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
+{
+  if (!e || !fr || !fr->src_luma) { fail_enc("kvz_cuda_enc_frame_begin: null argument"); return -1; }
+  if (fr->n_refs < 1 || fr->n_refs > KVZ_CUDA_MAX_REFS) { fail_enc("kvz_cuda_enc_frame_begin: bad n_refs"); return -1; }
+  if ((fr->tile_x & 63) || (fr->tile_y & 63) || (fr->tile_w & 7) || (fr->tile_h & 7) || fr->tile_w <= 0 || fr->tile_h <= 0 ||
+      fr->tile_x + fr->tile_w > e->cfg.width || fr->tile_y + fr->tile_h > e->cfg.height) {
+    fail_enc("kvz_cuda_enc_frame_begin: bad tile rectangle");
+    return -1;
+  }
+  std::lock_guard<std::mutex> guard(e->lock);
+  for (size_t i = 0; i < e->ctxs.size(); i++)
+    if (e->ctxs[i]->id == fr->frame_id) return (int)i;              // another thread began this (frame, tile)
+  if (cudaSetDevice(e->cfg.device) != cudaSuccess) { fail("cudaSetDevice", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+  const kvz_cuda_enc_cfg &cfg = e->cfg;
+  const uint64_t frame_num = fr->frame_id >> 16;
+
+  // ---- source plane: one upload per frame, shared by its tiles ----
+  CurPlane *cur = nullptr;
+  for (auto &c : e->cur) if (c.d && c.key == fr->src_key && c.frame_num == frame_num) cur = &c;
+  if (!cur) {
+    cur = &e->cur[e->cur_next];
+    e->cur_next = (e->cur_next + 1) & 3;
+    if (!cur->d && cudaMalloc(&cur->d, (size_t)cfg.width * cfg.height) != cudaSuccess) {
+      fail("cudaMalloc(source plane)", cudaGetLastError(), __FILE__, __LINE__); return -1;
+    }
+    cur->key = fr->src_key; cur->frame_num = frame_num;
+    if (cudaMemcpy2DAsync(cur->d, cfg.width, fr->src_luma, fr->src_stride, cfg.width, cfg.height, cudaMemcpyHostToDevice,
+                          e->stream) != cudaSuccess) { fail("upload of the source plane", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+  }
+
+  // ---- reference planes: drop what the DPB dropped, upload and border what is new ----
+  for (auto &s : e->slots) {
+    if (!s.live) continue;
+    bool listed = false;
+    for (int r = 0; r < fr->n_refs; r++) listed |= fr->refs[r].key == s.key && fr->refs[r].poc == s.poc;
+    if (!listed) s.live = false;
+  }
+  PlaneSlot *ref_slot[KVZ_CUDA_MAX_REFS];
+  for (int r = 0; r < fr->n_refs; r++) {
+    const kvz_cuda_enc_ref &rr = fr->refs[r];
+    if (!rr.luma) { fail_enc("kvz_cuda_enc_frame_begin: null reference plane"); return -1; }
+    PlaneSlot *s = nullptr;
+    for (auto &q : e->slots) if (q.live && q.key == rr.key && q.poc == rr.poc) s = &q;
+    if (!s) {
+      for (auto &q : e->slots) if (!q.live) { s = &q; break; }
+      if (!s) { fail_enc("kvz_cuda_enc_frame_begin: out of reference plane slots"); return -1; }
+      if (!s->d && cudaMalloc(&s->d, e->plane_bytes) != cudaSuccess) {
+        fail("cudaMalloc(reference plane)", cudaGetLastError(), __FILE__, __LINE__); return -1;
+      }
+      if (cudaMemcpy2DAsync(e->d_tmp, cfg.width, rr.luma, rr.stride, cfg.width, cfg.height, cudaMemcpyHostToDevice,
+                            e->stream) != cudaSuccess) { fail("upload of a reference plane", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+      if (!launch_pad_plane(e->d_tmp, cfg.width, cfg.height, cfg.width, s->d, kPad, e->pitch, 8, e->stream)) return -1;
+      s->key = rr.key; s->poc = rr.poc; s->live = true;
+      e->stats[2]++;
+    }
+    ref_slot[r] = s;
+  }
+
+  // ---- a context: one of an older frame whose searches are over, or a new one ----
+  FrameCtx *ctx = nullptr;
+  int handle = -1;
+  for (size_t i = 0; i < e->ctxs.size(); i++) {
+    FrameCtx *c = e->ctxs[i];
+    if ((c->id >> 16) != frame_num && c->inflight.load() == 0) { ctx = c; handle = (int)i; break; }
+  }
+  if (!ctx) {
+    ctx = new FrameCtx();
+    if (cudaEventCreateWithFlags(&ctx->ready, cudaEventDisableTiming) != cudaSuccess) {
+      fail("cudaEventCreate", cudaGetLastError(), __FILE__, __LINE__); delete ctx; return -1;
+    }
+    e->ctxs.push_back(ctx);
+    handle = (int)e->ctxs.size() - 1;
+  }
+  ctx->id = ~0ull;                                     // not findable until it is complete
+
+  // ---- boxes, within the map budget ----
+  const bool full = cfg.ime_search == KVZ_CUDA_IME_FULL;
+  size_t need = 0;
+  if (full) {
+    int spread = kFar;
+    for (;;) {
+      need = 0;
+      for (int r = 0; r < fr->n_refs; r++) {
+        choose_box(cfg.range, fr->refs[r].mv_hints, fr->refs[r].n_mv_hints, spread, ctx->box[r]);
+        need += box_bytes(fr->tile_w, fr->tile_h, ctx->box[r]);
+      }
+      if (need <= (size_t)cfg.max_map_mbytes << 20 || spread == 0) break;
+      spread = spread * 3 / 4;
+    }
+    if (need > ctx->map_bytes) {
+      if (ctx->maps) { cudaStreamSynchronize(e->stream); cudaFree(ctx->maps); ctx->maps = nullptr; ctx->map_bytes = 0; }
+      if (cudaMalloc(&ctx->maps, need) != cudaSuccess) { fail("cudaMalloc(SAD maps)", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+      ctx->map_bytes = need;
+    }
+  }
+
+  // ---- frame description of the decision kernels ----
+  MeFrame &f = ctx->f;
+  memset(&f, 0, sizeof(f));
+  f.cur = cur->d; f.cur_pitch = cfg.width;
+  f.width = cfg.width; f.height = cfg.height;
+  f.tile_x = fr->tile_x; f.tile_y = fr->tile_y; f.tile_w = fr->tile_w; f.tile_h = fr->tile_h;
+  f.ctus_x = (fr->tile_w + 63) / 64;
+  f.range = cfg.range; f.map_pitch = ime_map_pitch(cfg.range);
+  f.ime_search = cfg.ime_search; f.me_early_termination = cfg.me_early_termination; f.me_max_steps = cfg.me_max_steps;
+  f.fme_level = cfg.fme_level; f.owf = cfg.owf; f.wpp = cfg.wpp; f.sao_type = cfg.sao_type;
+  f.deblock_enable = cfg.deblock_enable; f.mv_constraint = cfg.mv_constraint;
+  f.max_ref_lcu_right = cfg.max_ref_lcu_right; f.max_ref_lcu_down = cfg.max_ref_lcu_down;
+  f.n_refs = fr->n_refs;
+  memcpy(f.ref_LX, fr->ref_LX, sizeof(f.ref_LX));
+  ImeSadParams ps[KVZ_CUDA_MAX_REFS];
+  uint8_t *at = ctx->maps;
+  unsigned long long disp = 0;
+  for (int r = 0; r < fr->n_refs; r++) {
+    f.refs[r].plane = ref_slot[r]->d; f.refs[r].pitch = e->pitch; f.refs[r].pad = kPad;
+    f.refs[r].n_sets = 0;
+    if (!full) continue;
+    const int *b = ctx->box[r];
+    void *lv[4];
+    for (int l = 0; l < 4; l++) {
+      lv[l] = at;
+      const size_t lb = level_entries(fr->tile_w, fr->tile_h, l) * (size_t)b[2] * b[3] * (l < 2 ? 2 : 4);
+      at += (lb + 255) & ~(size_t)255;
+    }
+    MeMapSet &ms = f.refs[r].sets[0];
+    f.refs[r].n_sets = 1;
+    ms.cx = b[0]; ms.cy = b[1]; ms.n_dx = b[2]; ms.n_dy = b[3];
+    ms.sad8 = (const uint16_t *)lv[0]; ms.sad16 = (const uint16_t *)lv[1];
+    ms.sad32 = (const uint32_t *)lv[2]; ms.sad64 = (const uint32_t *)lv[3];
+    ImeSadParams &p = ps[r];
+    memset(&p, 0, sizeof(p));
+    p.cur = cur->d; p.ref = ref_slot[r]->d;
+    p.width = cfg.width; p.height = cfg.height;
+    p.cur_pitch = cfg.width; p.ref_pitch = e->pitch; p.pad = kPad;
+    p.tile_x = fr->tile_x; p.tile_y = fr->tile_y; p.tile_w = fr->tile_w; p.tile_h = fr->tile_h;
+    p.ctus_x = (fr->tile_w + 63) / 64; p.ctus_y = (fr->tile_h + 63) / 64;
+    p.map_pitch = b[2];
+    p.sad8 = (uint16_t *)lv[0]; p.sad16 = (uint16_t *)lv[1]; p.sad32 = (uint32_t *)lv[2]; p.sad64 = (uint32_t *)lv[3];
+    disp += (unsigned long long)b[2] * b[3];
+  }
+  if (full) {
+    for (int r0 = 0; r0 < fr->n_refs; r0 += kImeMaxMulti) {
+      const int n = std::min(kImeMaxMulti, fr->n_refs - r0);
+      if (!launch_ime_sad_box_multi(ps + r0, ctx->box + r0, n, e->stream)) return -1;
+    }
+  }
+  if (cudaEventRecord(ctx->ready, e->stream) != cudaSuccess) { fail("cudaEventRecord", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+  e->stats[0]++;
+  e->stats[3] = need;
+  e->stats[4] = disp;
+  ctx->id = fr->frame_id;
+  return handle;
+}
+
+int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const kvz_cuda_me_pu *pu,
+                           const kvz_cuda_me_job *jobs, kvz_cuda_me_result *results)
+{
+  if (!e || !pu || !jobs || !results) return fail_enc("kvz_cuda_enc_search_pu: null argument");
+  FrameCtx *ctx = nullptr;
+  {
+    std::lock_guard<std::mutex> guard(e->lock);
+    if (handle >= 0 && handle < (int)e->ctxs.size()) ctx = e->ctxs[handle];
+    if (ctx) ctx->inflight++;
+  }
+  if (!ctx || ctx->id == ~0ull) { if (ctx) ctx->inflight--; return fail_enc("kvz_cuda_enc_search_pu: bad frame handle"); }
+  struct Release { FrameCtx *c; ~Release() { c->inflight--; } } release{ctx};
+  const int nj = pu->num_jobs;
+  if (nj < 1 || nj > KVZ_CUDA_MAX_REFS) return fail_enc("kvz_cuda_enc_search_pu: bad num_jobs");
+  if ((pu->w & 7) || (pu->h & 7) || pu->w == 0 || pu->h == 0 || pu->w > 64 || pu->h > 64)
+    return fail_enc("kvz_cuda_enc_search_pu: PU sides must be multiples of 8, at most 64 (SMP/AMP shapes 4, 12 are not searched here)");
+  for (int i = 0; i < nj; i++)
+    if (jobs[i].ref_idx >= ctx->f.n_refs) return fail_enc("kvz_cuda_enc_search_pu: ref_idx outside the frame's reference list");
+  if (!worker_ready(e)) return fail("per-thread stream / staging", cudaGetLastError(), __FILE__, __LINE__);
+  Worker &w = t_worker;
+  struct timespec ts0;
+  bool all_in_box = true;
+  if (e->timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
+  if (ctx->f.ime_search == KVZ_CUDA_IME_FULL)
+    for (int i = 0; i < nj; i++)
+      if (!job_in_box(*ctx, e->cfg.range, *pu, jobs[i])) { all_in_box = false; e->stats[6]++; }
+
+  kvz_cuda_me_pu *hp = reinterpret_cast<kvz_cuda_me_pu *>(w.h);
+  *hp = *pu;
+  hp->first_job = 0;
+  memcpy(w.h + kOffJobs, jobs, (size_t)nj * sizeof(kvz_cuda_me_job));
+  const size_t in_bytes = kOffJobs + (size_t)nj * sizeof(kvz_cuda_me_job);
+  KVZ_CUDA_TRY(cudaMemcpyAsync(w.d, w.h, in_bytes, cudaMemcpyHostToDevice, w.stream));
+  const uint64_t tag = ((uint64_t)handle << 48) ^ ctx->id;
+  if (w.seen_ctx != tag || w.seen_enc != e) {              // first call of this thread for this frame: wait for its maps
+    KVZ_CUDA_TRY(cudaStreamWaitEvent(w.stream, ctx->ready, 0));
+    w.seen_ctx = tag; w.seen_enc = e;
+  }
+  MeFrame f = ctx->f;
+  f.lambda_sqrt_i = lambda_sqrt_i;
+  if (!launch_me_search(f, reinterpret_cast<const kvz_cuda_me_pu *>(w.d),
+                        reinterpret_cast<const kvz_cuda_me_job *>(w.d + kOffJobs),
+                        reinterpret_cast<kvz_cuda_me_result *>(w.d + kOffResults), 1, w.stream)) return 0;
+  KVZ_CUDA_TRY(cudaMemcpyAsync(w.h + kOffResults, w.d + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result),
+                               cudaMemcpyDeviceToHost, w.stream));
+  KVZ_CUDA_TRY(cudaStreamSynchronize(w.stream));
+  memcpy(results, w.h + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result));
+  e->stats[1]++;
+  e->stats[5] += (unsigned long long)nj;
+  if (e->timing) {
+    struct timespec ts1;
+    clock_gettime(CLOCK_MONOTONIC, &ts1);
+    const int sz = std::max(pu->w, pu->h) > 32 ? 3 : std::max(pu->w, pu->h) > 16 ? 2 : std::max(pu->w, pu->h) > 8 ? 1 : 0;
+    e->t_ns[sz][all_in_box ? 0 : 1] += (unsigned long long)((ts1.tv_sec - ts0.tv_sec) * 1000000000ll + (ts1.tv_nsec - ts0.tv_nsec));
+    e->t_calls[sz][all_in_box ? 0 : 1]++;
+  }
+  return 1;
+}
+
+void kvz_cuda_enc_stats(const kvz_cuda_enc *e, unsigned long long stats[8])
+{
+  for (int i = 0; i < 8; i++) stats[i] = e ? e->stats[i].load() : 0ull;
+  if (e && e->timing)
+    for (int sz = 0; sz < 4; sz++)
+      for (int k = 0; k < 2; k++)
+        if (e->t_calls[sz][k].load())
+          fprintf(stderr, "kvz_cuda_enc: PU %2d  %-22s %8llu calls  %8.1f us/call\n", 8 << sz,
+                  k ? "some window on demand" : "all windows in the box", e->t_calls[sz][k].load(),
+                  e->t_ns[sz][k].load() / 1000.0 / e->t_calls[sz][k].load());
+}
+
+}  // extern "C"

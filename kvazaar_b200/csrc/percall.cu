@@ -8,6 +8,9 @@
 // batch of one, and waits.  This face exists for parity tests and the kernel sweep
 // (BASELINE config 5); a launch per 8x8 block is not how throughput is obtained.
 // Thread-safe through one lock (strategies are called from every threadqueue worker).
+#include <dlfcn.h>
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common.cuh"
@@ -29,6 +32,13 @@ int launch_intra_costs(const void *refs, const void *orig, const kvz_cuda_intra_
                        uint32_t *costs, void *preds, cudaStream_t stream, int bitdepth);
 int launch_interp(const void *plane, int pitch, int W, int H, int bitdepth, const kvz_cuda_interp_job *jobs, int n_jobs,
                   void *dst8, int16_t *dst16, cudaStream_t stream);
+int launch_rdoq_batch(const kvz_cuda_quant_cfg &cfg, const kvz_cuda_rdoq_ctx *d_ctx, const int16_t *d_coef,
+                      int16_t *d_q_coef, const kvz_cuda_rdoq_job *d_jobs, int n_jobs, int max_width, int skip4,
+                      cudaStream_t stream);
+int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, const void *pred, void *rec, int16_t *coeff,
+                                  const kvz_cuda_residual_job *jobs, int n_jobs, uint8_t *has_coeffs,
+                                  const kvz_cuda_rdoq_ctx *d_ctx, const kvz_cuda_rdoq_job *rdoq_jobs, int max_width,
+                                  int16_t *work, int rdoq_skip, cudaStream_t stream);
 
 namespace {
 
@@ -52,11 +62,32 @@ struct PerCall {
 
 PerCall g_pc;
 
+// the GPU of this process when the host never called kvz_cuda_init(): KVZ_CUDA_DEVICE, else LOCAL_RANK (one process per GPU), else 0
+int env_device()
+{
+  const char *v = getenv("KVZ_CUDA_DEVICE");
+  if (!v) v = getenv("LOCAL_RANK");
+  return v ? atoi(v) : 0;
+}
+
 [[noreturn]] void die(const char *what)
 {
   // a cost function cannot report failure (SURVEY.md 8b "Errors"): fail loudly, never fall back
   fprintf(stderr, "libkvz_cuda: %s failed: %s\n", what, g_last_error);
   abort();
+}
+
+// calls served per strategy family: picture, dct, quant, intra, ipol, sao, nal (kvz_cuda_percall_counts)
+unsigned long long g_family_calls[7];
+int family_of(const char *who)
+{
+  if (strstr(who, "sao")) return 5;
+  if (strstr(who, "checksum")) return 6;
+  if (strstr(who, "quant") || strstr(who, "coeff_abs_sum") || strstr(who, "rdoq")) return 2;
+  if (strstr(who, "dct") || strstr(who, "dst") || strstr(who, "transform")) return 1;
+  if (strstr(who, "angular") || strstr(who, "planar") || strstr(who, "intra")) return 3;
+  if (strstr(who, "sample") || strstr(who, "filter") || strstr(who, "ipol") || strstr(who, "interp")) return 4;
+  return 0;
 }
 
 // layout of the staging buffers for one call: [0, in_bytes) inputs, then outputs
@@ -65,7 +96,12 @@ struct Stage {
   size_t in_bytes = 0, out_bytes = 0;
   explicit Stage(const char *who) : guard(g_pc.lock)
   {
+    // strategies are called from every threadqueue worker; a fresh thread's current device is 0, not the one
+    // kvz_cuda_init() selected, so each call binds it (cheap when it already is)
+    if (g_device < 0 && !kvz_cuda_init(env_device())) die(who);
+    if (cudaSetDevice(g_device) != cudaSuccess) { fail("cudaSetDevice", cudaGetLastError(), __FILE__, __LINE__); die(who); }
     if (!g_pc.init()) { fail_msg("per-call staging buffers"); die(who); }
+    g_family_calls[family_of(who)]++;                       // under the lock
   }
   template <typename T> T *in(size_t count)      // reserve input space, 16-byte aligned
   {
@@ -305,6 +341,72 @@ int kvz_cuda_quantize_residual_host(const kvz_cuda_quant_cfg *cfg, int width, in
   return has[0];
 }
 
+// kvz_quantize_residual with cfg.rdoq_enable (quant-generic.c:211-221): the same call with kvz_rdoq between the
+// transform and the reconstruction.  ctx = the CABAC context states of the calling thread's encoder state, lambda =
+// state->lambda, tr_depth as computed at quant-generic.c:216-217.
+int kvz_cuda_quantize_residual_rdoq_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *ctx, double lambda,
+                                         int tr_depth, int rdoq_skip, int width, int color, int scan_order, int use_trskip,
+                                         int in_stride, int out_stride, const kvz_cuda_px *ref_in,
+                                         const kvz_cuda_px *pred_in, kvz_cuda_px *rec_out, kvz_cuda_coeff *coeff_out)
+{
+  const char *who = "kvz_cuda_quantize_residual_rdoq_host";
+  if (!cfg || !ctx) return fail_msg("kvz_cuda_quantize_residual_rdoq_host: bad argument");
+  Stage st(who);
+  const size_t nn = (size_t)width * width;
+  uint8_t *r = st.in<uint8_t>(nn), *p = st.in<uint8_t>(nn);
+  pack_rows(r, ref_in, width, width, (size_t)in_stride);
+  pack_rows(p, pred_in, width, width, (size_t)in_stride);
+  kvz_cuda_residual_job *jb = st.in<kvz_cuda_residual_job>(1);
+  memset(jb, 0, sizeof(*jb));
+  jb->in_stride = width; jb->out_stride = width;
+  jb->width = (uint8_t)width; jb->color = (uint8_t)color; jb->scan_idx = (uint8_t)scan_order;
+  jb->use_trskip = (uint8_t)use_trskip; jb->qp = (int8_t)cfg->qp; jb->cu_is_intra = (uint8_t)cfg->cu_is_intra;
+  kvz_cuda_rdoq_job *rj = st.in<kvz_cuda_rdoq_job>(1);
+  memset(rj, 0, sizeof(*rj));
+  rj->lambda = lambda; rj->width = (uint8_t)width; rj->type = color == 0 ? 0 : 2; rj->scan_idx = (uint8_t)scan_order;
+  rj->tr_depth = (uint8_t)tr_depth; rj->qp = (int8_t)cfg->qp; rj->cu_is_intra = (uint8_t)cfg->cu_is_intra;
+  kvz_cuda_rdoq_ctx *cx = st.in<kvz_cuda_rdoq_ctx>(1);
+  *cx = *ctx;
+  int16_t *work = st.in<int16_t>(nn);                  // device-only scratch: its staging copy is never read
+  uint8_t *rec = st.out<uint8_t>(nn);
+  int16_t *co = st.out<int16_t>(nn);
+  uint8_t *has = st.out<uint8_t>(1);
+  st.upload(who);
+  if (!launch_quantize_residual_rdoq(*cfg, st.dev(r), st.dev(p), st.dev(rec), st.dev(co), st.dev(jb), 1, st.dev(has), st.dev(cx),
+                                     st.dev(rj), width, st.dev(work), rdoq_skip, g_pc.stream)) die(who);
+  st.download(who);
+  memcpy(coeff_out, co, sizeof(int16_t) * nn);
+  // quant-generic.c:262-271: with no coefficients and rec_out == pred_in nothing is written
+  if (has[0] || rec_out != pred_in)
+    for (int y = 0; y < width; y++) memcpy(rec_out + (size_t)y * out_stride, rec + (size_t)y * width, (size_t)width);
+  return has[0];
+}
+
+// kvz_rdoq (rdo.c:548-885) for one block: the call kvz_quant's callers make when cfg.rdoq_enable (transform.c, intra RDO)
+int kvz_cuda_rdoq_host(const kvz_cuda_quant_cfg *cfg, const kvz_cuda_rdoq_ctx *ctx, double lambda, const kvz_cuda_coeff *coef,
+                       kvz_cuda_coeff *dest_coeff, int width, int type, int scan_idx, int tr_depth)
+{
+  const char *who = "kvz_cuda_rdoq_host";
+  if (!cfg || !ctx) return fail_msg("kvz_cuda_rdoq_host: bad argument");
+  Stage st(who);
+  const size_t nn = (size_t)width * width;
+  int16_t *in = st.in<int16_t>(nn);
+  memcpy(in, coef, sizeof(int16_t) * nn);
+  kvz_cuda_rdoq_job *rj = st.in<kvz_cuda_rdoq_job>(1);
+  memset(rj, 0, sizeof(*rj));
+  rj->lambda = lambda; rj->width = (uint8_t)width; rj->type = (uint8_t)type; rj->scan_idx = (uint8_t)scan_idx;
+  rj->tr_depth = (uint8_t)tr_depth; rj->qp = (int8_t)cfg->qp; rj->cu_is_intra = (uint8_t)cfg->cu_is_intra;
+  kvz_cuda_rdoq_ctx *cx = st.in<kvz_cuda_rdoq_ctx>(1);
+  *cx = *ctx;
+  int16_t *out = st.out<int16_t>(nn);
+  st.upload(who);
+  // rdoq_job.coef_offset addresses both arrays: the output array starts where the staged input does
+  if (!launch_rdoq_batch(*cfg, st.dev(cx), st.dev(in), st.dev(out), st.dev(rj), 1, width, 0, g_pc.stream)) die(who);
+  st.download(who);
+  memcpy(dest_coeff, out, sizeof(int16_t) * nn);
+  return 1;
+}
+
 // ---------------- intra ----------------
 // angular_pred_func / intra_pred_planar_func receive the references kvz_intra_predict has already
 // chosen (filtered or not), so the job runs as chroma (no smoothing, no boundary filters) and
@@ -447,10 +549,11 @@ static int cuda_usable()
     cudaGetLastError();
     return fail_msg("kvz_strategy_register_*_cuda: no CUDA device (there is no CPU fallback)");
   }
+  if (g_device < 0 && !kvz_cuda_init(env_device())) return 0;
   return 1;
 }
 
-int kvz_strategy_register_picture_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_picture_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -473,7 +576,7 @@ int kvz_strategy_register_picture_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_
   return ok;
 }
 
-int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_dct_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -488,7 +591,7 @@ int kvz_strategy_register_dct_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_regi
   return ok;
 }
 
-int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_quant_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -500,7 +603,7 @@ int kvz_strategy_register_quant_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_re
   return ok;
 }
 
-int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_intra_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -511,7 +614,7 @@ int kvz_strategy_register_intra_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_re
   return ok;
 }
 
-int kvz_strategy_register_ipol_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_ipol_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -553,7 +656,7 @@ void kvz_cuda_array_checksum(const kvz_cuda_px *data, const int height, const in
   checksum_out[2] = (unsigned char)(sum >> 8); checksum_out[3] = (unsigned char)sum;
 }
 
-int kvz_strategy_register_nal_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_nal_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -653,7 +756,7 @@ void kvz_cuda_sao_reconstruct_color_host(int bitdepth, const kvz_cuda_px *rec_da
   for (int y = 0; y < block_height; y++) memcpy(new_rec_data + (size_t)y * new_stride, out + (size_t)(y + b) * w + b, (size_t)block_width);
 }
 
-int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
+int kvz_strategy_register_sao_cuda_with(void *opaque, uint8_t bitdepth, kvz_cuda_register_fn register_fn)
 {
   if (!register_fn) return 0;
   if (bitdepth != 8) return 1;
@@ -665,5 +768,32 @@ int kvz_strategy_register_sao_cuda(void *opaque, uint8_t bitdepth, kvz_cuda_regi
   KVZ_REG("calc_sao_edge_dir", kvz_cuda_calc_sao_edge_dir);
   return ok;
 }
+
+void kvz_cuda_percall_counts(unsigned long long counts[7])
+{
+  std::lock_guard<std::mutex> guard(g_pc.lock);
+  for (int i = 0; i < 7; i++) counts[i] = g_family_calls[i];
+}
+
+// ---------------- the two-argument forms of SURVEY.md 8(b) ----------------
+// int kvz_strategy_register_<family>_cuda(void *opaque, uint8_t bitdepth), exactly like the reference's per-ISA
+// registration functions (e.g. kvz_strategy_register_picture_avx2, strategies/avx2/picture-avx2.h).  The host's
+// kvz_strategyselector_register (src/strategyselector.c:216-256) is looked up in the running process, so this
+// library keeps no link-time dependency on the encoder; a host that hides the symbol uses the *_with forms.
+static kvz_cuda_register_fn host_register_fn()
+{
+  static kvz_cuda_register_fn fn = nullptr;
+  if (!fn) fn = reinterpret_cast<kvz_cuda_register_fn>(dlsym(RTLD_DEFAULT, "kvz_strategyselector_register"));
+  if (!fn) fail_msg("kvz_strategy_register_*_cuda: kvz_strategyselector_register is not visible in this process "
+                    "(use kvz_strategy_register_*_cuda_with)");
+  return fn;
+}
+#define KVZ_REG2(family)                                                                      \
+  int kvz_strategy_register_##family##_cuda(void *opaque, uint8_t bitdepth)                   \
+  {                                                                                           \
+    kvz_cuda_register_fn fn = host_register_fn();                                             \
+    return fn ? kvz_strategy_register_##family##_cuda_with(opaque, bitdepth, fn) : 0;         \
+  }
+KVZ_REG2(picture) KVZ_REG2(dct) KVZ_REG2(quant) KVZ_REG2(intra) KVZ_REG2(ipol) KVZ_REG2(nal) KVZ_REG2(sao)
 
 }  // extern "C"

@@ -1,0 +1,290 @@
+/*
+ * kvazaar_b200/host/kvz_glue_search_inter.c -- Kvazaar's inter PU search with the reference loop on the device.
+ *
+ * Compiled INSTEAD of src/search_inter.c: it includes that file in place (from the reference tree, at build time)
+ * with its two entry points renamed, so every file-static helper of the reference (search_pu_inter_bipred,
+ * fracmv_within_tile, ...) is reachable here and the reference's own search stays available under the names
+ * kvz_search_cu_inter_host / kvz_search_cu_smp_host for KVZ_CUDA_MODE=off|percall.
+ *
+ * What this file adds is the replacement of search_pu_inter (src/search_inter.c:1451-1524): the merge and AMVP
+ * candidates are still derived by the host's own kvz_inter_get_merge_cand / kvz_inter_get_mv_cand from the working
+ * lcu_t -- that is what keeps the decisions in CTU wavefront order -- and the loop over the reference pictures
+ * (search_pu_inter_ref, :1134-1297: integer search, fractional refinement, merge match, AMVP choice, *inter_cost
+ * carry) is ONE call of kvz_cuda_enc_search_pu.
+ */
+#define kvz_search_cu_inter kvz_search_cu_inter_host
+#define kvz_search_cu_smp kvz_search_cu_smp_host
+#include "search_inter.c"
+#undef kvz_search_cu_inter
+#undef kvz_search_cu_smp
+
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "kvz_cuda_enc.h"
+#include "kvz_glue.h"
+
+/* ---- the session: one per process ("Only one encoder may be open at a time", src/kvazaar.h:619) ---- */
+static kvz_cuda_enc *g_enc = NULL;
+static const encoder_control_t *g_enc_ctrl = NULL;
+static pthread_mutex_t g_enc_lock = PTHREAD_MUTEX_INITIALIZER;
+
+static void glue_close_session(void)
+{
+  if (g_enc) {
+    if (getenv("KVZ_CUDA_STATS")) {
+      unsigned long long s[8];
+      kvz_cuda_enc_stats(g_enc, s);
+      fprintf(stderr, "kvz_cuda_enc: frames %llu, PU searches %llu, reference jobs %llu, reference planes uploaded %llu, "
+              "SAD maps of the last frame %.1f MiB (%llu displacements), reference jobs with a window outside the box %llu\n",
+              s[0], s[1], s[5], s[2], s[3] / 1048576.0, s[4], s[6]);
+    }
+    kvz_cuda_enc_close(g_enc);
+    g_enc = NULL;
+  }
+}
+
+static int glue_ime_search(const kvz_config *cfg, int *range)
+{
+  *range = 32;
+  switch (cfg->ime_algorithm) {
+    case KVZ_IME_FULL64: *range = 64; return KVZ_CUDA_IME_FULL;
+    case KVZ_IME_FULL32: case KVZ_IME_FULL: return KVZ_CUDA_IME_FULL;     /* search_inter.c:1208-1215 */
+    case KVZ_IME_FULL16: *range = 16; return KVZ_CUDA_IME_FULL;
+    case KVZ_IME_FULL8: *range = 8; return KVZ_CUDA_IME_FULL;
+    case KVZ_IME_TZ: return KVZ_CUDA_IME_TZ;
+    case KVZ_IME_DIA: return KVZ_CUDA_IME_DIA;
+    default: return KVZ_CUDA_IME_HEXBS;
+  }
+}
+
+static kvz_cuda_enc *glue_session(const encoder_state_t *state)
+{
+  const encoder_control_t *ctrl = state->encoder_control;
+  if (g_enc && g_enc_ctrl == ctrl) return g_enc;
+  pthread_mutex_lock(&g_enc_lock);
+  if (!g_enc || g_enc_ctrl != ctrl) {
+    static int registered = 0;
+    glue_close_session();
+    const kvz_config *cfg = &ctrl->cfg;
+    /* what the device search does not reproduce is refused, loudly -- never searched on the CPU instead */
+    if (cfg->owf != 0)
+      kvz_glue_die("KVZ_CUDA_MODE=batch needs --owf 0: with overlapped frames a reference picture is still being "
+                   "reconstructed while the next frame searches it (encoderstate.c:751-804), the session uploads whole pictures");
+    if (cfg->mv_rdo) kvz_glue_die("--mv-rdo (kvz_calc_mvd_cost_cabac, rdo.c:908) is not on the device");
+    if (cfg->smp_enable || cfg->amp_enable) kvz_glue_die("--smp / --amp PU shapes (4 and 12 sample sides) are not searched on the device");
+    if (ctrl->bitdepth != 8) kvz_glue_die("the encoder-session face is 8-bit only");
+    kvz_cuda_enc_cfg c;
+    memset(&c, 0, sizeof(c));
+    c.device = kvz_glue_device();
+    c.width = ctrl->in.width; c.height = ctrl->in.height; c.bitdepth = ctrl->bitdepth;
+    c.ime_search = glue_ime_search(cfg, &c.range);
+    c.me_early_termination = cfg->me_early_termination; c.me_max_steps = cfg->me_max_steps;
+    c.fme_level = cfg->fme_level;
+    c.owf = cfg->owf; c.wpp = cfg->wpp; c.sao_type = cfg->sao_type; c.deblock_enable = cfg->deblock_enable;
+    c.mv_constraint = cfg->mv_constraint;
+    c.max_ref_lcu_right = ctrl->max_inter_ref_lcu.right; c.max_ref_lcu_down = ctrl->max_inter_ref_lcu.down;
+    if (getenv("KVZ_CUDA_MAP_MBYTES")) c.max_map_mbytes = atoi(getenv("KVZ_CUDA_MAP_MBYTES"));
+    g_enc = kvz_cuda_enc_open(&c);
+    if (!g_enc) kvz_glue_die("kvz_cuda_enc_open");
+    g_enc_ctrl = ctrl;
+    if (!registered) { atexit(glue_close_session); registered = 1; }
+  }
+  pthread_mutex_unlock(&g_enc_lock);
+  return g_enc;
+}
+
+/* ---- per (frame, tile): a handle of the session, found again by every worker thread of the frame ---- */
+#define GLUE_FRAME_SLOTS 64
+static struct { uint64_t id; int handle; } g_frames[GLUE_FRAME_SLOTS];
+static int g_frames_next = 0;
+static pthread_mutex_t g_frames_lock = PTHREAD_MUTEX_INITIALIZER;
+
+/* quarter-pel vectors of the motion fields of the DPB, one sample per 16x16: where extra_mv (search_inter.c:1188-1206)
+ * and the merge candidates of this frame will probably point */
+static int glue_mv_hints(const encoder_state_t *state, int16_t *hints, int max_hints)
+{
+  const image_list_t *ref = state->frame->ref;
+  int n = 0;
+  for (unsigned r = 0; r < ref->used_size; r++) {
+    const cu_array_t *cua = ref->cu_arrays[r];
+    if (!cua) continue;
+    for (unsigned y = 8; y < cua->height; y += 16) {
+      for (unsigned x = 8; x < cua->width; x += 16) {
+        const cu_info_t *cu = kvz_cu_array_at_const(cua, x, y);
+        if (cu->type != CU_INTER) continue;
+        for (int l = 0; l < 2; l++) {
+          if (!(cu->inter.mv_dir & (1 << l)) || n >= max_hints) continue;
+          hints[2 * n] = cu->inter.mv[l][0]; hints[2 * n + 1] = cu->inter.mv[l][1];
+          n++;
+        }
+      }
+    }
+  }
+  return n;
+}
+
+static int glue_frame_handle(kvz_cuda_enc *enc, const encoder_state_t *state)
+{
+  const uint64_t id = ((uint64_t)(uint32_t)state->frame->num << 16) | (uint64_t)(state->tile->id & 0xFFFF);
+  for (int i = 0; i < GLUE_FRAME_SLOTS; i++)            /* racy read of a slot is fine: ids are unique and written last */
+    if (__atomic_load_n(&g_frames[i].id, __ATOMIC_ACQUIRE) == id + 1) return g_frames[i].handle;
+  pthread_mutex_lock(&g_frames_lock);
+  int handle = -1;
+  for (int i = 0; i < GLUE_FRAME_SLOTS; i++) if (g_frames[i].id == id + 1) handle = g_frames[i].handle;
+  if (handle < 0) {
+    const videoframe_t *vf = state->tile->frame;
+    const kvz_picture *src = vf->source->base_image ? vf->source->base_image : vf->source;
+    const image_list_t *ref = state->frame->ref;
+    const int max_hints = 1 << 16;
+    int16_t *hints = malloc(sizeof(int16_t) * 2 * max_hints);
+    const int n_hints = hints ? glue_mv_hints(state, hints, max_hints) : 0;
+    kvz_cuda_enc_frame f;
+    memset(&f, 0, sizeof(f));
+    f.frame_id = id;
+    f.src_luma = src->y; f.src_stride = src->stride; f.src_key = (uint64_t)(uintptr_t)src;
+    f.tile_x = state->tile->offset_x; f.tile_y = state->tile->offset_y;
+    f.tile_w = vf->width; f.tile_h = vf->height;
+    memcpy(f.ref_LX, state->frame->ref_LX, sizeof(f.ref_LX));
+    f.n_refs = (int)ref->used_size;
+    for (int r = 0; r < f.n_refs; r++) {
+      const kvz_picture *im = ref->images[r];
+      f.refs[r].luma = im->y; f.refs[r].stride = im->stride; f.refs[r].poc = ref->pocs[r];
+      f.refs[r].key = (uint64_t)(uintptr_t)im;
+      f.refs[r].mv_hints = hints; f.refs[r].n_mv_hints = n_hints;
+    }
+    handle = kvz_cuda_enc_frame_begin(enc, &f);
+    free(hints);
+    if (handle < 0) kvz_glue_die("kvz_cuda_enc_frame_begin");
+    KVZ_GLUE_COUNT(KVZ_GLUE_CNT_ME_FRAMES);
+    const int slot = g_frames_next;
+    g_frames_next = (g_frames_next + 1) % GLUE_FRAME_SLOTS;
+    g_frames[slot].handle = handle;
+    __atomic_store_n(&g_frames[slot].id, id + 1, __ATOMIC_RELEASE);
+  }
+  pthread_mutex_unlock(&g_frames_lock);
+  return handle;
+}
+
+/* which list holds picture ref_idx, and where (search_inter.c:1142-1162) */
+static void glue_list_of(const encoder_state_t *state, int ref_idx, int8_t *ref_list, int8_t *lx_idx)
+{
+  const int n = MAX(state->frame->ref_LX_size[0], state->frame->ref_LX_size[1]);
+  *ref_list = -1;
+  for (*lx_idx = 0; *lx_idx < n; (*lx_idx)++) {
+    if (*lx_idx < state->frame->ref_LX_size[0] && state->frame->ref_LX[0][*lx_idx] == ref_idx) { *ref_list = 0; return; }
+    if (*lx_idx < state->frame->ref_LX_size[1] && state->frame->ref_LX[1][*lx_idx] == ref_idx) { *ref_list = 1; return; }
+  }
+  kvz_glue_die("reference picture in neither list");
+}
+
+/* search_pu_inter (search_inter.c:1451-1524) with the reference loop on the device */
+static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_cu, int depth, part_mode_t part_mode,
+                                 int i_pu, lcu_t *lcu, double *inter_cost, uint32_t *inter_bitcost)
+{
+  *inter_cost = MAX_INT;
+  *inter_bitcost = MAX_INT;
+  const kvz_config *cfg = &state->encoder_control->cfg;
+  const videoframe_t *const frame = state->tile->frame;
+  const int width_cu = LCU_WIDTH >> depth;
+  const int x = PU_GET_X(part_mode, width_cu, x_cu, i_pu), y = PU_GET_Y(part_mode, width_cu, y_cu, i_pu);
+  const int width = PU_GET_W(part_mode, width_cu, i_pu), height = PU_GET_H(part_mode, width_cu, i_pu);
+  const bool merge_a1 = i_pu == 0 || width >= height;       /* second PUs of Nx2N.. / 2NxN.. (:1472-1477) */
+  const bool merge_b1 = i_pu == 0 || width <= height;
+  cu_info_t *cur_cu = LCU_GET_CU_AT_PX(lcu, SUB_SCU(x), SUB_SCU(y));
+
+  inter_search_info_t info = {
+    .state = state, .pic = frame->source, .origin = { x, y }, .width = width, .height = height,
+    .mvd_cost_func = calc_mvd_cost,
+  };
+  info.num_merge_cand = kvz_inter_get_merge_cand(state, x, y, width, height, merge_a1, merge_b1, info.merge_cand, lcu);
+  CU_SET_MV_CAND(cur_cu, 0, 0);
+  CU_SET_MV_CAND(cur_cu, 1, 0);
+
+  kvz_cuda_enc *enc = glue_session(state);
+  const int handle = glue_frame_handle(enc, state);
+  const int n_refs = (int)state->frame->ref->used_size;
+
+  kvz_cuda_me_pu pu;
+  kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
+  kvz_cuda_me_result res[KVZ_CUDA_MAX_REFS];
+  int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
+  memset(&pu, 0, sizeof(pu));
+  memset(jobs, 0, sizeof(jobs));
+  pu.x = (int16_t)x; pu.y = (int16_t)y; pu.w = (uint8_t)width; pu.h = (uint8_t)height;
+  pu.num_merge_cand = (uint8_t)info.num_merge_cand;
+  pu.num_jobs = (uint8_t)n_refs;
+  for (int i = 0; i < info.num_merge_cand; i++) {
+    const inter_merge_cand_t *m = &info.merge_cand[i];
+    pu.merge_cand[i].dir = m->dir;
+    pu.merge_cand[i].ref[0] = m->ref[0]; pu.merge_cand[i].ref[1] = m->ref[1];
+    memcpy(pu.merge_cand[i].mv, m->mv, sizeof(pu.merge_cand[i].mv));
+  }
+  for (int r = 0; r < n_refs; r++) {
+    glue_list_of(state, r, &ref_list[r], &lx_idx[r]);
+    /* AMVP candidates for this picture (:1164-1181); they depend on cur_cu only through mv_ref[list] */
+    const int8_t saved = cur_cu->inter.mv_ref[ref_list[r]];
+    cur_cu->inter.mv_ref[ref_list[r]] = lx_idx[r];
+    kvz_inter_get_mv_cand(state, x, y, width, height, info.mv_cand, cur_cu, lcu, ref_list[r]);
+    cur_cu->inter.mv_ref[ref_list[r]] = saved;
+    memcpy(jobs[r].mv_cand, info.mv_cand, sizeof(jobs[r].mv_cand));
+    /* the colocated CU's vector in that picture (:1188-1206) */
+    const int mid_x = state->tile->offset_x + x + (width >> 1), mid_y = state->tile->offset_y + y + (height >> 1);
+    const cu_info_t *ref_cu = kvz_cu_array_at_const(state->frame->ref->cu_arrays[r], mid_x, mid_y);
+    if (ref_cu->type == CU_INTER) {
+      const int l = (ref_cu->inter.mv_dir & 1) ? 0 : 1;
+      jobs[r].extra_mv[0] = ref_cu->inter.mv[l][0]; jobs[r].extra_mv[1] = ref_cu->inter.mv[l][1];
+    }
+    jobs[r].ref_idx = (uint8_t)r;
+  }
+
+  if (n_refs > 0) {
+    if (!kvz_cuda_enc_search_pu(enc, handle, (int)(state->lambda_sqrt + 0.5), &pu, jobs, res)) kvz_glue_die("kvz_cuda_enc_search_pu");
+    KVZ_GLUE_COUNT(KVZ_GLUE_CNT_ME_PU);
+  }
+
+  /* what search_pu_inter_ref writes when a picture lowers *inter_cost (:1281-1296), pictures in order */
+  for (int r = 0; r < n_refs; r++) {
+    if (!res[r].took) continue;
+    const int l = ref_list[r];
+    cur_cu->inter.mv_dir = l + 1;
+    cur_cu->merged = res[r].merged;
+    cur_cu->merge_idx = res[r].merge_idx;
+    cur_cu->inter.mv_ref[l] = lx_idx[r];
+    cur_cu->inter.mv[l][0] = res[r].mv[0];
+    cur_cu->inter.mv[l][1] = res[r].mv[1];
+    CU_SET_MV_CAND(cur_cu, l, res[r].mv_cand_idx);
+    *inter_cost = res[r].cost;
+    *inter_bitcost = res[r].bitcost + cur_cu->inter.mv_dir - 1 + lx_idx[r];
+  }
+
+  /* bi-prediction from pairs of merge candidates stays the reference's own function (:1304-1434): it predicts with
+   * the ipol strategies and costs with kvz_satd_any_size; info.mv_cand holds the last picture's candidates as there */
+  const bool can_use_bipred = state->frame->slicetype == KVZ_SLICE_B && cfg->bipred && width + height >= 16;
+  if (can_use_bipred) {
+    if (n_refs > 0) { info.ref_idx = n_refs - 1; info.ref = state->frame->ref->images[n_refs - 1]; }
+    search_pu_inter_bipred(&info, depth, lcu, cur_cu, inter_cost, inter_bitcost);
+  }
+}
+
+/* kvz_search_cu_inter (search_inter.c:1588-1610) */
+void kvz_search_cu_inter(encoder_state_t *const state, int x, int y, int depth, lcu_t *lcu, double *inter_cost,
+                         uint32_t *inter_bitcost)
+{
+  if (!(kvz_glue_mode() & KVZ_GLUE_BATCH)) {
+    kvz_search_cu_inter_host(state, x, y, depth, lcu, inter_cost, inter_bitcost);
+    return;
+  }
+  glue_search_pu_inter(state, x, y, depth, SIZE_2Nx2N, 0, lcu, inter_cost, inter_bitcost);
+  if (state->encoder_control->cfg.rdo >= 2) kvz_cu_cost_inter_rd2(state, x, y, depth, lcu, inter_cost, inter_bitcost);
+}
+
+/* kvz_search_cu_smp (search_inter.c:1627-1700): SMP / AMP are refused when the session opens, so in batch mode this
+ * is never reached with them enabled; the reference's function serves the other modes */
+void kvz_search_cu_smp(encoder_state_t *const state, int x, int y, int depth, part_mode_t part_mode, lcu_t *lcu,
+                       double *inter_cost, uint32_t *inter_bitcost)
+{
+  if (kvz_glue_mode() & KVZ_GLUE_BATCH) kvz_glue_die("kvz_search_cu_smp: SMP / AMP partitions are not searched on the device");
+  kvz_search_cu_smp_host(state, x, y, depth, part_mode, lcu, inter_cost, inter_bitcost);
+}

@@ -79,7 +79,7 @@ def test_registration_contract_without_device(ref_lib):
 
     reg = C.cast(ref_lib.kvz_strategyselector_register, C.c_void_p)
     for fam in ("picture", "dct", "quant", "intra", "ipol"):
-        fn = getattr(L, f"kvz_strategy_register_{fam}_cuda")
+        fn = getattr(L, f"kvz_strategy_register_{fam}_cuda_with")
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_uint8, C.c_void_p]
         lst = StrategyList()
         assert fn(C.byref(lst), 10, reg) == 1 and lst.count == 0

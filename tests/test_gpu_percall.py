@@ -223,7 +223,7 @@ def test_registers_into_the_reference_strategy_list(ref_lib):
     reg = C.cast(ref_lib.kvz_strategyselector_register, C.c_void_p)
     total = 0
     for fam, n in (("picture", 24), ("dct", 10), ("quant", 1), ("intra", 2), ("ipol", 8), ("nal", 1), ("sao", 2)):
-        fn = getattr(L, f"kvz_strategy_register_{fam}_cuda")
+        fn = getattr(L, f"kvz_strategy_register_{fam}_cuda_with")
         fn.restype, fn.argtypes = C.c_int, [C.c_void_p, C.c_uint8, C.c_void_p]
         lst = StrategyList()
         assert fn(C.byref(lst), 8, reg) == 1
