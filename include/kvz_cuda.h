@@ -248,6 +248,14 @@ enum kvz_cuda_ime_search {
 KVZ_CUDA_API int kvz_cuda_me_search(const kvz_cuda_me_frame *frame, const kvz_cuda_me_pu *d_pus, int n_pus,
                                     const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream);
 
+/* The same results from ONE launch with one CTA per PU (integer search, then refinement, inside the CTA): the form
+ * for a host that searches one PU -- or the PUs of one CTU anti-diagonal -- at a time, where launch and tail
+ * latency matter more than throughput (kvz_cuda_enc_search_pu, kvz_cuda_enc.h, calls it with n_pus = 1).  A window
+ * that no box map set holds is evaluated from a copy of the reference region in shared memory by the whole CTA
+ * (square window sets, n_dx == 0, are not consulted here).  d_pus / d_jobs / d_results may be mapped host memory. */
+KVZ_CUDA_API int kvz_cuda_me_search_fused(const kvz_cuda_me_frame *frame, const kvz_cuda_me_pu *d_pus, int n_pus,
+                                          const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream);
+
 /* ------------------------------------------------------------------ */
 /* BATCH face: block costs  (rows A1, A2, A6, A7, A8, A16)               */
 /* ------------------------------------------------------------------ */

@@ -145,6 +145,7 @@ SIGNATURES = {
     "kvz_cuda_bipred_blend": (C.c_int, [_VP, _VP, C.c_size_t, C.c_int, _VP, _VP]),
     "kvz_cuda_intra_mode_costs": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "kvz_cuda_me_search": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
+    "kvz_cuda_me_search_fused": (C.c_int, [C.POINTER(MeFrame), _VP, C.c_int, _VP, _VP, _VP]),
 }
 
 

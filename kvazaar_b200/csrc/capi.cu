@@ -278,8 +278,8 @@ int kvz_cuda_ime_sad_box_maps_multi(const kvz_cuda_ime_box_ref *refs, int n_refs
   return launch_ime_sad_box_multi(ps, boxes, n_refs, (cudaStream_t)stream);
 }
 
-int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
-                       const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream)
+static int me_search_common(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
+                            const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream, bool fused)
 {
   if (!fr || !d_pus || !d_jobs || !d_results || !fr->d_cur) return fail_msg("kvz_cuda_me_search: null argument");
   if (fr->bitdepth != 8) return fail_msg("kvz_cuda_me_search: only bitdepth 8 is implemented");
@@ -318,7 +318,20 @@ int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus,
       f.refs[i].sets[m].sad32 = r.mapsets[m].d_sad32; f.refs[i].sets[m].sad64 = r.mapsets[m].d_sad64;
     }
   }
+  if (fused) return launch_me_search_pu(f, d_pus, d_jobs, d_results, n_pus, (cudaStream_t)stream);
   return launch_me_search(f, d_pus, d_jobs, d_results, n_pus, (cudaStream_t)stream);
+}
+
+int kvz_cuda_me_search(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
+                       const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream)
+{
+  return me_search_common(fr, d_pus, n_pus, d_jobs, d_results, stream, false);
+}
+
+int kvz_cuda_me_search_fused(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d_pus, int n_pus,
+                             const kvz_cuda_me_job *d_jobs, kvz_cuda_me_result *d_results, void *stream)
+{
+  return me_search_common(fr, d_pus, n_pus, d_jobs, d_results, stream, true);
 }
 
 int kvz_cuda_block_costs(const void *d_a, const void *d_b, const kvz_cuda_block_job *d_jobs, int n_jobs,

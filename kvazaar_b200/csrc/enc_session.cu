@@ -88,26 +88,32 @@ namespace {
 
 int fail_enc(const char *what) { return fail_msg(what); }
 
-// One box per reference: the zero window plus the windows round the vectors the hints predict.  Hints are trimmed
-// to their 2nd..98th percentile per axis (a few wild vectors must not blow the box up) and the spread of the window
-// centres is capped so that the box stays inside +-kFar.
-void choose_box(int R, const int16_t *hints, int n_hints, int max_spread, int box[4])
+// One box per reference: the zero window plus the windows round the vectors the hints predict.  Window centres are
+// the whole-sample parts of the frame's merge candidates and colocated vectors (search_inter.c:898-955) -- vectors of
+// ANY reference, so one box serves all references.  The hints are trimmed to their 0.5th..99.5th percentile per axis
+// (a few wild vectors must not blow the box up) and widened by kBoxMargin, because the vectors this frame finds
+// scatter round the ones its references found.  Caps: the dense kernel stages n_dy + 63 reference rows in shared
+// memory (ime_box_max_rows(), 177) and the box maps are at most 272 displacements wide.
+constexpr int kBoxMargin = 24;
+void choose_box(int R, const int16_t *hints, int n_hints, int shrink_pct, int box[4])
 {
+  static const int margin = getenv("KVZ_CUDA_BOX_MARGIN") ? atoi(getenv("KVZ_CUDA_BOX_MARGIN")) : kBoxMargin;   // experiments
   int lox = 0, hix = 0, loy = 0, hiy = 0;
   if (hints && n_hints > 0) {
     std::vector<int> xs(n_hints), ys(n_hints);
     for (int i = 0; i < n_hints; i++) { xs[i] = hints[2 * i] >> 2; ys[i] = hints[2 * i + 1] >> 2; }
     std::sort(xs.begin(), xs.end());
     std::sort(ys.begin(), ys.end());
-    const int a = n_hints / 50, b = n_hints - 1 - n_hints / 50;
-    lox = std::min(0, xs[a]); hix = std::max(0, xs[b]);
-    loy = std::min(0, ys[a]); hiy = std::max(0, ys[b]);
+    const int a = n_hints / 200, b = n_hints - 1 - n_hints / 200;
+    lox = std::min(lox, xs[a]); hix = std::max(hix, xs[b]);
+    loy = std::min(loy, ys[a]); hiy = std::max(hiy, ys[b]);
   }
-  // vectors round to the next whole sample in some window centres ((mv + 2) >> 2, search_inter.c:268): one sample of slack
-  hix += 1; hiy += 1;
-  const int cap = std::max(0, std::min(max_spread, kFar - 8 - R));
-  lox = std::max(lox, -cap); loy = std::max(loy, -cap);
-  hix = std::min(hix, cap); hiy = std::min(hiy, cap);
+  lox -= margin; loy -= margin; hix += margin; hiy += margin;
+  const int cap_x = std::max(0, std::min((272 - 8 - (2 * R + 1)) / 2, kFar - 8 - R)) * shrink_pct / 100;
+  static const int max_rows = ime_box_max_rows();
+  const int cap_y = std::max(0, (max_rows - (2 * R + 1)) / 2) * shrink_pct / 100;
+  lox = std::max(lox, -cap_x); hix = std::min(hix, cap_x);
+  loy = std::max(loy, -cap_y); hiy = std::min(hiy, cap_y);
   box[0] = lox - R; box[1] = loy - R;
   box[2] = ((hix + R) - (lox - R) + 1 + 7) & ~7;
   box[3] = (hiy + R) - (loy - R) + 1;
@@ -155,8 +161,10 @@ bool worker_ready(kvz_cuda_enc *e)
   if (w.device == e->cfg.device && w.stream) return true;
   if (cudaSetDevice(e->cfg.device) != cudaSuccess) return false;      // every calling thread binds the session's device
   if (cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess) return false;
-  if (cudaHostAlloc(&w.h, kStageBytes, cudaHostAllocDefault) != cudaSuccess) return false;
-  if (cudaMalloc(&w.d, kStageBytes) != cudaSuccess) return false;
+  // pinned AND mapped: the kernel reads the PU and its jobs from, and writes its results to, this host buffer
+  // directly (one small PCIe read / write per call instead of two copy commands)
+  if (cudaHostAlloc(&w.h, kStageBytes, cudaHostAllocMapped) != cudaSuccess) return false;
+  if (cudaHostGetDevicePointer(reinterpret_cast<void **>(&w.d), w.h, 0) != cudaSuccess) return false;
   w.device = e->cfg.device;
   return true;
 }
@@ -290,15 +298,15 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   const bool full = cfg.ime_search == KVZ_CUDA_IME_FULL;
   size_t need = 0;
   if (full) {
-    int spread = kFar;
+    int shrink = 100;                                  // percent of the caps: boxes shrink until the maps fit the budget
     for (;;) {
       need = 0;
       for (int r = 0; r < fr->n_refs; r++) {
-        choose_box(cfg.range, fr->refs[r].mv_hints, fr->refs[r].n_mv_hints, spread, ctx->box[r]);
+        choose_box(cfg.range, fr->refs[r].mv_hints, fr->refs[r].n_mv_hints, shrink, ctx->box[r]);
         need += box_bytes(fr->tile_w, fr->tile_h, ctx->box[r]);
       }
-      if (need <= (size_t)cfg.max_map_mbytes << 20 || spread == 0) break;
-      spread = spread * 3 / 4;
+      if (need <= (size_t)cfg.max_map_mbytes << 20 || shrink == 0) break;
+      shrink = shrink * 3 / 4;
     }
     if (need > ctx->map_bytes) {
       if (ctx->maps) { cudaStreamSynchronize(e->stream); cudaFree(ctx->maps); ctx->maps = nullptr; ctx->map_bytes = 0; }
@@ -392,12 +400,6 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
     for (int i = 0; i < nj; i++)
       if (!job_in_box(*ctx, e->cfg.range, *pu, jobs[i])) { all_in_box = false; e->stats[6]++; }
 
-  kvz_cuda_me_pu *hp = reinterpret_cast<kvz_cuda_me_pu *>(w.h);
-  *hp = *pu;
-  hp->first_job = 0;
-  memcpy(w.h + kOffJobs, jobs, (size_t)nj * sizeof(kvz_cuda_me_job));
-  const size_t in_bytes = kOffJobs + (size_t)nj * sizeof(kvz_cuda_me_job);
-  KVZ_CUDA_TRY(cudaMemcpyAsync(w.d, w.h, in_bytes, cudaMemcpyHostToDevice, w.stream));
   const uint64_t tag = ((uint64_t)handle << 48) ^ ctx->id;
   if (w.seen_ctx != tag || w.seen_enc != e) {              // first call of this thread for this frame: wait for its maps
     KVZ_CUDA_TRY(cudaStreamWaitEvent(w.stream, ctx->ready, 0));
@@ -405,11 +407,11 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
   }
   MeFrame f = ctx->f;
   f.lambda_sqrt_i = lambda_sqrt_i;
-  if (!launch_me_search(f, reinterpret_cast<const kvz_cuda_me_pu *>(w.d),
-                        reinterpret_cast<const kvz_cuda_me_job *>(w.d + kOffJobs),
-                        reinterpret_cast<kvz_cuda_me_result *>(w.d + kOffResults), 1, w.stream)) return 0;
-  KVZ_CUDA_TRY(cudaMemcpyAsync(w.h + kOffResults, w.d + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result),
-                               cudaMemcpyDeviceToHost, w.stream));
+  kvz_cuda_me_pu one = *pu;
+  one.first_job = 0;
+  // the PU and its jobs go in the launch itself; the results come back through the mapped host buffer
+  if (!launch_me_search_pu(f, nullptr, nullptr, reinterpret_cast<kvz_cuda_me_result *>(w.d + kOffResults), 1, w.stream,
+                           &one, jobs)) return 0;
   KVZ_CUDA_TRY(cudaStreamSynchronize(w.stream));
   memcpy(results, w.h + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result));
   e->stats[1]++;
@@ -427,6 +429,16 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
 void kvz_cuda_enc_stats(const kvz_cuda_enc *e, unsigned long long stats[8])
 {
   for (int i = 0; i < 8; i++) stats[i] = e ? e->stats[i].load() : 0ull;
+  if (e && e->timing) {
+    unsigned long long ph[4][4];
+    cudaSetDevice(e->cfg.device);
+    cudaDeviceSynchronize();
+    if (me_pu_phase_times(ph))
+      for (int sz = 0; sz < 4; sz++)
+        if (ph[sz][3])
+          fprintf(stderr, "kvz_cuda_enc: PU %2d  device time per call: box scan %.1f us, CTA scan %.1f us, refinement %.1f us (%llu calls)\n",
+                  8 << sz, ph[sz][0] / 1000.0 / ph[sz][3], ph[sz][1] / 1000.0 / ph[sz][3], ph[sz][2] / 1000.0 / ph[sz][3], ph[sz][3]);
+  }
   if (e && e->timing)
     for (int sz = 0; sz < 4; sz++)
       for (int k = 0; k < 2; k++)

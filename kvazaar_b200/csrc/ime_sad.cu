@@ -611,6 +611,17 @@ int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaS
   return launch_r<0>(p, stream);
 }
 
+// the largest n_dy launch_ime_sad_box_multi accepts: the CTA stages n_dy (+ up to 7 alignment rows) + 63 reference rows
+int ime_box_max_rows()
+{
+  int best = 1;
+  for (int n = 1; n <= 272; n++) {
+    const int skip = (8 - ((n - 1) & 7)) & 7;
+    if (ws_smem_bytes(Geo(n + skip)) <= 113 * 1024) best = n;
+  }
+  return best;
+}
+
 int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream)
 {
   if (n <= 0 || n > kImeMaxMulti) return fail_msg("ime_sad_box_multi: 1..8 references per launch");

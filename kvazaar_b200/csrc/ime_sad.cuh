@@ -40,6 +40,8 @@ int launch_ime_sad_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, cudaS
 
 // 10-bit samples (uint16_t planes, pitches of `p` in bytes): ime_sad10.cu
 int launch_ime_sad10_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, int bitdepth, cudaStream_t stream);
+// largest box height (displacement rows) of launch_ime_sad_box_multi
+int ime_box_max_rows();
 // the boxes of n <= kImeMaxMulti references of one current picture in ONE launch; boxes[r] = {x0, y0, n_dx, n_dy}
 int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream);
 

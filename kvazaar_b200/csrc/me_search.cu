@@ -22,6 +22,8 @@
 //      (search_inter.c:1244-1256); then the merge-index match and select_mv_cand
 //      (search_inter.c:1258-1297).  A warp works on a PU up to 16x16 (four PUs per
 //      CTA), the whole 256-thread CTA on a larger one.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "me_search.cuh"
 #include "satd.cuh"
@@ -81,10 +83,12 @@ template <int G>
 struct Group {
   int tid;        // 0..G-1 inside the group
   int id;         // group index inside the CTA
+  int bar = 0;    // groups of several warps that are not the whole CTA: their named barrier (1..15); 0 = __syncthreads
   __device__ __forceinline__ void sync() const
   {
     if (G == 32) __syncwarp();
-    else __syncthreads();
+    else if (bar == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(G) : "memory");
   }
 };
 
@@ -269,6 +273,16 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
 }
 
+// development timers of the box scan (KVZ_CUDA_STATS): [0] table set-up, [1] seed, [2] stream, [3] scans timed
+__device__ unsigned long long g_box_scan_ns[4];
+__device__ int g_box_scan_timing;
+__device__ __forceinline__ unsigned long long gtime_ns()
+{
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 // per-warp scratch of the integer search
 template <bool BOX> struct ScanSmemT;
 template <> struct ScanSmemT<false> {         // per-window scan: static
@@ -364,6 +378,57 @@ __device__ KVZ_BOX_INLINE uint32_t box_key(const BoxCtx &b, uint32_t pos)
 __device__ KVZ_BOX_INLINE uint32_t box_tie(const BoxCtx &b, uint32_t pos_a, uint32_t pos_b)
 {
   return box_key(b, pos_b) < box_key(b, pos_a) ? pos_b : pos_a;
+}
+
+// The window centres search_mv_full visits, in order (search_inter.c:891-955): the zero vector, extra_mv >> 2 unless a
+// merge candidate rounds to it (mv_in_merge, :260-273), then every uni-directional merge candidate >> 2 that is not zero.
+__device__ __forceinline__ int build_windows(const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                                             const kvz_cuda_me_job &job, int (&wcx)[7], int (&wcy)[7])
+{
+  int nwin = 1;
+  wcx[0] = 0; wcy[0] = 0;
+  const int ex = job.extra_mv[0] >> 2, ey = job.extra_mv[1] >> 2;
+  bool in_merge = false;
+  for (int i = 0; i < pu.num_merge_cand; i++) {
+    const kvz_cuda_merge_cand &m = merge[i];
+    if (m.dir == 3) continue;
+    if (((m.mv[m.dir - 1][0] + 2) >> 2) == ex && ((m.mv[m.dir - 1][1] + 2) >> 2) == ey) in_merge = true;
+  }
+  if (!in_merge) { wcx[nwin] = ex; wcy[nwin] = ey; nwin++; }
+  for (int i = 0; i < pu.num_merge_cand; i++) {
+    const kvz_cuda_merge_cand &m = merge[i];
+    if (m.dir == 3) continue;
+    const int mx = m.mv[m.dir - 1][0] >> 2, my = m.mv[m.dir - 1][1] >> 2;
+    if (mx == 0 && my == 0) continue;
+    wcx[nwin] = mx; wcy[nwin] = my; nwin++;
+  }
+  return nwin;
+}
+
+// The winner of an integer search, key = cost << 32 | window << 16 | position in the window (~0: no candidate),
+// parked in the job's result record for the refinement
+__device__ void park_winner(unsigned long long best, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                            const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
+{
+  JobCtx j;
+  make_ctx(j, f, pu, merge, job);
+  const int R = f.range, K = 2 * R + 1;
+  int wcx[7], wcy[7];
+  build_windows(pu, merge, job, wcx, wcy);
+  int best_mvx = 0, best_mvy = 0;            // quarter-pel (info->best_mv starts at 0,0)
+  uint32_t best_cost = 0xFFFFFFFFu, best_bits = 0;
+  if (best != ~0ull) {
+    const int wi = (int)((best >> 16) & 0xFFFF), pos = (int)(best & 0xFFFF);
+    best_mvx = (wcx[wi] - R + pos % K) * 4;
+    best_mvy = (wcy[wi] - R + pos / K) * 4;
+    best_cost = (uint32_t)(best >> 32);
+    best_bits = mvd_cost_bits(j, best_mvx >> 2, best_mvy >> 2, 2);
+  }
+  kvz_cuda_me_result r;
+  r.mv[0] = (int16_t)best_mvx; r.mv[1] = (int16_t)best_mvy;
+  r.cost = best_cost; r.bitcost = best_bits;
+  r.merged = 0; r.merge_idx = 0; r.mv_cand_idx = 0; r.took = 0;
+  *out = r;
 }
 
 // ======================================================================================
@@ -547,13 +612,17 @@ __device__ void heuristic_job(int lane, const MeFrame &f, const kvz_cuda_me_pu &
   }
 }
 
+// returns false when the job belongs to the other instantiation (nothing written except the 0xFF mark of BOX)
+// BOX only: `nsub` warps share one job, warp `sub` of them streams every nsub-th step of the box and leaves its best
+// key in *part instead of parking a winner (the caller combines the parts, park_winner).
 template <bool BOX>
-__device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
-                         const kvz_cuda_me_job &job, kvz_cuda_me_result *out, bool after_box)
+__device__ bool scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                         const kvz_cuda_me_job &job, kvz_cuda_me_result *out, bool after_box, int sub = 0, int nsub = 1,
+                         unsigned long long *part = nullptr)
 {
   constexpr int G = 32;
   // the box instantiation ran first and marked the jobs it left for this one (took = 0xFF)
-  if (!BOX && after_box && __shfl_sync(0xffffffffu, lane == 0 ? (int)out->took : 0, 0) != 0xFF) return;
+  if (!BOX && after_box && __shfl_sync(0xffffffffu, lane == 0 ? (int)out->took : 0, 0) != 0xFF) return false;
   JobCtx j;
   make_ctx(j, f, pu, merge, job);
   const MeRef &ref = f.refs[job.ref_idx];
@@ -563,25 +632,8 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
   const uint8_t *cur = f.cur + (size_t)fy0 * f.cur_pitch + fx0;
 
   // ---- window list of search_mv_full ----
-  int wcx[7], wcy[7], nwin = 1;
-  wcx[0] = 0; wcy[0] = 0;
-  {
-    const int ex = job.extra_mv[0] >> 2, ey = job.extra_mv[1] >> 2;
-    bool in_merge = false;                       // mv_in_merge (search_inter.c:260-273)
-    for (int i = 0; i < pu.num_merge_cand; i++) {
-      const kvz_cuda_merge_cand &m = merge[i];
-      if (m.dir == 3) continue;
-      if (((m.mv[m.dir - 1][0] + 2) >> 2) == ex && ((m.mv[m.dir - 1][1] + 2) >> 2) == ey) in_merge = true;
-    }
-    if (!in_merge) { wcx[nwin] = ex; wcy[nwin] = ey; nwin++; }
-    for (int i = 0; i < pu.num_merge_cand; i++) {
-      const kvz_cuda_merge_cand &m = merge[i];
-      if (m.dir == 3) continue;
-      const int mx = m.mv[m.dir - 1][0] >> 2, my = m.mv[m.dir - 1][1] >> 2;
-      if (mx == 0 && my == 0) continue;
-      wcx[nwin] = mx; wcy[nwin] = my; nwin++;
-    }
-  }
+  int wcx[7], wcy[7];
+  const int nwin = build_windows(pu, merge, job, wcx, wcy);
 
   // level of the dense maps that holds this PU, if any
   int level = -1;
@@ -608,13 +660,16 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
   }
   if ((bi >= 0) != BOX) {                       // the other instantiation of the kernel owns this job
     if (BOX && lane == 0) out->took = 0xFF;
-    return;
+    return false;
   }
   if constexpr (BOX) {
     // Every displacement of the union of the windows is priced once.  A displacement belongs to the
     // FIRST window of the list that covers it (a later window meets it again with the same cost and
     // loses the tie), so the key of a candidate is (cost, that window, its position in that window).
     const MeMapSet &ms = ref.sets[bi];
+    const bool timed = g_box_scan_timing && lane == 0 && sub == 0;
+    unsigned long long tb0 = 0, tb1 = 0, tb2 = 0;
+    if (timed) tb0 = gtime_ns();
     BoxCtx bc;
     bc.f = &f; bc.j = &j; bc.sm = &sm; bc.wcx = wcx; bc.wcy = wcy; bc.nwin = nwin;
     bc.bx0 = ms.cx; bc.by0 = ms.cy; bc.R = R; bc.K = K; bc.free_mv = free_mv;
@@ -676,10 +731,10 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     __syncwarp();
     const int n_hit = sm.n_hit;
     bc.n_hit = n_hit;
+    if (timed) tb1 = gtime_ns();
     const int n = 8 >> level;
     const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
     const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
-    const int vpr = n_dx >> 3;
 
     const int z_r0 = -R - by0, z_c0 = -R - bx0;     // the zero window (window 0) inside the box
     int hitv[5];                                    // vectors that hold a merge-override entry: row << 13 | vector
@@ -753,30 +808,44 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     // multiple of 8.  Vector index i runs chunk by chunk, inside a chunk row-major (2 vectors per row, 1 in a half
     // chunk): the vectors of a chunk are contiguous in memory.  The traversal order is free -- ties are settled
     // by key, not by visiting order.
-    const int total = n_dy * vpr;
     const int nch = (n_dx + 15) >> 4, last_vpc = (n_dx & 8) ? 1 : 2;
-    const int L = 2 * n_dy;                                         // vectors of a full chunk
     const int pus_level = f.ctus_x * ((f.tile_h + 63) >> 6) * n * n;
     const bool wide = level >= 2;                                   // uint32 entries: two pieces per vector
     const uint4 *mp = wide ? reinterpret_cast<const uint4 *>(level == 2 ? ms.sad32 : ms.sad64)
                            : reinterpret_cast<const uint4 *>(level == 0 ? ms.sad8 : ms.sad16);
     const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
-    // cursor over the vectors of this lane: chunk c, index ic inside the chunk, off = position in the map (in
-    // vectors of 8 entries): off advances with ic and jumps to the next chunk's run when ic passes L
+    // Only the bounding rectangle of the job's windows is streamed: box rows r0 .. r0 + nr - 1 of chunks c0 .. c1
+    // (a box made for all PUs of a frame is much larger than the windows of one PU).
+    int r0, nr, c0, c1;
+    {
+      int lox = wcx[0], hix = wcx[0], loy = wcy[0], hiy = wcy[0];
+      for (int w = 1; w < nwin; w++) {
+        lox = min(lox, wcx[w]); hix = max(hix, wcx[w]);
+        loy = min(loy, wcy[w]); hiy = max(hiy, wcy[w]);
+      }
+      r0 = loy - R - by0; nr = hiy - loy + 2 * R + 1;
+      c0 = (lox - R - bx0) >> 4; c1 = (hix + R - bx0) >> 4;
+    }
+    const int vpc1 = (c1 == nch - 1) ? last_vpc : 2;                // vectors per row in chunk c1
+    const int total = nr * (2 * (c1 - c0) + vpc1);
+    // cursor over the vectors of this lane: chunk c, index ic inside the rows r0.. of the PU's run of that chunk,
+    // off = position in the map (in vectors of 8 entries)
     struct Cursor { int c, ic; size_t off; };
     const size_t chunk_stride = (size_t)2 * pus_level * n_dy;      // vectors of a full chunk, all PUs
-    const size_t pu_run = (size_t)prow * n_dy;                     // this PU's run inside a chunk starts at pu_run * vpc
+    const size_t pu_run = (size_t)prow * n_dy + r0;                // rows before the first streamed row of this PU, per chunk
+    auto run_len = [&](int c) { return nr * ((c == nch - 1) ? last_vpc : 2); };
+    auto run_off = [&](int c) { return (size_t)c * chunk_stride + pu_run * ((c == nch - 1) ? last_vpc : 2); };
     auto advance = [&](Cursor &k, int by) {
       k.ic += by; k.off += by;
-      while (k.c < nch - 1 && k.ic >= L) {
-        k.ic -= L; k.c++;
-        k.off += chunk_stride - L;
-        if (k.c == nch - 1 && last_vpc == 1) k.off -= pu_run;      // a half chunk has one vector per row
+      while (k.c < c1 && k.ic >= run_len(k.c)) {
+        k.ic -= run_len(k.c); k.c++;
+        k.off = run_off(k.c) + k.ic;
       }
     };
-    Cursor ci = { 0, 0, pu_run * (nch == 1 ? last_vpc : 2) }, cc = ci;      // issue / consume
-    advance(ci, lane); advance(cc, lane);
-    int issued = lane;
+    Cursor ci = { c0, 0, run_off(c0) }, cc = ci;                    // issue / consume
+    const int first = lane + G * sub, stride = G * nsub;              // this warp's vectors: first, first + stride, ...
+    advance(ci, first); advance(cc, first);
+    int issued = first;
     auto issue = [&](int slot) {
       if (issued < total) {
         const size_t v = ci.off;
@@ -788,7 +857,7 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
-      issued += G; advance(ci, G);
+      issued += stride; advance(ci, stride);
     };
     for (int t = 0; t < depth; t++) issue(t);
     // Early rejection: the exact cost of a few likely candidates (the window centres and the two AMVP
@@ -815,8 +884,9 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
       for (int o = 16; o > 0; o >>= 1) seed = min(seed, __shfl_xor_sync(0xffffffffu, seed, o));
     }
     uint32_t bound = seed;                          // min(seed, wbest)
+    if (timed) tb2 = gtime_ns();
     int slot = 0;
-    for (int i = lane; i < total; i += G) {
+    for (int i = first; i < total; i += stride) {
       if (wide) asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing / 2 - 1) : "memory");
       else asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing - 1) : "memory");
       uint32_t sad[8];
@@ -833,13 +903,18 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
       const uint32_t smin = min(min(min(sad[0], sad[1]), min(sad[2], sad[3])), min(min(sad[4], sad[5]), min(sad[6], sad[7])));
       if (smin <= bound) {
         const bool half = cc.c == nch - 1 && last_vpc == 1;
-        price(half ? cc.ic : cc.ic >> 1, 2 * cc.c + (half ? 0 : (cc.ic & 1)), sad);
+        price(r0 + (half ? cc.ic : cc.ic >> 1), 2 * cc.c + (half ? 0 : (cc.ic & 1)), sad);
         bound = min(bound, wbest);
       }
-      advance(cc, G);
+      advance(cc, stride);
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (wbest != 0xFFFFFFFFu) best = ((unsigned long long)wbest << 32) | box_key(bc, wpos);
+    if (timed) {
+      const unsigned long long tb3 = gtime_ns();
+      atomicAdd(&g_box_scan_ns[0], tb1 - tb0); atomicAdd(&g_box_scan_ns[1], tb2 - tb1);
+      atomicAdd(&g_box_scan_ns[2], tb3 - tb2); atomicAdd(&g_box_scan_ns[3], 1ull);
+    }
   } else {
   if constexpr (!BOX) {
   for (int wi = 0; wi < nwin; wi++) {
@@ -1036,24 +1111,13 @@ __device__ void scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
   }
   }
   best = warp_min(best);
-
-  // ---- winner of the integer search, parked in the job's result record ----
-  if (lane == 0) {
-    int best_mvx = 0, best_mvy = 0;            // quarter-pel (info->best_mv starts at 0,0)
-    uint32_t best_cost = 0xFFFFFFFFu, best_bits = 0;
-    if (best != ~0ull) {
-      const int wi = (int)((best >> 16) & 0xFFFF), pos = (int)(best & 0xFFFF);
-      best_mvx = (wcx[wi] - R + pos % K) * 4;
-      best_mvy = (wcy[wi] - R + pos / K) * 4;
-      best_cost = (uint32_t)(best >> 32);
-      best_bits = mvd_cost_bits(j, best_mvx >> 2, best_mvy >> 2, 2);
-    }
-    kvz_cuda_me_result r;
-    r.mv[0] = (int16_t)best_mvx; r.mv[1] = (int16_t)best_mvy;
-    r.cost = best_cost; r.bitcost = best_bits;
-    r.merged = 0; r.merge_idx = 0; r.mv_cand_idx = 0; r.took = 0;
-    *out = r;
+  if (part != nullptr) {                       // one of several warps on this job: the caller combines and parks
+    if (lane == 0) *part = best;
+    return true;
   }
+  // ---- winner of the integer search, parked in the job's result record ----
+  if (lane == 0) park_winner(best, f, pu, merge, job, out);
+  return true;
 }
 
 
@@ -1113,9 +1177,22 @@ struct RefineSmem {
   uint32_t cost4[4];
 };
 
-template <int G, int S>
+// Both outcomes of one job's refinement, computed before the *inter_cost of the references in front of it is known
+// (me_pu_kernel refines the references of a PU side by side): what search_pu_inter_ref leaves when the gate
+// `best_cost < *inter_cost` (search_inter.c:1241) lets search_frac run, and when it does not.
+struct RefineBoth {
+  int16_t int_mv[2];            // winner of the integer search
+  uint32_t int_cost, int_bits;  // its SAD-based cost (the gate's left-hand side) and bits
+  uint32_t satd_cost;           // gate closed: SATD at the integer vector + bits * lambda (search_inter.c:1244-1256)
+  int16_t fme_mv[2];            // gate open: search_frac's result
+  uint32_t fme_cost, fme_bits;
+};
+
+// SPEC: compute both outcomes into *both and return; the carry is resolved by refine_finish
+template <int G, int S, bool SPEC = false>
 __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFrame &f, const kvz_cuda_me_pu &pu,
-                           const kvz_cuda_me_job &job, uint32_t &inter_cost, kvz_cuda_me_result *out)
+                           const kvz_cuda_me_job &job, uint32_t &inter_cost, kvz_cuda_me_result *out,
+                           RefineBoth *both = nullptr)
 {
   JobCtx j;
   make_ctx(j, f, pu, sm.merge, job);
@@ -1127,8 +1204,13 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
   int best_mvx = out->mv[0], best_mvy = out->mv[1];
   uint32_t best_cost = out->cost, best_bits = out->bitcost;
 
-  const bool do_fme = f.fme_level > 0 && best_cost < inter_cost;
+  const bool do_fme = f.fme_level > 0 && (SPEC ? best_cost < 0xFFFFFFFFu : best_cost < inter_cost);
   const bool do_satd = !do_fme && best_cost < 0xFFFFFFFFu;
+  if (SPEC && g.tid == 0) {
+    both->int_mv[0] = (int16_t)best_mvx; both->int_mv[1] = (int16_t)best_mvy;
+    both->int_cost = best_cost; both->int_bits = best_bits;
+    both->satd_cost = 0xFFFFFFFFu; both->fme_cost = 0xFFFFFFFFu;
+  }
   if (do_fme || do_satd) {
     // ---- source window round the integer vector: columns -4..w+3(+pad), rows -4..h+4 ----
     // The window origin is clamped into the replicated border: with pad >= w + 20 this reads the same
@@ -1185,6 +1267,7 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
     }
     g.sync();
     const uint32_t satd_int = sm.cost4[0];
+    if (SPEC && g.tid == 0) both->satd_cost = satd_int + best_bits * (uint32_t)j.lambda;
 
     if (do_satd) {
       // search_inter.c:1244-1256
@@ -1333,6 +1416,13 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
       best_cost = fbest_cost; best_bits = fbest_bits;
     }
   }
+  if (SPEC) {
+    if (g.tid == 0 && do_fme) {
+      both->fme_mv[0] = (int16_t)best_mvx; both->fme_mv[1] = (int16_t)best_mvy;
+      both->fme_cost = best_cost; both->fme_bits = best_bits;
+    }
+    return;
+  }
 
   // ---- merge match, AMVP candidate choice, carry of *inter_cost (search_inter.c:1258-1297) ----
   int merged = 0, merge_idx = 0;
@@ -1361,6 +1451,42 @@ __device__ void refine_job(const Group<G> &g, RefineSmem<G, S> &sm, const MeFram
     r.mv_cand_idx = (uint8_t)cu_mv_cand; r.took = took ? 1 : 0;
     *out = r;
   }
+}
+
+// One thread: which of a job's two outcomes the carry selects, then the merge match and the AMVP candidate choice
+// (search_inter.c:1241-1297)
+__device__ void refine_finish(const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                              const kvz_cuda_me_job &job, const RefineBoth &b, uint32_t &inter_cost, kvz_cuda_me_result *out)
+{
+  JobCtx j;
+  make_ctx(j, f, pu, merge, job);
+  int mvx = b.int_mv[0], mvy = b.int_mv[1];
+  uint32_t cost = b.int_cost, bits = b.int_bits;
+  if (f.fme_level > 0 && b.int_cost < inter_cost) { mvx = b.fme_mv[0]; mvy = b.fme_mv[1]; cost = b.fme_cost; bits = b.fme_bits; }
+  else if (b.int_cost < 0xFFFFFFFFu) cost = b.satd_cost;
+  int merged = 0, merge_idx = 0;
+  {
+    const uint32_t q = pack_mv(mvx, mvy);
+    for (merge_idx = 0; merge_idx < pu.num_merge_cand; merge_idx++)
+      if (((j.mvalid >> merge_idx) & 1u) && j.mkey[merge_idx] == q) { merged = 1; break; }
+  }
+  int cu_mv_cand = 0;
+  if (!merged) {
+    const bool same = j.mv_cand[0][0] == j.mv_cand[1][0] && j.mv_cand[0][1] == j.mv_cand[1][1];
+    if (!same) {
+      const uint32_t c0 = mvd_bits(mvx - j.mv_cand[0][0], mvy - j.mv_cand[0][1]);
+      const uint32_t c1 = mvd_bits(mvx - j.mv_cand[1][0], mvy - j.mv_cand[1][1]);
+      cu_mv_cand = c1 < c0 ? 1 : 0;
+    }
+  }
+  const bool took = cost < inter_cost;
+  if (took) inter_cost = cost;
+  kvz_cuda_me_result r;
+  r.mv[0] = (int16_t)mvx; r.mv[1] = (int16_t)mvy;
+  r.cost = cost; r.bitcost = bits;
+  r.merged = (uint8_t)merged; r.merge_idx = (uint8_t)merge_idx;
+  r.mv_cand_idx = (uint8_t)cu_mv_cand; r.took = took ? 1 : 0;
+  *out = r;
 }
 
 template <int G, int S, int T>
@@ -1392,6 +1518,356 @@ me_refine_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__rest
   uint32_t inter_cost = 0x7FFFFFFFu;         // *inter_cost = MAX_INT (search_inter.c:1460)
   for (int q = 0; q < pu.num_jobs; q++)
     refine_job<G, S>(g, sm, f, pu, jobs[pu.first_job + q], inter_cost, results + pu.first_job + q);
+}
+
+
+// ======================================================================================
+// one PU per CTA, one launch: the form an encoder host calls while it walks its CTUs
+// (kvz_cuda_enc_search_pu, enc_session.cu).  Phase 1: the jobs whose windows all lie inside a box map
+// set, one warp each (scan_job<true>).  Phase 2: every other job, by the whole CTA: a window that lies
+// inside a box is read from the maps, any other window is evaluated from a copy of the reference region
+// in shared memory.  Phase 3: the refinement of the PU's jobs in order (refine_job).
+// ======================================================================================
+constexpr int kPuThreads = 512;
+
+// KVZ_CUDA_STATS: nanoseconds (globaltimer) the CTAs of me_pu_kernel spent per phase, by PU size class
+// [size 8/16/32/64][0 box scan, 1 CTA scan, 2 refinement, 3 calls]
+__device__ unsigned long long g_pu_phase_ns[4][4];
+__device__ __forceinline__ unsigned long long gtime()
+{
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+struct CoopSmem {
+  ScanSmemT<false> tab;                       // bit tables and merge overrides of the current window
+  unsigned long long wmin[kPuThreads / 32];
+  alignas(16) uint8_t cur[64 * 64];           // the PU's source rows, w bytes apart
+  alignas(16) uint32_t region[1];             // (2R + h) rows of `pitch_w` words: the reference round the window
+};
+
+__host__ __device__ inline int coop_region_pitch_words(int R, int w) { return (((2 * R + w + 3 + 3) >> 2) + 1) | 1; }
+__host__ __device__ inline size_t coop_smem_bytes(int R)
+{
+  return sizeof(CoopSmem) + (size_t)(2 * R + 64) * coop_region_pitch_words(R, 64) * 4;
+}
+
+// search_mv_full (search_inter.c:886-956) for one job by the whole CTA; the winner is parked in *out like scan_job does
+__device__ void coop_scan_job(CoopSmem &sm, const MeFrame &f, const kvz_cuda_me_pu &pu, const kvz_cuda_merge_cand *merge,
+                              const kvz_cuda_me_job &job, kvz_cuda_me_result *out)
+{
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  JobCtx j;
+  make_ctx(j, f, pu, merge, job);
+  const MeRef &ref = f.refs[job.ref_idx];
+  const int R = f.range, K = 2 * R + 1;
+  const bool free_mv = !(f.owf && f.wpp) && f.mv_constraint == 0;
+  const int fx0 = f.tile_x + j.x, fy0 = f.tile_y + j.y;
+
+  int wcx[7], wcy[7];
+  const int nwin = build_windows(pu, merge, job, wcx, wcy);
+  int level = -1;
+  if (j.w == j.h && (j.w == 8 || j.w == 16 || j.w == 32 || j.w == 64) && (j.x % j.w) == 0 && (j.y % j.h) == 0)
+    level = j.w == 8 ? 0 : j.w == 16 ? 1 : j.w == 32 ? 2 : 3;
+
+  // the PU's source block
+  __syncthreads();
+  for (int i = tid; i < j.h * (j.w >> 2); i += kPuThreads) {
+    const int r = i / (j.w >> 2), c = i - r * (j.w >> 2);
+    reinterpret_cast<uint32_t *>(sm.cur)[i] =
+        *reinterpret_cast<const uint32_t *>(f.cur + (size_t)(fy0 + r) * f.cur_pitch + fx0 + c * 4);
+  }
+
+  unsigned long long best = ~0ull;
+  for (int wi = 0; wi < nwin; wi++) {
+    const int cx = wcx[wi], cy = wcy[wi];
+    // a window wholly covered by earlier ones adds nothing (equal costs lose the tie to the earlier window)
+    bool dup = false;
+    for (int q = 0; q < wi; q++) dup |= wcx[q] == cx && wcy[q] == cy;
+    if (dup) continue;
+    __syncthreads();
+    for (int i = tid; i < K; i += kPuThreads) {
+      const int qx = (cx - R + i) * 4, qy = (cy - R + i) * 4;
+      const uint32_t lam = (uint32_t)j.lambda;
+      sm.tab.bt.gx[i] = make_uint2(lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
+      sm.tab.bt.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
+    }
+    if (tid == 0) {
+      int n = 0;
+#pragma unroll
+      for (int i = 0; i < 5; i++) {
+        if (!((j.mvalid >> i) & 1u)) continue;
+        const int mvx = (int16_t)(j.mkey[i] >> 16), mvy = (int16_t)(j.mkey[i] & 0xFFFFu);
+        if ((mvx & 3) || (mvy & 3)) continue;
+        const int col = (mvx >> 2) - (cx - R), row = (mvy >> 2) - (cy - R);
+        if (col < 0 || col >= K || row < 0 || row >= K) continue;
+        const int pos = row * K + col;
+        bool seen = false;
+        for (int q = 0; q < n; q++) seen |= sm.tab.hit_pos[q] == pos;
+        if (!seen) { sm.tab.hit_pos[n] = pos; sm.tab.hit_bits[n] = i; n++; }
+      }
+      sm.tab.n_hit = n;
+    }
+    // a box map set that holds the whole window?
+    int bi = -1;
+    if (level >= 0) {
+      for (int m = 0; m < ref.n_sets; m++) {
+        const MeMapSet &ms = ref.sets[m];
+        const void *mp = level == 0 ? (const void *)ms.sad8 : level == 1 ? (const void *)ms.sad16
+                       : level == 2 ? (const void *)ms.sad32 : (const void *)ms.sad64;
+        if (ms.n_dx > 0 && mp != nullptr && cx - R >= ms.cx && cx + R < ms.cx + ms.n_dx && cy - R >= ms.cy &&
+            cy + R < ms.cy + ms.n_dy) { bi = m; break; }
+      }
+    }
+    int off = 0, pitch_w = 0;
+    if (bi < 0) {
+      // ---- copy of the reference round the window: rows cy-R .. cy+R+h-1, columns cx-R .. cx+R+w-1 of the PU's
+      // position, every coordinate clamped into the bordered plane (== the per-sample clamp of image.c:320-452);
+      // the copy starts at a 4-byte boundary of the plane, `off` columns to the left ----
+      const int rx0 = fx0 + cx - R + ref.pad, ry0 = fy0 + cy - R + ref.pad;      // plane coordinates, may be outside
+      off = rx0 & 3;
+      const int ax0 = rx0 - off;
+      pitch_w = coop_region_pitch_words(R, j.w);
+      const int rows = 2 * R + j.h, words = (2 * R + j.w + off + 3) >> 2;
+      const int pw = f.width + 2 * ref.pad, ph = f.height + 2 * ref.pad;
+      const bool inside_x = ax0 >= 0 && ax0 + words * 4 <= pw;
+      for (int i = tid; i < rows * words; i += kPuThreads) {
+        const int r = i / words, c = i - r * words;
+        const int py = clampi(ry0 + r, 0, ph - 1);
+        const uint8_t *rowp = ref.plane + (size_t)py * ref.pitch;
+        uint32_t v;
+        if (inside_x) {
+          v = __ldg(reinterpret_cast<const uint32_t *>(rowp + ax0 + c * 4));
+        } else {
+          v = 0;
+#pragma unroll
+          for (int b = 0; b < 4; b++) v |= (uint32_t)rowp[clampi(ax0 + c * 4 + b, 0, pw - 1)] << (8 * b);
+        }
+        sm.region[r * pitch_w + c] = v;
+      }
+    }
+    __syncthreads();
+    WinCtx wc;
+    wc.f = &f; wc.j = &j; wc.sm = &sm.tab; wc.cx = cx; wc.cy = cy; wc.R = R; wc.K = K; wc.n_hit = sm.tab.n_hit; wc.free_mv = free_mv;
+    auto consider = [&](int row, int col, uint32_t sad) {
+      const int mx = cx - R + col, my = cy - R + row;
+      for (int q = 0; q < wi; q++)
+        if (mx >= wcx[q] - R && mx <= wcx[q] + R && my >= wcy[q] - R && my <= wcy[q] + R) return;
+      const uint32_t cost = exact_cost(wc, row, col, sad);
+      if (cost == 0xFFFFFFFFu) return;
+      const unsigned long long key = ((unsigned long long)cost << 32) | (unsigned)((wi << 16) | (row * K + col));
+      best = key < best ? key : best;
+    };
+    if (bi >= 0) {
+      const MeMapSet &ms = ref.sets[bi];
+      const int n = 8 >> level;
+      const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
+      const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
+      const size_t pus_level = (size_t)f.ctus_x * ((f.tile_h + 63) >> 6) * n * n;
+      const int nch = (ms.n_dx + 15) >> 4;
+      const bool half_last = (ms.n_dx & 8) != 0;
+      for (int p = tid; p < K * K; p += kPuThreads) {
+        const int row = p / K, col = p - row * K;
+        const int bx = cx - R + col - ms.cx, by = cy - R + row - ms.cy;      // entry of the box
+        const int c = bx >> 4, wc_ = (c == nch - 1 && half_last) ? 8 : 16;
+        const size_t at = (size_t)16 * c * pus_level * ms.n_dy + (prow * ms.n_dy + by) * wc_ + (bx - 16 * c);
+        const uint32_t sad = level < 2 ? (uint32_t)__ldg((level == 0 ? ms.sad8 : ms.sad16) + at)
+                                       : __ldg((level == 2 ? ms.sad32 : ms.sad64) + at);
+        consider(row, col, sad);
+      }
+    } else {
+      // a unit = 4 neighbouring columns of the copy (one word) in one window row: four candidates that share
+      // every word they read; candidate e of the unit starts e bytes into the word
+      const int qpr = (K + off + 3) >> 2;                       // units per window row
+      const int wpr = j.w >> 2;                                 // words per PU row
+      const uint32_t *cur32 = reinterpret_cast<const uint32_t *>(sm.cur);
+      for (int u = tid; u < K * qpr; u += kPuThreads) {
+        const int row = u / qpr, q = u - row * qpr;
+        uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        for (int y = 0; y < j.h; y++) {
+          const uint32_t *rw = sm.region + (row + y) * pitch_w + q;
+          const uint32_t *cw = cur32 + y * wpr;
+          uint32_t w0 = rw[0];
+          for (int k = 0; k < wpr; k++) {
+            const uint32_t w1 = rw[k + 1], c = cw[k];
+            a0 = sad4(c, w0, a0);
+            a1 = sad4(c, __funnelshift_r(w0, w1, 8), a1);
+            a2 = sad4(c, __funnelshift_r(w0, w1, 16), a2);
+            a3 = sad4(c, __funnelshift_r(w0, w1, 24), a3);
+            w0 = w1;
+          }
+        }
+        const uint32_t acc[4] = { a0, a1, a2, a3 };
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          const int col = q * 4 + e - off;
+          if (col >= 0 && col < K) consider(row, col, acc[e]);
+        }
+      }
+    }
+  }
+  best = warp_min(best);
+  __syncthreads();
+  if (lane == 0) sm.wmin[warp] = best;
+  __syncthreads();
+  if (tid == 0) {
+    for (int q = 1; q < kPuThreads / 32; q++) best = sm.wmin[q] < best ? sm.wmin[q] : best;
+    park_winner(best, f, pu, merge, job, out);
+  }
+}
+
+// a PU and its jobs as kernel arguments: the single-PU call of an encoder host has them in the launch itself
+// instead of behind a pointer the CTA would first have to chase (to mapped host memory: a PCIe round trip each)
+struct PuArgs {
+  kvz_cuda_me_pu pu;
+  kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
+};
+
+template <bool ARGS>
+__global__ void __launch_bounds__(kPuThreads)
+me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs args, const kvz_cuda_me_pu *__restrict__ pus,
+             const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *results, int n_pus, int box_dx, int box_dy,
+             int timing)
+{
+  unsigned long long t0 = 0, t1 = 0, t2 = 0;
+  if (timing && threadIdx.x == 0) t0 = gtime();
+  extern __shared__ __align__(16) unsigned char pu_dyn[];
+  __shared__ kvz_cuda_merge_cand merge[5];
+  __shared__ uint8_t handled[KVZ_CUDA_MAX_REFS];
+  __shared__ unsigned long long part[kPuThreads / 32];
+  // the PU, its jobs and its results live in shared memory while the CTA works: `pus`, `jobs` and `results` may be
+  // mapped HOST memory (kvz_cuda_enc_search_pu), read once and written once
+  __shared__ kvz_cuda_me_pu spu;
+  __shared__ kvz_cuda_me_job sjobs[KVZ_CUDA_MAX_REFS];
+  __shared__ kvz_cuda_me_result sres[KVZ_CUDA_MAX_REFS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (ARGS) {
+    if (threadIdx.x < sizeof(kvz_cuda_me_pu) / 4)
+      reinterpret_cast<uint32_t *>(&spu)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&args.pu)[threadIdx.x];
+    if (threadIdx.x < sizeof(sjobs) / 4)
+      reinterpret_cast<uint32_t *>(sjobs)[threadIdx.x] = reinterpret_cast<const uint32_t *>(args.jobs)[threadIdx.x];
+    if (threadIdx.x < KVZ_CUDA_MAX_REFS) handled[threadIdx.x] = 0;
+    __syncthreads();
+    if (threadIdx.x < 5) merge[threadIdx.x] = spu.merge_cand[threadIdx.x];
+    __syncthreads();
+  } else {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(pus + blockIdx.x);
+    if (threadIdx.x < sizeof(kvz_cuda_me_pu) / 4) reinterpret_cast<uint32_t *>(&spu)[threadIdx.x] = src[threadIdx.x];
+    if (threadIdx.x < KVZ_CUDA_MAX_REFS) handled[threadIdx.x] = 0;
+    __syncthreads();
+    const int nj = min((int)spu.num_jobs, KVZ_CUDA_MAX_REFS);
+    const uint32_t *jsrc = reinterpret_cast<const uint32_t *>(jobs + spu.first_job);
+    if (threadIdx.x < nj * (int)(sizeof(kvz_cuda_me_job) / 4)) reinterpret_cast<uint32_t *>(sjobs)[threadIdx.x] = jsrc[threadIdx.x];
+    if (threadIdx.x < 5) merge[threadIdx.x] = spu.merge_cand[threadIdx.x];
+    __syncthreads();
+  }
+  const kvz_cuda_me_pu &pu = spu;
+  const kvz_cuda_me_job *pj = sjobs;
+  kvz_cuda_me_result *pr = sres;
+  kvz_cuda_me_result *const gres = results + (ARGS ? 0u : spu.first_job);
+
+  // ---- phase 1: integer search ----
+  if (f.ime_search != KVZ_CUDA_IME_FULL) {
+    for (int q = warp; q < pu.num_jobs; q += kPuThreads / 32) heuristic_job(lane, f, pu, merge, pj[q], pr + q);
+  } else {
+    // the warps of the CTA are dealt out to the jobs: 4 warps per job up to 4 jobs, 2 up to 8, else 1
+    const int nsub = pu.num_jobs <= 4 ? 4 : pu.num_jobs <= 8 ? 2 : 1;
+    const int q = warp / nsub, sub = warp - q * nsub;
+    if (box_dx > 0 && q < pu.num_jobs) {
+      unsigned char *base = pu_dyn + warp * box_scan_warp_bytes(box_dx, box_dy);
+      uint4 *ring = reinterpret_cast<uint4 *>(base);
+      uint4 *gxv = ring + kScanRing * 32;
+      const int nv = box_dx / 8;
+      uint2 *gy = reinterpret_cast<uint2 *>(gxv + 4 * nv);
+      uint32_t *rowinfo = reinterpret_cast<uint32_t *>(gy + box_dy);
+      int *hits = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(rowinfo) + (((size_t)box_dy * 4 + 15) & ~(size_t)15));
+      ScanSmemT<true> sm = { ring, gxv, nv, gy, rowinfo, hits, hits + 5, hits[10] };
+      const bool ok = scan_job<true>(lane, sm, f, pu, merge, pj[q], pr + q, false, sub, nsub, &part[warp]);
+      if (lane == 0 && sub == 0 && ok) handled[q] = 1;
+    }
+    __syncthreads();
+    if (box_dx > 0 && q < pu.num_jobs && sub == 0 && lane == 0 && handled[q]) {
+      unsigned long long best = part[warp];
+      for (int k = 1; k < nsub; k++) best = part[warp + k] < best ? part[warp + k] : best;
+      park_winner(best, f, pu, merge, pj[q], pr + q);
+    }
+    // ---- phase 2: the jobs with a window outside every box ----
+    __syncthreads();
+    if (timing && threadIdx.x == 0) t1 = gtime();
+    CoopSmem &cs = *reinterpret_cast<CoopSmem *>(pu_dyn);
+    for (int q = 0; q < pu.num_jobs; q++)
+      if (!handled[q]) coop_scan_job(cs, f, pu, merge, pj[q], pr + q);
+  }
+  __threadfence_block();
+  __syncthreads();
+  if (timing && threadIdx.x == 0) { t2 = gtime(); if (!t1) t1 = t2; }
+
+  // ---- phase 3: refinement.  The references of the PU are refined SIDE BY SIDE, each by its own group of threads,
+  // with both outcomes of the `best_cost < *inter_cost` gate computed (refine_job<SPEC>); thread 0 then walks the
+  // references in order and lets the carry pick (refine_finish).  A 64-wide PU needs the whole CTA per reference. ----
+  __shared__ RefineBoth both[KVZ_CUDA_MAX_REFS];
+  const int msz = max((int)pu.w, (int)pu.h);
+  auto stage_cur = [&](uint8_t *dst, int pitch, int tid, int nthreads) {
+    for (int i = tid; i < pu.h * (pu.w >> 2); i += nthreads) {
+      const int r = i / (pu.w >> 2), c = i % (pu.w >> 2);
+      const uint8_t *src = f.cur + (size_t)(f.tile_y + pu.y + r) * f.cur_pitch + f.tile_x + pu.x + c * 4;
+      *reinterpret_cast<uint32_t *>(&dst[r * pitch + c * 4]) = *reinterpret_cast<const uint32_t *>(src);
+    }
+  };
+  uint32_t dummy = 0;
+  if (msz <= 16) {
+    using SM = RefineSmem<32, 16>;
+    constexpr int kGroups = 8;
+    if (warp < kGroups && warp < pu.num_jobs) {
+      SM &sm = reinterpret_cast<SM *>(pu_dyn)[warp];
+      Group<32> g;
+      g.tid = lane; g.id = warp;
+      stage_cur(sm.cur, SM::kCurPitch, lane, 32);
+      if (lane < 5) sm.merge[lane] = pu.merge_cand[lane];
+      g.sync();
+      for (int q = warp; q < pu.num_jobs; q += kGroups) refine_job<32, 16, true>(g, sm, f, pu, pj[q], dummy, pr + q, &both[q]);
+    }
+  } else if (msz <= 32) {
+    using SM = RefineSmem<128, 32>;
+    constexpr int kGroups = kPuThreads / 128;
+    const int gi = threadIdx.x >> 7;
+    if (gi < pu.num_jobs) {
+      SM &sm = reinterpret_cast<SM *>(pu_dyn)[gi];
+      Group<128> g;
+      g.tid = threadIdx.x & 127; g.id = gi; g.bar = 1 + gi;
+      stage_cur(sm.cur, SM::kCurPitch, g.tid, 128);
+      if (g.tid < 5) sm.merge[g.tid] = pu.merge_cand[g.tid];
+      g.sync();
+      for (int q = gi; q < pu.num_jobs; q += kGroups) refine_job<128, 32, true>(g, sm, f, pu, pj[q], dummy, pr + q, &both[q]);
+    }
+  } else {
+    using SM = RefineSmem<kPuThreads, 64>;
+    SM &sm = *reinterpret_cast<SM *>(pu_dyn);
+    Group<kPuThreads> g;
+    g.tid = threadIdx.x; g.id = 0;
+    stage_cur(sm.cur, SM::kCurPitch, g.tid, kPuThreads);
+    if (g.tid < 5) sm.merge[g.tid] = pu.merge_cand[g.tid];
+    g.sync();
+    for (int q = 0; q < pu.num_jobs; q++) refine_job<kPuThreads, 64, true>(g, sm, f, pu, pj[q], dummy, pr + q, &both[q]);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t inter_cost = 0x7FFFFFFFu;         // *inter_cost = MAX_INT (search_inter.c:1460)
+    for (int q = 0; q < pu.num_jobs; q++) refine_finish(f, pu, merge, pj[q], both[q], inter_cost, pr + q);
+  }
+  __syncthreads();
+  if (threadIdx.x < pu.num_jobs * (int)(sizeof(kvz_cuda_me_result) / 4))
+    reinterpret_cast<uint32_t *>(gres)[threadIdx.x] = reinterpret_cast<const uint32_t *>(sres)[threadIdx.x];
+  __threadfence_system();
+  if (timing && threadIdx.x == 0) {
+    const unsigned long long t3 = gtime();
+    const int m = max((int)pu.w, (int)pu.h), sz = m > 32 ? 3 : m > 16 ? 2 : m > 8 ? 1 : 0;
+    atomicAdd(&g_pu_phase_ns[sz][0], t1 - t0);
+    atomicAdd(&g_pu_phase_ns[sz][1], t2 - t1);
+    atomicAdd(&g_pu_phase_ns[sz][2], t3 - t2);
+    atomicAdd(&g_pu_phase_ns[sz][3], 1ull);
+  }
 }
 
 }  // namespace
@@ -1436,6 +1912,61 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
     count_launch();
     KVZ_CUDA_LAUNCH_CHECK();
   }
+  return 1;
+}
+
+// device time of me_pu_kernel's phases (KVZ_CUDA_STATS): out[size class][box scan ns, CTA scan ns, refinement ns, calls]
+int me_pu_phase_times(unsigned long long out[4][4])
+{
+  KVZ_CUDA_TRY(cudaMemcpyFromSymbol(out, g_pu_phase_ns, sizeof(g_pu_phase_ns)));
+  unsigned long long bs[4];
+  KVZ_CUDA_TRY(cudaMemcpyFromSymbol(bs, g_box_scan_ns, sizeof(bs)));
+  if (bs[3]) fprintf(stderr, "kvz_cuda_enc: box scan per job: tables %.1f us, seed %.1f us, stream %.1f us (%llu jobs)\n",
+                     bs[0] / 1000.0 / bs[3], bs[1] / 1000.0 / bs[3], bs[2] / 1000.0 / bs[3], bs[3]);
+  return 1;
+}
+
+// every PU by one CTA in ONE launch (me_pu_kernel).  host_pu / host_jobs non-null (n_pus == 1): the PU and its jobs
+// travel as kernel arguments and `pus` / `jobs` are not read; results[0..num_jobs) receives the results.
+int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
+                        kvz_cuda_me_result *results, int n_pus, cudaStream_t stream, const kvz_cuda_me_pu *host_pu,
+                        const kvz_cuda_me_job *host_jobs)
+{
+  if (n_pus <= 0) return 1;
+  int box_dx = 0, box_dy = 0;
+  for (int r = 0; r < f.n_refs; r++)
+    for (int m = 0; m < f.refs[r].n_sets; m++) {
+      if (f.refs[r].sets[m].n_dx > box_dx) box_dx = f.refs[r].sets[m].n_dx;
+      if (f.refs[r].sets[m].n_dy > box_dy) box_dy = f.refs[r].sets[m].n_dy;
+    }
+  if (f.ime_search != KVZ_CUDA_IME_FULL) box_dx = box_dy = 0;
+  size_t smem = sizeof(RefineSmem<kPuThreads, 64>);
+  if (8 * sizeof(RefineSmem<32, 16>) > smem) smem = 8 * sizeof(RefineSmem<32, 16>);
+  if ((kPuThreads / 128) * sizeof(RefineSmem<128, 32>) > smem) smem = (kPuThreads / 128) * sizeof(RefineSmem<128, 32>);
+  if (coop_smem_bytes(f.range) > smem) smem = coop_smem_bytes(f.range);
+  if (box_dx > 0 && (kPuThreads / 32) * box_scan_warp_bytes(box_dx, box_dy) > smem) smem = (kPuThreads / 32) * box_scan_warp_bytes(box_dx, box_dy);
+  static size_t opted = 0;                        // opt in once per size (one device per process)
+  if (smem > opted) {
+    KVZ_CUDA_TRY(cudaFuncSetAttribute(me_pu_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    KVZ_CUDA_TRY(cudaFuncSetAttribute(me_pu_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    opted = smem;
+  }
+  static const int timing = getenv("KVZ_CUDA_STATS") != nullptr;
+  static bool timing_set = false;
+  if (timing && !timing_set) { KVZ_CUDA_TRY(cudaMemcpyToSymbol(g_box_scan_timing, &timing, sizeof(int))); timing_set = true; }
+  PuArgs a;
+  if (host_pu != nullptr && host_jobs != nullptr && n_pus == 1) {
+    a.pu = *host_pu;
+    const int nj = host_pu->num_jobs < KVZ_CUDA_MAX_REFS ? host_pu->num_jobs : KVZ_CUDA_MAX_REFS;
+    memcpy(a.jobs, host_jobs, (size_t)nj * sizeof(kvz_cuda_me_job));
+    if (nj < KVZ_CUDA_MAX_REFS) memset(a.jobs + nj, 0, (size_t)(KVZ_CUDA_MAX_REFS - nj) * sizeof(kvz_cuda_me_job));
+    me_pu_kernel<true><<<1, kPuThreads, smem, stream>>>(f, a, nullptr, nullptr, results, 1, box_dx, box_dy, timing);
+  } else {
+    memset(&a, 0, sizeof(a));
+    me_pu_kernel<false><<<n_pus, kPuThreads, smem, stream>>>(f, a, pus, jobs, results, n_pus, box_dx, box_dy, timing);
+  }
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
   return 1;
 }
 

@@ -40,4 +40,12 @@ struct MeFrame {
 int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
                      kvz_cuda_me_result *results, int n_pus, cudaStream_t stream);
 
+// the same, every PU by one CTA in one launch (integer search with any window evaluated from shared memory when no
+// box holds it, then the refinement): the form for one PU at a time
+int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
+                        kvz_cuda_me_result *results, int n_pus, cudaStream_t stream, const kvz_cuda_me_pu *host_pu = nullptr,
+                        const kvz_cuda_me_job *host_jobs = nullptr);
+
+int me_pu_phase_times(unsigned long long out[4][4]);
+
 }  // namespace kvz

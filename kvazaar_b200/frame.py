@@ -259,11 +259,11 @@ class MeSearch:
                 ms.d_sad8, ms.d_sad16, ms.d_sad32, ms.d_sad64 = [x.data_ptr() for x in t]
         self._keep.append((padded_planes, maps))
 
-    def run(self, d_pus, n_pus, d_jobs, d_results):
-        """device tensors (uint8 views of the ME_*_DT arrays)"""
-        capi.check(capi.lib().kvz_cuda_me_search(
-            C.byref(self.frame), C.c_void_p(d_pus.data_ptr()), n_pus, C.c_void_p(d_jobs.data_ptr()),
-            C.c_void_p(d_results.data_ptr()), _stream_ptr()), "kvz_cuda_me_search")
+    def run(self, d_pus, n_pus, d_jobs, d_results, fused=False):
+        """device tensors (uint8 views of the ME_*_DT arrays); fused: kvz_cuda_me_search_fused (one CTA per PU, one launch)"""
+        fn = capi.lib().kvz_cuda_me_search_fused if fused else capi.lib().kvz_cuda_me_search
+        capi.check(fn(C.byref(self.frame), C.c_void_p(d_pus.data_ptr()), n_pus, C.c_void_p(d_jobs.data_ptr()),
+                      C.c_void_p(d_results.data_ptr()), _stream_ptr()), "kvz_cuda_me_search")
         return d_results
 
 

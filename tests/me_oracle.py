@@ -110,10 +110,11 @@ def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sq
     return res
 
 
-def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), box=None, **cfg):
+def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), box=None,
+               fused=False, **cfg):
     """The CUDA path through the C ABI for the same inputs (numpy in, numpy out).
     centres: extra square-window map sets; box: (x0, y0, n_dx, n_dy) of one box map set per reference
-    (jobs whose windows all lie inside it are searched from the box)."""
+    (jobs whose windows all lie inside it are searched from the box); fused: kvz_cuda_me_search_fused (one CTA per PU)."""
     import torch
     import kvazaar_b200 as kb
     from kvazaar_b200.frame import ME_RESULT_DT, MeSearch
@@ -139,7 +140,7 @@ def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_
     d_pus = torch.from_numpy(pus.view(np.uint8).reshape(-1)).cuda()
     d_jobs = torch.from_numpy(jobs.view(np.uint8).reshape(-1)).cuda()
     d_res = torch.zeros(len(jobs) * ME_RESULT_DT.itemsize, dtype=torch.uint8, device="cuda")
-    ms.run(d_pus, len(pus), d_jobs, d_res)
+    ms.run(d_pus, len(pus), d_jobs, d_res, fused=fused)
     torch.cuda.synchronize()
     return d_res.cpu().numpy().view(ME_RESULT_DT)
 
