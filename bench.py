@@ -1,22 +1,29 @@
 #!/usr/bin/env python
-"""bench.py -- the hot path of BASELINE.json config 2 on B200: full-search motion estimation
-of 1920x1080 8-bit frames (--me full32, -r 4: every 8x8/16x16/32x32/64x64 PU of the frame
-against 4 reference pictures, 65x65 integer candidates each).
+"""bench.py -- BASELINE.json's headline metric: 1080p encode frames/s of config 2
+(`--preset medium --me full32 --gop 8 -r 4`, 8-bit, synthetic yuv420p of SURVEY.md 8d) through the encoder's own public
+API (kvz_api: encoder_open / encoder_encode, src/kvazaar.h:545-707), with Kvazaar's inner motion loop on the B200.
 
-One "step" = one frame: for each of the 4 references pad the reference plane, produce the
-dense SAD maps (kvz_cuda_ime_sad_maps) and run the per-PU motion decision
-(kvz_cuda_me_search: exact search_mv_full + search_frac semantics, search_inter.c:886-1128).
+GPU arm (default): kvazaar_b200/host/_build/libkvazaar_cuda.so -- the reference encoder with the CUDA path bound in
+  (kvazaar_b200/host/, KVZ_CUDA_MODE=batch): per frame the source and the new reference picture go to the device, ONE
+  launch produces the dense SAD maps of every PU against every reference, and every search_pu_inter of the host's CTU
+  wavefront is one call of kvz_cuda_enc_search_pu (integer full search + fractional refinement + merge / AMVP choice).
+  The bitstream equals the reference's (tests/test_gpu_encode_parity.py); its md5 is in the JSON line of both arms.
+reference arm (--impl reference): oracle/_ref/libkvazaar_ref.so -- the UNMODIFIED reference, AVX2 strategies, same
+  options, same clip, same frames, all host threads.
 
-  value : ME Gcand/s with the planes already resident in HBM
-  e2e   : the same through the C ABI from HOST buffers (H2D of the current + reference luma
-          planes and D2H of the per-PU results inside the timed region)
-  --impl reference : the reference's own CPU code (oracle/_ref, search_mv_full +
-          search_frac through ref_shim) on all host threads, on a bounded sample of PUs.
+A step = one coded picture.  W warm-up pictures, then exactly K pictures timed (barrier + synchronize on both sides,
+CUDA events, max over ranks).  `e2e` is the plain run: pictures fed from HOST memory, every step copies its source and
+its new reference luma to the device and reads its results back.  `value` is the same run with the source luma of the
+timed pictures preloaded into HBM before the timed region (kvz_cuda_enc_preload_source).  With N > 1 every rank encodes
+its own clip on its own GPU with its share of the host threads (segment-parallel encoding: weak scaling, no data-path
+collective); value = all ranks' pictures / the slowest rank's time.
 
-Prints ONE JSON line (contract in the task statement / DESIGN.md section Measurement).
+The flat ME-stage benchmark of round 1 (Gcand/s over pre-made candidates) is tools/bench_me_stage.py.
+Prints ONE JSON line.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -25,32 +32,22 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "tests")):
+for _p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
 import numpy as np  # noqa: E402
 
-W, H, RANGE, NREFS = 1920, 1080, 32, 4
-PU_COUNTS = {8: 32400, 16: 8040, 32: 1980, 64: 480}       # 42900 PUs
-METRIC = "ME Gcand/s (1080p --me full32 -r 4: integer + fractional motion search, all 2Nx2N PUs 8..64)"
-UNIT = "Gcand/s"
+W, H = 1920, 1080
+OPTIONS = "--preset medium --me full32 --gop 8 -r 4 --owf 0"      # BASELINE configs[1]; --owf pinned
+METRIC = "1080p encode fps (config 2: --preset medium --me full32 --gop 8 -r 4, 8-bit, bit-identical bitstream)"
+UNIT = "frames/s"
+N8 = (W // 8) * (H // 8)                                          # 8x8 blocks per picture
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libkvazaar_ref.so")
 
 
-def cands_per_frame():
-    k = 2 * RANGE + 1
-    return sum(PU_COUNTS.values()) * k * k * NREFS
-
-
-def synth_frames(n, seed=2):
-    import kvzlibs
-    return kvzlibs.synth_luma(seed, W, H, n)
-
-
-# ----------------------------------------------------------------------------------------
-# clocks sampler (nvidia-smi during the timed region)
-# ----------------------------------------------------------------------------------------
 class Clocks:
+    """nvidia-smi sampler (SM clock, throttle reasons) over the timed region"""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -63,8 +60,7 @@ class Clocks:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                  "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
+            threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
@@ -94,108 +90,97 @@ class Clocks:
                     reasons.add(name)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        hi = sorted(sm)[len(sm) // 2:]           # upper half = samples under load
-        return {"sm_mhz": float(np.median(hi)), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "note": "plain median of the samples taken every 100 ms over the timed regions; the GPU idles while the "
+                        "host walks its CTUs, so low samples are idle clocks, not throttling"}
 
 
-# ----------------------------------------------------------------------------------------
-# reference arm: the reference's own CPU code on host threads
-# ----------------------------------------------------------------------------------------
-def reference_step_fn(frames, pus_per_level, threads, fme_level=4):
-    """Returns (fn, cands_per_call, description): fn() runs search_mv_full + search_frac of the
-    compiled reference (oracle/_ref via ref_shim, search_inter.c:886-1128) for a sample of the
-    frame's PUs -- same candidates as the GPU arm (kvazaar_b200.pipeline.frame_pus) -- against
-    NREFS references on `threads` host threads, carrying *inter_cost over each PU's reference
-    loop like search_pu_inter (search_inter.c:1505-1511)."""
-    import kvzlibs
-    from concurrent.futures import ThreadPoolExecutor
-    from kvazaar_b200.pipeline import frame_pus
-    L = kvzlibs.ref(1)
-    cur, refs = frames[NREFS], [frames[NREFS - 1 - i] for i in range(NREFS)]
-    pus, jobs = frame_pus(W, H, NREFS)
-    rs = np.random.default_rng(7)
-    chosen = []
-    for size, n in pus_per_level.items():
-        idx = np.nonzero(pus["w"] == size)[0]
-        chosen.extend(rs.choice(idx, n, replace=False).tolist())
-    work = []
-    for pi in chosen:
-        pu = pus[pi]
-        per_ref = []
-        for q in range(NREFS):
-            jb = jobs[int(pu["first_job"]) + q]
-            merge = [(int(m["dir"]), int(m["ref"][0]), int(m["ref"][1]), int(m["mv"][0][0]), int(m["mv"][0][1]),
-                      int(m["mv"][1][0]), int(m["mv"][1][1])) for m in pu["merge_cand"][:int(pu["num_merge_cand"])]]
-            _, rj = kvzlibs.job_pair(
-                width=W, height=H, origin_x=int(pu["x"]), origin_y=int(pu["y"]), pu_w=int(pu["w"]), pu_h=int(pu["h"]),
-                tile_off_x=0, tile_off_y=0, ref_idx=int(jb["ref_idx"]), lambda_sqrt=LAMBDA_SQRT,
-                mv_cand=jb["mv_cand"].tolist(), merge=merge, extra_mv=tuple(int(v) for v in jb["extra_mv"]),
-                owf=0, wpp=0, sao_type=3, deblock_enable=1, mv_constraint=0, max_ref_lcu_right=1,
-                max_ref_lcu_down=1, fme_level=fme_level, me_early_termination=0, me_max_steps=-1,
-                ime_algorithm=5)
-            rj.pic_y, rj.ref_y = cur.ctypes.data, refs[q].ctypes.data
-            per_ref.append(rj)
-        work.append(per_ref)
-    k = 2 * RANGE + 1
-
-    def one(per_ref):
-        inter_cost = 0x7FFFFFFF
-        for j in per_ref:
-            L.ref_shim_ime(C.byref(j))
-            if fme_level > 0 and j.best_cost < inter_cost:
-                L.ref_shim_fme(C.byref(j))
-            elif j.best_cost < 0xFFFFFFFF:
-                L.ref_shim_int_satd(C.byref(j))
-            if j.best_cost < inter_cost:
-                inter_cost = j.best_cost
-
-    pool = ThreadPoolExecutor(threads)
-
-    def fn():
-        list(pool.map(one, work))
-    desc = f"{sum(pus_per_level.values())} PUs ({pus_per_level}) x {NREFS} refs of one 1080p frame"
-    return fn, len(work) * NREFS * k * k, desc
+def make_frames(n, seed):
+    import make_clip
+    return list(make_clip.clip_planes(seed, W, H, n))
 
 
-# bounded CPU sample: 1/6 of the frame's PUs at every size (same mix as the full frame)
-REF_SAMPLE = {8: 5400, 16: 1340, 32: 330, 64: 80}
-LAMBDA_SQRT = 27.0     # sqrt(lambda) of a QP-32-class frame; cost = bits * (int)(lambda_sqrt + .5)
+class Run:
+    """Feeds a clip to one encoder and times the pictures [warmup, warmup + steps) as they come out."""
+
+    def __init__(self, lib, frames, threads, warmup, steps):
+        from kvazaar_b200 import encoder
+        opts = encoder.options_from_cli(OPTIONS)
+        opts["threads"] = str(threads)
+        self.enc = encoder.Encoder(lib, W, H, opts)
+        self.frames, self.warmup, self.steps = frames, warmup, steps
+        self.fed, self.out = 0, 0
+        self.md5 = hashlib.md5()
+        self.bits = []
+
+    def one_call(self):
+        pic = None
+        if self.fed < len(self.frames):
+            pic = self.enc.picture(*self.frames[self.fed])
+            self.fed += 1
+        data, info = self.enc.encode(pic)
+        if data is not None:
+            self.md5.update(data)
+            self.bits.append(len(data) * 8)
+            self.out += 1
+        elif pic is None:
+            raise RuntimeError("encoder ran dry before the timed pictures were out")
+        return data is not None
+
+    def until(self, n_out):
+        while self.out < n_out:
+            self.one_call()
+
+    def close(self):
+        self.enc.close()
 
 
 def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """the unmodified reference on the host cores: same options, clip and pictures; rank 0 only"""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
     threads = os.cpu_count() or 1
-    frames = synth_frames(NREFS + 1)
-    pus = REF_SAMPLE
-    fn, cands, sample = reference_step_fn(frames, pus, threads)
-    for _ in range(max(1, min(args.warmup, 1))):
-        fn()
+    steps, warmup = args.steps, args.warmup
+    frames = make_frames(warmup + steps + 9, seed=2)
+    r = Run(REF_LIB, frames, threads, warmup, steps)
+    r.until(warmup)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        fn()
-    dt = (time.perf_counter() - t0) / args.steps
-    v = cands / dt / 1e9
+    r.until(warmup + steps)
+    dt = time.perf_counter() - t0
+    md5 = r.md5.hexdigest()
+    r.close()
+    v = steps / dt
+    sample = f"pictures {warmup}..{warmup + steps - 1} in coding order of the 1080p clip (seed 2), {dt:.1f} s"
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage",
-                   "sample": sample},
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": dt * 1e3 / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"1920x1080 8-bit yuv420p, {OPTIONS} --threads {threads} (BASELINE configs[1])",
+                   "api": "kvz_api of oracle/_ref/libkvazaar_ref.so: the unmodified reference, AVX2 strategies",
+                   "bitstream_md5": md5, "md5_covers": f"the first {warmup + steps} pictures in coding order"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
-# ----------------------------------------------------------------------------------------
-# our arm
-# ----------------------------------------------------------------------------------------
+def cpu_baseline_sample(pictures=4, warmup=1):
+    """the reference arm of this file in a child process on a bounded sample (rank 0, N = 1)"""
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", str(pictures),
+                        "--warmup", str(warmup)], capture_output=True, text=True, timeout=1200, cwd=ROOT)
+    for ln in r.stdout.splitlines():
+        if ln.startswith("{"):
+            d = json.loads(ln)
+            cb = d["cpu_baseline"]
+            cb["sample"] += " (the first pictures of a GOP have 1-3 references: cheaper than steady state)"
+            cb["bitstream_md5"] = d["config"]["bitstream_md5"]
+            return cb
+    return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "sample": "failed: " + r.stderr[-300:]}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    import kvazaar_b200 as kb
+    from kvazaar_b200 import capi, encoder
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -205,180 +190,126 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    kb.init(local)
-
-    # every rank searches its own frames (same-temporal-layer frames of the GOP-8 pyramid are
-    # independent): weak scaling, no data-path collective inside the ME stage
-    frames = synth_frames(NREFS + 1, seed=2 + rank)
-    pipe = kb.MePipeline(W, H, RANGE, NREFS, lambda_sqrt=LAMBDA_SQRT, fme_level=4, use_boxes=not args.separate_windows)
-    host_cur = torch.from_numpy(frames[NREFS]).pin_memory()
-    host_refs = [torch.from_numpy(frames[NREFS - 1 - i]).pin_memory() for i in range(NREFS)]
-    pipe.upload(host_cur, host_refs)
+    os.environ["KVZ_CUDA_MODE"] = "batch"
+    os.environ["KVZ_CUDA_DEVICE"] = str(local)
+    threads = max(2, (os.cpu_count() or 2) // world)          # the ranks of one box share its host cores
+    steps, warmup = args.steps, args.warmup
+    if warmup < 2:
+        raise SystemExit("bench.py: --warmup must be at least 2 (the first picture is intra: the session opens on the second)")
+    frames = make_frames(warmup + steps + 9, seed=2 + rank)
+    L = capi.lib()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed_run(preload):
+        """one full encode of the clip; returns (ms of the timed pictures, per-run record)"""
+        r = Run(encoder.CUDA_LIB, frames, threads, warmup, steps)
+        glue = r.enc.lib
+        glue.kvz_glue_preload_source.argtypes = [C.c_int64, C.c_void_p, C.c_int]
+        r.until(warmup)
+        if preload:                                    # the source luma of every picture still to be fed, resident in HBM
+            for i in range(r.fed, len(frames)):
+                y = frames[i][0]
+                if not glue.kvz_glue_preload_source(i, y.ctypes.data_as(C.c_void_p), y.strides[0]):
+                    raise SystemExit("bench.py: kvz_glue_preload_source failed")
+        m0, s0 = (C.c_ulonglong * 8)(), (C.c_ulonglong * 8)()
+        glue.kvz_glue_enc_measurements(m0)
+        glue.kvz_glue_enc_stats(s0)
+        l0 = int(L.kvz_cuda_launch_count())
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(steps):
-            fn()
+        t0 = time.perf_counter()
+        r.until(warmup + steps)
         e1.record()
+        host_ms = (time.perf_counter() - t0) * 1e3
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
-
-    from kvazaar_b200 import shard
-    counter = [0]
-
-    def exchange():
-        # the one exchange step of the sharded pipeline: the rank that reconstructed the
-        # newest reference publishes its luma plane to all ranks over NCCL/NVLink
-        if world > 1:
-            shard.publish_reference(pipe.refs[0], src=counter[0] % world)
-            counter[0] += 1
-
-    def step_resident():
-        exchange()
-        pipe.step_resident()
-
-    def step_e2e():
-        exchange()
-        pipe.step_from_host(host_cur, host_refs)
+        m1 = (C.c_ulonglong * 8)()
+        glue.kvz_glue_enc_measurements(m1)
+        s1 = (C.c_ulonglong * 8)()
+        glue.kvz_glue_enc_stats(s1)
+        rec = {"ms": float(ms.item()), "host_ms": host_ms, "launches": int(L.kvz_cuda_launch_count()) - l0,
+               "m": [int(b) - int(a) for a, b in zip(m0, m1)], "pu_searches": int(s1[1]) - int(s0[1]),
+               "ref_jobs": int(s1[5]) - int(s0[5]), "jobs_outside_box": int(s1[6]) - int(s0[6]),
+               "map_mib_last": int(s1[3]) / 2 ** 20, "md5": r.md5.hexdigest()}
+        r.close()
+        return rec
 
     clocks = Clocks(local)
     if rank == 0:
         clocks.start()
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
-    l0 = kb.launch_count()
-    ms = timed(step_resident, args.steps)
-    launches = kb.launch_count() - l0
-
-    # e2e through the C ABI from host buffers: every step uploads its inputs (H2D stream) and downloads its
-    # results (D2H stream); consecutive steps overlap their copies with each other's kernels
-    def step_e2e_pipelined():
-        exchange()
-        pipe.step_from_host_pipelined(host_cur, host_refs)
-
-    for _ in range(2):
-        step_e2e()
-    ms_e2e_serial = timed(step_e2e, args.steps)
-    for _ in range(2):
-        step_e2e_pipelined()
-    pipe.flush_pipelined()
-
-    def run_pipelined():
-        step_e2e_pipelined()
-
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        run_pipelined()
-    pipe.flush_pipelined()                   # the last step's results are on the host
-    torch.cuda.current_stream().wait_stream(pipe._d2h)
-    e1.record()
-    barrier()
-    ms_t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
-    ms_e2e = float(ms_t.item())
-    if world > 1:
-        pipe.upload(host_cur, host_refs)      # restore this rank's own reference 0 for the kernel timings
-
-    # per-kernel times, each kernel alone with events on the launching stream
-    sad_ms = pipe.time_sad_kernel(iters=max(5, args.steps))
-    search_ms = pipe.time_me_search(iters=max(3, args.steps // 2))
-    # keep the same load up for >= 1.5 s so that nvidia-smi (100 ms period) sees it
-    t_end = time.perf_counter() + 1.5
-    while time.perf_counter() < t_end:
-        pipe.step_resident()
-        torch.cuda.synchronize()
+    e2e = timed_run(preload=False)                     # the plain run: everything from host memory
+    res = timed_run(preload=True)                      # source luma of the timed pictures resident before the timed region
     clk = clocks.stop() if rank == 0 else None
-    if clk is not None:
-        clk["note"] = "sampled every 100 ms from warm-up to the end of 1.5 s of identical untimed steps"
-
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    cands = cands_per_frame() * world
-    value = cands / (ms / args.steps * 1e-3) / 1e9
-    e2e = cands / (ms_e2e / args.steps * 1e-3) / 1e9
-    peaks = {}
+
+    fps = world * steps / (res["ms"] / 1e3)
+    fps_e2e = world * steps / (e2e["ms"] / 1e3)
+    m = e2e["m"]
+    peak = capi.measure_int_pipe_peak()
+    dense_ms = m[4] / 1e6 / max(1, m[3])
+    achieved = (m[5] / max(1, m[3])) / (dense_ms / 1e3) / 1e12 if m[3] else 0.0
+    hbm_peak = None
     try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
         pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    int_peak = kb.measure_int_pipe_peak()
-    abs_diffs = pipe.algorithmic_abs_diffs            # of all SAD launches of one step
-    map_bytes = pipe.algorithmic_map_bytes + NREFS * 2 * W * H
-    n_sad = pipe.n_sad_launches
-    achieved_ops = abs_diffs / (sad_ms * 1e-3)
-    step_ms = ms / args.steps
-    kernel = "ime_sad_multi_kernel (boxes of all references, one launch)" if pipe.use_boxes else "ime_sad_dense_kernel<32>"
-    traffic = pipe.NCU_TRAFFIC_BYTES if (pipe.use_boxes and world >= 1) else None    # captured for the default (box) launches
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "1920x1080 8-bit, --me full32 -r 4 (BASELINE configs[1]), ME stage: "
-                               "pad + dense SAD maps + per-PU decision (search_mv_full) + fractional "
-                               "refinement (search_frac), 42900 PUs x 4 refs per step",
-                   "candidates": "value counts the nominal window only, %d = PUs x 4225 x refs per step, for both arms; "
-                                 "search_mv_full also visits the extra_mv / merge-candidate windows (%d windows of 4225 "
-                                 "per PU here), which the reference arm re-evaluates where they overlap while the device "
-                                 "evaluates each distinct displacement of a PU once (%d SADs per step), with "
-                                 "bit-identical decisions"
-                                 % (cands_per_frame(), sum(len(c) for c in pipe.centres),
-                                    sum(pipe.union_area) * (32400 + 8040 + 1980 + 480)),
-                   "frames_per_s": 1e3 / step_ms * world,
-                   "l2": "per step %.0f MB of SAD maps are written and read back: larger than the 126 MB L2, "
-                         "no flush needed" % (pipe.map_bytes / 1e6),
-                   "stages": pipe.stages + (["publish_reference (NCCL broadcast of one luma plane) x1"] if world > 1 else []),
-                   "parallelism": "frames of one temporal layer per GPU (weak scaling), no data-path collective in ME",
-                   "kernel_ms": {"ime_sad x%d" % n_sad: sad_ms, "me_search (scan + refine x2)": search_ms,
-                                 "share_sad": sad_ms / step_ms, "share_me_search": search_ms / step_ms}},
+        "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": res["ms"] / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic", "gpu_launches": e2e["launches"],
+        "config": {
+            "workload": f"1920x1080 8-bit yuv420p, {OPTIONS} --threads {threads} (BASELINE configs[1]); a step = one coded picture",
+            "api": "kvz_api (encoder_open / encoder_encode) of kvazaar_b200/host/_build/libkvazaar_cuda.so, KVZ_CUDA_MODE=batch",
+            "bitstream_md5": e2e["md5"], "md5_covers": f"the first {warmup + steps} pictures in coding order of rank 0's clip (seed 2); "
+                                                       "equal to the reference arm's = bit-identical",
+            "bitstream_md5_preloaded_run": res["md5"],
+            "host_threads_per_rank": threads,
+            "value_vs_e2e": "value: source luma of the timed pictures preloaded into HBM (kvz_cuda_enc_preload_source); "
+                            "e2e: every picture from host memory. Reconstructed reference pictures come from the host's own "
+                            "in-loop filters in both runs.",
+            "pu_searches_per_step": e2e["pu_searches"] / steps,
+            "reference_jobs_per_step": e2e["ref_jobs"] / steps,
+            "share_of_jobs_with_a_window_outside_the_box": e2e["jobs_outside_box"] / max(1, e2e["ref_jobs"]),
+            "sad_maps_mib_last_picture": e2e["map_mib_last"],
+            "l2": "the SAD maps of one picture (several GB) exceed the 126 MB L2; no flush needed",
+            "parallelism": "one encoder and one clip per rank (segment-parallel encoding), ranks share the host's cores; "
+                           "no data-path collective",
+            "device_stages_per_step": ["upload source + new reference luma, pad_plane", "ime_sad_multi_kernel x1 (dense SAD maps, all references)",
+                                       "me_pu_kernel x (PU searches of the picture): box scan | CTA window scan, refinement"],
+        },
+        "roofline": {
+            "kernel": "ime_sad_multi_kernel (dense SAD maps of one picture against all its references, one launch)",
+            "bound": "int_pipe", "achieved": achieved, "peak": peak / 1e12, "unit": "Tabsdiff/s",
+            "frac": achieved / (peak / 1e12) if peak else None,
+            "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",
+            "launches": m[3], "ms_per_launch": dense_ms,
+            "algorithmic_abs_diffs_per_launch": m[5] / max(1, m[3]),
+            "map_bytes_per_launch": m[6] / max(1, m[3]),
+            "hbm_frac_of_map_writes": (m[6] / max(1, m[3])) / (dense_ms / 1e3) / 1e9 / hbm_peak if (hbm_peak and m[3]) else None,
+            "traffic": None,
+            "traffic_note": "no ncu capture of this launch inside the bench; see profiles/ for the round's captures",
+            "share_of_step_ms": dense_ms / (e2e["ms"] / steps),
+        },
         "clocks": clk,
-        "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-                "mode": "host buffers through the C ABI; each step copies all its inputs H2D and all its results D2H, "
-                        "the copies of neighbouring steps overlap the kernels (two buffer sets, H2D / D2H streams)",
-                "serial_ms_per_step": ms_e2e_serial / args.steps},
-        "gpu_launches": int(launches),
-        # the dense SAD kernel is bound by the integer (ALU) pipe; the denominator is
-        # measured in this run by a register-only VABSDIFF4 loop (MEASURED_PEAKS.json has no integer figure).
-        # achieved = the absolute differences the step's %d launches must evaluate / their summed duration.
-        "roofline": {"kernel": kernel, "bound": "int_pipe",
-                     "achieved": achieved_ops / 1e12, "peak": int_peak / 1e12, "unit": "Tabsdiff/s",
-                     "frac": achieved_ops / int_peak,
-                     "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",
-                     "algorithmic_abs_diffs": abs_diffs, "launches": n_sad, "ms_per_launch": sad_ms / n_sad,
-                     "traffic": traffic},
-        "roofline_hbm": {"kernel": kernel, "bound": "hbm",
-                         "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "traffic": traffic, "algorithmic_bytes": map_bytes},
+        "e2e": {"value": fps_e2e, "unit": UNIT, "ms_per_step": e2e["ms"] / steps, "host_ms_per_step": e2e["host_ms"] / steps,
+                "h2d_bytes_per_step": (m[0] + m[1]) / steps, "d2h_bytes_per_step": m[2] / steps,
+                "mode": "pictures fed from host memory through kvz_api; per step: source luma + the new reference luma copied to "
+                        "the device, PU / job records sent with each launch, results read back through mapped host memory"},
     }
-    # bounded CPU baseline on the same host, rank 0, N=1 only
     if world == 1 and not args.no_cpu_baseline:
-        threads = os.cpu_count() or 1
-        fn, c, sample = reference_step_fn(frames, REF_SAMPLE, threads)
-        t0 = time.perf_counter()
-        fn()
-        dt = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": c / dt / 1e9, "unit": UNIT, "cores": threads, "kind": "reference",
-                               "sample": sample + f", {dt:.1f} s"}
+        out["cpu_baseline"] = cpu_baseline_sample()
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -387,15 +318,13 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--separate-windows", action="store_true",
-                    help="one square-window SAD map set per window centre instead of one box per reference")
     args = ap.parse_args()
-    # stdout carries exactly ONE JSON line: whatever libraries write to file descriptor 1 while the bench runs (NCCL's
-    # version banner, for one) goes to stderr instead; the result line is written to the real stdout at the end
+    # stdout carries exactly ONE JSON line: whatever libraries write to file descriptor 1 while the bench runs goes to
+    # stderr instead; the result line is written to the real stdout at the end
     sys.stdout.flush()
     real_stdout = os.dup(1)
     os.dup2(2, 1)
@@ -403,7 +332,7 @@ def main():
     global print
     builtin_print = print
 
-    def print(*a, **k):                      # noqa: A001 -- the two result prints of this file
+    def print(*a, **k):                      # noqa: A001 -- the result print of this file
         lines.append(" ".join(str(x) for x in a))
 
     try:

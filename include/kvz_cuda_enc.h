@@ -56,6 +56,7 @@ typedef struct kvz_cuda_enc_frame {
   const void *src_luma;         /* source luma of the WHOLE picture in host memory (frame->source->base_image->y) */
   int32_t src_stride;
   uint64_t src_key;             /* identity of the source picture: tiles of one frame share one upload */
+  int64_t src_pts;              /* frame->source->pts: a picture preloaded under this number is used without an upload */
   int32_t tile_x, tile_y, tile_w, tile_h;   /* state->tile->offset_x / y, state->tile->frame->width / height */
   uint8_t ref_LX[2][16];        /* state->frame->ref_LX */
   int32_t n_refs;               /* state->frame->ref->used_size */
@@ -79,11 +80,24 @@ KVZ_CUDA_API int kvz_cuda_enc_search_pu(kvz_cuda_enc *enc, int frame_handle, int
                                         const kvz_cuda_me_pu *pu, const kvz_cuda_me_job *jobs,
                                         kvz_cuda_me_result *results);
 
+/* Optional: put the source luma of the picture with presentation number `pts` into device memory ahead of time
+ * (a host whose input is already on the device, or a benchmark that wants its inputs resident before the timed
+ * region).  kvz_cuda_enc_frame_begin then uses it instead of uploading; it is dropped when its frame has begun.
+ * Replaces nothing in the reference. */
+KVZ_CUDA_API int kvz_cuda_enc_preload_source(kvz_cuda_enc *enc, int64_t pts, const void *luma, int32_t stride);
+
 /* counters since open: stats[0] frames begun, [1] PU searches, [2] reference planes uploaded, [3] bytes of SAD maps
  * of the last frame, [4] map displacements of the last frame (sum over references of n_dx * n_dy),
  * [5] reference-jobs searched, [6] jobs not served entirely from a box (some window evaluated on demand: host-side
  * estimate from the candidate list) */
 KVZ_CUDA_API void kvz_cuda_enc_stats(const kvz_cuda_enc *enc, unsigned long long stats[8]);
+
+/* measurement counters since open (bench.py): m[0] bytes copied host -> device (planes), m[1] bytes of PU / job
+ * arguments sent with the launches, m[2] bytes of results read back, m[3] dense SAD launches (ime_sad_multi_kernel)
+ * whose duration is known, m[4] their summed duration in nanoseconds (CUDA events on the launching stream),
+ * m[5] the pixel absolute differences those launches had to evaluate (8x8 level: 64 per 8x8 block and displacement,
+ * SURVEY.md 8d), m[6] bytes of SAD maps they wrote, m[7] source planes taken from a preload */
+KVZ_CUDA_API void kvz_cuda_enc_measurements(kvz_cuda_enc *enc, unsigned long long m[8]);
 
 #ifdef __cplusplus
 }

@@ -35,6 +35,12 @@ struct PlaneSlot {
 struct CurPlane {
   uint64_t key = 0, frame_num = ~0ull;
   uint8_t *d = nullptr;
+  bool preloaded = false;             // d belongs to a Preload record (kvz_cuda_enc_preload_source), not to this slot
+};
+
+struct Preload {
+  int64_t pts;
+  uint8_t *d;
 };
 
 struct FrameCtx {
@@ -43,6 +49,9 @@ struct FrameCtx {
   uint8_t *maps = nullptr;
   size_t map_bytes = 0;               // allocated
   cudaEvent_t ready = nullptr;
+  cudaEvent_t dense0 = nullptr, dense1 = nullptr;    // round the dense SAD launch of this frame
+  bool dense_pending = false;
+  unsigned long long dense_absdiffs = 0, dense_map_bytes = 0;
   std::atomic<int> inflight{0};
   int box[KVZ_CUDA_MAX_REFS][4];      // x0, y0, n_dx, n_dy per reference
 };
@@ -77,7 +86,10 @@ struct kvz_cuda_enc {
   CurPlane cur[4];
   int cur_next = 0;
   std::vector<FrameCtx *> ctxs;
+  std::vector<Preload> preloads;
+  std::vector<uint8_t *> spare_planes;                 // source planes handed back by consumed preloads
   std::atomic<unsigned long long> stats[8];
+  std::atomic<unsigned long long> meas[8];
   // KVZ_CUDA_STATS: wall time of kvz_cuda_enc_search_pu by PU size (8, 16, 32, 64) and by whether every window of
   // every job lay inside its reference's box
   bool timing = false;
@@ -155,6 +167,20 @@ bool job_in_box(const FrameCtx &c, int R, const kvz_cuda_me_pu &pu, const kvz_cu
   return lox - R >= b[0] && hix + R < b[0] + b[2] && loy - R >= b[1] && hiy + R < b[1] + b[3];
 }
 
+// the duration of a context's dense SAD launch, once it has finished (CUDA events on the launching stream)
+void harvest_dense(kvz_cuda_enc *e, FrameCtx *c, bool wait)
+{
+  if (!c->dense_pending) return;
+  if (wait) cudaEventSynchronize(c->dense1);
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, c->dense0, c->dense1) != cudaSuccess) { cudaGetLastError(); return; }
+  c->dense_pending = false;
+  e->meas[3]++;
+  e->meas[4] += (unsigned long long)((double)ms * 1e6);
+  e->meas[5] += c->dense_absdiffs;
+  e->meas[6] += c->dense_map_bytes;
+}
+
 bool worker_ready(kvz_cuda_enc *e)
 {
   Worker &w = t_worker;
@@ -189,6 +215,7 @@ kvz_cuda_enc *kvz_cuda_enc_open(const kvz_cuda_enc_cfg *cfg)
   e->cfg = *cfg;
   if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 32768;
   for (auto &s : e->stats) s = 0;
+  for (auto &s : e->meas) s = 0;
   for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) { e->t_ns[a][b] = 0; e->t_calls[a][b] = 0; }
   e->timing = getenv("KVZ_CUDA_STATS") != nullptr;
   e->pitch = (cfg->width + 2 * kPad + 63) & ~63;
@@ -208,10 +235,14 @@ void kvz_cuda_enc_close(kvz_cuda_enc *e)
   cudaSetDevice(e->cfg.device);
   cudaDeviceSynchronize();
   for (auto &s : e->slots) if (s.d) cudaFree(s.d);
-  for (auto &c : e->cur) if (c.d) cudaFree(c.d);
+  for (auto &c : e->cur) if (c.d && !c.preloaded) cudaFree(c.d);
+  for (auto &p : e->preloads) cudaFree(p.d);
+  for (auto *p : e->spare_planes) cudaFree(p);
   for (FrameCtx *c : e->ctxs) {
     if (c->maps) cudaFree(c->maps);
     if (c->ready) cudaEventDestroy(c->ready);
+    if (c->dense0) cudaEventDestroy(c->dense0);
+    if (c->dense1) cudaEventDestroy(c->dense1);
     delete c;
   }
   if (e->d_tmp) cudaFree(e->d_tmp);
@@ -241,12 +272,26 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   if (!cur) {
     cur = &e->cur[e->cur_next];
     e->cur_next = (e->cur_next + 1) & 3;
-    if (!cur->d && cudaMalloc(&cur->d, (size_t)cfg.width * cfg.height) != cudaSuccess) {
-      fail("cudaMalloc(source plane)", cudaGetLastError(), __FILE__, __LINE__); return -1;
-    }
+    if (cur->preloaded) { e->spare_planes.push_back(cur->d); cur->d = nullptr; cur->preloaded = false; }
     cur->key = fr->src_key; cur->frame_num = frame_num;
-    if (cudaMemcpy2DAsync(cur->d, cfg.width, fr->src_luma, fr->src_stride, cfg.width, cfg.height, cudaMemcpyHostToDevice,
-                          e->stream) != cudaSuccess) { fail("upload of the source plane", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+    bool found = false;
+    for (size_t i = 0; i < e->preloads.size(); i++) {
+      if (e->preloads[i].pts != fr->src_pts) continue;
+      if (cur->d) e->spare_planes.push_back(cur->d);
+      cur->d = e->preloads[i].d; cur->preloaded = true;
+      e->preloads.erase(e->preloads.begin() + i);
+      e->meas[7]++;
+      found = true;
+      break;
+    }
+    if (!found) {
+      if (!cur->d && cudaMalloc(&cur->d, (size_t)cfg.width * cfg.height) != cudaSuccess) {
+        fail("cudaMalloc(source plane)", cudaGetLastError(), __FILE__, __LINE__); return -1;
+      }
+      if (cudaMemcpy2DAsync(cur->d, cfg.width, fr->src_luma, fr->src_stride, cfg.width, cfg.height, cudaMemcpyHostToDevice,
+                            e->stream) != cudaSuccess) { fail("upload of the source plane", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+      e->meas[0] += (unsigned long long)cfg.width * cfg.height;
+    }
   }
 
   // ---- reference planes: drop what the DPB dropped, upload and border what is new ----
@@ -273,6 +318,7 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
       if (!launch_pad_plane(e->d_tmp, cfg.width, cfg.height, cfg.width, s->d, kPad, e->pitch, 8, e->stream)) return -1;
       s->key = rr.key; s->poc = rr.poc; s->live = true;
       e->stats[2]++;
+      e->meas[0] += (unsigned long long)cfg.width * cfg.height;
     }
     ref_slot[r] = s;
   }
@@ -286,13 +332,15 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   }
   if (!ctx) {
     ctx = new FrameCtx();
-    if (cudaEventCreateWithFlags(&ctx->ready, cudaEventDisableTiming) != cudaSuccess) {
+    if (cudaEventCreateWithFlags(&ctx->ready, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreate(&ctx->dense0) != cudaSuccess || cudaEventCreate(&ctx->dense1) != cudaSuccess) {
       fail("cudaEventCreate", cudaGetLastError(), __FILE__, __LINE__); delete ctx; return -1;
     }
     e->ctxs.push_back(ctx);
     handle = (int)e->ctxs.size() - 1;
   }
   ctx->id = ~0ull;                                     // not findable until it is complete
+  harvest_dense(e, ctx, true);
 
   // ---- boxes, within the map budget ----
   const bool full = cfg.ime_search == KVZ_CUDA_IME_FULL;
@@ -360,10 +408,15 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
     disp += (unsigned long long)b[2] * b[3];
   }
   if (full) {
+    cudaEventRecord(ctx->dense0, e->stream);
     for (int r0 = 0; r0 < fr->n_refs; r0 += kImeMaxMulti) {
       const int n = std::min(kImeMaxMulti, fr->n_refs - r0);
       if (!launch_ime_sad_box_multi(ps + r0, ctx->box + r0, n, e->stream)) return -1;
     }
+    cudaEventRecord(ctx->dense1, e->stream);
+    ctx->dense_pending = true;
+    ctx->dense_absdiffs = level_entries(fr->tile_w, fr->tile_h, 0) * 64ull * disp;
+    ctx->dense_map_bytes = need;
   }
   if (cudaEventRecord(ctx->ready, e->stream) != cudaSuccess) { fail("cudaEventRecord", cudaGetLastError(), __FILE__, __LINE__); return -1; }
   e->stats[0]++;
@@ -416,6 +469,8 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
   memcpy(results, w.h + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result));
   e->stats[1]++;
   e->stats[5] += (unsigned long long)nj;
+  e->meas[1] += sizeof(kvz_cuda_me_pu) + (unsigned long long)nj * sizeof(kvz_cuda_me_job);
+  e->meas[2] += (unsigned long long)nj * sizeof(kvz_cuda_me_result);
   if (e->timing) {
     struct timespec ts1;
     clock_gettime(CLOCK_MONOTONIC, &ts1);
@@ -424,6 +479,31 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
     e->t_calls[sz][all_in_box ? 0 : 1]++;
   }
   return 1;
+}
+
+int kvz_cuda_enc_preload_source(kvz_cuda_enc *e, int64_t pts, const void *luma, int32_t stride)
+{
+  if (!e || !luma) return fail_enc("kvz_cuda_enc_preload_source: null argument");
+  std::lock_guard<std::mutex> guard(e->lock);
+  KVZ_CUDA_TRY(cudaSetDevice(e->cfg.device));
+  Preload p;
+  p.pts = pts; p.d = nullptr;
+  if (!e->spare_planes.empty()) { p.d = e->spare_planes.back(); e->spare_planes.pop_back(); }
+  else KVZ_CUDA_TRY(cudaMalloc(&p.d, (size_t)e->cfg.width * e->cfg.height));
+  KVZ_CUDA_TRY(cudaMemcpy2DAsync(p.d, e->cfg.width, luma, stride, e->cfg.width, e->cfg.height, cudaMemcpyHostToDevice, e->stream));
+  KVZ_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  e->preloads.push_back(p);
+  return 1;
+}
+
+void kvz_cuda_enc_measurements(kvz_cuda_enc *e, unsigned long long m[8])
+{
+  if (e) {
+    std::lock_guard<std::mutex> guard(e->lock);
+    cudaSetDevice(e->cfg.device);
+    for (FrameCtx *c : e->ctxs) harvest_dense(e, c, true);
+  }
+  for (int i = 0; i < 8; i++) m[i] = e ? e->meas[i].load() : 0ull;
 }
 
 void kvz_cuda_enc_stats(const kvz_cuda_enc *e, unsigned long long stats[8])

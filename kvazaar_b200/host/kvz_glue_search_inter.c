@@ -59,14 +59,30 @@ static int glue_ime_search(const kvz_config *cfg, int *range)
   }
 }
 
+/* per (frame, tile): a handle of the session, found again by every worker thread of the frame */
+#define GLUE_FRAME_SLOTS 64
+static struct { uint64_t id; int handle; } g_frames[GLUE_FRAME_SLOTS];
+static int g_frames_next = 0;
+static pthread_mutex_t g_frames_lock = PTHREAD_MUTEX_INITIALIZER;
+static int32_t g_enc_last_num = -1;       /* highest state->frame->num searched with this session */
+
 static kvz_cuda_enc *glue_session(const encoder_state_t *state)
 {
   const encoder_control_t *ctrl = state->encoder_control;
-  if (g_enc && g_enc_ctrl == ctrl) return g_enc;
+  const int32_t num = state->frame->num;
+  /* a frame number that went backwards is a new encoder (kvz_api has no hook where the glue could see encoder_close):
+   * the session and what it cached of the old encoder's pictures are dropped */
+  if (g_enc && g_enc_ctrl == ctrl && num >= g_enc_last_num) {
+    if (num > g_enc_last_num) g_enc_last_num = num;
+    return g_enc;
+  }
   pthread_mutex_lock(&g_enc_lock);
-  if (!g_enc || g_enc_ctrl != ctrl) {
+  if (!g_enc || g_enc_ctrl != ctrl || num < g_enc_last_num) {
     static int registered = 0;
     glue_close_session();
+    pthread_mutex_lock(&g_frames_lock);
+    memset(g_frames, 0, sizeof(g_frames));
+    pthread_mutex_unlock(&g_frames_lock);
     const kvz_config *cfg = &ctrl->cfg;
     /* what the device search does not reproduce is refused, loudly -- never searched on the CPU instead */
     if (cfg->owf != 0)
@@ -89,17 +105,33 @@ static kvz_cuda_enc *glue_session(const encoder_state_t *state)
     g_enc = kvz_cuda_enc_open(&c);
     if (!g_enc) kvz_glue_die("kvz_cuda_enc_open");
     g_enc_ctrl = ctrl;
+    g_enc_last_num = num;
     if (!registered) { atexit(glue_close_session); registered = 1; }
   }
   pthread_mutex_unlock(&g_enc_lock);
   return g_enc;
 }
 
-/* ---- per (frame, tile): a handle of the session, found again by every worker thread of the frame ---- */
-#define GLUE_FRAME_SLOTS 64
-static struct { uint64_t id; int handle; } g_frames[GLUE_FRAME_SLOTS];
-static int g_frames_next = 0;
-static pthread_mutex_t g_frames_lock = PTHREAD_MUTEX_INITIALIZER;
+/* ---- for drivers of the library (bench.py): measurement counters of the session and source preloading ---- */
+KVZ_PUBLIC int kvz_glue_enc_measurements(unsigned long long m[8])
+{
+  if (!g_enc) return 0;
+  kvz_cuda_enc_measurements(g_enc, m);
+  return 1;
+}
+
+KVZ_PUBLIC int kvz_glue_enc_stats(unsigned long long s[8])
+{
+  if (!g_enc) return 0;
+  kvz_cuda_enc_stats(g_enc, s);
+  return 1;
+}
+
+/* the source luma of the picture the host will feed with presentation number `pts`, put on the device ahead of time */
+KVZ_PUBLIC int kvz_glue_preload_source(int64_t pts, const uint8_t *luma, int stride)
+{
+  return g_enc ? kvz_cuda_enc_preload_source(g_enc, pts, luma, stride) : 0;
+}
 
 /* quarter-pel vectors of the motion fields of the DPB, one sample per 16x16: where extra_mv (search_inter.c:1188-1206)
  * and the merge candidates of this frame will probably point */
@@ -144,6 +176,7 @@ static int glue_frame_handle(kvz_cuda_enc *enc, const encoder_state_t *state)
     memset(&f, 0, sizeof(f));
     f.frame_id = id;
     f.src_luma = src->y; f.src_stride = src->stride; f.src_key = (uint64_t)(uintptr_t)src;
+    f.src_pts = src->pts;
     f.tile_x = state->tile->offset_x; f.tile_y = state->tile->offset_y;
     f.tile_w = vf->width; f.tile_h = vf->height;
     memcpy(f.ref_LX, state->frame->ref_LX, sizeof(f.ref_LX));

@@ -1,6 +1,7 @@
-"""bench.py contract checks that need no GPU: the reference arm (the compiled reference's search_mv_full +
-search_frac on the host cores) prints exactly ONE JSON line on stdout with the keys the driver reads, whatever
-else the process writes goes to stderr; and our arm refuses to run without a CUDA device (no CPU fallback)."""
+"""bench.py contract checks that need no GPU: the reference arm (the unmodified reference encoding the first pictures
+of the 1080p config-2 clip through kvz_api on the host cores) prints exactly ONE JSON line on stdout with the keys the
+driver reads, whatever else the process writes goes to stderr; and our arm refuses to run without a CUDA device (no
+CPU fallback)."""
 import json
 import os
 import subprocess
@@ -21,7 +22,8 @@ def test_reference_arm_prints_one_json_line():
     lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
     assert len(lines) == 1, r.stdout[:2000]
     d = json.loads(lines[0])
-    assert d["impl"] == "reference" and d["unit"] == "Gcand/s" and d["higher_is_better"] is True
+    assert d["impl"] == "reference" and d["unit"] == "frames/s" and d["higher_is_better"] is True
+    assert len(d["config"]["bitstream_md5"]) == 32
     assert d["n_gpus"] == 1 and d["steps"] == 1 and d["value"] > 0
     assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
@@ -32,7 +34,7 @@ def test_our_arm_fails_loudly_without_a_gpu():
     import torch
     if torch.cuda.is_available():
         pytest.skip("a CUDA device is present")
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1"],
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "2"],
                        capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode != 0
     assert not r.stdout.strip()
