@@ -39,7 +39,11 @@ for _p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "tools")):
 import numpy as np  # noqa: E402
 
 W, H = 1920, 1080
-OPTIONS = "--preset medium --me full32 --gop 8 -r 4 --owf 0"      # BASELINE configs[1]; --owf pinned
+# BASELINE configs[1]; --owf is pinned (the bitstream depends on owf = 0 vs > 0 when WPP is on) to
+# 3, which is what the reference's own `--owf auto` resolves to for 1080p on 16 or more threads (encoder.c:240-279): the
+# reference arm runs as its CLI would by default (0.28 frames/s at --owf 0, 0.66 at 2, 0.72 at 4 on the 16-thread GPU
+# box).  KVZ_BENCH_OWF overrides it for both arms.
+OPTIONS = "--preset medium --me full32 --gop 8 -r 4 --owf " + os.environ.get("KVZ_BENCH_OWF", "3")
 METRIC = "1080p encode fps (config 2: --preset medium --me full32 --gop 8 -r 4, 8-bit, bit-identical bitstream)"
 UNIT = "frames/s"
 N8 = (W // 8) * (H // 8)                                          # 8x8 blocks per picture

@@ -34,7 +34,7 @@ typedef struct kvz_cuda_enc_cfg {
   int32_t owf, wpp;             /* cfg.owf, cfg.wpp (fracmv_within_tile) */
   int32_t sao_type, deblock_enable, mv_constraint;
   int32_t max_ref_lcu_right, max_ref_lcu_down;   /* encoder_control->max_inter_ref_lcu (encoder.c:240-241) */
-  int32_t max_map_mbytes;       /* cap of the dense SAD maps of one frame in MiB; 0 = default (32768) */
+  int32_t max_map_mbytes;       /* cap of the dense SAD maps of the owf + 1 frames in flight, MiB; 0 = default (98304) */
 } kvz_cuda_enc_cfg;
 
 /* Replaces nothing in the reference; called once next to kvz_strategyselector_init (src/kvazaar.c:81). */
@@ -43,12 +43,15 @@ KVZ_CUDA_API void kvz_cuda_enc_close(kvz_cuda_enc *enc);
 
 /* one picture of state->frame->ref (src/imagelist.h:38-48) */
 typedef struct kvz_cuda_enc_ref {
-  const void *luma;             /* ref->images[i]->y: reconstructed luma in HOST memory, complete */
+  const void *luma;             /* ref->images[i]->y: reconstructed luma in HOST memory; complete unless in_flight */
   int32_t stride;               /* samples per row */
   int32_t poc;                  /* ref->pocs[i] */
   uint64_t key;                 /* identity of the picture (its address): a picture already resident is not uploaded again */
   const int16_t *mv_hints;      /* quarter-pel (x, y) pairs sampled from the motion field ref->cu_arrays[i]: where the */
   int32_t n_mv_hints;           /* search windows of this frame will probably be centred (extra_mv, merge candidates) */
+  int32_t in_flight;            /* --owf > 0: the picture is still being reconstructed by one of the owf previous encoder states
+                                   (encoderstate.c:751-804).  Its 64x64 blocks are then uploaded, and this frame's SAD maps
+                                   against it computed, CTU by CTU as the host's CTU dependencies guarantee them */
 } kvz_cuda_enc_ref;
 
 typedef struct kvz_cuda_enc_frame {

@@ -29,7 +29,14 @@ struct PlaneSlot {
   uint64_t key = 0;
   int poc = 0;
   bool live = false;
+  uint64_t last_listed = 0;           // number of the newest frame whose reference list holds this picture
   uint8_t *d = nullptr;               // (w + 2 kPad) x (h + 2 kPad), pitch bytes per row
+  // a picture that was still being reconstructed when a frame first listed it (--owf > 0): its 64x64 blocks are
+  // uploaded one by one as the host's CTU dependencies guarantee them (ensure_blocks)
+  bool partial = false;
+  const uint8_t *host = nullptr;      // its luma in host memory
+  int host_stride = 0;
+  std::vector<uint8_t> have;          // per 64x64 block of the picture: uploaded (and complete on the device)
 };
 
 struct CurPlane {
@@ -54,15 +61,22 @@ struct FrameCtx {
   unsigned long long dense_absdiffs = 0, dense_map_bytes = 0;
   std::atomic<int> inflight{0};
   int box[KVZ_CUDA_MAX_REFS][4];      // x0, y0, n_dx, n_dy per reference
+  // references that were in flight when the frame began: their maps are made CTU by CTU (ctu_begin)
+  int n_partial = 0;
+  PlaneSlot *partial_slot[KVZ_CUDA_MAX_REFS];
+  ImeSadParams partial_ps[KVZ_CUDA_MAX_REFS];
+  int partial_box[KVZ_CUDA_MAX_REFS][4];
 };
 
 // per calling thread: a stream and the staging of one PU, its jobs and results
 struct Worker {
   int device = -1;
   cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;         // KVZ_CUDA_BLOCKING_SYNC: the thread sleeps on this instead of spinning
   uint8_t *h = nullptr, *d = nullptr;
   uint64_t seen_ctx = ~0ull;
   const void *seen_enc = nullptr;
+  int seen_ctu = -1;                  // the CTU of seen_ctx this thread last prepared (ctu_begin)
 };
 thread_local Worker t_worker;
 
@@ -83,8 +97,7 @@ struct kvz_cuda_enc {
   cudaStream_t stream = nullptr;      // frame-level work: uploads, borders, dense maps
   uint8_t *d_tmp = nullptr;           // un-bordered upload of a reference
   PlaneSlot slots[kMaxSlots];
-  CurPlane cur[4];
-  int cur_next = 0;
+  std::vector<CurPlane> cur;
   std::vector<FrameCtx *> ctxs;
   std::vector<Preload> preloads;
   std::vector<uint8_t *> spare_planes;                 // source planes handed back by consumed preloads
@@ -181,12 +194,73 @@ void harvest_dense(kvz_cuda_enc *e, FrameCtx *c, bool wait)
   e->meas[6] += c->dense_map_bytes;
 }
 
+// --owf > 0.  Before a thread searches its first PU of CTU (cx, cy) of a frame that lists pictures still in flight:
+// (1) every 64x64 block of those pictures that the motion vector restriction lets this CTU reach (fracmv_within_tile,
+// search_inter.c:87-140: at most max_ref_lcu_down rows below, right + down at most max_ref_lcu_right + max_ref_lcu_down
+// blocks away) is brought to the device if it is not there yet.  The host's CTU job dependency (encoderstate.c:786-801)
+// guarantees those blocks are reconstructed; the last samples of a block wait for its right / lower neighbour's in-loop
+// filters (the restriction's margins keep vectors off them until then), so every block is uploaded with 16 samples of
+// its left / upper neighbours: a block's late strips arrive with the neighbour that finishes them.  (2) the dense SAD maps
+// of this CTU against those pictures, on the thread's own stream, in front of its PU searches.  Samples that are not
+// final yet only ever feed displacements the restriction excludes.
+int ctu_begin(kvz_cuda_enc *e, FrameCtx *ctx, int cx, int cy, cudaStream_t stream)
+{
+  const kvz_cuda_enc_cfg &cfg = e->cfg;
+  const int W = cfg.width, H = cfg.height;
+  const int ctus_x = (W + 63) / 64, ctus_y = (H + 63) / 64;
+  const int down = cfg.max_ref_lcu_down, reach = cfg.max_ref_lcu_down + cfg.max_ref_lcu_right;
+  // picture-level CTU position (tiles with --owf are refused by the glue; tile offsets are multiples of 64 anyway)
+  const int pcx = cx + ctx->f.tile_x / 64, pcy = cy + ctx->f.tile_y / 64;
+  bool uploaded = false;
+  int marks[64][2], n_marks = 0;
+  PlaneSlot *mark_slot[64];
+  for (int i = 0; i < ctx->n_partial; i++) {
+    PlaneSlot *s = ctx->partial_slot[i];
+    if (!s->partial) continue;                       // completed by a later frame's begin in the meantime
+    for (int ry = 0; ry <= std::min(pcy + down, ctus_y - 1); ry++) {
+      const int rx_max = std::min(pcx + reach - (ry - pcy), ctus_x - 1);
+      for (int rx = 0; rx <= rx_max; rx++) {
+        if (s->have[(size_t)ry * ctus_x + rx]) continue;
+        const int x0 = std::max(0, rx * 64 - 16), y0 = std::max(0, ry * 64 - 16);
+        const int x1 = std::min(W, (rx + 1) * 64), y1 = std::min(H, (ry + 1) * 64);
+        KVZ_CUDA_TRY(cudaMemcpy2DAsync(s->d + (size_t)(y0 + kPad) * e->pitch + x0 + kPad, e->pitch,
+                                       s->host + (size_t)y0 * s->host_stride + x0, s->host_stride, x1 - x0, y1 - y0,
+                                       cudaMemcpyHostToDevice, stream));
+        if (!launch_pad_patch(s->d, W, H, kPad, e->pitch, x0, y0, x1 - x0, y1 - y0, 8, stream)) return 0;
+        e->meas[0] += (unsigned long long)(x1 - x0) * (y1 - y0);
+        uploaded = true;
+        if (n_marks == 64) {                         // flush: complete on the device before anybody is told
+          KVZ_CUDA_TRY(cudaStreamSynchronize(stream));
+          for (int k = 0; k < n_marks; k++) mark_slot[k]->have[(size_t)marks[k][1] * ctus_x + marks[k][0]] = 1;
+          n_marks = 0;
+        }
+        marks[n_marks][0] = rx; marks[n_marks][1] = ry; mark_slot[n_marks] = s; n_marks++;
+      }
+    }
+  }
+  if (uploaded) {
+    // other frames in flight may list the same picture: a block counts as present only once it is complete on the device
+    KVZ_CUDA_TRY(cudaStreamSynchronize(stream));
+    for (int k = 0; k < n_marks; k++) mark_slot[k]->have[(size_t)marks[k][1] * ctus_x + marks[k][0]] = 1;
+  }
+  if (ctx->f.ime_search == KVZ_CUDA_IME_FULL && ctx->n_partial > 0) {
+    const int ctu = cy * ctx->f.ctus_x + cx;
+    for (int r0 = 0; r0 < ctx->n_partial; r0 += kImeMaxMulti) {
+      const int n = std::min(kImeMaxMulti, ctx->n_partial - r0);
+      if (!launch_ime_sad_box_multi(ctx->partial_ps + r0, ctx->partial_box + r0, n, stream, ctu)) return 0;
+    }
+  }
+  return 1;
+}
+
 bool worker_ready(kvz_cuda_enc *e)
 {
   Worker &w = t_worker;
   if (w.device == e->cfg.device && w.stream) return true;
   if (cudaSetDevice(e->cfg.device) != cudaSuccess) return false;      // every calling thread binds the session's device
   if (cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess) return false;
+  if (getenv("KVZ_CUDA_BLOCKING_SYNC") &&
+      cudaEventCreateWithFlags(&w.done, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) return false;
   // pinned AND mapped: the kernel reads the PU and its jobs from, and writes its results to, this host buffer
   // directly (one small PCIe read / write per call instead of two copy commands)
   if (cudaHostAlloc(&w.h, kStageBytes, cudaHostAllocMapped) != cudaSuccess) return false;
@@ -213,7 +287,7 @@ kvz_cuda_enc *kvz_cuda_enc_open(const kvz_cuda_enc_cfg *cfg)
   if (!kvz_cuda_init(cfg->device)) return nullptr;
   kvz_cuda_enc *e = new kvz_cuda_enc();
   e->cfg = *cfg;
-  if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 32768;
+  if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 98304;       // of 180 GB; shared by the owf + 1 frames in flight
   for (auto &s : e->stats) s = 0;
   for (auto &s : e->meas) s = 0;
   for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) { e->t_ns[a][b] = 0; e->t_calls[a][b] = 0; }
@@ -267,11 +341,14 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   const uint64_t frame_num = fr->frame_id >> 16;
 
   // ---- source plane: one upload per frame, shared by its tiles ----
+  // planes, contexts and slots of frame n may be reused once frame n + owf + 1 begins: the encoder has owf + 1 states in
+  // a ring (kvazaar.c:96-126), so that frame's state is being reused, i.e. the frame is complete
+  const uint64_t window = (uint64_t)(cfg.owf > 0 ? cfg.owf : 0) + 1;
   CurPlane *cur = nullptr;
   for (auto &c : e->cur) if (c.d && c.key == fr->src_key && c.frame_num == frame_num) cur = &c;
   if (!cur) {
-    cur = &e->cur[e->cur_next];
-    e->cur_next = (e->cur_next + 1) & 3;
+    for (auto &c : e->cur) if (c.frame_num == ~0ull || c.frame_num + window <= frame_num) { cur = &c; break; }
+    if (!cur) { e->cur.emplace_back(); cur = &e->cur.back(); }
     if (cur->preloaded) { e->spare_planes.push_back(cur->d); cur->d = nullptr; cur->preloaded = false; }
     cur->key = fr->src_key; cur->frame_num = frame_num;
     bool found = false;
@@ -294,29 +371,43 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
     }
   }
 
-  // ---- reference planes: drop what the DPB dropped, upload and border what is new ----
+  // ---- reference planes: keep what some frame in flight lists, upload and border what is new ----
   for (auto &s : e->slots) {
     if (!s.live) continue;
-    bool listed = false;
-    for (int r = 0; r < fr->n_refs; r++) listed |= fr->refs[r].key == s.key && fr->refs[r].poc == s.poc;
-    if (!listed) s.live = false;
+    for (int r = 0; r < fr->n_refs; r++)
+      if (fr->refs[r].key == s.key && fr->refs[r].poc == s.poc && frame_num > s.last_listed) s.last_listed = frame_num;
+    if (s.last_listed + window <= frame_num) s.live = false;       // no frame that can still be searching lists it
   }
+  const int pic_ctus_x = (cfg.width + 63) / 64, pic_ctus_y = (cfg.height + 63) / 64;
   PlaneSlot *ref_slot[KVZ_CUDA_MAX_REFS];
   for (int r = 0; r < fr->n_refs; r++) {
     const kvz_cuda_enc_ref &rr = fr->refs[r];
     if (!rr.luma) { fail_enc("kvz_cuda_enc_frame_begin: null reference plane"); return -1; }
     PlaneSlot *s = nullptr;
     for (auto &q : e->slots) if (q.live && q.key == rr.key && q.poc == rr.poc) s = &q;
-    if (!s) {
+    const bool fresh = s == nullptr;
+    if (fresh) {
       for (auto &q : e->slots) if (!q.live) { s = &q; break; }
       if (!s) { fail_enc("kvz_cuda_enc_frame_begin: out of reference plane slots"); return -1; }
       if (!s->d && cudaMalloc(&s->d, e->plane_bytes) != cudaSuccess) {
         fail("cudaMalloc(reference plane)", cudaGetLastError(), __FILE__, __LINE__); return -1;
       }
+      s->key = rr.key; s->poc = rr.poc; s->live = true; s->last_listed = frame_num;
+      s->partial = rr.in_flight != 0;
+      s->host = static_cast<const uint8_t *>(rr.luma); s->host_stride = rr.stride;
+      if (s->partial) s->have.assign((size_t)pic_ctus_x * pic_ctus_y, 0);
+    }
+    // whole picture at once: a new complete picture, or one that was in flight when it was first listed and is done now
+    if ((fresh && !s->partial) || (!fresh && s->partial && !rr.in_flight)) {
       if (cudaMemcpy2DAsync(e->d_tmp, cfg.width, rr.luma, rr.stride, cfg.width, cfg.height, cudaMemcpyHostToDevice,
                             e->stream) != cudaSuccess) { fail("upload of a reference plane", cudaGetLastError(), __FILE__, __LINE__); return -1; }
       if (!launch_pad_plane(e->d_tmp, cfg.width, cfg.height, cfg.width, s->d, kPad, e->pitch, 8, e->stream)) return -1;
-      s->key = rr.key; s->poc = rr.poc; s->live = true;
+      if (s->partial) {
+        // threads of an older frame may be bringing this picture's blocks in one by one: they stop doing so when the
+        // flag falls, so the whole picture has to be on the device before it does
+        if (cudaStreamSynchronize(e->stream) != cudaSuccess) { fail("stream sync", cudaGetLastError(), __FILE__, __LINE__); return -1; }
+        s->partial = false;
+      }
       e->stats[2]++;
       e->meas[0] += (unsigned long long)cfg.width * cfg.height;
     }
@@ -328,7 +419,7 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   int handle = -1;
   for (size_t i = 0; i < e->ctxs.size(); i++) {
     FrameCtx *c = e->ctxs[i];
-    if ((c->id >> 16) != frame_num && c->inflight.load() == 0) { ctx = c; handle = (int)i; break; }
+    if (c->id != ~0ull && (c->id >> 16) + window <= frame_num && c->inflight.load() == 0) { ctx = c; handle = (int)i; break; }
   }
   if (!ctx) {
     ctx = new FrameCtx();
@@ -353,7 +444,7 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
         choose_box(cfg.range, fr->refs[r].mv_hints, fr->refs[r].n_mv_hints, shrink, ctx->box[r]);
         need += box_bytes(fr->tile_w, fr->tile_h, ctx->box[r]);
       }
-      if (need <= (size_t)cfg.max_map_mbytes << 20 || shrink == 0) break;
+      if (need <= ((size_t)cfg.max_map_mbytes << 20) / window || shrink == 0) break;     // owf + 1 frames hold maps at once
       shrink = shrink * 3 / 4;
     }
     if (need > ctx->map_bytes) {
@@ -378,12 +469,19 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   f.n_refs = fr->n_refs;
   memcpy(f.ref_LX, fr->ref_LX, sizeof(f.ref_LX));
   ImeSadParams ps[KVZ_CUDA_MAX_REFS];
+  int ps_box[KVZ_CUDA_MAX_REFS][4];
+  int n_full = 0;
   uint8_t *at = ctx->maps;
-  unsigned long long disp = 0;
+  unsigned long long disp = 0, disp_full = 0;
+  ctx->n_partial = 0;
   for (int r = 0; r < fr->n_refs; r++) {
     f.refs[r].plane = ref_slot[r]->d; f.refs[r].pitch = e->pitch; f.refs[r].pad = kPad;
     f.refs[r].n_sets = 0;
-    if (!full) continue;
+    if (!full) {
+      // the heuristic searches read the reference plane directly: a picture in flight needs its blocks too
+      if (ref_slot[r]->partial) { ctx->partial_slot[ctx->n_partial] = ref_slot[r]; ctx->n_partial++; }
+      continue;
+    }
     const int *b = ctx->box[r];
     void *lv[4];
     for (int l = 0; l < 4; l++) {
@@ -396,7 +494,8 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
     ms.cx = b[0]; ms.cy = b[1]; ms.n_dx = b[2]; ms.n_dy = b[3];
     ms.sad8 = (const uint16_t *)lv[0]; ms.sad16 = (const uint16_t *)lv[1];
     ms.sad32 = (const uint32_t *)lv[2]; ms.sad64 = (const uint32_t *)lv[3];
-    ImeSadParams &p = ps[r];
+    const bool part = ref_slot[r]->partial;
+    ImeSadParams &p = part ? ctx->partial_ps[ctx->n_partial] : ps[n_full];
     memset(&p, 0, sizeof(p));
     p.cur = cur->d; p.ref = ref_slot[r]->d;
     p.width = cfg.width; p.height = cfg.height;
@@ -406,16 +505,25 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
     p.map_pitch = b[2];
     p.sad8 = (uint16_t *)lv[0]; p.sad16 = (uint16_t *)lv[1]; p.sad32 = (uint32_t *)lv[2]; p.sad64 = (uint32_t *)lv[3];
     disp += (unsigned long long)b[2] * b[3];
+    if (part) {
+      memcpy(ctx->partial_box[ctx->n_partial], b, sizeof(int) * 4);
+      ctx->partial_slot[ctx->n_partial] = ref_slot[r];
+      ctx->n_partial++;
+    } else {
+      memcpy(ps_box[n_full], b, sizeof(int) * 4);
+      disp_full += (unsigned long long)b[2] * b[3];
+      n_full++;
+    }
   }
-  if (full) {
+  if (full && n_full > 0) {
     cudaEventRecord(ctx->dense0, e->stream);
-    for (int r0 = 0; r0 < fr->n_refs; r0 += kImeMaxMulti) {
-      const int n = std::min(kImeMaxMulti, fr->n_refs - r0);
-      if (!launch_ime_sad_box_multi(ps + r0, ctx->box + r0, n, e->stream)) return -1;
+    for (int r0 = 0; r0 < n_full; r0 += kImeMaxMulti) {
+      const int n = std::min(kImeMaxMulti, n_full - r0);
+      if (!launch_ime_sad_box_multi(ps + r0, ps_box + r0, n, e->stream)) return -1;
     }
     cudaEventRecord(ctx->dense1, e->stream);
     ctx->dense_pending = true;
-    ctx->dense_absdiffs = level_entries(fr->tile_w, fr->tile_h, 0) * 64ull * disp;
+    ctx->dense_absdiffs = level_entries(fr->tile_w, fr->tile_h, 0) * 64ull * disp_full;
     ctx->dense_map_bytes = need;
   }
   if (cudaEventRecord(ctx->ready, e->stream) != cudaSuccess) { fail("cudaEventRecord", cudaGetLastError(), __FILE__, __LINE__); return -1; }
@@ -456,7 +564,14 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
   const uint64_t tag = ((uint64_t)handle << 48) ^ ctx->id;
   if (w.seen_ctx != tag || w.seen_enc != e) {              // first call of this thread for this frame: wait for its maps
     KVZ_CUDA_TRY(cudaStreamWaitEvent(w.stream, ctx->ready, 0));
-    w.seen_ctx = tag; w.seen_enc = e;
+    w.seen_ctx = tag; w.seen_enc = e; w.seen_ctu = -1;
+  }
+  if (ctx->n_partial > 0) {                                // --owf: references in flight are prepared CTU by CTU
+    const int cx = pu->x >> 6, cy = pu->y >> 6, ctu = cy * ctx->f.ctus_x + cx;
+    if (w.seen_ctu != ctu) {
+      if (!ctu_begin(e, ctx, cx, cy, w.stream)) return 0;
+      w.seen_ctu = ctu;
+    }
   }
   MeFrame f = ctx->f;
   f.lambda_sqrt_i = lambda_sqrt_i;
@@ -465,7 +580,12 @@ int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const
   // the PU and its jobs go in the launch itself; the results come back through the mapped host buffer
   if (!launch_me_search_pu(f, nullptr, nullptr, reinterpret_cast<kvz_cuda_me_result *>(w.d + kOffResults), 1, w.stream,
                            &one, jobs)) return 0;
-  KVZ_CUDA_TRY(cudaStreamSynchronize(w.stream));
+  if (w.done) {
+    KVZ_CUDA_TRY(cudaEventRecord(w.done, w.stream));
+    KVZ_CUDA_TRY(cudaEventSynchronize(w.done));
+  } else {
+    KVZ_CUDA_TRY(cudaStreamSynchronize(w.stream));
+  }
   memcpy(results, w.h + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result));
   e->stats[1]++;
   e->stats[5] += (unsigned long long)nj;

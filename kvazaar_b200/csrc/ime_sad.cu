@@ -520,6 +520,7 @@ struct ImeSadMulti {
   ImeSadParams p[kImeMaxMulti];
   int full_end[kImeMaxMulti];     // cumulative CTA count after reference r
   int n;
+  int ctu_only;                   // >= 0: the maps of this one CTU only (grid = the chunks of every reference)
 };
 
 __global__ void __launch_bounds__(kWsThreads, 2)
@@ -530,7 +531,8 @@ ime_sad_multi_kernel(const __grid_constant__ ImeSadMulti m)
   int r = 0;
   while (bid >= m.full_end[r]) r++;
   const int local = bid - (r ? m.full_end[r - 1] : 0);
-  const int ctu = local / m.p[r].n_chunks, chunk = local - ctu * m.p[r].n_chunks;
+  const int ctu = m.ctu_only >= 0 ? m.ctu_only : local / m.p[r].n_chunks;
+  const int chunk = m.ctu_only >= 0 ? local : local - ctu * m.p[r].n_chunks;
   chunk_cta_ws(m.p[r], smem_raw, ctu, chunk);
 }
 
@@ -546,7 +548,33 @@ __global__ void pad_plane_kernel(const PIX *src, int w, int h, int src_pitch, PI
   dst[(size_t)y * dst_pitch + x] = src[(size_t)sy * src_pitch + sx];
 }
 
+// Re-replicate the border of an already bordered plane after the frame rectangle [x0, x0 + w) x [y0, y0 + h) of its
+// interior changed: every border sample whose clamped source lies in the rectangle.  In place.
+template <typename PIX>
+__global__ void pad_patch_kernel(PIX *plane, int W, int H, int pad, int pitch, int ex0, int ey0, int ew, int eh)
+{
+  const int x = ex0 + blockIdx.x * blockDim.x + threadIdx.x, y = ey0 + blockIdx.y;
+  if (x >= ex0 + ew || y >= ey0 + eh) return;
+  if (x >= 0 && x < W && y >= 0 && y < H) return;                  // interior: already there
+  const int sx = clampi(x, 0, W - 1), sy = clampi(y, 0, H - 1);
+  plane[(size_t)(y + pad) * pitch + (x + pad)] = plane[(size_t)(sy + pad) * pitch + (sx + pad)];
+}
+
 }  // namespace
+
+int launch_pad_patch(void *plane, int W, int H, int pad, int pitch, int x0, int y0, int w, int h, int bitdepth,
+                     cudaStream_t stream)
+{
+  if (x0 > 0 && y0 > 0 && x0 + w < W && y0 + h < H) return 1;      // touches no edge
+  const int ex0 = x0 == 0 ? -pad : x0, ey0 = y0 == 0 ? -pad : y0;
+  const int ex1 = x0 + w == W ? W + pad : x0 + w, ey1 = y0 + h == H ? H + pad : y0 + h;
+  dim3 grid((ex1 - ex0 + 127) / 128, ey1 - ey0);
+  if (bitdepth == 8) pad_patch_kernel<uint8_t><<<grid, 128, 0, stream>>>((uint8_t *)plane, W, H, pad, pitch, ex0, ey0, ex1 - ex0, ey1 - ey0);
+  else pad_patch_kernel<uint16_t><<<grid, 128, 0, stream>>>((uint16_t *)plane, W, H, pad, pitch, ex0, ey0, ex1 - ex0, ey1 - ey0);
+  count_launch();
+  KVZ_CUDA_LAUNCH_CHECK();
+  return 1;
+}
 
 int ime_map_pitch(int range) { return ((2 * range + 1) + 15) & ~15; }
 
@@ -622,12 +650,13 @@ int ime_box_max_rows()
   return best;
 }
 
-int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream)
+int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream, int ctu_only)
 {
   if (n <= 0 || n > kImeMaxMulti) return fail_msg("ime_sad_box_multi: 1..8 references per launch");
   ImeSadMulti m;
   memset(&m, 0, sizeof(m));
   m.n = n;
+  m.ctu_only = ctu_only;
   size_t smem = 0;
   int total = 0;
   for (int r = 0; r < n; r++) {
@@ -636,11 +665,16 @@ int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int 
     const size_t sb = ws_smem_bytes(Geo(m.p[r].n_dy));
     if (sb > smem) smem = sb;
     const int n_ctu = m.p[r].ctus_x * m.p[r].ctus_y;
-    total += n_ctu * m.p[r].n_chunks;
+    if (ctu_only >= n_ctu) return fail_msg("ime_sad_box_multi: CTU index outside the tile");
+    total += (ctu_only >= 0 ? 1 : n_ctu) * m.p[r].n_chunks;
     m.full_end[r] = total;
   }
   if (smem > 113 * 1024) return fail_msg("ime_sad: too many displacement rows for the shared-memory tile");
-  KVZ_CUDA_TRY(cudaFuncSetAttribute(ime_sad_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static size_t opted = 0;                        // opt in once per size (any host thread may launch this)
+  if (smem > opted) {
+    KVZ_CUDA_TRY(cudaFuncSetAttribute(ime_sad_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    opted = smem;
+  }
   ime_sad_multi_kernel<<<total, kWsThreads, smem, stream>>>(m);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();

@@ -43,6 +43,10 @@ int launch_ime_sad10_box(ImeSadParams p, int x0, int y0, int n_dx, int n_dy, int
 // largest box height (displacement rows) of launch_ime_sad_box_multi
 int ime_box_max_rows();
 // the boxes of n <= kImeMaxMulti references of one current picture in ONE launch; boxes[r] = {x0, y0, n_dx, n_dy}
-int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream);
+// ctu_only >= 0: only the maps of that CTU (what a host computes when the reference is still being reconstructed)
+int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int n, cudaStream_t stream, int ctu_only = -1);
+// after the frame rectangle (x0, y0, w, h) of a bordered plane's interior changed: re-replicate the border it feeds
+int launch_pad_patch(void *plane, int W, int H, int pad, int pitch, int x0, int y0, int w, int h, int bitdepth,
+                     cudaStream_t stream);
 
 }  // namespace kvz

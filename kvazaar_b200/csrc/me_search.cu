@@ -276,6 +276,7 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
 // development timers of the box scan (KVZ_CUDA_STATS): [0] table set-up, [1] seed, [2] stream, [3] scans timed
 __device__ unsigned long long g_box_scan_ns[4];
 __device__ int g_box_scan_timing;
+__device__ int g_pu_use_seed = 1;       // KVZ_CUDA_PU_SEED=0 switches the early-rejection seed of me_pu_kernel off (experiments)
 __device__ __forceinline__ unsigned long long gtime_ns()
 {
   unsigned long long t;
@@ -676,18 +677,77 @@ __device__ bool scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     uint32_t wbest = 0xFFFFFFFFu, wpos = 0;          // best cost so far and its box entry (row << 16 | col)
     const int bx0 = ms.cx, by0 = ms.cy, n_dx = ms.n_dx, n_dy = ms.n_dy;
     bool close_x;
+    // the bounding rectangle of the job's windows inside the box: rows r0 .. r0 + nr - 1, chunks c0 .. c1 (16 columns
+    // each).  Only that part of the box is streamed and only its rows / columns get table entries.
+    int r0, nr, c0, c1;
     {
-      int lox = wcx[0], hix = wcx[0];
-      for (int w = 1; w < nwin; w++) { lox = min(lox, wcx[w]); hix = max(hix, wcx[w]); }
+      int lox = wcx[0], hix = wcx[0], loy = wcy[0], hiy = wcy[0];
+      for (int w = 1; w < nwin; w++) {
+        lox = min(lox, wcx[w]); hix = max(hix, wcx[w]);
+        loy = min(loy, wcy[w]); hiy = max(hiy, wcy[w]);
+      }
       close_x = hix - lox <= K;
+      r0 = loy - R - by0; nr = hiy - loy + 2 * R + 1;
+      c0 = (lox - R - bx0) >> 4; c1 = (hix + R - bx0) >> 4;
     }
+    const int n = 8 >> level;
+    const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
+    const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
+    // the first map vectors are requested before the tables are built: their latency hides behind that work
+    // Vectors of 8 entries in row-major order, 32 per step.  A lane streams its vectors through a ring in
+    // shared memory with cp.async: kScanRing 16-byte pieces (8 vectors of uint16 entries, 4 of uint32) are
+    // in flight per lane while one is priced -- the scan is bound by HBM latency, not by registers.
+    // Box maps are CHUNK-MAJOR (ime_sad.cu): map[chunk][pu][row][16], the last chunk 8 wide when n_dx is an odd
+    // multiple of 8.  Vector index i runs chunk by chunk, inside a chunk row-major (2 vectors per row, 1 in a half
+    // chunk): the vectors of a chunk are contiguous in memory.  The traversal order is free -- ties are settled
+    // by key, not by visiting order.
+    const int nch = (n_dx + 15) >> 4, last_vpc = (n_dx & 8) ? 1 : 2;
+    const int pus_level = f.ctus_x * ((f.tile_h + 63) >> 6) * n * n;
+    const bool wide = level >= 2;                                   // uint32 entries: two pieces per vector
+    const uint4 *mp = wide ? reinterpret_cast<const uint4 *>(level == 2 ? ms.sad32 : ms.sad64)
+                           : reinterpret_cast<const uint4 *>(level == 0 ? ms.sad8 : ms.sad16);
+    const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
+    const int vpc1 = (c1 == nch - 1) ? last_vpc : 2;                // vectors per row in chunk c1
+    const int total = nr * (2 * (c1 - c0) + vpc1);
+    // cursor over the vectors of this lane: chunk c, index ic inside the rows r0.. of the PU's run of that chunk,
+    // off = position in the map (in vectors of 8 entries)
+    struct Cursor { int c, ic; size_t off; };
+    const size_t chunk_stride = (size_t)2 * pus_level * n_dy;      // vectors of a full chunk, all PUs
+    const size_t pu_run = (size_t)prow * n_dy + r0;                // rows before the first streamed row of this PU, per chunk
+    auto run_len = [&](int c) { return nr * ((c == nch - 1) ? last_vpc : 2); };
+    auto run_off = [&](int c) { return (size_t)c * chunk_stride + pu_run * ((c == nch - 1) ? last_vpc : 2); };
+    auto advance = [&](Cursor &k, int by) {
+      k.ic += by; k.off += by;
+      while (k.c < c1 && k.ic >= run_len(k.c)) {
+        k.ic -= run_len(k.c); k.c++;
+        k.off = run_off(k.c) + k.ic;
+      }
+    };
+    Cursor ci = { c0, 0, run_off(c0) }, cc = ci;                    // issue / consume
+    const int first = lane + G * sub, stride = G * nsub;              // this warp's vectors: first, first + stride, ...
+    advance(ci, first); advance(cc, first);
+    int issued = first;
+    auto issue = [&](int slot) {
+      if (issued < total) {
+        const size_t v = ci.off;
+        if (wide) {
+          cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * v);
+          cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * v + 1);
+        } else {
+          cp_async16(&sm.ring[slot * 32 + lane], mp + v);
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      issued += stride; advance(ci, stride);
+    };
+    for (int t = 0; t < depth; t++) issue(t);
     __syncwarp();
-    for (int i = lane; i < n_dx; i += G) {
+    for (int i = 16 * c0 + lane; i < min(n_dx, 16 * (c1 + 1)); i += G) {
       const int qx = (bx0 + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
       sm.set_gx(i, lam * golomb_bits(abs(qx - j.mv_cand[0][0])), lam * golomb_bits(abs(qx - j.mv_cand[1][0])));
     }
-    for (int i = lane; i < n_dy; i += G) {
+    for (int i = r0 + lane; i < r0 + nr; i += G) {
       const int qy = (by0 + i) * 4;
       const uint32_t lam = (uint32_t)j.lambda;
       sm.gy[i] = make_uint2(lam * golomb_bits(abs(qy - j.mv_cand[0][1])), lam * golomb_bits(abs(qy - j.mv_cand[1][1])));
@@ -732,9 +792,6 @@ __device__ bool scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
     const int n_hit = sm.n_hit;
     bc.n_hit = n_hit;
     if (timed) tb1 = gtime_ns();
-    const int n = 8 >> level;
-    const int ctu = (j.y >> 6) * f.ctus_x + (j.x >> 6);
-    const size_t prow = (size_t)ctu * n * n + ((j.y & 63) / j.h) * n + (j.x & 63) / j.w;
 
     const int z_r0 = -R - by0, z_c0 = -R - bx0;     // the zero window (window 0) inside the box
     int hitv[5];                                    // vectors that hold a merge-override entry: row << 13 | vector
@@ -801,70 +858,12 @@ __device__ bool scan_job(int lane, ScanSmemT<BOX> &sm, const MeFrame &f, const k
       for (; eq; eq &= eq - 1) claim(cost, ((uint32_t)row << 16) | (uint32_t)(c0 + __ffs((int)eq) - 1));
     };
 
-    // Vectors of 8 entries in row-major order, 32 per step.  A lane streams its vectors through a ring in
-    // shared memory with cp.async: kScanRing 16-byte pieces (8 vectors of uint16 entries, 4 of uint32) are
-    // in flight per lane while one is priced -- the scan is bound by HBM latency, not by registers.
-    // Box maps are CHUNK-MAJOR (ime_sad.cu): map[chunk][pu][row][16], the last chunk 8 wide when n_dx is an odd
-    // multiple of 8.  Vector index i runs chunk by chunk, inside a chunk row-major (2 vectors per row, 1 in a half
-    // chunk): the vectors of a chunk are contiguous in memory.  The traversal order is free -- ties are settled
-    // by key, not by visiting order.
-    const int nch = (n_dx + 15) >> 4, last_vpc = (n_dx & 8) ? 1 : 2;
-    const int pus_level = f.ctus_x * ((f.tile_h + 63) >> 6) * n * n;
-    const bool wide = level >= 2;                                   // uint32 entries: two pieces per vector
-    const uint4 *mp = wide ? reinterpret_cast<const uint4 *>(level == 2 ? ms.sad32 : ms.sad64)
-                           : reinterpret_cast<const uint4 *>(level == 0 ? ms.sad8 : ms.sad16);
-    const int depth = wide ? kScanRing / 2 : kScanRing;             // vectors in flight
-    // Only the bounding rectangle of the job's windows is streamed: box rows r0 .. r0 + nr - 1 of chunks c0 .. c1
-    // (a box made for all PUs of a frame is much larger than the windows of one PU).
-    int r0, nr, c0, c1;
-    {
-      int lox = wcx[0], hix = wcx[0], loy = wcy[0], hiy = wcy[0];
-      for (int w = 1; w < nwin; w++) {
-        lox = min(lox, wcx[w]); hix = max(hix, wcx[w]);
-        loy = min(loy, wcy[w]); hiy = max(hiy, wcy[w]);
-      }
-      r0 = loy - R - by0; nr = hiy - loy + 2 * R + 1;
-      c0 = (lox - R - bx0) >> 4; c1 = (hix + R - bx0) >> 4;
-    }
-    const int vpc1 = (c1 == nch - 1) ? last_vpc : 2;                // vectors per row in chunk c1
-    const int total = nr * (2 * (c1 - c0) + vpc1);
-    // cursor over the vectors of this lane: chunk c, index ic inside the rows r0.. of the PU's run of that chunk,
-    // off = position in the map (in vectors of 8 entries)
-    struct Cursor { int c, ic; size_t off; };
-    const size_t chunk_stride = (size_t)2 * pus_level * n_dy;      // vectors of a full chunk, all PUs
-    const size_t pu_run = (size_t)prow * n_dy + r0;                // rows before the first streamed row of this PU, per chunk
-    auto run_len = [&](int c) { return nr * ((c == nch - 1) ? last_vpc : 2); };
-    auto run_off = [&](int c) { return (size_t)c * chunk_stride + pu_run * ((c == nch - 1) ? last_vpc : 2); };
-    auto advance = [&](Cursor &k, int by) {
-      k.ic += by; k.off += by;
-      while (k.c < c1 && k.ic >= run_len(k.c)) {
-        k.ic -= run_len(k.c); k.c++;
-        k.off = run_off(k.c) + k.ic;
-      }
-    };
-    Cursor ci = { c0, 0, run_off(c0) }, cc = ci;                    // issue / consume
-    const int first = lane + G * sub, stride = G * nsub;              // this warp's vectors: first, first + stride, ...
-    advance(ci, first); advance(cc, first);
-    int issued = first;
-    auto issue = [&](int slot) {
-      if (issued < total) {
-        const size_t v = ci.off;
-        if (wide) {
-          cp_async16(&sm.ring[(2 * slot) * 32 + lane], mp + 2 * v);
-          cp_async16(&sm.ring[(2 * slot + 1) * 32 + lane], mp + 2 * v + 1);
-        } else {
-          cp_async16(&sm.ring[slot * 32 + lane], mp + v);
-        }
-      }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      issued += stride; advance(ci, stride);
-    };
-    for (int t = 0; t < depth; t++) issue(t);
     // Early rejection: the exact cost of a few likely candidates (the window centres and the two AMVP
     // predictors, where they are searched) bounds the minimum from above; a vector whose smallest SAD
     // already exceeds that bound (bit costs are >= 0) can hold neither the winner nor a tie with it.
     uint32_t seed = 0xFFFFFFFFu;
-    {
+    // (measured in the encode, 1080p, B200: with the seed 5.4 / 7.2 / 7.8 frames/s at --owf 0 / 2 / 4, without 5.2 / 6.1 / 7.1)
+    if (part == nullptr || g_pu_use_seed) {
       int sx = 0, sy = 0;
       bool have = false;
       if (lane < nwin) { sx = wcx[lane]; sy = wcy[lane]; have = true; }
@@ -1954,6 +1953,12 @@ int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_c
   static const int timing = getenv("KVZ_CUDA_STATS") != nullptr;
   static bool timing_set = false;
   if (timing && !timing_set) { KVZ_CUDA_TRY(cudaMemcpyToSymbol(g_box_scan_timing, &timing, sizeof(int))); timing_set = true; }
+  static bool seed_set = false;
+  if (!seed_set) {
+    const int use = getenv("KVZ_CUDA_PU_SEED") ? atoi(getenv("KVZ_CUDA_PU_SEED")) : 1;
+    if (!use) KVZ_CUDA_TRY(cudaMemcpyToSymbol(g_pu_use_seed, &use, sizeof(int)));
+    seed_set = true;
+  }
   PuArgs a;
   if (host_pu != nullptr && host_jobs != nullptr && n_pus == 1) {
     a.pu = *host_pu;

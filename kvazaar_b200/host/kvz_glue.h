@@ -36,6 +36,8 @@ extern unsigned long long kvz_glue_count[KVZ_GLUE_CNT_N];
 #define KVZ_GLUE_COUNT(family) __atomic_fetch_add(&kvz_glue_count[family], 1ull, __ATOMIC_RELAXED)
 void kvz_glue_counters(unsigned long long out[KVZ_GLUE_CNT_N]);
 
+void kvz_glue_session_close(void);  /* kvz_glue_search_inter.c: drop the encoder session (kvz_api encoder_open / encoder_close) */
+
 void kvz_glue_die(const char *what);   /* no CPU fallback: report kvz_cuda_last_error() and abort */
 
 #endif

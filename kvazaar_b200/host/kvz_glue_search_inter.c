@@ -45,6 +45,14 @@ static void glue_close_session(void)
   }
 }
 
+void kvz_glue_session_close(void)
+{
+  pthread_mutex_lock(&g_enc_lock);
+  glue_close_session();
+  g_enc_ctrl = NULL;
+  pthread_mutex_unlock(&g_enc_lock);
+}
+
 static int glue_ime_search(const kvz_config *cfg, int *range)
 {
   *range = 32;
@@ -64,20 +72,13 @@ static int glue_ime_search(const kvz_config *cfg, int *range)
 static struct { uint64_t id; int handle; } g_frames[GLUE_FRAME_SLOTS];
 static int g_frames_next = 0;
 static pthread_mutex_t g_frames_lock = PTHREAD_MUTEX_INITIALIZER;
-static int32_t g_enc_last_num = -1;       /* highest state->frame->num searched with this session */
 
 static kvz_cuda_enc *glue_session(const encoder_state_t *state)
 {
   const encoder_control_t *ctrl = state->encoder_control;
-  const int32_t num = state->frame->num;
-  /* a frame number that went backwards is a new encoder (kvz_api has no hook where the glue could see encoder_close):
-   * the session and what it cached of the old encoder's pictures are dropped */
-  if (g_enc && g_enc_ctrl == ctrl && num >= g_enc_last_num) {
-    if (num > g_enc_last_num) g_enc_last_num = num;
-    return g_enc;
-  }
+  if (g_enc && g_enc_ctrl == ctrl) return g_enc;       /* the session lives as long as its encoder (kvz_glue_api.c) */
   pthread_mutex_lock(&g_enc_lock);
-  if (!g_enc || g_enc_ctrl != ctrl || num < g_enc_last_num) {
+  if (!g_enc || g_enc_ctrl != ctrl) {
     static int registered = 0;
     glue_close_session();
     pthread_mutex_lock(&g_frames_lock);
@@ -85,9 +86,11 @@ static kvz_cuda_enc *glue_session(const encoder_state_t *state)
     pthread_mutex_unlock(&g_frames_lock);
     const kvz_config *cfg = &ctrl->cfg;
     /* what the device search does not reproduce is refused, loudly -- never searched on the CPU instead */
-    if (cfg->owf != 0)
-      kvz_glue_die("KVZ_CUDA_MODE=batch needs --owf 0: with overlapped frames a reference picture is still being "
-                   "reconstructed while the next frame searches it (encoderstate.c:751-804), the session uploads whole pictures");
+    if (cfg->owf != 0 && (cfg->tiles_width_count > 1 || cfg->tiles_height_count > 1))
+      kvz_glue_die("KVZ_CUDA_MODE=batch: --owf > 0 together with --tiles is not supported (pictures in flight are brought "
+                   "to the device by the CTU dependencies of one wavefront, encoderstate.c:786-801)");
+    if (cfg->owf != 0 && !cfg->wpp)
+      kvz_glue_die("KVZ_CUDA_MODE=batch: --owf > 0 needs --wpp (without it the motion vectors into a picture in flight are not restricted)");
     if (cfg->mv_rdo) kvz_glue_die("--mv-rdo (kvz_calc_mvd_cost_cabac, rdo.c:908) is not on the device");
     if (cfg->smp_enable || cfg->amp_enable) kvz_glue_die("--smp / --amp PU shapes (4 and 12 sample sides) are not searched on the device");
     if (ctrl->bitdepth != 8) kvz_glue_die("the encoder-session face is 8-bit only");
@@ -105,7 +108,6 @@ static kvz_cuda_enc *glue_session(const encoder_state_t *state)
     g_enc = kvz_cuda_enc_open(&c);
     if (!g_enc) kvz_glue_die("kvz_cuda_enc_open");
     g_enc_ctrl = ctrl;
-    g_enc_last_num = num;
     if (!registered) { atexit(glue_close_session); registered = 1; }
   }
   pthread_mutex_unlock(&g_enc_lock);
@@ -186,6 +188,15 @@ static int glue_frame_handle(kvz_cuda_enc *enc, const encoder_state_t *state)
       f.refs[r].luma = im->y; f.refs[r].stride = im->stride; f.refs[r].poc = ref->pocs[r];
       f.refs[r].key = (uint64_t)(uintptr_t)im;
       f.refs[r].mv_hints = hints; f.refs[r].n_mv_hints = n_hints;
+      /* still being reconstructed?  the owf previous encoder states are the frames that can be (kvazaar.c:96-126) */
+      const encoder_state_t *ps = state;
+      for (int k = 0; k < state->encoder_control->cfg.owf; k++) {
+        ps = ps->previous_encoder_state;
+        if (ps == state) break;
+        /* a tile-level state holds a sub-image of the picture (encoderstate.c:869-903): compare the owners of the samples */
+        const kvz_picture *prec = ps->tile->frame->rec;
+        if (prec && (prec == im || prec->base_image == im->base_image)) f.refs[r].in_flight = 1;
+      }
     }
     handle = kvz_cuda_enc_frame_begin(enc, &f);
     free(hints);

@@ -33,6 +33,13 @@ CASES = {
     "tiles_2x2_full16": (416, 240, 9, 2, "--preset medium --me full16 --gop 8 -r 2 --tiles 2x2 --owf 0"),
     # a picture that is not a multiple of 64 in either direction and white noise (worst case for early-outs)
     "odd_size_full16": (200, 136, 9, 5, "--preset medium --me full16 --gop 8 -r 4 --owf 0"),
+    # overlapped wavefront (frames in flight, encoderstate.c:751-804): pictures still being reconstructed are brought to
+    # the device block by block and their SAD maps made per CTU; vectors restricted by fracmv_within_tile
+    "owf2_full32": (416, 240, 17, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 2"),
+    "owf1_full16_bipred": (416, 240, 17, 3, "--preset medium --me full16 --gop 8 -r 3 --bipred --owf 1"),
+    "owf3_lowdelay_hexbs": (416, 240, 16, 1, "--preset fast --gop lp-g4d3t1 --owf 3"),
+    "owf4_odd_size_full8": (200, 136, 17, 5, "--preset medium --me full8 --gop 8 -r 4 --owf 4"),
+    "owf2_1080p_full32": (1920, 1080, 6, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 2"),
     # config 2 itself, first frames
     "c2_1080p_3frames": (1920, 1080, 3, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 0"),
 }

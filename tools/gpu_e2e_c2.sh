@@ -9,6 +9,6 @@ K=kvazaar_b200/host/_build/kvazaar_cuda
 T=$(nproc)
 C=/tmp/kvz_clips; mkdir -p $C
 [ -f $C/c2.yuv ] || python tools/make_clip.py $C/c2.yuv 1920 1080 17 2
-env "$@" KVZ_CUDA_STATS=1 KVZ_CUDA_MODE=batch timeout 900 $K -i $C/c2.yuv --input-res 1920x1080 -o $OUT/c2.hevc \
-  --preset medium --me full32 --gop 8 -r 4 --threads $T --owf 0 -n $N 2>&1 | grep -E "FPS|kvz_|wall"
+env "$@" KVZ_CUDA_STATS=${STATS:-1} KVZ_CUDA_MODE=batch timeout 900 $K -i $C/c2.yuv --input-res 1920x1080 -o $OUT/c2.hevc \
+  --preset medium --me full32 --gop 8 -r 4 --threads ${THREADS:-$T} --owf ${OWF:-0} -n $N 2>&1 | grep -E "FPS|kvz_|wall"
 md5sum $OUT/c2.hevc; rm -f $OUT/c2.hevc
