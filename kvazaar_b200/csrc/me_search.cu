@@ -1798,8 +1798,7 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
     for (int q = 0; q < pu.num_jobs; q++)
       if (!handled[q]) coop_scan_job(cs, f, pu, merge, pj[q], pr + q);
   }
-  __threadfence_block();
-  __syncthreads();
+  __syncthreads();                         // the parked winners (shared memory) are visible to the refinement
   if (timing && threadIdx.x == 0) { t2 = gtime(); if (!t1) t1 = t2; }
 
   // ---- phase 3: refinement.  The references of the PU are refined SIDE BY SIDE, each by its own group of threads,
@@ -1858,7 +1857,7 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
   __syncthreads();
   if (threadIdx.x < pu.num_jobs * (int)(sizeof(kvz_cuda_me_result) / 4))
     reinterpret_cast<uint32_t *>(gres)[threadIdx.x] = reinterpret_cast<const uint32_t *>(sres)[threadIdx.x];
-  __threadfence_system();
+  // (no system fence: the host reads the mapped results after the kernel has completed, which orders them)
   if (timing && threadIdx.x == 0) {
     const unsigned long long t3 = gtime();
     const int m = max((int)pu.w, (int)pu.h), sz = m > 32 ? 3 : m > 16 ? 2 : m > 8 ? 1 : 0;
