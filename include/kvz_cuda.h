@@ -170,7 +170,8 @@ typedef struct kvz_cuda_merge_cand {
 /* one search_pu_inter() call (search_inter.c:1451-1524): a PU and its merge candidates */
 typedef struct kvz_cuda_me_pu {
   int16_t x, y;                 /* luma origin, tile-relative (info->origin) */
-  uint8_t w, h;                 /* multiples of 8, <= 64 */
+  uint8_t w, h;                 /* multiples of 8, <= 64; other shapes (SMP / AMP sides 4, 12) are NOT searched: their jobs
+                                   come back with cost 0xFFFFFFFF and took = 0xFE */
   uint8_t num_merge_cand;
   uint8_t num_jobs;             /* references searched: jobs[first_job .. first_job+num_jobs) in ref_idx order */
   uint32_t first_job;
@@ -207,7 +208,7 @@ typedef struct kvz_cuda_me_mapset {
 
 typedef struct kvz_cuda_me_ref {
   const void *d_ref_padded;     /* border-replicated luma of the reference picture */
-  int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 64 (and what the maps needed) */
+  int32_t ref_pitch, ref_pad;   /* bytes per row; border >= 84 = 64 + 20 (and what the maps needed) */
   int32_t n_mapsets;            /* a job whose windows all lie inside a box set is searched from that box; else each */
   int32_t reserved;             /* window whose centre matches a window set is read from it and every other window
                                    is evaluated on demand (0 sets = everything on demand) */

@@ -304,7 +304,10 @@ static int me_search_common(const kvz_cuda_me_frame *fr, const kvz_cuda_me_pu *d
   memcpy(f.ref_LX, fr->ref_LX, sizeof(f.ref_LX));
   for (int i = 0; i < fr->n_refs; i++) {
     const kvz_cuda_me_ref &r = fr->refs[i];
-    if (!r.d_ref_padded || r.ref_pad < 64 || (r.ref_pitch & 3)) return fail_msg("kvz_cuda_me_search: bad reference plane");
+    // the refinement stages a (w + 20) x (h + 9) window by clamping its ORIGIN into the border: that equals the
+    // per-sample clamp of kvz_get_extended_block (ipol-generic.c:761-781) only with a border of at least 64 + 20
+    if (!r.d_ref_padded || r.ref_pad < 84 || (r.ref_pitch & 3))
+      return fail_msg("kvz_cuda_me_search: bad reference plane (border must be at least 84 samples, pitch a multiple of 4)");
     f.refs[i].plane = (const uint8_t *)r.d_ref_padded; f.refs[i].pitch = r.ref_pitch; f.refs[i].pad = r.ref_pad;
     if (r.n_mapsets < 0 || r.n_mapsets > KVZ_CUDA_MAX_MAPSETS) return fail_msg("kvz_cuda_me_search: bad n_mapsets");
     f.refs[i].n_sets = r.n_mapsets;

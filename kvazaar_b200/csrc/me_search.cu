@@ -1505,6 +1505,14 @@ me_refine_kernel(const __grid_constant__ MeFrame f, const kvz_cuda_me_pu *__rest
   const kvz_cuda_me_pu &pu = pus[pi];
   const bool small = pu.w <= 16 && pu.h <= 16;
   if (small != (S == 16)) return;            // the other instantiation owns this PU
+  if ((pu.w | pu.h) & 7) {                   // sides 4 / 12 (SMP / AMP): the 4-sample SATD strips are not implemented
+    for (int q = g.tid; q < pu.num_jobs; q += G) {
+      kvz_cuda_me_result r = {};
+      r.cost = 0xFFFFFFFFu; r.took = 0xFE;
+      results[pu.first_job + q] = r;
+    }
+    return;
+  }
 
   // stage the PU's source block (pitch 64) and its merge candidates
   for (int i = g.tid; i < pu.h * (pu.w >> 2); i += G) {
@@ -1806,6 +1814,14 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
   // references in order and lets the carry pick (refine_finish).  A 64-wide PU needs the whole CTA per reference. ----
   __shared__ RefineBoth both[KVZ_CUDA_MAX_REFS];
   const int msz = max((int)pu.w, (int)pu.h);
+  if ((pu.w | pu.h) & 7) {                   // sides 4 / 12 (SMP / AMP): the 4-sample SATD strips are not implemented
+    if (threadIdx.x < pu.num_jobs) {
+      kvz_cuda_me_result r = {};
+      r.cost = 0xFFFFFFFFu; r.took = 0xFE;
+      gres[threadIdx.x] = r;
+    }
+    return;
+  }
   auto stage_cur = [&](uint8_t *dst, int pitch, int tid, int nthreads) {
     for (int i = tid; i < pu.h * (pu.w >> 2); i += nthreads) {
       const int r = i / (pu.w >> 2), c = i % (pu.w >> 2);

@@ -72,10 +72,9 @@ def window_centres(pus, jobs, n_refs, max_sets=3):
 
 
 class MePipeline:
-    # dram__bytes_read.sum + dram__bytes_write.sum of the dense SAD launch of one step (ime_sad_multi_kernel, the four
-    # boxes of the default 1080p / full32 / 4-reference workload), from profiles/r01e_prof_sad_summary.txt
-    # (ncu --set full): 17.9 MB read + 2082.6 MB written
-    NCU_TRAFFIC_BYTES = 2100454000
+    # where the DRAM traffic of the dense SAD launch of one step was last measured (ncu --set full); bench lines name the
+    # file instead of repeating a number as if it were measured in their run
+    NCU_TRAFFIC_SOURCE = "profiles/r01e_prof_sad_summary.txt: 17.9 MB read + 2082.6 MB written for the four r01 boxes"
 
     def __init__(self, width, height, rng, n_refs, lambda_sqrt=27.0, fme_level=4, device="cuda", use_boxes=True):
         """use_boxes: one box of displacements per reference that covers the zero window and the frequent
@@ -266,5 +265,3 @@ class MePipeline:
             self.padded[r].fill_from(self.refs[r])
         return self.time_stage(self.sad_maps, iters)
 
-    def kernel_time_ms(self, name):
-        return 0.0

@@ -111,7 +111,7 @@ def oracle_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sq
 
 
 def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_i, use_maps=True, centres=(), box=None,
-               fused=False, **cfg):
+               fused=False, pad=None, **cfg):
     """The CUDA path through the C ABI for the same inputs (numpy in, numpy out).
     centres: extra square-window map sets; box: (x0, y0, n_dx, n_dy) of one box map set per reference
     (jobs whose windows all lie inside it are searched from the box); fused: kvz_cuda_me_search_fused (one CTA per PU)."""
@@ -122,7 +122,7 @@ def gpu_search(pus, jobs, cur, refs, width, height, rng, fme_level, lambda_sqrt_
     max_c = max([0] + [max(abs(c[0]), abs(c[1])) for c in centres])
     ime = kb.ImeSearch(width, height, rng, max_center=max_c)
     bx = kb.ImeBoxSearch(width, height, box) if box is not None else None
-    pad = max(ime.pad, bx.pad if bx else 0)
+    pad = pad if pad is not None else max(ime.pad, bx.pad if bx else 0)      # pad: explicit border (no dense maps then)
     planes, maps = [], []
     for r in refs:
         pp = kb.PaddedPlane(width, height, pad).fill_from(torch.from_numpy(r).cuda())

@@ -13,13 +13,14 @@ pytestmark = pytest.mark.gpu
 
 
 def _run(width, height, rng, fme, n_refs, count, seed, box=None, use_maps=True, sizes=(8, 16, 32, 64), far_prob=0.05,
-         mv_span=None, **cfg):
+         mv_span=None, pad=None, **cfg):
     rs = np.random.default_rng(seed)
     f = kvzlibs.synth_luma(seed, width, height, n_refs + 1)
     cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
     pus, jobs = me_oracle.random_pus(rs, width, height, n_refs, count, sizes=sizes, mv_span=mv_span or rng, far_prob=far_prob)
     lam = int(rs.integers(3, 45))
-    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps, box=box, fused=True, **cfg)
+    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, fme, lam, use_maps=use_maps, box=box, fused=True, pad=pad,
+                               **cfg)
     want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, fme, lam, **cfg)
     me_oracle.assert_results_equal(got, want, pus)
     return got
@@ -87,3 +88,24 @@ def test_equals_the_three_launch_form_on_a_batch():
     a = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, 4, 27, box=(-32, -24, 72, 57))
     b = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, 4, 27, box=(-32, -24, 72, 57), fused=True)
     me_oracle.assert_results_equal(b, a, pus)
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_minimum_border_with_vectors_far_outside(fused):
+    """kvz_cuda_me_search accepts reference borders from 84 samples (64 + the 20 the refinement's window adds): with
+    64-wide PUs and merge candidates hundreds of samples outside the picture the staged windows must still equal the
+    per-sample clamp of kvz_get_extended_block"""
+    width, height, rng, n_refs = 256, 192, 8, 2
+    rs = np.random.default_rng(91)
+    f = kvzlibs.synth_luma(91, width, height, n_refs + 1)
+    cur, refs = f[n_refs], [f[n_refs - 1 - i] for i in range(n_refs)]
+    pus, jobs = me_oracle.random_pus(rs, width, height, n_refs, 40, sizes=(32, 64), mv_span=rng, far_prob=0.6)
+    got = me_oracle.gpu_search(pus, jobs, cur, refs, width, height, rng, 4, 23, use_maps=False, fused=fused, pad=84)
+    want = me_oracle.oracle_search(pus, jobs, cur, refs, width, height, rng, 4, 23)
+    me_oracle.assert_results_equal(got, want, pus)
+
+
+def test_border_below_84_is_refused():
+    from kvazaar_b200 import capi
+    with pytest.raises(capi.KvzCudaError, match="border must be at least 84"):
+        _run(200, 136, 8, 2, 1, 4, 92, use_maps=False, pad=80)

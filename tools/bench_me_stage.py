@@ -1,5 +1,7 @@
 #!/usr/bin/env python
-"""bench.py -- the hot path of BASELINE.json config 2 on B200: full-search motion estimation
+"""tools/bench_me_stage.py -- round 1's bench.py (the headline bench is now the encode, /bench.py): the flat ME stage
+of BASELINE.json config 2 on B200 over PRE-MADE candidates (every PU the same merge / AMVP candidates: the best case of
+the kernels, not an encode): full-search motion estimation
 of 1920x1080 8-bit frames (--me full32, -r 4: every 8x8/16x16/32x32/64x64 PU of the frame
 against 4 reference pictures, 65x65 integer candidates each).
 
@@ -238,11 +240,17 @@ def run_ours(args):
     from kvazaar_b200 import shard
     counter = [0]
 
+    published = torch.empty_like(pipe.refs[0]) if world > 1 else None
+
     def exchange():
-        # the one exchange step of the sharded pipeline: the rank that reconstructed the
-        # newest reference publishes its luma plane to all ranks over NCCL/NVLink
+        # the one exchange step of the sharded pipeline: the rank that reconstructed the newest
+        # reference publishes its luma plane to all ranks over NCCL/NVLink.  It arrives in a buffer of its own:
+        # the host-buffer steps upload into pipe.refs[] on another stream, which a broadcast into the same
+        # tensor would race with (the published plane is what a frame-sharded encoder would search next)
         if world > 1:
-            shard.publish_reference(pipe.refs[0], src=counter[0] % world)
+            if counter[0] % world == rank:
+                published.copy_(pipe.refs[0])
+            shard.publish_reference(published, src=counter[0] % world)
             counter[0] += 1
 
     def step_resident():
@@ -326,7 +334,7 @@ def run_ours(args):
     achieved_ops = abs_diffs / (sad_ms * 1e-3)
     step_ms = ms / args.steps
     kernel = "ime_sad_multi_kernel (boxes of all references, one launch)" if pipe.use_boxes else "ime_sad_dense_kernel<32>"
-    traffic = pipe.NCU_TRAFFIC_BYTES if (pipe.use_boxes and world >= 1) else None    # captured for the default (box) launches
+    traffic = None                                    # not measured in this run; see roofline.traffic_source
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
@@ -363,7 +371,7 @@ def run_ours(args):
                      "frac": achieved_ops / int_peak,
                      "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",
                      "algorithmic_abs_diffs": abs_diffs, "launches": n_sad, "ms_per_launch": sad_ms / n_sad,
-                     "traffic": traffic},
+                     "traffic": traffic, "traffic_source": pipe.NCU_TRAFFIC_SOURCE},
         "roofline_hbm": {"kernel": kernel, "bound": "hbm",
                          "achieved": map_bytes / (sad_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": map_bytes / (sad_ms * 1e-3) / 1e9 / hbm_peak,
