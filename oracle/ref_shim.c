@@ -741,3 +741,76 @@ int ref_shim_mv_cand(const ref_cand_frame *f, int x, int y, int w, int h, int re
   cand_env_free(e, f);
   return 1;
 }
+
+/* ---- config 5: speed loops over the selected strategies, in the shape of tests/speed_tests.c:144-303 (one thread, a
+ * buffer of `blocks` contiguous n x n blocks walked `reps` times).  Returns the seconds the walks took; 0 on a bad
+ * request.  what: 0 sad_NxN, 1 satd_NxN, 2 dct, 3 idct, 4 dct + quant (sign hiding on), 5 quarter-pel luma
+ * interpolation of an n x n block (both fractions non-zero) ---- */
+#include <time.h>
+#include "strategies/strategies-picture.h"
+#include "strategies/strategies-ipol.h"
+
+double ref_shim_speed(int what, int n, int blocks, int reps)
+{
+  const size_t nn = (size_t)n * n;
+  if (blocks <= 0 || reps <= 0) return 0.0;
+  struct timespec t0, t1;
+  unsigned sink = 0;
+  if (what == 0 || what == 1) {
+    cost_pixel_nxn_func *fn = what == 0 ? kvz_pixels_get_sad_func(n) : kvz_pixels_get_satd_func(n);
+    if (!fn) return 0.0;
+    kvz_pixel *a = NULL, *b = NULL;
+    if (posix_memalign((void **)&a, 64, nn * blocks) || posix_memalign((void **)&b, 64, nn * blocks)) return 0.0;
+    for (size_t i = 0; i < nn * blocks; i++) { a[i] = (kvz_pixel)(i * 7 + (i >> 5)); b[i] = (kvz_pixel)(i * 13 + (i >> 3)); }
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (int r = 0; r < reps; r++)
+      for (int k = 0; k < blocks; k++) sink += fn(a + k * nn, b + k * nn);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    free(a); free(b);
+  } else if (what >= 2 && what <= 4) {
+    if (n > 32) return 0.0;
+    dct_func *fn = what == 3 ? kvz_get_idct_func((int8_t)n, COLOR_Y, CU_INTER) : kvz_get_dct_func((int8_t)n, COLOR_Y, CU_INTER);
+    if (!fn) return 0.0;
+    int16_t *in = NULL, *out = NULL, *q = NULL;
+    if (posix_memalign((void **)&in, 64, 2 * nn * blocks) || posix_memalign((void **)&out, 64, 2 * nn * blocks) ||
+        posix_memalign((void **)&q, 64, 2 * nn * blocks)) return 0.0;
+    for (size_t i = 0; i < nn * blocks; i++) in[i] = (int16_t)((int)((i * 31 + (i >> 4)) % 121) - 60);
+    ref_q_cfg c; memset(&c, 0, sizeof(c));
+    c.qp = 32; c.signhide = 1;
+    fake_qenv *e = qenv_make(&c);
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (int r = 0; r < reps; r++)
+      for (int k = 0; k < blocks; k++) {
+        fn(KVZ_BIT_DEPTH, in + k * nn, out + k * nn);
+        if (what == 4) kvz_quant(&e->state, out + k * nn, q + k * nn, n, n, 0, 0, CU_INTER);
+      }
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    sink += (unsigned)out[0] + (unsigned)q[0];
+    qenv_free(e);
+    free(in); free(out); free(q);
+  } else if (what == 5) {
+    /* blocks cut from one plane `stride` wide with the 8-tap margins round them */
+    const int stride = 4096, rows = n + 8;
+    const int per_row = stride / (n + 8);
+    const int plane_rows = (blocks / per_row + 1) * rows;
+    kvz_pixel *src = NULL, *dst = NULL;
+    if (posix_memalign((void **)&src, 64, (size_t)stride * plane_rows) || posix_memalign((void **)&dst, 64, nn * blocks)) return 0.0;
+    for (size_t i = 0; i < (size_t)stride * plane_rows; i++) src[i] = (kvz_pixel)(i * 11 + (i >> 7));
+    encoder_control_t *ctrl = calloc(1, sizeof(*ctrl));
+    ctrl->bitdepth = KVZ_BIT_DEPTH;
+    const int16_t mv[2] = { 1, 3 };
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (int r = 0; r < reps; r++)
+      for (int k = 0; k < blocks; k++) {
+        kvz_pixel *p = src + (size_t)(k / per_row) * rows * stride + (size_t)(k % per_row) * (n + 8) + 4 * stride + 4;
+        kvz_sample_quarterpel_luma(ctrl, p, (int16_t)stride, n, n, dst + k * nn, (int16_t)n, 1, 1, mv);
+      }
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    sink += dst[0];
+    free(ctrl); free(src); free(dst);
+  } else {
+    return 0.0;
+  }
+  volatile unsigned keep = sink; (void)keep;
+  return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}
