@@ -83,13 +83,25 @@ KVZ_CUDA_API int kvz_cuda_enc_search_pu(kvz_cuda_enc *enc, int frame_handle, int
                                         const kvz_cuda_me_pu *pu, const kvz_cuda_me_job *jobs,
                                         kvz_cuda_me_result *results);
 
+/* The same search split in two, so that a host can have searches in flight while it does its own work (residual
+ * coding, intra search) and can launch a PU ahead of time with the candidates it EXPECTS the PU to get: begin sends
+ * 1..4 PUs of one CTU in one launch and returns at once; end blocks until PU `pu_index` of that launch has its results.
+ * `jobs` holds KVZ_CUDA_MAX_REFS records per PU (PU i's jobs at jobs[i * KVZ_CUDA_MAX_REFS ..], pus[i].num_jobs used).
+ * A host that launched ahead must compare the PU and job records it sent with the real ones when the PU's turn comes
+ * and search again when they differ -- the device computes exactly what it is given (kvazaar_b200/host/ does this, so
+ * decisions stay the reference's).  Tickets belong to the calling thread; a thread's 32nd-next begin reuses a ticket's
+ * slot, after which end() on it fails ("expired").  Nothing in the reference corresponds to the split. */
+KVZ_CUDA_API int kvz_cuda_enc_search_begin(kvz_cuda_enc *enc, int frame_handle, int lambda_sqrt_i, int n_pus,
+                                           const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs, int *ticket);
+KVZ_CUDA_API int kvz_cuda_enc_search_end(kvz_cuda_enc *enc, int ticket, int pu_index, kvz_cuda_me_result *results);
+
 /* Optional: put the source luma of the picture with presentation number `pts` into device memory ahead of time
  * (a host whose input is already on the device, or a benchmark that wants its inputs resident before the timed
  * region).  kvz_cuda_enc_frame_begin then uses it instead of uploading; it is dropped when its frame has begun.
  * Replaces nothing in the reference. */
 KVZ_CUDA_API int kvz_cuda_enc_preload_source(kvz_cuda_enc *enc, int64_t pts, const void *luma, int32_t stride);
 
-/* counters since open: stats[0] frames begun, [1] PU searches, [2] reference planes uploaded, [3] bytes of SAD maps
+/* counters since open: stats[0] frames begun, [1] PU searches launched (including the ones launched ahead), [2] reference planes uploaded, [3] bytes of SAD maps
  * of the last frame, [4] map displacements of the last frame (sum over references of n_dx * n_dy),
  * [5] reference-jobs searched, [6] jobs not served entirely from a box (some window evaluated on demand: host-side
  * estimate from the candidate list) */

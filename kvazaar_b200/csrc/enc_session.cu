@@ -6,6 +6,8 @@
 // references are bordered and ONE launch produces the dense SAD maps of every PU of the frame against every
 // reference (ime_sad.cu); each per-PU call then only prices / scans those maps and refines the winner
 // (me_search.cu) on the calling thread's own stream, so the calls of the wavefront's CTU rows overlap on the GPU.
+#include <sched.h>
+#include <string.h>
 #include <time.h>
 
 #include <algorithm>
@@ -69,20 +71,44 @@ struct FrameCtx {
 };
 
 // per calling thread: a stream and the staging of one PU, its jobs and results
+// Per calling thread: kStreams streams and a ring of kSlots launch slots in pinned, mapped host memory.  A slot holds the
+// results of the up to kMePuArgsMax PUs of one launch and one completion word per PU; slot i always uses stream
+// i % kStreams, so a slot is not written by two launches at once.  A ticket = slot | generation << 8.
+constexpr int kStreams = 4, kSlots = 32;
+constexpr size_t kSlotResults = (size_t)kMePuArgsMax * KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result);
+constexpr size_t kSlotBytes = kSlotResults + 64;                      // + the completion words on a line of their own
+constexpr size_t kStageBytes = kSlots * kSlotBytes;
+
 struct Worker {
   int device = -1;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t done = nullptr;         // KVZ_CUDA_BLOCKING_SYNC: the thread sleeps on this instead of spinning
+  cudaStream_t streams[kStreams] = {};
+  cudaEvent_t ctu_ready = nullptr;    // --owf: the blocks and maps ctu_begin prepared on streams[0]
   uint8_t *h = nullptr, *d = nullptr;
-  uint64_t seen_ctx = ~0ull;
   const void *seen_enc = nullptr;
-  int seen_ctu = -1;                  // the CTU of seen_ctx this thread last prepared (ctu_begin)
+  uint64_t seen_ctx[kStreams];        // the frame context whose `ready` event the stream has waited for
+  int seen_ctu[kStreams];             // the CTU of that context whose ctu_ready the stream has waited for
+  int cur_ctu = -1;                   // the CTU this thread last prepared (ctu_begin)
+  uint64_t cur_ctx = ~0ull;
+  uint32_t next_slot = 0;
+  uint32_t gen[kSlots] = {};          // generation of the slot's last launch (the value its completion words receive)
+  uint8_t n_pus[kSlots] = {};
+  uint8_t n_jobs[kSlots][kMePuArgsMax] = {};
+  uint8_t size_class[kSlots][kMePuArgsMax] = {};
 };
 thread_local Worker t_worker;
 
-constexpr size_t kOffJobs = 128, kOffResults = kOffJobs + KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_job);
-constexpr size_t kStageBytes = kOffResults + KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result);
-static_assert(sizeof(kvz_cuda_me_pu) <= kOffJobs, "staging layout");
+// How a thread waits for a search it needs (KVZ_CUDA_WAIT): "spin" (default) = poll the completion word the kernel
+// writes into mapped memory after its results; "yield" = the same with sched_yield() between polls, for hosts that run
+// more worker threads than cores.
+enum WaitMode { kWaitSpin = 1, kWaitYield = 2 };
+WaitMode wait_mode()
+{
+  static const WaitMode m = [] {
+    const char *v = getenv("KVZ_CUDA_WAIT");
+    return v && !strcmp(v, "yield") ? kWaitYield : kWaitSpin;
+  }();
+  return m;
+}
 
 }  // namespace
 }  // namespace kvz
@@ -256,15 +282,18 @@ int ctu_begin(kvz_cuda_enc *e, FrameCtx *ctx, int cx, int cy, cudaStream_t strea
 bool worker_ready(kvz_cuda_enc *e)
 {
   Worker &w = t_worker;
-  if (w.device == e->cfg.device && w.stream) return true;
+  if (w.device == e->cfg.device && w.streams[0]) return true;
   if (cudaSetDevice(e->cfg.device) != cudaSuccess) return false;      // every calling thread binds the session's device
-  if (cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking) != cudaSuccess) return false;
-  if (getenv("KVZ_CUDA_BLOCKING_SYNC") &&
-      cudaEventCreateWithFlags(&w.done, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) return false;
-  // pinned AND mapped: the kernel reads the PU and its jobs from, and writes its results to, this host buffer
-  // directly (one small PCIe read / write per call instead of two copy commands)
+  for (int i = 0; i < kStreams; i++) {
+    if (cudaStreamCreateWithFlags(&w.streams[i], cudaStreamNonBlocking) != cudaSuccess) return false;
+    w.seen_ctx[i] = ~0ull; w.seen_ctu[i] = -1;
+  }
+  if (cudaEventCreateWithFlags(&w.ctu_ready, cudaEventDisableTiming) != cudaSuccess) return false;
+  // pinned AND mapped: the kernel writes its results and completion words straight into this host buffer (one small
+  // PCIe write per PU instead of a copy command); the PUs and their jobs travel as kernel arguments
   if (cudaHostAlloc(&w.h, kStageBytes, cudaHostAllocMapped) != cudaSuccess) return false;
   if (cudaHostGetDevicePointer(reinterpret_cast<void **>(&w.d), w.h, 0) != cudaSuccess) return false;
+  memset(w.h, 0, kStageBytes);
   w.device = e->cfg.device;
   return true;
 }
@@ -534,69 +563,142 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   return handle;
 }
 
-int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const kvz_cuda_me_pu *pu,
-                           const kvz_cuda_me_job *jobs, kvz_cuda_me_result *results)
+int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, int n_pus, const kvz_cuda_me_pu *pus,
+                              const kvz_cuda_me_job *jobs, int *ticket)
 {
-  if (!e || !pu || !jobs || !results) return fail_enc("kvz_cuda_enc_search_pu: null argument");
+  if (!e || !pus || !jobs || !ticket) return fail_enc("kvz_cuda_enc_search_begin: null argument");
+  if (n_pus < 1 || n_pus > kMePuArgsMax) return fail_enc("kvz_cuda_enc_search_begin: 1..4 PUs per launch");
   FrameCtx *ctx = nullptr;
   {
     std::lock_guard<std::mutex> guard(e->lock);
     if (handle >= 0 && handle < (int)e->ctxs.size()) ctx = e->ctxs[handle];
     if (ctx) ctx->inflight++;
   }
-  if (!ctx || ctx->id == ~0ull) { if (ctx) ctx->inflight--; return fail_enc("kvz_cuda_enc_search_pu: bad frame handle"); }
+  if (!ctx || ctx->id == ~0ull) { if (ctx) ctx->inflight--; return fail_enc("kvz_cuda_enc_search_begin: bad frame handle"); }
   struct Release { FrameCtx *c; ~Release() { c->inflight--; } } release{ctx};
-  const int nj = pu->num_jobs;
-  if (nj < 1 || nj > KVZ_CUDA_MAX_REFS) return fail_enc("kvz_cuda_enc_search_pu: bad num_jobs");
-  if ((pu->w & 7) || (pu->h & 7) || pu->w == 0 || pu->h == 0 || pu->w > 64 || pu->h > 64)
-    return fail_enc("kvz_cuda_enc_search_pu: PU sides must be multiples of 8, at most 64 (SMP/AMP shapes 4, 12 are not searched here)");
-  for (int i = 0; i < nj; i++)
-    if (jobs[i].ref_idx >= ctx->f.n_refs) return fail_enc("kvz_cuda_enc_search_pu: ref_idx outside the frame's reference list");
-  if (!worker_ready(e)) return fail("per-thread stream / staging", cudaGetLastError(), __FILE__, __LINE__);
-  Worker &w = t_worker;
-  struct timespec ts0;
-  bool all_in_box = true;
-  if (e->timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
-  if (ctx->f.ime_search == KVZ_CUDA_IME_FULL)
+  const int ctu_x = pus[0].x >> 6, ctu_y = pus[0].y >> 6;
+  unsigned long long n_jobs_total = 0;
+  for (int p = 0; p < n_pus; p++) {
+    const kvz_cuda_me_pu &pu = pus[p];
+    const int nj = pu.num_jobs;
+    if (nj < 1 || nj > KVZ_CUDA_MAX_REFS) return fail_enc("kvz_cuda_enc_search_begin: bad num_jobs");
+    if ((pu.w & 7) || (pu.h & 7) || pu.w == 0 || pu.h == 0 || pu.w > 64 || pu.h > 64)
+      return fail_enc("kvz_cuda_enc_search_begin: PU sides must be multiples of 8, at most 64 (SMP/AMP shapes 4, 12 are not searched here)");
+    if ((pu.x >> 6) != ctu_x || (pu.y >> 6) != ctu_y) return fail_enc("kvz_cuda_enc_search_begin: the PUs of one launch must lie in one CTU");
     for (int i = 0; i < nj; i++)
-      if (!job_in_box(*ctx, e->cfg.range, *pu, jobs[i])) { all_in_box = false; e->stats[6]++; }
+      if (jobs[(size_t)p * KVZ_CUDA_MAX_REFS + i].ref_idx >= ctx->f.n_refs)
+        return fail_enc("kvz_cuda_enc_search_begin: ref_idx outside the frame's reference list");
+    n_jobs_total += (unsigned long long)nj;
+  }
+  if (!worker_ready(e)) return fail("per-thread streams / staging", cudaGetLastError(), __FILE__, __LINE__);
+  Worker &w = t_worker;
+  if (e->timing && ctx->f.ime_search == KVZ_CUDA_IME_FULL)
+    for (int p = 0; p < n_pus; p++)
+      for (int i = 0; i < pus[p].num_jobs; i++)
+        if (!job_in_box(*ctx, e->cfg.range, pus[p], jobs[(size_t)p * KVZ_CUDA_MAX_REFS + i])) e->stats[6]++;
 
   const uint64_t tag = ((uint64_t)handle << 48) ^ ctx->id;
-  if (w.seen_ctx != tag || w.seen_enc != e) {              // first call of this thread for this frame: wait for its maps
-    KVZ_CUDA_TRY(cudaStreamWaitEvent(w.stream, ctx->ready, 0));
-    w.seen_ctx = tag; w.seen_enc = e; w.seen_ctu = -1;
+  if (w.seen_enc != e || w.cur_ctx != tag) {
+    w.seen_enc = e; w.cur_ctx = tag; w.cur_ctu = -1;
+    for (int i = 0; i < kStreams; i++) { w.seen_ctx[i] = ~0ull; w.seen_ctu[i] = -1; }
   }
-  if (ctx->n_partial > 0) {                                // --owf: references in flight are prepared CTU by CTU
-    const int cx = pu->x >> 6, cy = pu->y >> 6, ctu = cy * ctx->f.ctus_x + cx;
-    if (w.seen_ctu != ctu) {
-      if (!ctu_begin(e, ctx, cx, cy, w.stream)) return 0;
-      w.seen_ctu = ctu;
-    }
+  const int ctu = ctu_y * ctx->f.ctus_x + ctu_x;
+  if (ctx->n_partial > 0 && w.cur_ctu != ctu) {            // --owf: references in flight are prepared CTU by CTU
+    if (w.seen_ctx[0] != tag) { KVZ_CUDA_TRY(cudaStreamWaitEvent(w.streams[0], ctx->ready, 0)); w.seen_ctx[0] = tag; }
+    if (!ctu_begin(e, ctx, ctu_x, ctu_y, w.streams[0])) return 0;
+    KVZ_CUDA_TRY(cudaEventRecord(w.ctu_ready, w.streams[0]));
+    w.cur_ctu = ctu; w.seen_ctu[0] = ctu;
+  }
+  const uint32_t slot = w.next_slot++ % kSlots;
+  const int si = (int)(slot % kStreams);
+  cudaStream_t stream = w.streams[si];
+  if (w.seen_ctx[si] != tag) {                               // first launch of this stream for this frame: wait for its maps
+    KVZ_CUDA_TRY(cudaStreamWaitEvent(stream, ctx->ready, 0));
+    w.seen_ctx[si] = tag; w.seen_ctu[si] = -1;
+  }
+  if (ctx->n_partial > 0 && w.seen_ctu[si] != ctu) {
+    KVZ_CUDA_TRY(cudaStreamWaitEvent(stream, w.ctu_ready, 0));
+    w.seen_ctu[si] = ctu;
   }
   MeFrame f = ctx->f;
   f.lambda_sqrt_i = lambda_sqrt_i;
-  kvz_cuda_me_pu one = *pu;
-  one.first_job = 0;
-  // the PU and its jobs go in the launch itself; the results come back through the mapped host buffer
-  if (!launch_me_search_pu(f, nullptr, nullptr, reinterpret_cast<kvz_cuda_me_result *>(w.d + kOffResults), 1, w.stream,
-                           &one, jobs)) return 0;
-  if (w.done) {
-    KVZ_CUDA_TRY(cudaEventRecord(w.done, w.stream));
-    KVZ_CUDA_TRY(cudaEventSynchronize(w.done));
-  } else {
-    KVZ_CUDA_TRY(cudaStreamSynchronize(w.stream));
+  const uint32_t gen = ++w.gen[slot];
+  uint8_t *dslot = w.d + (size_t)slot * kSlotBytes;
+  // the PUs and their jobs go in the launch itself; results and completion words come back through the mapped slot
+  if (!launch_me_search_pu(f, nullptr, nullptr, reinterpret_cast<kvz_cuda_me_result *>(dslot), n_pus, stream, pus, jobs,
+                           reinterpret_cast<uint32_t *>(dslot + kSlotResults), gen)) return 0;
+  w.n_pus[slot] = (uint8_t)n_pus;
+  for (int p = 0; p < n_pus; p++) {
+    w.n_jobs[slot][p] = pus[p].num_jobs;
+    const int m = std::max(pus[p].w, pus[p].h);
+    w.size_class[slot][p] = m > 32 ? 3 : m > 16 ? 2 : m > 8 ? 1 : 0;
   }
-  memcpy(results, w.h + kOffResults, (size_t)nj * sizeof(kvz_cuda_me_result));
-  e->stats[1]++;
-  e->stats[5] += (unsigned long long)nj;
-  e->meas[1] += sizeof(kvz_cuda_me_pu) + (unsigned long long)nj * sizeof(kvz_cuda_me_job);
+  *ticket = (int)(slot | (gen & 0x7FFFFFu) << 8);
+  e->stats[1] += (unsigned long long)n_pus;
+  e->stats[5] += n_jobs_total;
+  e->meas[1] += (unsigned long long)n_pus * sizeof(kvz_cuda_me_pu) + n_jobs_total * sizeof(kvz_cuda_me_job);
+  return 1;
+}
+
+int kvz_cuda_enc_search_end(kvz_cuda_enc *e, int ticket, int pu_index, kvz_cuda_me_result *results)
+{
+  if (!e || !results || ticket < 0) return fail_enc("kvz_cuda_enc_search_end: bad argument");
+  Worker &w = t_worker;
+  if (!w.h) return fail_enc("kvz_cuda_enc_search_end: this thread began no search");
+  const uint32_t slot = (uint32_t)ticket & 0xFFu, gen = w.gen[slot % kSlots];
+  if (slot >= (uint32_t)kSlots || ((uint32_t)ticket >> 8) != (gen & 0x7FFFFFu))
+    return fail_enc("kvz_cuda_enc_search_end: the ticket has expired (its slot was used by a later launch of this thread)");
+  if (pu_index < 0 || pu_index >= w.n_pus[slot]) return fail_enc("kvz_cuda_enc_search_end: bad pu_index");
+  const uint8_t *hslot = w.h + (size_t)slot * kSlotBytes;
+  const volatile uint32_t *flag = reinterpret_cast<const volatile uint32_t *>(hslot + kSlotResults) + pu_index;
+  const WaitMode wm = wait_mode();
+  struct timespec ts0;
+  const bool timed = e->timing;
+  if (timed) clock_gettime(CLOCK_MONOTONIC, &ts0);
+  for (unsigned spins = 1; *flag != gen; spins++) {
+    if (wm == kWaitYield) sched_yield(); else __builtin_ia32_pause();
+    if ((spins & 0x3FFFF) == 0) {                          // now and then: did the launch die?
+      const cudaError_t st = cudaStreamQuery(w.streams[slot % kStreams]);
+      if (st == cudaSuccess) {
+        if (*flag != gen) return fail_enc("kvz_cuda_enc_search_end: the search finished without reporting");
+        break;
+      }
+      if (st != cudaErrorNotReady) return fail("kvz_cuda_enc_search_end", st, __FILE__, __LINE__);
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  if (timed) {
+    struct timespec ts1;
+    clock_gettime(CLOCK_MONOTONIC, &ts1);
+    const int sz = w.size_class[slot][pu_index];
+    e->t_ns[sz][1] += (unsigned long long)((ts1.tv_sec - ts0.tv_sec) * 1000000000ll + (ts1.tv_nsec - ts0.tv_nsec));
+    e->t_calls[sz][1]++;
+  }
+  const int nj = w.n_jobs[slot][pu_index];
+  memcpy(results, hslot + (size_t)pu_index * KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result), (size_t)nj * sizeof(kvz_cuda_me_result));
   e->meas[2] += (unsigned long long)nj * sizeof(kvz_cuda_me_result);
+  return 1;
+}
+
+int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const kvz_cuda_me_pu *pu,
+                           const kvz_cuda_me_job *jobs, kvz_cuda_me_result *results)
+{
+  if (!e || !pu || !jobs || !results) return fail_enc("kvz_cuda_enc_search_pu: null argument");
+  struct timespec ts0;
+  if (e->timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
+  kvz_cuda_me_job padded[KVZ_CUDA_MAX_REFS];
+  const int nj = pu->num_jobs;
+  if (nj < 1 || nj > KVZ_CUDA_MAX_REFS) return fail_enc("kvz_cuda_enc_search_pu: bad num_jobs");
+  memcpy(padded, jobs, (size_t)nj * sizeof(kvz_cuda_me_job));
+  int ticket = -1;
+  if (!kvz_cuda_enc_search_begin(e, handle, lambda_sqrt_i, 1, pu, padded, &ticket)) return 0;
+  if (!kvz_cuda_enc_search_end(e, ticket, 0, results)) return 0;
   if (e->timing) {
     struct timespec ts1;
     clock_gettime(CLOCK_MONOTONIC, &ts1);
     const int sz = std::max(pu->w, pu->h) > 32 ? 3 : std::max(pu->w, pu->h) > 16 ? 2 : std::max(pu->w, pu->h) > 8 ? 1 : 0;
-    e->t_ns[sz][all_in_box ? 0 : 1] += (unsigned long long)((ts1.tv_sec - ts0.tv_sec) * 1000000000ll + (ts1.tv_nsec - ts0.tv_nsec));
-    e->t_calls[sz][all_in_box ? 0 : 1]++;
+    e->t_ns[sz][0] += (unsigned long long)((ts1.tv_sec - ts0.tv_sec) * 1000000000ll + (ts1.tv_nsec - ts0.tv_nsec));
+    e->t_calls[sz][0]++;
   }
   return 1;
 }
@@ -644,7 +746,7 @@ void kvz_cuda_enc_stats(const kvz_cuda_enc *e, unsigned long long stats[8])
       for (int k = 0; k < 2; k++)
         if (e->t_calls[sz][k].load())
           fprintf(stderr, "kvz_cuda_enc: PU %2d  %-22s %8llu calls  %8.1f us/call\n", 8 << sz,
-                  k ? "some window on demand" : "all windows in the box", e->t_calls[sz][k].load(),
+                  k ? "waited in search_end          " : "blocking search_pu (begin + end)", e->t_calls[sz][k].load(),
                   e->t_ns[sz][k].load() / 1000.0 / e->t_calls[sz][k].load());
 }
 

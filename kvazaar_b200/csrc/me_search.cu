@@ -1730,12 +1730,13 @@ struct PuArgs {
   kvz_cuda_me_pu pu;
   kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
 };
+struct PuArgsN { PuArgs a[kMePuArgsMax]; };     // the PUs of one launch that travel as kernel arguments (CTA i takes a[i])
 
 template <bool ARGS>
 __global__ void __launch_bounds__(kPuThreads)
-me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs args, const kvz_cuda_me_pu *__restrict__ pus,
+me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgsN argsn, const kvz_cuda_me_pu *__restrict__ pus,
              const kvz_cuda_me_job *__restrict__ jobs, kvz_cuda_me_result *results, int n_pus, int box_dx, int box_dy,
-             int timing)
+             int timing, volatile uint32_t *done_flag, uint32_t done_seq)
 {
   unsigned long long t0 = 0, t1 = 0, t2 = 0;
   if (timing && threadIdx.x == 0) t0 = gtime();
@@ -1747,9 +1748,10 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
   // mapped HOST memory (kvz_cuda_enc_search_pu), read once and written once
   __shared__ kvz_cuda_me_pu spu;
   __shared__ kvz_cuda_me_job sjobs[KVZ_CUDA_MAX_REFS];
-  __shared__ kvz_cuda_me_result sres[KVZ_CUDA_MAX_REFS];
+  __shared__ __align__(16) kvz_cuda_me_result sres[KVZ_CUDA_MAX_REFS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (ARGS) {
+    const PuArgs &args = argsn.a[blockIdx.x];
     if (threadIdx.x < sizeof(kvz_cuda_me_pu) / 4)
       reinterpret_cast<uint32_t *>(&spu)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&args.pu)[threadIdx.x];
     if (threadIdx.x < sizeof(sjobs) / 4)
@@ -1772,7 +1774,7 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
   const kvz_cuda_me_pu &pu = spu;
   const kvz_cuda_me_job *pj = sjobs;
   kvz_cuda_me_result *pr = sres;
-  kvz_cuda_me_result *const gres = results + (ARGS ? 0u : spu.first_job);
+  kvz_cuda_me_result *const gres = results + (ARGS ? blockIdx.x * (unsigned)KVZ_CUDA_MAX_REFS : spu.first_job);
 
   // ---- phase 1: integer search ----
   if (f.ime_search != KVZ_CUDA_IME_FULL) {
@@ -1871,9 +1873,16 @@ me_pu_kernel(const __grid_constant__ MeFrame f, const __grid_constant__ PuArgs a
     for (int q = 0; q < pu.num_jobs; q++) refine_finish(f, pu, merge, pj[q], both[q], inter_cost, pr + q);
   }
   __syncthreads();
-  if (threadIdx.x < pu.num_jobs * (int)(sizeof(kvz_cuda_me_result) / 4))
-    reinterpret_cast<uint32_t *>(gres)[threadIdx.x] = reinterpret_cast<const uint32_t *>(sres)[threadIdx.x];
-  // (no system fence: the host reads the mapped results after the kernel has completed, which orders them)
+  static_assert(sizeof(kvz_cuda_me_result) == 16, "one 16-byte store per result");
+  if (threadIdx.x < pu.num_jobs && threadIdx.x < 32)
+    reinterpret_cast<uint4 *>(gres)[threadIdx.x] = reinterpret_cast<const uint4 *>(sres)[threadIdx.x];
+  // A host that polls instead of synchronising the stream (kvz_cuda_enc_search_pu) names a word of mapped memory:
+  // it receives this call's sequence number after the results, behind a system-scope fence.  Without one the host
+  // reads the results after the kernel has completed, which orders them.
+  if (done_flag != nullptr && threadIdx.x < 32) {
+    __syncwarp();
+    if (threadIdx.x == 0) { __threadfence_system(); done_flag[ARGS ? blockIdx.x : 0] = done_seq; }
+  }
   if (timing && threadIdx.x == 0) {
     const unsigned long long t3 = gtime();
     const int m = max((int)pu.w, (int)pu.h), sz = m > 32 ? 3 : m > 16 ? 2 : m > 8 ? 1 : 0;
@@ -1940,11 +1949,12 @@ int me_pu_phase_times(unsigned long long out[4][4])
   return 1;
 }
 
-// every PU by one CTA in ONE launch (me_pu_kernel).  host_pu / host_jobs non-null (n_pus == 1): the PU and its jobs
-// travel as kernel arguments and `pus` / `jobs` are not read; results[0..num_jobs) receives the results.
+// every PU by one CTA in ONE launch (me_pu_kernel).  host_pu / host_jobs non-null (n_pus <= kMePuArgsMax): the PUs and
+// their jobs (KVZ_CUDA_MAX_REFS job records per PU) travel as kernel arguments and `pus` / `jobs` are not read; the
+// results of PU i go to results[i * KVZ_CUDA_MAX_REFS ..], done_flag[i] receives done_seq after them.
 int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
                         kvz_cuda_me_result *results, int n_pus, cudaStream_t stream, const kvz_cuda_me_pu *host_pu,
-                        const kvz_cuda_me_job *host_jobs)
+                        const kvz_cuda_me_job *host_jobs, uint32_t *done_flag, uint32_t done_seq)
 {
   if (n_pus <= 0) return 1;
   int box_dx = 0, box_dy = 0;
@@ -1974,16 +1984,20 @@ int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_c
     if (!use) KVZ_CUDA_TRY(cudaMemcpyToSymbol(g_pu_use_seed, &use, sizeof(int)));
     seed_set = true;
   }
-  PuArgs a;
-  if (host_pu != nullptr && host_jobs != nullptr && n_pus == 1) {
-    a.pu = *host_pu;
-    const int nj = host_pu->num_jobs < KVZ_CUDA_MAX_REFS ? host_pu->num_jobs : KVZ_CUDA_MAX_REFS;
-    memcpy(a.jobs, host_jobs, (size_t)nj * sizeof(kvz_cuda_me_job));
-    if (nj < KVZ_CUDA_MAX_REFS) memset(a.jobs + nj, 0, (size_t)(KVZ_CUDA_MAX_REFS - nj) * sizeof(kvz_cuda_me_job));
-    me_pu_kernel<true><<<1, kPuThreads, smem, stream>>>(f, a, nullptr, nullptr, results, 1, box_dx, box_dy, timing);
+  if (host_pu != nullptr && host_jobs != nullptr) {
+    if (n_pus > kMePuArgsMax) return fail_msg("launch_me_search_pu: too many PUs for the argument form");
+    PuArgsN a;
+    for (int i = 0; i < n_pus; i++) {
+      a.a[i].pu = host_pu[i];
+      a.a[i].pu.first_job = 0;
+      const int nj = host_pu[i].num_jobs < KVZ_CUDA_MAX_REFS ? host_pu[i].num_jobs : KVZ_CUDA_MAX_REFS;
+      memcpy(a.a[i].jobs, host_jobs + (size_t)i * KVZ_CUDA_MAX_REFS, (size_t)nj * sizeof(kvz_cuda_me_job));
+      if (nj < KVZ_CUDA_MAX_REFS) memset(a.a[i].jobs + nj, 0, (size_t)(KVZ_CUDA_MAX_REFS - nj) * sizeof(kvz_cuda_me_job));
+    }
+    me_pu_kernel<true><<<n_pus, kPuThreads, smem, stream>>>(f, a, nullptr, nullptr, results, n_pus, box_dx, box_dy, timing, done_flag, done_seq);
   } else {
-    memset(&a, 0, sizeof(a));
-    me_pu_kernel<false><<<n_pus, kPuThreads, smem, stream>>>(f, a, pus, jobs, results, n_pus, box_dx, box_dy, timing);
+    static const PuArgsN none = {};
+    me_pu_kernel<false><<<n_pus, kPuThreads, smem, stream>>>(f, none, pus, jobs, results, n_pus, box_dx, box_dy, timing, nullptr, 0u);
   }
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();

@@ -6,6 +6,7 @@
 
 namespace kvz {
 
+constexpr int kMePuArgsMax = 4;   // PUs one launch_me_search_pu can carry as kernel arguments
 constexpr int kMeMaxBox = 272;     // largest box side (displacements) kvz_cuda_me_search reads
 
 struct MeMapSet {
@@ -41,10 +42,12 @@ int launch_me_search(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda
                      kvz_cuda_me_result *results, int n_pus, cudaStream_t stream);
 
 // the same, every PU by one CTA in one launch (integer search with any window evaluated from shared memory when no
-// box holds it, then the refinement): the form for one PU at a time
+// box holds it, then the refinement): the form for a few PUs at a time.  host_pu / host_jobs (n_pus <= kMePuArgsMax,
+// KVZ_CUDA_MAX_REFS job records per PU): sent as kernel arguments; PU i's results go to results[i * KVZ_CUDA_MAX_REFS ..]
+// and done_flag[i] (mapped host memory) receives done_seq after them, for a caller that polls instead of synchronising
 int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs,
                         kvz_cuda_me_result *results, int n_pus, cudaStream_t stream, const kvz_cuda_me_pu *host_pu = nullptr,
-                        const kvz_cuda_me_job *host_jobs = nullptr);
+                        const kvz_cuda_me_job *host_jobs = nullptr, uint32_t *done_flag = nullptr, uint32_t done_seq = 0);
 
 int me_pu_phase_times(unsigned long long out[4][4]);
 

@@ -27,6 +27,8 @@
 
 /* ---- the session: one per process ("Only one encoder may be open at a time", src/kvazaar.h:619) ---- */
 static kvz_cuda_enc *g_enc = NULL;
+static uint64_t g_epoch = 0;                 /* bumped when a session opens: launches made under an older one never match */
+static unsigned long long g_spec_cnt[4];     /* PU searches answered by a launch made ahead, searched on the spot, PUs launched ahead, PUs launched */
 static const encoder_control_t *g_enc_ctrl = NULL;
 static pthread_mutex_t g_enc_lock = PTHREAD_MUTEX_INITIALIZER;
 
@@ -39,6 +41,8 @@ static void glue_close_session(void)
       fprintf(stderr, "kvz_cuda_enc: frames %llu, PU searches %llu, reference jobs %llu, reference planes uploaded %llu, "
               "SAD maps of the last frame %.1f MiB (%llu displacements), reference jobs with a window outside the box %llu\n",
               s[0], s[1], s[5], s[2], s[3] / 1048576.0, s[4], s[6]);
+      fprintf(stderr, "kvz_glue: PU searches the host asked for: %llu answered by a launch made ahead, %llu searched on the spot; "
+              "PUs launched %llu, of them ahead of time %llu\n", g_spec_cnt[0], g_spec_cnt[1], g_spec_cnt[3], g_spec_cnt[2]);
     }
     kvz_cuda_enc_close(g_enc);
     g_enc = NULL;
@@ -105,8 +109,11 @@ static kvz_cuda_enc *glue_session(const encoder_state_t *state)
     c.mv_constraint = cfg->mv_constraint;
     c.max_ref_lcu_right = ctrl->max_inter_ref_lcu.right; c.max_ref_lcu_down = ctrl->max_inter_ref_lcu.down;
     if (getenv("KVZ_CUDA_MAP_MBYTES")) c.max_map_mbytes = atoi(getenv("KVZ_CUDA_MAP_MBYTES"));
+    /* every worker thread launches on four streams of its own: give them hardware queues (read when CUDA starts) */
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     g_enc = kvz_cuda_enc_open(&c);
     if (!g_enc) kvz_glue_die("kvz_cuda_enc_open");
+    __atomic_fetch_add(&g_epoch, 1, __ATOMIC_SEQ_CST);
     g_enc_ctrl = ctrl;
     if (!registered) { atexit(glue_close_session); registered = 1; }
   }
@@ -223,6 +230,185 @@ static void glue_list_of(const encoder_state_t *state, int ref_idx, int8_t *ref_
   kvz_glue_die("reference picture in neither list");
 }
 
+/* ---- the inputs of one device search, and searches launched ahead of time ----
+ *
+ * The host walks the CU quadtree in z-order and every kvz_search_cu_inter blocks for the device (~50 us).  Most of
+ * that wait is hidden by launching a PU BEFORE the walk reaches it, with the candidates the PU will get if the
+ * decisions in between turn out as expected: after the search of CU c the next CU of the walk (its next sibling, or
+ * an ancestor's) is launched under the hypothesis "c stays as just searched", together with the chain of top-left
+ * children at the same origin (their neighbours all lie outside the CU, so their candidates are known already).
+ * When the walk arrives, the REAL candidates are derived from the real lcu_t as always and compared, record by
+ * record, with what was sent: equal -> the results are taken (same inputs, same frame state, a deterministic search);
+ * different -> the launch is ignored and the PU is searched now.  Decisions are therefore exactly the reference's;
+ * a wrong guess costs device time only.  KVZ_CUDA_SPECULATE=0 switches it off. */
+typedef struct {
+  kvz_cuda_me_pu pu;
+  kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
+} glue_inputs;
+
+#define GLUE_SPEC_SLOTS 32          /* = the ticket slots of a thread (kvz_cuda_enc.h) */
+#define GLUE_SPEC_PUS 4
+typedef struct {
+  int valid, ticket, idx, handle, lambda;
+  uint64_t epoch, frame_id;
+  glue_inputs in;
+} glue_spec;
+static __thread glue_spec t_spec[GLUE_SPEC_SLOTS][GLUE_SPEC_PUS];
+static __thread lcu_t *t_hyp = NULL;
+
+static int glue_speculate(void)
+{
+  static int on = -1;
+  if (on < 0) on = !(getenv("KVZ_CUDA_SPECULATE") && atoi(getenv("KVZ_CUDA_SPECULATE")) == 0);
+  return on;
+}
+
+/* the PU record and the per-picture job records search_pu_inter / search_pu_inter_ref derive for a PU
+ * (search_inter.c:1469-1481 merge candidates, :1164-1181 AMVP candidates, :1188-1206 colocated vector), from the CU
+ * array of `lcu` -- the real one, or a hypothetical copy.  Reads only lcu->cu; writes nothing but *in, *info. */
+static void glue_build_inputs(encoder_state_t *state, int x, int y, int width, int height, bool merge_a1, bool merge_b1,
+                              lcu_t *lcu, inter_search_info_t *info, glue_inputs *in, int8_t *ref_list, int8_t *lx_idx)
+{
+  const int n_refs = (int)state->frame->ref->used_size;
+  memset(in, 0, sizeof(*in));
+  info->num_merge_cand = kvz_inter_get_merge_cand(state, x, y, width, height, merge_a1, merge_b1, info->merge_cand, lcu);
+  kvz_cuda_me_pu *pu = &in->pu;
+  pu->x = (int16_t)x; pu->y = (int16_t)y; pu->w = (uint8_t)width; pu->h = (uint8_t)height;
+  pu->num_merge_cand = (uint8_t)info->num_merge_cand;
+  pu->num_jobs = (uint8_t)n_refs;
+  for (int i = 0; i < info->num_merge_cand; i++) {
+    const inter_merge_cand_t *m = &info->merge_cand[i];
+    pu->merge_cand[i].dir = m->dir;
+    pu->merge_cand[i].ref[0] = m->ref[0]; pu->merge_cand[i].ref[1] = m->ref[1];
+    memcpy(pu->merge_cand[i].mv, m->mv, sizeof(pu->merge_cand[i].mv));
+  }
+  cu_info_t probe;                                    /* kvz_inter_get_mv_cand reads cur_cu only for mv_ref[list] */
+  memset(&probe, 0, sizeof(probe));
+  for (int r = 0; r < n_refs; r++) {
+    glue_list_of(state, r, &ref_list[r], &lx_idx[r]);
+    probe.inter.mv_ref[ref_list[r]] = lx_idx[r];
+    kvz_inter_get_mv_cand(state, x, y, width, height, info->mv_cand, &probe, lcu, ref_list[r]);
+    memcpy(in->jobs[r].mv_cand, info->mv_cand, sizeof(in->jobs[r].mv_cand));
+    /* the colocated CU's vector in that picture (:1188-1206) */
+    const int mid_x = state->tile->offset_x + x + (width >> 1), mid_y = state->tile->offset_y + y + (height >> 1);
+    const cu_info_t *ref_cu = kvz_cu_array_at_const(state->frame->ref->cu_arrays[r], mid_x, mid_y);
+    if (ref_cu->type == CU_INTER) {
+      const int l = (ref_cu->inter.mv_dir & 1) ? 0 : 1;
+      in->jobs[r].extra_mv[0] = ref_cu->inter.mv[l][0]; in->jobs[r].extra_mv[1] = ref_cu->inter.mv[l][1];
+    }
+    in->jobs[r].ref_idx = (uint8_t)r;
+  }
+}
+
+static bool glue_same_inputs(const glue_inputs *a, const glue_inputs *b)
+{
+  return memcmp(&a->pu, &b->pu, sizeof(a->pu)) == 0 &&
+         memcmp(a->jobs, b->jobs, (size_t)a->pu.num_jobs * sizeof(kvz_cuda_me_job)) == 0;
+}
+
+static glue_spec *glue_spec_find(uint64_t frame_id, int handle, int lambda, const glue_inputs *in)
+{
+  for (int s = 0; s < GLUE_SPEC_SLOTS; s++)
+    for (int k = 0; k < GLUE_SPEC_PUS; k++) {
+      glue_spec *e = &t_spec[s][k];
+      if (e->valid && e->in.pu.x == in->pu.x && e->in.pu.y == in->pu.y && e->in.pu.w == in->pu.w && e->epoch == g_epoch &&
+          e->frame_id == frame_id && e->handle == handle && e->lambda == lambda && glue_same_inputs(&e->in, in)) return e;
+    }
+  return NULL;
+}
+
+/* search_cu's test for calling kvz_search_cu_inter at `depth` (search.c:446-468) */
+static bool glue_cu_is_searched(const encoder_state_t *state, int x, int y, int depth)
+{
+  const encoder_control_t *ctrl = state->encoder_control;
+  const videoframe_t *frame = state->tile->frame;
+  const int cu_width = LCU_WIDTH >> depth;
+  if (x + cu_width > frame->width || y + cu_width > frame->height) return false;
+  if (state->frame->slicetype == KVZ_SLICE_I || depth > MAX_DEPTH) return false;
+  const int cu_width_inter_min = LCU_WIDTH >> ctrl->cfg.pu_depth_inter.max;
+  return WITHIN(depth, ctrl->cfg.pu_depth_inter.min, ctrl->cfg.pu_depth_inter.max) ||
+         (x & ~(cu_width_inter_min - 1)) + cu_width_inter_min > frame->width ||
+         (y & ~(cu_width_inter_min - 1)) + cu_width_inter_min > frame->height;
+}
+
+/* Sends `first` (when non-NULL: the PU the caller needs now) and the top-left chain (x, y, depth), (x, y, depth + 1), ...
+ * derived from `lcu` in one launch; chain PUs already in flight with the same records are left out.  Returns the
+ * ticket, or -1 when there was nothing to send. */
+static int glue_launch(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t frame_id, int handle, int lambda,
+                       const glue_inputs *first, int x, int y, int depth, lcu_t *lcu)
+{
+  kvz_cuda_me_pu pus[GLUE_SPEC_PUS];
+  kvz_cuda_me_job jobs[GLUE_SPEC_PUS * KVZ_CUDA_MAX_REFS];
+  glue_inputs sent[GLUE_SPEC_PUS];
+  int n = 0;
+  if (first) sent[n++] = *first;
+  if (glue_speculate() && lcu)
+    for (int d = depth; d <= MAX_DEPTH && n < GLUE_SPEC_PUS; d++) {
+      if (!glue_cu_is_searched(state, x, y, d)) continue;
+      inter_search_info_t info;
+      int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
+      const int w = LCU_WIDTH >> d;
+      glue_build_inputs(state, x, y, w, w, true, true, lcu, &info, &sent[n], ref_list, lx_idx);
+      if (sent[n].pu.num_jobs == 0 || glue_spec_find(frame_id, handle, lambda, &sent[n])) continue;
+      n++;
+    }
+  if (n == 0) return -1;
+  for (int i = 0; i < n; i++) {
+    pus[i] = sent[i].pu;
+    memcpy(jobs + i * KVZ_CUDA_MAX_REFS, sent[i].jobs, sizeof(sent[i].jobs));
+  }
+  int ticket = -1;
+  if (!kvz_cuda_enc_search_begin(enc, handle, lambda, n, pus, jobs, &ticket)) kvz_glue_die("kvz_cuda_enc_search_begin");
+  glue_spec *row = t_spec[ticket & 0xFF];
+  for (int i = 0; i < GLUE_SPEC_PUS; i++) row[i].valid = 0;
+  for (int i = 0; i < n; i++) {
+    glue_spec *e = &row[i];
+    e->valid = 1; e->ticket = ticket; e->idx = i; e->handle = handle; e->lambda = lambda;
+    e->epoch = g_epoch; e->frame_id = frame_id; e->in = sent[i];
+  }
+  __atomic_fetch_add(&g_spec_cnt[3], (unsigned long long)n, __ATOMIC_RELAXED);
+  __atomic_fetch_add(&g_spec_cnt[2], (unsigned long long)(n - (first ? 1 : 0)), __ATOMIC_RELAXED);
+  return ticket;
+}
+
+/* the CU search_cu visits once the subtree of CU (x, y, depth) is finished (search.c:680-683: z-order; a CU that
+ * lies outside the frame returns at once, :437-440) -- inside the same CTU, else 0 */
+static int glue_next_cu(const videoframe_t *frame, int *x, int *y, int *depth)
+{
+  int cx = *x, cy = *y, d = *depth;
+  while (d > 0) {
+    const int s = LCU_WIDTH >> d;
+    int i = ((cy / s) & 1) * 2 + ((cx / s) & 1);
+    const int px = cx & ~(2 * s - 1), py = cy & ~(2 * s - 1);
+    if (i == 3) { cx = px; cy = py; d--; continue; }
+    i++;
+    cx = px + (i & 1) * s; cy = py + (i >> 1) * s;
+    if (cx >= frame->width || cy >= frame->height) continue;
+    *x = cx; *y = cy; *depth = d;
+    return 1;
+  }
+  return 0;
+}
+
+/* after the search of CU (x, y, depth): launch the next CU of the walk as if this CU stayed as `cur_cu` now says */
+static void glue_launch_next(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t frame_id, int handle, int lambda,
+                             int x, int y, int depth, const lcu_t *lcu, const cu_info_t *cur_cu, bool found_inter)
+{
+  int nx = x, ny = y, nd = depth;
+  if (!glue_next_cu(state->tile->frame, &nx, &ny, &nd)) return;
+  if (!t_hyp) {
+    t_hyp = malloc(sizeof(lcu_t));
+    if (!t_hyp) kvz_glue_die("out of memory");
+  }
+  memcpy(t_hyp->cu, lcu->cu, sizeof(lcu->cu));
+  cu_info_t filled = *cur_cu;
+  filled.type = found_inter ? CU_INTER : CU_INTRA;
+  const int w = LCU_WIDTH >> depth, xl = SUB_SCU(x), yl = SUB_SCU(y);
+  for (int yy = yl; yy < yl + w; yy += 4)
+    for (int xx = xl; xx < xl + w; xx += 4) *LCU_GET_CU_AT_PX(t_hyp, xx, yy) = filled;
+  glue_launch(state, enc, frame_id, handle, lambda, NULL, nx, ny, nd, t_hyp);
+}
+
 /* search_pu_inter (search_inter.c:1451-1524) with the reference loop on the device */
 static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_cu, int depth, part_mode_t part_mode,
                                  int i_pu, lcu_t *lcu, double *inter_cost, uint32_t *inter_bitcost)
@@ -242,49 +428,34 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
     .state = state, .pic = frame->source, .origin = { x, y }, .width = width, .height = height,
     .mvd_cost_func = calc_mvd_cost,
   };
-  info.num_merge_cand = kvz_inter_get_merge_cand(state, x, y, width, height, merge_a1, merge_b1, info.merge_cand, lcu);
+  glue_inputs in;
+  int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
+  glue_build_inputs(state, x, y, width, height, merge_a1, merge_b1, lcu, &info, &in, ref_list, lx_idx);
   CU_SET_MV_CAND(cur_cu, 0, 0);
   CU_SET_MV_CAND(cur_cu, 1, 0);
 
   kvz_cuda_enc *enc = glue_session(state);
   const int handle = glue_frame_handle(enc, state);
+  const uint64_t frame_id = ((uint64_t)state->frame->num << 16) | (uint64_t)(state->tile->id & 0xFFFF);
+  const int lambda = (int)(state->lambda_sqrt + 0.5);
   const int n_refs = (int)state->frame->ref->used_size;
-
-  kvz_cuda_me_pu pu;
-  kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
+  const bool square = part_mode == SIZE_2Nx2N;
   kvz_cuda_me_result res[KVZ_CUDA_MAX_REFS];
-  int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
-  memset(&pu, 0, sizeof(pu));
-  memset(jobs, 0, sizeof(jobs));
-  pu.x = (int16_t)x; pu.y = (int16_t)y; pu.w = (uint8_t)width; pu.h = (uint8_t)height;
-  pu.num_merge_cand = (uint8_t)info.num_merge_cand;
-  pu.num_jobs = (uint8_t)n_refs;
-  for (int i = 0; i < info.num_merge_cand; i++) {
-    const inter_merge_cand_t *m = &info.merge_cand[i];
-    pu.merge_cand[i].dir = m->dir;
-    pu.merge_cand[i].ref[0] = m->ref[0]; pu.merge_cand[i].ref[1] = m->ref[1];
-    memcpy(pu.merge_cand[i].mv, m->mv, sizeof(pu.merge_cand[i].mv));
-  }
-  for (int r = 0; r < n_refs; r++) {
-    glue_list_of(state, r, &ref_list[r], &lx_idx[r]);
-    /* AMVP candidates for this picture (:1164-1181); they depend on cur_cu only through mv_ref[list] */
-    const int8_t saved = cur_cu->inter.mv_ref[ref_list[r]];
-    cur_cu->inter.mv_ref[ref_list[r]] = lx_idx[r];
-    kvz_inter_get_mv_cand(state, x, y, width, height, info.mv_cand, cur_cu, lcu, ref_list[r]);
-    cur_cu->inter.mv_ref[ref_list[r]] = saved;
-    memcpy(jobs[r].mv_cand, info.mv_cand, sizeof(jobs[r].mv_cand));
-    /* the colocated CU's vector in that picture (:1188-1206) */
-    const int mid_x = state->tile->offset_x + x + (width >> 1), mid_y = state->tile->offset_y + y + (height >> 1);
-    const cu_info_t *ref_cu = kvz_cu_array_at_const(state->frame->ref->cu_arrays[r], mid_x, mid_y);
-    if (ref_cu->type == CU_INTER) {
-      const int l = (ref_cu->inter.mv_dir & 1) ? 0 : 1;
-      jobs[r].extra_mv[0] = ref_cu->inter.mv[l][0]; jobs[r].extra_mv[1] = ref_cu->inter.mv[l][1];
-    }
-    jobs[r].ref_idx = (uint8_t)r;
-  }
+  memset(res, 0, sizeof(res));
 
   if (n_refs > 0) {
-    if (!kvz_cuda_enc_search_pu(enc, handle, (int)(state->lambda_sqrt + 0.5), &pu, jobs, res)) kvz_glue_die("kvz_cuda_enc_search_pu");
+    bool have = false;
+    glue_spec *e = glue_speculate() ? glue_spec_find(frame_id, handle, lambda, &in) : NULL;
+    if (e) {                                             /* launched ahead with exactly these records */
+      have = kvz_cuda_enc_search_end(enc, e->ticket, e->idx, res) != 0;
+      e->valid = 0;
+    }
+    __atomic_fetch_add(&g_spec_cnt[have ? 0 : 1], 1ull, __ATOMIC_RELAXED);
+    if (!have) {                                         /* search it now; its top-left children ride along */
+      const int ticket = glue_launch(state, enc, frame_id, handle, lambda, &in, x, y, depth + 1, square ? lcu : NULL);
+      if (!kvz_cuda_enc_search_end(enc, ticket, 0, res)) kvz_glue_die("kvz_cuda_enc_search_end");
+      t_spec[ticket & 0xFF][0].valid = 0;
+    }
     KVZ_GLUE_COUNT(KVZ_GLUE_CNT_ME_PU);
   }
 
@@ -310,6 +481,9 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
     if (n_refs > 0) { info.ref_idx = n_refs - 1; info.ref = state->frame->ref->images[n_refs - 1]; }
     search_pu_inter_bipred(&info, depth, lcu, cur_cu, inter_cost, inter_bitcost);
   }
+
+  if (n_refs > 0 && square && glue_speculate())
+    glue_launch_next(state, enc, frame_id, handle, lambda, x, y, depth, lcu, cur_cu, *inter_cost < MAX_INT);
 }
 
 /* kvz_search_cu_inter (search_inter.c:1588-1610) */

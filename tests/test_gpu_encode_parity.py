@@ -40,8 +40,9 @@ def test_batch_mode_bitstream_equals_reference(name, golden, tmp_path):
     assert r["md5"] == golden[name]["md5"], name
     assert r["frames"] == [tuple(f) for f in golden[name]["frames"]]
     c = _counters(r["stderr"])
-    # the device did the searching: one call per search_pu_inter, at least one kernel each, every inter frame begun
-    assert c["me_pu_searches"] > 50 * (case[2] - 1) and c["launches"] >= c["me_pu_searches"]
+    # the device did the searching: every search_pu_inter answered by the device (one launch carries up to four PUs,
+    # most of them sent ahead of the walk: kvz_glue_search_inter.c), every inter frame begun
+    assert c["me_pu_searches"] > 50 * (case[2] - 1) and c["launches"] >= c["me_pu_searches"] // 4
     assert c["me_frames"] >= case[2] - 1 - (case[2] - 1) // 64
     if os.path.exists(ec.REF_BIN) and name in ("c2_small_full32", "tiles_2x2_full16"):
         live = ec.encode(ec.REF_BIN, str(tmp_path), name, case, THREADS)
