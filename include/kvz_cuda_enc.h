@@ -85,7 +85,7 @@ KVZ_CUDA_API int kvz_cuda_enc_search_pu(kvz_cuda_enc *enc, int frame_handle, int
 
 /* The same search split in two, so that a host can have searches in flight while it does its own work (residual
  * coding, intra search) and can launch a PU ahead of time with the candidates it EXPECTS the PU to get: begin sends
- * 1..4 PUs of one CTU in one launch and returns at once; end blocks until PU `pu_index` of that launch has its results.
+ * 1..8 PUs of one CTU in one launch and returns at once; end blocks until PU `pu_index` of that launch has its results.
  * `jobs` holds KVZ_CUDA_MAX_REFS records per PU (PU i's jobs at jobs[i * KVZ_CUDA_MAX_REFS ..], pus[i].num_jobs used).
  * A host that launched ahead must compare the PU and job records it sent with the real ones when the PU's turn comes
  * and search again when they differ -- the device computes exactly what it is given (kvazaar_b200/host/ does this, so

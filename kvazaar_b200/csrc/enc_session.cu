@@ -567,7 +567,7 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
                               const kvz_cuda_me_job *jobs, int *ticket)
 {
   if (!e || !pus || !jobs || !ticket) return fail_enc("kvz_cuda_enc_search_begin: null argument");
-  if (n_pus < 1 || n_pus > kMePuArgsMax) return fail_enc("kvz_cuda_enc_search_begin: 1..4 PUs per launch");
+  if (n_pus < 1 || n_pus > kMePuArgsMax) return fail_enc("kvz_cuda_enc_search_begin: 1..8 PUs per launch");
   FrameCtx *ctx = nullptr;
   {
     std::lock_guard<std::mutex> guard(e->lock);

@@ -6,7 +6,7 @@
 
 namespace kvz {
 
-constexpr int kMePuArgsMax = 4;   // PUs one launch_me_search_pu can carry as kernel arguments
+constexpr int kMePuArgsMax = 8;   // PUs one launch_me_search_pu can carry as kernel arguments
 constexpr int kMeMaxBox = 272;     // largest box side (displacements) kvz_cuda_me_search reads
 
 struct MeMapSet {

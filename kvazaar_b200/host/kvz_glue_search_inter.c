@@ -19,6 +19,7 @@
 #undef kvz_search_cu_smp
 
 #include <pthread.h>
+#include <time.h>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -28,6 +29,8 @@
 /* ---- the session: one per process ("Only one encoder may be open at a time", src/kvazaar.h:619) ---- */
 static kvz_cuda_enc *g_enc = NULL;
 static uint64_t g_epoch = 0;                 /* bumped when a session opens: launches made under an older one never match */
+static unsigned long long g_glue_ns[4];          /* KVZ_CUDA_STATS: ns in deriving the real records, waiting for results, launching ahead; calls */
+static unsigned long long g_spec_by_size[4][2];   /* by PU size 8, 16, 32, 64: answered ahead, searched on the spot */
 static unsigned long long g_spec_cnt[4];     /* PU searches answered by a launch made ahead, searched on the spot, PUs launched ahead, PUs launched */
 static const encoder_control_t *g_enc_ctrl = NULL;
 static pthread_mutex_t g_enc_lock = PTHREAD_MUTEX_INITIALIZER;
@@ -43,6 +46,11 @@ static void glue_close_session(void)
               s[0], s[1], s[5], s[2], s[3] / 1048576.0, s[4], s[6]);
       fprintf(stderr, "kvz_glue: PU searches the host asked for: %llu answered by a launch made ahead, %llu searched on the spot; "
               "PUs launched %llu, of them ahead of time %llu\n", g_spec_cnt[0], g_spec_cnt[1], g_spec_cnt[3], g_spec_cnt[2]);
+      if (g_glue_ns[3])
+        fprintf(stderr, "kvz_glue: per search_pu_inter: records %.1f us, lookup + wait for the results %.1f us, bi-prediction + launching ahead %.1f us\n",
+                g_glue_ns[0] / 1e3 / g_glue_ns[3], g_glue_ns[1] / 1e3 / g_glue_ns[3], g_glue_ns[2] / 1e3 / g_glue_ns[3]);
+      for (int i = 0; i < 4; i++)
+        fprintf(stderr, "kvz_glue: PU %2d: %llu answered ahead, %llu searched on the spot\n", 8 << i, g_spec_by_size[i][0], g_spec_by_size[i][1]);
     }
     kvz_cuda_enc_close(g_enc);
     g_enc = NULL;
@@ -247,14 +255,41 @@ typedef struct {
 } glue_inputs;
 
 #define GLUE_SPEC_SLOTS 32          /* = the ticket slots of a thread (kvz_cuda_enc.h) */
-#define GLUE_SPEC_PUS 4
+#define GLUE_SPEC_PUS 8           /* = the PUs one kvz_cuda_enc_search_begin takes */
 typedef struct {
   int valid, ticket, idx, handle, lambda;
   uint64_t epoch, frame_id;
   glue_inputs in;
 } glue_spec;
 static __thread glue_spec t_spec[GLUE_SPEC_SLOTS][GLUE_SPEC_PUS];
+/* what a lookup scans: 8 bytes per entry (the records themselves are 368 bytes apart); 0 = no entry */
+static __thread uint64_t t_key[GLUE_SPEC_SLOTS][GLUE_SPEC_PUS];
+static uint64_t glue_key(const glue_inputs *in)
+{
+  return 1ull << 63 | (uint64_t)(uint16_t)in->pu.x << 32 | (uint64_t)(uint16_t)in->pu.y << 16 | (uint64_t)in->pu.w << 8 | in->pu.h;
+}
 static __thread lcu_t *t_hyp = NULL;
+
+/* KVZ_GLUE_TRACE=1: the searches and launches of the first CTU of frame 1 on stderr (debugging the launching ahead) */
+static int kvz_glue_trace(void)
+{
+  static int on = -1;
+  if (on < 0) on = getenv("KVZ_GLUE_TRACE") != NULL;
+  return on;
+}
+
+static int glue_timing(void)
+{
+  static int on = -1;
+  if (on < 0) on = getenv("KVZ_CUDA_STATS") != NULL;
+  return on;
+}
+static unsigned long long glue_now(void)
+{
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (unsigned long long)ts.tv_sec * 1000000000ull + (unsigned long long)ts.tv_nsec;
+}
 
 static int glue_speculate(void)
 {
@@ -277,10 +312,15 @@ static void glue_build_inputs(encoder_state_t *state, int x, int y, int width, i
   pu->num_merge_cand = (uint8_t)info->num_merge_cand;
   pu->num_jobs = (uint8_t)n_refs;
   for (int i = 0; i < info->num_merge_cand; i++) {
+    /* only the lists `dir` names are set by the derivation (inter.c:1375-1530); the others stay zero here, so that
+     * two derivations from the same CU array give the same bytes whatever their callers' stacks held */
     const inter_merge_cand_t *m = &info->merge_cand[i];
     pu->merge_cand[i].dir = m->dir;
-    pu->merge_cand[i].ref[0] = m->ref[0]; pu->merge_cand[i].ref[1] = m->ref[1];
-    memcpy(pu->merge_cand[i].mv, m->mv, sizeof(pu->merge_cand[i].mv));
+    for (int l = 0; l < 2; l++)
+      if (m->dir & (1 << l)) {
+        pu->merge_cand[i].ref[l] = m->ref[l];
+        pu->merge_cand[i].mv[l][0] = m->mv[l][0]; pu->merge_cand[i].mv[l][1] = m->mv[l][1];
+      }
   }
   cu_info_t probe;                                    /* kvz_inter_get_mv_cand reads cur_cu only for mv_ref[list] */
   memset(&probe, 0, sizeof(probe));
@@ -308,11 +348,13 @@ static bool glue_same_inputs(const glue_inputs *a, const glue_inputs *b)
 
 static glue_spec *glue_spec_find(uint64_t frame_id, int handle, int lambda, const glue_inputs *in)
 {
+  const uint64_t key = glue_key(in);
   for (int s = 0; s < GLUE_SPEC_SLOTS; s++)
     for (int k = 0; k < GLUE_SPEC_PUS; k++) {
+      if (t_key[s][k] != key) continue;
       glue_spec *e = &t_spec[s][k];
-      if (e->valid && e->in.pu.x == in->pu.x && e->in.pu.y == in->pu.y && e->in.pu.w == in->pu.w && e->epoch == g_epoch &&
-          e->frame_id == frame_id && e->handle == handle && e->lambda == lambda && glue_same_inputs(&e->in, in)) return e;
+      if (e->valid && e->epoch == g_epoch && e->frame_id == frame_id && e->handle == handle && e->lambda == lambda &&
+          glue_same_inputs(&e->in, in)) return e;
     }
   return NULL;
 }
@@ -331,43 +373,62 @@ static bool glue_cu_is_searched(const encoder_state_t *state, int x, int y, int 
          (y & ~(cu_width_inter_min - 1)) + cu_width_inter_min > frame->height;
 }
 
-/* Sends `first` (when non-NULL: the PU the caller needs now) and the top-left chain (x, y, depth), (x, y, depth + 1), ...
- * derived from `lcu` in one launch; chain PUs already in flight with the same records are left out.  Returns the
- * ticket, or -1 when there was nothing to send. */
-static int glue_launch(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t frame_id, int handle, int lambda,
-                       const glue_inputs *first, int x, int y, int depth, lcu_t *lcu)
+/* the PUs of one launch being put together */
+typedef struct {
+  glue_inputs sent[GLUE_SPEC_PUS];
+  int n, n_needed_now;
+} glue_batch;
+
+/* adds CU (x, y, depth) as search_cu would search it, with the records `lcu` gives it -- unless search_cu would not
+ * search it there, or the same records are in flight already */
+static void glue_batch_add_cu(encoder_state_t *state, glue_batch *b, uint64_t frame_id, int handle, int lambda,
+                              int x, int y, int depth, lcu_t *lcu)
 {
+  if (b->n >= GLUE_SPEC_PUS || !glue_cu_is_searched(state, x, y, depth)) return;
+  inter_search_info_t info;
+  int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
+  const int w = LCU_WIDTH >> depth;
+  glue_inputs *in = &b->sent[b->n];
+  glue_build_inputs(state, x, y, w, w, true, true, lcu, &info, in, ref_list, lx_idx);
+  if (in->pu.num_jobs == 0 || glue_spec_find(frame_id, handle, lambda, in)) return;
+  b->n++;
+}
+
+/* the top-left chain (x, y, depth), (x, y, depth + 1), ...: search_cu reaches each of them before any other CU of the
+ * subtree, so their neighbours are the ones `lcu` has now */
+static void glue_batch_add_chain(encoder_state_t *state, glue_batch *b, uint64_t frame_id, int handle, int lambda,
+                                 int x, int y, int depth, lcu_t *lcu)
+{
+  for (int d = depth; d <= MAX_DEPTH; d++) glue_batch_add_cu(state, b, frame_id, handle, lambda, x, y, d, lcu);
+}
+
+/* one launch for the batch; returns its ticket, or -1 when the batch is empty */
+static int glue_batch_launch(kvz_cuda_enc *enc, uint64_t frame_id, int handle, int lambda, const glue_batch *b)
+{
+  if (b->n == 0) return -1;
   kvz_cuda_me_pu pus[GLUE_SPEC_PUS];
   kvz_cuda_me_job jobs[GLUE_SPEC_PUS * KVZ_CUDA_MAX_REFS];
-  glue_inputs sent[GLUE_SPEC_PUS];
-  int n = 0;
-  if (first) sent[n++] = *first;
-  if (glue_speculate() && lcu)
-    for (int d = depth; d <= MAX_DEPTH && n < GLUE_SPEC_PUS; d++) {
-      if (!glue_cu_is_searched(state, x, y, d)) continue;
-      inter_search_info_t info;
-      int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
-      const int w = LCU_WIDTH >> d;
-      glue_build_inputs(state, x, y, w, w, true, true, lcu, &info, &sent[n], ref_list, lx_idx);
-      if (sent[n].pu.num_jobs == 0 || glue_spec_find(frame_id, handle, lambda, &sent[n])) continue;
-      n++;
-    }
-  if (n == 0) return -1;
-  for (int i = 0; i < n; i++) {
-    pus[i] = sent[i].pu;
-    memcpy(jobs + i * KVZ_CUDA_MAX_REFS, sent[i].jobs, sizeof(sent[i].jobs));
+  for (int i = 0; i < b->n; i++) {
+    pus[i] = b->sent[i].pu;
+    memcpy(jobs + i * KVZ_CUDA_MAX_REFS, b->sent[i].jobs, sizeof(b->sent[i].jobs));
+  }
+  if (kvz_glue_trace() && (frame_id >> 16) == 1 && pus[0].x < 64 && pus[0].y < 64) {
+    fprintf(stderr, "T launch");
+    for (int i = 0; i < b->n; i++) fprintf(stderr, " (%d,%d,%d)", pus[i].x, pus[i].y, pus[i].w);
+    fprintf(stderr, "\n");
   }
   int ticket = -1;
-  if (!kvz_cuda_enc_search_begin(enc, handle, lambda, n, pus, jobs, &ticket)) kvz_glue_die("kvz_cuda_enc_search_begin");
+  if (!kvz_cuda_enc_search_begin(enc, handle, lambda, b->n, pus, jobs, &ticket)) kvz_glue_die("kvz_cuda_enc_search_begin");
   glue_spec *row = t_spec[ticket & 0xFF];
-  for (int i = 0; i < GLUE_SPEC_PUS; i++) row[i].valid = 0;
-  for (int i = 0; i < n; i++) {
+  for (int i = 0; i < GLUE_SPEC_PUS; i++) { row[i].valid = 0; t_key[ticket & 0xFF][i] = 0; }
+  for (int i = 0; i < b->n; i++) {
     glue_spec *e = &row[i];
+    t_key[ticket & 0xFF][i] = glue_key(&b->sent[i]);
     e->valid = 1; e->ticket = ticket; e->idx = i; e->handle = handle; e->lambda = lambda;
-    e->epoch = g_epoch; e->frame_id = frame_id; e->in = sent[i];
+    e->epoch = g_epoch; e->frame_id = frame_id; e->in = b->sent[i];
   }
-  __atomic_fetch_add(&g_spec_cnt[3], (unsigned long long)n, __ATOMIC_RELAXED);
-  __atomic_fetch_add(&g_spec_cnt[2], (unsigned long long)(n - (first ? 1 : 0)), __ATOMIC_RELAXED);
+  __atomic_fetch_add(&g_spec_cnt[3], (unsigned long long)b->n, __ATOMIC_RELAXED);
+  __atomic_fetch_add(&g_spec_cnt[2], (unsigned long long)(b->n - b->n_needed_now), __ATOMIC_RELAXED);
   return ticket;
 }
 
@@ -390,12 +451,19 @@ static int glue_next_cu(const videoframe_t *frame, int *x, int *y, int *depth)
   return 0;
 }
 
-/* after the search of CU (x, y, depth): launch the next CU of the walk as if this CU stayed as `cur_cu` now says */
+/* After the search of CU (x, y, depth), under the hypothesis that the CU stays as `cur_cu` says now: launches the next
+ * CU of the walk with its top-left chain, and -- when the CU can be split -- its children 1..3 as they will be searched
+ * if the children before them come out like the CU itself (smooth motion; when they do not, the child is launched
+ * again after its predecessor, by this same function). */
 static void glue_launch_next(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t frame_id, int handle, int lambda,
                              int x, int y, int depth, const lcu_t *lcu, const cu_info_t *cur_cu, bool found_inter)
 {
   int nx = x, ny = y, nd = depth;
-  if (!glue_next_cu(state->tile->frame, &nx, &ny, &nd)) return;
+  const bool has_next = glue_next_cu(state->tile->frame, &nx, &ny, &nd) != 0;
+  static int children = -1;                                   /* KVZ_CUDA_SPEC_CHILDREN=0: experiments */
+  if (children < 0) children = !(getenv("KVZ_CUDA_SPEC_CHILDREN") && atoi(getenv("KVZ_CUDA_SPEC_CHILDREN")) == 0);
+  const bool has_children = children && depth < MAX_DEPTH && depth < state->encoder_control->cfg.pu_depth_inter.max;
+  if (!has_next && !has_children) return;
   if (!t_hyp) {
     t_hyp = malloc(sizeof(lcu_t));
     if (!t_hyp) kvz_glue_die("out of memory");
@@ -406,7 +474,16 @@ static void glue_launch_next(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t
   const int w = LCU_WIDTH >> depth, xl = SUB_SCU(x), yl = SUB_SCU(y);
   for (int yy = yl; yy < yl + w; yy += 4)
     for (int xx = xl; xx < xl + w; xx += 4) *LCU_GET_CU_AT_PX(t_hyp, xx, yy) = filled;
-  glue_launch(state, enc, frame_id, handle, lambda, NULL, nx, ny, nd, t_hyp);
+  glue_batch b;
+  b.n = b.n_needed_now = 0;
+  if (has_next) glue_batch_add_chain(state, &b, frame_id, handle, lambda, nx, ny, nd, t_hyp);
+  if (has_children && found_inter) {
+    const int h = w >> 1;
+    glue_batch_add_cu(state, &b, frame_id, handle, lambda, x + h, y, depth + 1, t_hyp);
+    glue_batch_add_cu(state, &b, frame_id, handle, lambda, x, y + h, depth + 1, t_hyp);
+    glue_batch_add_cu(state, &b, frame_id, handle, lambda, x + h, y + h, depth + 1, t_hyp);
+  }
+  glue_batch_launch(enc, frame_id, handle, lambda, &b);
 }
 
 /* search_pu_inter (search_inter.c:1451-1524) with the reference loop on the device */
@@ -430,6 +507,8 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
   };
   glue_inputs in;
   int8_t ref_list[KVZ_CUDA_MAX_REFS], lx_idx[KVZ_CUDA_MAX_REFS];
+  const int timing = glue_timing();
+  unsigned long long t0 = timing ? glue_now() : 0, t1 = 0, t2 = 0;
   glue_build_inputs(state, x, y, width, height, merge_a1, merge_b1, lcu, &info, &in, ref_list, lx_idx);
   CU_SET_MV_CAND(cur_cu, 0, 0);
   CU_SET_MV_CAND(cur_cu, 1, 0);
@@ -443,6 +522,7 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
   kvz_cuda_me_result res[KVZ_CUDA_MAX_REFS];
   memset(res, 0, sizeof(res));
 
+  if (timing) t1 = glue_now();
   if (n_refs > 0) {
     bool have = false;
     glue_spec *e = glue_speculate() ? glue_spec_find(frame_id, handle, lambda, &in) : NULL;
@@ -451,13 +531,20 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
       e->valid = 0;
     }
     __atomic_fetch_add(&g_spec_cnt[have ? 0 : 1], 1ull, __ATOMIC_RELAXED);
+    if (kvz_glue_trace() && x < 64 && y < 64 && state->frame->num == 1) fprintf(stderr, "T search %d %d %d %s\n", x, y, width, have ? "hit" : "miss");
+    __atomic_fetch_add(&g_spec_by_size[width > 32 ? 3 : width > 16 ? 2 : width > 8 ? 1 : 0][have ? 0 : 1], 1ull, __ATOMIC_RELAXED);
     if (!have) {                                         /* search it now; its top-left children ride along */
-      const int ticket = glue_launch(state, enc, frame_id, handle, lambda, &in, x, y, depth + 1, square ? lcu : NULL);
+      glue_batch b;
+      b.n = b.n_needed_now = 1;
+      b.sent[0] = in;
+      if (square && glue_speculate()) glue_batch_add_chain(state, &b, frame_id, handle, lambda, x, y, depth + 1, lcu);
+      const int ticket = glue_batch_launch(enc, frame_id, handle, lambda, &b);
       if (!kvz_cuda_enc_search_end(enc, ticket, 0, res)) kvz_glue_die("kvz_cuda_enc_search_end");
       t_spec[ticket & 0xFF][0].valid = 0;
     }
     KVZ_GLUE_COUNT(KVZ_GLUE_CNT_ME_PU);
   }
+  if (timing) t2 = glue_now();
 
   /* what search_pu_inter_ref writes when a picture lowers *inter_cost (:1281-1296), pictures in order */
   for (int r = 0; r < n_refs; r++) {
@@ -484,6 +571,13 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
 
   if (n_refs > 0 && square && glue_speculate())
     glue_launch_next(state, enc, frame_id, handle, lambda, x, y, depth, lcu, cur_cu, *inter_cost < MAX_INT);
+  if (timing) {
+    const unsigned long long t3 = glue_now();
+    __atomic_fetch_add(&g_glue_ns[0], t1 - t0, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_glue_ns[1], t2 - t1, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_glue_ns[2], t3 - t2, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_glue_ns[3], 1ull, __ATOMIC_RELAXED);
+  }
 }
 
 /* kvz_search_cu_inter (search_inter.c:1588-1610) */

@@ -110,7 +110,7 @@ class Session:
         return res
 
     def search_begin(self, handle, lambda_sqrt_i, pus, jobs_per_pu):
-        """1..4 PUs of one CTU in one launch; jobs_per_pu[i] = the job records of pus[i]; returns the ticket"""
+        """1..8 PUs of one CTU in one launch; jobs_per_pu[i] = the job records of pus[i]; returns the ticket"""
         pus = np.ascontiguousarray(pus, ME_PU_DT)
         padded = np.zeros(len(pus) * MAX_REFS, ME_JOB_DT)
         for i, jb in enumerate(jobs_per_pu):

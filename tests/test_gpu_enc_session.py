@@ -45,8 +45,8 @@ def test_begin_end_several_pus_per_launch_equals_oracle():
         got = np.zeros_like(want)
         pending = []
         for idx in by_ctu.values():
-            for k in range(0, len(idx), 4):                       # launches of 1..4 PUs, several in flight at once
-                grp = idx[k:k + 4]
+            for k in range(0, len(idx), 5):                       # launches of 1..5 PUs, several in flight at once
+                grp = idx[k:k + 5]
                 t = s.search_begin(handle, lam, pus[grp], [jobs[i * NREFS:(i + 1) * NREFS] for i in grp])
                 pending.append((t, grp))
                 if len(pending) == 6:
@@ -75,8 +75,8 @@ def test_tickets_expire_and_bad_launches_are_refused():
         a = next(i for i in range(len(pus)) if (int(pus[i]["x"]) >> 6, int(pus[i]["y"]) >> 6) != (int(pus[0]["x"]) >> 6, int(pus[0]["y"]) >> 6))
         with pytest.raises(RuntimeError, match="one CTU"):
             s.search_begin(handle, lam, pus[[0, a]], [jobs[:NREFS], jobs[a * NREFS:(a + 1) * NREFS]])
-        with pytest.raises(RuntimeError, match="1..4"):
-            s.search_begin(handle, lam, pus[:5], [jobs[i * NREFS:(i + 1) * NREFS] for i in range(5)])
+        with pytest.raises(RuntimeError, match="1..8"):
+            s.search_begin(handle, lam, pus[:9], [jobs[i * NREFS:(i + 1) * NREFS] for i in range(9)])
         with pytest.raises(RuntimeError, match="handle"):
             s.search_begin(handle + 7, lam, pus[:1], [jobs[:NREFS]])
     finally:

@@ -5,7 +5,7 @@ set -u
 cd "$(dirname "$0")/.."
 OUT=gpurun_out; mkdir -p $OUT
 N=${1:-9}; shift || true
-K=kvazaar_b200/host/_build/kvazaar_cuda
+K=${KBIN:-kvazaar_b200/host/_build/kvazaar_cuda}
 T=$(nproc)
 C=/tmp/kvz_clips; mkdir -p $C
 [ -f $C/c2.yuv ] || python tools/make_clip.py $C/c2.yuv 1920 1080 17 2
