@@ -85,10 +85,12 @@ struct Worker {
   cudaEvent_t ctu_ready = nullptr;    // --owf: the blocks and maps ctu_begin prepared on streams[0]
   uint8_t *h = nullptr, *d = nullptr;
   const void *seen_enc = nullptr;
+  uint64_t seen_serial = 0;           // a later session may get the address of a closed one
   uint64_t seen_ctx[kStreams];        // the frame context whose `ready` event the stream has waited for
   int seen_ctu[kStreams];             // the CTU of that context whose ctu_ready the stream has waited for
   int cur_ctu = -1;                   // the CTU this thread last prepared (ctu_begin)
   uint64_t cur_ctx = ~0ull;
+  FrameCtx *ctx_of[64] = {};          // frame handle -> context, as last looked up under the session's lock
   uint32_t next_slot = 0;
   uint32_t gen[kSlots] = {};          // generation of the slot's last launch (the value its completion words receive)
   uint8_t n_pus[kSlots] = {};
@@ -117,6 +119,7 @@ using namespace kvz;
 
 struct kvz_cuda_enc {
   kvz_cuda_enc_cfg cfg;
+  uint64_t serial = 0;                // unique per open
   int pitch = 0;                      // bytes per row of the bordered planes
   size_t plane_bytes = 0;
   std::mutex lock;
@@ -315,6 +318,8 @@ kvz_cuda_enc *kvz_cuda_enc_open(const kvz_cuda_enc_cfg *cfg)
   if (cfg->fme_level < 0 || cfg->fme_level > 4) { fail_enc("kvz_cuda_enc_open: fme_level must be 0..4"); return nullptr; }
   if (!kvz_cuda_init(cfg->device)) return nullptr;
   kvz_cuda_enc *e = new kvz_cuda_enc();
+  static std::atomic<uint64_t> serials{0};
+  e->serial = ++serials;
   e->cfg = *cfg;
   if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 98304;       // of 180 GB; shared by the owf + 1 frames in flight
   for (auto &s : e->stats) s = 0;
@@ -568,13 +573,18 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
 {
   if (!e || !pus || !jobs || !ticket) return fail_enc("kvz_cuda_enc_search_begin: null argument");
   if (n_pus < 1 || n_pus > kMePuArgsMax) return fail_enc("kvz_cuda_enc_search_begin: 1..8 PUs per launch");
+  // contexts are created once and live until the session closes, so a thread may keep the pointer it looked up under
+  // the lock (the vector that holds them may grow); a context is recycled only for a frame owf + 1 later, when the
+  // host has long stopped searching this one
   FrameCtx *ctx = nullptr;
-  {
+  Worker &w0 = t_worker;
+  if (w0.seen_enc == e && w0.seen_serial == e->serial && handle >= 0 && handle < 64) ctx = w0.ctx_of[handle];
+  if (!ctx) {
     std::lock_guard<std::mutex> guard(e->lock);
     if (handle >= 0 && handle < (int)e->ctxs.size()) ctx = e->ctxs[handle];
-    if (ctx) ctx->inflight++;
   }
-  if (!ctx || ctx->id == ~0ull) { if (ctx) ctx->inflight--; return fail_enc("kvz_cuda_enc_search_begin: bad frame handle"); }
+  if (!ctx || ctx->id == ~0ull) return fail_enc("kvz_cuda_enc_search_begin: bad frame handle");
+  ctx->inflight++;
   struct Release { FrameCtx *c; ~Release() { c->inflight--; } } release{ctx};
   const int ctu_x = pus[0].x >> 6, ctu_y = pus[0].y >> 6;
   unsigned long long n_jobs_total = 0;
@@ -598,8 +608,11 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
         if (!job_in_box(*ctx, e->cfg.range, pus[p], jobs[(size_t)p * KVZ_CUDA_MAX_REFS + i])) e->stats[6]++;
 
   const uint64_t tag = ((uint64_t)handle << 48) ^ ctx->id;
-  if (w.seen_enc != e || w.cur_ctx != tag) {
-    w.seen_enc = e; w.cur_ctx = tag; w.cur_ctu = -1;
+  const bool same_session = w.seen_enc == e && w.seen_serial == e->serial;
+  if (!same_session) for (auto &c : w.ctx_of) c = nullptr;
+  if (handle < 64) w.ctx_of[handle] = ctx;
+  if (!same_session || w.cur_ctx != tag) {
+    w.seen_enc = e; w.seen_serial = e->serial; w.cur_ctx = tag; w.cur_ctu = -1;
     for (int i = 0; i < kStreams; i++) { w.seen_ctx[i] = ~0ull; w.seen_ctu[i] = -1; }
   }
   const int ctu = ctu_y * ctx->f.ctus_x + ctu_x;
