@@ -290,11 +290,11 @@ def run_ours(args):
             "l2": "the SAD maps of one picture (several GB) exceed the 126 MB L2; no flush needed",
             "parallelism": "one encoder and one clip per rank (segment-parallel encoding), ranks share the host's cores; "
                            "no data-path collective",
-            "device_stages_per_step": ["upload source + new reference luma, pad_plane", "ime_sad_multi_kernel x1 (dense SAD maps, all references)",
+            "device_stages_per_step": ["upload source + new reference luma, pad_plane", "ime_sad_multi_tma_kernel (dense SAD maps of all complete references in one launch; one launch per CTU for references still in flight)",
                                        "me_pu_kernel x (PU searches of the picture): box scan | CTA window scan, refinement"],
         },
         "roofline": {
-            "kernel": "ime_sad_multi_kernel (dense SAD maps of one picture against all its references, one launch)",
+            "kernel": "ime_sad_multi_tma_kernel (dense SAD maps of one picture against its references; reference tile rows staged by TMA)",
             "bound": "int_pipe", "achieved": achieved, "peak": peak / 1e12, "unit": "Tabsdiff/s",
             "frac": achieved / (peak / 1e12) if peak else None,
             "peak_source": "kvz_cuda_measure_int_pipe_peak: VABSDIFF4.U8.ACC register loop, measured in this run",

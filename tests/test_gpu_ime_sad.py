@@ -169,6 +169,26 @@ def test_box_maps_multi_equals_single():
             assert torch.equal(a.maps[level], b.maps[level]), (r, level)
 
 
+@pytest.mark.parametrize("name", ["x-15_72x19", "x-1_16x41", "five", "one_177"])
+def test_tma_and_cp_async_staging_write_the_same_maps(name):
+    """kvz_cuda_ime_sad_box_maps_multi stages its reference tile rows with one TMA load per CTA (cp.async.bulk.tensor,
+    the default) or with cp.async words (KVZ_CUDA_SAD_TMA=0): every map entry must be the same, for window starts at
+    any byte alignment (TMA itself only starts at multiples of 16 bytes).  The switch is read once per process, so
+    each staging runs in a process of its own (tools/tma_probe.py); the in-process tests above check the default
+    against the oracle."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for tma in ("1", "0"):
+        p = subprocess.run([sys.executable, os.path.join(root, "tools", "tma_probe.py"), name], capture_output=True, text=True,
+                           timeout=300, env=dict(os.environ, KVZ_CUDA_SAD_TMA=tma))
+        assert p.returncode == 0, p.stderr[-600:]
+        digests.append(p.stdout.strip().splitlines()[-1].split("sha1")[-1].strip())
+    assert len(digests[0]) == 40 and digests[0] == digests[1]
+
+
 @pytest.mark.parametrize("box", [(-8, -8, 32, 17), (-20, 3, 40, 9), (5, -12, 16, 21), (-3, -3, 8, 7)])
 def test_box_maps_10bit(box):
     """bitdepth 10 (uint16 samples): kvz_cuda_ime_sad_box_maps vs the oracle's kvz_image_calc_sad of the 10-bit build

@@ -57,7 +57,7 @@ def main():
     n8 = (W // 8) * (H // 8)
     absd = n8 * 64 * NREFS * BOX[2] * BOX[3]
     t_sad, t_pu = ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])
-    print(f"dense SAD (ime_sad_multi_kernel, {NREFS} refs x {BOX[2]}x{BOX[3]}): {t_sad:.3f} ms = {absd / t_sad / 1e9:.1f} T abs-diff/s; "
+    print(f"dense SAD (ime_sad_multi[_tma]_kernel, {NREFS} refs x {BOX[2]}x{BOX[3]}): {t_sad:.3f} ms = {absd / t_sad / 1e9:.1f} T abs-diff/s; "
           f"me_pu_kernel over {len(pus)} PUs x {NREFS} refs in one launch: {t_pu:.3f} ms = {t_pu * 1e3 / len(pus):.2f} us per PU of GPU throughput")
 
 
