@@ -101,6 +101,36 @@ def test_random_blocks_vs_oracle():
         assert got.tolist() == want, n
 
 
+@pytest.mark.parametrize("n,count", [(4, 200), (8, 200), (4, 32), (8, 33), (4, 31)])
+def test_batches_of_small_blocks_vs_oracle(n, count):
+    """Batches that are all 4x4 (one job per thread) or all 8x8 (one per 8 lanes), strided and contiguous, SAD / SATD /
+    reg_sad mixed, with a ragged tail that takes the warp-per-job path; and a batch with one larger block in the middle."""
+    from kvazaar_b200 import blocks
+    O = kvzlibs.oracle()
+    rs = np.random.default_rng(100 + n + count)
+    a = rs.integers(0, 256, (96, 160), dtype=np.uint8)
+    b = rs.integers(0, 256, (96, 176), dtype=np.uint8)
+    for spoil in (False, True):
+        jobs, want = [], []
+        for i in range(count):
+            kind = (blocks.COST_REG_SAD, blocks.COST_SAD_NXN, blocks.COST_SATD_NXN)[int(rs.integers(0, 3))]
+            w = h = n
+            if spoil and i == 40 % count:
+                w = h = 16
+            ox, oy = int(rs.integers(0, 140)), int(rs.integers(0, 70))
+            ao, bo = oy * 160 + ox, oy * 176 + ox
+            av, bv = a.reshape(-1)[ao:], b.reshape(-1)[bo:]
+            if kind == blocks.COST_SATD_NXN:
+                ca = np.ascontiguousarray(a[oy:oy + h, ox:ox + w]).reshape(-1)
+                cb = np.ascontiguousarray(b[oy:oy + h, ox:ox + w]).reshape(-1)
+                want.append(O.kvzo_satd_nxn_8(w, ptr(ca), ptr(cb)))
+            else:
+                want.append(O.kvzo_reg_sad_8(ptr(av), ptr(bv), w, h, 160, 176))
+            jobs.append((ao, bo, 160, 176, w, h, kind))
+        got = _gpu_block(a, b, np.array(jobs, blocks.BLOCK_JOB_DT))
+        assert got.tolist() == want, (n, count, spoil)
+
+
 def test_image_costs_vs_oracle_1080p():
     import torch
     from kvazaar_b200 import blocks
