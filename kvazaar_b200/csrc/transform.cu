@@ -459,6 +459,226 @@ static int residual_grid(int n_jobs)
   return groups < sm_count() * 8 ? groups : sm_count() * 8;
 }
 
+// ---- 4x4 and 8x8 transforms of a batch: one block per THREAD ----
+// A frame's worth of small blocks is where a warp (let alone a CTA) per block idles: here the block lives in the
+// thread's registers, both passes are fully unrolled exact int32 products (the same sums as fwd_pass_smem /
+// inv_pass_smem, dct-generic.c:258, 571-583), the NxN matrix is read from shared memory (every lane reads the same
+// entry: a broadcast), and the block moves as 16-byte vectors.
+template <int N>
+__global__ void __launch_bounds__(kThreads)
+transform_small_kernel(int dst4, int inverse, int bitdepth, const int16_t *__restrict__ in, int16_t *__restrict__ out, int count)
+{
+  __shared__ int16_t m[N * N];
+  for (int i = threadIdx.x; i < N * N; i += kThreads) {
+    const int k = i / N, n = i - k * N;
+    int v;
+    if (dst4) v = c_dst4[k][n];
+    else {
+      int q = ((32 / N) * k * (2 * n + 1)) & 127;
+      if (q > 64) q = 128 - q;
+      v = q <= 32 ? c_hevc_cos_q[q] : -c_hevc_cos_q[64 - q];
+    }
+    m[i] = (int16_t)v;
+  }
+  __syncthreads();
+  constexpr int lg = N == 4 ? 2 : 3;
+  constexpr int kVec = N * N / 8;                       // 16-byte vectors per block
+  for (int blk = blockIdx.x * kThreads + threadIdx.x; blk < count; blk += gridDim.x * kThreads) {
+    int a[N * N], b[N * N];
+    const uint4 *src = reinterpret_cast<const uint4 *>(in + (size_t)blk * N * N);
+#pragma unroll
+    for (int v = 0; v < kVec; v++) {
+      const uint4 q = __ldg(src + v);
+      const uint32_t w[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        a[v * 8 + 2 * i] = (int)(int16_t)(w[i] & 0xFFFFu);
+        a[v * 8 + 2 * i + 1] = (int)(int16_t)(w[i] >> 16);
+      }
+    }
+    if (!inverse) {
+      const int s1 = lg - 1 + (bitdepth - 8), s2 = lg + 6;
+      const int r1 = s1 > 0 ? 1 << (s1 - 1) : 0, r2 = 1 << (s2 - 1);
+#pragma unroll
+      for (int k = 0; k < N; k++)
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+          int s = 0;
+#pragma unroll
+          for (int n = 0; n < N; n++) s += (int)m[k * N + n] * a[j * N + n];
+          b[k * N + j] = (int)(int16_t)((s + r1) >> s1);
+        }
+#pragma unroll
+      for (int k = 0; k < N; k++)
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+          int s = 0;
+#pragma unroll
+          for (int n = 0; n < N; n++) s += (int)m[k * N + n] * b[j * N + n];
+          a[k * N + j] = (int)(int16_t)((s + r2) >> s2);
+        }
+    } else {
+      const int s2 = 12 - (bitdepth - 8);
+#pragma unroll
+      for (int j = 0; j < N; j++)
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+          int s = 0;
+#pragma unroll
+          for (int k = 0; k < N; k++) s += (int)m[k * N + n] * a[k * N + j];
+          b[j * N + n] = clampi((s + 64) >> 7, -32768, 32767);
+        }
+#pragma unroll
+      for (int j = 0; j < N; j++)
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+          int s = 0;
+#pragma unroll
+          for (int k = 0; k < N; k++) s += (int)m[k * N + n] * b[k * N + j];
+          a[j * N + n] = clampi((s + (1 << (s2 - 1))) >> s2, -32768, 32767);
+        }
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(out + (size_t)blk * N * N);
+#pragma unroll
+    for (int v = 0; v < kVec; v++) {
+      uint32_t w[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) w[i] = ((uint32_t)a[v * 8 + 2 * i] & 0xFFFFu) | ((uint32_t)a[v * 8 + 2 * i + 1] << 16);
+      dst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
+// ---- 16x16 and 32x32 transforms of a batch: one block row per LANE ----
+// N lanes hold the N rows of a block in registers (two 16x16 blocks or one 32x32 block per warp).  A pass is N*N
+// multiply-adds per lane whose matrix entries are immediates (hevc_m<N>(k, n) folds after unrolling); between the
+// passes the block is transposed through a pitch N + 2 shared-memory tile (conflict-free both ways), with warp
+// barriers only.  Same sums, shifts and clips as fwd_pass_smem / inv_pass_smem (dct-generic.c:258, 571-583).
+__host__ __device__ constexpr int hevc_cos_at(int m)
+{
+  switch (m) {
+    case 0: return 64; case 1: return 90; case 2: return 90; case 3: return 90; case 4: return 89; case 5: return 88;
+    case 6: return 87; case 7: return 85; case 8: return 83; case 9: return 82; case 10: return 80; case 11: return 78;
+    case 12: return 75; case 13: return 73; case 14: return 70; case 15: return 67; case 16: return 64; case 17: return 61;
+    case 18: return 57; case 19: return 54; case 20: return 50; case 21: return 46; case 22: return 43; case 23: return 38;
+    case 24: return 36; case 25: return 31; case 26: return 25; case 27: return 22; case 28: return 18; case 29: return 13;
+    case 30: return 9; case 31: return 4; default: return 0;
+  }
+}
+template <int N>
+__host__ __device__ constexpr int hevc_m(int k, int n)
+{
+  int q = ((32 / N) * k * (2 * n + 1)) & 127;
+  if (q > 64) q = 128 - q;
+  return q <= 32 ? hevc_cos_at(q) : -hevc_cos_at(64 - q);
+}
+
+template <int N, bool INV>
+__global__ void __launch_bounds__(kThreads)
+transform_rows_kernel(int bitdepth, const int16_t *__restrict__ in, int16_t *__restrict__ out, int count)
+{
+  constexpr int kPerWarp = 32 / N, kPitch = N + 2, lg = N == 16 ? 4 : 5;
+  __shared__ int16_t tiles[kWarps][kPerWarp][N * kPitch];
+  // 32x32: 2 x 1024 multiply-adds with immediate operands would be 32 KB of straight-line code per pass pair (measured:
+  // 5.5 ms per 32768 blocks, instruction fetch bound); the matrix rows come from shared memory instead (every lane
+  // reads the same 16 bytes: a broadcast) in a loop over the output index.  INV reads columns: the table is transposed.
+  __shared__ __align__(16) int32_t mtab[N == 32 ? 32 * 32 : 4];
+  if (N == 32) {
+    for (int i = threadIdx.x; i < 32 * 32; i += kThreads) {
+      const int r = i >> 5, c = i & 31;
+      mtab[i] = INV ? hevc_m<32>(c, r) : hevc_m<32>(r, c);      // forward: row k of M; inverse: column n of M
+    }
+    __syncthreads();
+  }
+  auto dot = [&](int o, const int (&v)[N]) {                   // forward: sum_n M[o][n] v[n]; inverse: sum_k M[k][o] v[k]
+    int s = 0;
+    if (N == 32) {
+      const int4 *row = reinterpret_cast<const int4 *>(mtab + o * 32);
+#pragma unroll
+      for (int q = 0; q < N / 4; q++) {
+        const int4 mm = row[q];
+        s += mm.x * v[4 * q] + mm.y * v[4 * q + 1] + mm.z * v[4 * q + 2] + mm.w * v[4 * q + 3];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < N; i++) s += (INV ? hevc_m<N>(i, o) : hevc_m<N>(o, i)) * v[i];
+    }
+    return s;
+  };
+  constexpr int kUnroll = N == 32 ? 2 : N;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sub = lane / N, j = lane % N;
+  int16_t *t = tiles[warp][sub];
+  for (int base = (blockIdx.x * kWarps + warp) * kPerWarp; base < count; base += gridDim.x * kWarps * kPerWarp) {
+    const int blk = base + sub;
+    const bool on = blk < count;
+    int x[N], y[N];
+    {
+      const uint4 *src = reinterpret_cast<const uint4 *>(in + ((size_t)(on ? blk : base) * N + j) * N);
+#pragma unroll
+      for (int v = 0; v < N / 8; v++) {
+        const uint4 q = __ldg(src + v);
+        const uint32_t w[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          x[v * 8 + 2 * i] = (int)(int16_t)(w[i] & 0xFFFFu);
+          x[v * 8 + 2 * i + 1] = (int)(int16_t)(w[i] >> 16);
+        }
+      }
+    }
+    if (!INV) {
+      const int s1 = lg - 1 + (bitdepth - 8), s2 = lg + 6;
+      const int r1 = 1 << (s1 - 1), r2 = 1 << (s2 - 1);
+      // pass 1: lane j makes column j of b:  b[k][j] = (sum_n M[k][n] a[j][n] + r1) >> s1
+#pragma unroll kUnroll
+      for (int k = 0; k < N; k++) t[k * kPitch + j] = (int16_t)((dot(k, x) + r1) >> s1);
+      __syncwarp();
+#pragma unroll
+      for (int n = 0; n < N; n++) x[n] = t[j * kPitch + n];                 // row j of b
+      __syncwarp();
+      // pass 2: column j of the result:  c[k][j] = (sum_n M[k][n] b[j][n] + r2) >> s2
+#pragma unroll kUnroll
+      for (int k = 0; k < N; k++) t[k * kPitch + j] = (int16_t)((dot(k, x) + r2) >> s2);
+      __syncwarp();
+#pragma unroll
+      for (int n = 0; n < N; n++) y[n] = t[j * kPitch + n];                 // row j of the result
+      __syncwarp();
+    } else {
+      const int s2 = 12 - (bitdepth - 8);
+#pragma unroll
+      for (int n = 0; n < N; n++) t[j * kPitch + n] = (int16_t)x[n];
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < N; k++) x[k] = t[k * kPitch + j];                 // column j of a
+      __syncwarp();
+      // pass 1: row j of b:  b[j][n] = clip16((sum_k M[k][n] a[k][j] + 64) >> 7)
+#pragma unroll kUnroll
+      for (int n = 0; n < N; n++) t[j * kPitch + n] = (int16_t)clampi((dot(n, x) + 64) >> 7, -32768, 32767);
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < N; k++) x[k] = t[k * kPitch + j];                 // column j of b
+      __syncwarp();
+      // pass 2: row j of the result:  c[j][n] = clip16((sum_k M[k][n] b[k][j] + r) >> s2)
+      // (the result goes through the tile as well when the loop is not unrolled: y[] must stay in registers)
+#pragma unroll kUnroll
+      for (int n = 0; n < N; n++) t[j * kPitch + n] = (int16_t)clampi((dot(n, x) + (1 << (s2 - 1))) >> s2, -32768, 32767);
+      __syncwarp();
+#pragma unroll
+      for (int n = 0; n < N; n++) y[n] = t[j * kPitch + n];
+      __syncwarp();
+    }
+    if (on) {
+      uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)blk * N + j) * N);
+#pragma unroll
+      for (int v = 0; v < N / 8; v++) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] = ((uint32_t)y[v * 8 + 2 * i] & 0xFFFFu) | ((uint32_t)y[v * 8 + 2 * i + 1] << 16);
+        dst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+}
+
 template <typename K>
 static int opt_in_smem(K kern)
 {
@@ -471,6 +691,27 @@ int launch_transform_batch(int n, int dst4, int inverse, int bitdepth, const int
 {
   if (!valid_n(n) || (dst4 && n != 4)) return fail_msg("transform: n must be 4, 8, 16 or 32 (DST only for 4)");
   if (count <= 0) return 1;
+  if (n <= 8 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {     // a block per thread
+    int grid = (count + kThreads - 1) / kThreads;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
+    if (n == 4) transform_small_kernel<4><<<grid, kThreads, 0, stream>>>(dst4, inverse, bitdepth, in, out, count);
+    else transform_small_kernel<8><<<grid, kThreads, 0, stream>>>(dst4, inverse, bitdepth, in, out, count);
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+    return 1;
+  }
+  if (n >= 16 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {    // a block row per lane
+    const int per_cta = kWarps * (32 / n);
+    int grid = (count + per_cta - 1) / per_cta;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
+    if (n == 16 && !inverse) transform_rows_kernel<16, false><<<grid, kThreads, 0, stream>>>(bitdepth, in, out, count);
+    else if (n == 16) transform_rows_kernel<16, true><<<grid, kThreads, 0, stream>>>(bitdepth, in, out, count);
+    else if (!inverse) transform_rows_kernel<32, false><<<grid, kThreads, 0, stream>>>(bitdepth, in, out, count);
+    else transform_rows_kernel<32, true><<<grid, kThreads, 0, stream>>>(bitdepth, in, out, count);
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+    return 1;
+  }
   if (!opt_in_smem(transform_batch_kernel)) return 0;
   const int grid = batch_grid(n, count);
   transform_batch_kernel<<<grid, kThreads, sizeof(BlockSmem), stream>>>(n, dst4, inverse, bitdepth, in, out, count);
