@@ -221,9 +221,10 @@ def run_ours(args):
                 y = frames[i][0]
                 if not glue.kvz_glue_preload_source(i, y.ctypes.data_as(C.c_void_p), y.strides[0]):
                     raise SystemExit("bench.py: kvz_glue_preload_source failed")
-        m0, s0 = (C.c_ulonglong * 8)(), (C.c_ulonglong * 8)()
+        m0, s0, c0 = (C.c_ulonglong * 8)(), (C.c_ulonglong * 8)(), (C.c_ulonglong * 4)()
         glue.kvz_glue_enc_measurements(m0)
         glue.kvz_glue_enc_stats(s0)
+        glue.kvz_glue_spec_counts(c0)
         l0 = int(L.kvz_cuda_launch_count())
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -238,10 +239,12 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         m1 = (C.c_ulonglong * 8)()
         glue.kvz_glue_enc_measurements(m1)
-        s1 = (C.c_ulonglong * 8)()
+        s1, c1 = (C.c_ulonglong * 8)(), (C.c_ulonglong * 4)()
         glue.kvz_glue_enc_stats(s1)
+        glue.kvz_glue_spec_counts(c1)
         rec = {"ms": float(ms.item()), "host_ms": host_ms, "launches": int(L.kvz_cuda_launch_count()) - l0,
-               "m": [int(b) - int(a) for a, b in zip(m0, m1)], "pu_searches": int(s1[1]) - int(s0[1]),
+               "m": [int(b) - int(a) for a, b in zip(m0, m1)], "pus_launched": int(s1[1]) - int(s0[1]),
+               "answered_ahead": int(c1[0]) - int(c0[0]), "searched_on_the_spot": int(c1[1]) - int(c0[1]),
                "ref_jobs": int(s1[5]) - int(s0[5]), "jobs_outside_box": int(s1[6]) - int(s0[6]),
                "map_mib_last": int(s1[3]) / 2 ** 20, "md5": r.md5.hexdigest()}
         r.close()
@@ -283,7 +286,9 @@ def run_ours(args):
             "value_vs_e2e": "value: source luma of the timed pictures preloaded into HBM (kvz_cuda_enc_preload_source); "
                             "e2e: every picture from host memory. Reconstructed reference pictures come from the host's own "
                             "in-loop filters in both runs.",
-            "pu_searches_per_step": e2e["pu_searches"] / steps,
+            "pu_searches_per_step": (e2e["answered_ahead"] + e2e["searched_on_the_spot"]) / steps,
+            "share_of_searches_answered_by_a_launch_made_ahead": e2e["answered_ahead"] / max(1, e2e["answered_ahead"] + e2e["searched_on_the_spot"]),
+            "pus_launched_per_step": e2e["pus_launched"] / steps,
             "reference_jobs_per_step": e2e["ref_jobs"] / steps,
             "share_of_jobs_with_a_window_outside_the_box": e2e["jobs_outside_box"] / max(1, e2e["ref_jobs"]),
             "sad_maps_mib_last_picture": e2e["map_mib_last"],

@@ -602,7 +602,7 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
   }
   if (!worker_ready(e)) return fail("per-thread streams / staging", cudaGetLastError(), __FILE__, __LINE__);
   Worker &w = t_worker;
-  if (e->timing && ctx->f.ime_search == KVZ_CUDA_IME_FULL)
+  if (ctx->f.ime_search == KVZ_CUDA_IME_FULL)
     for (int p = 0; p < n_pus; p++)
       for (int i = 0; i < pus[p].num_jobs; i++)
         if (!job_in_box(*ctx, e->cfg.range, pus[p], jobs[(size_t)p * KVZ_CUDA_MAX_REFS + i])) e->stats[6]++;

@@ -144,6 +144,12 @@ KVZ_PUBLIC int kvz_glue_enc_stats(unsigned long long s[8])
   return 1;
 }
 
+/* c[0] searches answered by a launch made ahead, c[1] searched on the spot, c[2] PUs launched ahead, c[3] PUs launched */
+KVZ_PUBLIC void kvz_glue_spec_counts(unsigned long long c[4])
+{
+  for (int i = 0; i < 4; i++) c[i] = __atomic_load_n(&g_spec_cnt[i], __ATOMIC_RELAXED);
+}
+
 /* the source luma of the picture the host will feed with presentation number `pts`, put on the device ahead of time */
 KVZ_PUBLIC int kvz_glue_preload_source(int64_t pts, const uint8_t *luma, int stride)
 {
