@@ -445,6 +445,8 @@ static int sm_count()
   return g_sms;
 }
 
+static int ilog2_host(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
+
 // persistent CTAs: 4 per SM; a CTA serves kWarps blocks at a time when they are 4x4 / 8x8
 static int batch_grid(int n, int count)
 {
@@ -679,6 +681,139 @@ transform_rows_kernel(int bitdepth, const int16_t *__restrict__ in, int16_t *__r
   }
 }
 
+// ---- kvz_quant of a batch, one 16-coefficient group per THREAD (blocks of 4x4, 8x8, 16x16) ----
+// The quantiser proper is per coefficient and the sign-bit hiding per coefficient group (quant-generic.c:69-162); what
+// a block shares is the sum of its levels (hiding needs >= 2) and which group is the last one with a level.  So a
+// thread takes a group -- its 4x4 corner of the block as four 8-byte loads, visited in the scan's order through a
+// compile-time permutation, everything in registers -- and the (N/4)^2 lanes of a block exchange the two block-wide
+// facts with shuffles.  Same arithmetic as quant_block; the backward walk with its strict '<' is kept as it is.
+__host__ __device__ constexpr int cg_raster(int scan, int k)     // raster index (y * 4 + x) of the k-th coefficient of a group
+{
+  constexpr int diag[16] = { 0, 4, 1, 8, 5, 2, 12, 9, 6, 3, 13, 10, 7, 14, 11, 15 };
+  return scan == 0 ? diag[k] : scan == 1 ? k : (k & 3) * 4 + (k >> 2);
+}
+
+template <int N, int SCAN>
+__global__ void __launch_bounds__(kThreads)
+quant_groups_kernel(kvz_cuda_quant_cfg c, int type, const int16_t *__restrict__ in, int16_t *__restrict__ out, int count)
+{
+  constexpr int G = (N / 4) * (N / 4), kPerCta = kThreads / G, lg = N == 4 ? 2 : N == 8 ? 3 : 4;
+  __shared__ uint8_t gxs[16], gys[16];
+  if (threadIdx.x == 0) square_scan(SCAN, N / 4, gxs, gys);
+  __syncthreads();
+  const int qp_s = scaled_qp(type, c.qp, (c.bitdepth - 8) * 6);
+  const long long qc = c_quant_scale[qp_s % 6];
+  const int q_bits = 14 + qp_s / 6 + (15 - c.bitdepth - lg);
+  const int add = (c.slice_is_intra ? 171 : 85) << (q_bits - 9);
+  const int g = threadIdx.x % G;
+  const int gx = gxs[g], gy = gys[g];
+  for (int base = blockIdx.x * kPerCta; base < count; base += gridDim.x * kPerCta) {
+    const int blk = base + threadIdx.x / G;
+    const bool on = blk < count;
+    const size_t corner = (size_t)(on ? blk : base) * N * N + (size_t)gy * 4 * N + gx * 4;
+    int a[16];
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2 *>(in + corner + (size_t)y * N));
+      a[4 * y] = (int)(int16_t)(v.x & 0xFFFFu); a[4 * y + 1] = (int)(int16_t)(v.x >> 16);
+      a[4 * y + 2] = (int)(int16_t)(v.y & 0xFFFFu); a[4 * y + 3] = (int)(int16_t)(v.y >> 16);
+    }
+    int q[16], dl[16];
+    uint32_t neg = 0, my_sum = 0;
+    bool any = false;
+#pragma unroll
+    for (int n = 0; n < 16; n++) {
+      const int cf = a[cg_raster(SCAN, n)];
+      const long long prod = (long long)abs(cf) * qc;
+      int level = (int)((prod + add) >> q_bits);
+      my_sum += (uint32_t)level;
+      dl[n] = (int)((prod - ((long long)level << q_bits)) >> (q_bits - 8));
+      if (cf < 0) { level = -level; neg |= 1u << n; }
+      q[n] = clampi(level, -32768, 32767);
+      any |= q[n] != 0;
+    }
+    uint32_t acc = my_sum;
+    int last_cg = any ? g : -1;
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+      acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      last_cg = max(last_cg, __shfl_xor_sync(0xffffffffu, last_cg, o));
+    }
+    if (c.signhide && acc >= 2) {
+      int first = 16, last = -1, qfirst = 0;
+#pragma unroll
+      for (int n = 0; n < 16; n++) if (q[n] != 0) last = n;
+#pragma unroll
+      for (int n = 15; n >= 0; n--) if (q[n] != 0) { first = n; qfirst = q[n]; }
+      if (last - first >= 4) {
+        int sum = 0;
+#pragma unroll
+        for (int n = 0; n < 16; n++) if (n >= first && n <= last) sum += q[n];
+        const int signbit = qfirst > 0 ? 0 : 1;
+        if (signbit != (sum & 1)) {
+          const int top = g == last_cg ? last : 15;
+          int best = 0x7FFFFFFF, bestn = -1, change = 0;
+#pragma unroll
+          for (int n = 15; n >= 0; n--) {
+            if (n > top) continue;
+            int cost = 0x7FFFFFFF, cur_change = 0;
+            if (q[n] != 0) {
+              if (dl[n] > 0) { cost = -dl[n]; cur_change = 1; }
+              else if (n == first && abs(q[n]) == 1) { cost = 0x7FFFFFFF; }
+              else { cost = dl[n]; cur_change = -1; }
+            } else if (n < first && (int)((neg >> n) & 1u) != signbit) {
+              cost = 0x7FFFFFFF;
+            } else {
+              cost = -dl[n]; cur_change = 1;
+            }
+            if (cost < best) { best = cost; change = cur_change; bestn = n; }
+          }
+          if (bestn >= 0) {
+#pragma unroll
+            for (int n = 0; n < 16; n++)
+              if (n == bestn) {
+                int ch = change;
+                if (q[n] == 32767 || q[n] == -32768) ch = -1;
+                q[n] = (int)(int16_t)(((neg >> n) & 1u) ? q[n] - ch : q[n] + ch);
+              }
+          }
+        }
+      }
+    }
+    if (on) {
+#pragma unroll
+      for (int n = 0; n < 16; n++) a[cg_raster(SCAN, n)] = q[n];
+#pragma unroll
+      for (int y = 0; y < 4; y++) {
+        const uint32_t lo = ((uint32_t)a[4 * y] & 0xFFFFu) | ((uint32_t)a[4 * y + 1] << 16);
+        const uint32_t hi = ((uint32_t)a[4 * y + 2] & 0xFFFFu) | ((uint32_t)a[4 * y + 3] << 16);
+        *reinterpret_cast<uint2 *>(out + corner + (size_t)y * N) = make_uint2(lo, hi);
+      }
+    }
+  }
+}
+
+// kvz_dequant with the flat scaling list (quant-generic.c:279-321) is per coefficient: 8 levels per thread
+__global__ void __launch_bounds__(256)
+dequant_flat_kernel(kvz_cuda_quant_cfg c, int lg, int type, const int16_t *__restrict__ in, int16_t *__restrict__ out, size_t n8)
+{
+  const int qp_s = scaled_qp(type, c.qp, (c.bitdepth - 8) * 6);
+  const int shift = 20 - 14 - (15 - c.bitdepth - lg);
+  const int scale = c_inv_quant_scale[qp_s % 6] << (qp_s / 6);
+  const int add = 1 << (shift - 1);
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n8; i += (size_t)gridDim.x * 256) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(in) + i);
+    uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int lo = clampi(((int)(int16_t)(w[k] & 0xFFFFu) * scale + add) >> shift, -32768, 32767);
+      const int hi = clampi(((int)(int16_t)(w[k] >> 16) * scale + add) >> shift, -32768, 32767);
+      w[k] = ((uint32_t)lo & 0xFFFFu) | ((uint32_t)hi << 16);
+    }
+    reinterpret_cast<uint4 *>(out)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 template <typename K>
 static int opt_in_smem(K kern)
 {
@@ -725,6 +860,29 @@ int launch_quant_batch(const kvz_cuda_quant_cfg &c, int n, int type, int scan_id
 {
   if (!valid_n(n)) return fail_msg("quant: n must be 4, 8, 16 or 32");
   if (count <= 0) return 1;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (aligned && dequant) {
+    const size_t n8 = (size_t)count * n * n / 8;
+    size_t grid = (n8 + 255) / 256;
+    if (grid > (size_t)sm_count() * 16) grid = (size_t)sm_count() * 16;
+    dequant_flat_kernel<<<(int)grid, 256, 0, stream>>>(c, ilog2_host(n), type, in, out, n8);
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+    return 1;
+  }
+  if (aligned && n <= 16 && scan_idx >= 0 && scan_idx <= 2) {        // a coefficient group per thread
+    const int per_cta = kThreads / ((n / 4) * (n / 4));
+    int grid = (count + per_cta - 1) / per_cta;
+    if (grid > sm_count() * 16) grid = sm_count() * 16;
+#define KVZ_QUANT_GROUPS(NN, SS) quant_groups_kernel<NN, SS><<<grid, kThreads, 0, stream>>>(c, type, in, out, count)
+    if (n == 4) { if (scan_idx == 0) KVZ_QUANT_GROUPS(4, 0); else if (scan_idx == 1) KVZ_QUANT_GROUPS(4, 1); else KVZ_QUANT_GROUPS(4, 2); }
+    else if (n == 8) { if (scan_idx == 0) KVZ_QUANT_GROUPS(8, 0); else if (scan_idx == 1) KVZ_QUANT_GROUPS(8, 1); else KVZ_QUANT_GROUPS(8, 2); }
+    else { if (scan_idx == 0) KVZ_QUANT_GROUPS(16, 0); else if (scan_idx == 1) KVZ_QUANT_GROUPS(16, 1); else KVZ_QUANT_GROUPS(16, 2); }
+#undef KVZ_QUANT_GROUPS
+    count_launch();
+    KVZ_CUDA_LAUNCH_CHECK();
+    return 1;
+  }
   if (!opt_in_smem(quant_batch_kernel)) return 0;
   const int grid = batch_grid(n, count);
   quant_batch_kernel<<<grid, kThreads, sizeof(BlockSmem), stream>>>(c, n, type, scan_idx, dequant, in, out, count);
