@@ -310,6 +310,10 @@ def run_ours(args):
             "traffic": None,
             "traffic_note": "no ncu capture of this launch inside the bench; see profiles/ for the round's captures",
             "share_of_step_ms": dense_ms / (e2e["ms"] / steps),
+            # BASELINE's second metric, ME Gcand/s = (PU, reference, integer vector) costs produced per second: every map
+            # entry is one; the 8x8 level has abs_diffs / 64 of them and the four levels together 85 / 64 of that
+            "me_gcand_per_s_dense_kernel": (m[5] / 64 * 85 / 64) / (m[4] / 1e9) / 1e9 if m[4] else None,
+            "me_gcand_per_s_in_encode": (m[5] / 64 * 85 / 64) / (e2e["ms"] / 1e3) / 1e9,
         },
         "clocks": clk,
         "e2e": {"value": fps_e2e, "unit": UNIT, "ms_per_step": e2e["ms"] / steps, "host_ms_per_step": e2e["host_ms"] / steps,
