@@ -199,6 +199,8 @@ def run_ours(args):
     os.environ["KVZ_CUDA_MODE"] = "batch"
     os.environ["KVZ_CUDA_DEVICE"] = str(local)
     threads = max(2, (os.cpu_count() or 2) // world)          # the ranks of one box share its host cores
+    if os.environ.get("KVZ_BENCH_THREADS"):                  # experiments: worker threads per rank
+        threads = int(os.environ["KVZ_BENCH_THREADS"])
     steps, warmup = args.steps, args.warmup
     if warmup < 2:
         raise SystemExit("bench.py: --warmup must be at least 2 (the first picture is intra: the session opens on the second)")

@@ -425,6 +425,7 @@ static int glue_batch_launch(kvz_cuda_enc *enc, uint64_t frame_id, int handle, i
   }
   int ticket = -1;
   if (!kvz_cuda_enc_search_begin(enc, handle, lambda, b->n, pus, jobs, &ticket)) kvz_glue_die("kvz_cuda_enc_search_begin");
+  if ((ticket & 0xFF) >= GLUE_SPEC_SLOTS) kvz_glue_die("kvz_cuda_enc_search_begin: ticket slot beyond the glue's table");
   glue_spec *row = t_spec[ticket & 0xFF];
   for (int i = 0; i < GLUE_SPEC_PUS; i++) { row[i].valid = 0; t_key[ticket & 0xFF][i] = 0; }
   for (int i = 0; i < b->n; i++) {
