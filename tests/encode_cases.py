@@ -42,6 +42,12 @@ CASES = {
     "owf2_1080p_full32": (1920, 1080, 6, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 2"),
     # config 2 itself, first frames
     "c2_1080p_3frames": (1920, 1080, 3, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 0"),
+    # the bench's configuration for a whole GOP: frames in flight and PU searches launched ahead of the CU walk
+    "c2_1080p_owf3_gop": (1920, 1080, 9, 2, "--preset medium --me full32 --gop 8 -r 4 --owf 3"),
+    # search range 64 (windows of 129 x 129: the boxes are at their caps and many windows are evaluated on demand)
+    "full64_small": (416, 240, 9, 2, "--preset medium --me full64 --gop 8 -r 2 --owf 0"),
+    # the hostile clip: white noise, arbitrary vectors, nothing predicts anything (launches ahead mostly miss)
+    "noise_full16_owf1": (416, 240, 6, 99, "--preset medium --me full16 --gop 8 -r 2 --owf 1"),
 }
 # cases cheap enough for the per-call face (one launch per strategy call)
 PERCALL_CASES = {

@@ -1,5 +1,5 @@
 """Writes the seeded synthetic yuv420p clips of SURVEY.md 8(d): luma = kvzlibs.synth_luma (band-limited texture,
-global motion (+5,+3) px/frame, +-4 noise), U = Y[::2,::2]//2 + 2^(BD-2), V = 2^BD-1-U.
+global motion (+5,+3) px/frame, +-4 noise; seed 99 = white noise), U = Y[::2,::2]//2 + 2^(BD-2), V = 2^BD-1-U.
 usage: python tools/make_clip.py OUT.yuv WIDTH HEIGHT FRAMES SEED [BITDEPTH]"""
 import os
 import sys
@@ -10,8 +10,18 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."
 import kvzlibs  # noqa: E402
 
 
+def luma_frames(seed, w, h, frames, bitdepth=8):
+    """seed 99: the hostile clip of SURVEY.md 8(d) -- uniform white noise, a new field every frame (no early-out ever
+    fires, motion vectors are arbitrary); any other seed: kvzlibs.synth_luma"""
+    if seed == 99:
+        rng = np.random.default_rng(99)
+        dt = np.uint8 if bitdepth == 8 else np.uint16
+        return [rng.integers(0, 1 << bitdepth, (h, w)).astype(dt) for _ in range(frames)]
+    return kvzlibs.synth_luma(seed, w, h, frames, bitdepth)
+
+
 def clip_planes(seed, w, h, frames, bitdepth=8):
-    for y in kvzlibs.synth_luma(seed, w, h, frames, bitdepth):
+    for y in luma_frames(seed, w, h, frames, bitdepth):
         u = (y[::2, ::2] // 2 + (1 << (bitdepth - 2))).astype(y.dtype)
         v = ((1 << bitdepth) - 1 - u).astype(y.dtype)
         yield y, u, v
