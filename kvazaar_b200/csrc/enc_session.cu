@@ -136,6 +136,7 @@ struct kvz_cuda_enc {
   // every job lay inside its reference's box
   bool timing = false;
   std::atomic<unsigned long long> t_ns[4][2], t_calls[4][2];
+  std::atomic<unsigned long long> t_host[4][2];      // KVZ_CUDA_STATS: {ns, calls} of ctu_begin, the PU launch call, frame_begin, stream waits
 };
 
 namespace {
@@ -324,7 +325,7 @@ kvz_cuda_enc *kvz_cuda_enc_open(const kvz_cuda_enc_cfg *cfg)
   if (e->cfg.max_map_mbytes <= 0) e->cfg.max_map_mbytes = 98304;       // of 180 GB; shared by the owf + 1 frames in flight
   for (auto &s : e->stats) s = 0;
   for (auto &s : e->meas) s = 0;
-  for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) { e->t_ns[a][b] = 0; e->t_calls[a][b] = 0; }
+  for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) { e->t_ns[a][b] = 0; e->t_calls[a][b] = 0; e->t_host[a][b] = 0; }
   e->timing = getenv("KVZ_CUDA_STATS") != nullptr;
   e->pitch = (cfg->width + 2 * kPad + 63) & ~63;
   e->plane_bytes = (size_t)e->pitch * (cfg->height + 2 * kPad);
@@ -370,6 +371,16 @@ int kvz_cuda_enc_frame_begin(kvz_cuda_enc *e, const kvz_cuda_enc_frame *fr)
   std::lock_guard<std::mutex> guard(e->lock);
   for (size_t i = 0; i < e->ctxs.size(); i++)
     if (e->ctxs[i]->id == fr->frame_id) return (int)i;              // another thread began this (frame, tile)
+  struct FbTimer {
+    kvz_cuda_enc *e; struct timespec t0;
+    explicit FbTimer(kvz_cuda_enc *e_) : e(e_) { if (e->timing) clock_gettime(CLOCK_MONOTONIC, &t0); }
+    ~FbTimer() {
+      if (!e->timing) return;
+      struct timespec t1; clock_gettime(CLOCK_MONOTONIC, &t1);
+      e->t_host[2][0] += (unsigned long long)((t1.tv_sec - t0.tv_sec) * 1000000000ll + (t1.tv_nsec - t0.tv_nsec));
+      e->t_host[2][1]++;
+    }
+  } fb_timer(e);
   if (cudaSetDevice(e->cfg.device) != cudaSuccess) { fail("cudaSetDevice", cudaGetLastError(), __FILE__, __LINE__); return -1; }
   const kvz_cuda_enc_cfg &cfg = e->cfg;
   const uint64_t frame_num = fr->frame_id >> 16;
@@ -618,8 +629,15 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
   const int ctu = ctu_y * ctx->f.ctus_x + ctu_x;
   if (ctx->n_partial > 0 && w.cur_ctu != ctu) {            // --owf: references in flight are prepared CTU by CTU
     if (w.seen_ctx[0] != tag) { KVZ_CUDA_TRY(cudaStreamWaitEvent(w.streams[0], ctx->ready, 0)); w.seen_ctx[0] = tag; }
+    struct timespec c0, c1;
+    if (e->timing) clock_gettime(CLOCK_MONOTONIC, &c0);
     if (!ctu_begin(e, ctx, ctu_x, ctu_y, w.streams[0])) return 0;
     KVZ_CUDA_TRY(cudaEventRecord(w.ctu_ready, w.streams[0]));
+    if (e->timing) {
+      clock_gettime(CLOCK_MONOTONIC, &c1);
+      e->t_host[0][0] += (unsigned long long)((c1.tv_sec - c0.tv_sec) * 1000000000ll + (c1.tv_nsec - c0.tv_nsec));
+      e->t_host[0][1]++;
+    }
     w.cur_ctu = ctu; w.seen_ctu[0] = ctu;
   }
   const uint32_t slot = w.next_slot++ % kSlots;
@@ -638,8 +656,15 @@ int kvz_cuda_enc_search_begin(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, in
   const uint32_t gen = ++w.gen[slot];
   uint8_t *dslot = w.d + (size_t)slot * kSlotBytes;
   // the PUs and their jobs go in the launch itself; results and completion words come back through the mapped slot
+  struct timespec l0, l1;
+  if (e->timing) clock_gettime(CLOCK_MONOTONIC, &l0);
   if (!launch_me_search_pu(f, nullptr, nullptr, reinterpret_cast<kvz_cuda_me_result *>(dslot), n_pus, stream, pus, jobs,
                            reinterpret_cast<uint32_t *>(dslot + kSlotResults), gen)) return 0;
+  if (e->timing) {
+    clock_gettime(CLOCK_MONOTONIC, &l1);
+    e->t_host[1][0] += (unsigned long long)((l1.tv_sec - l0.tv_sec) * 1000000000ll + (l1.tv_nsec - l0.tv_nsec));
+    e->t_host[1][1]++;
+  }
   w.n_pus[slot] = (uint8_t)n_pus;
   for (int p = 0; p < n_pus; p++) {
     w.n_jobs[slot][p] = pus[p].num_jobs;
@@ -753,6 +778,13 @@ void kvz_cuda_enc_stats(const kvz_cuda_enc *e, unsigned long long stats[8])
         if (ph[sz][3])
           fprintf(stderr, "kvz_cuda_enc: PU %2d  device time per call: box scan %.1f us, CTA scan %.1f us, refinement %.1f us (%llu calls)\n",
                   8 << sz, ph[sz][0] / 1000.0 / ph[sz][3], ph[sz][1] / 1000.0 / ph[sz][3], ph[sz][2] / 1000.0 / ph[sz][3], ph[sz][3]);
+  }
+  if (e && e->timing) {
+    static const char *names[4] = { "ctu_begin (blocks of pictures in flight + the CTU's dense launch)", "the PU launch call", "frame_begin", "-" };
+    for (int i = 0; i < 3; i++)
+      if (e->t_host[i][1].load())
+        fprintf(stderr, "kvz_cuda_enc: host time in %s: %llu calls, %.1f us each\n", names[i], e->t_host[i][1].load(),
+                e->t_host[i][0].load() / 1000.0 / e->t_host[i][1].load());
   }
   if (e && e->timing)
     for (int sz = 0; sz < 4; sz++)

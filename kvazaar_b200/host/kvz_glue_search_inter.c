@@ -29,6 +29,7 @@
 /* ---- the session: one per process ("Only one encoder may be open at a time", src/kvazaar.h:619) ---- */
 static kvz_cuda_enc *g_enc = NULL;
 static uint64_t g_epoch = 0;                 /* bumped when a session opens: launches made under an older one never match */
+static unsigned long long g_part_ns[6];          /* KVZ_CUDA_STATS: merge list, AMVP, colocated vectors, launch call, record derivations, calls of glue_build_inputs */
 static unsigned long long g_glue_ns[4];          /* KVZ_CUDA_STATS: ns in deriving the real records, waiting for results, launching ahead; calls */
 static unsigned long long g_spec_by_size[4][2];   /* by PU size 8, 16, 32, 64: answered ahead, searched on the spot */
 static unsigned long long g_spec_cnt[4];     /* PU searches answered by a launch made ahead, searched on the spot, PUs launched ahead, PUs launched */
@@ -49,6 +50,10 @@ static void glue_close_session(void)
       if (g_glue_ns[3])
         fprintf(stderr, "kvz_glue: per search_pu_inter: records %.1f us, lookup + wait for the results %.1f us, bi-prediction + launching ahead %.1f us\n",
                 g_glue_ns[0] / 1e3 / g_glue_ns[3], g_glue_ns[1] / 1e3 / g_glue_ns[3], g_glue_ns[2] / 1e3 / g_glue_ns[3]);
+      if (g_part_ns[5])
+        fprintf(stderr, "kvz_glue: per derivation of a PU's records (%llu): merge list %.2f us, AMVP %.2f us, colocated vectors %.2f us; per launch (%llu): %.2f us\n",
+                g_part_ns[5], g_part_ns[0] / 1e3 / g_part_ns[5], g_part_ns[1] / 1e3 / g_part_ns[5], g_part_ns[2] / 1e3 / g_part_ns[5],
+                g_part_ns[4], g_part_ns[4] ? g_part_ns[3] / 1e3 / g_part_ns[4] : 0.0);
       for (int i = 0; i < 4; i++)
         fprintf(stderr, "kvz_glue: PU %2d: %llu answered ahead, %llu searched on the spot\n", 8 << i, g_spec_by_size[i][0], g_spec_by_size[i][1]);
     }
@@ -244,6 +249,9 @@ static void glue_list_of(const encoder_state_t *state, int ref_idx, int8_t *ref_
   kvz_glue_die("reference picture in neither list");
 }
 
+void kvz_glue_inter_get_mv_cands(const encoder_state_t *const state, int32_t x, int32_t y, int32_t width, int32_t height,
+                                 lcu_t *lcu, int n, const int8_t *reflist, const int8_t *lx_idx, int16_t (*mv_cand)[2][2]);
+
 /* ---- the inputs of one device search, and searches launched ahead of time ----
  *
  * The host walks the CU quadtree in z-order and every kvz_search_cu_inter blocks for the device (~50 us).  Most of
@@ -311,8 +319,11 @@ static void glue_build_inputs(encoder_state_t *state, int x, int y, int width, i
                               lcu_t *lcu, inter_search_info_t *info, glue_inputs *in, int8_t *ref_list, int8_t *lx_idx)
 {
   const int n_refs = (int)state->frame->ref->used_size;
+  const int timing = glue_timing();
+  const unsigned long long p0 = timing ? glue_now() : 0;
   memset(in, 0, sizeof(*in));
   info->num_merge_cand = kvz_inter_get_merge_cand(state, x, y, width, height, merge_a1, merge_b1, info->merge_cand, lcu);
+  const unsigned long long p1 = timing ? glue_now() : 0;
   kvz_cuda_me_pu *pu = &in->pu;
   pu->x = (int16_t)x; pu->y = (int16_t)y; pu->w = (uint8_t)width; pu->h = (uint8_t)height;
   pu->num_merge_cand = (uint8_t)info->num_merge_cand;
@@ -328,13 +339,14 @@ static void glue_build_inputs(encoder_state_t *state, int x, int y, int width, i
         pu->merge_cand[i].mv[l][0] = m->mv[l][0]; pu->merge_cand[i].mv[l][1] = m->mv[l][1];
       }
   }
-  cu_info_t probe;                                    /* kvz_inter_get_mv_cand reads cur_cu only for mv_ref[list] */
-  memset(&probe, 0, sizeof(probe));
+  /* the AMVP candidates of every picture from ONE derivation of the PU's neighbours (kvz_glue_inter.c) */
+  int16_t cands[KVZ_CUDA_MAX_REFS][2][2];
+  for (int r = 0; r < n_refs; r++) glue_list_of(state, r, &ref_list[r], &lx_idx[r]);
+  kvz_glue_inter_get_mv_cands(state, x, y, width, height, lcu, n_refs, ref_list, lx_idx, cands);
+  if (n_refs > 0) memcpy(info->mv_cand, cands[n_refs - 1], sizeof(info->mv_cand));      /* as the reference's loop leaves it */
+  const unsigned long long p2 = timing ? glue_now() : 0;
   for (int r = 0; r < n_refs; r++) {
-    glue_list_of(state, r, &ref_list[r], &lx_idx[r]);
-    probe.inter.mv_ref[ref_list[r]] = lx_idx[r];
-    kvz_inter_get_mv_cand(state, x, y, width, height, info->mv_cand, &probe, lcu, ref_list[r]);
-    memcpy(in->jobs[r].mv_cand, info->mv_cand, sizeof(in->jobs[r].mv_cand));
+    memcpy(in->jobs[r].mv_cand, cands[r], sizeof(in->jobs[r].mv_cand));
     /* the colocated CU's vector in that picture (:1188-1206) */
     const int mid_x = state->tile->offset_x + x + (width >> 1), mid_y = state->tile->offset_y + y + (height >> 1);
     const cu_info_t *ref_cu = kvz_cu_array_at_const(state->frame->ref->cu_arrays[r], mid_x, mid_y);
@@ -343,6 +355,13 @@ static void glue_build_inputs(encoder_state_t *state, int x, int y, int width, i
       in->jobs[r].extra_mv[0] = ref_cu->inter.mv[l][0]; in->jobs[r].extra_mv[1] = ref_cu->inter.mv[l][1];
     }
     in->jobs[r].ref_idx = (uint8_t)r;
+  }
+  if (timing) {
+    const unsigned long long p3 = glue_now();
+    __atomic_fetch_add(&g_part_ns[0], p1 - p0, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_part_ns[1], p2 - p1, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_part_ns[2], p3 - p2, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_part_ns[5], 1ull, __ATOMIC_RELAXED);
   }
 }
 
@@ -424,7 +443,9 @@ static int glue_batch_launch(kvz_cuda_enc *enc, uint64_t frame_id, int handle, i
     fprintf(stderr, "\n");
   }
   int ticket = -1;
+  const unsigned long long l0 = glue_timing() ? glue_now() : 0;
   if (!kvz_cuda_enc_search_begin(enc, handle, lambda, b->n, pus, jobs, &ticket)) kvz_glue_die("kvz_cuda_enc_search_begin");
+  if (l0) { __atomic_fetch_add(&g_part_ns[3], glue_now() - l0, __ATOMIC_RELAXED); __atomic_fetch_add(&g_part_ns[4], 1ull, __ATOMIC_RELAXED); }
   if ((ticket & 0xFF) >= GLUE_SPEC_SLOTS) kvz_glue_die("kvz_cuda_enc_search_begin: ticket slot beyond the glue's table");
   glue_spec *row = t_spec[ticket & 0xFF];
   for (int i = 0; i < GLUE_SPEC_PUS; i++) { row[i].valid = 0; t_key[ticket & 0xFF][i] = 0; }
