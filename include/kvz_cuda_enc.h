@@ -89,11 +89,14 @@ KVZ_CUDA_API int kvz_cuda_enc_search_pu(kvz_cuda_enc *enc, int frame_handle, int
  * `jobs` holds KVZ_CUDA_MAX_REFS records per PU (PU i's jobs at jobs[i * KVZ_CUDA_MAX_REFS ..], pus[i].num_jobs used).
  * A host that launched ahead must compare the PU and job records it sent with the real ones when the PU's turn comes
  * and search again when they differ -- the device computes exactly what it is given (kvazaar_b200/host/ does this, so
- * decisions stay the reference's).  Tickets belong to the calling thread; a thread's 32nd-next begin reuses a ticket's
+ * decisions stay the reference's).  Tickets belong to the calling thread; a thread's 64th-next begin reuses a ticket's
  * slot, after which end() on it fails ("expired").  Nothing in the reference corresponds to the split. */
 KVZ_CUDA_API int kvz_cuda_enc_search_begin(kvz_cuda_enc *enc, int frame_handle, int lambda_sqrt_i, int n_pus,
                                            const kvz_cuda_me_pu *pus, const kvz_cuda_me_job *jobs, int *ticket);
 KVZ_CUDA_API int kvz_cuda_enc_search_end(kvz_cuda_enc *enc, int ticket, int pu_index, kvz_cuda_me_result *results);
+/* does not block: 1 when kvz_cuda_enc_search_end would return at once, 0 when the PU is still being searched, -1 when the
+ * ticket has expired (or is not the calling thread's) */
+KVZ_CUDA_API int kvz_cuda_enc_search_ready(kvz_cuda_enc *enc, int ticket, int pu_index);
 
 /* Optional: put the source luma of the picture with presentation number `pts` into device memory ahead of time
  * (a host whose input is already on the device, or a benchmark that wants its inputs resident before the timed

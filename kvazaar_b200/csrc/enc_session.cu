@@ -74,7 +74,7 @@ struct FrameCtx {
 // Per calling thread: kStreams streams and a ring of kSlots launch slots in pinned, mapped host memory.  A slot holds the
 // results of the up to kMePuArgsMax PUs of one launch and one completion word per PU; slot i always uses stream
 // i % kStreams, so a slot is not written by two launches at once.  A ticket = slot | generation << 8.
-constexpr int kStreams = 4, kSlots = 32;
+constexpr int kStreams = 4, kSlots = 64;
 constexpr size_t kSlotResults = (size_t)kMePuArgsMax * KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result);
 constexpr size_t kSlotBytes = kSlotResults + 64;                      // + the completion words on a line of their own
 constexpr size_t kStageBytes = kSlots * kSlotBytes;
@@ -716,6 +716,18 @@ int kvz_cuda_enc_search_end(kvz_cuda_enc *e, int ticket, int pu_index, kvz_cuda_
   memcpy(results, hslot + (size_t)pu_index * KVZ_CUDA_MAX_REFS * sizeof(kvz_cuda_me_result), (size_t)nj * sizeof(kvz_cuda_me_result));
   e->meas[2] += (unsigned long long)nj * sizeof(kvz_cuda_me_result);
   return 1;
+}
+
+int kvz_cuda_enc_search_ready(kvz_cuda_enc *e, int ticket, int pu_index)
+{
+  Worker &w = t_worker;
+  if (!e || ticket < 0 || !w.h) return -1;
+  const uint32_t slot = (uint32_t)ticket & 0xFFu;
+  if (slot >= (uint32_t)kSlots) return -1;
+  const uint32_t gen = w.gen[slot];
+  if (((uint32_t)ticket >> 8) != (gen & 0x7FFFFFu) || pu_index < 0 || pu_index >= w.n_pus[slot]) return -1;
+  const volatile uint32_t *flag = reinterpret_cast<const volatile uint32_t *>(w.h + (size_t)slot * kSlotBytes + kSlotResults) + pu_index;
+  return *flag == gen ? 1 : 0;
 }
 
 int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda_sqrt_i, const kvz_cuda_me_pu *pu,

@@ -268,7 +268,7 @@ typedef struct {
   kvz_cuda_me_job jobs[KVZ_CUDA_MAX_REFS];
 } glue_inputs;
 
-#define GLUE_SPEC_SLOTS 32          /* = the ticket slots of a thread (kvz_cuda_enc.h) */
+#define GLUE_SPEC_SLOTS 64          /* = the ticket slots of a thread (kvz_cuda_enc.h) */
 #define GLUE_SPEC_PUS 8           /* = the PUs one kvz_cuda_enc_search_begin takes */
 typedef struct {
   int valid, ticket, idx, handle, lambda;
@@ -479,6 +479,29 @@ static int glue_next_cu(const videoframe_t *frame, int *x, int *y, int *depth)
   return 0;
 }
 
+/* what search_pu_inter_ref writes into the CU when a picture lowers *inter_cost (:1281-1296), pictures in order;
+ * true when some picture did */
+static bool glue_apply_results(cu_info_t *cu, const kvz_cuda_me_result *res, int n_refs, const int8_t *ref_list,
+                               const int8_t *lx_idx, double *inter_cost, uint32_t *inter_bitcost)
+{
+  bool any = false;
+  for (int r = 0; r < n_refs; r++) {
+    if (!res[r].took) continue;
+    const int l = ref_list[r];
+    cu->inter.mv_dir = l + 1;
+    cu->merged = res[r].merged;
+    cu->merge_idx = res[r].merge_idx;
+    cu->inter.mv_ref[l] = lx_idx[r];
+    cu->inter.mv[l][0] = res[r].mv[0];
+    cu->inter.mv[l][1] = res[r].mv[1];
+    CU_SET_MV_CAND(cu, l, res[r].mv_cand_idx);
+    *inter_cost = res[r].cost;
+    *inter_bitcost = res[r].bitcost + cu->inter.mv_dir - 1 + lx_idx[r];
+    any = true;
+  }
+  return any;
+}
+
 /* After the search of CU (x, y, depth), under the hypothesis that the CU stays as `cur_cu` says now: launches the next
  * CU of the walk with its top-left chain, and -- when the CU can be split -- its children 1..3 as they will be searched
  * if the children before them come out like the CU itself (smooth motion; when they do not, the child is launched
@@ -574,20 +597,7 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
   }
   if (timing) t2 = glue_now();
 
-  /* what search_pu_inter_ref writes when a picture lowers *inter_cost (:1281-1296), pictures in order */
-  for (int r = 0; r < n_refs; r++) {
-    if (!res[r].took) continue;
-    const int l = ref_list[r];
-    cur_cu->inter.mv_dir = l + 1;
-    cur_cu->merged = res[r].merged;
-    cur_cu->merge_idx = res[r].merge_idx;
-    cur_cu->inter.mv_ref[l] = lx_idx[r];
-    cur_cu->inter.mv[l][0] = res[r].mv[0];
-    cur_cu->inter.mv[l][1] = res[r].mv[1];
-    CU_SET_MV_CAND(cur_cu, l, res[r].mv_cand_idx);
-    *inter_cost = res[r].cost;
-    *inter_bitcost = res[r].bitcost + cur_cu->inter.mv_dir - 1 + lx_idx[r];
-  }
+  glue_apply_results(cur_cu, res, n_refs, ref_list, lx_idx, inter_cost, inter_bitcost);
 
   /* bi-prediction from pairs of merge candidates stays the reference's own function (:1304-1434): it predicts with
    * the ipol strategies and costs with kvz_satd_any_size; info.mv_cand holds the last picture's candidates as there */

@@ -52,6 +52,8 @@ def _lib():
         L.kvz_cuda_enc_search_begin.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
         L.kvz_cuda_enc_search_end.restype = C.c_int
         L.kvz_cuda_enc_search_end.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.kvz_cuda_enc_search_ready.restype = C.c_int
+        L.kvz_cuda_enc_search_ready.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L._enc_bound = True
     return L
 
@@ -120,6 +122,9 @@ class Session:
                                                 C.byref(ticket)):
             raise RuntimeError("kvz_cuda_enc_search_begin: " + _err())
         return ticket.value
+
+    def search_ready(self, ticket, pu_index):
+        return self.L.kvz_cuda_enc_search_ready(self.h, ticket, pu_index)
 
     def search_end(self, ticket, pu_index, n_jobs):
         res = np.zeros(n_jobs, ME_RESULT_DT)

@@ -16,7 +16,7 @@
 
 struct kvz_cuda_enc { kvz_cuda_enc_cfg cfg; uint64_t frames[64]; int n_frames; unsigned long long stats[8]; };
 
-#define SLOTS 32
+#define SLOTS 64
 #define PUS 8
 static __thread struct {
   uint32_t gen[SLOTS], next;
@@ -93,6 +93,14 @@ int kvz_cuda_enc_search_end(kvz_cuda_enc *e, int ticket, int pu_index, kvz_cuda_
   if (pu_index < 0 || pu_index >= t.n_pus[slot]) return fail("stub: bad pu_index");
   memcpy(results, t.res[slot][pu_index], (size_t)t.n_jobs[slot][pu_index] * sizeof(kvz_cuda_me_result));
   return 1;
+}
+
+int kvz_cuda_enc_search_ready(kvz_cuda_enc *e, int ticket, int pu_index)
+{
+  (void)e;
+  const uint32_t slot = (uint32_t)ticket & 0xFF;
+  if (ticket < 0 || slot >= SLOTS || ((uint32_t)ticket >> 8) != (t.gen[slot] & 0x7FFFFFu) || pu_index < 0 || pu_index >= t.n_pus[slot]) return -1;
+  return 1;                                   /* the stand-in "searches" inside begin */
 }
 
 int kvz_cuda_enc_search_pu(kvz_cuda_enc *e, int handle, int lambda, const kvz_cuda_me_pu *pu, const kvz_cuda_me_job *jobs,

@@ -67,11 +67,14 @@ def test_tickets_expire_and_bad_launches_are_refused():
     try:
         first = s.search_begin(handle, lam, pus[:1], [jobs[:NREFS]])
         got0 = s.search_end(first, 0, NREFS)
+        assert s.search_ready(first, 0) == 1 and s.search_ready(first, 1) == -1
         me_oracle.assert_results_equal(got0, want[:NREFS])
-        for i in range(32):                                        # the thread's 32 slots go round once
-            s.search_end(s.search_begin(handle, lam, pus[i:i + 1], [jobs[i * NREFS:(i + 1) * NREFS]]), 0, NREFS)
+        for i in range(64):                                        # the thread's 64 slots go round once
+            k = i % len(pus)
+            s.search_end(s.search_begin(handle, lam, pus[k:k + 1], [jobs[k * NREFS:(k + 1) * NREFS]]), 0, NREFS)
         with pytest.raises(RuntimeError, match="expired"):
             s.search_end(first, 0, NREFS)
+        assert s.search_ready(first, 0) == -1
         a = next(i for i in range(len(pus)) if (int(pus[i]["x"]) >> 6, int(pus[i]["y"]) >> 6) != (int(pus[0]["x"]) >> 6, int(pus[0]["y"]) >> 6))
         with pytest.raises(RuntimeError, match="one CTU"):
             s.search_begin(handle, lam, pus[[0, a]], [jobs[:NREFS], jobs[a * NREFS:(a + 1) * NREFS]])
