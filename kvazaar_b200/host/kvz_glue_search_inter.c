@@ -31,6 +31,7 @@ static kvz_cuda_enc *g_enc = NULL;
 static uint64_t g_epoch = 0;                 /* bumped when a session opens: launches made under an older one never match */
 static unsigned long long g_part_ns[6];          /* KVZ_CUDA_STATS: merge list, AMVP, colocated vectors, launch call, record derivations, calls of glue_build_inputs */
 static unsigned long long g_glue_ns[4];          /* KVZ_CUDA_STATS: ns in deriving the real records, waiting for results, launching ahead; calls */
+static unsigned long long g_origin8[3][2];         /* KVZ_CUDA_STATS, 8x8 PUs answered ahead by origin of the launch: count, ns waited */
 static unsigned long long g_spec_by_size[4][2];   /* by PU size 8, 16, 32, 64: answered ahead, searched on the spot */
 static unsigned long long g_spec_cnt[4];     /* PU searches answered by a launch made ahead, searched on the spot, PUs launched ahead, PUs launched */
 static const encoder_control_t *g_enc_ctrl = NULL;
@@ -54,6 +55,13 @@ static void glue_close_session(void)
         fprintf(stderr, "kvz_glue: per derivation of a PU's records (%llu): merge list %.2f us, AMVP %.2f us, colocated vectors %.2f us; per launch (%llu): %.2f us\n",
                 g_part_ns[5], g_part_ns[0] / 1e3 / g_part_ns[5], g_part_ns[1] / 1e3 / g_part_ns[5], g_part_ns[2] / 1e3 / g_part_ns[5],
                 g_part_ns[4], g_part_ns[4] ? g_part_ns[3] / 1e3 / g_part_ns[4] : 0.0);
+      {
+        static const char *on[3] = { "rode along with a search on the spot", "next CU of the walk and its chain", "child under the inherit hypothesis" };
+        for (int i = 0; i < 3; i++)
+          if (g_origin8[i][0])
+            fprintf(stderr, "kvz_glue: 8x8 searches answered by a launch that %s: %llu, waited %.1f us each\n", on[i], g_origin8[i][0],
+                    g_origin8[i][1] / 1e3 / g_origin8[i][0]);
+      }
       for (int i = 0; i < 4; i++)
         fprintf(stderr, "kvz_glue: PU %2d: %llu answered ahead, %llu searched on the spot\n", 8 << i, g_spec_by_size[i][0], g_spec_by_size[i][1]);
     }
@@ -272,6 +280,7 @@ typedef struct {
 #define GLUE_SPEC_PUS 8           /* = the PUs one kvz_cuda_enc_search_begin takes */
 typedef struct {
   int valid, ticket, idx, handle, lambda;
+  int origin;                       /* statistics: 0 rode along with a search made on the spot, 1 next CU of the walk / its chain, 2 child under the inherit hypothesis */
   uint64_t epoch, frame_id;
   glue_inputs in;
 } glue_spec;
@@ -401,7 +410,8 @@ static bool glue_cu_is_searched(const encoder_state_t *state, int x, int y, int 
 /* the PUs of one launch being put together */
 typedef struct {
   glue_inputs sent[GLUE_SPEC_PUS];
-  int n, n_needed_now;
+  uint8_t origin[GLUE_SPEC_PUS];
+  int n, n_needed_now, cur_origin;
 } glue_batch;
 
 /* adds CU (x, y, depth) as search_cu would search it, with the records `lcu` gives it -- unless search_cu would not
@@ -416,6 +426,7 @@ static void glue_batch_add_cu(encoder_state_t *state, glue_batch *b, uint64_t fr
   glue_inputs *in = &b->sent[b->n];
   glue_build_inputs(state, x, y, w, w, true, true, lcu, &info, in, ref_list, lx_idx);
   if (in->pu.num_jobs == 0 || glue_spec_find(frame_id, handle, lambda, in)) return;
+  b->origin[b->n] = (uint8_t)b->cur_origin;
   b->n++;
 }
 
@@ -453,7 +464,7 @@ static int glue_batch_launch(kvz_cuda_enc *enc, uint64_t frame_id, int handle, i
     glue_spec *e = &row[i];
     t_key[ticket & 0xFF][i] = glue_key(&b->sent[i]);
     e->valid = 1; e->ticket = ticket; e->idx = i; e->handle = handle; e->lambda = lambda;
-    e->epoch = g_epoch; e->frame_id = frame_id; e->in = b->sent[i];
+    e->epoch = g_epoch; e->frame_id = frame_id; e->in = b->sent[i]; e->origin = b->origin[i];
   }
   __atomic_fetch_add(&g_spec_cnt[3], (unsigned long long)b->n, __ATOMIC_RELAXED);
   __atomic_fetch_add(&g_spec_cnt[2], (unsigned long long)(b->n - b->n_needed_now), __ATOMIC_RELAXED);
@@ -527,7 +538,9 @@ static void glue_launch_next(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t
     for (int xx = xl; xx < xl + w; xx += 4) *LCU_GET_CU_AT_PX(t_hyp, xx, yy) = filled;
   glue_batch b;
   b.n = b.n_needed_now = 0;
+  b.cur_origin = 1;
   if (has_next) glue_batch_add_chain(state, &b, frame_id, handle, lambda, nx, ny, nd, t_hyp);
+  b.cur_origin = 2;
   if (has_children && found_inter) {
     const int h = w >> 1;
     glue_batch_add_cu(state, &b, frame_id, handle, lambda, x + h, y, depth + 1, t_hyp);
@@ -578,8 +591,13 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
     bool have = false;
     glue_spec *e = glue_speculate() ? glue_spec_find(frame_id, handle, lambda, &in) : NULL;
     if (e) {                                             /* launched ahead with exactly these records */
+      const unsigned long long w0 = timing ? glue_now() : 0;
       have = kvz_cuda_enc_search_end(enc, e->ticket, e->idx, res) != 0;
       e->valid = 0;
+      if (timing && have && width == 8) {
+        __atomic_fetch_add(&g_origin8[e->origin][0], 1ull, __ATOMIC_RELAXED);
+        __atomic_fetch_add(&g_origin8[e->origin][1], glue_now() - w0, __ATOMIC_RELAXED);
+      }
     }
     __atomic_fetch_add(&g_spec_cnt[have ? 0 : 1], 1ull, __ATOMIC_RELAXED);
     if (kvz_glue_trace() && x < 64 && y < 64 && state->frame->num == 1) fprintf(stderr, "T search %d %d %d %s\n", x, y, width, have ? "hit" : "miss");
@@ -587,6 +605,7 @@ static void glue_search_pu_inter(encoder_state_t *const state, int x_cu, int y_c
     if (!have) {                                         /* search it now; its top-left children ride along */
       glue_batch b;
       b.n = b.n_needed_now = 1;
+      b.cur_origin = 0; b.origin[0] = 0;
       b.sent[0] = in;
       if (square && glue_speculate()) glue_batch_add_chain(state, &b, frame_id, handle, lambda, x, y, depth + 1, lcu);
       const int ticket = glue_batch_launch(enc, frame_id, handle, lambda, &b);
