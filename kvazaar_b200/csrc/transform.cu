@@ -407,12 +407,17 @@ __global__ void __launch_bounds__(kThreads)
 quantize_residual_kernel(kvz_cuda_quant_cfg c, const PIX *__restrict__ ref, const PIX *__restrict__ pred,
                          PIX *__restrict__ rec, int16_t *__restrict__ coeff_out,
                          const kvz_cuda_residual_job *__restrict__ jobs, int n_jobs, uint8_t *__restrict__ has_coeffs,
-                         int16_t *__restrict__ work, int rdoq_skip)
+                         int16_t *__restrict__ work, int rdoq_skip, int skip_all4)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   int tt_small = -1, scan_small = -1, tt_big = -1, scan_big = -1;     // what the warp's / the CTA's tables hold
   for (int j0 = blockIdx.x * kWarps; j0 < n_jobs; j0 += gridDim.x * kWarps) {
     const int nj = min(kWarps, n_jobs - j0);
+    if (skip_all4) {                            // groups of 32 jobs that are all 4x4 were done by quantize_residual4_kernel
+      const int g0 = j0 & ~31, li = g0 + (threadIdx.x & 31);
+      const int is4 = li >= n_jobs || jobs[li].width == 4;
+      if (__syncthreads_and(is4)) continue;
+    }
     bool small = true;
     for (int q = 0; q < nj; q++) small &= jobs[j0 + q].width <= kSmallN;
     __syncthreads();                            // the two paths overlay the same shared memory
@@ -431,6 +436,210 @@ quantize_residual_kernel(kvz_cuda_quant_cfg c, const PIX *__restrict__ ref, cons
         residual_job<STAGE, kThreads>(sm, c, ref, pred, rec, coeff_out, jobs[j0 + q], has_coeffs + j0 + q, work, rdoq_skip,
                                       threadIdx.x, tt_big, scan_big);
     }
+  }
+}
+
+// raster index (y * 4 + x) of the k-th coefficient of a 4x4 group in the three scans (square_scan of transform.cuh)
+__host__ __device__ constexpr int cg_raster(int scan, int k)     // raster index (y * 4 + x) of the k-th coefficient of a group
+{
+  constexpr int diag[16] = { 0, 4, 1, 8, 5, 2, 12, 9, 6, 3, 13, 10, 7, 14, 11, 15 };
+  return scan == 0 ? diag[k] : scan == 1 ? k : (k & 3) * 4 + (k >> 2);
+}
+
+// ---- kvz_quantize_residual (scalar quantiser) for 4x4 blocks: one block per THREAD ----
+// A frame has more 4x4 transform blocks than anything else, and a warp per 16-sample block spends its time on barriers
+// and idle lanes.  A warp takes 32 consecutive jobs; when all of them are 4x4 every thread does one: residual, DCT /
+// DST / transform skip, quantiser with sign hiding over the block's one coefficient group, dequantiser, inverse and
+// reconstruction, all in registers -- the same arithmetic as residual_job (transform.c:151-181, quant-generic.c:180-273).
+// Groups that hold another size are left to quantize_residual_kernel (skip_all4).
+template <int SCAN>
+__device__ __forceinline__ bool quant4_regs(const int (&a)[16], int (&q)[16], const kvz_cuda_quant_cfg &c, int type)
+{
+  const int qp_s = scaled_qp(type, c.qp, (c.bitdepth - 8) * 6);
+  const long long qc = c_quant_scale[qp_s % 6];
+  const int q_bits = 14 + qp_s / 6 + (15 - c.bitdepth - 2);
+  const int add = (c.slice_is_intra ? 171 : 85) << (q_bits - 9);
+  int lv[16], dl[16];
+  uint32_t neg = 0, acc = 0;
+  bool any = false;
+#pragma unroll
+  for (int n = 0; n < 16; n++) {
+    const int cf = a[cg_raster(SCAN, n)];
+    const long long prod = (long long)abs(cf) * qc;
+    int level = (int)((prod + add) >> q_bits);
+    acc += (uint32_t)level;
+    dl[n] = (int)((prod - ((long long)level << q_bits)) >> (q_bits - 8));
+    if (cf < 0) { level = -level; neg |= 1u << n; }
+    lv[n] = clampi(level, -32768, 32767);
+    any |= lv[n] != 0;
+  }
+  if (c.signhide && acc >= 2) {
+    int first = 16, last = -1, qfirst = 0;
+#pragma unroll
+    for (int n = 0; n < 16; n++) if (lv[n] != 0) last = n;
+#pragma unroll
+    for (int n = 15; n >= 0; n--) if (lv[n] != 0) { first = n; qfirst = lv[n]; }
+    if (last - first >= 4) {
+      int sum = 0;
+#pragma unroll
+      for (int n = 0; n < 16; n++) if (n >= first && n <= last) sum += lv[n];
+      const int signbit = qfirst > 0 ? 0 : 1;
+      if (signbit != (sum & 1)) {
+        int best = 0x7FFFFFFF, bestn = -1, change = 0;          // the block's only group is its last one: the walk starts at `last`
+#pragma unroll
+        for (int n = 15; n >= 0; n--) {
+          if (n > last) continue;
+          int cost = 0x7FFFFFFF, cur_change = 0;
+          if (lv[n] != 0) {
+            if (dl[n] > 0) { cost = -dl[n]; cur_change = 1; }
+            else if (n == first && abs(lv[n]) == 1) { cost = 0x7FFFFFFF; }
+            else { cost = dl[n]; cur_change = -1; }
+          } else if (n < first && (int)((neg >> n) & 1u) != signbit) {
+            cost = 0x7FFFFFFF;
+          } else {
+            cost = -dl[n]; cur_change = 1;
+          }
+          if (cost < best) { best = cost; change = cur_change; bestn = n; }
+        }
+#pragma unroll
+        for (int n = 0; n < 16; n++)
+          if (n == bestn) {
+            int ch = change;
+            if (lv[n] == 32767 || lv[n] == -32768) ch = -1;
+            lv[n] = (int)(int16_t)(((neg >> n) & 1u) ? lv[n] - ch : lv[n] + ch);
+          }
+      }
+    }
+  }
+  any = false;
+#pragma unroll
+  for (int n = 0; n < 16; n++) { q[cg_raster(SCAN, n)] = lv[n]; any |= lv[n] != 0; }
+  return any;
+}
+
+template <typename PIX>
+__global__ void __launch_bounds__(kThreads)
+quantize_residual4_kernel(kvz_cuda_quant_cfg c, const PIX *__restrict__ ref, const PIX *__restrict__ pred,
+                          PIX *__restrict__ rec, int16_t *__restrict__ coeff_out,
+                          const kvz_cuda_residual_job *__restrict__ jobs, int n_jobs, uint8_t *__restrict__ has_coeffs)
+{
+  __shared__ int16_t mats[2][16];                            // [0] the 4-point DCT, [1] the 4x4 DST
+  if (threadIdx.x < 32) {
+    const int k = (threadIdx.x & 15) >> 2, n = threadIdx.x & 3;
+    int v;
+    if (threadIdx.x >= 16) v = c_dst4[k][n];
+    else {
+      int q = (8 * k * (2 * n + 1)) & 127;
+      if (q > 64) q = 128 - q;
+      v = q <= 32 ? c_hevc_cos_q[q] : -c_hevc_cos_q[64 - q];
+    }
+    mats[threadIdx.x >> 4][threadIdx.x & 15] = (int16_t)v;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warps = gridDim.x * (kThreads / 32);
+  for (int g = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5); g * 32 < n_jobs; g += warps) {
+    const int ji = g * 32 + lane;
+    const bool on = ji < n_jobs;
+    kvz_cuda_residual_job jb;
+    if (on) jb = jobs[ji]; else jb.width = 4;
+    if (!__all_sync(0xffffffffu, jb.width == 4)) continue;
+    if (!on) continue;
+    c.qp = jb.qp;
+    c.cu_is_intra = jb.cu_is_intra;
+    const bool luma = jb.color == 0;
+    const int16_t *m = mats[luma && jb.cu_is_intra ? 1 : 0];          // strategies-dct.c:59-113
+    const PIX *rp = ref + jb.ref_offset, *pp = pred + jb.pred_offset;
+    int a[16], p[16];
+#pragma unroll
+    for (int y = 0; y < 4; y++)
+#pragma unroll
+      for (int x = 0; x < 4; x++) {
+        p[4 * y + x] = (int)pp[(size_t)y * jb.in_stride + x];
+        a[4 * y + x] = (int)(int16_t)((int)rp[(size_t)y * jb.in_stride + x] - p[4 * y + x]);
+      }
+    const int ts_shift = 15 - c.bitdepth - 2;
+    int b[16];
+    if (jb.use_trskip) {                                               // transform.c:151-161
+#pragma unroll
+      for (int i = 0; i < 16; i++) a[i] = (int)(int16_t)(a[i] << ts_shift);
+    } else {                                                           // dct-generic.c:258, 571-572
+      const int s1 = 1 + (c.bitdepth - 8), r1 = 1 << (s1 - 1);
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          int s = 0;
+#pragma unroll
+          for (int n = 0; n < 4; n++) s += (int)m[k * 4 + n] * a[j * 4 + n];
+          b[k * 4 + j] = (int)(int16_t)((s + r1) >> s1);
+        }
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          int s = 0;
+#pragma unroll
+          for (int n = 0; n < 4; n++) s += (int)m[k * 4 + n] * b[j * 4 + n];
+          a[k * 4 + j] = (int)(int16_t)((s + 128) >> 8);
+        }
+    }
+    int q[16];
+    const int qtype = luma ? 0 : 2;
+    bool any;
+    if (jb.scan_idx == 0) any = quant4_regs<0>(a, q, c, qtype);
+    else if (jb.scan_idx == 1) any = quant4_regs<1>(a, q, c, qtype);
+    else any = quant4_regs<2>(a, q, c, qtype);
+    int16_t *co = coeff_out + jb.coeff_offset;
+#pragma unroll
+    for (int i = 0; i < 16; i++) co[i] = (int16_t)q[i];
+    PIX *op = rec + jb.rec_offset;
+    if (any) {
+      const int dtype = luma ? 0 : (jb.color == 1 ? 2 : 3);           // kvz_dequant (quant-generic.c:279-321, flat list)
+      const int qp_s = scaled_qp(dtype, c.qp, (c.bitdepth - 8) * 6);
+      const int shift = 20 - 14 - (15 - c.bitdepth - 2);
+      const int scale = c_inv_quant_scale[qp_s % 6] << (qp_s / 6);
+      const int dadd = 1 << (shift - 1);
+#pragma unroll
+      for (int i = 0; i < 16; i++) a[i] = clampi((q[i] * scale + dadd) >> shift, -32768, 32767);
+      if (jb.use_trskip) {                                             // transform.c:169-181
+        const int off = 1 << (ts_shift - 1);
+#pragma unroll
+        for (int i = 0; i < 16; i++) a[i] = (int)(int16_t)((a[i] + off) >> ts_shift);
+      } else {                                                         // dct-generic.c:582-583
+        const int s2 = 12 - (c.bitdepth - 8);
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+          for (int n = 0; n < 4; n++) {
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) s += (int)m[k * 4 + n] * a[k * 4 + j];
+            b[j * 4 + n] = clampi((s + 64) >> 7, -32768, 32767);
+          }
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+          for (int n = 0; n < 4; n++) {
+            int s = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) s += (int)m[k * 4 + n] * b[k * 4 + j];
+            a[j * 4 + n] = clampi((s + (1 << (s2 - 1))) >> s2, -32768, 32767);
+          }
+      }
+      const int pix_max = (1 << c.bitdepth) - 1;
+#pragma unroll
+      for (int y = 0; y < 4; y++)
+#pragma unroll
+        for (int x = 0; x < 4; x++)
+          op[(size_t)y * jb.out_stride + x] = (PIX)clampi((int)(int16_t)(a[4 * y + x] + p[4 * y + x]), 0, pix_max);
+    } else {
+#pragma unroll
+      for (int y = 0; y < 4; y++)
+#pragma unroll
+        for (int x = 0; x < 4; x++) op[(size_t)y * jb.out_stride + x] = (PIX)p[4 * y + x];
+    }
+    has_coeffs[ji] = (uint8_t)(any ? 1 : 0);
   }
 }
 
@@ -687,11 +896,6 @@ transform_rows_kernel(int bitdepth, const int16_t *__restrict__ in, int16_t *__r
 // thread takes a group -- its 4x4 corner of the block as four 8-byte loads, visited in the scan's order through a
 // compile-time permutation, everything in registers -- and the (N/4)^2 lanes of a block exchange the two block-wide
 // facts with shuffles.  Same arithmetic as quant_block; the backward walk with its strict '<' is kept as it is.
-__host__ __device__ constexpr int cg_raster(int scan, int k)     // raster index (y * 4 + x) of the k-th coefficient of a group
-{
-  constexpr int diag[16] = { 0, 4, 1, 8, 5, 2, 12, 9, 6, 3, 13, 10, 7, 14, 11, 15 };
-  return scan == 0 ? diag[k] : scan == 1 ? k : (k & 3) * 4 + (k >> 2);
-}
 
 template <int N, int SCAN>
 __global__ void __launch_bounds__(kThreads)
@@ -905,12 +1109,21 @@ int launch_quantize_residual(const kvz_cuda_quant_cfg &c, const void *ref, const
 {
   if (n_jobs <= 0) return 1;
   if (!opt_in_smem(quantize_residual_kernel<0, uint8_t>) || !opt_in_smem(quantize_residual_kernel<0, uint16_t>)) return 0;
-  if (c.bitdepth > 8)
+  // groups of 32 jobs that are all 4x4: a block per thread; everything else: the group kernel, which skips those groups
+  int grid4 = (n_jobs + kThreads - 1) / kThreads;
+  if (grid4 > sm_count() * 16) grid4 = sm_count() * 16;
+  if (c.bitdepth > 8) {
+    quantize_residual4_kernel<uint16_t><<<grid4, kThreads, 0, stream>>>(c, (const uint16_t *)ref, (const uint16_t *)pred,
+                                                                       (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs);
     quantize_residual_kernel<0, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
-  else
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0, 1);
+  } else {
+    quantize_residual4_kernel<uint8_t><<<grid4, kThreads, 0, stream>>>(c, (const uint8_t *)ref, (const uint8_t *)pred,
+                                                                      (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs);
     quantize_residual_kernel<0, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0);
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, nullptr, 0, 1);
+  }
+  count_launch();
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;
@@ -932,19 +1145,19 @@ int launch_quantize_residual_rdoq(const kvz_cuda_quant_cfg &c, const void *ref, 
   const bool wide = c.bitdepth > 8;
   if (wide)
     quantize_residual_kernel<1, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip, 0);
   else
     quantize_residual_kernel<1, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   if (!launch_rdoq_batch(c, d_ctx, work, coeff, rdoq_jobs, n_jobs, max_width, rdoq_skip, stream)) return 0;
   if (wide)
     quantize_residual_kernel<2, uint16_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+        c, (const uint16_t *)ref, (const uint16_t *)pred, (uint16_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip, 0);
   else
     quantize_residual_kernel<2, uint8_t><<<residual_grid(n_jobs), kThreads, sizeof(BlockSmem), stream>>>(
-        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip);
+        c, (const uint8_t *)ref, (const uint8_t *)pred, (uint8_t *)rec, coeff, jobs, n_jobs, has_coeffs, work, rdoq_skip, 0);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
   return 1;

@@ -97,8 +97,10 @@ def test_fused_quantize_residual(bitdepth):
     for intra_slice in (0, 1):
         for signhide in (0, 1):
             rows, coff = [], 0
-            for _ in range(120):
-                n = int(rs.choice([4, 8, 16, 32]))
+            # 120 jobs of mixed sizes, then 70 that are all 4x4: groups of 32 jobs that are all 4x4 take the block-per-thread
+            # kernel (one full group, one ragged one), the mixed groups the group kernel
+            for k in range(190):
+                n = int(rs.choice([4, 8, 16, 32])) if k < 120 else 4
                 x, y = int(rs.integers(0, (W - n) // 4 + 1)) * 4, int(rs.integers(0, (H - n) // 4 + 1)) * 4
                 color = int(rs.integers(0, 3)) if n < 32 else 0
                 rows.append((y * W + x, y * W + x, y * W + x, coff, W, W, n, color,
