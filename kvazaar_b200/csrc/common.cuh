@@ -3,6 +3,7 @@
 // B200 (sm_100a) only.  No CPU fallback anywhere: every entry point returns 0
 // and records an error string if CUDA is unavailable or a launch fails.
 #pragma once
+#include <mutex>
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -19,6 +20,20 @@ inline int fail(const char *what, cudaError_t e, const char *file, int line)
 {
   snprintf(g_last_error, sizeof(g_last_error), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
   return 0;
+}
+
+// Raises a kernel's dynamic shared-memory limit to `bytes` once per size, from any host thread: the sizes two threads
+// ask for may differ (frames with boxes of different heights are in flight together), so the comparison and the
+// attribute call are one critical section and the recorded size only grows.
+template <typename K>
+inline cudaError_t opt_in_dynamic_smem(K kernel, size_t bytes, size_t &recorded, std::mutex &lock)
+{
+  if (bytes <= __atomic_load_n(&recorded, __ATOMIC_ACQUIRE)) return cudaSuccess;
+  std::lock_guard<std::mutex> guard(lock);
+  if (bytes <= recorded) return cudaSuccess;
+  const cudaError_t st = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (st == cudaSuccess) __atomic_store_n(&recorded, bytes, __ATOMIC_RELEASE);
+  return st;
 }
 
 inline int fail_msg(const char *what)

@@ -763,10 +763,8 @@ static int launch_multi_tma(const ImeSadMulti &m, cudaStream_t stream)
   }
   if (smem > 113 * 1024) return fail_msg("ime_sad (TMA): too many displacement rows for the shared-memory tile");
   static size_t opted = 0;
-  if (smem > opted) {
-    KVZ_CUDA_TRY(cudaFuncSetAttribute(ime_sad_multi_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    opted = smem;
-  }
+  static std::mutex opt_lock;
+  KVZ_CUDA_TRY(opt_in_dynamic_smem(ime_sad_multi_tma_kernel, smem, opted, opt_lock));
   ime_sad_multi_tma_kernel<<<m.full_end[m.n - 1], kWsThreads, smem, stream>>>(t);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();
@@ -801,10 +799,8 @@ int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int 
     use_tma = use_tma && !(reinterpret_cast<uintptr_t>(m.p[r].ref) & 15) && !(m.p[r].ref_pitch & 15) && Geo(m.p[r].n_dy).rows <= 256;
   if (use_tma) return launch_multi_tma(m, stream);
   static size_t opted = 0;                        // opt in once per size (any host thread may launch this)
-  if (smem > opted) {
-    KVZ_CUDA_TRY(cudaFuncSetAttribute(ime_sad_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    opted = smem;
-  }
+  static std::mutex opt_lock;
+  KVZ_CUDA_TRY(opt_in_dynamic_smem(ime_sad_multi_kernel, smem, opted, opt_lock));
   ime_sad_multi_kernel<<<total, kWsThreads, smem, stream>>>(m);
   count_launch();
   KVZ_CUDA_LAUNCH_CHECK();

@@ -1969,12 +1969,10 @@ int launch_me_search_pu(const MeFrame &f, const kvz_cuda_me_pu *pus, const kvz_c
   if ((kPuThreads / 128) * sizeof(RefineSmem<128, 32>) > smem) smem = (kPuThreads / 128) * sizeof(RefineSmem<128, 32>);
   if (coop_smem_bytes(f.range) > smem) smem = coop_smem_bytes(f.range);
   if (box_dx > 0 && (kPuThreads / 32) * box_scan_warp_bytes(box_dx, box_dy) > smem) smem = (kPuThreads / 32) * box_scan_warp_bytes(box_dx, box_dy);
-  static size_t opted = 0;                        // opt in once per size (one device per process)
-  if (smem > opted) {
-    KVZ_CUDA_TRY(cudaFuncSetAttribute(me_pu_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    KVZ_CUDA_TRY(cudaFuncSetAttribute(me_pu_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    opted = smem;
-  }
+  static size_t opted_args = 0, opted_batch = 0;  // opt in once per size (one device per process; any host thread)
+  static std::mutex opt_lock;
+  KVZ_CUDA_TRY(opt_in_dynamic_smem(me_pu_kernel<true>, smem, opted_args, opt_lock));
+  KVZ_CUDA_TRY(opt_in_dynamic_smem(me_pu_kernel<false>, smem, opted_batch, opt_lock));
   static const int timing = getenv("KVZ_CUDA_STATS") != nullptr;
   static bool timing_set = false;
   if (timing && !timing_set) { KVZ_CUDA_TRY(cudaMemcpyToSymbol(g_box_scan_timing, &timing, sizeof(int))); timing_set = true; }
