@@ -96,6 +96,19 @@ struct Worker {
   uint8_t n_pus[kSlots] = {};
   uint8_t n_jobs[kSlots][kMePuArgsMax] = {};
   uint8_t size_class[kSlots][kMePuArgsMax] = {};
+  // a host creates its worker threads per encoder: what a thread holds goes when the thread ends (launches made ahead
+  // and never collected may still be running: the streams are drained first).  After the runtime has shut down the
+  // calls fail and are ignored.
+  ~Worker()
+  {
+    if (device < 0) return;
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return; }
+    for (auto &s : streams)
+      if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); s = nullptr; }
+    if (ctu_ready) cudaEventDestroy(ctu_ready);
+    if (h) cudaFreeHost(h);
+    cudaGetLastError();
+  }
 };
 thread_local Worker t_worker;
 
