@@ -291,7 +291,7 @@ static uint64_t glue_key(const glue_inputs *in)
 {
   return 1ull << 63 | (uint64_t)(uint16_t)in->pu.x << 32 | (uint64_t)(uint16_t)in->pu.y << 16 | (uint64_t)in->pu.w << 8 | in->pu.h;
 }
-static __thread lcu_t *t_hyp = NULL;
+static __thread lcu_t t_hyp_storage;                          /* the hypothetical CU array (only ->cu is used); freed with its thread */
 
 /* KVZ_GLUE_TRACE=1: the searches and launches of the first CTU of frame 1 on stderr (debugging the launching ahead) */
 static int kvz_glue_trace(void)
@@ -526,10 +526,7 @@ static void glue_launch_next(encoder_state_t *state, kvz_cuda_enc *enc, uint64_t
   if (children < 0) children = !(getenv("KVZ_CUDA_SPEC_CHILDREN") && atoi(getenv("KVZ_CUDA_SPEC_CHILDREN")) == 0);
   const bool has_children = children && depth < MAX_DEPTH && depth < state->encoder_control->cfg.pu_depth_inter.max;
   if (!has_next && !has_children) return;
-  if (!t_hyp) {
-    t_hyp = malloc(sizeof(lcu_t));
-    if (!t_hyp) kvz_glue_die("out of memory");
-  }
+  lcu_t *const t_hyp = &t_hyp_storage;
   memcpy(t_hyp->cu, lcu->cu, sizeof(lcu->cu));
   cu_info_t filled = *cur_cu;
   filled.type = found_inter ? CU_INTER : CU_INTRA;
