@@ -57,3 +57,34 @@ def test_launching_ahead_does_not_change_the_bitstream(name, stub, tmp_path):
     if "--owf 0" in CASES[name][4]:                                     # with --owf 0 the bitstream does not depend on --threads
         one_thread, _ = _run(stub, tmp, name, 1)
         assert one_thread == plain
+
+
+def test_kvz_api_driver_gives_the_cli_bitstream(stub, tmp_path):
+    """kvazaar_b200/encoder.py (kvz_api through ctypes, the library dlopen'ed: what bench.py drives) and the reference's CLI
+    linked against the same library produce the same bitstream -- with the stand-in device, on the CPU."""
+    import sys
+    name = "medium_full32"
+    w, h, n, seed, opts = CASES[name]
+    cli, _ = _run(stub, str(tmp_path), name, 4)
+    code = f"""
+import sys, hashlib
+sys.path.insert(0, {os.path.join(ROOT, 'tools')!r}); sys.path.insert(0, {ROOT!r})
+import make_clip
+from kvazaar_b200 import encoder
+frames = list(make_clip.clip_planes({seed}, {w}, {h}, {n}))
+md5, out = hashlib.md5(), 0
+with encoder.Encoder(encoder.CUDA_LIB, {w}, {h}, encoder.options_from_cli({opts!r} + ' --threads 4')) as e:
+    for y, u, v in frames:
+        d, _ = e.encode(e.picture(y, u, v))
+        if d: md5.update(d); out += 1
+    while out < {n}:
+        d, _ = e.encode(None)
+        if d is None: break
+        md5.update(d); out += 1
+print(out, md5.hexdigest())
+"""
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, LD_PRELOAD=stub, KVZ_CUDA_MODE="batch"))
+    assert p.returncode == 0, p.stderr[-600:]
+    out, md5 = p.stdout.strip().splitlines()[-1].split()
+    assert int(out) == n and md5 == cli
