@@ -727,21 +727,30 @@ int ime_box_max_rows()
   return best;
 }
 
+typedef CUresult (*TmaEncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// the driver's cuTensorMapEncodeTiled, looked up once; null when this driver does not have it (then: cp.async staging)
+static TmaEncodeFn tma_encode_fn()
+{
+  static const TmaEncodeFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return reinterpret_cast<TmaEncodeFn>(p);
+  }();
+  return fn;
+}
+
 // The same launch with the raw tile rows fetched by TMA.  One tensor map per reference: the bordered
 // plane as a 2-D byte tensor {pitch, rows}, box {112 bytes, n_dy + 63 rows} (at most 256 rows per box: 240 here).
 static int launch_multi_tma(const ImeSadMulti &m, cudaStream_t stream)
 {
-  typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                               const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-  static EncodeFn encode = nullptr;
-  if (!encode) {
-    void *fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    KVZ_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-    if (!fn || qres != cudaDriverEntryPointSuccess) return fail_msg("ime_sad (TMA): cuTensorMapEncodeTiled is not available");
-    encode = reinterpret_cast<EncodeFn>(fn);
-  }
+  const TmaEncodeFn encode = tma_encode_fn();
+  if (!encode) return fail_msg("ime_sad (TMA): cuTensorMapEncodeTiled is not available");
   ImeSadMultiTma t;
   t.m = m;
   size_t smem = 0;
@@ -794,7 +803,7 @@ int launch_ime_sad_box_multi(const ImeSadParams *ps, const int (*boxes)[4], int 
   // raw tile rows by TMA (stage_tile_tma; measured 2 % faster than the cp.async staging at 1080p) whenever every
   // plane can be described by a tensor map: base and pitch multiples of 16 bytes.  KVZ_CUDA_SAD_TMA=0: cp.async.
   static const bool allow_tma = !(getenv("KVZ_CUDA_SAD_TMA") && atoi(getenv("KVZ_CUDA_SAD_TMA")) == 0);
-  bool use_tma = allow_tma;
+  bool use_tma = allow_tma && tma_encode_fn() != nullptr;
   for (int r = 0; r < n; r++)
     use_tma = use_tma && !(reinterpret_cast<uintptr_t>(m.p[r].ref) & 15) && !(m.p[r].ref_pitch & 15) && Geo(m.p[r].n_dy).rows <= 256;
   if (use_tma) return launch_multi_tma(m, stream);
